@@ -1,0 +1,639 @@
+// api.cu -- C ABI of libstitch_b200.so (include/stitch_b200.h): contexts, jobs,
+// tile upload, binning, kernel launches, band download.  Host-side C++ only
+// orchestrates; every pixel is touched by the CUDA kernels in decode.cu,
+// compose.cu, fused.cu and jpeg.cu.  There is deliberately no CPU fallback.
+#include "../../include/stitch_b200.h"
+#include "common.cuh"
+#include "kernels.h"
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace stitch;
+
+// ---------------------------------------------------------------------------
+struct stitch_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  int sm_count = 148;
+  std::string err;
+  cudaEvent_t ev[6] = {};
+  DevStatus *d_status = nullptr;   // device error word
+  DevStatus *h_status = nullptr;   // pinned mirror
+};
+
+struct TileRec {
+  stitch_tile_desc d;
+  uint8_t *d_src = nullptr;   // uploaded bytes (inflated stream or dense rows); owned unless external
+  bool src_external = false;
+  size_t src_len = 0;
+  uint8_t *d_pix = nullptr;   // dense unfiltered rows (== d_src for filtered==0)
+  uint32_t pitch = 0;
+  uint8_t *d_pass = nullptr;  // Adam7 pass scratch
+  std::vector<UnfStream> streams;
+  bool has_a7 = false;
+  A7Image a7;
+  bool decoded = false;
+};
+
+struct stitch_job {
+  stitch_ctx *ctx = nullptr;
+  stitch_job_desc desc;
+  uint32_t bpp = 4;  // output bytes per pixel
+  std::vector<TileRec> tiles;
+  bool finalized = false;
+  // device-side job state
+  DevTile *d_tiles = nullptr;
+  uint32_t *d_bin_start = nullptr, *d_bin_tiles = nullptr;
+  UnfStream *d_streams = nullptr; size_t streams_cap = 0;
+  A7Image *d_a7 = nullptr; size_t a7_cap = 0;
+  uint32_t bins_x = 0, bins_y = 0, bin_w_log2 = 6, bin_h_log2 = 4, bin_y_origin = 0;
+  // band buffers
+  uint8_t *d_canvas = nullptr; size_t canvas_bytes = 0; size_t canvas_pitch = 0;
+  uint8_t *d_out = nullptr; size_t out_bytes = 0;
+  size_t out_pitch = 0, out_lead = 0, out_row_bytes = 0;
+  uint32_t last_y0 = 0, last_y1 = 0;
+  int status = STITCH_OK;
+};
+
+static int fail(stitch_ctx *ctx, int code, const char *fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  if (ctx) ctx->err = buf;
+  return code;
+}
+
+#define CK(call)                                                                         \
+  do {                                                                                   \
+    cudaError_t e_ = (call);                                                             \
+    if (e_ != cudaSuccess)                                                               \
+      return fail(ctx, e_ == cudaErrorMemoryAllocation ? STITCH_E_NOMEM : STITCH_E_CUDA, \
+                  "CUDA error %s at %s:%d (%s)", cudaGetErrorName(e_), __FILE__, __LINE__, cudaGetErrorString(e_)); \
+  } while (0)
+
+static inline size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+static int samples_per_pixel(uint32_t ct) {
+  switch (ct) { case 0: return 1; case 2: return 3; case 3: return 1; case 4: return 2; case 6: return 4; default: return -1; }
+}
+static size_t scanline_bytes(uint32_t w, uint32_t bd, uint32_t ct) {
+  return (size_t)(((uint64_t)w * bd * (uint64_t)samples_per_pixel(ct) + 7) / 8);
+}
+
+static int dev_alloc(stitch_ctx *ctx, void **p, size_t bytes) {
+  CK(cudaMallocAsync(p, bytes ? bytes : 16, ctx->stream));
+  return STITCH_OK;
+}
+static void dev_free(stitch_ctx *ctx, void *p) {
+  if (p) cudaFreeAsync(p, ctx->stream);
+}
+
+// ---------------------------------------------------------------------------
+extern "C" int stitch_abi_version(void) { return STITCH_ABI_VERSION; }
+
+extern "C" int stitch_ctx_create(int device_id, stitch_ctx **out) {
+  if (!out) return STITCH_E_INVALID;
+  *out = nullptr;
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n <= 0 || device_id < 0 || device_id >= n) {
+    cudaGetLastError();
+    return STITCH_E_NODEVICE;
+  }
+  stitch_ctx *ctx = new stitch_ctx();
+  ctx->device = device_id;
+  if (cudaSetDevice(device_id) != cudaSuccess) { delete ctx; return STITCH_E_NODEVICE; }
+  cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device_id);
+  if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return STITCH_E_CUDA; }
+  ctx->own_stream = true;
+  for (auto &ev : ctx->ev) cudaEventCreate(&ev);
+  // keep freed device memory cached in the pool: jobs reuse it without new cudaMalloc calls
+  cudaMemPool_t pool;
+  if (cudaDeviceGetDefaultMemPool(&pool, device_id) == cudaSuccess) {
+    uint64_t thr = UINT64_MAX;
+    cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+  }
+  cudaMalloc((void **)&ctx->d_status, sizeof(DevStatus));
+  cudaHostAlloc((void **)&ctx->h_status, sizeof(DevStatus), cudaHostAllocDefault);
+  if (!ctx->d_status || !ctx->h_status) { delete ctx; return STITCH_E_NOMEM; }
+  *out = ctx;
+  return STITCH_OK;
+}
+
+extern "C" void stitch_ctx_destroy(stitch_ctx *ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  for (auto &ev : ctx->ev) if (ev) cudaEventDestroy(ev);
+  if (ctx->d_status) cudaFree(ctx->d_status);
+  if (ctx->h_status) cudaFreeHost(ctx->h_status);
+  if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
+  delete ctx;
+}
+
+extern "C" int stitch_ctx_set_stream(stitch_ctx *ctx, void *cuda_stream) {
+  if (!ctx) return STITCH_E_INVALID;
+  cudaSetDevice(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
+  ctx->stream = (cudaStream_t)cuda_stream;
+  ctx->own_stream = false;
+  return STITCH_OK;
+}
+
+extern "C" const char *stitch_last_error(const stitch_ctx *ctx) { return ctx ? ctx->err.c_str() : "no context"; }
+
+// ---------------------------------------------------------------------------
+extern "C" int stitch_job_create(stitch_ctx *ctx, const stitch_job_desc *desc, stitch_job **out) {
+  if (!ctx || !desc || !out) return STITCH_E_INVALID;
+  *out = nullptr;
+  if (desc->canvas_w == 0 || desc->canvas_h == 0) return fail(ctx, STITCH_E_INVALID, "Invalid dimensions: %ux%u", desc->canvas_w, desc->canvas_h);
+  if (desc->out_bit_depth != 8 && desc->out_bit_depth != 16) return fail(ctx, STITCH_E_INVALID, "out_bit_depth must be 8 or 16");
+  if (desc->out_kind > STITCH_OUT_JPEG_ENTROPY) return fail(ctx, STITCH_E_INVALID, "unknown out_kind %u", desc->out_kind);
+  if (desc->out_kind == STITCH_OUT_JPEG_ENTROPY) {
+    if (desc->out_bit_depth != 8) return fail(ctx, STITCH_E_INVALID, "JPEG output requires 8-bit RGBA");
+    if (desc->jpeg_quality < 1 || desc->jpeg_quality > 100)
+      return fail(ctx, STITCH_E_INVALID, "Invalid quality: %u (must be 1-100)", desc->jpeg_quality);
+  }
+  if ((uint64_t)desc->canvas_w * (desc->out_bit_depth == 16 ? 8 : 4) >= (1ull << 25))
+    return fail(ctx, STITCH_E_INVALID, "canvas rows above 32 MiB are not supported");
+  stitch_job *job = new stitch_job();
+  job->ctx = ctx;
+  job->desc = *desc;
+  if (job->desc.band_y1 == 0 || job->desc.band_y1 > desc->canvas_h) { job->desc.band_y0 = 0; job->desc.band_y1 = desc->canvas_h; }
+  if (job->desc.band_y0 >= job->desc.band_y1) { delete job; return fail(ctx, STITCH_E_INVALID, "empty band"); }
+  job->bpp = desc->out_bit_depth == 16 ? 8 : 4;
+  cudaSetDevice(ctx->device);
+  *out = job;
+  return STITCH_OK;
+}
+
+static void free_tile(stitch_ctx *ctx, TileRec &t) {
+  if (t.d_pix && t.d_pix != t.d_src) dev_free(ctx, t.d_pix);
+  if (t.d_src && !t.src_external) dev_free(ctx, t.d_src);
+  dev_free(ctx, t.d_pass);
+  t.d_pix = t.d_src = t.d_pass = nullptr;
+}
+
+extern "C" void stitch_job_destroy(stitch_job *job) {
+  if (!job) return;
+  stitch_ctx *ctx = job->ctx;
+  cudaSetDevice(ctx->device);
+  for (auto &t : job->tiles) free_tile(ctx, t);
+  dev_free(ctx, job->d_tiles); dev_free(ctx, job->d_bin_start); dev_free(ctx, job->d_bin_tiles);
+  dev_free(ctx, job->d_streams); dev_free(ctx, job->d_a7);
+  dev_free(ctx, job->d_canvas); dev_free(ctx, job->d_out);
+  cudaStreamSynchronize(ctx->stream);
+  delete job;
+}
+
+// Adam7 geometry (src/adam7.ts:23-43)
+static const int A7_XS[7] = {0, 4, 0, 2, 0, 1, 0}, A7_YS[7] = {0, 0, 4, 0, 2, 0, 1};
+static const int A7_DX[7] = {8, 8, 4, 4, 2, 2, 1}, A7_DY[7] = {8, 8, 8, 4, 4, 2, 2};
+static uint32_t a7_extent(uint32_t dim, int start, int step) {
+  return (int64_t)dim <= start ? 0u : (uint32_t)(((int64_t)dim - start + step - 1) / step);
+}
+
+// Validates the descriptor and stream length the way the reference does while
+// reading, and prepares the unfilter chains.  d_src must already be set.
+static int prepare_tile(stitch_ctx *ctx, stitch_job *job, TileRec &t, uint32_t tile_no) {
+  const stitch_tile_desc &d = t.d;
+  const int spp = samples_per_pixel(d.color_type);
+  if (spp < 0 || d.color_type == 3 || src_fmt(d.color_type, d.bit_depth) == FMT_INVALID) {
+    if (d.color_type == 3 || spp < 0)  // pixel-ops.ts:609-611 (palette reaches convertScanline and throws)
+      return fail(ctx, STITCH_E_COLOR, "Unsupported source color type: %u", d.color_type);
+    return fail(ctx, STITCH_E_INVALID, "Unsupported bit depth %u for color type %u", d.bit_depth, d.color_type);
+  }
+  if (d.width == 0 || d.height == 0) return fail(ctx, STITCH_E_INVALID, "tile #%u has zero size", d.image_idx + 1);
+  if (d.vis_w && d.vis_h) {
+    if (d.dst_x < 0 || d.dst_y < 0 || (uint64_t)d.dst_x + d.vis_w > job->desc.canvas_w ||
+        (uint64_t)d.dst_y + d.vis_h > job->desc.canvas_h || (uint64_t)d.src_off_x + d.vis_w > d.width ||
+        (uint64_t)d.src_off_y + d.vis_h > d.height)
+      return fail(ctx, STITCH_E_INVALID, "tile #%u rectangle is outside the canvas or its source", d.image_idx + 1);
+  }
+  const size_t rb = scanline_bytes(d.width, d.bit_depth, d.color_type);
+  const uint32_t fbpp = (uint32_t)((spp * d.bit_depth + 7) / 8);
+  if (rb >= (1ull << 31)) return fail(ctx, STITCH_E_INVALID, "tile row too large");
+  t.streams.clear();
+  t.has_a7 = false;
+  if (!d.filtered) {
+    if (t.src_len < rb * d.height)  // image-concat-core.ts:427-448 (decoder ended early / wrong row length)
+      return fail(ctx, STITCH_E_TRUNCATED, "Expected %u scanlines, decoded %zu", d.height, rb ? t.src_len / rb : 0);
+    t.d_pix = t.d_src;
+    t.pitch = (uint32_t)rb;
+    t.decoded = true;
+    return STITCH_OK;
+  }
+  t.pitch = (uint32_t)round_up(rb, 16);
+  if (!d.interlace) {
+    if (t.src_len < (rb + 1) * (size_t)d.height)  // png-decoder.ts:209-211
+      return fail(ctx, STITCH_E_TRUNCATED, "Expected %u scanlines, decoded %zu", d.height, t.src_len / (rb + 1));
+    int rc = dev_alloc(ctx, (void **)&t.d_pix, (size_t)t.pitch * d.height);
+    if (rc) return rc;
+    UnfStream s{};
+    s.src = t.d_src; s.dst = t.d_pix; s.src_stride = (uint32_t)rb + 1; s.row_bytes = (uint32_t)rb;
+    s.dst_pitch = t.pitch; s.rows = d.height; s.bpp = fbpp; s.last_row_bytes = (uint32_t)rb;
+    s.tile = tile_no; s.pass = 0;
+    t.streams.push_back(s);
+    return STITCH_OK;
+  }
+  // Adam7: walk the passes exactly like deinterlaceAdam7 (adam7.ts:61-107)
+  size_t off = 0, scratch = 0;
+  size_t pass_off[7], pass_scr[7];
+  uint32_t pw[7], ph[7], prb[7], ppitch[7];
+  uint32_t last_avail[7];
+  for (int p = 0; p < 7; p++) {
+    pw[p] = a7_extent(d.width, A7_XS[p], A7_DX[p]);
+    ph[p] = a7_extent(d.height, A7_YS[p], A7_DY[p]);
+    prb[p] = (uint32_t)(((uint64_t)pw[p] * d.bit_depth * spp + 7) / 8);
+    ppitch[p] = (uint32_t)round_up(prb[p], 16);
+    pass_off[p] = off; pass_scr[p] = scratch; last_avail[p] = prb[p];
+    if (pw[p] == 0 || ph[p] == 0) { pw[p] = ph[p] = 0; continue; }  // adam7.ts:68-70
+    for (uint32_t y = 0; y < ph[p]; y++) {
+      if (off >= t.src_len)  // adam7.ts:79-82
+        return fail(ctx, STITCH_E_TRUNCATED, "Unexpected end of decompressed data at pass %d, line %u", p + 1, y);
+      off += 1;
+      const size_t avail = std::min((size_t)prb[p], t.src_len - off);  // :87-88 slice shortens the last line
+      if (y == ph[p] - 1) last_avail[p] = (uint32_t)avail;
+      else if (avail < prb[p]) {  // a short line that is not the stream's last: the next line read throws
+        return fail(ctx, STITCH_E_TRUNCATED, "Unexpected end of decompressed data at pass %d, line %u", p + 1, y + 1);
+      }
+      off += avail;
+    }
+    scratch += (size_t)ppitch[p] * ph[p];
+  }
+  int rc = dev_alloc(ctx, (void **)&t.d_pass, scratch + 16);
+  if (rc) return rc;
+  rc = dev_alloc(ctx, (void **)&t.d_pix, (size_t)t.pitch * d.height);
+  if (rc) return rc;
+  memset(&t.a7, 0, sizeof t.a7);
+  for (int p = 0; p < 7; p++) {
+    t.a7.pass_pix[p] = t.d_pass + pass_scr[p];
+    t.a7.pass_pitch[p] = ppitch[p]; t.a7.pass_w[p] = pw[p]; t.a7.pass_h[p] = ph[p];
+    if (!pw[p] || !ph[p]) continue;
+    UnfStream s{};
+    s.src = t.d_src + pass_off[p]; s.dst = t.d_pass + pass_scr[p]; s.src_stride = prb[p] + 1; s.row_bytes = prb[p];
+    s.dst_pitch = ppitch[p]; s.rows = ph[p]; s.bpp = fbpp; s.last_row_bytes = last_avail[p];
+    s.tile = tile_no; s.pass = (uint32_t)p + 1;
+    t.streams.push_back(s);
+  }
+  t.a7.dst = t.d_pix; t.a7.dst_pitch = t.pitch; t.a7.width = d.width; t.a7.height = d.height;
+  t.a7.bit_depth = d.bit_depth; t.a7.bpp = fbpp; t.a7.row_bytes = (uint32_t)rb;
+  t.has_a7 = true;
+  return STITCH_OK;
+}
+
+static int add_tile_common(stitch_job *job, const stitch_tile_desc *tile, const uint8_t *host, const void *dev, size_t len) {
+  if (!job || !tile || (!host && !dev && len)) return STITCH_E_INVALID;
+  stitch_ctx *ctx = job->ctx;
+  cudaSetDevice(ctx->device);
+  TileRec t;
+  t.d = *tile;
+  t.src_len = len;
+  if (dev) {
+    t.d_src = (uint8_t *)dev;
+    t.src_external = true;
+  } else {
+    // +32: the unfilter kernel may read a few bytes past a row with vector loads
+    int rc = dev_alloc(ctx, (void **)&t.d_src, round_up(len, 16) + 32);
+    if (rc) return rc;
+  }
+  int rc = prepare_tile(ctx, job, t, (uint32_t)job->tiles.size());
+  if (rc) { free_tile(ctx, t); return rc; }
+  if (host && len) {
+    cudaError_t e = cudaMemcpyAsync(t.d_src, host, len, cudaMemcpyHostToDevice, ctx->stream);
+    if (e != cudaSuccess) { free_tile(ctx, t); return fail(ctx, STITCH_E_CUDA, "H2D failed: %s", cudaGetErrorString(e)); }
+  }
+  job->tiles.push_back(std::move(t));
+  job->finalized = false;
+  return STITCH_OK;
+}
+
+extern "C" int stitch_job_add_tile(stitch_job *job, const stitch_tile_desc *tile, const uint8_t *data, size_t len) {
+  return add_tile_common(job, tile, data, nullptr, len);
+}
+extern "C" int stitch_job_add_tile_device(stitch_job *job, const stitch_tile_desc *tile, const void *device_data, size_t len) {
+  if (((uintptr_t)device_data & 15u) != 0) return fail(job ? job->ctx : nullptr, STITCH_E_INVALID, "device_data must be 16-byte aligned");
+  return add_tile_common(job, tile, nullptr, device_data, len);
+}
+
+// ---------------------------------------------------------------------------
+template <class T>
+static int upload_array(stitch_ctx *ctx, const std::vector<T> &v, T **d_ptr, size_t *cap) {
+  if (v.size() > *cap) {
+    dev_free(ctx, *d_ptr);
+    *d_ptr = nullptr;
+    *cap = 0;
+    int rc = dev_alloc(ctx, (void **)d_ptr, v.size() * sizeof(T));
+    if (rc) return rc;
+    *cap = v.size();
+  }
+  if (!v.empty()) CK(cudaMemcpyAsync(*d_ptr, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
+  return STITCH_OK;
+}
+
+static int reset_status(stitch_ctx *ctx) {
+  CK(cudaMemsetAsync(ctx->d_status, 0xff, sizeof(DevStatus), ctx->stream));
+  return STITCH_OK;
+}
+
+// Reads the device error word (stream must be synchronised by the caller).
+static int check_status(stitch_ctx *ctx, stitch_job *job) {
+  const unsigned long long e = ctx->h_status->first_error;
+  if (e == ~0ull) return STITCH_OK;
+  const uint32_t ft = (uint32_t)(e & 0xffu);
+  if (job) job->status = STITCH_E_FILTER;
+  return fail(ctx, STITCH_E_FILTER, "Unknown filter type: %u", ft);  // png-filter.ts:78-79
+}
+
+static int decode_tiles(stitch_job *job, int force, uint32_t *launches) {
+  stitch_ctx *ctx = job->ctx;
+  std::vector<UnfStream> streams;
+  std::vector<A7Image> a7;
+  uint32_t a7_max_rb = 0, a7_max_h = 0;
+  for (auto &t : job->tiles) {
+    if (!t.d.filtered) continue;
+    if (t.decoded && !force) continue;
+    for (auto &s : t.streams) streams.push_back(s);
+    if (t.has_a7) {
+      a7.push_back(t.a7);
+      a7_max_rb = std::max(a7_max_rb, t.a7.row_bytes);
+      a7_max_h = std::max(a7_max_h, t.a7.height);
+    }
+    t.decoded = true;
+  }
+  if (streams.empty()) return STITCH_OK;
+  // longest chains first: the grid is scheduled in order, so this trims the tail
+  std::stable_sort(streams.begin(), streams.end(), [](const UnfStream &a, const UnfStream &b) {
+    return (uint64_t)a.rows + a.row_bytes / a.bpp > (uint64_t)b.rows + b.row_bytes / b.bpp;
+  });
+  int rc = upload_array(ctx, streams, &job->d_streams, &job->streams_cap);
+  if (rc) return rc;
+  CK(launch_unfilter(job->d_streams, (uint32_t)streams.size(), ctx->d_status, ctx->stream));
+  if (launches) (*launches)++;
+  if (!a7.empty()) {
+    rc = upload_array(ctx, a7, &job->d_a7, &job->a7_cap);
+    if (rc) return rc;
+    CK(launch_adam7_gather(job->d_a7, (uint32_t)a7.size(), a7_max_rb, a7_max_h, ctx->stream));
+    if (launches) (*launches)++;
+  }
+  return STITCH_OK;
+}
+
+extern "C" int stitch_job_decode(stitch_job *job, int force, stitch_timings *t) {
+  if (!job) return STITCH_E_INVALID;
+  stitch_ctx *ctx = job->ctx;
+  cudaSetDevice(ctx->device);
+  uint32_t launches = 0;
+  int rc = reset_status(ctx);
+  if (rc) return rc;
+  CK(cudaEventRecord(ctx->ev[0], ctx->stream));
+  rc = decode_tiles(job, force, &launches);
+  if (rc) return rc;
+  CK(cudaEventRecord(ctx->ev[1], ctx->stream));
+  CK(cudaMemcpyAsync(ctx->h_status, ctx->d_status, sizeof(DevStatus), cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  if (t) {
+    memset(t, 0, sizeof *t);
+    cudaEventElapsedTime(&t->decode_ms, ctx->ev[0], ctx->ev[1]);
+    t->total_ms = t->decode_ms;
+    t->launches = launches;
+  }
+  return check_status(ctx, job);
+}
+
+// Sort tiles back-to-front and bin their rectangles (positioned-layout.ts:201-242
+// builds a per-row list; a 2-D bin grid serves the same purpose for a GPU).
+static int finalize_job(stitch_job *job) {
+  stitch_ctx *ctx = job->ctx;
+  const stitch_job_desc &jd = job->desc;
+  std::vector<uint32_t> order;
+  for (uint32_t i = 0; i < job->tiles.size(); i++)
+    if (job->tiles[i].d.vis_w && job->tiles[i].d.vis_h) order.push_back(i);
+  std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) {
+    const stitch_tile_desc &x = job->tiles[a].d, &y = job->tiles[b].d;
+    if (x.z_index != y.z_index) return x.z_index < y.z_index;
+    return x.image_idx < y.image_idx;
+  });
+  std::vector<DevTile> dt(order.size());
+  for (size_t k = 0; k < order.size(); k++) {
+    const TileRec &t = job->tiles[order[k]];
+    DevTile &o = dt[k];
+    o.pix = t.d_pix; o.pitch = t.pitch; o.fmt = src_fmt(t.d.color_type, t.d.bit_depth);
+    o.x0 = t.d.dst_x; o.y0 = t.d.dst_y; o.x1 = t.d.dst_x + (int32_t)t.d.vis_w; o.y1 = t.d.dst_y + (int32_t)t.d.vis_h;
+    o.sx0 = (int32_t)t.d.src_off_x; o.sy0 = (int32_t)t.d.src_off_y;
+    o.opaque = (t.d.color_type == 0 || t.d.color_type == 2) ? 1u : 0u;
+    o.pad = 0;
+  }
+  // bins cover the job's band plus the halo row above it
+  const uint32_t ys = jd.band_y0 ? jd.band_y0 - 1 : 0;
+  const uint32_t bw = 1u << job->bin_w_log2, bh = 1u << job->bin_h_log2;
+  job->bin_y_origin = ys / bh * bh;
+  job->bins_x = (jd.canvas_w + bw - 1) / bw;
+  job->bins_y = (jd.band_y1 - job->bin_y_origin + bh - 1) / bh;
+  const size_t n_bins = (size_t)job->bins_x * job->bins_y;
+  std::vector<uint32_t> start(n_bins + 1, 0);
+  auto bin_range = [&](const DevTile &o, uint32_t &bx0, uint32_t &bx1, uint32_t &by0, uint32_t &by1) -> bool {
+    const int64_t ya = std::max<int64_t>(o.y0, job->bin_y_origin), yb = std::min<int64_t>(o.y1, jd.band_y1);
+    if (ya >= yb) return false;
+    bx0 = (uint32_t)o.x0 >> job->bin_w_log2; bx1 = ((uint32_t)o.x1 - 1) >> job->bin_w_log2;
+    by0 = (uint32_t)(ya - job->bin_y_origin) >> job->bin_h_log2; by1 = (uint32_t)(yb - 1 - job->bin_y_origin) >> job->bin_h_log2;
+    return true;
+  };
+  for (const DevTile &o : dt) {
+    uint32_t bx0, bx1, by0, by1;
+    if (!bin_range(o, bx0, bx1, by0, by1)) continue;
+    for (uint32_t by = by0; by <= by1; by++)
+      for (uint32_t bx = bx0; bx <= bx1; bx++) start[(size_t)by * job->bins_x + bx + 1]++;
+  }
+  for (size_t i = 0; i < n_bins; i++) start[i + 1] += start[i];
+  std::vector<uint32_t> fill(start.begin(), start.end() - 1), list(start[n_bins] ? start[n_bins] : 1);
+  for (uint32_t k = 0; k < dt.size(); k++) {
+    uint32_t bx0, bx1, by0, by1;
+    if (!bin_range(dt[k], bx0, bx1, by0, by1)) continue;
+    for (uint32_t by = by0; by <= by1; by++)
+      for (uint32_t bx = bx0; bx <= bx1; bx++) list[fill[(size_t)by * job->bins_x + bx]++] = k;
+  }
+  dev_free(ctx, job->d_tiles); dev_free(ctx, job->d_bin_start); dev_free(ctx, job->d_bin_tiles);
+  job->d_tiles = nullptr; job->d_bin_start = nullptr; job->d_bin_tiles = nullptr;
+  int rc;
+  if ((rc = dev_alloc(ctx, (void **)&job->d_tiles, dt.size() * sizeof(DevTile)))) return rc;
+  if ((rc = dev_alloc(ctx, (void **)&job->d_bin_start, start.size() * sizeof(uint32_t)))) return rc;
+  if ((rc = dev_alloc(ctx, (void **)&job->d_bin_tiles, list.size() * sizeof(uint32_t)))) return rc;
+  if (!dt.empty()) CK(cudaMemcpyAsync(job->d_tiles, dt.data(), dt.size() * sizeof(DevTile), cudaMemcpyHostToDevice, ctx->stream));
+  CK(cudaMemcpyAsync(job->d_bin_start, start.data(), start.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+  CK(cudaMemcpyAsync(job->d_bin_tiles, list.data(), list.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+  // the host vectors are pageable: the async copies above have already staged them
+  CK(cudaStreamSynchronize(ctx->stream));
+  job->finalized = true;
+  return STITCH_OK;
+}
+
+static int ensure_buffer(stitch_ctx *ctx, uint8_t **p, size_t *have, size_t need) {
+  if (need <= *have) return STITCH_OK;
+  dev_free(ctx, *p);
+  *p = nullptr; *have = 0;
+  int rc = dev_alloc(ctx, (void **)p, need);
+  if (rc) return rc;
+  *have = need;
+  return STITCH_OK;
+}
+
+static void bg_words(const stitch_job_desc &d, uint32_t &lo, uint32_t &hi) {
+  memcpy(&lo, d.background, 4);
+  memcpy(&hi, d.background + 4, 4);
+  if (d.out_bit_depth != 16) hi = 0;
+}
+
+extern "C" int stitch_job_run_band(stitch_job *job, uint32_t y0, uint32_t y1, uint8_t *out, size_t cap,
+                                   size_t *out_len, stitch_timings *tm) {
+  if (!job) return STITCH_E_INVALID;
+  stitch_ctx *ctx = job->ctx;
+  const stitch_job_desc &jd = job->desc;
+  cudaSetDevice(ctx->device);
+  if (out_len) *out_len = 0;
+  if (y0 >= y1 || y0 < jd.band_y0 || y1 > jd.band_y1)
+    return fail(ctx, STITCH_E_INVALID, "rows [%u,%u) are outside the job's band [%u,%u)", y0, y1, jd.band_y0, jd.band_y1);
+  if (jd.out_kind == STITCH_OUT_JPEG_ENTROPY) return stitch_jpeg_run_band(job, y0, y1, out, cap, out_len, tm);
+  const size_t row_bytes = (size_t)jd.canvas_w * job->bpp;
+  const uint32_t n_rows = y1 - y0;
+  const bool png = jd.out_kind == STITCH_OUT_PNG_FILTERED;
+  const size_t host_row = row_bytes + (png ? 1 : 0);
+  if (out && cap < host_row * n_rows) return fail(ctx, STITCH_E_CAPACITY, "output buffer too small: need %zu bytes", host_row * n_rows);
+
+  uint32_t launches = 0;
+  int rc = reset_status(ctx);
+  if (rc) return rc;
+  CK(cudaEventRecord(ctx->ev[0], ctx->stream));  // pending H2D copies are already queued on the stream
+  CK(cudaEventRecord(ctx->ev[1], ctx->stream));
+  if ((rc = decode_tiles(job, 0, &launches))) return rc;
+  CK(cudaEventRecord(ctx->ev[2], ctx->stream));
+  if (!job->finalized && (rc = finalize_job(job))) return rc;
+
+  ComposeParams cp{};
+  cp.tiles = job->d_tiles; cp.bin_start = job->d_bin_start; cp.bin_tiles = job->d_bin_tiles;
+  cp.bins_x = job->bins_x; cp.bin_w_log2 = job->bin_w_log2; cp.bin_h_log2 = job->bin_h_log2;
+  cp.bin_y_origin = job->bin_y_origin; cp.canvas_w = jd.canvas_w; cp.alpha_blend = jd.alpha_blend;
+  bg_words(jd, cp.bg_lo, cp.bg_hi);
+
+  const size_t pitch16 = round_up(row_bytes, 16);
+  if (png) {
+    const uint32_t ys = y0 ? y0 - 1 : 0;  // 1-row halo: the predictor row is recomputed, not exchanged
+    job->canvas_pitch = pitch16;
+    if ((rc = ensure_buffer(ctx, &job->d_canvas, &job->canvas_bytes, pitch16 * (size_t)(y1 - ys)))) return rc;
+    job->out_pitch = 16 + pitch16; job->out_lead = 15; job->out_row_bytes = host_row;
+    if ((rc = ensure_buffer(ctx, &job->d_out, &job->out_bytes, job->out_pitch * (size_t)n_rows))) return rc;
+    cp.y_begin = ys; cp.y_end = y1; cp.out = job->d_canvas; cp.out_pitch = pitch16;
+    CK(launch_compose(cp, jd.out_bit_depth == 16, ctx->stream));
+    FilterParams fp{};
+    fp.rows = job->d_canvas + (size_t)(y0 - ys) * pitch16; fp.in_pitch = pitch16;
+    fp.prev0 = y0 ? job->d_canvas : nullptr;
+    fp.n_rows = n_rows; fp.row_bytes = (uint32_t)row_bytes; fp.bpp = job->bpp;
+    fp.out = job->d_out; fp.out_pitch = job->out_pitch; fp.lead = (uint32_t)job->out_lead;
+    CK(launch_filter_rows(fp, ctx->stream));
+    launches += 2;
+  } else {
+    job->out_pitch = pitch16; job->out_lead = 0; job->out_row_bytes = host_row;
+    if ((rc = ensure_buffer(ctx, &job->d_out, &job->out_bytes, pitch16 * (size_t)n_rows))) return rc;
+    cp.y_begin = y0; cp.y_end = y1; cp.out = job->d_out; cp.out_pitch = pitch16;
+    CK(launch_compose(cp, jd.out_bit_depth == 16, ctx->stream));
+    launches += 1;
+  }
+  CK(cudaEventRecord(ctx->ev[3], ctx->stream));
+  if (out) {
+    CK(cudaMemcpy2DAsync(out, host_row, job->d_out + job->out_lead, job->out_pitch, host_row, n_rows,
+                         cudaMemcpyDeviceToHost, ctx->stream));
+    if (out_len) *out_len = host_row * n_rows;
+  }
+  CK(cudaEventRecord(ctx->ev[4], ctx->stream));
+  CK(cudaMemcpyAsync(ctx->h_status, ctx->d_status, sizeof(DevStatus), cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  job->last_y0 = y0; job->last_y1 = y1;
+  if (tm) {
+    memset(tm, 0, sizeof *tm);
+    cudaEventElapsedTime(&tm->h2d_ms, ctx->ev[0], ctx->ev[1]);
+    cudaEventElapsedTime(&tm->decode_ms, ctx->ev[1], ctx->ev[2]);
+    cudaEventElapsedTime(&tm->compose_ms, ctx->ev[2], ctx->ev[3]);
+    cudaEventElapsedTime(&tm->d2h_ms, ctx->ev[3], ctx->ev[4]);
+    cudaEventElapsedTime(&tm->total_ms, ctx->ev[0], ctx->ev[4]);
+    tm->launches = launches;
+  }
+  return check_status(ctx, job);
+}
+
+extern "C" int stitch_job_band_device(stitch_job *job, void **ptr, size_t *pitch, size_t *lead, size_t *row_bytes) {
+  if (!job || !job->d_out) return STITCH_E_STATE;
+  if (ptr) *ptr = job->d_out;
+  if (pitch) *pitch = job->out_pitch;
+  if (lead) *lead = job->out_lead;
+  if (row_bytes) *row_bytes = job->out_row_bytes;
+  return STITCH_OK;
+}
+
+extern "C" int stitch_job_status(stitch_job *job) { return job ? job->status : STITCH_E_INVALID; }
+
+// ---------------------------------------------------------------------------
+extern "C" int stitch_decode_image(stitch_ctx *ctx, const stitch_tile_desc *tile, const uint8_t *data, size_t len,
+                                   uint8_t *out, size_t cap, size_t *out_len) {
+  if (!ctx || !tile || !out) return STITCH_E_INVALID;
+  if (out_len) *out_len = 0;
+  stitch_job_desc jd{};
+  jd.canvas_w = std::max(1u, tile->width); jd.canvas_h = std::max(1u, tile->height);
+  jd.out_bit_depth = 8; jd.out_kind = STITCH_OUT_RAW_RGBA;
+  stitch_job *job = nullptr;
+  int rc = stitch_job_create(ctx, &jd, &job);
+  if (rc) return rc;
+  stitch_tile_desc td = *tile;
+  td.dst_x = td.dst_y = 0; td.src_off_x = td.src_off_y = 0; td.vis_w = td.width; td.vis_h = td.height;
+  rc = stitch_job_add_tile(job, &td, data, len);
+  if (!rc) rc = stitch_job_decode(job, 0, nullptr);
+  if (!rc) {
+    const TileRec &t = job->tiles[0];
+    const size_t rb = scanline_bytes(td.width, td.bit_depth, td.color_type);
+    if (cap < rb * td.height) rc = fail(ctx, STITCH_E_CAPACITY, "output buffer too small: need %zu bytes", rb * td.height);
+    else {
+      cudaError_t e = cudaMemcpy2DAsync(out, rb, t.d_pix, t.pitch, rb, td.height, cudaMemcpyDeviceToHost, ctx->stream);
+      if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+      if (e != cudaSuccess) rc = fail(ctx, STITCH_E_CUDA, "D2H failed: %s", cudaGetErrorString(e));
+      else if (out_len) *out_len = rb * td.height;
+    }
+  }
+  stitch_job_destroy(job);
+  return rc;
+}
+
+extern "C" int stitch_filter_rows(stitch_ctx *ctx, const uint8_t *rows, const uint8_t *prev_row, uint32_t n_rows,
+                                  size_t row_bytes, uint32_t bpp, uint8_t *out, size_t cap) {
+  if (!ctx || !rows || !out || !n_rows || !row_bytes || !bpp) return STITCH_E_INVALID;
+  if (cap < (row_bytes + 1) * n_rows) return fail(ctx, STITCH_E_CAPACITY, "output buffer too small");
+  if (row_bytes >= (1ull << 25)) return fail(ctx, STITCH_E_INVALID, "rows above 32 MiB are not supported");
+  cudaSetDevice(ctx->device);
+  const size_t pitch = round_up(row_bytes, 16), opitch = 16 + pitch;
+  uint8_t *d_in = nullptr, *d_out = nullptr;
+  int rc = dev_alloc(ctx, (void **)&d_in, pitch * ((size_t)n_rows + 1));
+  if (rc) return rc;
+  rc = dev_alloc(ctx, (void **)&d_out, opitch * n_rows);
+  if (rc) { dev_free(ctx, d_in); return rc; }
+  cudaError_t e = cudaSuccess;
+  if (prev_row) e = cudaMemcpyAsync(d_in, prev_row, row_bytes, cudaMemcpyHostToDevice, ctx->stream);
+  if (e == cudaSuccess)
+    e = cudaMemcpy2DAsync(d_in + pitch, pitch, rows, row_bytes, row_bytes, n_rows, cudaMemcpyHostToDevice, ctx->stream);
+  FilterParams fp{};
+  fp.rows = d_in + pitch; fp.in_pitch = pitch; fp.prev0 = prev_row ? d_in : nullptr; fp.n_rows = n_rows;
+  fp.row_bytes = (uint32_t)row_bytes; fp.bpp = bpp; fp.out = d_out; fp.out_pitch = opitch; fp.lead = 15;
+  if (e == cudaSuccess) e = launch_filter_rows(fp, ctx->stream);
+  if (e == cudaSuccess)
+    e = cudaMemcpy2DAsync(out, row_bytes + 1, d_out + 15, opitch, row_bytes + 1, n_rows, cudaMemcpyDeviceToHost, ctx->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+  dev_free(ctx, d_in); dev_free(ctx, d_out);
+  if (e != cudaSuccess) return fail(ctx, STITCH_E_CUDA, "filter_rows failed: %s", cudaGetErrorString(e));
+  return STITCH_OK;
+}

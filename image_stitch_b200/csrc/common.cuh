@@ -1,0 +1,233 @@
+// common.cuh -- shared device structs and per-pixel device functions.
+// sm_100a only.  Reference citations are relative to jburnhams/image-stitch v1.1.53.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace stitch {
+
+// ---- source pixel formats (colour type x bit depth the reference accepts) ----
+enum SrcFmt : uint32_t {
+  FMT_RGBA8 = 0, FMT_RGB8, FMT_GA8, FMT_G8, FMT_G4, FMT_G2, FMT_G1,
+  FMT_RGBA16, FMT_RGB16, FMT_GA16, FMT_G16, FMT_INVALID
+};
+
+__host__ __device__ inline uint32_t src_fmt(uint32_t color_type, uint32_t bit_depth) {
+  switch (color_type) {
+    case 6: return bit_depth == 8 ? FMT_RGBA8 : bit_depth == 16 ? FMT_RGBA16 : FMT_INVALID;
+    case 2: return bit_depth == 8 ? FMT_RGB8 : bit_depth == 16 ? FMT_RGB16 : FMT_INVALID;
+    case 4: return bit_depth == 8 ? FMT_GA8 : bit_depth == 16 ? FMT_GA16 : FMT_INVALID;
+    case 0:
+      switch (bit_depth) {
+        case 8: return FMT_G8; case 16: return FMT_G16; case 4: return FMT_G4;
+        case 2: return FMT_G2; case 1: return FMT_G1; default: return FMT_INVALID;
+      }
+    default: return FMT_INVALID;
+  }
+}
+
+// One placed input as the compose kernels see it (sorted by (z_index, image_idx)).
+struct DevTile {
+  const uint8_t *pix;  // dense unfiltered rows in SOURCE format
+  uint32_t pitch;      // bytes between rows
+  uint32_t fmt;        // SrcFmt
+  int32_t x0, y0;      // clipped top-left on the canvas
+  int32_t x1, y1;      // exclusive bottom-right on the canvas
+  int32_t sx0, sy0;    // source pixel that lands on (x0,y0): sourceOffsetX/Y
+  uint32_t opaque;     // 1: every pixel has alpha == max (no alpha channel, or verified by decode)
+  uint32_t pad;
+};
+
+// One dependency chain for kernel (a): a non-interlaced image or one Adam7 pass.
+struct UnfStream {
+  const uint8_t *src;      // first filter byte of the chain
+  uint8_t *dst;            // dense output rows
+  uint32_t src_stride;     // 1 + row_bytes
+  uint32_t row_bytes;
+  uint32_t dst_pitch;
+  uint32_t rows;
+  uint32_t bpp;            // filter distance: ceil(spp*bitDepth/8), png-filter.ts:186-211
+  uint32_t last_row_bytes; // bytes available for the final row (adam7.ts:87-88 slice semantics)
+  uint32_t tile;           // for error reports
+  uint32_t pass;           // 0 = not interlaced, 1..7 Adam7 pass
+};
+
+// Adam7 gather parameters for one interlaced image.
+struct A7Image {
+  const uint8_t *pass_pix[7];
+  uint32_t pass_pitch[7];
+  uint32_t pass_w[7], pass_h[7];
+  uint8_t *dst;
+  uint32_t dst_pitch;
+  uint32_t width, height;
+  uint32_t bit_depth, bpp;  // bpp in bytes (>=1)
+  uint32_t row_bytes;
+};
+
+// device error word: 0 = none, else (kind<<56 | tile<<24 | row/aux)
+struct DevStatus {
+  unsigned long long first_error;
+};
+
+// ---------------------------------------------------------------------------
+// convertScanline (src/pixel-ops.ts:496-633) for one pixel.
+// 16->8 uses Math.round(v*255/65535) == (v+128)/257 for all v (exhaustively
+// checked in tests/test_oracle_unit.py); n-bit -> 8 is v*255/(2^n-1) exactly.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t scale16to8(uint32_t v) { return (v + 128u) / 257u; }
+
+__device__ __forceinline__ uint32_t ld_be16(const uint8_t *p) { return ((uint32_t)p[0] << 8) | p[1]; }
+
+// Returns the pixel as RGBA8 in memory order (byte0=R ... byte3=A).
+__device__ __forceinline__ uint32_t fetch_rgba8(const DevTile &t, uint32_t sx, uint32_t sy) {
+  const uint8_t *row = t.pix + (size_t)sy * t.pitch;
+  switch (t.fmt) {
+    case FMT_RGBA8: return *reinterpret_cast<const uint32_t *>(row + 4u * sx);
+    case FMT_RGB8: {
+      const uint8_t *p = row + 3u * sx;
+      return (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | 0xFF000000u;
+    }
+    case FMT_GA8: {
+      uint32_t ga = *reinterpret_cast<const uint16_t *>(row + 2u * sx);
+      uint32_t g = ga & 0xFFu, a = ga >> 8;
+      return g * 0x010101u | (a << 24);
+    }
+    case FMT_G8: return (uint32_t)row[sx] * 0x010101u | 0xFF000000u;
+    case FMT_G4: {
+      uint32_t v = (row[sx >> 1] >> ((~sx & 1u) * 4u)) & 0xFu;
+      return (v * 17u) * 0x010101u | 0xFF000000u;
+    }
+    case FMT_G2: {
+      uint32_t v = (row[sx >> 2] >> ((~sx & 3u) * 2u)) & 0x3u;
+      return (v * 85u) * 0x010101u | 0xFF000000u;
+    }
+    case FMT_G1: {
+      uint32_t v = (row[sx >> 3] >> (~sx & 7u)) & 0x1u;
+      return (v * 255u) * 0x010101u | 0xFF000000u;
+    }
+    case FMT_RGBA16: {
+      const uint8_t *p = row + 8u * sx;
+      uint2 w = *reinterpret_cast<const uint2 *>(p);  // pitch and 8*sx keep this 8-byte aligned
+      uint32_t r = __byte_perm(w.x, 0, 0x4401), g = __byte_perm(w.x, 0, 0x4423);
+      uint32_t b = __byte_perm(w.y, 0, 0x4401), a = __byte_perm(w.y, 0, 0x4423);
+      return scale16to8(r) | (scale16to8(g) << 8) | (scale16to8(b) << 16) | (scale16to8(a) << 24);
+    }
+    case FMT_RGB16: {
+      const uint8_t *p = row + 6u * sx;
+      return scale16to8(ld_be16(p)) | (scale16to8(ld_be16(p + 2)) << 8) | (scale16to8(ld_be16(p + 4)) << 16) |
+             0xFF000000u;
+    }
+    case FMT_GA16: {
+      const uint8_t *p = row + 4u * sx;
+      uint32_t g = scale16to8(ld_be16(p)), a = scale16to8(ld_be16(p + 2));
+      return g * 0x010101u | (a << 24);
+    }
+    case FMT_G16: {
+      uint32_t g = scale16to8(ld_be16(row + 2u * sx));
+      return g * 0x010101u | 0xFF000000u;
+    }
+    default: return 0u;
+  }
+}
+
+// Returns the pixel as RGBA16 in memory order: x = bytes R_hi R_lo G_hi G_lo, y = B_hi B_lo A_hi A_lo.
+// 8->16 is Math.round(v*65535/255) == v*257, i.e. the byte repeated (pixel-ops.ts:312-326).
+__device__ __forceinline__ uint2 fetch_rgba16(const DevTile &t, uint32_t sx, uint32_t sy) {
+  const uint8_t *row = t.pix + (size_t)sy * t.pitch;
+  switch (t.fmt) {
+    case FMT_RGBA16: return *reinterpret_cast<const uint2 *>(row + 8u * sx);
+    case FMT_RGB16: {
+      const uint8_t *p = row + 6u * sx;
+      uint32_t x = (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24);
+      uint32_t y = (uint32_t)p[4] | ((uint32_t)p[5] << 8) | 0xFFFF0000u;
+      return make_uint2(x, y);
+    }
+    case FMT_GA16: {
+      uint32_t w = *reinterpret_cast<const uint32_t *>(row + 4u * sx);  // g_hi g_lo a_hi a_lo
+      uint32_t gg = __byte_perm(w, 0, 0x1010);
+      return make_uint2(gg, __byte_perm(w, 0, 0x3210) & 0xFFFF0000u | (gg & 0xFFFFu));
+    }
+    case FMT_G16: {
+      uint32_t g = *reinterpret_cast<const uint16_t *>(row + 2u * sx);
+      uint32_t gg = g | (g << 16);
+      return make_uint2(gg, (gg & 0xFFFFu) | 0xFFFF0000u);
+    }
+    default: {
+      uint32_t p8 = fetch_rgba8(t, sx, sy);  // every <=8-bit format: sample s -> bytes [s,s]
+      uint32_t x = __byte_perm(p8, 0, 0x1100);
+      uint32_t y = __byte_perm(p8, 0, 0x3322);
+      return make_uint2(x, y);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// compositeScanline (src/pixel-ops.ts:646-736) for one pixel, bit-exact:
+// IEEE doubles, the reference's association order, explicit round-to-nearest
+// intrinsics so that no FMA contraction can change a result.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t js_round_pos(double v) {  // Math.round for v >= 0
+  double r = floor(v);
+  return (uint32_t)r + ((__dsub_rn(v, r) >= 0.5) ? 1u : 0u);
+}
+
+__device__ __forceinline__ uint32_t blend8(uint32_t dst, uint32_t src) {
+  uint32_t sa = src >> 24;
+  if (sa == 255u) return src;  // srcAlpha >= 0.9999 <=> 255   (:707-711)
+  if (sa == 0u) return dst;    // srcAlpha > 0.0001 fails only for 0 (:712, :732)
+  double sA = __ddiv_rn((double)sa, 255.0);
+  double dA = __ddiv_rn((double)(dst >> 24), 255.0);
+  double om = __dsub_rn(1.0, sA);
+  double oA = __dadd_rn(sA, __dmul_rn(dA, om));  // :715
+  // oA >= sA >= 1/255 > 0.0001, so the :717 guard always passes here
+  uint32_t out = 0;
+#pragma unroll
+  for (int c = 0; c < 3; c++) {
+    double s = (double)((src >> (8 * c)) & 0xFFu), d = (double)((dst >> (8 * c)) & 0xFFu);
+    double v = __ddiv_rn(__dadd_rn(__dmul_rn(s, sA), __dmul_rn(__dmul_rn(d, dA), om)), oA);  // :722-723
+    v = v < 255.0 ? v : 255.0;
+    v = v > 0.0 ? v : 0.0;
+    out |= js_round_pos(v) << (8 * c);
+  }
+  out |= js_round_pos(__dmul_rn(oA, 255.0)) << 24;  // :728
+  return out;
+}
+
+__device__ __forceinline__ uint32_t be16_of(uint32_t w, int hi_half) {  // sample from the byte image
+  return hi_half ? __byte_perm(w, 0, 0x4423) : __byte_perm(w, 0, 0x4401);
+}
+__device__ __forceinline__ uint32_t to_be16(uint32_t v) { return ((v >> 8) & 0xFFu) | ((v & 0xFFu) << 8); }
+
+__device__ __forceinline__ uint2 blend16(uint2 dst, uint2 src) {
+  uint32_t sa = be16_of(src.y, 1);
+  // (sa/65535 >= 0.9999) <=> sa >= 65529 ; (sa/65535 > 0.0001) <=> sa >= 7  (:670-677)
+  if (sa >= 65529u) return src;
+  if (sa < 7u) return dst;
+  double sA = __ddiv_rn((double)sa, 65535.0);
+  double dA = __ddiv_rn((double)be16_of(dst.y, 1), 65535.0);
+  double om = __dsub_rn(1.0, sA);
+  double oA = __dadd_rn(sA, __dmul_rn(dA, om));
+  uint32_t ch[3];
+#pragma unroll
+  for (int c = 0; c < 3; c++) {
+    uint32_t sw = c < 2 ? src.x : src.y, dw = c < 2 ? dst.x : dst.y;
+    double s = (double)be16_of(sw, c & 1), d = (double)be16_of(dw, c & 1);
+    double v = __ddiv_rn(__dadd_rn(__dmul_rn(s, sA), __dmul_rn(__dmul_rn(d, dA), om)), oA);
+    v = v < 65535.0 ? v : 65535.0;
+    v = v > 0.0 ? v : 0.0;
+    ch[c] = js_round_pos(v);
+  }
+  uint32_t av = js_round_pos(__dmul_rn(oA, 65535.0));
+  return make_uint2(to_be16(ch[0]) | (to_be16(ch[1]) << 16), to_be16(ch[2]) | (to_be16(av) << 16));
+}
+
+// ---------------------------------------------------------------------------
+// PNG filter arithmetic on 4 packed bytes (src/png-filter.ts:16-25, :88-142)
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ int paeth1(int a, int b, int c) {
+  int p = a + b - c;
+  int pa = abs(p - a), pb = abs(p - b), pc = abs(p - c);
+  return (pa <= pb && pa <= pc) ? a : (pb <= pc ? b : c);
+}
+
+}  // namespace stitch

@@ -1,0 +1,45 @@
+// kernels.h -- launcher prototypes shared by the translation units of libstitch_b200.so
+#pragma once
+#include "common.cuh"
+
+struct stitch_job;
+struct stitch_timings;
+
+namespace stitch {
+
+struct ComposeParams {
+  const DevTile *tiles;       // sorted by (z_index, image_idx)
+  const uint32_t *bin_start;  // CSR over bins, bins_x * bins_y + 1 entries
+  const uint32_t *bin_tiles;  // tile indices, back to front within a bin
+  uint32_t bins_x, bin_w_log2, bin_h_log2;
+  uint32_t bin_y_origin;      // canvas row of bin row 0
+  uint32_t canvas_w;
+  uint32_t y_begin, y_end;    // canvas rows to produce
+  uint32_t alpha_blend;
+  uint32_t bg_lo, bg_hi;      // background pixel, memory order
+  uint8_t *out;               // row (y - y_begin) at out + (y - y_begin) * out_pitch
+  size_t out_pitch;
+};
+
+struct FilterParams {
+  const uint8_t *rows;   // raw rows; row r at rows + r*in_pitch
+  size_t in_pitch;
+  const uint8_t *prev0;  // raw row above row 0, or nullptr (previousLine === null)
+  uint32_t n_rows;
+  uint32_t row_bytes;
+  uint32_t bpp;
+  uint8_t *out;          // row r: filter byte at out + r*out_pitch + lead, data right after it
+  size_t out_pitch;
+  uint32_t lead;
+};
+
+cudaError_t launch_unfilter(const UnfStream *d_streams, uint32_t n_streams, DevStatus *d_status, cudaStream_t st);
+cudaError_t launch_adam7_gather(const A7Image *d_images, uint32_t n_images, uint32_t max_row_bytes,
+                                uint32_t max_height, cudaStream_t st);
+cudaError_t launch_compose(const ComposeParams &p, bool out16, cudaStream_t st);
+cudaError_t launch_filter_rows(const FilterParams &p, cudaStream_t st);
+
+}  // namespace stitch
+
+int stitch_jpeg_run_band(stitch_job *job, uint32_t y0, uint32_t y1, uint8_t *out, size_t cap, size_t *out_len,
+                         stitch_timings *tm);

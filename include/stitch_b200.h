@@ -1,0 +1,183 @@
+/*
+ * stitch_b200.h -- C ABI of libstitch_b200.so, the B200-native replacement for
+ * image-stitch's pixel pipeline (inflated scanlines in, filtered PNG scanlines
+ * / raw RGBA rows / entropy-coded JPEG MCUs out).
+ *
+ * The reference (jburnhams/image-stitch v1.1.53, TypeScript) has no FFI seam
+ * around this path: the functions below replace ordinary TS functions that the
+ * row generators call inline.  Each entry point names what it replaces
+ * (paths relative to the reference tree).  INTEGRATION.md shows the N-API
+ * addon and the Python/ctypes binding over this header.
+ *
+ * Conventions: every function returns STITCH_OK (0) or a negative
+ * stitch_status; stitch_last_error(ctx) returns the reference's own message
+ * text for that failure ("Unknown filter type: 9", "Unsupported source color
+ * type: 3", ...).  All pointers are plain host pointers unless the name says
+ * "device".  No torch / C++ types cross this boundary.
+ *
+ * Threading: calls on one ctx are serialised by the caller.  One ctx drives
+ * one CUDA device (one process per GPU; row bands of one canvas are spread
+ * over ranks by the host).
+ */
+#ifndef STITCH_B200_H
+#define STITCH_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define STITCH_ABI_VERSION 1
+
+typedef enum stitch_status {
+  STITCH_OK = 0,
+  STITCH_E_INVALID = -1,   /* bad argument / descriptor */
+  STITCH_E_CUDA = -2,      /* CUDA runtime failure (message carries cudaGetErrorString) */
+  STITCH_E_NOMEM = -3,
+  STITCH_E_FILTER = -4,    /* "Unknown filter type: N"            src/png-filter.ts:78-79 */
+  STITCH_E_COLOR = -5,     /* "Unsupported source color type: N"  src/pixel-ops.ts:609-611 */
+  STITCH_E_TRUNCATED = -6, /* "Expected H scanlines, decoded N" src/decoders/png-decoder.ts:209-211,
+                              "Unexpected end of decompressed data at pass P, line L" src/adam7.ts:80-82 */
+  STITCH_E_STATE = -7,     /* call order violated */
+  STITCH_E_CAPACITY = -8,  /* caller buffer too small */
+  STITCH_E_NODEVICE = -10  /* no CUDA device: there is no CPU fallback */
+} stitch_status;
+
+typedef enum stitch_out_kind {
+  STITCH_OUT_PNG_FILTERED = 0, /* rows of [filter byte + W*bpp]: filterScanline src/png-filter.ts:148-181 */
+  STITCH_OUT_RAW_RGBA = 1,     /* composited rows W*bpp: generateRawScanlines src/image-concat-core.ts:691-831 */
+  STITCH_OUT_JPEG_ENTROPY = 2  /* entropy-coded MCU rows: StreamingJpegEncoder.encode_strip, src/jpeg-encoder.ts:155-166 */
+} stitch_out_kind;
+
+typedef struct stitch_ctx stitch_ctx;
+typedef struct stitch_job stitch_job;
+
+/* One stitch job = one output canvas. Replaces the per-call state of
+ * CoreStreamingConcatenator.streamGridMode / streamPositionedMode
+ * (src/image-concat-core.ts:1008-1217). */
+typedef struct stitch_job_desc {
+  uint32_t canvas_w, canvas_h;
+  uint32_t out_bit_depth;  /* 8 | 16: determineCommonFormat src/pixel-ops.ts:293-307; forced 8 for JPEG */
+  uint32_t out_kind;       /* stitch_out_kind */
+  uint32_t alpha_blend;    /* 1: alpha-over (positioned default); 0: dest.set (grid mode, enableAlphaBlending:false) */
+  uint32_t jpeg_quality;   /* 1..100, JPEG only (src/jpeg-encoder.ts:109-114) */
+  uint8_t background[8];   /* one pixel in OUTPUT format: getTransparentColor src/pixel-ops.ts:255-287 */
+  uint32_t band_y0, band_y1; /* rows this job will ever be asked for (multi-GPU row band); 0,0 = whole canvas */
+  uint32_t reserved[4];
+} stitch_job_desc;
+
+/* One placed input. Produced by the host from calculateLayout
+ * (src/image-concat-core.ts:132-204) or clipImagesToCanvas
+ * (src/positioned-layout.ts:107-190). */
+typedef struct stitch_tile_desc {
+  uint32_t width, height;        /* source image size */
+  uint32_t bit_depth;            /* 1,2,4,8,16 */
+  uint32_t color_type;           /* 0,2,4,6 (3 = palette raises STITCH_E_COLOR like the reference) */
+  uint32_t interlace;            /* 1: Adam7 stream, src/adam7.ts:52-110 */
+  uint32_t filtered;             /* 1: data = inflated IDAT stream with filter bytes (src/decoders/png-decoder.ts:63-229)
+                                    0: data = dense unfiltered rows (foreign ImageDecoder.scanlines()) */
+  int32_t dst_x, dst_y;          /* clipped top-left on the canvas, >= 0 */
+  uint32_t src_off_x, src_off_y; /* ClippedImageInfo.sourceOffsetX/Y */
+  uint32_t vis_w, vis_h;         /* visible size after clipping */
+  int32_t z_index;               /* composite order key 1 (src/positioned-layout.ts:229-234) */
+  uint32_t image_idx;            /* composite order key 2, and the "#N" of error messages */
+} stitch_tile_desc;
+
+/* Per-call device timings (CUDA events on the ctx stream), milliseconds. */
+typedef struct stitch_timings {
+  float h2d_ms;       /* tile uploads still pending when the call started */
+  float decode_ms;    /* kernel (a): unfilter + Adam7 */
+  float compose_ms;   /* kernels (b)+(c) fused, or (b) then (c), or (b)+(d) */
+  float d2h_ms;       /* band download */
+  float total_ms;
+  uint32_t launches;  /* kernels launched by this call */
+  uint32_t reserved;
+} stitch_timings;
+
+/* JPEG band result header (STITCH_OUT_JPEG_ENTROPY).  The entropy bytes of a
+ * band are byte-aligned on their own (bit-padded with 1s at the end only when
+ * `final` is set); the host splices bands with stitch_jpeg_splice(). */
+typedef struct stitch_jpeg_band_info {
+  uint64_t n_bits;     /* entropy bits produced for this band before byte stuffing */
+  int32_t last_dc[3];  /* DC predictors after the band's last MCU (Y, Cb, Cr) */
+  uint32_t reserved;
+} stitch_jpeg_band_info;
+
+/* ---- context ------------------------------------------------------------ */
+
+/* device_id: CUDA ordinal.  Fails with STITCH_E_NODEVICE when no GPU is
+ * visible -- by design there is no CPU path behind this ABI. */
+int stitch_ctx_create(int device_id, stitch_ctx **out);
+void stitch_ctx_destroy(stitch_ctx *ctx);
+/* Use an existing cudaStream_t (e.g. torch's current stream) for all work. */
+int stitch_ctx_set_stream(stitch_ctx *ctx, void *cuda_stream);
+const char *stitch_last_error(const stitch_ctx *ctx);
+int stitch_abi_version(void);
+
+/* ---- job ---------------------------------------------------------------- */
+
+int stitch_job_create(stitch_ctx *ctx, const stitch_job_desc *desc, stitch_job **out);
+void stitch_job_destroy(stitch_job *job);
+
+/* Registers one input and starts its upload.  `data` is borrowed until the
+ * call returns (it is copied through a pinned staging ring).  Validates what
+ * the reference validates while reading: colour type (pixel-ops.ts:609-611),
+ * stream length (png-decoder.ts:209-211, adam7.ts:79-82); filter bytes are
+ * validated on the device by stitch_job_decode. */
+int stitch_job_add_tile(stitch_job *job, const stitch_tile_desc *tile, const uint8_t *data, size_t len);
+
+/* Same, but `device_data` already lives in this ctx's device memory (16-byte
+ * aligned, stays valid and unmodified until the job is destroyed). */
+int stitch_job_add_tile_device(stitch_job *job, const stitch_tile_desc *tile, const void *device_data, size_t len);
+
+/* Kernel (a): unfilterScanline (src/png-filter.ts:34-83) over every row of
+ * every pending tile + deinterlaceAdam7 (src/adam7.ts:52-110).  Idempotent
+ * unless `force` is set (bench: re-run with inputs resident in HBM). */
+int stitch_job_decode(stitch_job *job, int force, stitch_timings *t);
+
+/* Kernels (b)+(c) (PNG), (b) (RAW) or (b)+(d) (JPEG) for canvas rows
+ * [y0,y1): convertScanline (src/pixel-ops.ts:496-633), row assembly
+ * (src/image-concat-core.ts:404-545, :551-685), compositeScanline
+ * (src/pixel-ops.ts:646-736), filterScanline (src/png-filter.ts:148-181).
+ * Runs stitch_job_decode first when needed.
+ *  out != NULL: the band is copied to host memory `out` (cap bytes):
+ *      PNG  (y1-y0) rows of [filter byte + W*bpp]
+ *      RAW  (y1-y0) rows of W*bpp
+ *      JPEG stitch_jpeg_band_info followed by the band's entropy bytes
+ *           (y0 % 8 == 0; y1 % 8 == 0 or y1 == canvas_h)
+ *  out == NULL: the result stays on the device (stitch_job_band_device).
+ * The PNG predictor row for y0 > 0 is recomputed on the device (1-row halo). */
+int stitch_job_run_band(stitch_job *job, uint32_t y0, uint32_t y1, uint8_t *out, size_t cap,
+                        size_t *out_len, stitch_timings *t);
+
+/* Device address / pitch of the last computed band (row r of the band starts
+ * at ptr + r*pitch; for PNG the filter byte is at ptr + r*pitch + lead). */
+int stitch_job_band_device(stitch_job *job, void **ptr, size_t *pitch, size_t *lead, size_t *row_bytes);
+
+/* First decode error seen on the device, in the reference's wording. */
+int stitch_job_status(stitch_job *job);
+
+/* ---- stand-alone pieces (unit-level parity) ------------------------------- */
+
+/* Kernel (a) alone: inflated stream -> dense unfiltered rows in SOURCE format
+ * (what ImageDecoder.scanlines() yields, src/decoders/types.ts:55-61). */
+int stitch_decode_image(stitch_ctx *ctx, const stitch_tile_desc *tile, const uint8_t *data, size_t len,
+                        uint8_t *out, size_t cap, size_t *out_len);
+
+/* Kernel (c) alone: filterScanline over `rows` rows of `row_bytes` bytes.
+ * prev_row (may be NULL) is the raw row above rows[0]. out: rows*(1+row_bytes). */
+int stitch_filter_rows(stitch_ctx *ctx, const uint8_t *rows, const uint8_t *prev_row, uint32_t n_rows,
+                       size_t row_bytes, uint32_t bpp, uint8_t *out, size_t cap);
+
+/* ---- JPEG container helpers (host side of src/jpeg-encoder.ts) ------------ */
+
+/* Writes SOI + JFIF APP0 + DQT + SOF0 + DHT + SOS for the encoder definition in
+ * DESIGN.md (what the external encoder emits with its first strip). */
+int stitch_jpeg_header(uint32_t width, uint32_t height, uint32_t quality, uint8_t *out, size_t cap, size_t *out_len);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* STITCH_B200_H */
