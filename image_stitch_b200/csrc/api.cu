@@ -9,6 +9,7 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -52,7 +53,9 @@ struct stitch_job {
   uint32_t *d_bin_start = nullptr, *d_bin_tiles = nullptr;
   UnfStream *d_streams = nullptr; size_t streams_cap = 0;
   A7Image *d_a7 = nullptr; size_t a7_cap = 0;
-  uint32_t bins_x = 0, bins_y = 0, bin_w_log2 = 6, bin_h_log2 = 4, bin_y_origin = 0;
+  uint32_t bins_x = 0, bins_y = 0, bin_w_log2 = 9, bin_h_log2 = 4, bin_y_origin = 0;
+  uint32_t *d_sync = nullptr; size_t sync_words = 0;   // fused kernel: rowsum | band_done | ticket
+  bool force_two_pass = false;
   // band buffers
   uint8_t *d_canvas = nullptr; size_t canvas_bytes = 0; size_t canvas_pitch = 0;
   uint8_t *d_out = nullptr; size_t out_bytes = 0;
@@ -171,6 +174,7 @@ extern "C" int stitch_job_create(stitch_ctx *ctx, const stitch_job_desc *desc, s
   if (job->desc.band_y1 == 0 || job->desc.band_y1 > desc->canvas_h) { job->desc.band_y0 = 0; job->desc.band_y1 = desc->canvas_h; }
   if (job->desc.band_y0 >= job->desc.band_y1) { delete job; return fail(ctx, STITCH_E_INVALID, "empty band"); }
   job->bpp = desc->out_bit_depth == 16 ? 8 : 4;
+  { const char *e = getenv("STITCH_B200_TWO_PASS"); job->force_two_pass = e && e[0] == '1'; }
   cudaSetDevice(ctx->device);
   *out = job;
   return STITCH_OK;
@@ -190,7 +194,7 @@ extern "C" void stitch_job_destroy(stitch_job *job) {
   for (auto &t : job->tiles) free_tile(ctx, t);
   dev_free(ctx, job->d_tiles); dev_free(ctx, job->d_bin_start); dev_free(ctx, job->d_bin_tiles);
   dev_free(ctx, job->d_streams); dev_free(ctx, job->d_a7);
-  dev_free(ctx, job->d_canvas); dev_free(ctx, job->d_out);
+  dev_free(ctx, job->d_canvas); dev_free(ctx, job->d_out); dev_free(ctx, job->d_sync);
   cudaStreamSynchronize(ctx->stream);
   delete job;
 }
@@ -433,19 +437,20 @@ static int finalize_job(stitch_job *job) {
     o.opaque = (t.d.color_type == 0 || t.d.color_type == 2) ? 1u : 0u;
     o.pad = 0;
   }
-  // bins cover the job's band plus the halo row above it
-  const uint32_t ys = jd.band_y0 ? jd.band_y0 - 1 : 0;
-  const uint32_t bw = 1u << job->bin_w_log2, bh = 1u << job->bin_h_log2;
-  job->bin_y_origin = ys / bh * bh;
+  // Bins are the fused kernel's items (absolute grid: FB_R rows x FB_SWW words).  A bin also lists
+  // tiles that touch the row above it or the pixel left of it (filter predictors are recomputed).
+  const uint32_t bh = fused_rows_per_band(), bw = fused_words_per_seg() / (job->bpp / 4);
+  job->bin_h_log2 = 0; while ((1u << job->bin_h_log2) < bh) job->bin_h_log2++;
+  job->bin_w_log2 = 0; while ((1u << job->bin_w_log2) < bw) job->bin_w_log2++;
+  job->bin_y_origin = 0;
   job->bins_x = (jd.canvas_w + bw - 1) / bw;
-  job->bins_y = (jd.band_y1 - job->bin_y_origin + bh - 1) / bh;
+  job->bins_y = (jd.canvas_h + bh - 1) / bh;
   const size_t n_bins = (size_t)job->bins_x * job->bins_y;
   std::vector<uint32_t> start(n_bins + 1, 0);
   auto bin_range = [&](const DevTile &o, uint32_t &bx0, uint32_t &bx1, uint32_t &by0, uint32_t &by1) -> bool {
-    const int64_t ya = std::max<int64_t>(o.y0, job->bin_y_origin), yb = std::min<int64_t>(o.y1, jd.band_y1);
-    if (ya >= yb) return false;
-    bx0 = (uint32_t)o.x0 >> job->bin_w_log2; bx1 = ((uint32_t)o.x1 - 1) >> job->bin_w_log2;
-    by0 = (uint32_t)(ya - job->bin_y_origin) >> job->bin_h_log2; by1 = (uint32_t)(yb - 1 - job->bin_y_origin) >> job->bin_h_log2;
+    if (o.x1 <= o.x0 || o.y1 <= o.y0) return false;
+    bx0 = (uint32_t)o.x0 >> job->bin_w_log2; bx1 = std::min((uint32_t)o.x1 >> job->bin_w_log2, job->bins_x - 1);
+    by0 = (uint32_t)o.y0 >> job->bin_h_log2; by1 = std::min((uint32_t)o.y1 >> job->bin_h_log2, job->bins_y - 1);
     return true;
   };
   for (const DevTile &o : dt) {
@@ -526,20 +531,46 @@ extern "C" int stitch_job_run_band(stitch_job *job, uint32_t y0, uint32_t y1, ui
 
   const size_t pitch16 = round_up(row_bytes, 16);
   if (png) {
-    const uint32_t ys = y0 ? y0 - 1 : 0;  // 1-row halo: the predictor row is recomputed, not exchanged
-    job->canvas_pitch = pitch16;
-    if ((rc = ensure_buffer(ctx, &job->d_canvas, &job->canvas_bytes, pitch16 * (size_t)(y1 - ys)))) return rc;
     job->out_pitch = 16 + pitch16; job->out_lead = 15; job->out_row_bytes = host_row;
     if ((rc = ensure_buffer(ctx, &job->d_out, &job->out_bytes, job->out_pitch * (size_t)n_rows))) return rc;
-    cp.y_begin = ys; cp.y_end = y1; cp.out = job->d_canvas; cp.out_pitch = pitch16;
-    CK(launch_compose(cp, jd.out_bit_depth == 16, ctx->stream));
-    FilterParams fp{};
-    fp.rows = job->d_canvas + (size_t)(y0 - ys) * pitch16; fp.in_pitch = pitch16;
-    fp.prev0 = y0 ? job->d_canvas : nullptr;
-    fp.n_rows = n_rows; fp.row_bytes = (uint32_t)row_bytes; fp.bpp = job->bpp;
-    fp.out = job->d_out; fp.out_pitch = job->out_pitch; fp.lead = (uint32_t)job->out_lead;
-    CK(launch_filter_rows(fp, ctx->stream));
-    launches += 2;
+    bool fused_done = false;
+    if (!job->force_two_pass) {
+      // fused single pass: rowsum[n_rows][8] | band_done[n_bands] | ticket
+      const uint32_t bh = fused_rows_per_band();
+      const uint32_t band0 = y0 / bh, n_bands = (y1 - 1) / bh - band0 + 1;
+      const size_t words = (size_t)n_rows * 8 + n_bands + 4;
+      if (words > job->sync_words) {
+        dev_free(ctx, job->d_sync); job->d_sync = nullptr; job->sync_words = 0;
+        if ((rc = dev_alloc(ctx, (void **)&job->d_sync, words * 4))) return rc;
+        job->sync_words = words;
+      }
+      CK(cudaMemsetAsync(job->d_sync, 0, words * 4, ctx->stream));
+      FusedParams fp{};
+      fp.tiles = job->d_tiles; fp.bin_start = job->d_bin_start; fp.bin_tiles = job->d_bin_tiles;
+      fp.bins_x = job->bins_x; fp.canvas_w = jd.canvas_w; fp.y_begin = y0; fp.y_end = y1; fp.band0 = band0;
+      fp.n_bands = n_bands; fp.nseg = job->bins_x; fp.alpha_blend = jd.alpha_blend;
+      bg_words(jd, fp.bg_lo, fp.bg_hi);
+      fp.rowsum = job->d_sync; fp.band_done = job->d_sync + (size_t)n_rows * 8; fp.ticket = fp.band_done + n_bands;
+      fp.out = job->d_out; fp.out_pitch = job->out_pitch; fp.lead = (uint32_t)job->out_lead;
+      cudaError_t fe = launch_fused(fp, jd.out_bit_depth == 16, ctx->sm_count, ctx->stream);
+      if (fe == cudaSuccess) { fused_done = true; launches += 1; }
+      else if (fe != cudaErrorInvalidConfiguration) CK(fe);
+      else cudaGetLastError();
+    }
+    if (!fused_done) {  // rows too wide for a resident band: composite to HBM, then filter-select
+      const uint32_t ys = y0 ? y0 - 1 : 0;  // 1-row halo: the predictor row is recomputed, not exchanged
+      job->canvas_pitch = pitch16;
+      if ((rc = ensure_buffer(ctx, &job->d_canvas, &job->canvas_bytes, pitch16 * (size_t)(y1 - ys)))) return rc;
+      cp.y_begin = ys; cp.y_end = y1; cp.out = job->d_canvas; cp.out_pitch = pitch16;
+      CK(launch_compose(cp, jd.out_bit_depth == 16, ctx->stream));
+      FilterParams fp{};
+      fp.rows = job->d_canvas + (size_t)(y0 - ys) * pitch16; fp.in_pitch = pitch16;
+      fp.prev0 = y0 ? job->d_canvas : nullptr;
+      fp.n_rows = n_rows; fp.row_bytes = (uint32_t)row_bytes; fp.bpp = job->bpp;
+      fp.out = job->d_out; fp.out_pitch = job->out_pitch; fp.lead = (uint32_t)job->out_lead;
+      CK(launch_filter_rows(fp, ctx->stream));
+      launches += 2;
+    }
   } else {
     job->out_pitch = pitch16; job->out_lead = 0; job->out_row_bytes = host_row;
     if ((rc = ensure_buffer(ctx, &job->d_out, &job->out_bytes, pitch16 * (size_t)n_rows))) return rc;

@@ -33,6 +33,30 @@ struct FilterParams {
   uint32_t lead;
 };
 
+// Fused composite + filter-select (fused.cu).  Bins are the items: FB_R rows x FB_SWW words,
+// each bin's tile list also holds tiles touching the row above / the pixel left of it.
+struct FusedParams {
+  const DevTile *tiles;
+  const uint32_t *bin_start;
+  const uint32_t *bin_tiles;
+  uint32_t bins_x;            // = nseg
+  uint32_t canvas_w;
+  uint32_t y_begin, y_end;    // canvas rows to produce
+  uint32_t band0;             // absolute index (y / FB_R) of the first band
+  uint32_t n_bands, nseg;
+  uint32_t alpha_blend;
+  uint32_t bg_lo, bg_hi;
+  uint32_t *rowsum;           // [(y_end - y_begin)][8], zeroed
+  uint32_t *band_done;        // [n_bands], zeroed
+  uint32_t *ticket;           // zeroed
+  uint8_t *out;               // row r: filter byte at out + r*out_pitch + lead
+  size_t out_pitch;
+  uint32_t lead;
+};
+cudaError_t launch_fused(const FusedParams &p, bool out16, int sm_count, cudaStream_t st);
+uint32_t fused_rows_per_band();
+uint32_t fused_words_per_seg();
+
 cudaError_t launch_unfilter(const UnfStream *d_streams, uint32_t n_streams, DevStatus *d_status, cudaStream_t st);
 cudaError_t launch_adam7_gather(const A7Image *d_images, uint32_t n_images, uint32_t max_row_bytes,
                                 uint32_t max_height, cudaStream_t st);

@@ -203,3 +203,46 @@ def test_empty_canvas_and_single_pixel(ctx):
     t = [dict(width=1, height=1, bit_depth=8, color_type=6, pixels=np.array([[200, 100, 50, 128]], np.uint8))]
     want = orc.render_rows(1, 1, 8, bg, True, t, 0, 1, 0)
     assert np.array_equal(run_job(ctx, 1, 1, 8, bg, True, t, 0), want)
+
+
+@pytest.mark.parametrize("two_pass", [False, True])
+@pytest.mark.parametrize("out_bd,cw,ch", [(8, 1301, 75), (8, 2048, 33), (16, 700, 50), (8, 513, 17), (16, 257, 16)])
+def test_wide_canvas_multi_segment(ctx, monkeypatch, two_pass, out_bd, cw, ch):
+    """Rows spanning several 2 KB segments (cross-CTA cost reduction), ragged right edges,
+    bands that start inside an item; both the fused kernel and the two-pass fallback."""
+    if two_pass:
+        monkeypatch.setenv("STITCH_B200_TWO_PASS", "1")
+    rng = np.random.default_rng(cw + ch)
+    tiles = []
+    for i in range(10):
+        bd, ct = [(8, 6), (8, 2), (16, 6), (8, 4)][i % 4]
+        w, h = int(rng.integers(40, 700)), int(rng.integers(8, 60))
+        x, y = int(rng.integers(-50, cw - 20)), int(rng.integers(-10, ch - 4))
+        left, top, right, bottom = max(0, x), max(0, y), min(cw, x + w), min(ch, y + h)
+        tiles.append(dict(width=w, height=h, bit_depth=bd, color_type=ct,
+                          pixels=H.synth_pixels(rng, w, h, bd, ct, ["opaque", "any"][i % 2]),
+                          dst_x=left, dst_y=top, src_off_x=max(0, -x), src_off_y=max(0, -y), vis_w=right - left,
+                          vis_h=bottom - top, z_index=int(rng.integers(0, 3)), image_idx=i))
+    bg = bytes([7, 7, 9, 9, 11, 11, 200, 200]) if out_bd == 16 else bytes([7, 9, 11, 200])
+    for blend in (True, False):
+        want = orc.render_rows(cw, ch, out_bd, bg, blend, tiles, 0, ch, 0)
+        got = run_job(ctx, cw, ch, out_bd, bg, blend, tiles, 0)
+        assert np.array_equal(got, want), (out_bd, cw, ch, blend)
+        cuts = sorted(set([0, 1, min(ch, 5), min(ch, 16), min(ch, 23), ch]))
+        banded = run_job(ctx, cw, ch, out_bd, bg, blend, tiles, 0, bands=list(zip(cuts, cuts[1:])))
+        assert np.array_equal(banded, want)
+
+
+def test_filter_costs_extreme_bytes(ctx):
+    """Bytes around 0x80 and wrap-arounds: the |signed byte| cost must match for every candidate."""
+    rng = np.random.default_rng(11)
+    w, h = 1024, 40
+    pix = rng.choice(np.array([0, 1, 127, 128, 129, 254, 255], np.uint8), size=(h, w * 4))
+    tiles = [dict(width=w, height=h, bit_depth=8, color_type=6, pixels=pix)]
+    want = orc.render_rows(w, h, 8, bytes(4), False, tiles, 0, h, 0)
+    got = run_job(ctx, w, h, 8, bytes(4), False, tiles, 0)
+    assert np.array_equal(got, want)
+    pix2 = rng.integers(0, 256, size=(h, w * 4), dtype=np.uint8)   # noise: near-ties between filters
+    tiles = [dict(width=w, height=h, bit_depth=8, color_type=6, pixels=pix2)]
+    want = orc.render_rows(w, h, 8, bytes(4), False, tiles, 0, h, 0)
+    assert np.array_equal(run_job(ctx, w, h, 8, bytes(4), False, tiles, 0), want)

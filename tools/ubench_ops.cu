@@ -1,0 +1,43 @@
+// Micro-benchmark: per-SM throughput of the instructions the filter-selection kernel leans on.
+#include <cstdio>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#define ITER 4096
+template <int OP> __global__ void k(unsigned *out, unsigned seed) {
+  unsigned a0 = seed + threadIdx.x, a1 = a0 * 3, a2 = a0 * 5, a3 = a0 * 7, a4 = a0 * 11, a5 = a0 * 13, a6 = a0 * 17, a7 = a0 * 19;
+  unsigned b = seed * 7 + 1;
+  __half2 h0 = __floats2half2_rn(1.f, 2.f), h1 = h0, h2 = h0, h3 = h0, h4 = h0, h5 = h0, h6 = h0, h7 = h0, hb = __floats2half2_rn(0.5f, 0.25f);
+  for (int i = 0; i < ITER; i++) {
+    if (OP == 0) { a0 = __vabsdiffu4(a0, b); a1 = __vabsdiffu4(a1, b); a2 = __vabsdiffu4(a2, b); a3 = __vabsdiffu4(a3, b); a4 = __vabsdiffu4(a4, b); a5 = __vabsdiffu4(a5, b); a6 = __vabsdiffu4(a6, b); a7 = __vabsdiffu4(a7, b); }
+    if (OP == 1) { a0 = __vsadu4(a0, b) + a0; a1 = __vsadu4(a1, b) + a1; a2 = __vsadu4(a2, b) + a2; a3 = __vsadu4(a3, b) + a3; a4 = __vsadu4(a4, b) + a4; a5 = __vsadu4(a5, b) + a5; a6 = __vsadu4(a6, b) + a6; a7 = __vsadu4(a7, b) + a7; }
+    if (OP == 2) { a0 = __byte_perm(a0, b, 0x4140); a1 = __byte_perm(a1, b, 0x4140); a2 = __byte_perm(a2, b, 0x4140); a3 = __byte_perm(a3, b, 0x4140); a4 = __byte_perm(a4, b, 0x4140); a5 = __byte_perm(a5, b, 0x4140); a6 = __byte_perm(a6, b, 0x4140); a7 = __byte_perm(a7, b, 0x4140); }
+    if (OP == 3) { a0 = (a0 & b) ^ (a0 >> 3); a1 = (a1 & b) ^ (a1 >> 3); a2 = (a2 & b) ^ (a2 >> 3); a3 = (a3 & b) ^ (a3 >> 3); a4 = (a4 & b) ^ (a4 >> 3); a5 = (a5 & b) ^ (a5 >> 3); a6 = (a6 & b) ^ (a6 >> 3); a7 = (a7 & b) ^ (a7 >> 3); }
+    if (OP == 4) { h0 = __hfma2(h0, hb, hb); h1 = __hfma2(h1, hb, hb); h2 = __hfma2(h2, hb, hb); h3 = __hfma2(h3, hb, hb); h4 = __hfma2(h4, hb, hb); h5 = __hfma2(h5, hb, hb); h6 = __hfma2(h6, hb, hb); h7 = __hfma2(h7, hb, hb); }
+    if (OP == 5) { h0 = __hle2(__habs2(h0), hb); h1 = __hle2(__habs2(h1), hb); h2 = __hle2(__habs2(h2), hb); h3 = __hle2(__habs2(h3), hb); h4 = __hle2(__habs2(h4), hb); h5 = __hle2(__habs2(h5), hb); h6 = __hle2(__habs2(h6), hb); h7 = __hle2(__habs2(h7), hb); }
+    if (OP == 6) { h0 = __hmin2(__habs2(h0), hb); h1 = __hmin2(__habs2(h1), hb); h2 = __hmin2(__habs2(h2), hb); h3 = __hmin2(__habs2(h3), hb); h4 = __hmin2(__habs2(h4), hb); h5 = __hmin2(__habs2(h5), hb); h6 = __hmin2(__habs2(h6), hb); h7 = __hmin2(__habs2(h7), hb); }
+    if (OP == 7) { a0 = __dp4a(a0, b, a0); a1 = __dp4a(a1, b, a1); a2 = __dp4a(a2, b, a2); a3 = __dp4a(a3, b, a3); a4 = __dp4a(a4, b, a4); a5 = __dp4a(a5, b, a5); a6 = __dp4a(a6, b, a6); a7 = __dp4a(a7, b, a7); }
+    if (OP == 8) { h0 = __hadd2(h0, hb); a0 = (a0 & b) ^ (a0 >> 3); h1 = __hadd2(h1, hb); a1 = (a1 & b) ^ (a1 >> 3); h2 = __hadd2(h2, hb); a2 = (a2 & b) ^ (a2 >> 3); h3 = __hadd2(h3, hb); a3 = (a3 & b) ^ (a3 >> 3); h4 = __hadd2(h4, hb); a4 = (a4 & b) ^ (a4 >> 3); h5 = __hadd2(h5, hb); a5 = (a5 & b) ^ (a5 >> 3); h6 = __hadd2(h6, hb); a6 = (a6 & b) ^ (a6 >> 3); h7 = __hadd2(h7, hb); a7 = (a7 & b) ^ (a7 >> 3); }
+    if (OP == 9) { a0 = __shfl_up_sync(~0u, a0, 1); a1 = __shfl_up_sync(~0u, a1, 1); a2 = __shfl_up_sync(~0u, a2, 1); a3 = __shfl_up_sync(~0u, a3, 1); a4 = __shfl_up_sync(~0u, a4, 1); a5 = __shfl_up_sync(~0u, a5, 1); a6 = __shfl_up_sync(~0u, a6, 1); a7 = __shfl_up_sync(~0u, a7, 1); }
+  }
+  unsigned r = a0 ^ a1 ^ a2 ^ a3 ^ a4 ^ a5 ^ a6 ^ a7;
+  __half2 hs = __hadd2(__hadd2(__hadd2(h0, h1), __hadd2(h2, h3)), __hadd2(__hadd2(h4, h5), __hadd2(h6, h7)));
+  r ^= *reinterpret_cast<unsigned *>(&hs);
+  if (r == 0x12345) out[0] = r;
+}
+template <int OP> void run(const char *name, int ops_per_iter) {
+  unsigned *d; cudaMalloc(&d, 4);
+  cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+  int blocks = 148 * 4, threads = 512;
+  k<OP><<<blocks, threads>>>(d, 1); cudaDeviceSynchronize();
+  cudaEventRecord(e0); k<OP><<<blocks, threads>>>(d, 1); cudaEventRecord(e1); cudaEventSynchronize(e1);
+  float ms; cudaEventElapsedTime(&ms, e0, e1);
+  double thread_ops = (double)blocks * threads * ITER * ops_per_iter;
+  // lanes per clock per SM, assuming 1.92 GHz
+  printf("%-28s %8.3f ms  %7.1f thread-ops/clk/SM (at 1.92 GHz)\n", name, ms, thread_ops / (ms * 1e-3) / 148 / 1.92e9);
+}
+int main() {
+  run<0>("VABSDIFF4.U8", 8); run<1>("VABSDIFF4.U8.ACC(+IADD)", 16); run<2>("PRMT", 8); run<3>("LOP3+SHF (2 ops)", 16);
+  run<4>("HFMA2", 8); run<5>("HSET2.BF.LE |a|", 8); run<6>("HMNMX2 |a|", 8); run<7>("IDP.4A", 8);
+  run<8>("HADD2 + LOP3/SHF mix (3 ops)", 24); run<9>("SHFL.UP", 8);
+  return 0;
+}
