@@ -52,6 +52,9 @@ struct stitch_job {
   DevTile *d_tiles = nullptr;
   uint32_t *d_bin_start = nullptr, *d_bin_tiles = nullptr;
   UnfStream *d_streams = nullptr; size_t streams_cap = 0;
+  UnfStream *d_slow = nullptr; size_t slow_cap = 0;          // chains with a truncated final row (legacy kernel)
+  UnfUnit *d_units = nullptr; size_t units_cap = 0;
+  uint32_t *d_uprog = nullptr; size_t uprog_cap = 0;         // wavefront kernel: progress words | ticket
   A7Image *d_a7 = nullptr; size_t a7_cap = 0;
   uint32_t bins_x = 0, bins_y = 0, bin_w_log2 = 9, bin_h_log2 = 4, bin_y_origin = 0;
   uint32_t *d_sync = nullptr; size_t sync_words = 0;   // fused kernel: rowsum | band_done | ticket
@@ -194,6 +197,7 @@ extern "C" void stitch_job_destroy(stitch_job *job) {
   for (auto &t : job->tiles) free_tile(ctx, t);
   dev_free(ctx, job->d_tiles); dev_free(ctx, job->d_bin_start); dev_free(ctx, job->d_bin_tiles);
   dev_free(ctx, job->d_streams); dev_free(ctx, job->d_a7);
+  dev_free(ctx, job->d_slow); dev_free(ctx, job->d_units); dev_free(ctx, job->d_uprog);
   dev_free(ctx, job->d_canvas); dev_free(ctx, job->d_out); dev_free(ctx, job->d_sync);
   cudaStreamSynchronize(ctx->stream);
   delete job;
@@ -246,6 +250,7 @@ static int prepare_tile(stitch_ctx *ctx, stitch_job *job, TileRec &t, uint32_t t
     s.src = t.d_src; s.dst = t.d_pix; s.src_stride = (uint32_t)rb + 1; s.row_bytes = (uint32_t)rb;
     s.dst_pitch = t.pitch; s.rows = d.height; s.bpp = fbpp; s.last_row_bytes = (uint32_t)rb;
     s.tile = tile_no; s.pass = 0;
+    s.src_end = t.d_src + round_up(t.src_len, 16);
     t.streams.push_back(s);
     return STITCH_OK;
   }
@@ -287,6 +292,7 @@ static int prepare_tile(stitch_ctx *ctx, stitch_job *job, TileRec &t, uint32_t t
     s.src = t.d_src + pass_off[p]; s.dst = t.d_pass + pass_scr[p]; s.src_stride = prb[p] + 1; s.row_bytes = prb[p];
     s.dst_pitch = ppitch[p]; s.rows = ph[p]; s.bpp = fbpp; s.last_row_bytes = last_avail[p];
     s.tile = tile_no; s.pass = (uint32_t)p + 1;
+    s.src_end = t.d_src + round_up(t.src_len, 16);
     t.streams.push_back(s);
   }
   t.a7.dst = t.d_pix; t.a7.dst_pitch = t.pitch; t.a7.width = d.width; t.a7.height = d.height;
@@ -375,16 +381,49 @@ static int decode_tiles(stitch_job *job, int force, uint32_t *launches) {
     t.decoded = true;
   }
   if (streams.empty()) return STITCH_OK;
-  // longest chains first: the grid is scheduled in order, so this trims the tail
-  std::stable_sort(streams.begin(), streams.end(), [](const UnfStream &a, const UnfStream &b) {
-    return (uint64_t)a.rows + a.row_bytes / a.bpp > (uint64_t)b.rows + b.row_bytes / b.bpp;
-  });
-  int rc = upload_array(ctx, streams, &job->d_streams, &job->streams_cap);
-  if (rc) return rc;
-  CK(launch_unfilter(job->d_streams, (uint32_t)streams.size(), ctx->d_status, ctx->stream));
-  if (launches) (*launches)++;
+  // Chains whose final row is cut short (Adam7 slice semantics, adam7.ts:87-88) keep the legacy kernel;
+  // everything else runs on the wavefront kernel, one unit per 32-row group, handed out group-major so
+  // that all chains advance together and a unit's predecessor is always already running.
+  std::vector<UnfStream> fast, slow;
+  for (auto &s : streams) (s.last_row_bytes == s.row_bytes ? fast : slow).push_back(s);
+  if (!fast.empty()) {
+    std::stable_sort(fast.begin(), fast.end(), [](const UnfStream &a, const UnfStream &b) { return a.rows > b.rows; });
+    uint32_t prog = 0, max_groups = 0;
+    for (auto &s : fast) {
+      s.prog_base = prog;
+      const uint32_t ng = (s.rows + 31u) / 32u;
+      prog += ng;
+      max_groups = std::max(max_groups, ng);
+    }
+    std::vector<UnfUnit> units;
+    units.reserve(prog);
+    for (uint32_t g = 0; g < max_groups; g++)
+      for (uint32_t i = 0; i < fast.size(); i++) {
+        if (g >= (fast[i].rows + 31u) / 32u) break;  // sorted by rows: no later chain has this group either
+        units.push_back(UnfUnit{i, g});
+      }
+    int rc = upload_array(ctx, fast, &job->d_streams, &job->streams_cap);
+    if (rc) return rc;
+    if ((rc = upload_array(ctx, units, &job->d_units, &job->units_cap))) return rc;
+    const size_t words = (size_t)prog + 4;
+    if (words > job->uprog_cap) {
+      dev_free(ctx, job->d_uprog); job->d_uprog = nullptr; job->uprog_cap = 0;
+      if ((rc = dev_alloc(ctx, (void **)&job->d_uprog, words * 4))) return rc;
+      job->uprog_cap = words;
+    }
+    CK(cudaMemsetAsync(job->d_uprog, 0, words * 4, ctx->stream));
+    CK(launch_unfilter_wave(job->d_streams, job->d_units, (uint32_t)units.size(), job->d_uprog, job->d_uprog + prog,
+                            ctx->d_status, ctx->sm_count, ctx->stream));
+    if (launches) (*launches)++;
+  }
+  if (!slow.empty()) {
+    int rc = upload_array(ctx, slow, &job->d_slow, &job->slow_cap);
+    if (rc) return rc;
+    CK(launch_unfilter(job->d_slow, (uint32_t)slow.size(), ctx->d_status, ctx->stream));
+    if (launches) (*launches)++;
+  }
   if (!a7.empty()) {
-    rc = upload_array(ctx, a7, &job->d_a7, &job->a7_cap);
+    int rc = upload_array(ctx, a7, &job->d_a7, &job->a7_cap);
     if (rc) return rc;
     CK(launch_adam7_gather(job->d_a7, (uint32_t)a7.size(), a7_max_rb, a7_max_h, ctx->stream));
     if (launches) (*launches)++;

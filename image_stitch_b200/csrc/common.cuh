@@ -50,6 +50,15 @@ struct UnfStream {
   uint32_t last_row_bytes; // bytes available for the final row (adam7.ts:87-88 slice semantics)
   uint32_t tile;           // for error reports
   uint32_t pass;           // 0 = not interlaced, 1..7 Adam7 pass
+  const uint8_t *src_end;  // 16-byte granules starting at or after this address are never read
+  uint32_t prog_base;      // index of this chain's first progress word (one per 32-row group)
+  uint32_t pad;
+};
+
+// One work unit of the wavefront unfilter kernel: a 32-row group of one chain.
+struct UnfUnit {
+  uint32_t stream;
+  uint32_t group;
 };
 
 // Adam7 gather parameters for one interlaced image.
@@ -228,6 +237,51 @@ __device__ __forceinline__ int paeth1(int a, int b, int c) {
   int p = a + b - c;
   int pa = abs(p - a), pb = abs(p - b), pc = abs(p - c);
   return (pa <= pb && pa <= pc) ? a : (pb <= pc ? b : c);
+}
+
+// ---------------------------------------------------------------------------
+// Packed-byte helpers shared by the unfilter and filter-selection kernels.
+// Four bytes live in one register; the Paeth predictor is evaluated two bytes
+// at a time in half2 (1024+v is exact in fp16, so are all differences).
+// ---------------------------------------------------------------------------
+}  // namespace stitch
+#include <cuda_fp16.h>
+namespace stitch {
+
+struct H4 { __half2 lo, hi; };  // bytes 0,1 and bytes 2,3 as 1024+v
+__device__ __forceinline__ H4 unpack_h4(uint32_t w) {
+  H4 r;
+  uint32_t a = __byte_perm(w, 0x64646464u, 0x4140), b = __byte_perm(w, 0x64646464u, 0x4342);
+  r.lo = *reinterpret_cast<__half2 *>(&a);
+  r.hi = *reinterpret_cast<__half2 *>(&b);
+  return r;
+}
+// paethPredictor (png-filter.ts:16-25) on two lanes; ties a, then b, then c.
+__device__ __forceinline__ __half2 paeth_h2(__half2 a, __half2 b, __half2 c) {
+  const __half2 d1 = __hsub2(b, c);  // p - a
+  const __half2 d2 = __hsub2(a, c);  // p - b
+  const __half2 s = __hadd2(d1, d2);  // p - c
+  const __half2 pb = __habs2(d2), pc = __habs2(s);
+  const __half2 t1 = __hle2(pb, pc);                        // pb <= pc
+  const __half2 t2 = __hle2(__habs2(d1), __hmin2(pb, pc));  // pa <= pb && pa <= pc
+  const __half2 pk1 = __hfma2(t1, d1, c);                   // t1 ? b : c
+  return __hfma2(t2, __hsub2(a, pk1), pk1);                 // t2 ? a : pk1
+}
+__device__ __forceinline__ uint32_t pack_h4(__half2 lo, __half2 hi) {  // low byte of each 1024+v
+  return __byte_perm(*reinterpret_cast<uint32_t *>(&lo), *reinterpret_cast<uint32_t *>(&hi), 0x6420);
+}
+__device__ __forceinline__ uint32_t paeth4_h(const H4 &a, const H4 &b, const H4 &c) {
+  return pack_h4(paeth_h2(a.lo, b.lo, c.lo), paeth_h2(a.hi, b.hi, c.hi));
+}
+// per-byte (a + b) mod 256
+__device__ __forceinline__ uint32_t add4(uint32_t a, uint32_t b) {
+  return ((a & 0x7f7f7f7fu) + (b & 0x7f7f7f7fu)) ^ ((a ^ b) & 0x80808080u);
+}
+// per-byte floor((a + b) / 2)
+__device__ __forceinline__ uint32_t avg4(uint32_t a, uint32_t b) { return (a & b) + (((a ^ b) & 0xfefefefeu) >> 1); }
+// per-byte (x - p) mod 256
+__device__ __forceinline__ uint32_t sub4(uint32_t x, uint32_t p) {
+  return ((x | 0x80808080u) - (p & 0x7f7f7f7fu)) ^ ((x ^ ~p) & 0x80808080u);
 }
 
 }  // namespace stitch

@@ -19,14 +19,6 @@ namespace stitch {
 
 static constexpr int UNF_WARPS = 16;  // warps per CTA = row groups in flight per chain
 
-// mod-256 add of 4 packed bytes
-__device__ __forceinline__ uint32_t add4(uint32_t a, uint32_t b) {
-  return ((a & 0x7f7f7f7fu) + (b & 0x7f7f7f7fu)) ^ ((a ^ b) & 0x80808080u);
-}
-// floor((a+b)/2) per byte
-__device__ __forceinline__ uint32_t avg4(uint32_t a, uint32_t b) {
-  return (a & b) + (((a ^ b) & 0xfefefefeu) >> 1);
-}
 __device__ __forceinline__ uint32_t paeth4(uint32_t a, uint32_t b, uint32_t c) {
   uint32_t r = 0;
 #pragma unroll

@@ -41,34 +41,7 @@ __device__ __forceinline__ uint32_t acc_abs_s4(uint32_t v, uint32_t acc) {
   asm("vabsdiff4.u32.s32.s32.add %0, %1, %2, %3;" : "=r"(r) : "r"(v), "r"(0u), "r"(acc));
   return r;
 }
-__device__ __forceinline__ uint32_t favg4(uint32_t a, uint32_t b) { return (a & b) + (((a ^ b) >> 1) & 0x7f7f7f7fu); }
-__device__ __forceinline__ uint32_t sub4(uint32_t x, uint32_t p) {  // per-byte (x - p) mod 256
-  return ((x | 0x80808080u) - (p & 0x7f7f7f7fu)) ^ ((x ^ ~p) & 0x80808080u);
-}
-
-struct H4 { __half2 lo, hi; };  // four bytes as 1024+v in half precision (exact)
-__device__ __forceinline__ H4 unpack_h4(uint32_t w) {
-  H4 r;
-  uint32_t a = __byte_perm(w, 0x64646464u, 0x4140), b = __byte_perm(w, 0x64646464u, 0x4342);
-  r.lo = *reinterpret_cast<__half2 *>(&a);
-  r.hi = *reinterpret_cast<__half2 *>(&b);
-  return r;
-}
-// paethPredictor (png-filter.ts:16-25) on two lanes; ties a, then b, then c.
-__device__ __forceinline__ __half2 paeth_h2(__half2 a, __half2 b, __half2 c) {
-  const __half2 d1 = __hsub2(b, c);  // p - a
-  const __half2 d2 = __hsub2(a, c);  // p - b
-  const __half2 s = __hadd2(d1, d2);  // p - c
-  const __half2 pb = __habs2(d2), pc = __habs2(s);
-  const __half2 t1 = __hle2(pb, pc);                   // pb <= pc
-  const __half2 t2 = __hle2(__habs2(d1), __hmin2(pb, pc));  // pa <= pb && pa <= pc
-  const __half2 pk1 = __hfma2(t1, d1, c);              // t1 ? b : c
-  return __hfma2(t2, __hsub2(a, pk1), pk1);            // t2 ? a : pk1
-}
-__device__ __forceinline__ uint32_t paeth4_h(const H4 &a, const H4 &b, const H4 &c) {
-  __half2 lo = paeth_h2(a.lo, b.lo, c.lo), hi = paeth_h2(a.hi, b.hi, c.hi);
-  return __byte_perm(*reinterpret_cast<uint32_t *>(&lo), *reinterpret_cast<uint32_t *>(&hi), 0x6420);
-}
+__device__ __forceinline__ uint32_t favg4(uint32_t a, uint32_t b) { return avg4(a, b); }
 
 // ---- phase A: composite one 16-byte quad of canvas row y ------------------------
 template <int BPW>

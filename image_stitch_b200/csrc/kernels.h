@@ -58,6 +58,9 @@ uint32_t fused_rows_per_band();
 uint32_t fused_words_per_seg();
 
 cudaError_t launch_unfilter(const UnfStream *d_streams, uint32_t n_streams, DevStatus *d_status, cudaStream_t st);
+cudaError_t launch_unfilter_wave(const UnfStream *d_streams, const UnfUnit *d_units, uint32_t n_units,
+                                 uint32_t *d_progress, uint32_t *d_ticket, DevStatus *d_status, int sm_count,
+                                 cudaStream_t st);
 cudaError_t launch_adam7_gather(const A7Image *d_images, uint32_t n_images, uint32_t max_row_bytes,
                                 uint32_t max_height, cudaStream_t st);
 cudaError_t launch_compose(const ComposeParams &p, bool out16, cudaStream_t st);

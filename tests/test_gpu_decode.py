@@ -97,3 +97,38 @@ def test_adam7_partial_last_line_reads_zero(ctx):
     want = orc.deinterlace_adam7(cut, 2, 2, 8, 6)
     got = ctx.decode_image(2, 2, 8, 6, 1, cut)
     assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("bd,ct", FORMATS)
+def test_wide_and_tall_random_streams(ctx, bd, ct):
+    """Several column blocks and several 32-row groups per chain (wavefront kernel seams),
+    arbitrary filtered bytes with every filter type."""
+    rng = np.random.default_rng(300 + bd * 7 + ct)
+    for (w, h) in ((1500, 70), (130, 300), (4099, 33)):
+        n = orc.scanline_bytes(w, bd, ct)
+        stream = rng.integers(0, 256, size=(h, n + 1), dtype=np.uint8)
+        stream[:, 0] = rng.integers(0, 5, size=h)
+        want = orc.decode_scanlines(stream.reshape(-1), w, h, bd, ct, 0)
+        got = ctx.decode_image(w, h, bd, ct, 0, stream.tobytes())
+        assert np.array_equal(got, want), (w, h, bd, ct)
+
+
+def test_many_tiles_one_job_decode(ctx):
+    """Many chains of different heights in one launch (group-major unit order)."""
+    rng = np.random.default_rng(77)
+    job = _native.Job(ctx, 4096, 4096, 8, _native.OUT_RAW_RGBA, False, bytes(4))
+    shapes = [(64, 200), (300, 31), (33, 33), (512, 130), (7, 65), (1024, 96)]
+    wants, x = [], 0
+    for k, (w, h) in enumerate(shapes):
+        stream = rng.integers(0, 256, size=(h, w * 4 + 1), dtype=np.uint8)
+        stream[:, 0] = rng.integers(0, 5, size=h)
+        wants.append((x, w, h, orc.decode_scanlines(stream.reshape(-1), w, h, 8, 6, 0).reshape(h, w * 4)))
+        job.add_tile(stream.tobytes(), width=w, height=h, bit_depth=8, color_type=6, interlace=0, filtered=1,
+                     dst_x=x, dst_y=0, z_index=0, image_idx=k)
+        x += w
+    out, _ = job.run_band(0, 256)
+    out = np.frombuffer(out, dtype=np.uint8).reshape(256, 4096 * 4)
+    for (x0, w, h, want) in wants:
+        hh = min(h, 256)
+        assert np.array_equal(out[:hh, x0 * 4:(x0 + w) * 4], want[:hh])
+    job.close()

@@ -17,6 +17,16 @@ template <int OP> __global__ void k(unsigned *out, unsigned seed) {
     if (OP == 6) { h0 = __hmin2(__habs2(h0), hb); h1 = __hmin2(__habs2(h1), hb); h2 = __hmin2(__habs2(h2), hb); h3 = __hmin2(__habs2(h3), hb); h4 = __hmin2(__habs2(h4), hb); h5 = __hmin2(__habs2(h5), hb); h6 = __hmin2(__habs2(h6), hb); h7 = __hmin2(__habs2(h7), hb); }
     if (OP == 7) { a0 = __dp4a(a0, b, a0); a1 = __dp4a(a1, b, a1); a2 = __dp4a(a2, b, a2); a3 = __dp4a(a3, b, a3); a4 = __dp4a(a4, b, a4); a5 = __dp4a(a5, b, a5); a6 = __dp4a(a6, b, a6); a7 = __dp4a(a7, b, a7); }
     if (OP == 8) { h0 = __hadd2(h0, hb); a0 = (a0 & b) ^ (a0 >> 3); h1 = __hadd2(h1, hb); a1 = (a1 & b) ^ (a1 >> 3); h2 = __hadd2(h2, hb); a2 = (a2 & b) ^ (a2 >> 3); h3 = __hadd2(h3, hb); a3 = (a3 & b) ^ (a3 >> 3); h4 = __hadd2(h4, hb); a4 = (a4 & b) ^ (a4 >> 3); h5 = __hadd2(h5, hb); a5 = (a5 & b) ^ (a5 >> 3); h6 = __hadd2(h6, hb); a6 = (a6 & b) ^ (a6 >> 3); h7 = __hadd2(h7, hb); a7 = (a7 & b) ^ (a7 >> 3); }
+    if (OP == 10) { h0 = __hadd2(h0, hb); h1 = __hadd2(h1, hb); h2 = __hadd2(h2, hb); h3 = __hadd2(h3, hb); h4 = __hadd2(h4, hb); h5 = __hadd2(h5, hb); h6 = __hadd2(h6, hb); h7 = __hadd2(h7, hb); }
+    if (OP == 11) { a0 = __vminu4(a0, b); a1 = __vminu4(a1, b); a2 = __vminu4(a2, b); a3 = __vminu4(a3, b); a4 = __vminu4(a4, b); a5 = __vminu4(a5, b); a6 = __vminu4(a6, b); a7 = __vminu4(a7, b); }
+    if (OP == 12) { a0 = __vcmpgeu4(a0, b); a1 = __vcmpgeu4(a1, b); a2 = __vcmpgeu4(a2, b); a3 = __vcmpgeu4(a3, b); a4 = __vcmpgeu4(a4, b); a5 = __vcmpgeu4(a5, b); a6 = __vcmpgeu4(a6, b); a7 = __vcmpgeu4(a7, b); }
+    if (OP == 13) { a0 = __vavgu4(a0, b); a1 = __vavgu4(a1, b); a2 = __vavgu4(a2, b); a3 = __vavgu4(a3, b); a4 = __vavgu4(a4, b); a5 = __vavgu4(a5, b); a6 = __vavgu4(a6, b); a7 = __vavgu4(a7, b); }
+    if (OP == 14) { a0 = __vimin3_s16x2(a0, b, a1); a1 = __vimin3_s16x2(a1, b, a2); a2 = __vimin3_s16x2(a2, b, a3); a3 = __vimin3_s16x2(a3, b, a4); a4 = __vimin3_s16x2(a4, b, a5); a5 = __vimin3_s16x2(a5, b, a6); a6 = __vimin3_s16x2(a6, b, a7); a7 = __vimin3_s16x2(a7, b, a0); }
+    if (OP == 15) { a0 = __vabsdiffs2(a0, b); a1 = __vabsdiffs2(a1, b); a2 = __vabsdiffs2(a2, b); a3 = __vabsdiffs2(a3, b); a4 = __vabsdiffs2(a4, b); a5 = __vabsdiffs2(a5, b); a6 = __vabsdiffs2(a6, b); a7 = __vabsdiffs2(a7, b); }
+    if (OP == 16) { a0 = __vaddus4(a0, b); a1 = __vaddus4(a1, b); a2 = __vaddus4(a2, b); a3 = __vaddus4(a3, b); a4 = __vaddus4(a4, b); a5 = __vaddus4(a5, b); a6 = __vaddus4(a6, b); a7 = __vaddus4(a7, b); }
+    if (OP == 17) { a0 = a0 * 257u + b; a1 = a1 * 257u + b; a2 = a2 * 257u + b; a3 = a3 * 257u + b; a4 = a4 * 257u + b; a5 = a5 * 257u + b; a6 = a6 * 257u + b; a7 = a7 * 257u + b; }
+    if (OP == 18) { a0 = __vsub4(a0, b); a1 = __vsub4(a1, b); a2 = __vsub4(a2, b); a3 = __vsub4(a3, b); a4 = __vsub4(a4, b); a5 = __vsub4(a5, b); a6 = __vsub4(a6, b); a7 = __vsub4(a7, b); }
+    if (OP == 19) { h0 = __hadd2(h0, hb); a0 = __byte_perm(a0, b, 0x4140); h1 = __hfma2(h1, hb, hb); a1 = (a1 & b) ^ (a1 >> 3); h2 = __hadd2(h2, hb); a2 = __byte_perm(a2, b, 0x4140); h3 = __hfma2(h3, hb, hb); a3 = (a3 & b) ^ (a3 >> 3); }
     if (OP == 9) { a0 = __shfl_up_sync(~0u, a0, 1); a1 = __shfl_up_sync(~0u, a1, 1); a2 = __shfl_up_sync(~0u, a2, 1); a3 = __shfl_up_sync(~0u, a3, 1); a4 = __shfl_up_sync(~0u, a4, 1); a5 = __shfl_up_sync(~0u, a5, 1); a6 = __shfl_up_sync(~0u, a6, 1); a7 = __shfl_up_sync(~0u, a7, 1); }
   }
   unsigned r = a0 ^ a1 ^ a2 ^ a3 ^ a4 ^ a5 ^ a6 ^ a7;
@@ -39,5 +49,7 @@ int main() {
   run<0>("VABSDIFF4.U8", 8); run<1>("VABSDIFF4.U8.ACC(+IADD)", 16); run<2>("PRMT", 8); run<3>("LOP3+SHF (2 ops)", 16);
   run<4>("HFMA2", 8); run<5>("HSET2.BF.LE |a|", 8); run<6>("HMNMX2 |a|", 8); run<7>("IDP.4A", 8);
   run<8>("HADD2 + LOP3/SHF mix (3 ops)", 24); run<9>("SHFL.UP", 8);
+  run<10>("HADD2", 8); run<11>("vminu4", 8); run<12>("vcmpgeu4", 8); run<13>("vavgu4 (ceil avg)", 8); run<14>("vimin3_s16x2 (DPX)", 8);
+  run<15>("vabsdiffs2", 8); run<16>("vaddus4", 8); run<17>("IMAD", 8); run<18>("vsub4", 8); run<19>("mix 2 half + PRMT + LOP3/SHF (6 ops)", 6);
   return 0;
 }
