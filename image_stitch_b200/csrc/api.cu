@@ -575,7 +575,7 @@ extern "C" int stitch_job_run_band(stitch_job *job, uint32_t y0, uint32_t y1, ui
     bool fused_done = false;
     if (!job->force_two_pass) {
       // fused single pass: rowsum[n_rows][8] | band_done[n_bands] | ticket
-      const uint32_t bh = fused_rows_per_band();
+      const uint32_t bh = fused_unit_rows();
       const uint32_t band0 = y0 / bh, n_bands = (y1 - 1) / bh - band0 + 1;
       const size_t words = (size_t)n_rows * 8 + n_bands + 4;
       if (words > job->sync_words) {
@@ -587,7 +587,8 @@ extern "C" int stitch_job_run_band(stitch_job *job, uint32_t y0, uint32_t y1, ui
       FusedParams fp{};
       fp.tiles = job->d_tiles; fp.bin_start = job->d_bin_start; fp.bin_tiles = job->d_bin_tiles;
       fp.bins_x = job->bins_x; fp.canvas_w = jd.canvas_w; fp.y_begin = y0; fp.y_end = y1; fp.band0 = band0;
-      fp.n_bands = n_bands; fp.nseg = job->bins_x; fp.alpha_blend = jd.alpha_blend;
+      fp.n_bands = n_bands;
+      fp.nseg = (uint32_t)((row_bytes / 4 + fused_unit_words() - 1) / fused_unit_words()); fp.alpha_blend = jd.alpha_blend;
       bg_words(jd, fp.bg_lo, fp.bg_hi);
       fp.rowsum = job->d_sync; fp.band_done = job->d_sync + (size_t)n_rows * 8; fp.ticket = fp.band_done + n_bands;
       fp.out = job->d_out; fp.out_pitch = job->out_pitch; fp.lead = (uint32_t)job->out_lead;

@@ -1,49 +1,72 @@
 // fused.cu -- kernels (b)+(c) in ONE pass over HBM: normalise + composite the
-// tiles of a canvas segment into shared memory, compute the five PNG filter
-// costs (src/png-filter.ts:148-181), agree on the per-row winner across the
-// CTAs that share a row, and write the filtered scanlines.  HBM traffic is
-// "read every visible tile pixel once, write every output byte once".
+// tiles under a canvas patch, compute the five PNG filter costs
+// (src/png-filter.ts:148-181), agree on the per-row winner across all the
+// warps that share a canvas row, and write the filtered scanlines.  HBM
+// traffic is "read every visible tile pixel once, write every output byte
+// once" (the 1-row halo above a patch is an L2 hit: the patch above is being
+// processed at the same time).
 //
-// Work decomposition: an ITEM is FB_R canvas rows x FB_SWW 32-bit words
-// (2 KB of every row).  A row's cost is a sum over all items of its band, so
-// items publish partial sums with red.global.add and bump a per-band counter;
-// an item writes its rows once the counter says the band is complete.  Items
-// are handed out in band-major order by an atomic ticket to a persistent grid
-// that is fully resident (grid <= SMs x occupancy, and >= items per band), so
-// every item a CTA waits for is already running: no deadlock, no grid sync.
+// Work decomposition: a UNIT is FU_R canvas rows x 128 32-bit words (one
+// 16-byte quad per lane per row) and belongs to ONE WARP; warps are independent
+// workers with a private shared-memory stash, so there is no CTA barrier
+// anywhere.  A row's cost is a sum over all units of its band: units publish
+// partial sums with red.global.add and bump a per-band counter; a warp writes
+// its rows once the counter says the band is complete.  Units are handed out
+// band-major by an atomic ticket to a grid that is fully resident and has at
+// least as many warps as a band has units, so every unit a warp waits for is
+// already running: no deadlock, no grid sync.
 //
-// Arithmetic: bytes stay packed four to a register.  cost(candidate) =
-// sum |signed byte| = VABSDIFF4.S8.ACC(|x - pred|, 0) with |x - pred| from
-// VABSDIFF4.U8 (both native, 64 lanes/clk/SM on the ALU pipe); the Paeth
-// predictor is evaluated two bytes at a time in half2 (exact for 9-bit
-// integers) on the FMA pipe, which runs concurrently with the ALU pipe.
-#include <cuda_fp16.h>
-
+//   phase A   raw stash <- cp.async of the one tile that covers the unit (grid
+//             mosaics, opaque layers), else the generic per-quad compositor
+//   sweep     rows top to bottom, previous row carried in registers already
+//             unpacked to half2; per word: None/Sub/Up/Average costs on packed
+//             bytes (VABSDIFF4 + accumulate), Paeth two bytes at a time in
+//             half2 (exact for 9-bit integers); the Paeth residual falls out of
+//             the half2 pipeline as (x - pred + 1280) whose low byte is the
+//             filtered byte, and is stashed for phase B
+//   phase B   winner per row (first minimum: None, Sub, Up, Average, Paeth),
+//             one 128-bit store per lane per row
 #include "common.cuh"
 #include "kernels.h"
 
 namespace stitch {
 
-static constexpr int FB_R = 16;            // rows per item
-static constexpr int FB_SWW = 512;         // 32-bit words per item row (2 KB): 512 px RGBA8 / 256 px RGBA16
-static constexpr int FB_QPR = FB_SWW / 4;  // 16-byte quads per item row
-static constexpr int FB_PITCH = FB_SWW + 4;  // raw row pitch in words: [.. left context][FB_SWW words]
-static constexpr int FB_THREADS = 256;
-static constexpr int FB_RAW_WORDS = (FB_R + 1) * FB_PITCH;
-static constexpr int FB_PF_WORDS = FB_R * FB_SWW;
-static constexpr size_t FB_SMEM = (size_t)(FB_RAW_WORDS + FB_PF_WORDS) * 4;
+static constexpr int FB_R = 16;     // bin height (host binning granularity), rows
+static constexpr int FB_SWW = 512;  // bin width in 32-bit words
+
+static constexpr int FU_R = 16;                      // rows per unit
+static constexpr int FU_SW = 128;                    // words per unit row
+static constexpr int FU_WARPS = 4;                   // workers per CTA
+static constexpr int FU_RAW_WORDS = (FU_R + 1) * FU_SW;  // row 0 = predictor row above the unit
+static constexpr int FU_PF_WORDS = FU_R * FU_SW;
+static constexpr int FU_LC_WORDS = ((FU_R + 1) * 2 + 3) / 4 * 4;  // two words left of every row
+static constexpr int FU_WARP_WORDS = FU_RAW_WORDS + FU_PF_WORDS + FU_LC_WORDS;
+static constexpr size_t FU_CTA_SMEM = (size_t)FU_WARPS * FU_WARP_WORDS * 4;
+static_assert(FB_R % FU_R == 0 && FB_SWW % FU_SW == 0, "a unit must lie inside one bin");
 
 // ---- packed-byte helpers ------------------------------------------------------
 __device__ __forceinline__ uint32_t absdiff_u4(uint32_t a, uint32_t b) { return __vabsdiffu4(a, b); }
-// acc + sum over bytes of |sext8(v)|
+// acc + sum over bytes of |sext8(v)|  ==  acc + sum of min(b, 256 - b)   (png-filter.ts:165-171)
 __device__ __forceinline__ uint32_t acc_abs_s4(uint32_t v, uint32_t acc) {
   uint32_t r;
   asm("vabsdiff4.u32.s32.s32.add %0, %1, %2, %3;" : "=r"(r) : "r"(v), "r"(0u), "r"(acc));
   return r;
 }
-__device__ __forceinline__ uint32_t favg4(uint32_t a, uint32_t b) { return avg4(a, b); }
 
-// ---- phase A: composite one 16-byte quad of canvas row y ------------------------
+// Paeth-filtered bytes of two lanes: low byte of (x - paeth(a,b,c) + 1280) in each half.
+__device__ __forceinline__ __half2 paeth_resid_h2(__half2 x, __half2 a, __half2 b, __half2 c) {
+  const __half2 d1 = __hsub2(b, c);   // p - a
+  const __half2 d2 = __hsub2(a, c);   // p - b
+  const __half2 s = __hadd2(d1, d2);  // p - c
+  const __half2 pb = __habs2(d2), pc = __habs2(s);
+  const __half2 t1 = __hle2(pb, pc);                        // pb <= pc
+  const __half2 t2 = __hle2(__habs2(d1), __hmin2(pb, pc));  // pa <= pb && pa <= pc
+  const __half2 pk1 = __hfma2(t1, d1, c);                   // t1 ? b : c
+  const __half2 w = __hadd2(__hsub2(x, pk1), __float2half2_rn(1280.f));
+  return __hfma2(t2, __hsub2(pk1, a), w);                   // x - (t2 ? a : pk1) + 1280, exact in [1025,1535]
+}
+
+// ---- generic compositor: one 16-byte quad of canvas row y ------------------------
 template <int BPW>
 __device__ __forceinline__ uint4 compose_quad(const FusedParams &p, const uint32_t *list, uint32_t n_list, int xw, int y) {
   constexpr int PX = 4 / BPW;  // pixels per quad
@@ -105,203 +128,263 @@ __device__ __forceinline__ uint4 compose_quad(const FusedParams &p, const uint32
   return make_uint4(w[0], w[1], w[2], w[3]);
 }
 
-// ---- phase B helper: filtered quad for a known winner -----------------------------
-template <int BPW>
-__device__ __forceinline__ uint4 filter_quad(uint32_t ft, const uint4 &cur, const uint4 &up, const uint32_t *lc,
-                                             const uint4 &pf) {
-  const uint32_t x[4] = {cur.x, cur.y, cur.z, cur.w}, b[4] = {up.x, up.y, up.z, up.w};
-  uint32_t o[4];
-#pragma unroll
-  for (int j = 0; j < 4; j++) {
-    const uint32_t a = j >= BPW ? x[j - BPW] : lc[j];
-    switch (ft) {
-      case 1: o[j] = sub4(x[j], a); break;
-      case 2: o[j] = sub4(x[j], b[j]); break;
-      case 3: o[j] = sub4(x[j], favg4(a, b[j])); break;
-      default: o[j] = x[j]; break;
-    }
-  }
-  if (ft == 4u) return pf;
-  return make_uint4(o[0], o[1], o[2], o[3]);
+__device__ __forceinline__ void fu_cp_async16(void *smem, const void *gmem) {
+  const uint32_t sa = (uint32_t)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gmem) : "memory");
 }
-
-__device__ __forceinline__ uint32_t ld_volatile_u32(const uint32_t *p) {
+__device__ __forceinline__ uint32_t fu_ld_acquire(const uint32_t *p) {
   uint32_t v;
-  asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(p));
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
 
+// One row of the sweep.  GUARD: the unit reaches past the right edge of the canvas.
+// hb/hlu: the row above, unpacked (input); hx/hlc: this row, unpacked (output, becomes the next row's hb/hlu).
+template <int BPW, bool GUARD>
+__device__ __forceinline__ void sweep_row(const uint4 cur, const uint32_t lc0, const uint32_t lc1, const uint4 up,
+                                          const H4 (&hb)[4], const H4 (&hlu)[2], H4 (&hx)[4], H4 (&hlc)[2], int qw,
+                                          int wmax, uint32_t *pf_out, uint32_t (&sum)[5]) {
+  const uint32_t x[4] = {cur.x, cur.y, cur.z, cur.w}, b[4] = {up.x, up.y, up.z, up.w};
+  const uint32_t lc[2] = {lc0, lc1};
+  if (BPW == 2) hlc[0] = unpack_h4(lc0);
+  hlc[1] = unpack_h4(lc1);
+  uint32_t s0 = 0, s1 = 0, s2 = 0, s3 = 0, s4 = 0, pf[4];
+#pragma unroll
+  for (int j = 0; j < 4; j++) {
+    hx[j] = unpack_h4(x[j]);
+    const uint32_t a = j >= BPW ? x[j - BPW] : lc[2 - BPW + j];
+    const H4 &ha = j >= BPW ? hx[j - BPW] : hlc[2 - BPW + j];
+    const H4 &hc = j >= BPW ? hb[j - BPW] : hlu[2 - BPW + j];
+    pf[j] = pack_h4(paeth_resid_h2(hx[j].lo, ha.lo, hb[j].lo, hc.lo), paeth_resid_h2(hx[j].hi, ha.hi, hb[j].hi, hc.hi));
+    if (!GUARD || qw + j < wmax) {  // words past the canvas edge carry no cost
+      s0 = acc_abs_s4(x[j], s0);
+      s1 = acc_abs_s4(absdiff_u4(x[j], a), s1);
+      s2 = acc_abs_s4(absdiff_u4(x[j], b[j]), s2);
+      s3 = acc_abs_s4(absdiff_u4(x[j], avg4(a, b[j])), s3);
+      s4 = acc_abs_s4(pf[j], s4);
+    }
+  }
+  *reinterpret_cast<uint4 *>(pf_out) = make_uint4(pf[0], pf[1], pf[2], pf[3]);
+  sum[0] = s0; sum[1] = s1; sum[2] = s2; sum[3] = s3; sum[4] = s4;
+}
+
+// Row r of the unit: loads, left context, costs, warp reduction, one red.global per candidate.
 template <int BPW>
-__global__ void __launch_bounds__(FB_THREADS, 3) fused_kernel(const FusedParams p) {
-  extern __shared__ __align__(16) uint32_t smem[];
-  uint32_t *raw = smem;                  // (FB_R+1) rows: row 0 = predictor row, words [4-BPW,4) = left context
-  uint32_t *pfw = smem + FB_RAW_WORDS;   // Paeth-filtered words of the item
-  __shared__ uint32_t s_item;
-  __shared__ uint32_t s_sum[FB_R][5];
-  const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
-  const uint32_t n_items = p.n_bands * p.nseg;
-  const int wmax = (int)p.canvas_w * BPW;  // words per canvas row
+__device__ __forceinline__ void sweep_step(const uint32_t *raw_row, const uint32_t *lcs_row, uint32_t *pf_row,
+                                           uint32_t *rs_row, uint32_t lane, const uint32_t (&lmask)[5], bool guard,
+                                           int qw, int wmax, uint4 &up, const H4 (&hb)[4], const H4 (&hlu)[2],
+                                           H4 (&hx)[4], H4 (&hlc)[2]) {
+  const uint4 cur = *reinterpret_cast<const uint4 *>(raw_row + 4 * lane);
+  uint32_t c0 = BPW == 2 ? __shfl_up_sync(0xffffffffu, cur.z, 1) : 0u;
+  uint32_t c1 = __shfl_up_sync(0xffffffffu, cur.w, 1);
+  if (lane == 0u) { c0 = lcs_row[0]; c1 = lcs_row[1]; }
+  uint32_t sum[5];
+  if (guard) sweep_row<BPW, true>(cur, c0, c1, up, hb, hlu, hx, hlc, qw, wmax, pf_row + 4 * lane, sum);
+  else sweep_row<BPW, false>(cur, c0, c1, up, hb, hlu, hx, hlc, qw, wmax, pf_row + 4 * lane, sum);
+  uint32_t v = 0u;
+#pragma unroll
+  for (int f = 0; f < 5; f++) v |= __reduce_add_sync(0xffffffffu, sum[f]) & lmask[f];
+  if (lane < 5u) atomicAdd(rs_row + lane, v);
+  up = cur;
+}
+
+template <int BPW>
+__global__ void __launch_bounds__(FU_WARPS * 32) fused_kernel(const FusedParams p) {
+  extern __shared__ __align__(16) uint32_t fu_smem[];
+  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  uint32_t *raw = fu_smem + warp * FU_WARP_WORDS;  // (FU_R+1) x 128 words, row 0 = predictor row
+  uint32_t *pfw = raw + FU_RAW_WORDS;              // Paeth-filtered words
+  uint32_t *lcs = pfw + FU_PF_WORDS;               // [row][2]: the two words left of the unit
+  const uint32_t n_units = p.n_bands * p.nseg;
+  const int wmax = (int)p.canvas_w * BPW;          // words per canvas row
+  constexpr int PXQ = 4 / BPW;                     // pixels per quad
+  uint32_t lmask[5];                               // lane f keeps candidate f's row sum
+#pragma unroll
+  for (int f = 0; f < 5; f++) lmask[f] = lane == (uint32_t)f ? 0xffffffffu : 0u;
 
   for (;;) {
-    __syncthreads();  // previous item's smem is no longer in use
-    if (tid == 0) s_item = atomicAdd(p.ticket, 1u);
-    if (tid < FB_R * 5) (&s_sum[0][0])[tid] = 0u;
-    __syncthreads();
-    const uint32_t item = s_item;
-    if (item >= n_items) break;
-    const uint32_t band = item / p.nseg, seg = item - band * p.nseg;
+    uint32_t u = 0u;
+    if (lane == 0u) u = atomicAdd(p.ticket, 1u);
+    u = __shfl_sync(0xffffffffu, u, 0);
+    if (u >= n_units) break;
+    const uint32_t band = u / p.nseg, seg = u - band * p.nseg;
     const uint32_t band_abs = p.band0 + band;
-    const int ya = max((int)p.y_begin, (int)(band_abs * FB_R));
-    const int yb = min((int)p.y_end, (int)((band_abs + 1) * FB_R));
+    const int ya = max((int)p.y_begin, (int)(band_abs * FU_R));
+    const int yb = min((int)p.y_end, (int)((band_abs + 1) * FU_R));
     const int nrows = yb - ya;
-    const int xw0 = (int)seg * FB_SWW;
-    const uint32_t bin = band_abs * p.bins_x + seg;
+    const int xw0 = (int)seg * FU_SW, qw = xw0 + 4 * (int)lane;
+    const bool guard = xw0 + FU_SW > wmax;
+    const uint32_t bin = (band_abs * FU_R / FB_R) * p.bins_x + (uint32_t)(xw0 / FB_SWW);
     const uint32_t b0 = p.bin_start[bin], n_list = p.bin_start[bin + 1] - b0;
     const uint32_t *list = p.bin_tiles + b0;
 
-    // ---- phase A: composite (nrows + 1) x FB_SWW words into shared memory ----
-    for (int idx = (int)tid; idx < (nrows + 1) * FB_QPR; idx += FB_THREADS) {
-      const int rr = idx / FB_QPR, q = idx - rr * FB_QPR;
-      const int y = ya - 1 + rr;
-      uint4 v = make_uint4(0u, 0u, 0u, 0u);  // previousLine === null above row 0: predictor bytes are 0
-      if (y >= 0 && xw0 + 4 * q < wmax) v = compose_quad<BPW>(p, list, n_list, xw0 + 4 * q, y);
-      *reinterpret_cast<uint4 *>(raw + rr * FB_PITCH + 4 + 4 * q) = v;
+    // ---- is the unit a plain window of one tile? (warp-uniform) ----
+    const int X0 = xw0 / BPW, X1 = min((int)p.canvas_w, (xw0 + FU_SW) / BPW);  // unit's pixel columns
+    const uint8_t *fast_src = nullptr;  // tile byte that lands on (X0, ya)
+    uint32_t fast_pitch = 0;
+    bool halo_fast = false, left_fast = false;
+    for (int k = (int)n_list - 1; k >= 0; k--) {
+      const DevTile &t = p.tiles[list[k]];
+      if (t.y0 >= yb || t.y1 <= ya || t.x0 >= X1 || t.x1 <= X0) continue;
+      // top-most tile that touches the unit
+      const bool covers = t.y0 <= ya && t.y1 >= yb && t.x0 <= X0 && t.x1 >= X1;
+      const bool overwrite = p.alpha_blend == 0u || t.opaque;
+      const bool native = BPW == 1 ? t.fmt == FMT_RGBA8 : t.fmt == FMT_RGBA16;
+      if (covers && overwrite && native && ((X1 - X0) % PXQ) == 0) {
+        const uint8_t *src = t.pix + (size_t)(ya - t.y0 + t.sy0) * t.pitch + (size_t)(X0 - t.x0 + t.sx0) * (4u * BPW);
+        if (((reinterpret_cast<uintptr_t>(src) | t.pitch) & 15u) == 0) {
+          fast_src = src; fast_pitch = t.pitch;
+          halo_fast = t.y0 <= ya - 1;
+          left_fast = t.x0 <= X0 - 1;
+        }
+      }
+      break;
     }
-    if ((int)tid <= nrows) {  // left context: the pixel just left of the segment (0 at the canvas edge)
-      const int y = ya - 1 + (int)tid;
+
+    // ---- phase A: raw stash <- composited pixels of rows ya-1 .. yb-1 ----
+    for (int rr = 0; rr <= nrows; rr++) {
+      const int y = ya - 1 + rr;
+      uint32_t *dst = raw + rr * FU_SW + 4 * lane;
+      if (y < 0 || qw >= wmax) {  // previousLine === null above row 0: predictor bytes are 0
+        *reinterpret_cast<uint4 *>(dst) = make_uint4(0u, 0u, 0u, 0u);
+      } else if (fast_src && (rr > 0 || halo_fast)) {
+        fu_cp_async16(dst, fast_src + (ptrdiff_t)(rr - 1) * (ptrdiff_t)fast_pitch + 16u * lane);
+      } else {
+        *reinterpret_cast<uint4 *>(dst) = compose_quad<BPW>(p, list, n_list, qw, y);
+      }
+    }
+    if ((int)lane <= nrows) {  // the pixel just left of the unit (0 at the canvas edge)
+      const int y = ya - 1 + (int)lane;
       uint32_t c0 = 0u, c1 = 0u;
       if (y >= 0 && xw0 > 0) {
-        const int xw = xw0 - BPW, qa = xw & ~3;
-        const uint4 v = compose_quad<BPW>(p, list, n_list, qa, y);
-        const uint32_t vv[4] = {v.x, v.y, v.z, v.w};
-        if (BPW == 1) c1 = vv[3]; else { c0 = vv[2]; c1 = vv[3]; }
-      }
-      raw[tid * FB_PITCH + 2] = c0;
-      raw[tid * FB_PITCH + 3] = c1;
-    }
-    __syncthreads();
-
-    // ---- filter costs: warp = (128-word strip, half of the rows), one quad per lane, sweeping down ----
-    {
-      const uint32_t strip = warp & 3u, grp = warp >> 2;
-      const int r_begin = (int)grp * (FB_R / 2), r_end = min(nrows, r_begin + FB_R / 2);
-      const int qw = (int)(strip * 128u + lane * 4u);  // word offset of my quad inside the item row
-      uint4 up = make_uint4(0, 0, 0, 0);
-      uint32_t lu[2] = {0u, 0u};  // words preceding `up` (context of the row above)
-      H4 hb[4], hlu[2];           // unpacked up / up-left
-      for (int r = r_begin; r < r_end; r++) {
-        const uint32_t *row_up = raw + r * FB_PITCH + 4, *row_cur = row_up + FB_PITCH;
-        if (r == r_begin) {
-          up = *reinterpret_cast<const uint4 *>(row_up + qw);
-          lu[0] = row_up[qw - 2]; lu[1] = row_up[qw - 1];
-          hb[0] = unpack_h4(up.x); hb[1] = unpack_h4(up.y); hb[2] = unpack_h4(up.z); hb[3] = unpack_h4(up.w);
-          hlu[0] = unpack_h4(lu[0]); hlu[1] = unpack_h4(lu[1]);
+        if (fast_src && left_fast && (lane > 0 || halo_fast)) {
+          const uint32_t *lp = reinterpret_cast<const uint32_t *>(fast_src + (ptrdiff_t)((int)lane - 1) * (ptrdiff_t)fast_pitch);
+          c1 = __ldg(lp - 1);
+          if (BPW == 2) c0 = __ldg(lp - 2);
+        } else {
+          const uint4 v = compose_quad<BPW>(p, list, n_list, (xw0 - BPW) & ~3, y);
+          c1 = v.w;
+          if (BPW == 2) c0 = v.z;
         }
-        const uint4 cur = *reinterpret_cast<const uint4 *>(row_cur + qw);
-        const uint32_t lc[2] = {row_cur[qw - 2], row_cur[qw - 1]};
-        const uint32_t x[4] = {cur.x, cur.y, cur.z, cur.w}, b[4] = {up.x, up.y, up.z, up.w};
-        H4 hx[4], hlc[2];
-        hlc[0] = unpack_h4(lc[0]); hlc[1] = unpack_h4(lc[1]);
-        uint32_t s0 = 0, s1 = 0, s2 = 0, s3 = 0, s4 = 0, pf[4];
-#pragma unroll
-        for (int j = 0; j < 4; j++) {
-          hx[j] = unpack_h4(x[j]);
-          const uint32_t a = j >= BPW ? x[j - BPW] : lc[2 - BPW + j];
-          const H4 &ha = j >= BPW ? hx[j - BPW] : hlc[2 - BPW + j];
-          const H4 &hc = j >= BPW ? hb[j - BPW] : hlu[2 - BPW + j];
-          const uint32_t pk = paeth4_h(ha, hb[j], hc);
-          pf[j] = sub4(x[j], pk);
-          if (xw0 + qw + j < wmax) {  // words past the canvas edge carry no cost
-            s0 = acc_abs_s4(x[j], s0);
-            s1 = acc_abs_s4(absdiff_u4(x[j], a), s1);
-            s2 = acc_abs_s4(absdiff_u4(x[j], b[j]), s2);
-            s3 = acc_abs_s4(absdiff_u4(x[j], favg4(a, b[j])), s3);
-            s4 = acc_abs_s4(pf[j], s4);
+      }
+      lcs[lane * 2] = c0;
+      lcs[lane * 2 + 1] = c1;
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncwarp();
+
+    // ---- sweep: filter costs of every row, Paeth residuals into the stash ----
+    {
+      uint4 up = *reinterpret_cast<const uint4 *>(raw + 4 * lane);
+      uint32_t l0 = __shfl_up_sync(0xffffffffu, up.z, 1), l1 = __shfl_up_sync(0xffffffffu, up.w, 1);
+      if (lane == 0u) { l0 = lcs[0]; l1 = lcs[1]; }
+      H4 hA[4], hlA[2], hB[4], hlB[2];  // two unpacked rows, used alternately as "above" and "current"
+      hA[0] = unpack_h4(up.x); hA[1] = unpack_h4(up.y); hA[2] = unpack_h4(up.z); hA[3] = unpack_h4(up.w);
+      hlA[0] = unpack_h4(l0); hlA[1] = unpack_h4(l1);
+      const uint32_t *raw_row = raw + FU_SW;
+      const uint32_t *lcs_row = lcs + 2;
+      uint32_t *pf_row = pfw;
+      uint32_t *rs_row = p.rowsum + (size_t)(ya - (int)p.y_begin) * 8;
+      int r = 0;
+      for (; r + 2 <= nrows; r += 2) {
+        sweep_step<BPW>(raw_row, lcs_row, pf_row, rs_row, lane, lmask, guard, qw, wmax, up, hA, hlA, hB, hlB);
+        sweep_step<BPW>(raw_row + FU_SW, lcs_row + 2, pf_row + FU_SW, rs_row + 8, lane, lmask, guard, qw, wmax, up, hB,
+                        hlB, hA, hlA);
+        raw_row += 2 * FU_SW; lcs_row += 4; pf_row += 2 * FU_SW; rs_row += 16;
+      }
+      if (r < nrows) sweep_step<BPW>(raw_row, lcs_row, pf_row, rs_row, lane, lmask, guard, qw, wmax, up, hA, hlA, hB, hlB);
+    }
+    // publish: the unit's partial sums are out; count it as done for its band, wait for the others.
+    // Every lane polls the same word (one broadcast load), so the warp never diverges here.
+    __syncwarp();
+    if (lane == 0u) {
+      __threadfence();
+      atomicAdd(p.band_done + band, 1u);
+    }
+    __syncwarp();
+    while (fu_ld_acquire(p.band_done + band) < p.nseg) __nanosleep(64);
+
+    // ---- phase B: winner per row, filtered bytes out ----
+    uint32_t my_ft = 0u;
+    if ((int)lane < nrows) {
+      const uint32_t *rs = p.rowsum + (size_t)(ya + (int)lane - (int)p.y_begin) * 8;
+      const uint4 v = __ldcg(reinterpret_cast<const uint4 *>(rs));
+      const uint32_t v4 = __ldcg(rs + 4);
+      uint32_t best = v.x;
+      if (v.y < best) { best = v.y; my_ft = 1u; }   // strict '<': first minimum wins (png-filter.ts:174)
+      if (v.z < best) { best = v.z; my_ft = 2u; }
+      if (v.w < best) { best = v.w; my_ft = 3u; }
+      if (v4 < best) { best = v4; my_ft = 4u; }
+    }
+    {
+      uint8_t *orow = p.out + (size_t)(ya - (int)p.y_begin) * p.out_pitch + p.lead;
+      const uint32_t *cur_row = raw + FU_SW + 4 * lane, *pf_row = pfw + 4 * lane, *lcs_row = lcs + 2;
+      const bool whole = qw + 4 <= wmax;
+      for (int r = 0; r < nrows; r++, orow += p.out_pitch, cur_row += FU_SW, pf_row += FU_SW, lcs_row += 2) {
+        const uint32_t ft = __shfl_sync(0xffffffffu, my_ft, r);
+        if (seg == 0u && lane == 0u) orow[0] = (uint8_t)ft;
+        uint4 o;
+        if (ft == 4u) {
+          o = *reinterpret_cast<const uint4 *>(pf_row);
+        } else {
+          const uint4 cur = *reinterpret_cast<const uint4 *>(cur_row);
+          o = cur;
+          if (ft == 2u) {
+            const uint4 upq = *reinterpret_cast<const uint4 *>(cur_row - FU_SW);
+            o = make_uint4(sub4(cur.x, upq.x), sub4(cur.y, upq.y), sub4(cur.z, upq.z), sub4(cur.w, upq.w));
+          } else if (ft != 0u) {
+            uint32_t c0 = BPW == 2 ? __shfl_up_sync(0xffffffffu, cur.z, 1) : 0u;
+            uint32_t c1 = __shfl_up_sync(0xffffffffu, cur.w, 1);
+            if (lane == 0u) { c0 = lcs_row[0]; c1 = lcs_row[1]; }
+            const uint32_t a0 = BPW == 1 ? c1 : c0, a1 = BPW == 1 ? cur.x : c1;
+            const uint32_t a2 = BPW == 1 ? cur.y : cur.x, a3 = BPW == 1 ? cur.z : cur.y;
+            if (ft == 1u) {
+              o = make_uint4(sub4(cur.x, a0), sub4(cur.y, a1), sub4(cur.z, a2), sub4(cur.w, a3));
+            } else {
+              const uint4 upq = *reinterpret_cast<const uint4 *>(cur_row - FU_SW);
+              o = make_uint4(sub4(cur.x, avg4(a0, upq.x)), sub4(cur.y, avg4(a1, upq.y)), sub4(cur.z, avg4(a2, upq.z)),
+                             sub4(cur.w, avg4(a3, upq.w)));
+            }
           }
         }
-        *reinterpret_cast<uint4 *>(pfw + r * FB_SWW + qw) = make_uint4(pf[0], pf[1], pf[2], pf[3]);
-        s0 = __reduce_add_sync(0xffffffffu, s0); s1 = __reduce_add_sync(0xffffffffu, s1);
-        s2 = __reduce_add_sync(0xffffffffu, s2); s3 = __reduce_add_sync(0xffffffffu, s3);
-        s4 = __reduce_add_sync(0xffffffffu, s4);
-        if (lane < 5u) {
-          const uint32_t v = lane == 0 ? s0 : lane == 1 ? s1 : lane == 2 ? s2 : lane == 3 ? s3 : s4;
-          atomicAdd(&s_sum[r][lane], v);
-        }
-        // this row becomes the row above
-        up = cur; lu[0] = lc[0]; lu[1] = lc[1];
-#pragma unroll
-        for (int j = 0; j < 4; j++) hb[j] = hx[j];
-        hlu[0] = hlc[0]; hlu[1] = hlc[1];
-      }
-    }
-    __syncthreads();
-    // publish the item's partial sums, then count the item as done for its band
-    if ((int)tid < nrows * 5) {
-      const int r = (int)tid / 5, f = (int)tid - r * 5;
-      atomicAdd(p.rowsum + (size_t)(ya + r - (int)p.y_begin) * 8 + f, s_sum[r][f]);
-      __threadfence();
-    }
-    __syncthreads();
-    if (tid == 0) {
-      atomicAdd(p.band_done + band, 1u);
-      while (ld_volatile_u32(p.band_done + band) < p.nseg) __nanosleep(100);
-      __threadfence();
-    }
-    __syncthreads();
-
-    // ---- phase B: one warp per row writes the winner's bytes ----
-    for (int r = (int)warp; r < nrows; r += FB_THREADS / 32) {
-      const uint32_t *rs = p.rowsum + (size_t)(ya + r - (int)p.y_begin) * 8;
-      uint32_t best = __ldcg(rs), ft = 0;
-#pragma unroll
-      for (uint32_t f = 1; f < 5; f++) {
-        const uint32_t v = __ldcg(rs + f);
-        if (v < best) { best = v; ft = f; }   // strict '<': first minimum wins (png-filter.ts:174)
-      }
-      uint8_t *orow = p.out + (size_t)(ya + r - (int)p.y_begin) * p.out_pitch + p.lead;
-      if (seg == 0 && lane == 0) orow[0] = (uint8_t)ft;
-      uint32_t *odat = reinterpret_cast<uint32_t *>(orow + 1) + xw0;
-      const uint32_t *row_up = raw + r * FB_PITCH + 4, *row_cur = row_up + FB_PITCH;
-      for (int q = (int)lane; q < FB_QPR; q += 32) {
-        const int qw = 4 * q;
-        if (xw0 + qw >= wmax) break;
-        const uint4 cur = *reinterpret_cast<const uint4 *>(row_cur + qw);
-        const uint4 up = *reinterpret_cast<const uint4 *>(row_up + qw);
-        const uint4 pf = *reinterpret_cast<const uint4 *>(pfw + r * FB_SWW + qw);
-        const uint32_t lc[2] = {row_cur[qw - 2], row_cur[qw - 1]};
-        const uint32_t lcc[2] = {lc[2 - BPW], lc[1]};
-        const uint4 o = filter_quad<BPW>(ft, cur, up, lcc, pf);
-        if (xw0 + qw + 4 <= wmax) {
-          *reinterpret_cast<uint4 *>(odat + qw) = o;
-        } else {
-          const uint32_t ov[4] = {o.x, o.y, o.z, o.w};
-          for (int j = 0; xw0 + qw + j < wmax; j++) odat[qw + j] = ov[j];
+        uint32_t *odat = reinterpret_cast<uint32_t *>(orow + 1) + qw;
+        if (whole) {
+          *reinterpret_cast<uint4 *>(odat) = o;
+        } else if (qw < wmax) {
+          odat[0] = o.x;
+          if (qw + 1 < wmax) odat[1] = o.y;
+          if (qw + 2 < wmax) odat[2] = o.z;
         }
       }
     }
+    __syncwarp();  // the stash is reused by the next unit
   }
-}
-
-cudaError_t launch_fused(const FusedParams &p, bool out16, int sm_count, cudaStream_t st) {
-  static int occ8 = -1, occ16 = -1;
-  if (occ8 < 0) {
-    cudaFuncSetAttribute(fused_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FB_SMEM);
-    cudaFuncSetAttribute(fused_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FB_SMEM);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ8, fused_kernel<1>, FB_THREADS, FB_SMEM);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ16, fused_kernel<2>, FB_THREADS, FB_SMEM);
-  }
-  const int occ = out16 ? occ16 : occ8;
-  if (occ < 1) return cudaErrorLaunchOutOfResources;
-  const uint32_t resident = (uint32_t)(occ * sm_count);
-  if (resident < p.nseg) return cudaErrorInvalidConfiguration;  // caller falls back to the two-pass path
-  const uint32_t n_items = p.n_bands * p.nseg;
-  const uint32_t grid = n_items < resident ? n_items : resident;
-  if (out16) fused_kernel<2><<<grid, FB_THREADS, FB_SMEM, st>>>(p);
-  else fused_kernel<1><<<grid, FB_THREADS, FB_SMEM, st>>>(p);
-  return cudaGetLastError();
 }
 
 uint32_t fused_rows_per_band() { return FB_R; }
 uint32_t fused_words_per_seg() { return FB_SWW; }
+uint32_t fused_unit_rows() { return FU_R; }
+uint32_t fused_unit_words() { return FU_SW; }
+
+cudaError_t launch_fused(const FusedParams &p, bool out16, int sm_count, cudaStream_t st) {
+  static int occ8 = -1, occ16 = -1;
+  if (occ8 < 0) {
+    cudaFuncSetAttribute(fused_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FU_CTA_SMEM);
+    cudaFuncSetAttribute(fused_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FU_CTA_SMEM);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ8, fused_kernel<1>, FU_WARPS * 32, FU_CTA_SMEM);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ16, fused_kernel<2>, FU_WARPS * 32, FU_CTA_SMEM);
+  }
+  const int occ = out16 ? occ16 : occ8;
+  if (occ < 1) return cudaErrorLaunchOutOfResources;
+  const uint32_t resident_warps = (uint32_t)(occ * sm_count * FU_WARPS);
+  if (resident_warps < p.nseg) return cudaErrorInvalidConfiguration;  // caller falls back to the two-pass path
+  const uint32_t n_units = p.n_bands * p.nseg;
+  const uint32_t want = (n_units + FU_WARPS - 1) / FU_WARPS, resident = (uint32_t)(occ * sm_count);
+  const uint32_t grid = want < resident ? want : resident;
+  if (out16) fused_kernel<2><<<grid, FU_WARPS * 32, FU_CTA_SMEM, st>>>(p);
+  else fused_kernel<1><<<grid, FU_WARPS * 32, FU_CTA_SMEM, st>>>(p);
+  return cudaGetLastError();
+}
 
 }  // namespace stitch

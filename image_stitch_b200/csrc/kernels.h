@@ -33,17 +33,18 @@ struct FilterParams {
   uint32_t lead;
 };
 
-// Fused composite + filter-select (fused.cu).  Bins are the items: FB_R rows x FB_SWW words,
-// each bin's tile list also holds tiles touching the row above / the pixel left of it.
+// Fused composite + filter-select (fused.cu).  Bins are FB_R rows x FB_SWW words; each bin's tile list
+// also holds tiles touching the row above / the pixel left of it.  Units (one per warp) are
+// fused_unit_rows() x fused_unit_words() and never straddle a bin.
 struct FusedParams {
   const DevTile *tiles;
   const uint32_t *bin_start;
   const uint32_t *bin_tiles;
-  uint32_t bins_x;            // = nseg
+  uint32_t bins_x;
   uint32_t canvas_w;
   uint32_t y_begin, y_end;    // canvas rows to produce
   uint32_t band0;             // absolute index (y / FB_R) of the first band
-  uint32_t n_bands, nseg;
+  uint32_t n_bands, nseg;    // unit bands in [y_begin,y_end), units per band
   uint32_t alpha_blend;
   uint32_t bg_lo, bg_hi;
   uint32_t *rowsum;           // [(y_end - y_begin)][8], zeroed
@@ -56,6 +57,8 @@ struct FusedParams {
 cudaError_t launch_fused(const FusedParams &p, bool out16, int sm_count, cudaStream_t st);
 uint32_t fused_rows_per_band();
 uint32_t fused_words_per_seg();
+uint32_t fused_unit_rows();
+uint32_t fused_unit_words();
 
 cudaError_t launch_unfilter(const UnfStream *d_streams, uint32_t n_streams, DevStatus *d_status, cudaStream_t st);
 cudaError_t launch_unfilter_wave(const UnfStream *d_streams, const UnfUnit *d_units, uint32_t n_units,
