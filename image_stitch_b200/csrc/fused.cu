@@ -34,14 +34,14 @@ namespace stitch {
 static constexpr int FB_R = 16;     // bin height (host binning granularity), rows
 static constexpr int FB_SWW = 512;  // bin width in 32-bit words
 
-static constexpr int FU_R = 16;                      // rows per unit
+static constexpr int FU_R = 8;                       // rows per unit
 static constexpr int FU_SW = 128;                    // words per unit row
 static constexpr int FU_WARPS = 4;                   // workers per CTA
 static constexpr int FU_RAW_WORDS = (FU_R + 1) * FU_SW;  // row 0 = predictor row above the unit
 static constexpr int FU_PF_WORDS = FU_R * FU_SW;
 static constexpr int FU_LC_WORDS = ((FU_R + 1) * 2 + 3) / 4 * 4;  // two words left of every row
 static constexpr int FU_WARP_WORDS = FU_RAW_WORDS + FU_PF_WORDS + FU_LC_WORDS;
-static constexpr size_t FU_CTA_SMEM = (size_t)FU_WARPS * FU_WARP_WORDS * 4;
+static constexpr size_t FU_CTA_SMEM = (size_t)FU_WARPS * 2 * FU_WARP_WORDS * 4;  // two stashes per warp
 static_assert(FB_R % FU_R == 0 && FB_SWW % FU_SW == 0, "a unit must lie inside one bin");
 
 // ---- packed-byte helpers ------------------------------------------------------
@@ -188,178 +188,218 @@ __device__ __forceinline__ void sweep_step(const uint32_t *raw_row, const uint32
   up = cur;
 }
 
+// What phase B needs to know about a unit after its sweep is over.
+struct UnitRef {
+  uint32_t band, seg;
+  int ya, nrows;
+};
+
+// ---- phase A + sweep + publish of one unit into `stash` ---------------------------
+template <int BPW>
+__device__ __forceinline__ UnitRef unit_costs(const FusedParams &p, const uint32_t u, uint32_t *stash, const uint32_t lane,
+                                              const uint32_t (&lmask)[5]) {
+  constexpr int PXQ = 4 / BPW;  // pixels per quad
+  uint32_t *raw = stash, *pfw = stash + FU_RAW_WORDS, *lcs = pfw + FU_PF_WORDS;
+  const int wmax = (int)p.canvas_w * BPW;  // words per canvas row
+  const uint32_t band = u / p.nseg, seg = u - band * p.nseg;
+  const uint32_t band_abs = p.band0 + band;
+  const int ya = max((int)p.y_begin, (int)(band_abs * FU_R));
+  const int yb = min((int)p.y_end, (int)((band_abs + 1) * FU_R));
+  const int nrows = yb - ya;
+  const int xw0 = (int)seg * FU_SW, qw = xw0 + 4 * (int)lane;
+  const bool guard = xw0 + FU_SW > wmax;
+  const uint32_t bin = (band_abs * FU_R / FB_R) * p.bins_x + (uint32_t)(xw0 / FB_SWW);
+  const uint32_t b0 = p.bin_start[bin], n_list = p.bin_start[bin + 1] - b0;
+  const uint32_t *list = p.bin_tiles + b0;
+
+  // ---- is the unit a plain window of one tile? (warp-uniform) ----
+  const int X0 = xw0 / BPW, X1 = min((int)p.canvas_w, (xw0 + FU_SW) / BPW);  // unit's pixel columns
+  const uint8_t *fast_src = nullptr;  // tile byte that lands on (X0, ya)
+  uint32_t fast_pitch = 0;
+  bool halo_fast = false, left_fast = false;
+  for (int k = (int)n_list - 1; k >= 0; k--) {
+    const DevTile &t = p.tiles[list[k]];
+    if (t.y0 >= yb || t.y1 <= ya || t.x0 >= X1 || t.x1 <= X0) continue;
+    // top-most tile that touches the unit
+    const bool covers = t.y0 <= ya && t.y1 >= yb && t.x0 <= X0 && t.x1 >= X1;
+    const bool overwrite = p.alpha_blend == 0u || t.opaque;
+    const bool native = BPW == 1 ? t.fmt == FMT_RGBA8 : t.fmt == FMT_RGBA16;
+    if (covers && overwrite && native && ((X1 - X0) % PXQ) == 0) {
+      const uint8_t *src = t.pix + (size_t)(ya - t.y0 + t.sy0) * t.pitch + (size_t)(X0 - t.x0 + t.sx0) * (4u * BPW);
+      if (((reinterpret_cast<uintptr_t>(src) | t.pitch) & 15u) == 0) {
+        fast_src = src; fast_pitch = t.pitch;
+        halo_fast = t.y0 <= ya - 1;
+        left_fast = t.x0 <= X0 - 1;
+      }
+    }
+    break;
+  }
+
+  // ---- phase A: raw stash <- composited pixels of rows ya-1 .. yb-1 ----
+  {
+    uint32_t *dst = raw + 4 * lane;
+    const bool inside = qw < wmax;
+    // predictor row
+    if (ya == 0 || !inside) *reinterpret_cast<uint4 *>(dst) = make_uint4(0u, 0u, 0u, 0u);  // previousLine === null
+    else if (fast_src && halo_fast) fu_cp_async16(dst, fast_src - fast_pitch + 16u * lane);
+    else *reinterpret_cast<uint4 *>(dst) = compose_quad<BPW>(p, list, n_list, qw, ya - 1);
+    dst += FU_SW;
+    if (!inside) {
+      for (int rr = 0; rr < nrows; rr++, dst += FU_SW) *reinterpret_cast<uint4 *>(dst) = make_uint4(0u, 0u, 0u, 0u);
+    } else if (fast_src) {
+      const uint8_t *src = fast_src + 16u * lane;
+      for (int rr = 0; rr < nrows; rr++, dst += FU_SW, src += fast_pitch) fu_cp_async16(dst, src);
+    } else {
+      for (int rr = 0; rr < nrows; rr++, dst += FU_SW) *reinterpret_cast<uint4 *>(dst) = compose_quad<BPW>(p, list, n_list, qw, ya + rr);
+    }
+  }
+  if ((int)lane <= nrows) {  // the pixel just left of the unit (0 at the canvas edge)
+    const int y = ya - 1 + (int)lane;
+    uint32_t c0 = 0u, c1 = 0u;
+    if (y >= 0 && xw0 > 0) {
+      if (fast_src && left_fast && (lane > 0 || halo_fast)) {
+        const uint32_t *lp = reinterpret_cast<const uint32_t *>(fast_src + (ptrdiff_t)((int)lane - 1) * (ptrdiff_t)fast_pitch);
+        c1 = __ldg(lp - 1);
+        if (BPW == 2) c0 = __ldg(lp - 2);
+      } else {
+        const uint4 v = compose_quad<BPW>(p, list, n_list, (xw0 - BPW) & ~3, y);
+        c1 = v.w;
+        if (BPW == 2) c0 = v.z;
+      }
+    }
+    lcs[lane * 2] = c0;
+    lcs[lane * 2 + 1] = c1;
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  __syncwarp();
+
+  // ---- sweep: filter costs of every row, Paeth residuals into the stash ----
+  {
+    uint4 up = *reinterpret_cast<const uint4 *>(raw + 4 * lane);
+    uint32_t l0 = __shfl_up_sync(0xffffffffu, up.z, 1), l1 = __shfl_up_sync(0xffffffffu, up.w, 1);
+    if (lane == 0u) { l0 = lcs[0]; l1 = lcs[1]; }
+    H4 hA[4], hlA[2], hB[4], hlB[2];  // two unpacked rows, used alternately as "above" and "current"
+    hA[0] = unpack_h4(up.x); hA[1] = unpack_h4(up.y); hA[2] = unpack_h4(up.z); hA[3] = unpack_h4(up.w);
+    hlA[0] = unpack_h4(l0); hlA[1] = unpack_h4(l1);
+    const uint32_t *raw_row = raw + FU_SW;
+    const uint32_t *lcs_row = lcs + 2;
+    uint32_t *pf_row = pfw;
+    uint32_t *rs_row = p.rowsum + (size_t)(ya - (int)p.y_begin) * 8;
+    int r = 0;
+    for (; r + 2 <= nrows; r += 2) {
+      sweep_step<BPW>(raw_row, lcs_row, pf_row, rs_row, lane, lmask, guard, qw, wmax, up, hA, hlA, hB, hlB);
+      sweep_step<BPW>(raw_row + FU_SW, lcs_row + 2, pf_row + FU_SW, rs_row + 8, lane, lmask, guard, qw, wmax, up, hB,
+                      hlB, hA, hlA);
+      raw_row += 2 * FU_SW; lcs_row += 4; pf_row += 2 * FU_SW; rs_row += 16;
+    }
+    if (r < nrows) sweep_step<BPW>(raw_row, lcs_row, pf_row, rs_row, lane, lmask, guard, qw, wmax, up, hA, hlA, hB, hlB);
+  }
+  // publish: the unit's partial sums are out; count it as done for its band
+  __syncwarp();
+  if (lane == 0u) {
+    __threadfence();
+    atomicAdd(p.band_done + band, 1u);
+  }
+  __syncwarp();
+  UnitRef ref;
+  ref.band = band; ref.seg = seg; ref.ya = ya; ref.nrows = nrows;
+  return ref;
+}
+
+// ---- phase B: wait for the band, pick the winner per row, write the filtered bytes ----
+template <int BPW>
+__device__ __forceinline__ void unit_emit(const FusedParams &p, const UnitRef &ref, const uint32_t *stash, const uint32_t lane) {
+  const uint32_t *raw = stash, *pfw = stash + FU_RAW_WORDS, *lcs = pfw + FU_PF_WORDS;
+  const int wmax = (int)p.canvas_w * BPW;
+  const int ya = ref.ya, nrows = ref.nrows;
+  const int qw = (int)ref.seg * FU_SW + 4 * (int)lane;
+  // Every lane polls the same word (one broadcast load), so the warp never diverges here.
+  while (fu_ld_acquire(p.band_done + ref.band) < p.nseg) __nanosleep(64);
+
+  uint32_t my_ft = 0u;
+  if ((int)lane < nrows) {
+    const uint32_t *rs = p.rowsum + (size_t)(ya + (int)lane - (int)p.y_begin) * 8;
+    const uint4 v = __ldcg(reinterpret_cast<const uint4 *>(rs));
+    const uint32_t v4 = __ldcg(rs + 4);
+    uint32_t best = v.x;
+    if (v.y < best) { best = v.y; my_ft = 1u; }   // strict '<': first minimum wins (png-filter.ts:174)
+    if (v.z < best) { best = v.z; my_ft = 2u; }
+    if (v.w < best) { best = v.w; my_ft = 3u; }
+    if (v4 < best) { best = v4; my_ft = 4u; }
+  }
+  uint8_t *orow = p.out + (size_t)(ya - (int)p.y_begin) * p.out_pitch + p.lead;
+  const uint32_t *cur_row = raw + FU_SW + 4 * lane, *pf_row = pfw + 4 * lane, *lcs_row = lcs + 2;
+  const bool whole = qw + 4 <= wmax;
+  for (int r = 0; r < nrows; r++, orow += p.out_pitch, cur_row += FU_SW, pf_row += FU_SW, lcs_row += 2) {
+    const uint32_t ft = __shfl_sync(0xffffffffu, my_ft, r);
+    if (ref.seg == 0u && lane == 0u) orow[0] = (uint8_t)ft;
+    uint4 o;
+    if (ft == 4u) {
+      o = *reinterpret_cast<const uint4 *>(pf_row);
+    } else {
+      const uint4 cur = *reinterpret_cast<const uint4 *>(cur_row);
+      o = cur;
+      if (ft == 2u) {
+        const uint4 upq = *reinterpret_cast<const uint4 *>(cur_row - FU_SW);
+        o = make_uint4(sub4(cur.x, upq.x), sub4(cur.y, upq.y), sub4(cur.z, upq.z), sub4(cur.w, upq.w));
+      } else if (ft != 0u) {
+        uint32_t c0 = BPW == 2 ? __shfl_up_sync(0xffffffffu, cur.z, 1) : 0u;
+        uint32_t c1 = __shfl_up_sync(0xffffffffu, cur.w, 1);
+        if (lane == 0u) { c0 = lcs_row[0]; c1 = lcs_row[1]; }
+        const uint32_t a0 = BPW == 1 ? c1 : c0, a1 = BPW == 1 ? cur.x : c1;
+        const uint32_t a2 = BPW == 1 ? cur.y : cur.x, a3 = BPW == 1 ? cur.z : cur.y;
+        if (ft == 1u) {
+          o = make_uint4(sub4(cur.x, a0), sub4(cur.y, a1), sub4(cur.z, a2), sub4(cur.w, a3));
+        } else {
+          const uint4 upq = *reinterpret_cast<const uint4 *>(cur_row - FU_SW);
+          o = make_uint4(sub4(cur.x, avg4(a0, upq.x)), sub4(cur.y, avg4(a1, upq.y)), sub4(cur.z, avg4(a2, upq.z)),
+                         sub4(cur.w, avg4(a3, upq.w)));
+        }
+      }
+    }
+    uint32_t *odat = reinterpret_cast<uint32_t *>(orow + 1) + qw;
+    if (whole) {
+      *reinterpret_cast<uint4 *>(odat) = o;
+    } else if (qw < wmax) {
+      odat[0] = o.x;
+      if (qw + 1 < wmax) odat[1] = o.y;
+      if (qw + 2 < wmax) odat[2] = o.z;
+    }
+  }
+  __syncwarp();  // the stash is free again
+}
+
+// Software pipeline per warp: costs(u_k) run before emit(u_{k-1}), so that the band of u_{k-1} has had a
+// whole sweep's time to complete and the poll in unit_emit returns at once; the next ticket is fetched
+// while the current unit is swept.  Two stashes per warp.
 template <int BPW>
 __global__ void __launch_bounds__(FU_WARPS * 32) fused_kernel(const FusedParams p) {
   extern __shared__ __align__(16) uint32_t fu_smem[];
   const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-  uint32_t *raw = fu_smem + warp * FU_WARP_WORDS;  // (FU_R+1) x 128 words, row 0 = predictor row
-  uint32_t *pfw = raw + FU_RAW_WORDS;              // Paeth-filtered words
-  uint32_t *lcs = pfw + FU_PF_WORDS;               // [row][2]: the two words left of the unit
+  uint32_t *stash0 = fu_smem + warp * (2 * FU_WARP_WORDS), *stash1 = stash0 + FU_WARP_WORDS;
   const uint32_t n_units = p.n_bands * p.nseg;
-  const int wmax = (int)p.canvas_w * BPW;          // words per canvas row
-  constexpr int PXQ = 4 / BPW;                     // pixels per quad
-  uint32_t lmask[5];                               // lane f keeps candidate f's row sum
+  uint32_t lmask[5];  // lane f keeps candidate f's row sum
 #pragma unroll
   for (int f = 0; f < 5; f++) lmask[f] = lane == (uint32_t)f ? 0xffffffffu : 0u;
 
-  for (;;) {
-    uint32_t u = 0u;
-    if (lane == 0u) u = atomicAdd(p.ticket, 1u);
-    u = __shfl_sync(0xffffffffu, u, 0);
-    if (u >= n_units) break;
-    const uint32_t band = u / p.nseg, seg = u - band * p.nseg;
-    const uint32_t band_abs = p.band0 + band;
-    const int ya = max((int)p.y_begin, (int)(band_abs * FU_R));
-    const int yb = min((int)p.y_end, (int)((band_abs + 1) * FU_R));
-    const int nrows = yb - ya;
-    const int xw0 = (int)seg * FU_SW, qw = xw0 + 4 * (int)lane;
-    const bool guard = xw0 + FU_SW > wmax;
-    const uint32_t bin = (band_abs * FU_R / FB_R) * p.bins_x + (uint32_t)(xw0 / FB_SWW);
-    const uint32_t b0 = p.bin_start[bin], n_list = p.bin_start[bin + 1] - b0;
-    const uint32_t *list = p.bin_tiles + b0;
-
-    // ---- is the unit a plain window of one tile? (warp-uniform) ----
-    const int X0 = xw0 / BPW, X1 = min((int)p.canvas_w, (xw0 + FU_SW) / BPW);  // unit's pixel columns
-    const uint8_t *fast_src = nullptr;  // tile byte that lands on (X0, ya)
-    uint32_t fast_pitch = 0;
-    bool halo_fast = false, left_fast = false;
-    for (int k = (int)n_list - 1; k >= 0; k--) {
-      const DevTile &t = p.tiles[list[k]];
-      if (t.y0 >= yb || t.y1 <= ya || t.x0 >= X1 || t.x1 <= X0) continue;
-      // top-most tile that touches the unit
-      const bool covers = t.y0 <= ya && t.y1 >= yb && t.x0 <= X0 && t.x1 >= X1;
-      const bool overwrite = p.alpha_blend == 0u || t.opaque;
-      const bool native = BPW == 1 ? t.fmt == FMT_RGBA8 : t.fmt == FMT_RGBA16;
-      if (covers && overwrite && native && ((X1 - X0) % PXQ) == 0) {
-        const uint8_t *src = t.pix + (size_t)(ya - t.y0 + t.sy0) * t.pitch + (size_t)(X0 - t.x0 + t.sx0) * (4u * BPW);
-        if (((reinterpret_cast<uintptr_t>(src) | t.pitch) & 15u) == 0) {
-          fast_src = src; fast_pitch = t.pitch;
-          halo_fast = t.y0 <= ya - 1;
-          left_fast = t.x0 <= X0 - 1;
-        }
-      }
-      break;
-    }
-
-    // ---- phase A: raw stash <- composited pixels of rows ya-1 .. yb-1 ----
-    for (int rr = 0; rr <= nrows; rr++) {
-      const int y = ya - 1 + rr;
-      uint32_t *dst = raw + rr * FU_SW + 4 * lane;
-      if (y < 0 || qw >= wmax) {  // previousLine === null above row 0: predictor bytes are 0
-        *reinterpret_cast<uint4 *>(dst) = make_uint4(0u, 0u, 0u, 0u);
-      } else if (fast_src && (rr > 0 || halo_fast)) {
-        fu_cp_async16(dst, fast_src + (ptrdiff_t)(rr - 1) * (ptrdiff_t)fast_pitch + 16u * lane);
-      } else {
-        *reinterpret_cast<uint4 *>(dst) = compose_quad<BPW>(p, list, n_list, qw, y);
-      }
-    }
-    if ((int)lane <= nrows) {  // the pixel just left of the unit (0 at the canvas edge)
-      const int y = ya - 1 + (int)lane;
-      uint32_t c0 = 0u, c1 = 0u;
-      if (y >= 0 && xw0 > 0) {
-        if (fast_src && left_fast && (lane > 0 || halo_fast)) {
-          const uint32_t *lp = reinterpret_cast<const uint32_t *>(fast_src + (ptrdiff_t)((int)lane - 1) * (ptrdiff_t)fast_pitch);
-          c1 = __ldg(lp - 1);
-          if (BPW == 2) c0 = __ldg(lp - 2);
-        } else {
-          const uint4 v = compose_quad<BPW>(p, list, n_list, (xw0 - BPW) & ~3, y);
-          c1 = v.w;
-          if (BPW == 2) c0 = v.z;
-        }
-      }
-      lcs[lane * 2] = c0;
-      lcs[lane * 2 + 1] = c1;
-    }
-    asm volatile("cp.async.commit_group;" ::: "memory");
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
-    __syncwarp();
-
-    // ---- sweep: filter costs of every row, Paeth residuals into the stash ----
-    {
-      uint4 up = *reinterpret_cast<const uint4 *>(raw + 4 * lane);
-      uint32_t l0 = __shfl_up_sync(0xffffffffu, up.z, 1), l1 = __shfl_up_sync(0xffffffffu, up.w, 1);
-      if (lane == 0u) { l0 = lcs[0]; l1 = lcs[1]; }
-      H4 hA[4], hlA[2], hB[4], hlB[2];  // two unpacked rows, used alternately as "above" and "current"
-      hA[0] = unpack_h4(up.x); hA[1] = unpack_h4(up.y); hA[2] = unpack_h4(up.z); hA[3] = unpack_h4(up.w);
-      hlA[0] = unpack_h4(l0); hlA[1] = unpack_h4(l1);
-      const uint32_t *raw_row = raw + FU_SW;
-      const uint32_t *lcs_row = lcs + 2;
-      uint32_t *pf_row = pfw;
-      uint32_t *rs_row = p.rowsum + (size_t)(ya - (int)p.y_begin) * 8;
-      int r = 0;
-      for (; r + 2 <= nrows; r += 2) {
-        sweep_step<BPW>(raw_row, lcs_row, pf_row, rs_row, lane, lmask, guard, qw, wmax, up, hA, hlA, hB, hlB);
-        sweep_step<BPW>(raw_row + FU_SW, lcs_row + 2, pf_row + FU_SW, rs_row + 8, lane, lmask, guard, qw, wmax, up, hB,
-                        hlB, hA, hlA);
-        raw_row += 2 * FU_SW; lcs_row += 4; pf_row += 2 * FU_SW; rs_row += 16;
-      }
-      if (r < nrows) sweep_step<BPW>(raw_row, lcs_row, pf_row, rs_row, lane, lmask, guard, qw, wmax, up, hA, hlA, hB, hlB);
-    }
-    // publish: the unit's partial sums are out; count it as done for its band, wait for the others.
-    // Every lane polls the same word (one broadcast load), so the warp never diverges here.
-    __syncwarp();
-    if (lane == 0u) {
-      __threadfence();
-      atomicAdd(p.band_done + band, 1u);
-    }
-    __syncwarp();
-    while (fu_ld_acquire(p.band_done + band) < p.nseg) __nanosleep(64);
-
-    // ---- phase B: winner per row, filtered bytes out ----
-    uint32_t my_ft = 0u;
-    if ((int)lane < nrows) {
-      const uint32_t *rs = p.rowsum + (size_t)(ya + (int)lane - (int)p.y_begin) * 8;
-      const uint4 v = __ldcg(reinterpret_cast<const uint4 *>(rs));
-      const uint32_t v4 = __ldcg(rs + 4);
-      uint32_t best = v.x;
-      if (v.y < best) { best = v.y; my_ft = 1u; }   // strict '<': first minimum wins (png-filter.ts:174)
-      if (v.z < best) { best = v.z; my_ft = 2u; }
-      if (v.w < best) { best = v.w; my_ft = 3u; }
-      if (v4 < best) { best = v4; my_ft = 4u; }
-    }
-    {
-      uint8_t *orow = p.out + (size_t)(ya - (int)p.y_begin) * p.out_pitch + p.lead;
-      const uint32_t *cur_row = raw + FU_SW + 4 * lane, *pf_row = pfw + 4 * lane, *lcs_row = lcs + 2;
-      const bool whole = qw + 4 <= wmax;
-      for (int r = 0; r < nrows; r++, orow += p.out_pitch, cur_row += FU_SW, pf_row += FU_SW, lcs_row += 2) {
-        const uint32_t ft = __shfl_sync(0xffffffffu, my_ft, r);
-        if (seg == 0u && lane == 0u) orow[0] = (uint8_t)ft;
-        uint4 o;
-        if (ft == 4u) {
-          o = *reinterpret_cast<const uint4 *>(pf_row);
-        } else {
-          const uint4 cur = *reinterpret_cast<const uint4 *>(cur_row);
-          o = cur;
-          if (ft == 2u) {
-            const uint4 upq = *reinterpret_cast<const uint4 *>(cur_row - FU_SW);
-            o = make_uint4(sub4(cur.x, upq.x), sub4(cur.y, upq.y), sub4(cur.z, upq.z), sub4(cur.w, upq.w));
-          } else if (ft != 0u) {
-            uint32_t c0 = BPW == 2 ? __shfl_up_sync(0xffffffffu, cur.z, 1) : 0u;
-            uint32_t c1 = __shfl_up_sync(0xffffffffu, cur.w, 1);
-            if (lane == 0u) { c0 = lcs_row[0]; c1 = lcs_row[1]; }
-            const uint32_t a0 = BPW == 1 ? c1 : c0, a1 = BPW == 1 ? cur.x : c1;
-            const uint32_t a2 = BPW == 1 ? cur.y : cur.x, a3 = BPW == 1 ? cur.z : cur.y;
-            if (ft == 1u) {
-              o = make_uint4(sub4(cur.x, a0), sub4(cur.y, a1), sub4(cur.z, a2), sub4(cur.w, a3));
-            } else {
-              const uint4 upq = *reinterpret_cast<const uint4 *>(cur_row - FU_SW);
-              o = make_uint4(sub4(cur.x, avg4(a0, upq.x)), sub4(cur.y, avg4(a1, upq.y)), sub4(cur.z, avg4(a2, upq.z)),
-                             sub4(cur.w, avg4(a3, upq.w)));
-            }
-          }
-        }
-        uint32_t *odat = reinterpret_cast<uint32_t *>(orow + 1) + qw;
-        if (whole) {
-          *reinterpret_cast<uint4 *>(odat) = o;
-        } else if (qw < wmax) {
-          odat[0] = o.x;
-          if (qw + 1 < wmax) odat[1] = o.y;
-          if (qw + 2 < wmax) odat[2] = o.z;
-        }
-      }
-    }
-    __syncwarp();  // the stash is reused by the next unit
+  uint32_t u = 0u;
+  if (lane == 0u) u = atomicAdd(p.ticket, 1u);
+  u = __shfl_sync(0xffffffffu, u, 0);
+  UnitRef prev;
+  prev.nrows = 0; prev.band = 0; prev.seg = 0; prev.ya = 0;
+  bool have_prev = false;
+  uint32_t *cur_stash = stash0, *prev_stash = stash1;
+  while (u < n_units) {
+    uint32_t u_next = 0u;
+    if (lane == 0u) u_next = atomicAdd(p.ticket, 1u);  // consumed after the sweep
+    const UnitRef cur = unit_costs<BPW>(p, u, cur_stash, lane, lmask);
+    if (have_prev) unit_emit<BPW>(p, prev, prev_stash, lane);
+    prev = cur; have_prev = true;
+    uint32_t *t = cur_stash; cur_stash = prev_stash; prev_stash = t;
+    u = __shfl_sync(0xffffffffu, u_next, 0);
   }
+  if (have_prev) unit_emit<BPW>(p, prev, prev_stash, lane);
 }
 
 uint32_t fused_rows_per_band() { return FB_R; }
