@@ -574,10 +574,10 @@ extern "C" int stitch_job_run_band(stitch_job *job, uint32_t y0, uint32_t y1, ui
     if ((rc = ensure_buffer(ctx, &job->d_out, &job->out_bytes, job->out_pitch * (size_t)n_rows))) return rc;
     bool fused_done = false;
     if (!job->force_two_pass) {
-      // fused single pass: rowsum[n_rows][8] | band_done[n_bands] | ticket
+      // fused single pass: rowsum[n_rows][8] (64-bit) | ticket
       const uint32_t bh = fused_unit_rows();
       const uint32_t band0 = y0 / bh, n_bands = (y1 - 1) / bh - band0 + 1;
-      const size_t words = (size_t)n_rows * 8 + n_bands + 4;
+      const size_t words = (size_t)n_rows * 16 + 4;
       if (words > job->sync_words) {
         dev_free(ctx, job->d_sync); job->d_sync = nullptr; job->sync_words = 0;
         if ((rc = dev_alloc(ctx, (void **)&job->d_sync, words * 4))) return rc;
@@ -590,7 +590,7 @@ extern "C" int stitch_job_run_band(stitch_job *job, uint32_t y0, uint32_t y1, ui
       fp.n_bands = n_bands;
       fp.nseg = (uint32_t)((row_bytes / 4 + fused_unit_words() - 1) / fused_unit_words()); fp.alpha_blend = jd.alpha_blend;
       bg_words(jd, fp.bg_lo, fp.bg_hi);
-      fp.rowsum = job->d_sync; fp.band_done = job->d_sync + (size_t)n_rows * 8; fp.ticket = fp.band_done + n_bands;
+      fp.rowsum = reinterpret_cast<unsigned long long *>(job->d_sync); fp.ticket = job->d_sync + (size_t)n_rows * 16;
       fp.out = job->d_out; fp.out_pitch = job->out_pitch; fp.lead = (uint32_t)job->out_lead;
       cudaError_t fe = launch_fused(fp, jd.out_bit_depth == 16, ctx->sm_count, ctx->stream);
       if (fe == cudaSuccess) { fused_done = true; launches += 1; }

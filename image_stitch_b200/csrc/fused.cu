@@ -132,11 +132,6 @@ __device__ __forceinline__ void fu_cp_async16(void *smem, const void *gmem) {
   const uint32_t sa = (uint32_t)__cvta_generic_to_shared(smem);
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gmem) : "memory");
 }
-__device__ __forceinline__ uint32_t fu_ld_acquire(const uint32_t *p) {
-  uint32_t v;
-  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
 
 // One row of the sweep.  GUARD: the unit reaches past the right edge of the canvas.
 // hb/hlu: the row above, unpacked (input); hx/hlc: this row, unpacked (output, becomes the next row's hb/hlu).
@@ -171,7 +166,7 @@ __device__ __forceinline__ void sweep_row(const uint4 cur, const uint32_t lc0, c
 // Row r of the unit: loads, left context, costs, warp reduction, one red.global per candidate.
 template <int BPW>
 __device__ __forceinline__ void sweep_step(const uint32_t *raw_row, const uint32_t *lcs_row, uint32_t *pf_row,
-                                           uint32_t *rs_row, uint32_t lane, const uint32_t (&lmask)[5], bool guard,
+                                           unsigned long long *rs_row, uint32_t lane, const uint32_t (&lmask)[5], bool guard,
                                            int qw, int wmax, uint4 &up, const H4 (&hb)[4], const H4 (&hlu)[2],
                                            H4 (&hx)[4], H4 (&hlc)[2]) {
   const uint4 cur = *reinterpret_cast<const uint4 *>(raw_row + 4 * lane);
@@ -184,65 +179,77 @@ __device__ __forceinline__ void sweep_step(const uint32_t *raw_row, const uint32
   uint32_t v = 0u;
 #pragma unroll
   for (int f = 0; f < 5; f++) v |= __reduce_add_sync(0xffffffffu, sum[f]) & lmask[f];
-  if (lane < 5u) atomicAdd(rs_row + lane, v);
+  if (lane < 5u) atomicAdd(rs_row + lane, (1ull << 32) | (unsigned long long)v);  // sum | arrival count
   up = cur;
 }
 
-// What phase B needs to know about a unit after its sweep is over.
-struct UnitRef {
-  uint32_t band, seg;
-  int ya, nrows;
+// Everything a warp needs to know about one unit; built by unit_plan() one iteration ahead so that the
+// bin -> list -> tile load chain overlaps with the cp.async traffic of the unit before it.
+struct UnitPlan {
+  uint32_t seg;
+  int ya, nrows, xw0;
+  const uint32_t *list;
+  uint32_t n_list;
+  const uint8_t *fast_src;  // tile byte that lands on (X0, ya) when the unit is a plain window of one tile
+  uint32_t fast_pitch;
+  bool halo_fast, left_fast;
 };
 
-// ---- phase A + sweep + publish of one unit into `stash` ---------------------------
 template <int BPW>
-__device__ __forceinline__ UnitRef unit_costs(const FusedParams &p, const uint32_t u, uint32_t *stash, const uint32_t lane,
-                                              const uint32_t (&lmask)[5]) {
+__device__ __forceinline__ UnitPlan unit_plan(const FusedParams &p, const uint32_t u) {
   constexpr int PXQ = 4 / BPW;  // pixels per quad
-  uint32_t *raw = stash, *pfw = stash + FU_RAW_WORDS, *lcs = pfw + FU_PF_WORDS;
-  const int wmax = (int)p.canvas_w * BPW;  // words per canvas row
-  const uint32_t band = u / p.nseg, seg = u - band * p.nseg;
+  UnitPlan pl;
+  const uint32_t band = u / p.nseg;
+  pl.seg = u - band * p.nseg;
   const uint32_t band_abs = p.band0 + band;
   const int ya = max((int)p.y_begin, (int)(band_abs * FU_R));
   const int yb = min((int)p.y_end, (int)((band_abs + 1) * FU_R));
-  const int nrows = yb - ya;
-  const int xw0 = (int)seg * FU_SW, qw = xw0 + 4 * (int)lane;
-  const bool guard = xw0 + FU_SW > wmax;
+  pl.ya = ya; pl.nrows = yb - ya;
+  const int xw0 = (int)pl.seg * FU_SW;
+  pl.xw0 = xw0;
   const uint32_t bin = (band_abs * FU_R / FB_R) * p.bins_x + (uint32_t)(xw0 / FB_SWW);
-  const uint32_t b0 = p.bin_start[bin], n_list = p.bin_start[bin + 1] - b0;
+  const uint32_t b0 = __ldg(p.bin_start + bin), n_list = __ldg(p.bin_start + bin + 1) - b0;
   const uint32_t *list = p.bin_tiles + b0;
-
-  // ---- is the unit a plain window of one tile? (warp-uniform) ----
+  pl.list = list; pl.n_list = n_list;
   const int X0 = xw0 / BPW, X1 = min((int)p.canvas_w, (xw0 + FU_SW) / BPW);  // unit's pixel columns
-  const uint8_t *fast_src = nullptr;  // tile byte that lands on (X0, ya)
-  uint32_t fast_pitch = 0;
-  bool halo_fast = false, left_fast = false;
+  pl.fast_src = nullptr; pl.fast_pitch = 0; pl.halo_fast = false; pl.left_fast = false;
   for (int k = (int)n_list - 1; k >= 0; k--) {
-    const DevTile &t = p.tiles[list[k]];
-    if (t.y0 >= yb || t.y1 <= ya || t.x0 >= X1 || t.x1 <= X0) continue;
+    const DevTile &t = p.tiles[__ldg(list + k)];
+    const int tx0 = t.x0, ty0 = t.y0, tx1 = t.x1, ty1 = t.y1;
+    if (ty0 >= yb || ty1 <= ya || tx0 >= X1 || tx1 <= X0) continue;
     // top-most tile that touches the unit
-    const bool covers = t.y0 <= ya && t.y1 >= yb && t.x0 <= X0 && t.x1 >= X1;
+    const bool covers = ty0 <= ya && ty1 >= yb && tx0 <= X0 && tx1 >= X1;
     const bool overwrite = p.alpha_blend == 0u || t.opaque;
     const bool native = BPW == 1 ? t.fmt == FMT_RGBA8 : t.fmt == FMT_RGBA16;
     if (covers && overwrite && native && ((X1 - X0) % PXQ) == 0) {
-      const uint8_t *src = t.pix + (size_t)(ya - t.y0 + t.sy0) * t.pitch + (size_t)(X0 - t.x0 + t.sx0) * (4u * BPW);
-      if (((reinterpret_cast<uintptr_t>(src) | t.pitch) & 15u) == 0) {
-        fast_src = src; fast_pitch = t.pitch;
-        halo_fast = t.y0 <= ya - 1;
-        left_fast = t.x0 <= X0 - 1;
+      const uint32_t pitch = t.pitch;
+      const uint8_t *src = t.pix + (size_t)(ya - ty0 + t.sy0) * pitch + (size_t)(X0 - tx0 + t.sx0) * (4u * BPW);
+      if (((reinterpret_cast<uintptr_t>(src) | pitch) & 15u) == 0) {
+        pl.fast_src = src; pl.fast_pitch = pitch;
+        pl.halo_fast = ty0 <= ya - 1;
+        pl.left_fast = tx0 <= X0 - 1;
       }
     }
     break;
   }
+  return pl;
+}
 
-  // ---- phase A: raw stash <- composited pixels of rows ya-1 .. yb-1 ----
+// ---- phase A: raw stash <- composited pixels of rows ya-1 .. yb-1 (cp.async left in flight) ----
+template <int BPW>
+__device__ __forceinline__ void unit_load(const FusedParams &p, const UnitPlan &pl, uint32_t *stash, const uint32_t lane) {
+  uint32_t *raw = stash, *lcs = stash + FU_RAW_WORDS + FU_PF_WORDS;
+  const int wmax = (int)p.canvas_w * BPW;  // words per canvas row
+  const int ya = pl.ya, nrows = pl.nrows, xw0 = pl.xw0, qw = xw0 + 4 * (int)lane;
+  const uint8_t *fast_src = pl.fast_src;
+  const uint32_t fast_pitch = pl.fast_pitch;
   {
     uint32_t *dst = raw + 4 * lane;
     const bool inside = qw < wmax;
     // predictor row
     if (ya == 0 || !inside) *reinterpret_cast<uint4 *>(dst) = make_uint4(0u, 0u, 0u, 0u);  // previousLine === null
-    else if (fast_src && halo_fast) fu_cp_async16(dst, fast_src - fast_pitch + 16u * lane);
-    else *reinterpret_cast<uint4 *>(dst) = compose_quad<BPW>(p, list, n_list, qw, ya - 1);
+    else if (fast_src && pl.halo_fast) fu_cp_async16(dst, fast_src - fast_pitch + 16u * lane);
+    else *reinterpret_cast<uint4 *>(dst) = compose_quad<BPW>(p, pl.list, pl.n_list, qw, ya - 1);
     dst += FU_SW;
     if (!inside) {
       for (int rr = 0; rr < nrows; rr++, dst += FU_SW) *reinterpret_cast<uint4 *>(dst) = make_uint4(0u, 0u, 0u, 0u);
@@ -250,19 +257,20 @@ __device__ __forceinline__ UnitRef unit_costs(const FusedParams &p, const uint32
       const uint8_t *src = fast_src + 16u * lane;
       for (int rr = 0; rr < nrows; rr++, dst += FU_SW, src += fast_pitch) fu_cp_async16(dst, src);
     } else {
-      for (int rr = 0; rr < nrows; rr++, dst += FU_SW) *reinterpret_cast<uint4 *>(dst) = compose_quad<BPW>(p, list, n_list, qw, ya + rr);
+      for (int rr = 0; rr < nrows; rr++, dst += FU_SW)
+        *reinterpret_cast<uint4 *>(dst) = compose_quad<BPW>(p, pl.list, pl.n_list, qw, ya + rr);
     }
   }
   if ((int)lane <= nrows) {  // the pixel just left of the unit (0 at the canvas edge)
     const int y = ya - 1 + (int)lane;
     uint32_t c0 = 0u, c1 = 0u;
     if (y >= 0 && xw0 > 0) {
-      if (fast_src && left_fast && (lane > 0 || halo_fast)) {
+      if (fast_src && pl.left_fast && (lane > 0 || pl.halo_fast)) {
         const uint32_t *lp = reinterpret_cast<const uint32_t *>(fast_src + (ptrdiff_t)((int)lane - 1) * (ptrdiff_t)fast_pitch);
         c1 = __ldg(lp - 1);
         if (BPW == 2) c0 = __ldg(lp - 2);
       } else {
-        const uint4 v = compose_quad<BPW>(p, list, n_list, (xw0 - BPW) & ~3, y);
+        const uint4 v = compose_quad<BPW>(p, pl.list, pl.n_list, (xw0 - BPW) & ~3, y);
         c1 = v.w;
         if (BPW == 2) c0 = v.z;
       }
@@ -271,62 +279,74 @@ __device__ __forceinline__ UnitRef unit_costs(const FusedParams &p, const uint32
     lcs[lane * 2 + 1] = c1;
   }
   asm volatile("cp.async.commit_group;" ::: "memory");
-  asm volatile("cp.async.wait_group 0;" ::: "memory");
-  __syncwarp();
-
-  // ---- sweep: filter costs of every row, Paeth residuals into the stash ----
-  {
-    uint4 up = *reinterpret_cast<const uint4 *>(raw + 4 * lane);
-    uint32_t l0 = __shfl_up_sync(0xffffffffu, up.z, 1), l1 = __shfl_up_sync(0xffffffffu, up.w, 1);
-    if (lane == 0u) { l0 = lcs[0]; l1 = lcs[1]; }
-    H4 hA[4], hlA[2], hB[4], hlB[2];  // two unpacked rows, used alternately as "above" and "current"
-    hA[0] = unpack_h4(up.x); hA[1] = unpack_h4(up.y); hA[2] = unpack_h4(up.z); hA[3] = unpack_h4(up.w);
-    hlA[0] = unpack_h4(l0); hlA[1] = unpack_h4(l1);
-    const uint32_t *raw_row = raw + FU_SW;
-    const uint32_t *lcs_row = lcs + 2;
-    uint32_t *pf_row = pfw;
-    uint32_t *rs_row = p.rowsum + (size_t)(ya - (int)p.y_begin) * 8;
-    int r = 0;
-    for (; r + 2 <= nrows; r += 2) {
-      sweep_step<BPW>(raw_row, lcs_row, pf_row, rs_row, lane, lmask, guard, qw, wmax, up, hA, hlA, hB, hlB);
-      sweep_step<BPW>(raw_row + FU_SW, lcs_row + 2, pf_row + FU_SW, rs_row + 8, lane, lmask, guard, qw, wmax, up, hB,
-                      hlB, hA, hlA);
-      raw_row += 2 * FU_SW; lcs_row += 4; pf_row += 2 * FU_SW; rs_row += 16;
-    }
-    if (r < nrows) sweep_step<BPW>(raw_row, lcs_row, pf_row, rs_row, lane, lmask, guard, qw, wmax, up, hA, hlA, hB, hlB);
-  }
-  // publish: the unit's partial sums are out; count it as done for its band
-  __syncwarp();
-  if (lane == 0u) {
-    __threadfence();
-    atomicAdd(p.band_done + band, 1u);
-  }
-  __syncwarp();
-  UnitRef ref;
-  ref.band = band; ref.seg = seg; ref.ya = ya; ref.nrows = nrows;
-  return ref;
 }
 
-// ---- phase B: wait for the band, pick the winner per row, write the filtered bytes ----
+// ---- sweep: filter costs of every row, Paeth residuals into the stash, partial sums published ----
+template <int BPW>
+__device__ __forceinline__ void unit_sweep(const FusedParams &p, const UnitPlan &pl, uint32_t *stash, const uint32_t lane,
+                                           const uint32_t (&lmask)[5]) {
+  uint32_t *raw = stash, *pfw = stash + FU_RAW_WORDS, *lcs = pfw + FU_PF_WORDS;
+  const int wmax = (int)p.canvas_w * BPW;
+  const int nrows = pl.nrows, qw = pl.xw0 + 4 * (int)lane;
+  const bool guard = pl.xw0 + FU_SW > wmax;
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  __syncwarp();
+  uint4 up = *reinterpret_cast<const uint4 *>(raw + 4 * lane);
+  uint32_t l0 = __shfl_up_sync(0xffffffffu, up.z, 1), l1 = __shfl_up_sync(0xffffffffu, up.w, 1);
+  if (lane == 0u) { l0 = lcs[0]; l1 = lcs[1]; }
+  H4 hA[4], hlA[2], hB[4], hlB[2];  // two unpacked rows, used alternately as "above" and "current"
+  hA[0] = unpack_h4(up.x); hA[1] = unpack_h4(up.y); hA[2] = unpack_h4(up.z); hA[3] = unpack_h4(up.w);
+  hlA[0] = unpack_h4(l0); hlA[1] = unpack_h4(l1);
+  const uint32_t *raw_row = raw + FU_SW;
+  const uint32_t *lcs_row = lcs + 2;
+  uint32_t *pf_row = pfw;
+  unsigned long long *rs_row = p.rowsum + (size_t)(pl.ya - (int)p.y_begin) * 8;
+  int r = 0;
+  for (; r + 2 <= nrows; r += 2) {
+    sweep_step<BPW>(raw_row, lcs_row, pf_row, rs_row, lane, lmask, guard, qw, wmax, up, hA, hlA, hB, hlB);
+    sweep_step<BPW>(raw_row + FU_SW, lcs_row + 2, pf_row + FU_SW, rs_row + 8, lane, lmask, guard, qw, wmax, up, hB, hlB,
+                    hA, hlA);
+    raw_row += 2 * FU_SW; lcs_row += 4; pf_row += 2 * FU_SW; rs_row += 16;
+  }
+  if (r < nrows) sweep_step<BPW>(raw_row, lcs_row, pf_row, rs_row, lane, lmask, guard, qw, wmax, up, hA, hlA, hB, hlB);
+}
+
+// What phase B needs to know about a unit after its sweep is over.
+struct UnitRef {
+  uint32_t seg;
+  int ya, nrows;
+};
+
+// ---- phase B: wait until every unit of the band has added its sums, pick the winner per row, write ----
 template <int BPW>
 __device__ __forceinline__ void unit_emit(const FusedParams &p, const UnitRef &ref, const uint32_t *stash, const uint32_t lane) {
   const uint32_t *raw = stash, *pfw = stash + FU_RAW_WORDS, *lcs = pfw + FU_PF_WORDS;
   const int wmax = (int)p.canvas_w * BPW;
   const int ya = ref.ya, nrows = ref.nrows;
   const int qw = (int)ref.seg * FU_SW + 4 * (int)lane;
-  // Every lane polls the same word (one broadcast load), so the warp never diverges here.
-  while (fu_ld_acquire(p.band_done + ref.band) < p.nseg) __nanosleep(64);
-
+  // Each 64-bit row-sum word carries its own arrival count in the high half, so the sums need no fence
+  // and no separate "band done" flag: lane r reads row r's five words until all five are complete.
   uint32_t my_ft = 0u;
-  if ((int)lane < nrows) {
-    const uint32_t *rs = p.rowsum + (size_t)(ya + (int)lane - (int)p.y_begin) * 8;
-    const uint4 v = __ldcg(reinterpret_cast<const uint4 *>(rs));
-    const uint32_t v4 = __ldcg(rs + 4);
-    uint32_t best = v.x;
-    if (v.y < best) { best = v.y; my_ft = 1u; }   // strict '<': first minimum wins (png-filter.ts:174)
-    if (v.z < best) { best = v.z; my_ft = 2u; }
-    if (v.w < best) { best = v.w; my_ft = 3u; }
-    if (v4 < best) { best = v4; my_ft = 4u; }
+  for (;;) {
+    bool ready = true;
+    if ((int)lane < nrows) {
+      const unsigned long long *rs = p.rowsum + (size_t)(ya + (int)lane - (int)p.y_begin) * 8;
+      unsigned long long w0, w1, w2, w3, w4;
+      asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w0), "=l"(w1) : "l"(rs) : "memory");
+      asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w2), "=l"(w3) : "l"(rs + 2) : "memory");
+      asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(w4) : "l"(rs + 4) : "memory");
+      const uint32_t n = p.nseg;
+      ready = (uint32_t)(w0 >> 32) == n && (uint32_t)(w1 >> 32) == n && (uint32_t)(w2 >> 32) == n &&
+              (uint32_t)(w3 >> 32) == n && (uint32_t)(w4 >> 32) == n;
+      uint32_t best = (uint32_t)w0;
+      my_ft = 0u;
+      if ((uint32_t)w1 < best) { best = (uint32_t)w1; my_ft = 1u; }   // strict '<': first minimum wins (png-filter.ts:174)
+      if ((uint32_t)w2 < best) { best = (uint32_t)w2; my_ft = 2u; }
+      if ((uint32_t)w3 < best) { best = (uint32_t)w3; my_ft = 3u; }
+      if ((uint32_t)w4 < best) { best = (uint32_t)w4; my_ft = 4u; }
+    }
+    if (__all_sync(0xffffffffu, ready)) break;
+    __nanosleep(100);
   }
   uint8_t *orow = p.out + (size_t)(ya - (int)p.y_begin) * p.out_pitch + p.lead;
   const uint32_t *cur_row = raw + FU_SW + 4 * lane, *pf_row = pfw + 4 * lane, *lcs_row = lcs + 2;
@@ -370,36 +390,46 @@ __device__ __forceinline__ void unit_emit(const FusedParams &p, const UnitRef &r
   __syncwarp();  // the stash is free again
 }
 
-// Software pipeline per warp: costs(u_k) run before emit(u_{k-1}), so that the band of u_{k-1} has had a
-// whole sweep's time to complete and the poll in unit_emit returns at once; the next ticket is fetched
-// while the current unit is swept.  Two stashes per warp.
+// Software pipeline per warp (two stashes):
+//   load(u_k) issued -> plan(u_k+1) built while those copies fly -> sweep(u_k) -> emit(u_k-1)
+// so the band of u_k-1 has had a whole sweep's time to complete and the poll in unit_emit returns at
+// once; tickets are fetched two units ahead.
 template <int BPW>
-__global__ void __launch_bounds__(FU_WARPS * 32) fused_kernel(const FusedParams p) {
+__global__ void __launch_bounds__(FU_WARPS * 32, 3) fused_kernel(const FusedParams p) {
   extern __shared__ __align__(16) uint32_t fu_smem[];
   const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-  uint32_t *stash0 = fu_smem + warp * (2 * FU_WARP_WORDS), *stash1 = stash0 + FU_WARP_WORDS;
+  uint32_t *cur_stash = fu_smem + warp * (2 * FU_WARP_WORDS), *prev_stash = cur_stash + FU_WARP_WORDS;
   const uint32_t n_units = p.n_bands * p.nseg;
   uint32_t lmask[5];  // lane f keeps candidate f's row sum
 #pragma unroll
   for (int f = 0; f < 5; f++) lmask[f] = lane == (uint32_t)f ? 0xffffffffu : 0u;
 
-  uint32_t u = 0u;
-  if (lane == 0u) u = atomicAdd(p.ticket, 1u);
-  u = __shfl_sync(0xffffffffu, u, 0);
+  uint32_t t2 = 0u;
+  if (lane == 0u) t2 = atomicAdd(p.ticket, 2u);
+  const uint32_t u0 = __shfl_sync(0xffffffffu, t2, 0);
+  uint32_t u_next = u0 + 1u;
+  if (u0 >= n_units) return;
+  UnitPlan plan = unit_plan<BPW>(p, u0);
   UnitRef prev;
-  prev.nrows = 0; prev.band = 0; prev.seg = 0; prev.ya = 0;
+  prev.seg = 0; prev.ya = 0; prev.nrows = 0;
   bool have_prev = false;
-  uint32_t *cur_stash = stash0, *prev_stash = stash1;
-  while (u < n_units) {
-    uint32_t u_next = 0u;
-    if (lane == 0u) u_next = atomicAdd(p.ticket, 1u);  // consumed after the sweep
-    const UnitRef cur = unit_costs<BPW>(p, u, cur_stash, lane, lmask);
+  for (;;) {
+    uint32_t t = 0u;
+    if (lane == 0u) t = atomicAdd(p.ticket, 1u);  // the unit after next; consumed at the end of the iteration
+    unit_load<BPW>(p, plan, cur_stash, lane);
+    const bool more = u_next < n_units;
+    UnitPlan plan_next = plan;
+    if (more) plan_next = unit_plan<BPW>(p, u_next);
+    unit_sweep<BPW>(p, plan, cur_stash, lane, lmask);
     if (have_prev) unit_emit<BPW>(p, prev, prev_stash, lane);
-    prev = cur; have_prev = true;
-    uint32_t *t = cur_stash; cur_stash = prev_stash; prev_stash = t;
-    u = __shfl_sync(0xffffffffu, u_next, 0);
+    prev.seg = plan.seg; prev.ya = plan.ya; prev.nrows = plan.nrows;
+    have_prev = true;
+    uint32_t *sw = cur_stash; cur_stash = prev_stash; prev_stash = sw;
+    if (!more) break;
+    plan = plan_next;
+    u_next = __shfl_sync(0xffffffffu, t, 0);
   }
-  if (have_prev) unit_emit<BPW>(p, prev, prev_stash, lane);
+  unit_emit<BPW>(p, prev, prev_stash, lane);
 }
 
 uint32_t fused_rows_per_band() { return FB_R; }

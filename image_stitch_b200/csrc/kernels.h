@@ -47,8 +47,7 @@ struct FusedParams {
   uint32_t n_bands, nseg;    // unit bands in [y_begin,y_end), units per band
   uint32_t alpha_blend;
   uint32_t bg_lo, bg_hi;
-  uint32_t *rowsum;           // [(y_end - y_begin)][8], zeroed
-  uint32_t *band_done;        // [n_bands], zeroed
+  unsigned long long *rowsum; // [(y_end - y_begin)][8], zeroed: low half = cost sum, high half = units arrived
   uint32_t *ticket;           // zeroed
   uint8_t *out;               // row r: filter byte at out + r*out_pitch + lead
   size_t out_pitch;
