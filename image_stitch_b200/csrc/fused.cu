@@ -11,10 +11,10 @@
 // workers with a private shared-memory stash, so there is no CTA barrier
 // anywhere.  A row's cost is a sum over all units of its band: units publish
 // partial sums with red.global.add and bump a per-band counter; a warp writes
-// its rows once the counter says the band is complete.  Units are handed out
-// band-major by an atomic ticket to a grid that is fully resident and has at
-// least as many warps as a band has units, so every unit a warp waits for is
-// already running: no deadlock, no grid sync.
+// its rows once every unit of the band has arrived (the 64-bit sums carry their
+// own arrival count).  Units are dealt round-robin to a cooperatively launched
+// (fully resident) grid with at least as many warps as a band has units; see
+// fused_kernel for why no wait cycle can form.
 //
 //   phase A   raw stash <- cp.async of the one tile that covers the unit (grid
 //             mosaics, opaque layers), else the generic per-quad compositor
@@ -392,34 +392,36 @@ __device__ __forceinline__ void unit_emit(const FusedParams &p, const UnitRef &r
 
 // Software pipeline per warp (two stashes):
 //   load(u_k) issued -> plan(u_k+1) built while those copies fly -> sweep(u_k) -> emit(u_k-1)
-// so the band of u_k-1 has had a whole sweep's time to complete and the poll in unit_emit returns at
-// once; tickets are fetched two units ahead.
+// so the band of u_k-1 has had a whole sweep's time to complete and the poll in unit_emit returns at once.
+//
+// Units are dealt round-robin: warp w of W owns units w, w+W, w+2W, ...  The grid is launched
+// cooperatively (all W warps resident) with W >= units per band, so the units of one band belong to
+// distinct warps at iteration k-1, k or k+1 of their sequences.  emit at iteration k-1 waits only for
+// sweeps of iterations <= k+... of OTHER warps, and a sweep never waits: by induction on the iteration
+// index the wait graph has no cycle, whatever the timing (sweep_k <- emit_k-2 <- sweeps of iterations <= k-1).
 template <int BPW>
 __global__ void __launch_bounds__(FU_WARPS * 32, 3) fused_kernel(const FusedParams p) {
   extern __shared__ __align__(16) uint32_t fu_smem[];
   const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
   uint32_t *cur_stash = fu_smem + warp * (2 * FU_WARP_WORDS), *prev_stash = cur_stash + FU_WARP_WORDS;
   const uint32_t n_units = p.n_bands * p.nseg;
+  const uint32_t n_warps = gridDim.x * FU_WARPS;
   uint32_t lmask[5];  // lane f keeps candidate f's row sum
 #pragma unroll
   for (int f = 0; f < 5; f++) lmask[f] = lane == (uint32_t)f ? 0xffffffffu : 0u;
 
-  uint32_t t2 = 0u;
-  if (lane == 0u) t2 = atomicAdd(p.ticket, 2u);
-  const uint32_t u0 = __shfl_sync(0xffffffffu, t2, 0);
-  uint32_t u_next = u0 + 1u;
-  if (u0 >= n_units) return;
-  UnitPlan plan = unit_plan<BPW>(p, u0);
+  uint32_t u = blockIdx.x * FU_WARPS + warp;
+  if (u >= n_units) return;
+  UnitPlan plan = unit_plan<BPW>(p, u);
   UnitRef prev;
   prev.seg = 0; prev.ya = 0; prev.nrows = 0;
   bool have_prev = false;
   for (;;) {
-    uint32_t t = 0u;
-    if (lane == 0u) t = atomicAdd(p.ticket, 1u);  // the unit after next; consumed at the end of the iteration
     unit_load<BPW>(p, plan, cur_stash, lane);
-    const bool more = u_next < n_units;
+    u += n_warps;
+    const bool more = u < n_units;
     UnitPlan plan_next = plan;
-    if (more) plan_next = unit_plan<BPW>(p, u_next);
+    if (more) plan_next = unit_plan<BPW>(p, u);
     unit_sweep<BPW>(p, plan, cur_stash, lane, lmask);
     if (have_prev) unit_emit<BPW>(p, prev, prev_stash, lane);
     prev.seg = plan.seg; prev.ya = plan.ya; prev.nrows = plan.nrows;
@@ -427,7 +429,6 @@ __global__ void __launch_bounds__(FU_WARPS * 32, 3) fused_kernel(const FusedPara
     uint32_t *sw = cur_stash; cur_stash = prev_stash; prev_stash = sw;
     if (!more) break;
     plan = plan_next;
-    u_next = __shfl_sync(0xffffffffu, t, 0);
   }
   unit_emit<BPW>(p, prev, prev_stash, lane);
 }
@@ -447,14 +448,16 @@ cudaError_t launch_fused(const FusedParams &p, bool out16, int sm_count, cudaStr
   }
   const int occ = out16 ? occ16 : occ8;
   if (occ < 1) return cudaErrorLaunchOutOfResources;
-  const uint32_t resident_warps = (uint32_t)(occ * sm_count * FU_WARPS);
-  if (resident_warps < p.nseg) return cudaErrorInvalidConfiguration;  // caller falls back to the two-pass path
   const uint32_t n_units = p.n_bands * p.nseg;
   const uint32_t want = (n_units + FU_WARPS - 1) / FU_WARPS, resident = (uint32_t)(occ * sm_count);
   const uint32_t grid = want < resident ? want : resident;
-  if (out16) fused_kernel<2><<<grid, FU_WARPS * 32, FU_CTA_SMEM, st>>>(p);
-  else fused_kernel<1><<<grid, FU_WARPS * 32, FU_CTA_SMEM, st>>>(p);
-  return cudaGetLastError();
+  if (grid * FU_WARPS < p.nseg) return cudaErrorInvalidConfiguration;  // caller falls back to the two-pass path
+  // Cooperative launch: the runtime guarantees that every CTA of the grid is resident (or fails),
+  // which the wait-freedom argument above fused_kernel relies on.
+  FusedParams pp = p;
+  void *args[] = {&pp};
+  const void *fn = out16 ? (const void *)fused_kernel<2> : (const void *)fused_kernel<1>;
+  return cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(FU_WARPS * 32), args, FU_CTA_SMEM, st);
 }
 
 }  // namespace stitch
