@@ -116,6 +116,17 @@ int64_t orc_render_rows(uint32_t canvas_w, uint32_t canvas_h, int out_bit_depth,
                         const orc_tile *tiles, size_t n_tiles,
                         uint32_t y0, uint32_t y1, int out_kind, uint8_t *out, size_t cap);
 
+/* ---- JPEG half (jpeg_oracle.c; parity unpinned against the reference, pinned against libjpeg) ---- */
+void orc_jpeg_quant_tables(int quality, uint16_t lum[64], uint16_t chr[64]);
+void orc_jpeg_rgb_to_ycc(int r, int g, int b, int *y, int *cb, int *cr);
+void orc_jpeg_fdct_islow(int data[64]);
+int orc_jpeg_quantize(int coef, int quantval);
+int64_t orc_jpeg_coefficients(const uint8_t *rgba, size_t pitch, uint32_t width, uint32_t height, uint32_t y0,
+                              uint32_t y1, int quality, int16_t *coefs);
+int64_t orc_jpeg_encode_rows(const uint8_t *rgba, size_t pitch, uint32_t width, uint32_t height, uint32_t y0,
+                             uint32_t y1, int quality, uint8_t *out, size_t cap);
+int64_t orc_jpeg_header(uint32_t width, uint32_t height, int quality, uint8_t *out, size_t cap);
+
 #ifdef __cplusplus
 }
 #endif

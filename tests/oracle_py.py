@@ -179,3 +179,65 @@ def render_rows(canvas_w, canvas_h, out_bit_depth, background, alpha_blend, tile
     if n < 0:
         raise OracleError(int(n), f"oracle error {n}")
     return out[:n]
+
+
+# ---- JPEG half (oracle/jpeg_oracle.c) ---------------------------------------------------
+def _jpeg_setup():
+    l = lib()
+    if getattr(l, "_jpeg_ready", False):
+        return l
+    vp, sz = C.c_void_p, C.c_size_t
+    l.orc_jpeg_quant_tables.argtypes = [C.c_int, vp, vp]
+    l.orc_jpeg_quant_tables.restype = None
+    l.orc_jpeg_coefficients.argtypes = [vp, sz, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, vp]
+    l.orc_jpeg_coefficients.restype = C.c_int64
+    l.orc_jpeg_encode_rows.argtypes = [vp, sz, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, vp, sz]
+    l.orc_jpeg_encode_rows.restype = C.c_int64
+    l.orc_jpeg_header.argtypes = [C.c_uint32, C.c_uint32, C.c_int, vp, sz]
+    l.orc_jpeg_header.restype = C.c_int64
+    l.orc_jpeg_quantize.argtypes = [C.c_int, C.c_int]
+    l._jpeg_ready = True
+    return l
+
+
+def jpeg_quant_tables(quality):
+    l = _jpeg_setup()
+    a, b = np.zeros(64, np.uint16), np.zeros(64, np.uint16)
+    l.orc_jpeg_quant_tables(int(quality), _p(a), _p(b))
+    return a, b
+
+
+def jpeg_header(width, height, quality):
+    l = _jpeg_setup()
+    buf = np.zeros(1024, np.uint8)
+    n = l.orc_jpeg_header(width, height, int(quality), _p(buf), buf.size)
+    if n < 0:
+        raise OracleError(int(n), "invalid JPEG dimensions")
+    return buf[:n].tobytes()
+
+
+def jpeg_encode_rows(rgba_rows, width, height, y0, y1, quality):
+    """rgba_rows: uint8 array [(y1-y0), width*4] = canvas rows y0..y1-1. Returns the entropy bytes (with RSTm)."""
+    l = _jpeg_setup()
+    r = np.ascontiguousarray(rgba_rows, dtype=np.uint8).reshape(y1 - y0, width * 4)
+    cap = ((width + 7) // 8) * ((y1 - y0 + 7) // 8) * 3 * 260 + 64
+    out = np.zeros(cap, np.uint8)
+    n = l.orc_jpeg_encode_rows(_p(r), width * 4, width, height, y0, y1, int(quality), _p(out), cap)
+    if n < 0:
+        raise OracleError(int(n), f"oracle error {n}")
+    return out[:n].tobytes()
+
+
+def jpeg_coefficients(rgba_rows, width, height, y0, y1, quality):
+    l = _jpeg_setup()
+    r = np.ascontiguousarray(rgba_rows, dtype=np.uint8).reshape(y1 - y0, width * 4)
+    n = ((width + 7) // 8) * ((y1 - y0 + 7) // 8) * 3 * 64
+    out = np.zeros(n, np.int16)
+    l.orc_jpeg_coefficients(_p(r), width * 4, width, height, y0, y1, int(quality), _p(out))
+    return out.reshape(-1, 3, 64)
+
+
+def jpeg_file(rgba, width, height, quality):
+    """Whole JPEG file by the oracle: header + entropy segments + EOI."""
+    r = np.ascontiguousarray(rgba, dtype=np.uint8).reshape(height, width * 4)
+    return jpeg_header(width, height, quality) + jpeg_encode_rows(r, width, height, 0, height, quality) + b"\xff\xd9"
