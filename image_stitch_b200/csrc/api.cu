@@ -2,9 +2,7 @@
 // tile upload, binning, kernel launches, band download.  Host-side C++ only
 // orchestrates; every pixel is touched by the CUDA kernels in decode.cu,
 // compose.cu, fused.cu and jpeg.cu.  There is deliberately no CPU fallback.
-#include "../../include/stitch_b200.h"
-#include "common.cuh"
-#include "kernels.h"
+#include "job.h"
 
 #include <algorithm>
 #include <cstdarg>
@@ -16,58 +14,16 @@
 
 using namespace stitch;
 
-// ---------------------------------------------------------------------------
-struct stitch_ctx {
-  int device = 0;
-  cudaStream_t stream = nullptr;
-  bool own_stream = false;
-  int sm_count = 148;
-  std::string err;
-  cudaEvent_t ev[6] = {};
-  DevStatus *d_status = nullptr;   // device error word
-  DevStatus *h_status = nullptr;   // pinned mirror
-};
-
-struct TileRec {
-  stitch_tile_desc d;
-  uint8_t *d_src = nullptr;   // uploaded bytes (inflated stream or dense rows); owned unless external
-  bool src_external = false;
-  size_t src_len = 0;
-  uint8_t *d_pix = nullptr;   // dense unfiltered rows (== d_src for filtered==0)
-  uint32_t pitch = 0;
-  uint8_t *d_pass = nullptr;  // Adam7 pass scratch
-  std::vector<UnfStream> streams;
-  bool has_a7 = false;
-  A7Image a7;
-  bool decoded = false;
-};
-
-struct stitch_job {
-  stitch_ctx *ctx = nullptr;
-  stitch_job_desc desc;
-  uint32_t bpp = 4;  // output bytes per pixel
-  std::vector<TileRec> tiles;
-  bool finalized = false;
-  // device-side job state
-  DevTile *d_tiles = nullptr;
-  uint32_t *d_bin_start = nullptr, *d_bin_tiles = nullptr;
-  UnfStream *d_streams = nullptr; size_t streams_cap = 0;
-  UnfStream *d_slow = nullptr; size_t slow_cap = 0;          // chains with a truncated final row (legacy kernel)
-  UnfUnit *d_units = nullptr; size_t units_cap = 0;
-  uint32_t *d_uprog = nullptr; size_t uprog_cap = 0;         // wavefront kernel: progress words | ticket
-  A7Image *d_a7 = nullptr; size_t a7_cap = 0;
-  uint32_t bins_x = 0, bins_y = 0, bin_w_log2 = 9, bin_h_log2 = 4, bin_y_origin = 0;
-  uint32_t *d_sync = nullptr; size_t sync_words = 0;   // fused kernel: rowsum | band_done | ticket
-  bool force_two_pass = false;
-  // band buffers
-  uint8_t *d_canvas = nullptr; size_t canvas_bytes = 0; size_t canvas_pitch = 0;
-  uint8_t *d_out = nullptr; size_t out_bytes = 0;
-  size_t out_pitch = 0, out_lead = 0, out_row_bytes = 0;
-  uint32_t last_y0 = 0, last_y1 = 0;
-  int status = STITCH_OK;
-};
-
 static int fail(stitch_ctx *ctx, int code, const char *fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  if (ctx) ctx->err = buf;
+  return code;
+}
+int stitch_fail(stitch_ctx *ctx, int code, const char *fmt, ...) {
   char buf[512];
   va_list ap;
   va_start(ap, fmt);
@@ -199,6 +155,8 @@ extern "C" void stitch_job_destroy(stitch_job *job) {
   dev_free(ctx, job->d_streams); dev_free(ctx, job->d_a7);
   dev_free(ctx, job->d_slow); dev_free(ctx, job->d_units); dev_free(ctx, job->d_uprog);
   dev_free(ctx, job->d_canvas); dev_free(ctx, job->d_out); dev_free(ctx, job->d_sync);
+  for (auto &q : job->d_jpeg) dev_free(ctx, q);
+  if (job->h_jpeg_totals) cudaFreeHost(job->h_jpeg_totals);
   cudaStreamSynchronize(ctx->stream);
   delete job;
 }
@@ -521,6 +479,9 @@ static int finalize_job(stitch_job *job) {
   return STITCH_OK;
 }
 
+int stitch_dev_alloc(stitch_ctx *ctx, void **p, size_t bytes) { return dev_alloc(ctx, p, bytes); }
+void stitch_dev_free(stitch_ctx *ctx, void *p) { dev_free(ctx, p); }
+
 static int ensure_buffer(stitch_ctx *ctx, uint8_t **p, size_t *have, size_t need) {
   if (need <= *have) return STITCH_OK;
   dev_free(ctx, *p);
@@ -530,6 +491,8 @@ static int ensure_buffer(stitch_ctx *ctx, uint8_t **p, size_t *have, size_t need
   *have = need;
   return STITCH_OK;
 }
+
+int stitch_ensure_buffer(stitch_ctx *ctx, uint8_t **p, size_t *have, size_t need) { return ensure_buffer(ctx, p, have, need); }
 
 static void bg_words(const stitch_job_desc &d, uint32_t &lo, uint32_t &hi) {
   memcpy(&lo, d.background, 4);
@@ -546,12 +509,15 @@ extern "C" int stitch_job_run_band(stitch_job *job, uint32_t y0, uint32_t y1, ui
   if (out_len) *out_len = 0;
   if (y0 >= y1 || y0 < jd.band_y0 || y1 > jd.band_y1)
     return fail(ctx, STITCH_E_INVALID, "rows [%u,%u) are outside the job's band [%u,%u)", y0, y1, jd.band_y0, jd.band_y1);
-  if (jd.out_kind == STITCH_OUT_JPEG_ENTROPY) return stitch_jpeg_run_band(job, y0, y1, out, cap, out_len, tm);
+  const bool jpeg = jd.out_kind == STITCH_OUT_JPEG_ENTROPY;
+  if (jpeg && ((y0 & 7u) || ((y1 & 7u) && y1 != jd.canvas_h)))
+    return fail(ctx, STITCH_E_INVALID, "JPEG bands must start on a multiple of 8 rows and end on one or at the canvas bottom");
   const size_t row_bytes = (size_t)jd.canvas_w * job->bpp;
   const uint32_t n_rows = y1 - y0;
   const bool png = jd.out_kind == STITCH_OUT_PNG_FILTERED;
   const size_t host_row = row_bytes + (png ? 1 : 0);
-  if (out && cap < host_row * n_rows) return fail(ctx, STITCH_E_CAPACITY, "output buffer too small: need %zu bytes", host_row * n_rows);
+  if (out && !jpeg && cap < host_row * n_rows) return fail(ctx, STITCH_E_CAPACITY, "output buffer too small: need %zu bytes", host_row * n_rows);
+  size_t jpeg_bytes = 0;
 
   uint32_t launches = 0;
   int rc = reset_status(ctx);
@@ -611,6 +577,15 @@ extern "C" int stitch_job_run_band(stitch_job *job, uint32_t y0, uint32_t y1, ui
       CK(launch_filter_rows(fp, ctx->stream));
       launches += 2;
     }
+  } else if (jpeg) {
+    // composite the band into HBM, then kernel (d); MCU rows are independent entropy segments (jpeg.cu)
+    job->canvas_pitch = pitch16;
+    if ((rc = ensure_buffer(ctx, &job->d_canvas, &job->canvas_bytes, pitch16 * (size_t)n_rows))) return rc;
+    cp.y_begin = y0; cp.y_end = y1; cp.out = job->d_canvas; cp.out_pitch = pitch16;
+    CK(launch_compose(cp, false, ctx->stream));
+    launches += 1;
+    if ((rc = stitch_jpeg_encode_band(job, y0, y1, job->d_canvas, pitch16, &jpeg_bytes, &launches))) return rc;
+    job->out_pitch = jpeg_bytes; job->out_lead = 0; job->out_row_bytes = jpeg_bytes;
   } else {
     job->out_pitch = pitch16; job->out_lead = 0; job->out_row_bytes = host_row;
     if ((rc = ensure_buffer(ctx, &job->d_out, &job->out_bytes, pitch16 * (size_t)n_rows))) return rc;
@@ -619,7 +594,16 @@ extern "C" int stitch_job_run_band(stitch_job *job, uint32_t y0, uint32_t y1, ui
     launches += 1;
   }
   CK(cudaEventRecord(ctx->ev[3], ctx->stream));
-  if (out) {
+  if (out && jpeg) {
+    const size_t need = sizeof(stitch_jpeg_band_info) + jpeg_bytes;
+    if (cap < need) return fail(ctx, STITCH_E_CAPACITY, "output buffer too small: need %zu bytes", need);
+    stitch_jpeg_band_info info;
+    memset(&info, 0, sizeof info);
+    info.n_bits = (uint64_t)jpeg_bytes * 8;  // every MCU row restarts the DC predictors: last_dc stays 0
+    memcpy(out, &info, sizeof info);
+    if (jpeg_bytes) CK(cudaMemcpyAsync(out + sizeof info, job->d_out, jpeg_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    if (out_len) *out_len = need;
+  } else if (out) {
     CK(cudaMemcpy2DAsync(out, host_row, job->d_out + job->out_lead, job->out_pitch, host_row, n_rows,
                          cudaMemcpyDeviceToHost, ctx->stream));
     if (out_len) *out_len = host_row * n_rows;

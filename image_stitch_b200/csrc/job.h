@@ -1,0 +1,83 @@
+// job.h -- private state shared by the translation units of libstitch_b200.so (not part of the C ABI)
+#pragma once
+#include "../../include/stitch_b200.h"
+#include "common.cuh"
+#include "kernels.h"
+
+#include <string>
+#include <vector>
+
+// ---------------------------------------------------------------------------
+struct stitch_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  int sm_count = 148;
+  std::string err;
+  cudaEvent_t ev[6] = {};
+  stitch::DevStatus *d_status = nullptr;   // device error word
+  stitch::DevStatus *h_status = nullptr;   // pinned mirror
+};
+
+struct TileRec {
+  stitch_tile_desc d;
+  uint8_t *d_src = nullptr;   // uploaded bytes (inflated stream or dense rows); owned unless external
+  bool src_external = false;
+  size_t src_len = 0;
+  uint8_t *d_pix = nullptr;   // dense unfiltered rows (== d_src for filtered==0)
+  uint32_t pitch = 0;
+  uint8_t *d_pass = nullptr;  // Adam7 pass scratch
+  std::vector<stitch::UnfStream> streams;
+  bool has_a7 = false;
+  stitch::A7Image a7;
+  bool decoded = false;
+};
+
+struct stitch_job {
+  stitch_ctx *ctx = nullptr;
+  stitch_job_desc desc;
+  uint32_t bpp = 4;  // output bytes per pixel
+  std::vector<TileRec> tiles;
+  bool finalized = false;
+  // device-side job state
+  stitch::DevTile *d_tiles = nullptr;
+  uint32_t *d_bin_start = nullptr, *d_bin_tiles = nullptr;
+  stitch::UnfStream *d_streams = nullptr; size_t streams_cap = 0;
+  stitch::UnfStream *d_slow = nullptr; size_t slow_cap = 0;          // chains with a truncated final row (legacy kernel)
+  stitch::UnfUnit *d_units = nullptr; size_t units_cap = 0;
+  uint32_t *d_uprog = nullptr; size_t uprog_cap = 0;         // wavefront kernel: progress words | ticket
+  stitch::A7Image *d_a7 = nullptr; size_t a7_cap = 0;
+  uint32_t bins_x = 0, bins_y = 0, bin_w_log2 = 9, bin_h_log2 = 4, bin_y_origin = 0;
+  uint32_t *d_sync = nullptr; size_t sync_words = 0;   // fused kernel: rowsum | band_done | ticket
+  bool force_two_pass = false;
+  // band buffers
+  uint8_t *d_canvas = nullptr; size_t canvas_bytes = 0; size_t canvas_pitch = 0;
+  uint8_t *d_out = nullptr; size_t out_bytes = 0;
+  size_t out_pitch = 0, out_lead = 0, out_row_bytes = 0;
+  uint32_t last_y0 = 0, last_y1 = 0;
+  int status = STITCH_OK;
+  // JPEG scratch (jpeg.cu): coefficients, bit offsets, per-row sizes, unstuffed stream, pinned totals
+  uint8_t *d_jpeg[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  size_t jpeg_cap[5] = {0, 0, 0, 0, 0};
+  unsigned long long *h_jpeg_totals = nullptr;  // pinned: [0] unstuffed bytes, [1] output bytes
+  int jpeg_tables_quality = -1;
+};
+
+
+int stitch_fail(stitch_ctx *ctx, int code, const char *fmt, ...);
+int stitch_dev_alloc(stitch_ctx *ctx, void **p, size_t bytes);
+void stitch_dev_free(stitch_ctx *ctx, void *p);
+int stitch_ensure_buffer(stitch_ctx *ctx, uint8_t **p, size_t *have, size_t need);
+
+#define STITCH_CK(call)                                                                        \
+  do {                                                                                         \
+    cudaError_t e_ = (call);                                                                   \
+    if (e_ != cudaSuccess)                                                                     \
+      return stitch_fail(ctx, e_ == cudaErrorMemoryAllocation ? STITCH_E_NOMEM : STITCH_E_CUDA, \
+                         "CUDA error %s at %s:%d (%s)", cudaGetErrorName(e_), __FILE__, __LINE__, cudaGetErrorString(e_)); \
+  } while (0)
+
+// jpeg.cu: kernel (d) over composited RGBA8 rows [y0,y1) held at `canvas` (row y0 first).  Leaves the
+// entropy-coded bytes in job->d_out and their count in *out_bytes (stream synchronised once inside).
+int stitch_jpeg_encode_band(stitch_job *job, uint32_t y0, uint32_t y1, const uint8_t *canvas, size_t canvas_pitch,
+                            size_t *out_bytes, uint32_t *launches);

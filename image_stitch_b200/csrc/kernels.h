@@ -69,6 +69,3 @@ cudaError_t launch_compose(const ComposeParams &p, bool out16, cudaStream_t st);
 cudaError_t launch_filter_rows(const FilterParams &p, cudaStream_t st);
 
 }  // namespace stitch
-
-int stitch_jpeg_run_band(stitch_job *job, uint32_t y0, uint32_t y1, uint8_t *out, size_t cap, size_t *out_len,
-                         stitch_timings *tm);

@@ -1,0 +1,108 @@
+"""Kernel (d) parity: GPU JPEG entropy bytes vs the oracle (bit-exact), and the
+reference's structural JPEG tests (tests/unit/jpeg-structure.test.ts:52-237,
+tests/integration/jpeg-output.test.ts:29-272) restated through the public API."""
+import io
+
+import numpy as np
+import pytest
+
+import helpers as H
+import oracle_py as orc
+import image_stitch_b200 as stitch
+from image_stitch_b200 import _native
+from image_stitch_b200.jpeg_container import JpegBandSplicer, jpeg_header
+
+pytestmark = pytest.mark.gpu
+PIL = pytest.importorskip("PIL.Image")
+
+
+def _photo(rng, w, h):
+    yy, xx = np.mgrid[0:h, 0:w]
+    img = np.zeros((h, w, 4), np.float64)
+    for c in range(3):
+        img[..., c] = 128 + 90 * np.sin(xx / (7.0 + 3 * c) + c) * np.cos(yy / (11.0 - 2 * c)) + rng.normal(0, 12, (h, w))
+    img[..., 3] = 255
+    return np.clip(img, 0, 255).astype(np.uint8)
+
+
+def _gpu_entropy(ctx, rgba, w, h, quality, bands):
+    job = _native.Job(ctx, w, h, 8, _native.OUT_JPEG_ENTROPY, False, bytes(4), jpeg_quality=quality)
+    job.add_tile(rgba.tobytes(), width=w, height=h, bit_depth=8, color_type=6, interlace=0, filtered=0,
+                 dst_x=0, dst_y=0, z_index=0, image_idx=0)
+    sp = JpegBandSplicer()
+    out = b""
+    for a, b in bands:
+        data, _ = job.run_band(a, b)
+        out += sp.push(data)
+    job.close()
+    return out
+
+
+@pytest.mark.parametrize("w,h,quality", [(64, 48, 90), (33, 17, 75), (8, 8, 50), (1, 1, 85), (100, 9, 100),
+                                         (250, 131, 30), (2051, 77, 90), (640, 480, 1)])
+def test_entropy_bytes_match_oracle(ctx, w, h, quality):
+    rng = np.random.default_rng(w * 31 + h)
+    rgba = _photo(rng, w, h).reshape(h, w * 4)
+    want = orc.jpeg_encode_rows(rgba, w, h, 0, h, quality)
+    got = _gpu_entropy(ctx, rgba, w, h, quality, [(0, h)])
+    assert got == want
+
+
+def test_random_noise_many_ff_bytes(ctx):
+    """Noise at quality 100 produces long codes and many 0xFF bytes: stuffing and worst-case lengths."""
+    rng = np.random.default_rng(11)
+    w, h = 264, 72
+    rgba = rng.integers(0, 256, size=(h, w * 4), dtype=np.uint8)
+    want = orc.jpeg_encode_rows(rgba, w, h, 0, h, 100)
+    assert want.count(b"\xff\x00") > 10
+    assert _gpu_entropy(ctx, rgba, w, h, 100, [(0, h)]) == want
+
+
+def test_bands_equal_whole(ctx):
+    rng = np.random.default_rng(5)
+    w, h = 300, 101
+    rgba = _photo(rng, w, h).reshape(h, w * 4)
+    whole = _gpu_entropy(ctx, rgba, w, h, 90, [(0, h)])
+    parts = _gpu_entropy(ctx, rgba, w, h, 90, [(0, 8), (8, 64), (64, 96), (96, 101)])
+    assert parts == whole == orc.jpeg_encode_rows(rgba, w, h, 0, h, 90)
+
+
+def test_band_alignment_is_checked(ctx):
+    job = _native.Job(ctx, 16, 32, 8, _native.OUT_JPEG_ENTROPY, False, bytes(4), jpeg_quality=85)
+    job.add_tile(bytes(16 * 32 * 4), width=16, height=32, bit_depth=8, color_type=6, filtered=0)
+    with pytest.raises(_native.StitchError, match="multiple of 8"):
+        job.run_band(4, 16)
+    job.close()
+
+
+def test_header_matches_oracle():
+    for w, h, q in ((64, 48, 90), (65535, 1, 1), (17, 9, 100)):
+        assert jpeg_header(w, h, q) == orc.jpeg_header(w, h, q)
+    with pytest.raises(ValueError, match="Invalid quality"):
+        jpeg_header(8, 8, 0)
+    with pytest.raises(ValueError, match="Invalid dimensions"):
+        jpeg_header(0, 8, 50)
+
+
+def test_api_jpeg_output_structure_and_pixels():
+    """concatToBuffer({outputFormat:'jpeg'}): one SOI at 0, one EOI at the end, decodable, dims,
+    and the decoded image equals libjpeg's decode of the oracle's file."""
+    ins = [H.suite_bytes("basn2c08"), H.suite_bytes("basn6a08"), H.suite_bytes("basn0g08")]
+    opts = {"inputs": ins, "layout": {"columns": 3}, "output_format": "jpeg", "jpeg_quality": 90}
+    data = stitch.concat_to_buffer(opts)
+    assert data[:2] == b"\xff\xd8" and data[-2:] == b"\xff\xd9"
+    assert data.count(b"\xff\xd8") == 1 and data.count(b"\xff\xd9") == 1
+    img = np.asarray(PIL.open(io.BytesIO(data)).convert("RGB"))
+    assert img.shape == (32, 96, 3)
+    _, raw = H.oracle_stitch_rows(dict(opts, output_format="png"), out_kind=1)
+    want = orc.jpeg_file(np.frombuffer(raw, np.uint8).reshape(32, 96 * 4), 96, 32, 90)
+    assert data == want
+
+
+def test_api_jpeg_non_multiple_of_8_and_small_bands():
+    ins = [{"x": 0, "y": 0, "source": H.suite_bytes("basn2c08")}, {"x": 20, "y": 11, "source": H.suite_bytes("basn6a08")}]
+    opts = {"inputs": ins, "layout": {}, "output_format": "jpeg", "band_rows": 16}
+    data = stitch.concat_to_buffer(opts)
+    img = PIL.open(io.BytesIO(data))
+    assert img.size == (52, 43)
+    np.asarray(img.convert("RGB"))  # decodes
