@@ -346,15 +346,15 @@ static int decode_tiles(stitch_job *job, int force, uint32_t *launches) {
   for (auto &s : streams) (s.last_row_bytes == s.row_bytes ? fast : slow).push_back(s);
   if (!fast.empty()) {
     std::stable_sort(fast.begin(), fast.end(), [](const UnfStream &a, const UnfStream &b) { return a.rows > b.rows; });
-    uint32_t prog = 0, max_groups = 0;
+    uint32_t max_groups = 0;
+    size_t seam_blocks = 0;  // mailbox offsets in units of one 32-word block (256 B)
     for (auto &s : fast) {
-      s.prog_base = prog;
-      const uint32_t ng = (s.rows + 31u) / 32u;
-      prog += ng;
-      max_groups = std::max(max_groups, ng);
+      s.prog_base = (uint32_t)seam_blocks;
+      seam_blocks += unfilter_wave_seam_bytes(s.rows, s.row_bytes) / 256u;
+      max_groups = std::max(max_groups, (s.rows + 31u) / 32u);
     }
+    if (seam_blocks > 0xffffffffull) return fail(ctx, STITCH_E_INVALID, "too many unfilter blocks in one decode");
     std::vector<UnfUnit> units;
-    units.reserve(prog);
     for (uint32_t g = 0; g < max_groups; g++)
       for (uint32_t i = 0; i < fast.size(); i++) {
         if (g >= (fast[i].rows + 31u) / 32u) break;  // sorted by rows: no later chain has this group either
@@ -363,15 +363,23 @@ static int decode_tiles(stitch_job *job, int force, uint32_t *launches) {
     int rc = upload_array(ctx, fast, &job->d_streams, &job->streams_cap);
     if (rc) return rc;
     if ((rc = upload_array(ctx, units, &job->d_units, &job->units_cap))) return rc;
-    const size_t words = (size_t)prog + 4;
-    if (words > job->uprog_cap) {
+    const size_t bytes = 256u + seam_blocks * 256u;
+    if (bytes > job->uprog_cap) {
       dev_free(ctx, job->d_uprog); job->d_uprog = nullptr; job->uprog_cap = 0;
-      if ((rc = dev_alloc(ctx, (void **)&job->d_uprog, words * 4))) return rc;
-      job->uprog_cap = words;
+      if ((rc = dev_alloc(ctx, (void **)&job->d_uprog, bytes))) return rc;
+      job->uprog_cap = bytes;
+      CK(cudaMemsetAsync(job->d_uprog, 0, bytes, ctx->stream));  // tags of a fresh mailbox: epoch 0 = never written
     }
-    CK(cudaMemsetAsync(job->d_uprog, 0, words * 4, ctx->stream));
-    CK(launch_unfilter_wave(job->d_streams, job->d_units, (uint32_t)units.size(), job->d_uprog, job->d_uprog + prog,
-                            ctx->d_status, ctx->sm_count, ctx->stream));
+    if (++job->seam_epoch == 0u) {  // 2^32 decodes later the tags would repeat: start over
+      CK(cudaMemsetAsync(job->d_uprog, 0, job->uprog_cap, ctx->stream));
+      job->seam_epoch = 1u;
+    }
+    CK(cudaMemsetAsync(job->d_uprog, 0, 4, ctx->stream));  // ticket
+    uint32_t uniform_bpp = fast[0].bpp;
+    for (auto &s : fast) if (s.bpp != uniform_bpp) uniform_bpp = 0;
+    CK(launch_unfilter_wave(job->d_streams, job->d_units, (uint32_t)units.size(), job->d_uprog + 256, job->seam_epoch,
+                            reinterpret_cast<uint32_t *>(job->d_uprog), ctx->d_status, ctx->sm_count, uniform_bpp,
+                            ctx->stream));
     if (launches) (*launches)++;
   }
   if (!slow.empty()) {

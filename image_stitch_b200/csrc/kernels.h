@@ -60,9 +60,11 @@ uint32_t fused_unit_rows();
 uint32_t fused_unit_words();
 
 cudaError_t launch_unfilter(const UnfStream *d_streams, uint32_t n_streams, DevStatus *d_status, cudaStream_t st);
-cudaError_t launch_unfilter_wave(const UnfStream *d_streams, const UnfUnit *d_units, uint32_t n_units,
-                                 uint32_t *d_progress, uint32_t *d_ticket, DevStatus *d_status, int sm_count,
-                                 cudaStream_t st);
+// d_seam: mailbox of unfilter_wave_seam_bytes() per chain, zeroed once; epoch: a value never used with it before (> 0).
+size_t unfilter_wave_seam_bytes(uint32_t rows, uint32_t row_bytes);
+cudaError_t launch_unfilter_wave(const UnfStream *d_streams, const UnfUnit *d_units, uint32_t n_units, void *d_seam,
+                                 uint32_t epoch, uint32_t *d_ticket, DevStatus *d_status, int sm_count,
+                                 uint32_t uniform_bpp /* 0 = mixed */, cudaStream_t st);
 cudaError_t launch_adam7_gather(const A7Image *d_images, uint32_t n_images, uint32_t max_row_bytes,
                                 uint32_t max_height, cudaStream_t st);
 cudaError_t launch_compose(const ComposeParams &p, bool out16, cudaStream_t st);

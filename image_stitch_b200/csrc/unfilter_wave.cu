@@ -9,19 +9,30 @@
 //   unit      = one 32-row group of one chain; one WARP runs one unit at a time
 //   lane l    = row 32g+l; at step T it produces 32-bit word T-l of its row
 //   up word   = lane l-1's previous result, one SHFL per step; lane 0 reads the
-//               last row of group g-1 (written to HBM by another warp, guarded
-//               by a per-group progress word)
+//               last row of group g-1 (the "seam" row, produced by another warp)
 //   staging   = the rows of the inflated stream are unaligned (stride 1+rowBytes),
 //               so every 32-word column block of the 32 rows is fetched with
 //               16-byte cp.async granules (coalesced, 144 B per row incl. slack)
 //               into a 3-slot ring in shared memory; results overwrite the slot
 //               in place and leave as full 128-bit coalesced stores.
-//   schedule  = units are handed out group-major by an atomic ticket to a grid
-//               that is fully resident, so a unit's predecessor is always
-//               already running (no deadlock) and all chains advance together.
+//   seam      = a finished 32-word block of a group's last row is also written to a
+//               mailbox as 32 x (data, tag) pairs, one aligned 8-byte store per
+//               lane.  The consumer polls the pairs until every tag equals the
+//               epoch of this decode: data and tag travel in one single-copy
+//               atomic access, so no fence, no flag word and no acquire are
+//               needed (the LL protocol of collective libraries).
+//   schedule  = units are handed out group-major by an atomic ticket, so a unit
+//               only ever waits for a unit with an earlier ticket, which is
+//               already running (a waiting warp holds no unstarted ticket).
+//   step      = filters None/Sub/Up/Paeth are all "Paeth with some inputs forced
+//               to zero" (the PRMT that unpacks bytes to half2 does the forcing),
+//               Average is computed next to it and selected per lane: one
+//               branch-free instruction stream for all 32 rows whatever their
+//               filter types, fully unrolled over the 32 steps of a block.
 //
-// HBM traffic is the algorithmic minimum (+1/32 for the group seam rows): every
-// stream byte is read once, every pixel byte written once.
+// HBM traffic is the algorithmic minimum plus the seam rows (2/32 of the pixel
+// bytes written, 2/32 read): every stream byte is read once, every pixel byte
+// written once.
 #include "common.cuh"
 #include "kernels.h"
 
@@ -29,9 +40,10 @@ namespace stitch {
 
 static constexpr int UW_WARPS = 4;                          // independent workers per CTA
 static constexpr int UW_ROW_BYTES = 144;                    // 32 words + 16 B alignment slack
-static constexpr int UW_SLOT_BYTES = 33 * UW_ROW_BYTES;     // row 0 = row above the group, rows 1..32 = lanes
+static constexpr int UW_SLOT_BYTES = 33 * UW_ROW_BYTES;     // row 0 = seam row above the group, rows 1..32 = lanes
 static constexpr int UW_WARP_SMEM = 3 * UW_SLOT_BYTES;      // 14256 B
 static constexpr size_t UW_CTA_SMEM = (size_t)UW_WARPS * UW_WARP_SMEM;
+static constexpr uint32_t FULL = 0xffffffffu;
 
 __device__ __forceinline__ void cp_async16(void *smem, const void *gmem) {
   const uint32_t sa = (uint32_t)__cvta_generic_to_shared(smem);
@@ -39,13 +51,14 @@ __device__ __forceinline__ void cp_async16(void *smem, const void *gmem) {
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
-__device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t *p) {
-  uint32_t v;
-  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+// One (data, tag) pair of the seam mailbox: a single 8-byte access at gpu scope.
+__device__ __forceinline__ uint2 ld_pair(const uint2 *p) {
+  uint2 v;
+  asm volatile("ld.relaxed.gpu.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p) : "memory");
   return v;
 }
-__device__ __forceinline__ void st_release_u32(uint32_t *p, uint32_t v) {
-  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+__device__ __forceinline__ void st_pair(uint2 *p, uint32_t data, uint32_t tag) {
+  asm volatile("st.relaxed.gpu.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(data), "r"(tag) : "memory");
 }
 
 // byte `idx` of the 12-byte window [w2 | w1 | w0]
@@ -73,43 +86,92 @@ __device__ __forceinline__ void unf_byte(uint32_t ft, uint32_t f, uint32_t up, u
   cur |= ((x + pr) & 0xffu) << (8 * K);
 }
 
-// One 32-bit word of unfilterScanline.  o1/o2: my previous two result words, u1/u2: the previous two words
-// of the row above, up: the word above.
+// One 32-bit word of unfilterScanline for filter distances that are not a multiple of 4 (byte-serial).
+// o1/o2: my previous two result words, u1/u2: the previous two words of the row above, up: the word above.
 template <int BPP>
 __device__ __forceinline__ uint32_t unf_word(uint32_t ft, uint32_t f, uint32_t up, uint32_t o1, uint32_t o2, uint32_t u1,
                                              uint32_t u2) {
-  if constexpr (BPP == 4 || BPP == 8) {
-    const uint32_t a = BPP == 4 ? o1 : o2, c = BPP == 4 ? u1 : u2;
-    uint32_t pred;
-    switch (ft) {
-      case 1: pred = a; break;
-      case 2: pred = up; break;
-      case 3: pred = avg4(a, up); break;
-      case 4: pred = paeth4_h(unpack_h4(a), unpack_h4(up), unpack_h4(c)); break;
-      default: pred = 0u; break;
-    }
-    return add4(f, pred);
-  } else {
-    uint32_t cur = 0u;
-    unf_byte<BPP, 0>(ft, f, up, o1, o2, u1, u2, cur);
-    unf_byte<BPP, 1>(ft, f, up, o1, o2, u1, u2, cur);
-    unf_byte<BPP, 2>(ft, f, up, o1, o2, u1, u2, cur);
-    unf_byte<BPP, 3>(ft, f, up, o1, o2, u1, u2, cur);
-    return cur;
+  uint32_t cur = 0u;
+  unf_byte<BPP, 0>(ft, f, up, o1, o2, u1, u2, cur);
+  unf_byte<BPP, 1>(ft, f, up, o1, o2, u1, u2, cur);
+  unf_byte<BPP, 2>(ft, f, up, o1, o2, u1, u2, cur);
+  unf_byte<BPP, 3>(ft, f, up, o1, o2, u1, u2, cur);
+  return cur;
+}
+
+// ---------------------------------------------------------------------------
+// Branch-free step for filter distances 4 and 8 (whole words).
+// ---------------------------------------------------------------------------
+// Bytes become halves 1024+v through PRMT with the constant word 0x00000064:
+// selector nibble 4 picks 0x64, nibble 5 picks 0x00, so 0x4140 / 0x4342 unpack
+// bytes (0,1) / (2,3) and 0x4545 yields 1024+0 twice, i.e. "this input is zero".
+__device__ __forceinline__ __half2 unpack2(uint32_t w, uint32_t sel) {
+  const uint32_t r = __byte_perm(w, 0x64u, sel);
+  return *reinterpret_cast<const __half2 *>(&r);
+}
+struct LaneFilter {
+  uint32_t a_lo, a_hi, b_lo, b_hi, c_lo, c_hi;  // PRMT selectors for the left, up and up-left inputs
+  bool avg;
+};
+__device__ __forceinline__ LaneFilter lane_filter(uint32_t ft) {
+  LaneFilter k;
+  const bool ka = ft == 1u || ft == 3u || ft == 4u;  // Sub, Average, Paeth read the left pixel
+  const bool kb = ft >= 2u;                          // Up, Average, Paeth read the pixel above
+  const bool kc = ft == 4u;                          // Paeth reads the pixel above-left
+  k.a_lo = ka ? 0x4140u : 0x4545u; k.a_hi = ka ? 0x4342u : 0x4545u;
+  k.b_lo = kb ? 0x4140u : 0x4545u; k.b_hi = kb ? 0x4342u : 0x4545u;
+  k.c_lo = kc ? 0x4140u : 0x4545u; k.c_hi = kc ? 0x4342u : 0x4545u;
+  k.avg = ft == 3u;
+  return k;
+}
+// 1024 + floor((a + b) / 2): a + (b - 1024) is exact, and t/2 + 511.75 = 1023.75 + (a+b)/2 rounds (one
+// rounding, ulp 1, ties to even only at a+b = 0) to 1024 + floor((a+b)/2).
+__device__ __forceinline__ __half2 avg_h2(__half2 a, __half2 b) {
+  const __half2 t = __hadd2(a, __hsub2(b, __float2half2_rn(1024.f)));
+  return __hfma2(t, __float2half2_rn(0.5f), __float2half2_rn(511.75f));
+}
+template <int D>
+struct WaveState {       // D = filter distance in words
+  __half2 a_lo[D], a_hi[D];  // my last D results (left pixel), masked by the filter type
+  __half2 c_lo[D], c_hi[D];  // the last D words of the row above (above-left pixel), masked
+  uint32_t last;             // my last result, packed (what the lane below reads)
+};
+// f: filtered word; up: word above.  Returns the reconstructed word and advances the state.
+template <int D>
+__device__ __forceinline__ uint32_t wave_word(const LaneFilter &k, WaveState<D> &s, uint32_t f, uint32_t up) {
+  const __half2 m1024 = __float2half2_rn(-1024.f);
+  const __half2 b_lo = unpack2(up, k.b_lo), b_hi = unpack2(up, k.b_hi);
+  const __half2 f_lo = __hadd2(unpack2(f, 0x4140u), m1024), f_hi = __hadd2(unpack2(f, 0x4342u), m1024);
+  const __half2 p_lo = paeth_h2(s.a_lo[0], b_lo, s.c_lo[0]), p_hi = paeth_h2(s.a_hi[0], b_hi, s.c_hi[0]);
+  const __half2 v_lo = avg_h2(s.a_lo[0], b_lo), v_hi = avg_h2(s.a_hi[0], b_hi);
+  const __half2 r_lo = __hadd2(k.avg ? v_lo : p_lo, f_lo), r_hi = __hadd2(k.avg ? v_hi : p_hi, f_hi);
+  const uint32_t o = pack_h4(r_lo, r_hi);  // low byte of each 1024 + (pred + x): the sum mod 256
+#pragma unroll
+  for (int d = 0; d + 1 < D; d++) {
+    s.a_lo[d] = s.a_lo[d + 1]; s.a_hi[d] = s.a_hi[d + 1];
+    s.c_lo[d] = s.c_lo[d + 1]; s.c_hi[d] = s.c_hi[d + 1];
   }
+  s.a_lo[D - 1] = unpack2(o, k.a_lo); s.a_hi[D - 1] = unpack2(o, k.a_hi);
+  s.c_lo[D - 1] = unpack2(up, k.c_lo); s.c_hi[D - 1] = unpack2(up, k.c_hi);
+  s.last = o;
+  return o;
 }
 
 struct UwParams {
   const UnfStream *streams;
   const UnfUnit *units;
   uint32_t n_units;
-  uint32_t *progress;  // one word per (chain, group): column blocks of the group already in HBM
+  uint2 *seam;     // mailbox: 32 pairs per (chain, group, column block)
+  uint32_t epoch;  // tag of this decode (the mailbox is zeroed once, epochs start at 1)
   uint32_t *ticket;
   DevStatus *status;
 };
 
 template <int BPP>
-__device__ void run_unit(const UnfStream &s, const uint32_t g, uint8_t *ws, uint32_t *progress, DevStatus *status) {
+__device__ void run_unit(const UnfStream &s, const uint32_t g, uint8_t *ws, uint2 *seam, const uint32_t epoch,
+                         DevStatus *status) {
+  constexpr bool WORDS = BPP == 4 || BPP == 8;  // filter distance is a whole number of words
+  constexpr int D = WORDS ? BPP / 4 : 1;
   const uint32_t lane = threadIdx.x & 31u;
   const uint32_t r = g * 32u + lane;
   const bool valid = r < s.rows;
@@ -117,11 +179,10 @@ __device__ void run_unit(const UnfStream &s, const uint32_t g, uint8_t *ws, uint
   const uint32_t nwords = (s.row_bytes + 3u) >> 2;
   const uint32_t nblocks = (nwords + 31u) >> 5;
   const uint32_t n_groups = (s.rows + 31u) >> 5;
-  const bool publish = g + 1u < n_groups;
-  uint32_t *my_prog = progress + s.prog_base + g;
-  const uint32_t *prev_prog = my_prog - 1;
+  const bool publish = g + 1u < n_groups;  // implies rows_g == 32
   const bool has_above = g > 0u;
-  uint32_t known = 0u;  // blocks of the group above known to be in HBM
+  uint2 *my_seam = seam + ((size_t)s.prog_base + (size_t)g * nblocks) * 32u + lane;  // block b at +32*b
+  const uint2 *ab_seam = my_seam - (size_t)nblocks * 32u;                            // same, group above
 
   // my row inside the stream: filter byte, then row_bytes filtered bytes at an arbitrary alignment
   const uint8_t *src_row = s.src + (size_t)(valid ? r : 0u) * s.src_stride + 1;
@@ -136,17 +197,7 @@ __device__ void run_unit(const UnfStream &s, const uint32_t g, uint8_t *ws, uint
   const uint32_t sel = 0x3210u + 0x1111u * (sh & 3u);  // PRMT selector: 4 bytes starting at byte (sh & 3)
   const uint32_t my_row_off = (lane + 1u) * UW_ROW_BYTES;
   const uint32_t in_off = my_row_off + (sh & ~3u);
-  const uint8_t *above_row = has_above ? s.dst + (size_t)(g * 32u - 1u) * s.dst_pitch : nullptr;
 
-  auto wait_above = [&](uint32_t need) {
-    if (has_above && known < need) {
-      uint32_t v = 0u;
-      if (lane == 0u) {
-        while ((v = ld_acquire_u32(prev_prog)) < need) __nanosleep(100);
-      }
-      known = __shfl_sync(0xffffffffu, v, 0);
-    }
-  };
   auto issue_block = [&](uint32_t b) {
     uint8_t *slot = ws + (b % 3u) * UW_SLOT_BYTES;
 #pragma unroll
@@ -160,14 +211,12 @@ __device__ void run_unit(const UnfStream &s, const uint32_t g, uint8_t *ws, uint
         if (gp < s.src_end) cp_async16(slot + (row + 1u) * UW_ROW_BYTES + col * 16u, gp);
       }
     }
-    if (has_above && lane < 8u) {
-      const uint32_t off = b * 128u + lane * 16u;
-      if (off < s.dst_pitch) cp_async16(slot + lane * 16u, above_row + off);
-    }
     cp_async_commit();
   };
+  // Block b is complete (every lane has left it): pixels to HBM, last row also to the seam mailbox.
   auto store_block = [&](uint32_t b) {
     const uint8_t *slot = ws + (b % 3u) * UW_SLOT_BYTES;
+    if (publish) st_pair(my_seam + b * 32u, *reinterpret_cast<const uint32_t *>(slot + 32u * UW_ROW_BYTES + lane * 4u), epoch);
 #pragma unroll
     for (int it = 0; it < 8; it++) {
       const uint32_t row = (uint32_t)it * 4u + (lane >> 3), col = lane & 7u;
@@ -182,38 +231,87 @@ __device__ void run_unit(const UnfStream &s, const uint32_t g, uint8_t *ws, uint
   const uint32_t total_steps = nwords + rows_g - 1u;
   const uint32_t nphases = (total_steps + 31u) >> 5;
   uint32_t stored = 0u;
+  // state of the byte-serial path
   uint32_t o1 = 0u, o2 = 0u, u1 = 0u, u2 = 0u, last = 0u;
+  // state of the word path
+  const LaneFilter lf = lane_filter(ft);
+  WaveState<D> st;
+#pragma unroll
+  for (int d = 0; d < D; d++) st.a_lo[d] = st.a_hi[d] = st.c_lo[d] = st.c_hi[d] = __float2half2_rn(1024.f);
+  st.last = 0u;
 
-  wait_above(1u);
+  if (!has_above) {  // first group of the chain: the row above is all zero (png-filter.ts:41)
+#pragma unroll
+    for (int k = 0; k < 3; k++) *reinterpret_cast<uint32_t *>(ws + k * UW_SLOT_BYTES + lane * 4u) = 0u;
+  }
   issue_block(0u);
+  uint2 ab = make_uint2(0u, epoch);
+  if (has_above) ab = ld_pair(ab_seam);
   for (uint32_t p = 0; p < nphases; p++) {
     cp_async_wait_all();
     __syncwarp();
-    if (p >= 2u && stored < nblocks) {  // block p-2 is complete: every lane has left it
+    if (p >= 2u && stored < nblocks) {
       store_block(stored);
       stored++;
-      __syncwarp();
-      if (publish && lane == 0u) st_release_u32(my_prog, stored);
+      __syncwarp();  // the slot is refilled below
     }
-    if (p + 1u < nblocks) {
-      wait_above(p + 2u);
-      issue_block(p + 1u);
-    }
+    if (p + 1u < nblocks) issue_block(p + 1u);
     const uint32_t cur_slot = (p % 3u) * UW_SLOT_BYTES, prev_slot = ((p + 2u) % 3u) * UW_SLOT_BYTES;
-#pragma unroll 4
-    for (uint32_t i = 0; i < 32u; i++) {
-      uint32_t up = __shfl_up_sync(0xffffffffu, last, 1);
-      const uint32_t j = p * 32u + i - lane;  // wraps to a huge value while the lane has not started
-      if (valid && j < nwords) {
-        const uint32_t wi = j & 31u;
-        const uint32_t slot_off = lane <= i ? cur_slot : prev_slot;
-        const uint8_t *ip = ws + slot_off + in_off + wi * 4u;
-        const uint32_t f = __byte_perm(*reinterpret_cast<const uint32_t *>(ip),
-                                       *reinterpret_cast<const uint32_t *>(ip + 4), sel);
-        if (lane == 0u) up = has_above ? *reinterpret_cast<const uint32_t *>(ws + slot_off + wi * 4u) : 0u;
-        const uint32_t o = unf_word<BPP>(ft, f, up, o1, o2, u1, u2);
-        *reinterpret_cast<uint32_t *>(ws + slot_off + my_row_off + wi * 4u) = o;
-        o2 = o1; o1 = o; u2 = u1; u1 = up; last = o;
+    if (has_above && p < nblocks) {  // seam block p -> row 0 of the current slot; block p+1 is requested early
+      while (!__all_sync(FULL, ab.y == epoch)) {
+        __nanosleep(32);
+        if (ab.y != epoch) ab = ld_pair(ab_seam + p * 32u);
+      }
+      *reinterpret_cast<uint32_t *>(ws + cur_slot + lane * 4u) = ab.x;
+      if (p + 1u < nblocks) ab = ld_pair(ab_seam + (p + 1u) * 32u);
+      __syncwarp();
+    }
+    const bool full = rows_g == 32u && p >= 1u && (p + 1u) * 32u <= nwords;  // every lane is active in every step
+    if (WORDS && full) {
+      // lane l works in the current slot from step l on, before that in the tail of the previous one
+      const uint32_t in_cur = cur_slot + in_off - 4u * lane, in_prev = prev_slot + in_off - 4u * lane + 128u;
+      const uint32_t out_cur = cur_slot + my_row_off - 4u * lane, out_prev = prev_slot + my_row_off - 4u * lane + 128u;
+#pragma unroll
+      for (int c8 = 0; c8 < 4; c8++) {
+        uint32_t fw[8], sw[8];
+        *reinterpret_cast<uint4 *>(&sw[0]) = *reinterpret_cast<const uint4 *>(ws + cur_slot + c8 * 32);
+        *reinterpret_cast<uint4 *>(&sw[4]) = *reinterpret_cast<const uint4 *>(ws + cur_slot + c8 * 32 + 16);
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+          const int i = c8 * 8 + k;
+          const uint8_t *ip = ws + ((int)lane <= i ? in_cur : in_prev) + 4 * i;
+          fw[k] = __byte_perm(*reinterpret_cast<const uint32_t *>(ip), *reinterpret_cast<const uint32_t *>(ip + 4), sel);
+        }
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+          const int i = c8 * 8 + k;
+          uint32_t up = __shfl_up_sync(FULL, st.last, 1);
+          if (lane == 0u) up = sw[k];
+          const uint32_t o = wave_word<D>(lf, st, fw[k], up);
+          *reinterpret_cast<uint32_t *>(ws + ((int)lane <= i ? out_cur : out_prev) + 4 * i) = o;
+        }
+      }
+    } else {
+#pragma unroll 1
+      for (uint32_t i = 0; i < 32u; i++) {
+        uint32_t up = __shfl_up_sync(FULL, WORDS ? st.last : last, 1);
+        const uint32_t j = p * 32u + i - lane;  // wraps to a huge value while the lane has not started
+        if (valid && j < nwords) {
+          const uint32_t wi = j & 31u;
+          const uint32_t slot_off = lane <= i ? cur_slot : prev_slot;
+          const uint8_t *ip = ws + slot_off + in_off + wi * 4u;
+          const uint32_t f = __byte_perm(*reinterpret_cast<const uint32_t *>(ip),
+                                         *reinterpret_cast<const uint32_t *>(ip + 4), sel);
+          if (lane == 0u) up = *reinterpret_cast<const uint32_t *>(ws + slot_off + wi * 4u);
+          uint32_t o;
+          if constexpr (WORDS) {
+            o = wave_word<D>(lf, st, f, up);
+          } else {
+            o = unf_word<BPP>(ft, f, up, o1, o2, u1, u2);
+            o2 = o1; o1 = o; u2 = u1; u1 = up; last = o;
+          }
+          *reinterpret_cast<uint32_t *>(ws + slot_off + my_row_off + wi * 4u) = o;
+        }
       }
     }
   }
@@ -222,49 +320,74 @@ __device__ void run_unit(const UnfStream &s, const uint32_t g, uint8_t *ws, uint
     store_block(stored);
     stored++;
   }
-  __syncwarp();
-  if (publish && lane == 0u) st_release_u32(my_prog, nblocks);
   __syncwarp();  // the ring is reused by the next unit
 }
 
-__global__ void __launch_bounds__(UW_WARPS * 32) unfilter_wave_kernel(const UwParams p) {
+// KBPP > 0: every chain of the launch has this filter distance (the common case: one pixel format per job),
+// which keeps the specialised kernels small.  KBPP == 0: mixed formats, dispatch per unit.
+template <int KBPP>
+__global__ void __launch_bounds__(UW_WARPS * 32, (KBPP == 4 || KBPP == 8) ? 4 : 3)
+    unfilter_wave_kernel(const UwParams p) {
   extern __shared__ __align__(16) uint8_t uw_smem[];
   const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
   uint8_t *ws = uw_smem + warp * UW_WARP_SMEM;
   for (;;) {
     uint32_t u = 0u;
     if (lane == 0u) u = atomicAdd(p.ticket, 1u);
-    u = __shfl_sync(0xffffffffu, u, 0);
+    u = __shfl_sync(FULL, u, 0);
     if (u >= p.n_units) break;
     const UnfUnit un = p.units[u];
     const UnfStream s = p.streams[un.stream];
-    switch (s.bpp) {
-      case 1: run_unit<1>(s, un.group, ws, p.progress, p.status); break;
-      case 2: run_unit<2>(s, un.group, ws, p.progress, p.status); break;
-      case 3: run_unit<3>(s, un.group, ws, p.progress, p.status); break;
-      case 4: run_unit<4>(s, un.group, ws, p.progress, p.status); break;
-      case 6: run_unit<6>(s, un.group, ws, p.progress, p.status); break;
-      case 8: run_unit<8>(s, un.group, ws, p.progress, p.status); break;
-      default: break;
+    if (KBPP > 0) {
+      run_unit<KBPP == 0 ? 4 : KBPP>(s, un.group, ws, p.seam, p.epoch, p.status);
+    } else {
+      switch (s.bpp) {
+        case 1: run_unit<1>(s, un.group, ws, p.seam, p.epoch, p.status); break;
+        case 2: run_unit<2>(s, un.group, ws, p.seam, p.epoch, p.status); break;
+        case 3: run_unit<3>(s, un.group, ws, p.seam, p.epoch, p.status); break;
+        case 4: run_unit<4>(s, un.group, ws, p.seam, p.epoch, p.status); break;
+        case 6: run_unit<6>(s, un.group, ws, p.seam, p.epoch, p.status); break;
+        case 8: run_unit<8>(s, un.group, ws, p.seam, p.epoch, p.status); break;
+        default: break;
+      }
     }
   }
 }
 
-cudaError_t launch_unfilter_wave(const UnfStream *d_streams, const UnfUnit *d_units, uint32_t n_units,
-                                 uint32_t *d_progress, uint32_t *d_ticket, DevStatus *d_status, int sm_count,
-                                 cudaStream_t st) {
-  if (n_units == 0) return cudaSuccess;
+template <int KBPP>
+static cudaError_t launch_uw(const UwParams &p, int sm_count, cudaStream_t st) {
   static int occ = -1;
   if (occ < 0) {
-    cudaFuncSetAttribute(unfilter_wave_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)UW_CTA_SMEM);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, unfilter_wave_kernel, UW_WARPS * 32, UW_CTA_SMEM);
+    cudaFuncSetAttribute(unfilter_wave_kernel<KBPP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)UW_CTA_SMEM);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, unfilter_wave_kernel<KBPP>, UW_WARPS * 32, UW_CTA_SMEM);
   }
   if (occ < 1) return cudaErrorLaunchOutOfResources;
-  UwParams p{d_streams, d_units, n_units, d_progress, d_ticket, d_status};
-  const uint32_t resident = (uint32_t)(occ * sm_count);  // every CTA of the grid is resident: see the header
-  const uint32_t want = (n_units + UW_WARPS - 1) / UW_WARPS;
-  unfilter_wave_kernel<<<want < resident ? want : resident, UW_WARPS * 32, UW_CTA_SMEM, st>>>(p);
+  // Residency is not needed for correctness (see "schedule" above); the grid is sized to it for balance.
+  const uint32_t resident = (uint32_t)(occ * sm_count);
+  const uint32_t want = (p.n_units + UW_WARPS - 1) / UW_WARPS;
+  unfilter_wave_kernel<KBPP><<<want < resident ? want : resident, UW_WARPS * 32, UW_CTA_SMEM, st>>>(p);
   return cudaGetLastError();
+}
+
+size_t unfilter_wave_seam_bytes(uint32_t rows, uint32_t row_bytes) {
+  const size_t groups = (rows + 31u) / 32u, nblocks = ((row_bytes + 3u) / 4u + 31u) / 32u;
+  return groups * nblocks * 32u * sizeof(uint2);
+}
+
+cudaError_t launch_unfilter_wave(const UnfStream *d_streams, const UnfUnit *d_units, uint32_t n_units, void *d_seam,
+                                 uint32_t epoch, uint32_t *d_ticket, DevStatus *d_status, int sm_count,
+                                 uint32_t uniform_bpp, cudaStream_t st) {
+  if (n_units == 0) return cudaSuccess;
+  const UwParams p{d_streams, d_units, n_units, reinterpret_cast<uint2 *>(d_seam), epoch, d_ticket, d_status};
+  switch (uniform_bpp) {
+    case 1: return launch_uw<1>(p, sm_count, st);
+    case 2: return launch_uw<2>(p, sm_count, st);
+    case 3: return launch_uw<3>(p, sm_count, st);
+    case 4: return launch_uw<4>(p, sm_count, st);
+    case 6: return launch_uw<6>(p, sm_count, st);
+    case 8: return launch_uw<8>(p, sm_count, st);
+    default: return launch_uw<0>(p, sm_count, st);
+  }
 }
 
 }  // namespace stitch
