@@ -40,13 +40,23 @@ ALG_BYTES_PER_PX = 8.0          # fused composite+filter: read 4*coverage(=1) + 
 UNF_BYTES_PER_PX = 8.0          # unfilter: read 4 + write 4 per tile pixel
 
 
+WORKLOAD_CONFIG = {
+    "workload": "C2: 16x16 grid of 1024x1024 RGBA8 tiles (inflated filtered streams) -> 16384x16384 "
+                "filtered PNG scanlines per GPU; N GPUs = N row bands of one 16384x(16384*N) canvas",
+    "l2": "inputs (1.07 GB) and outputs (1.07 GB) per step exceed the 126 MB L2; no flush needed",
+    "step": "unfilter(256 tiles) + composite + filter-select",
+}
+
+
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--cpu-sample-rows", type=int, default=512)
+    ap.add_argument("--cpu-sample-rows", type=int, default=1024)
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU work in the cpu_baseline leg")
+    ap.add_argument("--cpu-threads", type=int, default=0, help="0 = all host cores (at most one per tile column)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
 
@@ -155,29 +165,36 @@ def cpu_sample(tiles, rows: int, threads: int, repeats: int = 1):
     return px / dt / 1e6, dt
 
 
+def cpu_threads(args) -> int:
+    return max(1, min(args.cpu_threads or (os.cpu_count() or 1), GRID))
+
+
 def run_reference(args, rank: int, world: int):
     if rank != 0:
         return
     tiles = make_tiles(2)
-    cores = os.cpu_count() or 1
-    threads = min(cores, GRID)
+    threads = cpu_threads(args)
     rows = args.cpu_sample_rows
+    # One step = `reps` passes over the sample; reps is fixed before the timed region so every step is the same work.
+    _, dt1 = cpu_sample(tiles, rows, threads)
+    reps = max(1, int(round(2.0 / max(dt1, 1e-3))))
     for _ in range(args.warmup):
-        cpu_sample(tiles, min(rows, 64), threads)
+        cpu_sample(tiles, rows, threads, 1)
     t0 = time.perf_counter()
     px = 0.0
     for _ in range(args.steps):
-        mp, dt = cpu_sample(tiles, rows, threads)
+        mp, dt = cpu_sample(tiles, rows, threads, reps)
         px += mp * dt
     total = time.perf_counter() - t0
     value = px / total
-    sample = f"top {min(rows, TILE)} canvas rows of the 16384-wide grid per step ({GRID} tile columns), unfilter+composite+filter"
+    sample = (f"{reps} x top {min(rows, TILE)} canvas rows of the 16384-wide grid per step ({GRID} tile columns), "
+              f"unfilter+composite+filter, {threads} threads")
     line = {
         "impl": "reference", "metric": "composited output MPix/s", "value": value, "unit": "MPix/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": total / args.steps * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": "C2: 16x16 grid of 1024x1024 RGBA8 tiles -> 16384x16384 PNG scanlines",
-                   "note": "CPU restatement of the TypeScript reference (oracle/, C, -O2); no JS runtime on this box"},
+        "config": dict(WORKLOAD_CONFIG, note="CPU restatement of the TypeScript reference (oracle/, C, -O2) on the host "
+                                             "cores; no JS runtime on this box; each step is a bounded sample"),
         "cpu_baseline": {"value": value, "unit": "MPix/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "MPix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -310,10 +327,7 @@ def run_ours(args, rank: int, world: int, local_rank: int):
         "metric": "composited output MPix/s", "value": value, "unit": "MPix/s", "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": "C2: 16x16 grid of 1024x1024 RGBA8 tiles (inflated filtered streams) -> 16384x16384 "
-                               "filtered PNG scanlines per GPU; N GPUs = N row bands of one 16384x(16384*N) canvas",
-                   "l2": "inputs (1.07 GB) and outputs (1.07 GB) per step exceed the 126 MB L2; no flush needed",
-                   "step": "unfilter(256 tiles) + composite + filter-select"},
+        "config": dict(WORKLOAD_CONFIG),
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": "MPix/s", "h2d_bytes_per_step": n_tiles * stream_len * world,
                 "d2h_bytes_per_step": out_row * CANVAS * world, "ms_per_step": e2e_ms / e2e_steps,
@@ -327,11 +341,14 @@ def run_ours(args, rank: int, world: int, local_rank: int):
                     "compose_filter": {"avg_ms": cmp_avg, "achieved_GBps": achieved, "frac": achieved / peak}},
     }
     if not args.no_cpu_baseline:
-        threads = 1
-        mp, dt = cpu_sample(tiles, args.cpu_sample_rows, threads)
+        threads = cpu_threads(args)
+        _, dt1 = cpu_sample(tiles, args.cpu_sample_rows, threads)
+        reps = max(1, int(round(args.cpu_seconds / max(dt1, 1e-3))))
+        mp, dt = cpu_sample(tiles, args.cpu_sample_rows, threads, reps)
         line["cpu_baseline"] = {"value": mp, "unit": "MPix/s", "cores": threads, "kind": "port",
-                                "sample": f"top {min(args.cpu_sample_rows, TILE)} rows of the same 16384-wide grid, "
-                                          f"{dt:.1f} s of oracle (C restatement of the TS reference) on 1 thread"}
+                                "sample": f"{reps} x top {min(args.cpu_sample_rows, TILE)} rows of the same 16384-wide grid "
+                                          f"({dt:.1f} s wall, {threads} threads) through the oracle "
+                                          f"(C restatement of the TS reference, oracle/)"}
     print(json.dumps(line), flush=True)
     ctx.close()
 

@@ -259,7 +259,7 @@ __device__ void run_unit(const UnfStream &s, const uint32_t g, uint8_t *ws, uint
     const uint32_t cur_slot = (p % 3u) * UW_SLOT_BYTES, prev_slot = ((p + 2u) % 3u) * UW_SLOT_BYTES;
     if (has_above && p < nblocks) {  // seam block p -> row 0 of the current slot; block p+1 is requested early
       while (!__all_sync(FULL, ab.y == epoch)) {
-        __nanosleep(32);
+        __nanosleep(100);
         if (ab.y != epoch) ab = ld_pair(ab_seam + p * 32u);
       }
       *reinterpret_cast<uint32_t *>(ws + cur_slot + lane * 4u) = ab.x;
