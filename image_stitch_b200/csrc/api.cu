@@ -154,7 +154,7 @@ extern "C" void stitch_job_destroy(stitch_job *job) {
   dev_free(ctx, job->d_tiles); dev_free(ctx, job->d_bin_start); dev_free(ctx, job->d_bin_tiles);
   dev_free(ctx, job->d_streams); dev_free(ctx, job->d_a7);
   dev_free(ctx, job->d_slow); dev_free(ctx, job->d_units); dev_free(ctx, job->d_uprog);
-  dev_free(ctx, job->d_canvas); dev_free(ctx, job->d_out); dev_free(ctx, job->d_sync);
+  dev_free(ctx, job->d_canvas); dev_free(ctx, job->d_out); dev_free(ctx, job->d_sync); dev_free(ctx, job->d_plans);
   for (auto &q : job->d_jpeg) dev_free(ctx, q);
   if (job->h_jpeg_totals) cudaFreeHost(job->h_jpeg_totals);
   cudaStreamSynchronize(ctx->stream);
@@ -566,8 +566,10 @@ extern "C" int stitch_job_run_band(stitch_job *job, uint32_t y0, uint32_t y1, ui
       bg_words(jd, fp.bg_lo, fp.bg_hi);
       fp.rowsum = reinterpret_cast<unsigned long long *>(job->d_sync); fp.ticket = job->d_sync + (size_t)n_rows * 16;
       fp.out = job->d_out; fp.out_pitch = job->out_pitch; fp.lead = (uint32_t)job->out_lead;
+      if ((rc = ensure_buffer(ctx, &job->d_plans, &job->plans_bytes, fused_plan_bytes(fp.n_bands * fp.nseg)))) return rc;
+      fp.plans = job->d_plans;
       cudaError_t fe = launch_fused(fp, jd.out_bit_depth == 16, ctx->sm_count, ctx->stream);
-      if (fe == cudaSuccess) { fused_done = true; launches += 1; }
+      if (fe == cudaSuccess) { fused_done = true; launches += 2; }
       else if (fe != cudaErrorInvalidConfiguration) CK(fe);
       else cudaGetLastError();
     }

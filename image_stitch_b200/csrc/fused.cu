@@ -195,19 +195,24 @@ struct UnitPlan {
   bool halo_fast, left_fast;
 };
 
-template <int BPW>
-__device__ __forceinline__ UnitPlan unit_plan(const FusedParams &p, const uint32_t u) {
-  constexpr int PXQ = 4 / BPW;  // pixels per quad
-  UnitPlan pl;
+// Rows and columns of unit u (pure arithmetic).
+__device__ __forceinline__ void unit_geom(const FusedParams &p, const uint32_t u, UnitPlan &pl) {
   const uint32_t band = u / p.nseg;
   pl.seg = u - band * p.nseg;
   const uint32_t band_abs = p.band0 + band;
   const int ya = max((int)p.y_begin, (int)(band_abs * FU_R));
   const int yb = min((int)p.y_end, (int)((band_abs + 1) * FU_R));
   pl.ya = ya; pl.nrows = yb - ya;
-  const int xw0 = (int)pl.seg * FU_SW;
-  pl.xw0 = xw0;
-  const uint32_t bin = (band_abs * FU_R / FB_R) * p.bins_x + (uint32_t)(xw0 / FB_SWW);
+  pl.xw0 = (int)pl.seg * FU_SW;
+}
+
+template <int BPW>
+__device__ __forceinline__ UnitPlan unit_plan(const FusedParams &p, const uint32_t u) {
+  constexpr int PXQ = 4 / BPW;  // pixels per quad
+  UnitPlan pl;
+  unit_geom(p, u, pl);
+  const int ya = pl.ya, yb = pl.ya + pl.nrows, xw0 = pl.xw0;
+  const uint32_t bin = ((uint32_t)ya / FB_R) * p.bins_x + (uint32_t)(xw0 / FB_SWW);
   const uint32_t b0 = __ldg(p.bin_start + bin), n_list = __ldg(p.bin_start + bin + 1) - b0;
   const uint32_t *list = p.bin_tiles + b0;
   pl.list = list; pl.n_list = n_list;
@@ -232,6 +237,51 @@ __device__ __forceinline__ UnitPlan unit_plan(const FusedParams &p, const uint32
     }
     break;
   }
+  return pl;
+}
+
+// The plans depend on the job's geometry only, not on pixel data: a small kernel writes one 32-byte record
+// per unit ahead of the fused kernel, whose warps then need a single load (instead of the dependent
+// bin -> list -> tile chain) between taking a ticket and issuing the unit's copies.
+struct __align__(16) PlanRec {
+  const uint8_t *fast_src;
+  uint32_t fast_pitch;
+  uint32_t list_off;   // into bin_tiles
+  uint32_t n_list;
+  uint32_t flags;      // bit 0 halo_fast, bit 1 left_fast
+  uint32_t pad[2];
+};
+static_assert(sizeof(PlanRec) == 32, "two 16-byte loads per record");
+
+template <int BPW>
+__global__ void fused_plan_kernel(const FusedParams p, PlanRec *recs, const uint32_t n_units) {
+  const uint32_t u = blockIdx.x * blockDim.x + threadIdx.x;
+  if (u >= n_units) return;
+  const UnitPlan pl = unit_plan<BPW>(p, u);
+  PlanRec r;
+  r.fast_src = pl.fast_src; r.fast_pitch = pl.fast_pitch;
+  r.list_off = (uint32_t)(pl.list - p.bin_tiles); r.n_list = pl.n_list;
+  r.flags = (pl.halo_fast ? 1u : 0u) | (pl.left_fast ? 2u : 0u);
+  r.pad[0] = r.pad[1] = 0u;
+  recs[u] = r;
+}
+
+struct PlanRaw { uint4 a, b; };
+__device__ __forceinline__ PlanRaw plan_fetch(const FusedParams &p, const uint32_t u) {
+  const uint4 *q = reinterpret_cast<const uint4 *>(reinterpret_cast<const PlanRec *>(p.plans) + u);
+  PlanRaw r;
+  r.a = __ldg(q); r.b = __ldg(q + 1);
+  return r;
+}
+__device__ __forceinline__ UnitPlan plan_make(const FusedParams &p, const uint32_t u, const PlanRaw &r) {
+  UnitPlan pl;
+  unit_geom(p, u, pl);
+  pl.fast_src = reinterpret_cast<const uint8_t *>(((unsigned long long)r.a.y << 32) | r.a.x);
+  pl.fast_pitch = r.a.z;
+  pl.list = p.bin_tiles + r.a.w;
+  pl.n_list = r.b.x;
+  pl.halo_fast = (r.b.y & 1u) != 0u;
+  pl.left_fast = (r.b.y & 2u) != 0u;
   return pl;
 }
 
@@ -317,20 +367,15 @@ struct UnitRef {
   int ya, nrows;
 };
 
-// ---- phase B: wait until every unit of the band has added its sums, pick the winner per row, write ----
-template <int BPW>
-__device__ __forceinline__ void unit_emit(const FusedParams &p, const UnitRef &ref, const uint32_t *stash, const uint32_t lane) {
-  const uint32_t *raw = stash, *pfw = stash + FU_RAW_WORDS, *lcs = pfw + FU_PF_WORDS;
-  const int wmax = (int)p.canvas_w * BPW;
-  const int ya = ref.ya, nrows = ref.nrows;
-  const int qw = (int)ref.seg * FU_SW + 4 * (int)lane;
-  // Each 64-bit row-sum word carries its own arrival count in the high half, so the sums need no fence
-  // and no separate "band done" flag: lane r reads row r's five words until all five are complete.
+// ---- phase B, part 1: wait until every unit of the band has added its sums; lane r gets row r's winner ----
+// Each 64-bit row-sum word carries its own arrival count in the high half, so the sums need no fence
+// and no separate "band done" flag: lane r reads row r's five words until all five are complete.
+__device__ __forceinline__ uint32_t unit_wait(const FusedParams &p, const UnitRef &ref, const uint32_t lane) {
   uint32_t my_ft = 0u;
   for (;;) {
     bool ready = true;
-    if ((int)lane < nrows) {
-      const unsigned long long *rs = p.rowsum + (size_t)(ya + (int)lane - (int)p.y_begin) * 8;
+    if ((int)lane < ref.nrows) {
+      const unsigned long long *rs = p.rowsum + (size_t)(ref.ya + (int)lane - (int)p.y_begin) * 8;
       unsigned long long w0, w1, w2, w3, w4;
       asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w0), "=l"(w1) : "l"(rs) : "memory");
       asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w2), "=l"(w3) : "l"(rs + 2) : "memory");
@@ -348,10 +393,20 @@ __device__ __forceinline__ void unit_emit(const FusedParams &p, const UnitRef &r
     if (__all_sync(0xffffffffu, ready)) break;
     __nanosleep(100);
   }
-  uint8_t *orow = p.out + (size_t)(ya - (int)p.y_begin) * p.out_pitch + p.lead;
-  const uint32_t *cur_row = raw + FU_SW + 4 * lane, *pf_row = pfw + 4 * lane, *lcs_row = lcs + 2;
+  return my_ft;
+}
+
+// ---- phase B, part 2: rows [r0, r1) of the unit: the winner's bytes, one 128-bit store per lane per row ----
+template <int BPW>
+__device__ __forceinline__ void unit_emit(const FusedParams &p, const UnitRef &ref, const uint32_t *stash, const uint32_t lane,
+                                          const uint32_t my_ft, const int r0, const int r1) {
+  const uint32_t *raw = stash, *pfw = stash + FU_RAW_WORDS, *lcs = pfw + FU_PF_WORDS;
+  const int wmax = (int)p.canvas_w * BPW;
+  const int qw = (int)ref.seg * FU_SW + 4 * (int)lane;
+  uint8_t *orow = p.out + (size_t)(ref.ya + r0 - (int)p.y_begin) * p.out_pitch + p.lead;
+  const uint32_t *cur_row = raw + (r0 + 1) * FU_SW + 4 * lane, *pf_row = pfw + r0 * FU_SW + 4 * lane, *lcs_row = lcs + 2 * (r0 + 1);
   const bool whole = qw + 4 <= wmax;
-  for (int r = 0; r < nrows; r++, orow += p.out_pitch, cur_row += FU_SW, pf_row += FU_SW, lcs_row += 2) {
+  for (int r = r0; r < r1; r++, orow += p.out_pitch, cur_row += FU_SW, pf_row += FU_SW, lcs_row += 2) {
     const uint32_t ft = __shfl_sync(0xffffffffu, my_ft, r);
     if (ref.seg == 0u && lane == 0u) orow[0] = (uint8_t)ft;
     uint4 o;
@@ -387,18 +442,23 @@ __device__ __forceinline__ void unit_emit(const FusedParams &p, const UnitRef &r
       if (qw + 2 < wmax) odat[2] = o.z;
     }
   }
-  __syncwarp();  // the stash is free again
 }
 
-// Software pipeline per warp (two stashes):
-//   load(u_k) issued -> plan(u_k+1) built while those copies fly -> sweep(u_k) -> emit(u_k-1)
-// so the band of u_k-1 has had a whole sweep's time to complete and the poll in unit_emit returns at once.
+// Software pipeline per warp (two stashes), units handed out by an atomic ticket:
 //
-// Units are dealt round-robin: warp w of W owns units w, w+W, w+2W, ...  The grid is launched
-// cooperatively (all W warps resident) with W >= units per band, so the units of one band belong to
-// distinct warps at iteration k-1, k or k+1 of their sequences.  emit at iteration k-1 waits only for
-// sweeps of iterations <= k+... of OTHER warps, and a sweep never waits: by induction on the iteration
-// index the wait graph has no cycle, whatever the timing (sweep_k <- emit_k-2 <- sweeps of iterations <= k-1).
+//   sweep(u_k) -> wait(u_k-1) -> take ticket u_k+1 -> emit(u_k-1), the ticket and the plan record of
+//   u_k+1 arriving meanwhile -> load(u_k+1) into the stash just emitted -> sweep(u_k+1) ...
+//
+// so the band of u_k-1 has had a whole sweep's time to complete and wait() normally returns at once.
+//
+// No wait cycle can form.  A warp blocks only in wait(), and whenever it does every ticket it has taken is
+// already swept (it takes the next one after wait() returns and sweeps it before it can block again: emit,
+// load and sweep never wait).  Suppose every running warp were blocked, and let B be the lowest band any
+// of them waits for.  Each blocked warp holds two tickets (u_k-1 and u_k) in bands >= B.  If some ticket of B
+// had not been taken yet, all held tickets would lie in B itself, but 2 x (running warps) > units per band
+// (launch_fused checks it; the cooperative launch makes the whole grid resident).  So all of B is taken;
+// its units are swept (held by blocked or finished warps), B is complete, and the warps waiting for it
+// are not blocked after all.
 template <int BPW>
 __global__ void __launch_bounds__(FU_WARPS * 32, 3) fused_kernel(const FusedParams p) {
   extern __shared__ __align__(16) uint32_t fu_smem[];
@@ -410,33 +470,44 @@ __global__ void __launch_bounds__(FU_WARPS * 32, 3) fused_kernel(const FusedPara
 #pragma unroll
   for (int f = 0; f < 5; f++) lmask[f] = lane == (uint32_t)f ? 0xffffffffu : 0u;
 
-  uint32_t u = blockIdx.x * FU_WARPS + warp;
+  uint32_t u = blockIdx.x * FU_WARPS + warp;  // first unit: the warp's own index; tickets continue from n_warps
   if (u >= n_units) return;
-  UnitPlan plan = unit_plan<BPW>(p, u);
+  UnitPlan plan = plan_make(p, u, plan_fetch(p, u));
+  unit_load<BPW>(p, plan, cur_stash, lane);
   UnitRef prev;
   prev.seg = 0; prev.ya = 0; prev.nrows = 0;
   bool have_prev = false;
   for (;;) {
-    unit_load<BPW>(p, plan, cur_stash, lane);
-    u += n_warps;
-    const bool more = u < n_units;
-    UnitPlan plan_next = plan;
-    if (more) plan_next = unit_plan<BPW>(p, u);
     unit_sweep<BPW>(p, plan, cur_stash, lane, lmask);
-    if (have_prev) unit_emit<BPW>(p, prev, prev_stash, lane);
+    uint32_t ft = 0u;
+    if (have_prev) ft = unit_wait(p, prev, lane);
+    uint32_t t = 0u;
+    if (lane == 0u) t = atomicAdd(p.ticket, 1u);
+    const int half = prev.nrows >> 1;
+    if (have_prev) unit_emit<BPW>(p, prev, prev_stash, lane, ft, 0, half);
+    u = n_warps + __shfl_sync(0xffffffffu, t, 0);
+    const bool more = u < n_units;
+    PlanRaw raw_next;
+    if (more) raw_next = plan_fetch(p, u);
+    if (have_prev) unit_emit<BPW>(p, prev, prev_stash, lane, ft, half, prev.nrows);
+    __syncwarp();  // prev_stash is free again
     prev.seg = plan.seg; prev.ya = plan.ya; prev.nrows = plan.nrows;
     have_prev = true;
     uint32_t *sw = cur_stash; cur_stash = prev_stash; prev_stash = sw;
     if (!more) break;
-    plan = plan_next;
+    plan = plan_make(p, u, raw_next);
+    unit_load<BPW>(p, plan, cur_stash, lane);
   }
-  unit_emit<BPW>(p, prev, prev_stash, lane);
+  const uint32_t ft = unit_wait(p, prev, lane);
+  unit_emit<BPW>(p, prev, prev_stash, lane, ft, 0, prev.nrows);
 }
 
 uint32_t fused_rows_per_band() { return FB_R; }
 uint32_t fused_words_per_seg() { return FB_SWW; }
 uint32_t fused_unit_rows() { return FU_R; }
 uint32_t fused_unit_words() { return FU_SW; }
+
+size_t fused_plan_bytes(uint32_t n_units) { return (size_t)n_units * sizeof(PlanRec); }
 
 cudaError_t launch_fused(const FusedParams &p, bool out16, int sm_count, cudaStream_t st) {
   static int occ8 = -1, occ16 = -1;
@@ -451,7 +522,13 @@ cudaError_t launch_fused(const FusedParams &p, bool out16, int sm_count, cudaStr
   const uint32_t n_units = p.n_bands * p.nseg;
   const uint32_t want = (n_units + FU_WARPS - 1) / FU_WARPS, resident = (uint32_t)(occ * sm_count);
   const uint32_t grid = want < resident ? want : resident;
-  if (grid * FU_WARPS < p.nseg) return cudaErrorInvalidConfiguration;  // caller falls back to the two-pass path
+  // wait-freedom needs 2 x warps > units per band (see fused_kernel); wider rows take the two-pass path
+  if (2u * grid * FU_WARPS <= p.nseg) return cudaErrorInvalidConfiguration;
+  PlanRec *recs = reinterpret_cast<PlanRec *>(p.plans);
+  if (out16) fused_plan_kernel<2><<<(n_units + 255u) / 256u, 256, 0, st>>>(p, recs, n_units);
+  else fused_plan_kernel<1><<<(n_units + 255u) / 256u, 256, 0, st>>>(p, recs, n_units);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
   // Cooperative launch: the runtime guarantees that every CTA of the grid is resident (or fails),
   // which the wait-freedom argument above fused_kernel relies on.
   FusedParams pp = p;

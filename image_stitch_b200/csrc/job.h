@@ -52,6 +52,7 @@ struct stitch_job {
   uint32_t *d_sync = nullptr; size_t sync_words = 0;   // fused kernel: rowsum | band_done | ticket
   bool force_two_pass = false;
   // band buffers
+  uint8_t *d_plans = nullptr; size_t plans_bytes = 0;  // fused kernel: per-unit plan records
   uint8_t *d_canvas = nullptr; size_t canvas_bytes = 0; size_t canvas_pitch = 0;
   uint8_t *d_out = nullptr; size_t out_bytes = 0;
   size_t out_pitch = 0, out_lead = 0, out_row_bytes = 0;

@@ -49,11 +49,13 @@ struct FusedParams {
   uint32_t bg_lo, bg_hi;
   unsigned long long *rowsum; // [(y_end - y_begin)][8], zeroed: low half = cost sum, high half = units arrived
   uint32_t *ticket;           // zeroed
+  void *plans;                // fused_plan_bytes(n_bands * nseg) of scratch: per-unit plan records
   uint8_t *out;               // row r: filter byte at out + r*out_pitch + lead
   size_t out_pitch;
   uint32_t lead;
 };
 cudaError_t launch_fused(const FusedParams &p, bool out16, int sm_count, cudaStream_t st);
+size_t fused_plan_bytes(uint32_t n_units);
 uint32_t fused_rows_per_band();
 uint32_t fused_words_per_seg();
 uint32_t fused_unit_rows();
