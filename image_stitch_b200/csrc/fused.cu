@@ -36,12 +36,21 @@ static constexpr int FB_SWW = 512;  // bin width in 32-bit words
 
 static constexpr int FU_R = 8;                       // rows per unit
 static constexpr int FU_SW = 128;                    // words per unit row
-static constexpr int FU_WARPS = 4;                   // workers per CTA
+static constexpr int FU_WARPS = 16;                  // workers per CTA (one CTA per SM)
 static constexpr int FU_RAW_WORDS = (FU_R + 1) * FU_SW;  // row 0 = predictor row above the unit
-static constexpr int FU_PF_WORDS = FU_R * FU_SW;
 static constexpr int FU_LC_WORDS = ((FU_R + 1) * 2 + 3) / 4 * 4;  // two words left of every row
-static constexpr int FU_WARP_WORDS = FU_RAW_WORDS + FU_PF_WORDS + FU_LC_WORDS;
-static constexpr size_t FU_CTA_SMEM = (size_t)FU_WARPS * 2 * FU_WARP_WORDS * 4;  // two stashes per warp
+static constexpr int FU_WARP_WORDS = FU_RAW_WORDS + FU_LC_WORDS;
+static constexpr int FU_SLOTS = 2;                   // stashes per warp
+static constexpr size_t FU_CTA_SMEM = (size_t)FU_WARPS * FU_SLOTS * FU_WARP_WORDS * 4 + 16;  // + TMEM base address
+// The Paeth residuals of a unit (FU_R rows x 16 bytes per lane) wait for the row winners in TENSOR MEMORY:
+// lane l of warp w owns TMEM lane 32 (w % 4) + l (a warp reaches only that quarter), warps w / 4 = 0..3 use
+// disjoint column ranges, one unit takes FU_R * 4 columns.  This is plain scratch use of
+// TMEM (tcgen05.st / tcgen05.ld, no MMA): it takes the residuals out of shared memory, which is what limits
+// the number of resident warps.
+static constexpr int FU_TMEM_SLOT_COLS = FU_R * 4;
+static constexpr int FU_TMEM_COLS = 256;             // power of two >= (FU_WARPS / 4) * FU_SLOTS * FU_TMEM_SLOT_COLS
+static constexpr int FU_MAX_CTAS = 512 / FU_TMEM_COLS;  // more CTAs per SM than this would spin in tcgen05.alloc
+static_assert((FU_WARPS / 4) * FU_SLOTS * FU_TMEM_SLOT_COLS <= FU_TMEM_COLS && FU_WARPS % 4 == 0, "TMEM stash layout");
 static_assert(FB_R % FU_R == 0 && FB_SWW % FU_SW == 0, "a unit must lie inside one bin");
 
 // ---- packed-byte helpers ------------------------------------------------------
@@ -51,6 +60,18 @@ __device__ __forceinline__ uint32_t acc_abs_s4(uint32_t v, uint32_t acc) {
   uint32_t r;
   asm("vabsdiff4.u32.s32.s32.add %0, %1, %2, %3;" : "=r"(r) : "r"(v), "r"(0u), "r"(acc));
   return r;
+}
+
+__device__ __forceinline__ void tmem_st4(uint32_t taddr, const uint4 v) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};"
+               ::"r"(taddr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ uint4 tmem_ld4(uint32_t taddr) {
+  uint4 v;
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(taddr) : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+  return v;
 }
 
 // Paeth-filtered bytes of two lanes: low byte of (x - paeth(a,b,c) + 1280) in each half.
@@ -138,7 +159,7 @@ __device__ __forceinline__ void fu_cp_async16(void *smem, const void *gmem) {
 template <int BPW, bool GUARD>
 __device__ __forceinline__ void sweep_row(const uint4 cur, const uint32_t lc0, const uint32_t lc1, const uint4 up,
                                           const H4 (&hb)[4], const H4 (&hlu)[2], H4 (&hx)[4], H4 (&hlc)[2], int qw,
-                                          int wmax, uint32_t *pf_out, uint32_t (&sum)[5]) {
+                                          int wmax, uint32_t pf_taddr, uint32_t (&sum)[5]) {
   const uint32_t x[4] = {cur.x, cur.y, cur.z, cur.w}, b[4] = {up.x, up.y, up.z, up.w};
   const uint32_t lc[2] = {lc0, lc1};
   if (BPW == 2) hlc[0] = unpack_h4(lc0);
@@ -159,13 +180,13 @@ __device__ __forceinline__ void sweep_row(const uint4 cur, const uint32_t lc0, c
       s4 = acc_abs_s4(pf[j], s4);
     }
   }
-  *reinterpret_cast<uint4 *>(pf_out) = make_uint4(pf[0], pf[1], pf[2], pf[3]);
+  tmem_st4(pf_taddr, make_uint4(pf[0], pf[1], pf[2], pf[3]));
   sum[0] = s0; sum[1] = s1; sum[2] = s2; sum[3] = s3; sum[4] = s4;
 }
 
 // Row r of the unit: loads, left context, costs, warp reduction, one red.global per candidate.
 template <int BPW>
-__device__ __forceinline__ void sweep_step(const uint32_t *raw_row, const uint32_t *lcs_row, uint32_t *pf_row,
+__device__ __forceinline__ void sweep_step(const uint32_t *raw_row, const uint32_t *lcs_row, uint32_t pf_row,
                                            unsigned long long *rs_row, uint32_t lane, const uint32_t (&lmask)[5], bool guard,
                                            int qw, int wmax, uint4 &up, const H4 (&hb)[4], const H4 (&hlu)[2],
                                            H4 (&hx)[4], H4 (&hlc)[2]) {
@@ -174,8 +195,8 @@ __device__ __forceinline__ void sweep_step(const uint32_t *raw_row, const uint32
   uint32_t c1 = __shfl_up_sync(0xffffffffu, cur.w, 1);
   if (lane == 0u) { c0 = lcs_row[0]; c1 = lcs_row[1]; }
   uint32_t sum[5];
-  if (guard) sweep_row<BPW, true>(cur, c0, c1, up, hb, hlu, hx, hlc, qw, wmax, pf_row + 4 * lane, sum);
-  else sweep_row<BPW, false>(cur, c0, c1, up, hb, hlu, hx, hlc, qw, wmax, pf_row + 4 * lane, sum);
+  if (guard) sweep_row<BPW, true>(cur, c0, c1, up, hb, hlu, hx, hlc, qw, wmax, pf_row, sum);
+  else sweep_row<BPW, false>(cur, c0, c1, up, hb, hlu, hx, hlc, qw, wmax, pf_row, sum);
   uint32_t v = 0u;
 #pragma unroll
   for (int f = 0; f < 5; f++) v |= __reduce_add_sync(0xffffffffu, sum[f]) & lmask[f];
@@ -288,7 +309,7 @@ __device__ __forceinline__ UnitPlan plan_make(const FusedParams &p, const uint32
 // ---- phase A: raw stash <- composited pixels of rows ya-1 .. yb-1 (cp.async left in flight) ----
 template <int BPW>
 __device__ __forceinline__ void unit_load(const FusedParams &p, const UnitPlan &pl, uint32_t *stash, const uint32_t lane) {
-  uint32_t *raw = stash, *lcs = stash + FU_RAW_WORDS + FU_PF_WORDS;
+  uint32_t *raw = stash, *lcs = stash + FU_RAW_WORDS;
   const int wmax = (int)p.canvas_w * BPW;  // words per canvas row
   const int ya = pl.ya, nrows = pl.nrows, xw0 = pl.xw0, qw = xw0 + 4 * (int)lane;
   const uint8_t *fast_src = pl.fast_src;
@@ -333,9 +354,9 @@ __device__ __forceinline__ void unit_load(const FusedParams &p, const UnitPlan &
 
 // ---- sweep: filter costs of every row, Paeth residuals into the stash, partial sums published ----
 template <int BPW>
-__device__ __forceinline__ void unit_sweep(const FusedParams &p, const UnitPlan &pl, uint32_t *stash, const uint32_t lane,
-                                           const uint32_t (&lmask)[5]) {
-  uint32_t *raw = stash, *pfw = stash + FU_RAW_WORDS, *lcs = pfw + FU_PF_WORDS;
+__device__ __forceinline__ void unit_sweep(const FusedParams &p, const UnitPlan &pl, uint32_t *stash, const uint32_t pf_taddr,
+                                           const uint32_t lane, const uint32_t (&lmask)[5]) {
+  uint32_t *raw = stash, *lcs = stash + FU_RAW_WORDS;
   const int wmax = (int)p.canvas_w * BPW;
   const int nrows = pl.nrows, qw = pl.xw0 + 4 * (int)lane;
   const bool guard = pl.xw0 + FU_SW > wmax;
@@ -349,16 +370,17 @@ __device__ __forceinline__ void unit_sweep(const FusedParams &p, const UnitPlan 
   hlA[0] = unpack_h4(l0); hlA[1] = unpack_h4(l1);
   const uint32_t *raw_row = raw + FU_SW;
   const uint32_t *lcs_row = lcs + 2;
-  uint32_t *pf_row = pfw;
+  uint32_t pf_row = pf_taddr;
   unsigned long long *rs_row = p.rowsum + (size_t)(pl.ya - (int)p.y_begin) * 8;
   int r = 0;
   for (; r + 2 <= nrows; r += 2) {
     sweep_step<BPW>(raw_row, lcs_row, pf_row, rs_row, lane, lmask, guard, qw, wmax, up, hA, hlA, hB, hlB);
-    sweep_step<BPW>(raw_row + FU_SW, lcs_row + 2, pf_row + FU_SW, rs_row + 8, lane, lmask, guard, qw, wmax, up, hB, hlB,
+    sweep_step<BPW>(raw_row + FU_SW, lcs_row + 2, pf_row + 4, rs_row + 8, lane, lmask, guard, qw, wmax, up, hB, hlB,
                     hA, hlA);
-    raw_row += 2 * FU_SW; lcs_row += 4; pf_row += 2 * FU_SW; rs_row += 16;
+    raw_row += 2 * FU_SW; lcs_row += 4; pf_row += 8; rs_row += 16;
   }
   if (r < nrows) sweep_step<BPW>(raw_row, lcs_row, pf_row, rs_row, lane, lmask, guard, qw, wmax, up, hA, hlA, hB, hlB);
+  asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
 }
 
 // What phase B needs to know about a unit after its sweep is over.
@@ -398,20 +420,22 @@ __device__ __forceinline__ uint32_t unit_wait(const FusedParams &p, const UnitRe
 
 // ---- phase B, part 2: rows [r0, r1) of the unit: the winner's bytes, one 128-bit store per lane per row ----
 template <int BPW>
-__device__ __forceinline__ void unit_emit(const FusedParams &p, const UnitRef &ref, const uint32_t *stash, const uint32_t lane,
-                                          const uint32_t my_ft, const int r0, const int r1) {
-  const uint32_t *raw = stash, *pfw = stash + FU_RAW_WORDS, *lcs = pfw + FU_PF_WORDS;
+__device__ __forceinline__ void unit_emit(const FusedParams &p, const UnitRef &ref, const uint32_t *stash,
+                                          const uint32_t pf_taddr, const uint32_t lane, const uint32_t my_ft, const int r0,
+                                          const int r1) {
+  const uint32_t *raw = stash, *lcs = stash + FU_RAW_WORDS;
   const int wmax = (int)p.canvas_w * BPW;
   const int qw = (int)ref.seg * FU_SW + 4 * (int)lane;
   uint8_t *orow = p.out + (size_t)(ref.ya + r0 - (int)p.y_begin) * p.out_pitch + p.lead;
-  const uint32_t *cur_row = raw + (r0 + 1) * FU_SW + 4 * lane, *pf_row = pfw + r0 * FU_SW + 4 * lane, *lcs_row = lcs + 2 * (r0 + 1);
+  const uint32_t *cur_row = raw + (r0 + 1) * FU_SW + 4 * lane, *lcs_row = lcs + 2 * (r0 + 1);
+  uint32_t pf_row = pf_taddr + 4u * (uint32_t)r0;
   const bool whole = qw + 4 <= wmax;
-  for (int r = r0; r < r1; r++, orow += p.out_pitch, cur_row += FU_SW, pf_row += FU_SW, lcs_row += 2) {
+  for (int r = r0; r < r1; r++, orow += p.out_pitch, cur_row += FU_SW, pf_row += 4, lcs_row += 2) {
     const uint32_t ft = __shfl_sync(0xffffffffu, my_ft, r);
     if (ref.seg == 0u && lane == 0u) orow[0] = (uint8_t)ft;
     uint4 o;
     if (ft == 4u) {
-      o = *reinterpret_cast<const uint4 *>(pf_row);
+      o = tmem_ld4(pf_row);
     } else {
       const uint4 cur = *reinterpret_cast<const uint4 *>(cur_row);
       o = cur;
@@ -460,10 +484,24 @@ __device__ __forceinline__ void unit_emit(const FusedParams &p, const UnitRef &r
 // its units are swept (held by blocked or finished warps), B is complete, and the warps waiting for it
 // are not blocked after all.
 template <int BPW>
-__global__ void __launch_bounds__(FU_WARPS * 32, 3) fused_kernel(const FusedParams p) {
+__global__ void __launch_bounds__(FU_WARPS * 32, 1) fused_kernel(const FusedParams p) {
   extern __shared__ __align__(16) uint32_t fu_smem[];
   const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-  uint32_t *cur_stash = fu_smem + warp * (2 * FU_WARP_WORDS), *prev_stash = cur_stash + FU_WARP_WORDS;
+  uint32_t *cur_stash = fu_smem + warp * (FU_SLOTS * FU_WARP_WORDS), *prev_stash = cur_stash + FU_WARP_WORDS;
+  // tensor memory for the residual stash: warp 0 allocates for the CTA, every warp uses its own lane quarter
+  uint32_t *tmem_slot = fu_smem + FU_WARPS * FU_SLOTS * FU_WARP_WORDS;
+  if (warp == 0u) {
+    const uint32_t sa = (uint32_t)__cvta_generic_to_shared(tmem_slot);
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(sa), "n"(FU_TMEM_COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_slot;
+  uint32_t cur_pf = tmem_base + (((warp & 3u) * 32u) << 16) + (warp >> 2) * (FU_SLOTS * FU_TMEM_SLOT_COLS);
+  uint32_t prev_pf = cur_pf + FU_TMEM_SLOT_COLS;
+
   const uint32_t n_units = p.n_bands * p.nseg;
   const uint32_t n_warps = gridDim.x * FU_WARPS;
   uint32_t lmask[5];  // lane f keeps candidate f's row sum
@@ -471,35 +509,42 @@ __global__ void __launch_bounds__(FU_WARPS * 32, 3) fused_kernel(const FusedPara
   for (int f = 0; f < 5; f++) lmask[f] = lane == (uint32_t)f ? 0xffffffffu : 0u;
 
   uint32_t u = blockIdx.x * FU_WARPS + warp;  // first unit: the warp's own index; tickets continue from n_warps
-  if (u >= n_units) return;
-  UnitPlan plan = plan_make(p, u, plan_fetch(p, u));
-  unit_load<BPW>(p, plan, cur_stash, lane);
-  UnitRef prev;
-  prev.seg = 0; prev.ya = 0; prev.nrows = 0;
-  bool have_prev = false;
-  for (;;) {
-    unit_sweep<BPW>(p, plan, cur_stash, lane, lmask);
-    uint32_t ft = 0u;
-    if (have_prev) ft = unit_wait(p, prev, lane);
-    uint32_t t = 0u;
-    if (lane == 0u) t = atomicAdd(p.ticket, 1u);
-    const int half = prev.nrows >> 1;
-    if (have_prev) unit_emit<BPW>(p, prev, prev_stash, lane, ft, 0, half);
-    u = n_warps + __shfl_sync(0xffffffffu, t, 0);
-    const bool more = u < n_units;
-    PlanRaw raw_next;
-    if (more) raw_next = plan_fetch(p, u);
-    if (have_prev) unit_emit<BPW>(p, prev, prev_stash, lane, ft, half, prev.nrows);
-    __syncwarp();  // prev_stash is free again
-    prev.seg = plan.seg; prev.ya = plan.ya; prev.nrows = plan.nrows;
-    have_prev = true;
-    uint32_t *sw = cur_stash; cur_stash = prev_stash; prev_stash = sw;
-    if (!more) break;
-    plan = plan_make(p, u, raw_next);
+  if (u < n_units) {
+    UnitPlan plan = plan_make(p, u, plan_fetch(p, u));
     unit_load<BPW>(p, plan, cur_stash, lane);
+    UnitRef prev;
+    prev.seg = 0; prev.ya = 0; prev.nrows = 0;
+    bool have_prev = false;
+    for (;;) {
+      unit_sweep<BPW>(p, plan, cur_stash, cur_pf, lane, lmask);
+      uint32_t ft = 0u;
+      if (have_prev) ft = unit_wait(p, prev, lane);
+      uint32_t t = 0u;
+      if (lane == 0u) t = atomicAdd(p.ticket, 1u);
+      const int half = prev.nrows >> 1;
+      if (have_prev) unit_emit<BPW>(p, prev, prev_stash, prev_pf, lane, ft, 0, half);
+      u = n_warps + __shfl_sync(0xffffffffu, t, 0);
+      const bool more = u < n_units;
+      PlanRaw raw_next;
+      if (more) raw_next = plan_fetch(p, u);
+      if (have_prev) unit_emit<BPW>(p, prev, prev_stash, prev_pf, lane, ft, half, prev.nrows);
+      __syncwarp();  // prev_stash is free again
+      prev.seg = plan.seg; prev.ya = plan.ya; prev.nrows = plan.nrows;
+      have_prev = true;
+      { uint32_t *sw = cur_stash; cur_stash = prev_stash; prev_stash = sw; }
+      { const uint32_t sw = cur_pf; cur_pf = prev_pf; prev_pf = sw; }
+      if (!more) break;
+      plan = plan_make(p, u, raw_next);
+      unit_load<BPW>(p, plan, cur_stash, lane);
+    }
+    const uint32_t ft = unit_wait(p, prev, lane);
+    unit_emit<BPW>(p, prev, prev_stash, prev_pf, lane, ft, 0, prev.nrows);
   }
-  const uint32_t ft = unit_wait(p, prev, lane);
-  unit_emit<BPW>(p, prev, prev_stash, lane, ft, 0, prev.nrows);
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 0u) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(FU_TMEM_COLS) : "memory");
+  }
 }
 
 uint32_t fused_rows_per_band() { return FB_R; }
@@ -517,8 +562,9 @@ cudaError_t launch_fused(const FusedParams &p, bool out16, int sm_count, cudaStr
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ8, fused_kernel<1>, FU_WARPS * 32, FU_CTA_SMEM);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ16, fused_kernel<2>, FU_WARPS * 32, FU_CTA_SMEM);
   }
-  const int occ = out16 ? occ16 : occ8;
+  int occ = out16 ? occ16 : occ8;
   if (occ < 1) return cudaErrorLaunchOutOfResources;
+  if (occ > FU_MAX_CTAS) occ = FU_MAX_CTAS;
   const uint32_t n_units = p.n_bands * p.nseg;
   const uint32_t want = (n_units + FU_WARPS - 1) / FU_WARPS, resident = (uint32_t)(occ * sm_count);
   const uint32_t grid = want < resident ? want : resident;
