@@ -36,7 +36,7 @@ static constexpr int FB_SWW = 512;  // bin width in 32-bit words
 
 static constexpr int FU_R = 8;                       // rows per unit
 static constexpr int FU_SW = 128;                    // words per unit row
-static constexpr int FU_WARPS = 16;                  // workers per CTA (one CTA per SM)
+static constexpr int FU_WARPS = 20;                  // workers per CTA (one CTA per SM)
 static constexpr int FU_RAW_WORDS = (FU_R + 1) * FU_SW;  // row 0 = predictor row above the unit
 static constexpr int FU_LC_WORDS = ((FU_R + 1) * 2 + 3) / 4 * 4;  // two words left of every row
 static constexpr int FU_WARP_WORDS = FU_RAW_WORDS + FU_LC_WORDS;
@@ -48,7 +48,7 @@ static constexpr size_t FU_CTA_SMEM = (size_t)FU_WARPS * FU_SLOTS * FU_WARP_WORD
 // TMEM (tcgen05.st / tcgen05.ld, no MMA): it takes the residuals out of shared memory, which is what limits
 // the number of resident warps.
 static constexpr int FU_TMEM_SLOT_COLS = FU_R * 4;
-static constexpr int FU_TMEM_COLS = 256;             // power of two >= (FU_WARPS / 4) * FU_SLOTS * FU_TMEM_SLOT_COLS
+static constexpr int FU_TMEM_COLS = 512;             // power of two >= (FU_WARPS / 4) * FU_SLOTS * FU_TMEM_SLOT_COLS
 static constexpr int FU_MAX_CTAS = 512 / FU_TMEM_COLS;  // more CTAs per SM than this would spin in tcgen05.alloc
 static_assert((FU_WARPS / 4) * FU_SLOTS * FU_TMEM_SLOT_COLS <= FU_TMEM_COLS && FU_WARPS % 4 == 0, "TMEM stash layout");
 static_assert(FB_R % FU_R == 0 && FB_SWW % FU_SW == 0, "a unit must lie inside one bin");
