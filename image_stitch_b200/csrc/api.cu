@@ -77,6 +77,11 @@ extern "C" int stitch_ctx_create(int device_id, stitch_ctx **out) {
   if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return STITCH_E_CUDA; }
   ctx->own_stream = true;
   for (auto &ev : ctx->ev) cudaEventCreate(&ev);
+  cudaStreamCreateWithFlags(&ctx->up, cudaStreamNonBlocking);
+  cudaStreamCreateWithFlags(&ctx->down, cudaStreamNonBlocking);
+  cudaEventCreateWithFlags(&ctx->ev_chunk, cudaEventDisableTiming);
+  cudaEventCreateWithFlags(&ctx->ev_down, cudaEventDisableTiming);
+  if (!ctx->up || !ctx->down || !ctx->ev_chunk || !ctx->ev_down) { delete ctx; return STITCH_E_CUDA; }
   // keep freed device memory cached in the pool: jobs reuse it without new cudaMalloc calls
   cudaMemPool_t pool;
   if (cudaDeviceGetDefaultMemPool(&pool, device_id) == cudaSuccess) {
@@ -94,7 +99,11 @@ extern "C" void stitch_ctx_destroy(stitch_ctx *ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
+  cudaStreamSynchronize(ctx->up);
+  cudaStreamSynchronize(ctx->down);
   for (auto &ev : ctx->ev) if (ev) cudaEventDestroy(ev);
+  cudaEventDestroy(ctx->ev_chunk); cudaEventDestroy(ctx->ev_down);
+  cudaStreamDestroy(ctx->up); cudaStreamDestroy(ctx->down);
   if (ctx->d_status) cudaFree(ctx->d_status);
   if (ctx->h_status) cudaFreeHost(ctx->h_status);
   if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -140,6 +149,11 @@ extern "C" int stitch_job_create(stitch_ctx *ctx, const stitch_job_desc *desc, s
 }
 
 static void free_tile(stitch_ctx *ctx, TileRec &t) {
+  if (t.up_event) {  // the upload may still be in flight: frees below are ordered on ctx->stream
+    if (!t.up_waited) cudaStreamWaitEvent(ctx->stream, t.up_event, 0);
+    cudaEventDestroy(t.up_event);
+    t.up_event = nullptr; t.up_waited = true;
+  }
   if (t.d_pix && t.d_pix != t.d_src) dev_free(ctx, t.d_pix);
   if (t.d_src && !t.src_external) dev_free(ctx, t.d_src);
   dev_free(ctx, t.d_pass);
@@ -270,15 +284,21 @@ static int add_tile_common(stitch_job *job, const stitch_tile_desc *tile, const 
     t.d_src = (uint8_t *)dev;
     t.src_external = true;
   } else {
-    // +32: the unfilter kernel may read a few bytes past a row with vector loads
-    int rc = dev_alloc(ctx, (void **)&t.d_src, round_up(len, 16) + 32);
-    if (rc) return rc;
+    // +32: the unfilter kernel may read a few bytes past a row with vector loads.  Allocated in the order of
+    // the upload stream, where the bytes are written; ctx->stream sees it through the tile's upload event.
+    CK(cudaMallocAsync((void **)&t.d_src, round_up(len, 16) + 32, ctx->up));
   }
   int rc = prepare_tile(ctx, job, t, (uint32_t)job->tiles.size());
   if (rc) { free_tile(ctx, t); return rc; }
   if (host && len) {
-    cudaError_t e = cudaMemcpyAsync(t.d_src, host, len, cudaMemcpyHostToDevice, ctx->stream);
+    cudaError_t e = cudaMemcpyAsync(t.d_src, host, len, cudaMemcpyHostToDevice, ctx->up);
     if (e != cudaSuccess) { free_tile(ctx, t); return fail(ctx, STITCH_E_CUDA, "H2D failed: %s", cudaGetErrorString(e)); }
+  }
+  if (!dev) {
+    cudaError_t e = cudaEventCreateWithFlags(&t.up_event, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventRecord(t.up_event, ctx->up);
+    if (e != cudaSuccess) { free_tile(ctx, t); return fail(ctx, STITCH_E_CUDA, "H2D failed: %s", cudaGetErrorString(e)); }
+    t.up_waited = false;
   }
   job->tiles.push_back(std::move(t));
   job->finalized = false;
@@ -322,14 +342,31 @@ static int check_status(stitch_ctx *ctx, stitch_job *job) {
   return fail(ctx, STITCH_E_FILTER, "Unknown filter type: %u", ft);  // png-filter.ts:78-79
 }
 
-static int decode_tiles(stitch_job *job, int force, uint32_t *launches) {
+// ctx->stream waits for the uploads of the tiles that touch canvas rows [ya, yb).
+static int wait_uploads(stitch_job *job, uint32_t ya, uint32_t yb) {
   stitch_ctx *ctx = job->ctx;
+  for (auto &t : job->tiles) {
+    if (t.up_waited) continue;
+    const int64_t ty0 = t.d.dst_y, ty1 = (int64_t)t.d.dst_y + t.d.vis_h;
+    if (t.d.vis_h && (ty1 <= (int64_t)ya || ty0 >= (int64_t)yb)) continue;
+    CK(cudaStreamWaitEvent(ctx->stream, t.up_event, 0));
+    t.up_waited = true;
+  }
+  return STITCH_OK;
+}
+
+// Unfilters (and de-interlaces) the tiles that touch canvas rows [ya, yb) and are not decoded yet.
+static int decode_tiles(stitch_job *job, int force, uint32_t *launches, uint32_t ya = 0, uint32_t yb = 0xffffffffu) {
+  stitch_ctx *ctx = job->ctx;
+  int wrc = wait_uploads(job, ya, yb);
+  if (wrc) return wrc;
   std::vector<UnfStream> streams;
   std::vector<A7Image> a7;
   uint32_t a7_max_rb = 0, a7_max_h = 0;
   for (auto &t : job->tiles) {
     if (!t.d.filtered) continue;
     if (t.decoded && !force) continue;
+    if (t.d.vis_h && ((int64_t)t.d.dst_y + t.d.vis_h <= (int64_t)ya || (int64_t)t.d.dst_y >= (int64_t)yb)) continue;
     for (auto &s : t.streams) streams.push_back(s);
     if (t.has_a7) {
       a7.push_back(t.a7);
@@ -508,6 +545,73 @@ static void bg_words(const stitch_job_desc &d, uint32_t &lo, uint32_t &hi) {
   if (d.out_bit_depth != 16) hi = 0;
 }
 
+// Rows [a, b) of a PNG-filtered or raw band into d_rows (row pitch job->out_pitch): decode the tiles the rows
+// need, composite, filter.  Everything is queued on ctx->stream; nothing is waited for.
+static int render_rows(stitch_job *job, uint32_t a, uint32_t b, uint8_t *d_rows, uint32_t *launches, cudaEvent_t ev_decoded) {
+  stitch_ctx *ctx = job->ctx;
+  const stitch_job_desc &jd = job->desc;
+  const bool png = jd.out_kind == STITCH_OUT_PNG_FILTERED;
+  const size_t row_bytes = (size_t)jd.canvas_w * job->bpp;
+  const size_t pitch16 = round_up(row_bytes, 16);
+  const uint32_t n_rows = b - a;
+  int rc;
+  if ((rc = decode_tiles(job, 0, launches, a ? a - 1 : 0, b))) return rc;  // +1 row: the PNG predictor row above
+  if (ev_decoded) CK(cudaEventRecord(ev_decoded, ctx->stream));
+  if (!job->finalized && (rc = finalize_job(job))) return rc;
+
+  ComposeParams cp{};
+  cp.tiles = job->d_tiles; cp.bin_start = job->d_bin_start; cp.bin_tiles = job->d_bin_tiles;
+  cp.bins_x = job->bins_x; cp.bin_w_log2 = job->bin_w_log2; cp.bin_h_log2 = job->bin_h_log2;
+  cp.bin_y_origin = job->bin_y_origin; cp.canvas_w = jd.canvas_w; cp.alpha_blend = jd.alpha_blend;
+  bg_words(jd, cp.bg_lo, cp.bg_hi);
+  if (!png) {
+    cp.y_begin = a; cp.y_end = b; cp.out = d_rows; cp.out_pitch = pitch16;
+    CK(launch_compose(cp, jd.out_bit_depth == 16, ctx->stream));
+    *launches += 1;
+    return STITCH_OK;
+  }
+  if (!job->force_two_pass) {
+    // fused single pass: rowsum[n_rows][8] (64-bit) | ticket
+    const uint32_t bh = fused_unit_rows();
+    const uint32_t band0 = a / bh, n_bands = (b - 1) / bh - band0 + 1;
+    const size_t words = (size_t)n_rows * 16 + 4;
+    if (words > job->sync_words) {
+      dev_free(ctx, job->d_sync); job->d_sync = nullptr; job->sync_words = 0;
+      if ((rc = dev_alloc(ctx, (void **)&job->d_sync, words * 4))) return rc;
+      job->sync_words = words;
+    }
+    CK(cudaMemsetAsync(job->d_sync, 0, words * 4, ctx->stream));
+    FusedParams fp{};
+    fp.tiles = job->d_tiles; fp.bin_start = job->d_bin_start; fp.bin_tiles = job->d_bin_tiles;
+    fp.bins_x = job->bins_x; fp.canvas_w = jd.canvas_w; fp.y_begin = a; fp.y_end = b; fp.band0 = band0;
+    fp.n_bands = n_bands;
+    fp.nseg = (uint32_t)((row_bytes / 4 + fused_unit_words() - 1) / fused_unit_words()); fp.alpha_blend = jd.alpha_blend;
+    bg_words(jd, fp.bg_lo, fp.bg_hi);
+    fp.rowsum = reinterpret_cast<unsigned long long *>(job->d_sync); fp.ticket = job->d_sync + (size_t)n_rows * 16;
+    fp.out = d_rows; fp.out_pitch = job->out_pitch; fp.lead = (uint32_t)job->out_lead;
+    if ((rc = ensure_buffer(ctx, &job->d_plans, &job->plans_bytes, fused_plan_bytes(fp.n_bands * fp.nseg)))) return rc;
+    fp.plans = job->d_plans;
+    cudaError_t fe = launch_fused(fp, jd.out_bit_depth == 16, ctx->sm_count, ctx->stream);
+    if (fe == cudaSuccess) { *launches += 2; return STITCH_OK; }
+    if (fe != cudaErrorInvalidConfiguration) CK(fe);
+    cudaGetLastError();
+  }
+  // rows too wide for the fused kernel: composite to HBM, then filter-select
+  const uint32_t ys = a ? a - 1 : 0;  // 1-row halo: the predictor row is recomputed, not exchanged
+  job->canvas_pitch = pitch16;
+  if ((rc = ensure_buffer(ctx, &job->d_canvas, &job->canvas_bytes, pitch16 * (size_t)(b - ys)))) return rc;
+  cp.y_begin = ys; cp.y_end = b; cp.out = job->d_canvas; cp.out_pitch = pitch16;
+  CK(launch_compose(cp, jd.out_bit_depth == 16, ctx->stream));
+  FilterParams fp{};
+  fp.rows = job->d_canvas + (size_t)(a - ys) * pitch16; fp.in_pitch = pitch16;
+  fp.prev0 = a ? job->d_canvas : nullptr;
+  fp.n_rows = n_rows; fp.row_bytes = (uint32_t)row_bytes; fp.bpp = job->bpp;
+  fp.out = d_rows; fp.out_pitch = job->out_pitch; fp.lead = (uint32_t)job->out_lead;
+  CK(launch_filter_rows(fp, ctx->stream));
+  *launches += 2;
+  return STITCH_OK;
+}
+
 extern "C" int stitch_job_run_band(stitch_job *job, uint32_t y0, uint32_t y1, uint8_t *out, size_t cap,
                                    size_t *out_len, stitch_timings *tm) {
   if (!job) return STITCH_E_INVALID;
@@ -526,68 +630,22 @@ extern "C" int stitch_job_run_band(stitch_job *job, uint32_t y0, uint32_t y1, ui
   const size_t host_row = row_bytes + (png ? 1 : 0);
   if (out && !jpeg && cap < host_row * n_rows) return fail(ctx, STITCH_E_CAPACITY, "output buffer too small: need %zu bytes", host_row * n_rows);
   size_t jpeg_bytes = 0;
+  const size_t pitch16 = round_up(row_bytes, 16);
 
   uint32_t launches = 0;
   int rc = reset_status(ctx);
   if (rc) return rc;
-  CK(cudaEventRecord(ctx->ev[0], ctx->stream));  // pending H2D copies are already queued on the stream
+  CK(cudaEventRecord(ctx->ev[0], ctx->stream));
   CK(cudaEventRecord(ctx->ev[1], ctx->stream));
-  if ((rc = decode_tiles(job, 0, &launches))) return rc;
-  CK(cudaEventRecord(ctx->ev[2], ctx->stream));
-  if (!job->finalized && (rc = finalize_job(job))) return rc;
-
-  ComposeParams cp{};
-  cp.tiles = job->d_tiles; cp.bin_start = job->d_bin_start; cp.bin_tiles = job->d_bin_tiles;
-  cp.bins_x = job->bins_x; cp.bin_w_log2 = job->bin_w_log2; cp.bin_h_log2 = job->bin_h_log2;
-  cp.bin_y_origin = job->bin_y_origin; cp.canvas_w = jd.canvas_w; cp.alpha_blend = jd.alpha_blend;
-  bg_words(jd, cp.bg_lo, cp.bg_hi);
-
-  const size_t pitch16 = round_up(row_bytes, 16);
-  if (png) {
-    job->out_pitch = 16 + pitch16; job->out_lead = 15; job->out_row_bytes = host_row;
-    if ((rc = ensure_buffer(ctx, &job->d_out, &job->out_bytes, job->out_pitch * (size_t)n_rows))) return rc;
-    bool fused_done = false;
-    if (!job->force_two_pass) {
-      // fused single pass: rowsum[n_rows][8] (64-bit) | ticket
-      const uint32_t bh = fused_unit_rows();
-      const uint32_t band0 = y0 / bh, n_bands = (y1 - 1) / bh - band0 + 1;
-      const size_t words = (size_t)n_rows * 16 + 4;
-      if (words > job->sync_words) {
-        dev_free(ctx, job->d_sync); job->d_sync = nullptr; job->sync_words = 0;
-        if ((rc = dev_alloc(ctx, (void **)&job->d_sync, words * 4))) return rc;
-        job->sync_words = words;
-      }
-      CK(cudaMemsetAsync(job->d_sync, 0, words * 4, ctx->stream));
-      FusedParams fp{};
-      fp.tiles = job->d_tiles; fp.bin_start = job->d_bin_start; fp.bin_tiles = job->d_bin_tiles;
-      fp.bins_x = job->bins_x; fp.canvas_w = jd.canvas_w; fp.y_begin = y0; fp.y_end = y1; fp.band0 = band0;
-      fp.n_bands = n_bands;
-      fp.nseg = (uint32_t)((row_bytes / 4 + fused_unit_words() - 1) / fused_unit_words()); fp.alpha_blend = jd.alpha_blend;
-      bg_words(jd, fp.bg_lo, fp.bg_hi);
-      fp.rowsum = reinterpret_cast<unsigned long long *>(job->d_sync); fp.ticket = job->d_sync + (size_t)n_rows * 16;
-      fp.out = job->d_out; fp.out_pitch = job->out_pitch; fp.lead = (uint32_t)job->out_lead;
-      if ((rc = ensure_buffer(ctx, &job->d_plans, &job->plans_bytes, fused_plan_bytes(fp.n_bands * fp.nseg)))) return rc;
-      fp.plans = job->d_plans;
-      cudaError_t fe = launch_fused(fp, jd.out_bit_depth == 16, ctx->sm_count, ctx->stream);
-      if (fe == cudaSuccess) { fused_done = true; launches += 2; }
-      else if (fe != cudaErrorInvalidConfiguration) CK(fe);
-      else cudaGetLastError();
-    }
-    if (!fused_done) {  // rows too wide for a resident band: composite to HBM, then filter-select
-      const uint32_t ys = y0 ? y0 - 1 : 0;  // 1-row halo: the predictor row is recomputed, not exchanged
-      job->canvas_pitch = pitch16;
-      if ((rc = ensure_buffer(ctx, &job->d_canvas, &job->canvas_bytes, pitch16 * (size_t)(y1 - ys)))) return rc;
-      cp.y_begin = ys; cp.y_end = y1; cp.out = job->d_canvas; cp.out_pitch = pitch16;
-      CK(launch_compose(cp, jd.out_bit_depth == 16, ctx->stream));
-      FilterParams fp{};
-      fp.rows = job->d_canvas + (size_t)(y0 - ys) * pitch16; fp.in_pitch = pitch16;
-      fp.prev0 = y0 ? job->d_canvas : nullptr;
-      fp.n_rows = n_rows; fp.row_bytes = (uint32_t)row_bytes; fp.bpp = job->bpp;
-      fp.out = job->d_out; fp.out_pitch = job->out_pitch; fp.lead = (uint32_t)job->out_lead;
-      CK(launch_filter_rows(fp, ctx->stream));
-      launches += 2;
-    }
-  } else if (jpeg) {
+  if (jpeg) {
+    if ((rc = decode_tiles(job, 0, &launches, y0, y1))) return rc;
+    CK(cudaEventRecord(ctx->ev[2], ctx->stream));
+    if (!job->finalized && (rc = finalize_job(job))) return rc;
+    ComposeParams cp{};
+    cp.tiles = job->d_tiles; cp.bin_start = job->d_bin_start; cp.bin_tiles = job->d_bin_tiles;
+    cp.bins_x = job->bins_x; cp.bin_w_log2 = job->bin_w_log2; cp.bin_h_log2 = job->bin_h_log2;
+    cp.bin_y_origin = job->bin_y_origin; cp.canvas_w = jd.canvas_w; cp.alpha_blend = jd.alpha_blend;
+    bg_words(jd, cp.bg_lo, cp.bg_hi);
     // composite the band into HBM, then kernel (d); MCU rows are independent entropy segments (jpeg.cu)
     job->canvas_pitch = pitch16;
     if ((rc = ensure_buffer(ctx, &job->d_canvas, &job->canvas_bytes, pitch16 * (size_t)n_rows))) return rc;
@@ -596,33 +654,56 @@ extern "C" int stitch_job_run_band(stitch_job *job, uint32_t y0, uint32_t y1, ui
     launches += 1;
     if ((rc = stitch_jpeg_encode_band(job, y0, y1, job->d_canvas, pitch16, &jpeg_bytes, &launches))) return rc;
     job->out_pitch = jpeg_bytes; job->out_lead = 0; job->out_row_bytes = jpeg_bytes;
+    CK(cudaEventRecord(ctx->ev[3], ctx->stream));
+    if (out) {
+      const size_t need = sizeof(stitch_jpeg_band_info) + jpeg_bytes;
+      if (cap < need) return fail(ctx, STITCH_E_CAPACITY, "output buffer too small: need %zu bytes", need);
+      stitch_jpeg_band_info info;
+      memset(&info, 0, sizeof info);
+      info.n_bits = (uint64_t)jpeg_bytes * 8;  // every MCU row restarts the DC predictors: last_dc stays 0
+      memcpy(out, &info, sizeof info);
+      if (jpeg_bytes) CK(cudaMemcpyAsync(out + sizeof info, job->d_out, jpeg_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+      if (out_len) *out_len = need;
+    }
   } else {
-    job->out_pitch = pitch16; job->out_lead = 0; job->out_row_bytes = host_row;
-    if ((rc = ensure_buffer(ctx, &job->d_out, &job->out_bytes, pitch16 * (size_t)n_rows))) return rc;
-    cp.y_begin = y0; cp.y_end = y1; cp.out = job->d_out; cp.out_pitch = pitch16;
-    CK(launch_compose(cp, jd.out_bit_depth == 16, ctx->stream));
-    launches += 1;
-  }
-  CK(cudaEventRecord(ctx->ev[3], ctx->stream));
-  if (out && jpeg) {
-    const size_t need = sizeof(stitch_jpeg_band_info) + jpeg_bytes;
-    if (cap < need) return fail(ctx, STITCH_E_CAPACITY, "output buffer too small: need %zu bytes", need);
-    stitch_jpeg_band_info info;
-    memset(&info, 0, sizeof info);
-    info.n_bits = (uint64_t)jpeg_bytes * 8;  // every MCU row restarts the DC predictors: last_dc stays 0
-    memcpy(out, &info, sizeof info);
-    if (jpeg_bytes) CK(cudaMemcpyAsync(out + sizeof info, job->d_out, jpeg_bytes, cudaMemcpyDeviceToHost, ctx->stream));
-    if (out_len) *out_len = need;
-  } else if (out) {
-    CK(cudaMemcpy2DAsync(out, host_row, job->d_out + job->out_lead, job->out_pitch, host_row, n_rows,
-                         cudaMemcpyDeviceToHost, ctx->stream));
-    if (out_len) *out_len = host_row * n_rows;
+    if (png) { job->out_pitch = 16 + pitch16; job->out_lead = 15; }
+    else { job->out_pitch = pitch16; job->out_lead = 0; }
+    job->out_row_bytes = host_row;
+    if ((rc = ensure_buffer(ctx, &job->d_out, &job->out_bytes, job->out_pitch * (size_t)n_rows))) return rc;
+    // With a host destination the band is produced in chunks of about 64 MB: chunk k goes down the bus on its
+    // own stream while chunk k+1 is computed and while later tiles are still coming up (add_tile queued
+    // them on the upload stream), so the bus is busy in both directions and the kernels hide behind it.
+    uint32_t chunk = n_rows;
+    if (out) {
+      const size_t want = ((size_t)64 << 20) / std::max<size_t>(host_row, 1);
+      chunk = (uint32_t)std::min<size_t>(n_rows, std::max<size_t>(64, want / 16 * 16));
+    }
+    bool first = true;
+    for (uint32_t a = y0; a < y1; a += chunk) {
+      const uint32_t b = (uint32_t)std::min<uint64_t>((uint64_t)a + chunk, y1);
+      uint8_t *d_rows = job->d_out + (size_t)(a - y0) * job->out_pitch;
+      if ((rc = render_rows(job, a, b, d_rows, &launches, first ? ctx->ev[2] : nullptr))) return rc;
+      first = false;
+      if (out) {
+        CK(cudaEventRecord(ctx->ev_chunk, ctx->stream));
+        CK(cudaStreamWaitEvent(ctx->down, ctx->ev_chunk, 0));
+        CK(cudaMemcpy2DAsync(out + (size_t)(a - y0) * host_row, host_row, d_rows + job->out_lead, job->out_pitch, host_row,
+                             b - a, cudaMemcpyDeviceToHost, ctx->down));
+      }
+    }
+    CK(cudaEventRecord(ctx->ev[3], ctx->stream));
+    if (out) {
+      CK(cudaEventRecord(ctx->ev_down, ctx->down));
+      CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_down, 0));
+      if (out_len) *out_len = host_row * n_rows;
+    }
   }
   CK(cudaEventRecord(ctx->ev[4], ctx->stream));
   CK(cudaMemcpyAsync(ctx->h_status, ctx->d_status, sizeof(DevStatus), cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));
   job->last_y0 = y0; job->last_y1 = y1;
   if (tm) {
+    // decode_ms covers the first chunk's decode only when the band is produced in several chunks
     memset(tm, 0, sizeof *tm);
     cudaEventElapsedTime(&tm->h2d_ms, ctx->ev[0], ctx->ev[1]);
     cudaEventElapsedTime(&tm->decode_ms, ctx->ev[1], ctx->ev[2]);

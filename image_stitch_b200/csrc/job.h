@@ -15,6 +15,10 @@ struct stitch_ctx {
   int sm_count = 148;
   std::string err;
   cudaEvent_t ev[6] = {};
+  // Host<->device copies run beside the kernels: uploads of tile bytes on `up`, downloads of finished row
+  // chunks on `down`; ordering is by events (one per tile, one per chunk).
+  cudaStream_t up = nullptr, down = nullptr;
+  cudaEvent_t ev_chunk = nullptr, ev_down = nullptr;
   stitch::DevStatus *d_status = nullptr;   // device error word
   stitch::DevStatus *h_status = nullptr;   // pinned mirror
 };
@@ -31,6 +35,8 @@ struct TileRec {
   bool has_a7 = false;
   stitch::A7Image a7;
   bool decoded = false;
+  cudaEvent_t up_event = nullptr;  // recorded on ctx->up after the tile's bytes were queued
+  bool up_waited = true;           // ctx->stream already waits for up_event
 };
 
 struct stitch_job {
