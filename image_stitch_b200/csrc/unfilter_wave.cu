@@ -198,32 +198,48 @@ __device__ void run_unit(const UnfStream &s, const uint32_t g, uint8_t *ws, uint
   const uint32_t my_row_off = (lane + 1u) * UW_ROW_BYTES;
   const uint32_t in_off = my_row_off + (sh & ~3u);
 
+  // Granule q = 32*it + lane of a block (q = 9*row + col) lands at slot + 144 + 16*q; its source offset from
+  // s.src for block 0 is computed once per unit (rows past the end get an offset that never passes the bound).
+  // Offsets are relative to the unit's first row so that they fit 32 bits for streams of any length.
+  const uint8_t *const unit_src = s.src + (size_t)(g * 32u) * s.src_stride;
+  const ptrdiff_t end_far = s.src_end - unit_src;
+  const int32_t end_off = (int32_t)(end_far < 0x3fffffff ? end_far : 0x3fffffff);
+  int32_t goff[9];
+#pragma unroll
+  for (int it = 0; it < 9; it++) {
+    const uint32_t q = (uint32_t)it * 32u + lane;
+    const uint32_t row = q / 9u, col = q - row * 9u;
+    const uint32_t ro = row * s.src_stride + 1u;
+    const uint32_t mis = (uint32_t)(reinterpret_cast<uintptr_t>(unit_src) + ro) & 15u;
+    goff[it] = row < rows_g ? (int32_t)(ro - mis + col * 16u) : 0x40000000;
+  }
   auto issue_block = [&](uint32_t b) {
-    uint8_t *slot = ws + (b % 3u) * UW_SLOT_BYTES;
+    uint8_t *slot = ws + (b % 3u) * UW_SLOT_BYTES + UW_ROW_BYTES + 16u * lane;
 #pragma unroll
     for (int it = 0; it < 9; it++) {
-      const uint32_t q = (uint32_t)it * 32u + lane;  // 288 granules: 32 rows x 9
-      const uint32_t row = q / 9u, col = q - row * 9u;
-      const uint32_t rr = g * 32u + row;
-      if (rr < s.rows) {
-        const uint8_t *rp = s.src + (size_t)rr * s.src_stride + 1;
-        const uint8_t *gp = rp - (reinterpret_cast<uintptr_t>(rp) & 15u) + (size_t)b * 128u + col * 16u;
-        if (gp < s.src_end) cp_async16(slot + (row + 1u) * UW_ROW_BYTES + col * 16u, gp);
-      }
+      const int32_t o = goff[it] + (int32_t)(b * 128u);
+      if (o < end_off) cp_async16(slot + it * 512, unit_src + o);
     }
     cp_async_commit();
   };
   // Block b is complete (every lane has left it): pixels to HBM, last row also to the seam mailbox.
+  uint8_t *const st_dst = s.dst + (size_t)(g * 32u + (lane >> 3)) * s.dst_pitch + (lane & 7u) * 16u;
+  const uint32_t st_src = ((lane >> 3) + 1u) * UW_ROW_BYTES + (lane & 7u) * 16u;
+  const size_t pitch4 = (size_t)s.dst_pitch * 4u;
   auto store_block = [&](uint32_t b) {
     const uint8_t *slot = ws + (b % 3u) * UW_SLOT_BYTES;
     if (publish) st_pair(my_seam + b * 32u, *reinterpret_cast<const uint32_t *>(slot + 32u * UW_ROW_BYTES + lane * 4u), epoch);
+    if (b * 128u + (lane & 7u) * 16u < s.dst_pitch) {
+      uint8_t *d = st_dst + b * 128u;
+      if (rows_g == 32u) {
 #pragma unroll
-    for (int it = 0; it < 8; it++) {
-      const uint32_t row = (uint32_t)it * 4u + (lane >> 3), col = lane & 7u;
-      const uint32_t rr = g * 32u + row, off = b * 128u + col * 16u;
-      if (rr < s.rows && off < s.dst_pitch) {
-        const uint4 v = *reinterpret_cast<const uint4 *>(slot + (row + 1u) * UW_ROW_BYTES + col * 16u);
-        *reinterpret_cast<uint4 *>(s.dst + (size_t)rr * s.dst_pitch + off) = v;
+        for (int it = 0; it < 8; it++)
+          *reinterpret_cast<uint4 *>(d + it * pitch4) = *reinterpret_cast<const uint4 *>(slot + st_src + it * 4 * UW_ROW_BYTES);
+      } else {
+#pragma unroll
+        for (int it = 0; it < 8; it++)
+          if ((uint32_t)it * 4u + (lane >> 3) < rows_g)
+            *reinterpret_cast<uint4 *>(d + it * pitch4) = *reinterpret_cast<const uint4 *>(slot + st_src + it * 4 * UW_ROW_BYTES);
       }
     }
   };
