@@ -260,6 +260,11 @@ __device__ void run_unit(const UnfStream &s, const uint32_t g, uint8_t *ws, uint
 #pragma unroll
     for (int k = 0; k < 3; k++) *reinterpret_cast<uint32_t *>(ws + k * UW_SLOT_BYTES + lane * 4u) = 0u;
   }
+  if (WORDS) {  // slot 2 is what lanes read before their first word (see the step loop)
+    uint4 *z = reinterpret_cast<uint4 *>(ws + 2 * UW_SLOT_BYTES + UW_ROW_BYTES);
+#pragma unroll
+    for (int k = 0; k < 9; k++) z[k * 32 + lane] = make_uint4(0u, 0u, 0u, 0u);
+  }
   issue_block(0u);
   uint2 ab = make_uint2(0u, epoch);
   if (has_above) ab = ld_pair(ab_seam);
@@ -282,8 +287,13 @@ __device__ void run_unit(const UnfStream &s, const uint32_t g, uint8_t *ws, uint
       if (p + 1u < nblocks) ab = ld_pair(ab_seam + (p + 1u) * 32u);
       __syncwarp();
     }
-    const bool full = rows_g == 32u && p >= 1u && (p + 1u) * 32u <= nwords;  // every lane is active in every step
-    if (WORDS && full) {
+    // Whole-word formats run every block through the branch-free steps, including the blocks where some lanes
+    // have not started or have already finished.  A lane that has not started reads zeros (slot 2 was cleared,
+    // the lane above still produces zeros), so it produces zeros and its state stays "left = above-left = 0"
+    // until its first real word; a lane past its last word, or without a row, computes garbage that nobody
+    // reads: store_block never writes rows >= rows_g or columns >= dst_pitch, blocks >= nblocks are never
+    // stored, and the lane below read this lane's last real word one step before.
+    if (WORDS) {
       // lane l works in the current slot from step l on, before that in the tail of the previous one
       const uint32_t in_cur = cur_slot + in_off - 4u * lane, in_prev = prev_slot + in_off - 4u * lane + 128u;
       const uint32_t out_cur = cur_slot + my_row_off - 4u * lane, out_prev = prev_slot + my_row_off - 4u * lane + 128u;
