@@ -181,3 +181,22 @@ def test_blend_against_python_floats():
         else:
             want = d.tolist()
         assert out == want
+
+
+def test_division_by_constant_is_exact():
+    """csrc/common.cuh div_const(): x/255 and x/65535 through q0 = x*y, r = fma(-b, q0, x), q = fma(r, y, q0)
+    with y = RN(1/b) must equal IEEE division for every integer x the blend can see (sA, dA of
+    src/pixel-ops.ts:694-700).  fma is emulated exactly with rationals."""
+    from fractions import Fraction
+
+    def fma(a, b, c):
+        return float(Fraction(a) * Fraction(b) + Fraction(c))   # Fraction -> float rounds to nearest even
+
+    for b, y_hex in ((255.0, "0x1.0101010101010p-8"), (65535.0, "0x1.0001000100010p-16")):
+        y = float.fromhex(y_hex)
+        assert y == 1.0 / b
+        for k in range(int(b) + 1):
+            a = float(k)
+            q0 = a * y
+            q = fma(fma(-b, q0, a), y, q0)
+            assert q == a / b, (b, k)
