@@ -168,7 +168,7 @@ extern "C" void stitch_job_destroy(stitch_job *job) {
   dev_free(ctx, job->d_tiles); dev_free(ctx, job->d_bin_start); dev_free(ctx, job->d_bin_tiles);
   dev_free(ctx, job->d_streams); dev_free(ctx, job->d_a7);
   dev_free(ctx, job->d_slow); dev_free(ctx, job->d_units); dev_free(ctx, job->d_uprog);
-  dev_free(ctx, job->d_canvas); dev_free(ctx, job->d_out); dev_free(ctx, job->d_sync); dev_free(ctx, job->d_plans);
+  dev_free(ctx, job->d_canvas); dev_free(ctx, job->d_out); dev_free(ctx, job->d_sync); dev_free(ctx, job->d_plans); dev_free(ctx, job->d_ctab);
   for (auto &q : job->d_jpeg) dev_free(ctx, q);
   if (job->h_jpeg_totals) cudaFreeHost(job->h_jpeg_totals);
   cudaStreamSynchronize(ctx->stream);
@@ -509,6 +509,27 @@ static int finalize_job(stitch_job *job) {
     for (uint32_t by = by0; by <= by1; by++)
       for (uint32_t bx = bx0; bx <= bx1; bx++) list[fill[(size_t)by * job->bins_x + bx]++] = k;
   }
+  // A bin is "plain" when it is empty or when its top-most tile covers it, overwrites what is below and is in
+  // the output's own format: its units then take the fused kernel's copy path.  render_rows() switches to
+  // composite-then-filter when too many bins of a band are not.
+  job->busy_bins.assign(job->bins_y + 1, 0);
+  const uint32_t native = jd.out_bit_depth == 16 ? (uint32_t)FMT_RGBA16 : (uint32_t)FMT_RGBA8;
+  for (uint32_t by = 0; by < job->bins_y; by++) {
+    uint32_t busy = 0;
+    for (uint32_t bx = 0; bx < job->bins_x; bx++) {
+      const size_t bin = (size_t)by * job->bins_x + bx;
+      if (start[bin + 1] == start[bin]) continue;
+      const DevTile &o = dt[list[start[bin + 1] - 1]];
+      const int32_t X0 = (int32_t)(bx << job->bin_w_log2), X1 = std::min<int64_t>((int64_t)X0 + bw, jd.canvas_w);
+      const int32_t Y0 = (int32_t)(by << job->bin_h_log2), Y1 = std::min<int64_t>((int64_t)Y0 + bh, jd.canvas_h);
+      const bool covers = o.x0 <= X0 && o.x1 >= X1 && o.y0 <= Y0 && o.y1 >= Y1;
+      const bool overwrite = !jd.alpha_blend || o.opaque;
+      const bool aligned = covers && o.pitch % 16u == 0 &&
+                           (reinterpret_cast<uintptr_t>(o.pix) + (size_t)(X0 - o.x0 + o.sx0) * job->bpp) % 16u == 0;
+      if (!(covers && overwrite && aligned && o.fmt == native)) busy++;
+    }
+    job->busy_bins[by + 1] = job->busy_bins[by] + busy;
+  }
   dev_free(ctx, job->d_tiles); dev_free(ctx, job->d_bin_start); dev_free(ctx, job->d_bin_tiles);
   job->d_tiles = nullptr; job->d_bin_start = nullptr; job->d_bin_tiles = nullptr;
   int rc;
@@ -538,6 +559,8 @@ static int ensure_buffer(stitch_ctx *ctx, uint8_t **p, size_t *have, size_t need
 }
 
 int stitch_ensure_buffer(stitch_ctx *ctx, uint8_t **p, size_t *have, size_t need) { return ensure_buffer(ctx, p, have, need); }
+
+static uint32_t native_fmt(uint32_t out_bit_depth) { return out_bit_depth == 16 ? (uint32_t)FMT_RGBA16 : (uint32_t)FMT_RGBA8; }
 
 static void bg_words(const stitch_job_desc &d, uint32_t &lo, uint32_t &hi) {
   memcpy(&lo, d.background, 4);
@@ -591,8 +614,35 @@ static int render_rows(stitch_job *job, uint32_t a, uint32_t b, uint8_t *d_rows,
     fp.out = d_rows; fp.out_pitch = job->out_pitch; fp.lead = (uint32_t)job->out_lead;
     if ((rc = ensure_buffer(ctx, &job->d_plans, &job->plans_bytes, fused_plan_bytes(fp.n_bands * fp.nseg)))) return rc;
     fp.plans = job->d_plans;
+    // How many of the band's bins need the generic compositor?  Few: one fused pass straight from the tiles.
+    // Many: composite the band (plus the predictor row above it) into HBM first and give the fused kernel that
+    // canvas as its only tile -- 8 more bytes of HBM traffic per pixel, but the expensive, uneven part of the
+    // work no longer sits inside the kernel whose warps wait for one another.
+    const uint32_t by0 = a >> job->bin_h_log2, by1 = (b - 1) >> job->bin_h_log2;
+    const uint64_t busy = job->busy_bins.empty() ? 0 : job->busy_bins[by1 + 1] - job->busy_bins[by0];
+    const bool via_canvas = busy * 8 > (uint64_t)(by1 - by0 + 1) * job->bins_x;
+    uint32_t extra = 0;
+    if (via_canvas) {
+      const uint32_t ys = a ? a - 1 : 0;
+      job->canvas_pitch = pitch16;
+      if ((rc = ensure_buffer(ctx, &job->d_canvas, &job->canvas_bytes, pitch16 * (size_t)(b - ys)))) return rc;
+      if ((rc = ensure_buffer(ctx, &job->d_ctab, &job->ctab_bytes, 256))) return rc;
+      CK(launch_compose_canvas(fp, jd.out_bit_depth == 16, job->d_canvas, pitch16, ys, b, ctx->stream));
+      struct { DevTile t; uint32_t pad[4]; uint32_t bin_start[2]; uint32_t bin_tiles[2]; } tab;
+      memset(&tab, 0, sizeof tab);
+      tab.t.pix = job->d_canvas; tab.t.pitch = (uint32_t)pitch16; tab.t.fmt = native_fmt(jd.out_bit_depth);
+      tab.t.x0 = 0; tab.t.y0 = (int32_t)ys; tab.t.x1 = (int32_t)jd.canvas_w; tab.t.y1 = (int32_t)b;
+      tab.t.opaque = 1;
+      tab.bin_start[1] = 1;
+      CK(cudaMemcpyAsync(job->d_ctab, &tab, sizeof tab, cudaMemcpyHostToDevice, ctx->stream));  // pageable: staged on return
+      fp.tiles = reinterpret_cast<const DevTile *>(job->d_ctab);
+      fp.bin_start = reinterpret_cast<const uint32_t *>(job->d_ctab + offsetof(decltype(tab), bin_start));
+      fp.bin_tiles = reinterpret_cast<const uint32_t *>(job->d_ctab + offsetof(decltype(tab), bin_tiles));
+      fp.single_bin = 1; fp.alpha_blend = 0;
+      extra = 1;
+    }
     cudaError_t fe = launch_fused(fp, jd.out_bit_depth == 16, ctx->sm_count, ctx->stream);
-    if (fe == cudaSuccess) { *launches += 2; return STITCH_OK; }
+    if (fe == cudaSuccess) { *launches += 2 + extra; return STITCH_OK; }
     if (fe != cudaErrorInvalidConfiguration) CK(fe);
     cudaGetLastError();
   }

@@ -233,7 +233,7 @@ __device__ __forceinline__ UnitPlan unit_plan(const FusedParams &p, const uint32
   UnitPlan pl;
   unit_geom(p, u, pl);
   const int ya = pl.ya, yb = pl.ya + pl.nrows, xw0 = pl.xw0;
-  const uint32_t bin = ((uint32_t)ya / FB_R) * p.bins_x + (uint32_t)(xw0 / FB_SWW);
+  const uint32_t bin = p.single_bin ? 0u : ((uint32_t)ya / FB_R) * p.bins_x + (uint32_t)(xw0 / FB_SWW);
   const uint32_t b0 = __ldg(p.bin_start + bin), n_list = __ldg(p.bin_start + bin + 1) - b0;
   const uint32_t *list = p.bin_tiles + b0;
   pl.list = list; pl.n_list = n_list;
@@ -551,6 +551,33 @@ uint32_t fused_rows_per_band() { return FB_R; }
 uint32_t fused_words_per_seg() { return FB_SWW; }
 uint32_t fused_unit_rows() { return FU_R; }
 uint32_t fused_unit_words() { return FU_SW; }
+
+// Normalise + composite rows [ys, ye) into a dense canvas in HBM, one 16-byte quad per thread.  Used ahead of
+// the fused kernel when many units of a band are not plain windows of one tile (overlaps, blending, foreign
+// formats): the composite is then perfectly parallel work with no cross-warp waits, and the fused kernel
+// reads the canvas back as a single opaque tile on its cp.async path.
+template <int BPW>
+__global__ void __launch_bounds__(256) compose_canvas_kernel(const FusedParams p, uint8_t *canvas, const size_t pitch,
+                                                             const uint32_t ys, const uint32_t ye) {
+  const int xw = 4 * (int)(blockIdx.x * blockDim.x + threadIdx.x);
+  if (xw >= (int)p.canvas_w * BPW) return;
+  for (uint32_t y = ys + blockIdx.y; y < ye; y += gridDim.y) {
+    const uint32_t bin = (y / FB_R) * p.bins_x + (uint32_t)(xw / FB_SWW);
+    const uint32_t b0 = __ldg(p.bin_start + bin), n_list = __ldg(p.bin_start + bin + 1) - b0;
+    const uint4 v = compose_quad<BPW>(p, p.bin_tiles + b0, n_list, xw, (int)y);
+    *reinterpret_cast<uint4 *>(canvas + (size_t)(y - ys) * pitch + (size_t)xw * 4u) = v;
+  }
+}
+
+cudaError_t launch_compose_canvas(const FusedParams &p, bool out16, uint8_t *canvas, size_t pitch, uint32_t ys,
+                                  uint32_t ye, cudaStream_t st) {
+  if (ye <= ys) return cudaSuccess;
+  const uint32_t quads = (p.canvas_w * (out16 ? 2u : 1u) + 3u) / 4u;
+  const dim3 grid((quads + 255u) / 256u, ye - ys < 65535u ? ye - ys : 65535u);
+  if (out16) compose_canvas_kernel<2><<<grid, 256, 0, st>>>(p, canvas, pitch, ys, ye);
+  else compose_canvas_kernel<1><<<grid, 256, 0, st>>>(p, canvas, pitch, ys, ye);
+  return cudaGetLastError();
+}
 
 size_t fused_plan_bytes(uint32_t n_units) { return (size_t)n_units * sizeof(PlanRec); }
 

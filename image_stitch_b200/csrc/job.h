@@ -59,6 +59,8 @@ struct stitch_job {
   bool force_two_pass = false;
   // band buffers
   uint8_t *d_plans = nullptr; size_t plans_bytes = 0;  // fused kernel: per-unit plan records
+  uint8_t *d_ctab = nullptr; size_t ctab_bytes = 0;    // canvas-as-one-tile tables: DevTile | bin_start[2] | bin_tiles[1]
+  std::vector<uint32_t> busy_bins;                     // prefix sum over bin rows of bins that need the generic compositor
   uint8_t *d_canvas = nullptr; size_t canvas_bytes = 0; size_t canvas_pitch = 0;
   uint8_t *d_out = nullptr; size_t out_bytes = 0;
   size_t out_pitch = 0, out_lead = 0, out_row_bytes = 0;

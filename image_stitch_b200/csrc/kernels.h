@@ -50,12 +50,15 @@ struct FusedParams {
   unsigned long long *rowsum; // [(y_end - y_begin)][8], zeroed: low half = cost sum, high half = units arrived
   uint32_t *ticket;           // zeroed
   void *plans;                // fused_plan_bytes(n_bands * nseg) of scratch: per-unit plan records
+  uint32_t single_bin;        // 1: bin_start/bin_tiles describe one bin that covers the whole canvas
   uint8_t *out;               // row r: filter byte at out + r*out_pitch + lead
   size_t out_pitch;
   uint32_t lead;
 };
 cudaError_t launch_fused(const FusedParams &p, bool out16, int sm_count, cudaStream_t st);
 size_t fused_plan_bytes(uint32_t n_units);
+cudaError_t launch_compose_canvas(const FusedParams &p, bool out16, uint8_t *canvas, size_t pitch, uint32_t ys,
+                                  uint32_t ye, cudaStream_t st);
 uint32_t fused_rows_per_band();
 uint32_t fused_words_per_seg();
 uint32_t fused_unit_rows();
