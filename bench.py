@@ -48,6 +48,23 @@ WORKLOAD_CONFIG = {
 }
 
 
+def profiled_traffic_bytes(summary="profiles/r1b_prof_fused_r1i.summary.csv"):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the composite+filter kernel from the committed
+    `ncu --set full` capture of this same workload (one launch).  None when the summary is missing."""
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), summary)
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    got = {}
+    try:
+        with open(path) as f:
+            for line in f:
+                parts = line.strip().split(",")
+                if len(parts) == 3 and parts[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum") and parts[0] not in got:
+                    got[parts[0]] = float(parts[2]) * scale.get(parts[1], 1.0)
+    except OSError:
+        return None
+    return sum(got.values()) if len(got) == 2 else None
+
+
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -334,7 +351,8 @@ def run_ours(args, rank: int, world: int, local_rank: int):
                 "last_step_device_ms": e2e_tm},
         "gpu_launches": value_launches,
         "roofline": {"bound": "hbm", "kernel": "composite+filter-select (kernels b+c)", "achieved": achieved, "peak": peak,
-                     "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": profiled_traffic_bytes(), "peak_source": peak_src,
+                     "traffic_source": "profiles/r1b_prof_fused_r1i.summary.csv (ncu --set full, one launch, bytes)",
                      "algorithmic_bytes_per_launch": alg_bytes, "avg_ms": cmp_avg,
                      "frac_of_8TBps": achieved / 8000.0},
         "kernels": {"unfilter": {"avg_ms": dec_avg, "achieved_GBps": unf_achieved, "frac": unf_achieved / peak},

@@ -52,6 +52,8 @@ struct stitch_job {
   stitch::UnfStream *d_slow = nullptr; size_t slow_cap = 0;          // chains with a truncated final row (legacy kernel)
   stitch::UnfUnit *d_units = nullptr; size_t units_cap = 0;
   uint8_t *d_uprog = nullptr; size_t uprog_cap = 0;          // wavefront kernel: ticket (256 B) | seam mailbox
+  std::vector<stitch::UnfStream> h_fast;  // chains whose tables are on the device (skip the upload when unchanged)
+  uint32_t n_fast_units = 0;
   uint32_t seam_epoch = 0;                                   // tag of the last decode that used the mailbox
   stitch::A7Image *d_a7 = nullptr; size_t a7_cap = 0;
   uint32_t bins_x = 0, bins_y = 0, bin_w_log2 = 9, bin_h_log2 = 4, bin_y_origin = 0;
