@@ -96,12 +96,14 @@ typedef struct stitch_timings {
   uint32_t reserved;
 } stitch_timings;
 
-/* JPEG band result header (STITCH_OUT_JPEG_ENTROPY).  The entropy bytes of a
- * band are byte-aligned on their own (bit-padded with 1s at the end only when
- * `final` is set); the host splices bands with stitch_jpeg_splice(). */
+/* JPEG band result header (STITCH_OUT_JPEG_ENTROPY).  The restart interval is
+ * one MCU row (the DRI segment of stitch_jpeg_header), so a band's payload is a
+ * byte-aligned run of complete entropy segments, each followed by its RSTm
+ * marker (none after the image's last MCU row): bands are spliced by plain
+ * concatenation in ascending row order, then EOI. */
 typedef struct stitch_jpeg_band_info {
-  uint64_t n_bits;     /* entropy bits produced for this band before byte stuffing */
-  int32_t last_dc[3];  /* DC predictors after the band's last MCU (Y, Cb, Cr) */
+  uint64_t n_bits;     /* 8 * payload bytes that follow this header (stuffing and RST markers included) */
+  int32_t last_dc[3];  /* always 0: every restart segment starts from zero DC predictors */
   uint32_t reserved;
 } stitch_jpeg_band_info;
 
@@ -121,8 +123,11 @@ int stitch_abi_version(void);
 int stitch_job_create(stitch_ctx *ctx, const stitch_job_desc *desc, stitch_job **out);
 void stitch_job_destroy(stitch_job *job);
 
-/* Registers one input and starts its upload.  `data` is borrowed until the
- * call returns (it is copied through a pinned staging ring).  Validates what
+/* Registers one input and starts its upload on the context's upload stream
+ * (kernels of earlier bands and downloads keep running meanwhile).  Pageable
+ * `data` is borrowed until the call returns; page-locked `data` (cudaHostAlloc /
+ * cudaHostRegister) is read asynchronously and must stay valid until the next
+ * stitch_job_decode / stitch_job_run_band that needs the tile returns.  Validates what
  * the reference validates while reading: colour type (pixel-ops.ts:609-611),
  * stream length (png-decoder.ts:209-211, adam7.ts:79-82); filter bytes are
  * validated on the device by stitch_job_decode. */
@@ -148,7 +153,12 @@ int stitch_job_decode(stitch_job *job, int force, stitch_timings *t);
  *      JPEG stitch_jpeg_band_info followed by the band's entropy bytes
  *           (y0 % 8 == 0; y1 % 8 == 0 or y1 == canvas_h)
  *  out == NULL: the result stays on the device (stitch_job_band_device).
- * The PNG predictor row for y0 > 0 is recomputed on the device (1-row halo). */
+ * The PNG predictor row for y0 > 0 is recomputed on the device (1-row halo).
+ * With a host destination a PNG / RAW band is produced in chunks of about
+ * 64 MB, each downloaded on its own stream while the next one is computed and
+ * later tiles are still uploading; only the tiles a chunk touches are decoded
+ * before it.  The call returns when `out` is complete.  In that case
+ * t->decode_ms covers the first chunk's decode only. */
 int stitch_job_run_band(stitch_job *job, uint32_t y0, uint32_t y1, uint8_t *out, size_t cap,
                         size_t *out_len, stitch_timings *t);
 
