@@ -707,8 +707,13 @@ extern "C" int stitch_job_run_band(stitch_job *job, uint32_t y0, uint32_t y1, ui
     // composite the band into HBM, then kernel (d); MCU rows are independent entropy segments (jpeg.cu)
     job->canvas_pitch = pitch16;
     if ((rc = ensure_buffer(ctx, &job->d_canvas, &job->canvas_bytes, pitch16 * (size_t)n_rows))) return rc;
-    cp.y_begin = y0; cp.y_end = y1; cp.out = job->d_canvas; cp.out_pitch = pitch16;
-    CK(launch_compose(cp, false, ctx->stream));
+    {  // the quad compositor of fused.cu (16-byte loads inside a tile) feeding the canvas
+      FusedParams fq{};
+      fq.tiles = job->d_tiles; fq.bin_start = job->d_bin_start; fq.bin_tiles = job->d_bin_tiles;
+      fq.bins_x = job->bins_x; fq.canvas_w = jd.canvas_w; fq.alpha_blend = jd.alpha_blend;
+      bg_words(jd, fq.bg_lo, fq.bg_hi);
+      CK(launch_compose_canvas(fq, false, job->d_canvas, pitch16, y0, y1, ctx->stream));
+    }
     launches += 1;
     if ((rc = stitch_jpeg_encode_band(job, y0, y1, job->d_canvas, pitch16, &jpeg_bytes, &launches))) return rc;
     job->out_pitch = jpeg_bytes; job->out_lead = 0; job->out_row_bytes = jpeg_bytes;

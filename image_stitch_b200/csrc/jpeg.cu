@@ -137,11 +137,14 @@ struct JpegGeom {
   uint32_t rows_in_band;    // canvas rows held at `canvas`
 };
 
-__global__ void __launch_bounds__(128) jpeg_dct_kernel(const uint8_t *canvas, size_t pitch, JpegGeom g, int16_t *coefs) {
+__global__ void __launch_bounds__(128) jpeg_dct_kernel(const uint8_t *canvas, size_t pitch, JpegGeom g, int16_t *coefs,
+                                                       unsigned long long *nzmask) {
   const uint32_t m = blockIdx.x * blockDim.x + threadIdx.x;  // MCU in the row
-  const uint32_t comp = blockIdx.z;                          // 0 Y, 1 Cb, 2 Cr
   if (m >= g.mcus) return;
-  for (uint32_t mr = blockIdx.y; mr < g.mrows; mr += gridDim.y) {
+  // The three components of an MCU are done by the same thread one after the other: the pixels come from
+  // HBM once, the second and third pass hit L1.
+  for (uint32_t it = blockIdx.y * 3u; it < g.mrows * 3u; it += (it % 3u == 2u) ? gridDim.y * 3u - 2u : 1u) {
+    const uint32_t mr = it / 3u, comp = it - mr * 3u;  // 0 Y, 1 Cb, 2 Cr
     int d[64];
 #pragma unroll
     for (int yy = 0; yy < 8; yy++) {
@@ -150,7 +153,7 @@ __global__ void __launch_bounds__(128) jpeg_dct_kernel(const uint8_t *canvas, si
       const uint8_t *row = canvas + (size_t)y * pitch;
       uint32_t px[8];
       if (m * 8u + 8u <= g.width) {
-        const uint4 a = *reinterpret_cast<const uint4 *>(row + (size_t)m * 32), b = *reinterpret_cast<const uint4 *>(row + (size_t)m * 32 + 16);
+        const uint4 a = __ldg(reinterpret_cast<const uint4 *>(row + (size_t)m * 32)), b = __ldg(reinterpret_cast<const uint4 *>(row + (size_t)m * 32 + 16));
         px[0] = a.x; px[1] = a.y; px[2] = a.z; px[3] = a.w; px[4] = b.x; px[5] = b.y; px[6] = b.z; px[7] = b.w;
       } else {
 #pragma unroll
@@ -177,6 +180,7 @@ __global__ void __launch_bounds__(128) jpeg_dct_kernel(const uint8_t *canvas, si
       fdct_1d(d[i], d[8 + i], d[16 + i], d[24 + i], d[32 + i], d[40 + i], d[48 + i], d[56 + i], false);
     const int cls = comp ? 1 : 0;
     uint32_t packed[32];
+    uint32_t nz_lo = 0u, nz_hi = 0u;  // bit k: AC coefficient k (zigzag order) is not zero
 #pragma unroll
     for (int k = 0; k < 64; k++) {
       const int c = d[zz_nat(k)];
@@ -184,8 +188,11 @@ __global__ void __launch_bounds__(128) jpeg_dct_kernel(const uint8_t *canvas, si
       const int qv = (int)__umulhi(n, c_recip[cls][k]);
       const uint32_t v16 = (uint32_t)(c < 0 ? -qv : qv) & 0xffffu;
       if (k & 1) packed[k >> 1] |= v16 << 16; else packed[k >> 1] = v16;
+      if (k > 0 && qv != 0) { if (k < 32) nz_lo |= 1u << (k & 31); else nz_hi |= 1u << (k & 31); }
     }
-    uint4 *o = reinterpret_cast<uint4 *>(coefs + (((size_t)mr * g.mcus + m) * 3 + comp) * 64);
+    const size_t blk_idx = ((size_t)mr * g.mcus + m) * 3 + comp;
+    nzmask[blk_idx] = ((unsigned long long)nz_hi << 32) | nz_lo;
+    uint4 *o = reinterpret_cast<uint4 *>(coefs + blk_idx * 64);
 #pragma unroll
     for (int k = 0; k < 8; k++) o[k] = make_uint4(packed[4 * k], packed[4 * k + 1], packed[4 * k + 2], packed[4 * k + 3]);
   }
@@ -204,55 +211,82 @@ __device__ __forceinline__ void load_huff(HuffSmem &h) {
 }
 
 // Walks one block's symbols.  EMIT: void(uint32_t code, uint32_t size) with size <= 27.
+// w: the block's 32 coefficient words (shared memory), mask: its non-zero AC positions.  Each thread steps
+// through ITS non-zero coefficients, so a warp iterates max-over-lanes(non-zeros) times, not 63 times with
+// a handful of lanes alive in each.
 template <class EMIT>
-__device__ __forceinline__ void code_block(const int16_t *blk, int pred, const uint32_t *dc, const uint32_t *ac, EMIT emit) {
-  const uint4 *q = reinterpret_cast<const uint4 *>(blk);
-  uint32_t w[32];
-#pragma unroll
-  for (int k = 0; k < 8; k++) { const uint4 v = q[k]; w[4 * k] = v.x; w[4 * k + 1] = v.y; w[4 * k + 2] = v.z; w[4 * k + 3] = v.w; }
+__device__ __forceinline__ void code_block(const uint32_t *w, unsigned long long mask, int pred, const uint32_t *dc,
+                                           const uint32_t *ac, EMIT emit) {
   const int dcv = (int)(int16_t)(w[0] & 0xffffu);
   const int diff = dcv - pred;
   uint32_t s = mag_bits(diff);
   uint32_t e = dc[s];
   // code then magnitude bits (negative values: low bits of diff - 1)
   emit(((e >> 8) << s) | ((uint32_t)(diff < 0 ? diff - 1 : diff) & ((1u << s) - 1u)), (e & 0xffu) + s);
-  uint32_t run = 0;
-#pragma unroll
-  for (int k = 1; k < 64; k++) {
-    const int v = (int)(int16_t)((k & 1) ? (w[k >> 1] >> 16) : (w[k >> 1] & 0xffffu));
-    if (v == 0) { run++; continue; }
+  int prev = 0;
+  while (mask) {
+    const int k = __ffsll((long long)mask) - 1;
+    mask &= mask - 1ull;
+    uint32_t run = (uint32_t)(k - prev - 1);
+    prev = k;
+    const uint32_t ww = w[k >> 1];
+    const int v = (int)(int16_t)((k & 1) ? (ww >> 16) : (ww & 0xffffu));
     while (run > 15u) { e = ac[0xF0]; emit(e >> 8, e & 0xffu); run -= 16u; }
     s = mag_bits(v);
     e = ac[(run << 4) | s];
     emit(((e >> 8) << s) | ((uint32_t)(v < 0 ? v - 1 : v) & ((1u << s) - 1u)), (e & 0xffu) + s);
-    run = 0;
   }
-  if (run) { e = ac[0]; emit(e >> 8, e & 0xffu); }
+  if (prev != 63) { e = ac[0]; emit(e >> 8, e & 0xffu); }
 }
 
-__device__ __forceinline__ int block_pred(const int16_t *coefs, uint32_t blk_in_row) {
-  return blk_in_row >= 3u ? (int)coefs[-3 * 64] : 0;  // previous MCU, same component; restart resets to 0
+// 256 consecutive blocks (32 KB) -> shared memory, coalesced; block t at words [33 t, 33 t + 32) (odd stride:
+// the threads' accesses to "their" block spread over the banks).
+static constexpr int JB_STRIDE = 33;
+__device__ __forceinline__ void stage_blocks(uint32_t *sm, const int16_t *coefs, size_t first_blk, size_t n_blk_total) {
+  const uint4 *src = reinterpret_cast<const uint4 *>(coefs + first_blk * 64);
+  const size_t avail = (n_blk_total - first_blk) * 8;  // 16-byte pieces left
+#pragma unroll
+  for (int j = 0; j < 8; j++) {
+    const uint32_t i = (uint32_t)j * 256u + threadIdx.x;
+    if (i < avail) {
+      const uint4 v = __ldg(src + i);
+      uint32_t *d = sm + (i >> 3) * JB_STRIDE + (i & 7u) * 4u;
+      d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+    }
+  }
+}
+
+// DC predictor of block t of a staged chunk: previous MCU, same component; a restart resets it to 0.
+// blk_in_row: the block's index inside its MCU row; the first 3 blocks of a chunk look at global memory.
+__device__ __forceinline__ int block_pred(const uint32_t *sm, uint32_t t, const int16_t *coefs, size_t blk, uint32_t blk_in_row) {
+  if (blk_in_row < 3u) return 0;
+  if (t >= 3u) return (int)(int16_t)(sm[(t - 3u) * JB_STRIDE] & 0xffffu);
+  return (int)__ldg(coefs + (blk - 3) * 64);
 }
 
 // ---- J2: code lengths + scan, one CTA per MCU row -------------------------------------------------------
-__global__ void __launch_bounds__(256) jpeg_len_kernel(const int16_t *coefs, JpegGeom g, uint32_t *bit_off, uint32_t *row_bits) {
+__global__ void __launch_bounds__(256) jpeg_len_kernel(const int16_t *coefs, const unsigned long long *nzmask, JpegGeom g,
+                                                       uint32_t *bit_off, uint32_t *row_bits) {
   __shared__ HuffSmem hs;
   __shared__ uint32_t warp_tot[8];
   __shared__ uint32_t s_base;
+  __shared__ uint32_t sblk[256 * JB_STRIDE];
   load_huff(hs);
   if (threadIdx.x == 0) s_base = 0;
   __syncthreads();
   const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
   for (uint32_t mr = blockIdx.x; mr < g.mrows; mr += gridDim.x) {
     const uint32_t n_blk = g.mcus * 3u;
-    const int16_t *row = coefs + (size_t)mr * n_blk * 64;
+    const size_t row0 = (size_t)mr * n_blk;
     for (uint32_t b0 = 0; b0 < n_blk; b0 += 256u) {
+      stage_blocks(sblk, coefs, row0 + b0, row0 + n_blk);
+      __syncthreads();
       const uint32_t b = b0 + threadIdx.x;
       uint32_t len = 0;
       if (b < n_blk) {
         const uint32_t cls = (b % 3u) ? 1u : 0u;
-        const int16_t *blk = row + (size_t)b * 64;
-        code_block(blk, block_pred(blk, b), hs.dc[cls], hs.ac[cls], [&](uint32_t, uint32_t size) { len += size; });
+        code_block(sblk + threadIdx.x * JB_STRIDE, nzmask[row0 + b], block_pred(sblk, threadIdx.x, coefs, row0 + b, b),
+                   hs.dc[cls], hs.ac[cls], [&](uint32_t, uint32_t size) { len += size; });
       }
       // block-wide exclusive scan
       uint32_t incl = len;
@@ -264,7 +298,7 @@ __global__ void __launch_bounds__(256) jpeg_len_kernel(const int16_t *coefs, Jpe
 #pragma unroll
       for (int k = 0; k < 8; k++) if ((uint32_t)k < warp) wbase += warp_tot[k];
       const uint32_t base = s_base;
-      if (b < n_blk) bit_off[(size_t)mr * n_blk + b] = base + wbase + incl - len;
+      if (b < n_blk) bit_off[row0 + b] = base + wbase + incl - len;
       __syncthreads();
       if (threadIdx.x == 255u) s_base = base + wbase + incl;
       __syncthreads();
@@ -343,21 +377,26 @@ struct BitSink {
   }
 };
 
-__global__ void __launch_bounds__(256) jpeg_emit_kernel(const int16_t *coefs, JpegGeom g, const uint32_t *bit_off,
-                                                        const uint32_t *row_bits, const unsigned long long *row_base,
-                                                        uint32_t *ubuf) {
+__global__ void __launch_bounds__(256) jpeg_emit_kernel(const int16_t *coefs, const unsigned long long *nzmask, JpegGeom g,
+                                                        const uint32_t *bit_off, const uint32_t *row_bits,
+                                                        const unsigned long long *row_base, uint32_t *ubuf) {
   __shared__ HuffSmem hs;
+  __shared__ uint32_t sblk[256 * JB_STRIDE];
   load_huff(hs);
-  __syncthreads();
   const uint32_t n_blk = g.mcus * 3u;
   const size_t total = (size_t)g.mrows * n_blk;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+  for (size_t c0 = (size_t)blockIdx.x * 256u; c0 < total; c0 += (size_t)gridDim.x * 256u) {
+    __syncthreads();  // the previous chunk is done with sblk (and the tables are loaded)
+    stage_blocks(sblk, coefs, c0, total);
+    __syncthreads();
+    const size_t i = c0 + threadIdx.x;
+    if (i >= total) continue;
     const uint32_t mr = (uint32_t)(i / n_blk), b = (uint32_t)(i - (size_t)mr * n_blk);
     const uint32_t cls = (b % 3u) ? 1u : 0u;
-    const int16_t *blk = coefs + i * 64;
     BitSink sink;
     sink.words = ubuf; sink.pos = row_base[mr] * 8ull + bit_off[i]; sink.acc = 0; sink.nacc = 0;
-    code_block(blk, block_pred(blk, b), hs.dc[cls], hs.ac[cls], [&](uint32_t code, uint32_t size) { sink.put(code, size); });
+    code_block(sblk + threadIdx.x * JB_STRIDE, nzmask[i], block_pred(sblk, threadIdx.x, coefs, i, b), hs.dc[cls], hs.ac[cls],
+               [&](uint32_t code, uint32_t size) { sink.put(code, size); });
     if (b == n_blk - 1u) {  // pad the row segment with 1-bits to a byte boundary
       const uint32_t pad = (8u - (row_bits[mr] & 7u)) & 7u;
       if (pad) sink.put((1u << pad) - 1u, pad);
@@ -470,6 +509,8 @@ int stitch_jpeg_encode_band(stitch_job *job, uint32_t y0, uint32_t y1, const uin
   const size_t rows_pad = ((size_t)g.mrows + 3) / 4 * 4;
   if ((rc = stitch_ensure_buffer(ctx, &job->d_jpeg[2], &job->jpeg_cap[2], rows_pad * 24 + 64))) return rc;
   if (!job->h_jpeg_totals) STITCH_CK(cudaHostAlloc((void **)&job->h_jpeg_totals, 16, cudaHostAllocDefault));
+  if ((rc = stitch_ensure_buffer(ctx, &job->d_jpeg[4], &job->jpeg_cap[4], n_blk * 8))) return rc;
+  unsigned long long *nzmask = reinterpret_cast<unsigned long long *>(job->d_jpeg[4]);
   int16_t *coefs = reinterpret_cast<int16_t *>(job->d_jpeg[0]);
   uint32_t *bit_off = reinterpret_cast<uint32_t *>(job->d_jpeg[1]);
   uint32_t *row_bits = reinterpret_cast<uint32_t *>(job->d_jpeg[2]);
@@ -479,12 +520,12 @@ int stitch_jpeg_encode_band(stitch_job *job, uint32_t y0, uint32_t y1, const uin
   unsigned long long *totals = out_base + rows_pad;
 
   {
-    dim3 grid((g.mcus + 127u) / 128u, g.mrows < 4096u ? g.mrows : 4096u, 3);
-    jpeg_dct_kernel<<<grid, 128, 0, ctx->stream>>>(canvas, canvas_pitch, g, coefs);
+    dim3 grid((g.mcus + 127u) / 128u, g.mrows < 4096u ? g.mrows : 4096u);
+    jpeg_dct_kernel<<<grid, 128, 0, ctx->stream>>>(canvas, canvas_pitch, g, coefs, nzmask);
     STITCH_CK(cudaGetLastError());
   }
   const uint32_t row_grid = g.mrows < 148u * 8u ? g.mrows : 148u * 8u;
-  jpeg_len_kernel<<<row_grid, 256, 0, ctx->stream>>>(coefs, g, bit_off, row_bits);
+  jpeg_len_kernel<<<row_grid, 256, 0, ctx->stream>>>(coefs, nzmask, g, bit_off, row_bits);
   STITCH_CK(cudaGetLastError());
   jpeg_rowscan_kernel<<<1, 1024, 0, ctx->stream>>>(row_bits, row_ff, g.mrows, first_mrow, total_mrows, 0, row_base, totals);
   STITCH_CK(cudaGetLastError());
@@ -498,7 +539,7 @@ int stitch_jpeg_encode_band(stitch_job *job, uint32_t y0, uint32_t y1, const uin
   {
     const size_t want = (n_blk + 255) / 256;
     const uint32_t grid = (uint32_t)(want < 148u * 16u ? want : 148u * 16u);
-    jpeg_emit_kernel<<<grid, 256, 0, ctx->stream>>>(coefs, g, bit_off, row_bits, row_base, reinterpret_cast<uint32_t *>(job->d_jpeg[3]));
+    jpeg_emit_kernel<<<grid, 256, 0, ctx->stream>>>(coefs, nzmask, g, bit_off, row_bits, row_base, reinterpret_cast<uint32_t *>(job->d_jpeg[3]));
     STITCH_CK(cudaGetLastError());
   }
   jpeg_ffcount_kernel<<<row_grid, 256, 0, ctx->stream>>>(job->d_jpeg[3], row_bits, row_base, g.mrows, row_ff);

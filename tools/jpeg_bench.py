@@ -1,0 +1,26 @@
+"""C5 shape: grid mosaic -> JPEG q=90 entropy bytes on the GPU (one 16384 x 16384 band per run), device timings."""
+import sys, os, time
+import numpy as np
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from image_stitch_b200 import _native, synth
+
+grid, tile = 16, 1024
+canvas = grid * tile
+rng = np.random.default_rng(5)
+raws = [synth.smooth_rgba8(rng, tile, tile, "opaque") for _ in range(4)]
+ctx = _native.Context(0)
+with _native.Job(ctx, canvas, canvas, 8, _native.OUT_JPEG_ENTROPY, False, bytes(4), jpeg_quality=90) as job:
+    for r in range(grid):
+        for c in range(grid):
+            job.add_tile(raws[(r * 5 + c * 3) % 4].reshape(-1), width=tile, height=tile, bit_depth=8, color_type=6,
+                         filtered=0, dst_x=c * tile, dst_y=r * tile, image_idx=r * grid + c)
+    for rows in (canvas, 2048):
+        best = None
+        for _ in range(4):
+            t0 = time.perf_counter()
+            _, tm = job.run_band(0, rows, download=False)
+            dt = (time.perf_counter() - t0) * 1e3
+            best = tm if best is None or tm["compose_ms"] < best["compose_ms"] else best
+        print(f"{rows} rows: compose+jpeg {best['compose_ms']:.3f} ms on device ({rows * canvas / best['compose_ms'] / 1e3:.0f} MPix/s), "
+              f"launches {best['launches']}, wall {dt:.2f} ms", flush=True)
+ctx.close()
