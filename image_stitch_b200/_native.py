@@ -20,7 +20,7 @@ OUT_PNG_FILTERED, OUT_RAW_RGBA, OUT_JPEG_ENTROPY = 0, 1, 2
 EXPORTS = [
     "stitch_abi_version", "stitch_ctx_create", "stitch_ctx_destroy", "stitch_ctx_set_stream",
     "stitch_last_error", "stitch_job_create", "stitch_job_destroy", "stitch_job_add_tile",
-    "stitch_job_add_tile_device", "stitch_job_decode", "stitch_job_run_band", "stitch_job_band_device",
+    "stitch_job_add_tile_device", "stitch_job_decode", "stitch_job_invalidate", "stitch_job_run_band", "stitch_job_band_device",
     "stitch_job_status", "stitch_decode_image", "stitch_filter_rows", "stitch_jpeg_header",
 ]
 
@@ -94,6 +94,7 @@ def load() -> C.CDLL:
     lib.stitch_job_add_tile.argtypes = [vp, C.POINTER(TileDesc), vp, sz]
     lib.stitch_job_add_tile_device.argtypes = [vp, C.POINTER(TileDesc), vp, sz]
     lib.stitch_job_decode.argtypes = [vp, C.c_int, C.POINTER(Timings)]
+    lib.stitch_job_invalidate.argtypes = [vp]
     lib.stitch_job_run_band.argtypes = [vp, C.c_uint32, C.c_uint32, vp, sz, C.POINTER(sz), C.POINTER(Timings)]
     lib.stitch_job_band_device.argtypes = [vp, C.POINTER(vp), C.POINTER(sz), C.POINTER(sz), C.POINTER(sz)]
     lib.stitch_job_status.argtypes = [vp]
@@ -254,6 +255,10 @@ class Job:
         t = Timings()
         self.ctx.check(self.lib.stitch_job_decode(self.handle, 1 if force else 0, C.byref(t)))
         return t.as_dict()
+
+    def invalidate(self) -> None:
+        """The next run_band unfilters its tiles again (inputs stay resident)."""
+        self.ctx.check(self.lib.stitch_job_invalidate(self.handle))
 
     def band_bytes(self, y0: int, y1: int) -> int:
         row = self.canvas_w * self.bpp + (1 if self.out_kind == OUT_PNG_FILTERED else 0)

@@ -442,6 +442,12 @@ static int decode_tiles(stitch_job *job, int force, uint32_t *launches, uint32_t
   return STITCH_OK;
 }
 
+extern "C" int stitch_job_invalidate(stitch_job *job) {
+  if (!job) return STITCH_E_INVALID;
+  for (auto &t : job->tiles) t.decoded = false;
+  return STITCH_OK;
+}
+
 extern "C" int stitch_job_decode(stitch_job *job, int force, stitch_timings *t) {
   if (!job) return STITCH_E_INVALID;
   stitch_ctx *ctx = job->ctx;

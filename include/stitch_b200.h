@@ -142,6 +142,12 @@ int stitch_job_add_tile_device(stitch_job *job, const stitch_tile_desc *tile, co
  * unless `force` is set (bench: re-run with inputs resident in HBM). */
 int stitch_job_decode(stitch_job *job, int force, stitch_timings *t);
 
+/* Forgets that the job's tiles were decoded (no device work): the next
+ * stitch_job_run_band unfilters again what its rows need, in the same stream
+ * submission as the composite -- one synchronisation per band instead of two.
+ * For repeated measurements with the inputs resident in HBM. */
+int stitch_job_invalidate(stitch_job *job);
+
 /* Kernels (b)+(c) (PNG), (b) (RAW) or (b)+(d) (JPEG) for canvas rows
  * [y0,y1): convertScanline (src/pixel-ops.ts:496-633), row assembly
  * (src/image-concat-core.ts:404-545, :551-685), compositeScanline
