@@ -35,6 +35,7 @@
 // written once.
 #include "common.cuh"
 #include "kernels.h"
+#include <type_traits>
 
 namespace stitch {
 
@@ -137,22 +138,33 @@ struct WaveState {       // D = filter distance in words
   uint32_t last;             // my last result, packed (what the lane below reads)
 };
 // f: filtered word; up: word above.  Returns the reconstructed word and advances the state.
-template <int D>
+// PAETH = false: no row of the warp's group uses the Paeth filter (a warp-uniform fact, checked once per unit).
+// None, Sub, Up and Average then share one form: t = 1024 + a' + b' with the unused input forced to zero is the
+// predictor itself for None/Sub/Up and halves to the Average predictor -- a third fewer instructions per step.
+template <int D, bool PAETH>
 __device__ __forceinline__ uint32_t wave_word(const LaneFilter &k, WaveState<D> &s, uint32_t f, uint32_t up) {
   const __half2 m1024 = __float2half2_rn(-1024.f);
   const __half2 b_lo = unpack2(up, k.b_lo), b_hi = unpack2(up, k.b_hi);
   const __half2 f_lo = __hadd2(unpack2(f, 0x4140u), m1024), f_hi = __hadd2(unpack2(f, 0x4342u), m1024);
-  const __half2 p_lo = paeth_h2(s.a_lo[0], b_lo, s.c_lo[0]), p_hi = paeth_h2(s.a_hi[0], b_hi, s.c_hi[0]);
-  const __half2 v_lo = avg_h2(s.a_lo[0], b_lo), v_hi = avg_h2(s.a_hi[0], b_hi);
+  const __half2 t_lo = __hadd2(s.a_lo[0], __hadd2(b_lo, m1024)), t_hi = __hadd2(s.a_hi[0], __hadd2(b_hi, m1024));
+  const __half2 v_lo = __hfma2(t_lo, __float2half2_rn(0.5f), __float2half2_rn(511.75f));  // see avg_h2
+  const __half2 v_hi = __hfma2(t_hi, __float2half2_rn(0.5f), __float2half2_rn(511.75f));
+  __half2 p_lo, p_hi;
+  if (PAETH) {
+    p_lo = paeth_h2(s.a_lo[0], b_lo, s.c_lo[0]);
+    p_hi = paeth_h2(s.a_hi[0], b_hi, s.c_hi[0]);
+  } else {
+    p_lo = t_lo; p_hi = t_hi;
+  }
   const __half2 r_lo = __hadd2(k.avg ? v_lo : p_lo, f_lo), r_hi = __hadd2(k.avg ? v_hi : p_hi, f_hi);
   const uint32_t o = pack_h4(r_lo, r_hi);  // low byte of each 1024 + (pred + x): the sum mod 256
 #pragma unroll
   for (int d = 0; d + 1 < D; d++) {
     s.a_lo[d] = s.a_lo[d + 1]; s.a_hi[d] = s.a_hi[d + 1];
-    s.c_lo[d] = s.c_lo[d + 1]; s.c_hi[d] = s.c_hi[d + 1];
+    if (PAETH) { s.c_lo[d] = s.c_lo[d + 1]; s.c_hi[d] = s.c_hi[d + 1]; }
   }
   s.a_lo[D - 1] = unpack2(o, k.a_lo); s.a_hi[D - 1] = unpack2(o, k.a_hi);
-  s.c_lo[D - 1] = unpack2(up, k.c_lo); s.c_hi[D - 1] = unpack2(up, k.c_hi);
+  if (PAETH) { s.c_lo[D - 1] = unpack2(up, k.c_lo); s.c_hi[D - 1] = unpack2(up, k.c_hi); }
   s.last = o;
   return o;
 }
@@ -251,6 +263,7 @@ __device__ void run_unit(const UnfStream &s, const uint32_t g, uint8_t *ws, uint
   uint32_t o1 = 0u, o2 = 0u, u1 = 0u, u2 = 0u, last = 0u;
   // state of the word path
   const LaneFilter lf = lane_filter(ft);
+  const bool any_paeth = __any_sync(FULL, ft == 4u);
   WaveState<D> st;
 #pragma unroll
   for (int d = 0; d < D; d++) st.a_lo[d] = st.a_hi[d] = st.c_lo[d] = st.c_hi[d] = __float2half2_rn(1024.f);
@@ -297,26 +310,30 @@ __device__ void run_unit(const UnfStream &s, const uint32_t g, uint8_t *ws, uint
       // lane l works in the current slot from step l on, before that in the tail of the previous one
       const uint32_t in_cur = cur_slot + in_off - 4u * lane, in_prev = prev_slot + in_off - 4u * lane + 128u;
       const uint32_t out_cur = cur_slot + my_row_off - 4u * lane, out_prev = prev_slot + my_row_off - 4u * lane + 128u;
+      auto block_steps = [&](auto paeth_tag) {
+        constexpr bool PAETH = decltype(paeth_tag)::value;
 #pragma unroll
-      for (int c8 = 0; c8 < 4; c8++) {
-        uint32_t fw[8], sw[8];
-        *reinterpret_cast<uint4 *>(&sw[0]) = *reinterpret_cast<const uint4 *>(ws + cur_slot + c8 * 32);
-        *reinterpret_cast<uint4 *>(&sw[4]) = *reinterpret_cast<const uint4 *>(ws + cur_slot + c8 * 32 + 16);
+        for (int c8 = 0; c8 < 4; c8++) {
+          uint32_t fw[8], sw[8];
+          *reinterpret_cast<uint4 *>(&sw[0]) = *reinterpret_cast<const uint4 *>(ws + cur_slot + c8 * 32);
+          *reinterpret_cast<uint4 *>(&sw[4]) = *reinterpret_cast<const uint4 *>(ws + cur_slot + c8 * 32 + 16);
 #pragma unroll
-        for (int k = 0; k < 8; k++) {
-          const int i = c8 * 8 + k;
-          const uint8_t *ip = ws + ((int)lane <= i ? in_cur : in_prev) + 4 * i;
-          fw[k] = __byte_perm(*reinterpret_cast<const uint32_t *>(ip), *reinterpret_cast<const uint32_t *>(ip + 4), sel);
+          for (int k = 0; k < 8; k++) {
+            const int i = c8 * 8 + k;
+            const uint8_t *ip = ws + ((int)lane <= i ? in_cur : in_prev) + 4 * i;
+            fw[k] = __byte_perm(*reinterpret_cast<const uint32_t *>(ip), *reinterpret_cast<const uint32_t *>(ip + 4), sel);
+          }
+#pragma unroll
+          for (int k = 0; k < 8; k++) {
+            const int i = c8 * 8 + k;
+            uint32_t up = __shfl_up_sync(FULL, st.last, 1);
+            if (lane == 0u) up = sw[k];
+            const uint32_t o = wave_word<D, PAETH>(lf, st, fw[k], up);
+            *reinterpret_cast<uint32_t *>(ws + ((int)lane <= i ? out_cur : out_prev) + 4 * i) = o;
+          }
         }
-#pragma unroll
-        for (int k = 0; k < 8; k++) {
-          const int i = c8 * 8 + k;
-          uint32_t up = __shfl_up_sync(FULL, st.last, 1);
-          if (lane == 0u) up = sw[k];
-          const uint32_t o = wave_word<D>(lf, st, fw[k], up);
-          *reinterpret_cast<uint32_t *>(ws + ((int)lane <= i ? out_cur : out_prev) + 4 * i) = o;
-        }
-      }
+      };
+      if (any_paeth) block_steps(std::true_type{}); else block_steps(std::false_type{});
     } else {
 #pragma unroll 1
       for (uint32_t i = 0; i < 32u; i++) {
@@ -331,7 +348,7 @@ __device__ void run_unit(const UnfStream &s, const uint32_t g, uint8_t *ws, uint
           if (lane == 0u) up = *reinterpret_cast<const uint32_t *>(ws + slot_off + wi * 4u);
           uint32_t o;
           if constexpr (WORDS) {
-            o = wave_word<D>(lf, st, f, up);
+            o = wave_word<D, true>(lf, st, f, up);
           } else {
             o = unf_word<BPP>(ft, f, up, o1, o2, u1, u2);
             o2 = o1; o1 = o; u2 = u1; u1 = up; last = o;
