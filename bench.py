@@ -100,7 +100,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "20"],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
@@ -285,12 +285,18 @@ def run_ours(args, rank: int, world: int, local_rank: int):
         launches += t2["launches"]
         return t2["decode_ms"], t2["compose_ms"]
 
-    for _ in range(max(args.warmup, 3)):
-        step_resident()
-    launches = 0
+    # The timed region is a few tens of milliseconds, shorter than nvidia-smi takes to start: the sampler runs
+    # from before the warm-up, the warm-up continues until its first line is in, and the same load is kept up
+    # after the timed region until two more lines arrive, so the samples bracket the region under load.
     sampler = ClockSampler(local_rank)
-    barrier()
     sampler.start()
+    t_w = time.perf_counter()
+    n_w = 0
+    while n_w < max(args.warmup, 3) or (sampler.proc and not sampler.lines and time.perf_counter() - t_w < 5.0):
+        step_resident()
+        n_w += 1
+    launches = 0
+    barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(ts)
     for _ in range(args.steps):
@@ -299,9 +305,13 @@ def run_ours(args, rank: int, world: int, local_rank: int):
         cmp_ms.append(c)
     e1.record(ts)
     barrier()
+    value_launches = launches
+    n_lines, t_w = len(sampler.lines), time.perf_counter()
+    while sampler.proc and len(sampler.lines) < n_lines + 2 and time.perf_counter() - t_w < 2.0:
+        step_resident()
+    torch.cuda.synchronize(dev)
     clocks = sampler.stop()
     ms_total = e0.elapsed_time(e1)
-    value_launches = launches
     job.close()
 
     # ---- e2e: host buffers in, host buffer out, every step --------------------------------
