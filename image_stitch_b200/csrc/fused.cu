@@ -561,19 +561,23 @@ __global__ void __launch_bounds__(256) compose_canvas_kernel(const FusedParams p
                                                              const uint32_t ys, const uint32_t ye) {
   const int xw = 4 * (int)(blockIdx.x * blockDim.x + threadIdx.x);
   if (xw >= (int)p.canvas_w * BPW) return;
-  for (uint32_t y = ys + blockIdx.y; y < ye; y += gridDim.y) {
-    const uint32_t bin = (y / FB_R) * p.bins_x + (uint32_t)(xw / FB_SWW);
-    const uint32_t b0 = __ldg(p.bin_start + bin), n_list = __ldg(p.bin_start + bin + 1) - b0;
-    const uint4 v = compose_quad<BPW>(p, p.bin_tiles + b0, n_list, xw, (int)y);
-    *reinterpret_cast<uint4 *>(canvas + (size_t)(y - ys) * pitch + (size_t)xw * 4u) = v;
-  }
+  // a thread walks down FU_R rows of one bin: the bin's tile list is looked up once
+  const uint32_t y0 = max(ys, (ys / FU_R + blockIdx.y) * FU_R), y1 = min(ye, (ys / FU_R + blockIdx.y + 1u) * FU_R);
+  if (y0 >= y1) return;
+  const uint32_t bin = (y0 / FB_R) * p.bins_x + (uint32_t)(xw / FB_SWW);
+  const uint32_t b0 = __ldg(p.bin_start + bin), n_list = __ldg(p.bin_start + bin + 1) - b0;
+  uint8_t *dst = canvas + (size_t)(y0 - ys) * pitch + (size_t)xw * 4u;
+  for (uint32_t y = y0; y < y1; y++, dst += pitch)
+    *reinterpret_cast<uint4 *>(dst) = compose_quad<BPW>(p, p.bin_tiles + b0, n_list, xw, (int)y);
 }
 
 cudaError_t launch_compose_canvas(const FusedParams &p, bool out16, uint8_t *canvas, size_t pitch, uint32_t ys,
                                   uint32_t ye, cudaStream_t st) {
   if (ye <= ys) return cudaSuccess;
   const uint32_t quads = (p.canvas_w * (out16 ? 2u : 1u) + 3u) / 4u;
-  const dim3 grid((quads + 255u) / 256u, ye - ys < 65535u ? ye - ys : 65535u);
+  const uint32_t groups = (ye - 1u) / FU_R - ys / FU_R + 1u;  // FU_R-row groups on the absolute grid
+  const dim3 grid((quads + 255u) / 256u, groups);
+  if (groups > 65535u) return cudaErrorInvalidConfiguration;
   if (out16) compose_canvas_kernel<2><<<grid, 256, 0, st>>>(p, canvas, pitch, ys, ye);
   else compose_canvas_kernel<1><<<grid, 256, 0, st>>>(p, canvas, pitch, ys, ye);
   return cudaGetLastError();

@@ -24,8 +24,9 @@ def smooth_rgba8(rng, w: int, h: int, alpha: str = "opaque") -> np.ndarray:
     return img.reshape(h, w * 4)
 
 
-def encode_filtered(pix: np.ndarray, bpp: int, force: int = -1) -> np.ndarray:
-    """[h, n] raw rows -> inflated IDAT stream [h*(n+1)] (PNG encoder side, vectorised over rows)."""
+def encode_filtered(pix: np.ndarray, bpp: int, force: int = -1, rng=None) -> np.ndarray:
+    """[h, n] raw rows -> inflated IDAT stream [h*(n+1)] (PNG encoder side, vectorised over rows).
+    force: -1 = min-sum-of-abs heuristic, 0..4 = that filter on every row, 5 = a random type per row (rng)."""
     h, n = pix.shape
     x = pix.astype(np.int16)
     a = np.zeros_like(x)
@@ -39,7 +40,9 @@ def encode_filtered(pix: np.ndarray, bpp: int, force: int = -1) -> np.ndarray:
     pae = np.where((pa <= pb) & (pa <= pc), a, np.where(pb <= pc, b, c))
     cands = [x, x - a, x - b, x - ((a + b) >> 1), x - pae]
     cands = [(v & 0xFF).astype(np.uint8) for v in cands]
-    if force >= 0:
+    if force == 5:
+        best = (rng or np.random.default_rng(0)).integers(0, 5, size=h)
+    elif force >= 0:
         best = np.full(h, force, np.int64)
     else:
         costs = np.stack([np.where(v > 127, 256 - v.astype(np.int32), v.astype(np.int32)).sum(axis=1) for v in cands])

@@ -17,9 +17,12 @@ for blend in (True, False):
                          dst_x=t["dst_x"], dst_y=t["dst_y"], src_off_x=t["src_off_x"], src_off_y=t["src_off_y"],
                          vis_w=t["vis_w"], vis_h=t["vis_h"], z_index=t["z_index"], image_idx=t["image_idx"])
         ms = []
+        got, tm = job.run_band(4096, 8192)          # with download first, like the test
+        print("  with download:", {k: round(v, 3) for k, v in tm.items()})
         for _ in range(4):
             _, tm = job.run_band(4096, 8192, download=False)
             ms.append(tm["compose_ms"])
         px = 4096 * canvas
+        print("  all runs (ms):", [round(m, 3) for m in ms])
         print(f"blend={blend}: compose+filter {min(ms):.3f} ms for 4096 x 32768 px = {px / min(ms) / 1e3:.0f} MPix/s", flush=True)
 ctx.close()
