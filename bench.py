@@ -72,7 +72,7 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-sample-rows", type=int, default=1024)
-    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU work in the cpu_baseline leg")
+    ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU work in the cpu_baseline leg")
     ap.add_argument("--cpu-threads", type=int, default=0, help="0 = all host cores (at most one per tile column)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -184,6 +184,21 @@ def cpu_sample(tiles, rows: int, threads: int, repeats: int = 1):
 
 def cpu_threads(args) -> int:
     return max(1, min(args.cpu_threads or (os.cpu_count() or 1), GRID))
+
+
+def host_codec_rates(tiles, level: int = 6):
+    """zlib inflate / deflate (level 6) on the host, outside the path's boundary (reported on
+    its own line): one tile's filtered stream, one thread."""
+    import zlib
+    raw = tiles[0][1].tobytes()
+    t0 = time.perf_counter()
+    comp = zlib.compress(raw, level)
+    t1 = time.perf_counter()
+    back = zlib.decompress(comp)
+    t2 = time.perf_counter()
+    assert back == raw
+    return {"deflate_MBps": len(raw) / (t1 - t0) / 1e6, "inflate_MBps": len(raw) / (t2 - t1) / 1e6, "level": level,
+            "ratio": len(raw) / len(comp), "sample": f"one {TILE}x{TILE} RGBA8 tile stream ({len(raw) / 1e6:.1f} MB), 1 thread"}
 
 
 def run_reference(args, rank: int, world: int):
@@ -373,10 +388,14 @@ def run_ours(args, rank: int, world: int, local_rank: int):
         _, dt1 = cpu_sample(tiles, args.cpu_sample_rows, threads)
         reps = max(1, int(round(args.cpu_seconds / max(dt1, 1e-3))))
         mp, dt = cpu_sample(tiles, args.cpu_sample_rows, threads, reps)
+        mp1, dt1s = cpu_sample(tiles, min(args.cpu_sample_rows, 256), 1, 1)   # the reference's own shape: one thread
         line["cpu_baseline"] = {"value": mp, "unit": "MPix/s", "cores": threads, "kind": "port",
                                 "sample": f"{reps} x top {min(args.cpu_sample_rows, TILE)} rows of the same 16384-wide grid "
                                           f"({dt:.1f} s wall, {threads} threads) through the oracle "
-                                          f"(C restatement of the TS reference, oracle/)"}
+                                          f"(C restatement of the TS reference, oracle/)",
+                                "single_thread_value": mp1,
+                                "single_thread_sample": f"top {min(args.cpu_sample_rows, 256)} rows, {dt1s:.1f} s"}
+        line["host_codec"] = host_codec_rates(tiles)
     print(json.dumps(line), flush=True)
     ctx.close()
 
