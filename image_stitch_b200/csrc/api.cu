@@ -744,8 +744,10 @@ extern "C" int stitch_job_run_band(stitch_job *job, uint32_t y0, uint32_t y1, ui
     // them on the upload stream), so the bus is busy in both directions and the kernels hide behind it.
     uint32_t chunk = n_rows;
     if (out) {
-      const size_t want = ((size_t)64 << 20) / std::max<size_t>(host_row, 1);
-      chunk = (uint32_t)std::min<size_t>(n_rows, std::max<size_t>(64, want / 16 * 16));
+      size_t chunk_bytes = (size_t)64 << 20;
+      if (const char *e = getenv("STITCH_CHUNK_BYTES")) chunk_bytes = std::max<size_t>(1, strtoull(e, nullptr, 10));  // tuning / tests
+      const size_t want = chunk_bytes / std::max<size_t>(host_row, 1);
+      chunk = (uint32_t)std::min<size_t>(n_rows, std::max<size_t>(16, want / 16 * 16));
     }
     bool first = true;
     for (uint32_t a = y0; a < y1; a += chunk) {

@@ -246,3 +246,33 @@ def test_filter_costs_extreme_bytes(ctx):
     tiles = [dict(width=w, height=h, bit_depth=8, color_type=6, pixels=pix2)]
     want = orc.render_rows(w, h, 8, bytes(4), False, tiles, 0, h, 0)
     assert np.array_equal(run_job(ctx, w, h, 8, bytes(4), False, tiles, 0), want)
+
+
+def test_chunked_download_seams_and_redecode(ctx, monkeypatch):
+    """stitch_job_run_band with a host destination works in chunks (uploads, kernels and downloads on three
+    streams, only the tiles a chunk touches are decoded before it): tiny chunks put the seams at arbitrary rows
+    of filtered tiles; stitch_job_invalidate + run_band must reproduce the same bytes."""
+    rng = np.random.default_rng(77)
+    cw, ch = 300, 333
+    tiles, streams = [], []
+    for i in range(9):
+        w, h = int(rng.integers(60, 140)), int(rng.integers(60, 140))
+        pix = H.synth_pixels(rng, w, h, 8, 6, ["opaque", "any"][i % 2])
+        streams.append(H.filter_image(pix, 4, "random", rng))
+        x, y = (i % 3) * 100, (i // 3) * 111
+        tiles.append(dict(width=w, height=h, bit_depth=8, color_type=6, pixels=pix, dst_x=x, dst_y=y,
+                          vis_w=min(w, cw - x), vis_h=min(h, ch - y), z_index=i, image_idx=i))
+    want = orc.render_rows(cw, ch, 8, bytes(4), True, tiles, 0, ch, 0)
+    for chunk_bytes in ("1", "40000", "1000000000"):
+        monkeypatch.setenv("STITCH_CHUNK_BYTES", chunk_bytes)
+        with _native.Job(ctx, cw, ch, 8, _native.OUT_PNG_FILTERED, True, bytes(4)) as job:
+            for t, st in zip(tiles, streams):
+                job.add_tile(st, width=t["width"], height=t["height"], bit_depth=8, color_type=6, filtered=1,
+                             dst_x=t["dst_x"], dst_y=t["dst_y"], vis_w=t["vis_w"], vis_h=t["vis_h"], z_index=t["z_index"],
+                             image_idx=t["image_idx"])
+            got, _ = job.run_band(0, ch)
+            assert np.array_equal(np.asarray(got), want), chunk_bytes
+            job.invalidate()
+            again, tm = job.run_band(0, ch)
+            assert np.array_equal(np.asarray(again), want), chunk_bytes
+            assert tm["launches"] >= 2
