@@ -354,7 +354,14 @@ __device__ __forceinline__ uint32_t add4(uint32_t a, uint32_t b) {
   return ((a & 0x7f7f7f7fu) + (b & 0x7f7f7f7fu)) ^ ((a ^ b) & 0x80808080u);
 }
 // per-byte floor((a + b) / 2)
-__device__ __forceinline__ uint32_t avg4(uint32_t a, uint32_t b) { return (a & b) + (((a ^ b) & 0xfefefefeu) >> 1); }
+// (a & b) + (((a ^ b) & 0xfe..fe) >> 1): the masked xor is one LOP3, the shift-and-add one IMAD.HI (x >> 1 is the
+// high word of x * 2^31), which also moves an instruction from the ALU pipe to the FMA pipe.
+__device__ __forceinline__ uint32_t avg4(uint32_t a, uint32_t b) {
+  uint32_t t, r;
+  asm("lop3.b32 %0, %1, %2, %3, 0x28;" : "=r"(t) : "r"(a), "r"(b), "r"(0xfefefefeu));
+  asm("mad.hi.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(t), "r"(0x80000000u), "r"(a & b));
+  return r;
+}
 // per-byte (x - p) mod 256
 __device__ __forceinline__ uint32_t sub4(uint32_t x, uint32_t p) {
   return ((x | 0x80808080u) - (p & 0x7f7f7f7fu)) ^ ((x ^ ~p) & 0x80808080u);
