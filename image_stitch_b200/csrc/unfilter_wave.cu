@@ -29,6 +29,8 @@
 //               Average is computed next to it and selected per lane: one
 //               branch-free instruction stream for all 32 rows whatever their
 //               filter types, fully unrolled over the 32 steps of a block.
+//               Filter distances of 1, 2, 3 and 6 bytes use the same predictor in
+//               rounds over the bytes of a word (byte_word below).
 //
 // HBM traffic is the algorithmic minimum plus the seam rows (2/32 of the pixel
 // bytes written, 2/32 read): every stream byte is read once, every pixel byte
@@ -169,6 +171,84 @@ __device__ __forceinline__ uint32_t wave_word(const LaneFilter &k, WaveState<D> 
   return o;
 }
 
+// ---------------------------------------------------------------------------
+// Branch-free step for filter distances that are not a whole number of words.
+// ---------------------------------------------------------------------------
+// State is kept packed (my previous two results, the previous two words above); the lane's filter type is
+// applied as three all-or-nothing byte masks on the packed operands.  A word is produced in rounds: a round
+// holds the bytes whose left neighbour (distance BPP) is already known -- 1 round for BPP 6 (all four bytes
+// look into earlier words), 2 for BPP 2 and 3, 4 for BPP 1 -- and each round is the same half2 predictor as
+// above on one or two bytes.
+struct ByteState {
+  uint32_t o1, o2, u1, u2, last;
+};
+struct ByteFilter {
+  uint32_t mA, mB, mC;  // 0 or ~0: does this row's filter read the left / up / up-left byte
+  bool avg;
+};
+__device__ __forceinline__ ByteFilter byte_filter(uint32_t ft) {
+  ByteFilter k;
+  k.mA = (ft == 1u || ft == 3u || ft == 4u) ? ~0u : 0u;
+  k.mB = ft >= 2u ? ~0u : 0u;
+  k.mC = ft == 4u ? ~0u : 0u;
+  k.avg = ft == 3u;
+  return k;
+}
+// 1024 + (pred + x) for two bytes; a, b, c as 1024+v (masked operands are 1024), x as plain v.
+template <bool PAETH>
+__device__ __forceinline__ __half2 pred_add(__half2 a, __half2 b, __half2 c, __half2 x, bool avg) {
+  const __half2 t = __hadd2(a, __hadd2(b, __float2half2_rn(-1024.f)));
+  const __half2 v = __hfma2(t, __float2half2_rn(0.5f), __float2half2_rn(511.75f));
+  const __half2 p = PAETH ? paeth_h2(a, b, c) : t;
+  return __hadd2(avg ? v : p, x);
+}
+__device__ __forceinline__ __half2 plain2(uint32_t w, uint32_t sel) {  // bytes -> plain values (not 1024-biased)
+  return __hadd2(unpack2(w, sel), __float2half2_rn(-1024.f));
+}
+template <int BPP, bool PAETH>
+__device__ __forceinline__ uint32_t byte_word(const ByteFilter &k, ByteState &s, uint32_t f, uint32_t up) {
+  const uint32_t B = up & k.mB, Cu = up & k.mC, C1 = s.u1 & k.mC, C2 = s.u2 & k.mC, A1 = s.o1 & k.mA, A2 = s.o2 & k.mA;
+  const __half2 zero = __float2half2_rn(1024.f);
+  uint32_t o;
+  if (BPP == 6) {
+    const uint32_t A = __byte_perm(A2, A1, 0x5432), C = __byte_perm(C2, C1, 0x5432);
+    const __half2 r0 = pred_add<PAETH>(unpack2(A, 0x4140u), unpack2(B, 0x4140u), unpack2(C, 0x4140u), plain2(f, 0x4140u), k.avg);
+    const __half2 r1 = pred_add<PAETH>(unpack2(A, 0x4342u), unpack2(B, 0x4342u), unpack2(C, 0x4342u), plain2(f, 0x4342u), k.avg);
+    o = pack_h4(r0, r1);
+  } else if (BPP == 3) {
+    const __half2 r0 = pred_add<PAETH>(unpack2(A1, 0x4241u), unpack2(B, 0x4140u), unpack2(C1, 0x4241u), plain2(f, 0x4140u), k.avg);
+    const __half2 r1 = pred_add<PAETH>(unpack2(A1, 0x4543u), unpack2(B, 0x4542u), unpack2(C1, 0x4543u), plain2(f, 0x4542u), k.avg);
+    // byte 3: left = byte 0 of this word (low half of r0, brought back to 1024 + v), up-left = byte 0 above
+    const uint32_t r0w = *reinterpret_cast<const uint32_t *>(&r0);
+    const __half2 a3 = k.mA ? unpack2(r0w, 0x4540u) : zero;
+    const __half2 r2 = pred_add<PAETH>(a3, unpack2(B, 0x4543u), unpack2(Cu, 0x4540u), plain2(f, 0x4543u), k.avg);
+    const uint32_t t = __byte_perm(r0w, *reinterpret_cast<const uint32_t *>(&r1), 0x4420);
+    o = __byte_perm(t, *reinterpret_cast<const uint32_t *>(&r2), 0x4210);
+  } else if (BPP == 2) {
+    const __half2 r0 = pred_add<PAETH>(unpack2(A1, 0x4342u), unpack2(B, 0x4140u), unpack2(C1, 0x4342u), plain2(f, 0x4140u), k.avg);
+    const uint32_t r0w = *reinterpret_cast<const uint32_t *>(&r0);
+    const uint32_t p0 = __byte_perm(r0w, 0u, 0x4420) & 0xffffu;  // bytes 0, 1 of the result
+    const __half2 a1 = k.mA ? unpack2(p0, 0x4140u) : zero;
+    const __half2 r1 = pred_add<PAETH>(a1, unpack2(B, 0x4342u), unpack2(Cu, 0x4140u), plain2(f, 0x4342u), k.avg);
+    o = pack_h4(r0, r1);
+  } else {  // BPP == 1
+    __half2 r[4];
+    r[0] = pred_add<PAETH>(unpack2(A1, 0x4543u), unpack2(B, 0x4540u), unpack2(C1, 0x4543u), plain2(f, 0x4540u), k.avg);
+#pragma unroll
+    for (int j = 1; j < 4; j++) {
+      const uint32_t prev = *reinterpret_cast<const uint32_t *>(&r[j - 1]);
+      const __half2 a = k.mA ? unpack2(prev, 0x4540u) : zero;
+      r[j] = pred_add<PAETH>(a, unpack2(B, 0x4540u + (uint32_t)j), unpack2(Cu, 0x4540u + (uint32_t)(j - 1)),
+                             plain2(f, 0x4540u + (uint32_t)j), k.avg);
+    }
+    const uint32_t t0 = __byte_perm(*reinterpret_cast<const uint32_t *>(&r[0]), *reinterpret_cast<const uint32_t *>(&r[1]), 0x4440);
+    const uint32_t t1 = __byte_perm(*reinterpret_cast<const uint32_t *>(&r[2]), *reinterpret_cast<const uint32_t *>(&r[3]), 0x4440);
+    o = __byte_perm(t0, t1, 0x5410);
+  }
+  s.o2 = s.o1; s.o1 = o; s.u2 = s.u1; s.u1 = up; s.last = o;
+  return o;
+}
+
 struct UwParams {
   const UnfStream *streams;
   const UnfUnit *units;
@@ -259,8 +339,10 @@ __device__ void run_unit(const UnfStream &s, const uint32_t g, uint8_t *ws, uint
   const uint32_t total_steps = nwords + rows_g - 1u;
   const uint32_t nphases = (total_steps + 31u) >> 5;
   uint32_t stored = 0u;
-  // state of the byte-serial path
-  uint32_t o1 = 0u, o2 = 0u, u1 = 0u, u2 = 0u, last = 0u;
+  // state of the byte-distance path
+  ByteState bs;
+  bs.o1 = bs.o2 = bs.u1 = bs.u2 = bs.last = 0u;
+  const ByteFilter bf = byte_filter(ft);
   // state of the word path
   const LaneFilter lf = lane_filter(ft);
   const bool any_paeth = __any_sync(FULL, ft == 4u);
@@ -273,7 +355,7 @@ __device__ void run_unit(const UnfStream &s, const uint32_t g, uint8_t *ws, uint
 #pragma unroll
     for (int k = 0; k < 3; k++) *reinterpret_cast<uint32_t *>(ws + k * UW_SLOT_BYTES + lane * 4u) = 0u;
   }
-  if (WORDS) {  // slot 2 is what lanes read before their first word (see the step loop)
+  {  // slot 2 is what lanes read before their first word (see the step loop)
     uint4 *z = reinterpret_cast<uint4 *>(ws + 2 * UW_SLOT_BYTES + UW_ROW_BYTES);
 #pragma unroll
     for (int k = 0; k < 9; k++) z[k * 32 + lane] = make_uint4(0u, 0u, 0u, 0u);
@@ -335,27 +417,33 @@ __device__ void run_unit(const UnfStream &s, const uint32_t g, uint8_t *ws, uint
       };
       if (any_paeth) block_steps(std::true_type{}); else block_steps(std::false_type{});
     } else {
+      // same walk with the byte-distance step; 8 steps unrolled, the loop over the four chunks is kept rolled
+      const uint32_t in_cur = cur_slot + in_off - 4u * lane, in_prev = prev_slot + in_off - 4u * lane + 128u;
+      const uint32_t out_cur = cur_slot + my_row_off - 4u * lane, out_prev = prev_slot + my_row_off - 4u * lane + 128u;
+      auto block_steps = [&](auto paeth_tag) {
+        constexpr bool PAETH = decltype(paeth_tag)::value;
 #pragma unroll 1
-      for (uint32_t i = 0; i < 32u; i++) {
-        uint32_t up = __shfl_up_sync(FULL, WORDS ? st.last : last, 1);
-        const uint32_t j = p * 32u + i - lane;  // wraps to a huge value while the lane has not started
-        if (valid && j < nwords) {
-          const uint32_t wi = j & 31u;
-          const uint32_t slot_off = lane <= i ? cur_slot : prev_slot;
-          const uint8_t *ip = ws + slot_off + in_off + wi * 4u;
-          const uint32_t f = __byte_perm(*reinterpret_cast<const uint32_t *>(ip),
-                                         *reinterpret_cast<const uint32_t *>(ip + 4), sel);
-          if (lane == 0u) up = *reinterpret_cast<const uint32_t *>(ws + slot_off + wi * 4u);
-          uint32_t o;
-          if constexpr (WORDS) {
-            o = wave_word<D, true>(lf, st, f, up);
-          } else {
-            o = unf_word<BPP>(ft, f, up, o1, o2, u1, u2);
-            o2 = o1; o1 = o; u2 = u1; u1 = up; last = o;
+        for (uint32_t c8 = 0; c8 < 4u; c8++) {
+          uint32_t fw[8], sw[8];
+          *reinterpret_cast<uint4 *>(&sw[0]) = *reinterpret_cast<const uint4 *>(ws + cur_slot + c8 * 32u);
+          *reinterpret_cast<uint4 *>(&sw[4]) = *reinterpret_cast<const uint4 *>(ws + cur_slot + c8 * 32u + 16u);
+#pragma unroll
+          for (int k = 0; k < 8; k++) {
+            const uint32_t i = c8 * 8u + (uint32_t)k;
+            const uint8_t *ip = ws + (lane <= i ? in_cur : in_prev) + 4u * i;
+            fw[k] = __byte_perm(*reinterpret_cast<const uint32_t *>(ip), *reinterpret_cast<const uint32_t *>(ip + 4), sel);
           }
-          *reinterpret_cast<uint32_t *>(ws + slot_off + my_row_off + wi * 4u) = o;
+#pragma unroll
+          for (int k = 0; k < 8; k++) {
+            const uint32_t i = c8 * 8u + (uint32_t)k;
+            uint32_t up = __shfl_up_sync(FULL, bs.last, 1);
+            if (lane == 0u) up = sw[k];
+            const uint32_t o = byte_word<WORDS ? 1 : BPP, PAETH>(bf, bs, fw[k], up);
+            *reinterpret_cast<uint32_t *>(ws + (lane <= i ? out_cur : out_prev) + 4u * i) = o;
+          }
         }
-      }
+      };
+      if (any_paeth) block_steps(std::true_type{}); else block_steps(std::false_type{});
     }
   }
   __syncwarp();
@@ -369,7 +457,7 @@ __device__ void run_unit(const UnfStream &s, const uint32_t g, uint8_t *ws, uint
 // KBPP > 0: every chain of the launch has this filter distance (the common case: one pixel format per job),
 // which keeps the specialised kernels small.  KBPP == 0: mixed formats, dispatch per unit.
 template <int KBPP>
-__global__ void __launch_bounds__(UW_WARPS * 32, (KBPP == 4 || KBPP == 8) ? 4 : 3)
+__global__ void __launch_bounds__(UW_WARPS * 32, 4)
     unfilter_wave_kernel(const UwParams p) {
   extern __shared__ __align__(16) uint8_t uw_smem[];
   const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
