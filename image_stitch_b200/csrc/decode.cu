@@ -178,6 +178,37 @@ __constant__ uint8_t c_a7_dy_log[7] = {3, 3, 3, 2, 2, 1, 1};
 __global__ void __launch_bounds__(256) adam7_gather_kernel(const A7Image *images) {
   const A7Image &im = images[blockIdx.z];
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;  // output byte in the row
+  if (im.bit_depth >= 8u && (im.bpp & 3u) == 0u) {
+    // pixels of 4 or 8 bytes: a thread moves one aligned 32-bit word (pass rows and output rows are 16-byte
+    // aligned), so the stores of a warp are 128 contiguous bytes
+    const uint32_t wpp = im.bpp >> 2;  // words per pixel
+    if (i * 4u >= im.row_bytes) return;
+    const uint32_t x = i / wpp, sub = i - x * wpp;
+    for (uint32_t y = blockIdx.y; y < im.height; y += gridDim.y) {
+      const uint32_t p = c_a7_pass[(y & 7u) * 8u + (x & 7u)];
+      const uint32_t px = (x - c_a7_xs[p]) >> c_a7_dx_log[p], py = (y - c_a7_ys[p]) >> c_a7_dy_log[p];
+      const uint32_t v = *reinterpret_cast<const uint32_t *>(im.pass_pix[p] + (size_t)py * im.pass_pitch[p] + (size_t)(px * wpp + sub) * 4u);
+      *reinterpret_cast<uint32_t *>(im.dst + (size_t)y * im.dst_pitch + (size_t)i * 4u) = v;
+    }
+    return;
+  }
+  if (im.bit_depth >= 8u && im.bpp > 1u) {
+    // pixels of 2, 3 or 6 bytes: a thread moves one pixel, the pass lookup is done once per pixel
+    if (i >= im.width) return;
+    const uint32_t bpp = im.bpp;
+    for (uint32_t y = blockIdx.y; y < im.height; y += gridDim.y) {
+      const uint32_t p = c_a7_pass[(y & 7u) * 8u + (i & 7u)];
+      const uint32_t px = (i - c_a7_xs[p]) >> c_a7_dx_log[p], py = (y - c_a7_ys[p]) >> c_a7_dy_log[p];
+      const uint8_t *src = im.pass_pix[p] + (size_t)py * im.pass_pitch[p] + (size_t)px * bpp;
+      uint8_t *dst = im.dst + (size_t)y * im.dst_pitch + (size_t)i * bpp;
+      if ((bpp & 1u) == 0u) {
+        for (uint32_t b = 0; b < bpp; b += 2u) *reinterpret_cast<uint16_t *>(dst + b) = *reinterpret_cast<const uint16_t *>(src + b);
+      } else {
+        for (uint32_t b = 0; b < bpp; b++) dst[b] = src[b];
+      }
+    }
+    return;
+  }
   if (i >= im.row_bytes) return;
   for (uint32_t y = blockIdx.y; y < im.height; y += gridDim.y) {
     uint32_t v = 0;
