@@ -15,7 +15,7 @@ _LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libstitch_
 STITCH_OK = 0
 E_INVALID, E_CUDA, E_NOMEM, E_FILTER, E_COLOR, E_TRUNCATED, E_STATE, E_CAPACITY, E_NODEVICE = (
     -1, -2, -3, -4, -5, -6, -7, -8, -10)
-OUT_PNG_FILTERED, OUT_RAW_RGBA, OUT_JPEG_ENTROPY = 0, 1, 2
+OUT_PNG_FILTERED, OUT_RAW_RGBA, OUT_JPEG_ENTROPY, OUT_PNG_DEFLATE = 0, 1, 2, 3
 
 EXPORTS = [
     "stitch_abi_version", "stitch_ctx_create", "stitch_ctx_destroy", "stitch_ctx_set_stream",
@@ -61,6 +61,10 @@ class Timings(C.Structure):
 
     def as_dict(self) -> dict:
         return {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved"}
+
+
+class DeflateBandInfo(C.Structure):
+    _fields_ = [("n_bytes", C.c_uint64), ("n_raw", C.c_uint64), ("adler", C.c_uint32), ("reserved", C.c_uint32)]
 
 
 class JpegBandInfo(C.Structure):
@@ -261,7 +265,10 @@ class Job:
         self.ctx.check(self.lib.stitch_job_invalidate(self.handle))
 
     def band_bytes(self, y0: int, y1: int) -> int:
-        row = self.canvas_w * self.bpp + (1 if self.out_kind == OUT_PNG_FILTERED else 0)
+        row = self.canvas_w * self.bpp + (1 if self.out_kind in (OUT_PNG_FILTERED, OUT_PNG_DEFLATE) else 0)
+        if self.out_kind == OUT_PNG_DEFLATE:   # worst case: every 32 KiB block stored, 10 bytes of framing each
+            raw = row * (y1 - y0)
+            return C.sizeof(DeflateBandInfo) + raw + (raw // 32768 + 1) * 10 + 64
         if self.out_kind == OUT_JPEG_ENTROPY:
             # worst case of baseline Huffman coding plus the band header
             mcus = ((self.canvas_w + 7) // 8) * ((y1 - y0 + 7) // 8)

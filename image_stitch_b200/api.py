@@ -65,6 +65,7 @@ class StreamingConcatenator:
         try:
             headers: List[PngHeader] = [image_header_to_png_header(d.get_header()) for d in decoders]
             plan = engine.plan_job(opts, inputs, headers, logger=_warn)
+            plan.device_deflate = bool(opts.device_deflate) and plan.output_format != "jpeg"
             self.plan = plan
             needed = sorted({p.image_idx for p in plan.placements})
             sources: Dict[int, TileSource] = {}
@@ -97,6 +98,18 @@ class StreamingConcatenator:
         yield serialize_chunk(create_ihdr(PngHeader(plan.canvas_w, plan.canvas_h, plan.out_bit_depth,
                                                     plan.out_color_type, 0, 0, 0)))
         scanline_size = plan.canvas_w * bpp + 1
+        if plan.device_deflate:
+            # the device already produced deflate blocks: one IDAT per band, zlib framing around them
+            from .deflate_container import ZLIB_HEADER, DeflateBandSplicer
+            splicer = DeflateBandSplicer()
+            head = ZLIB_HEADER
+            for y0, y1, data, tm in engine.run_plan(plan, sources, self.options.devices, self.options.band_rows, on_band):
+                self.last_timings.append(tm)
+                yield serialize_chunk(create_chunk("IDAT", head + splicer.push(data)))
+                head = b""
+            yield serialize_chunk(create_chunk("IDAT", head + splicer.finish()))
+            yield serialize_chunk(create_iend())
+            return
         batch_rows = max(50, (1 << 20) // scanline_size)          # :336-344
         deflater = zlib.compressobj(6)                              # level 6 (:341)
         rows_in_batch = 0

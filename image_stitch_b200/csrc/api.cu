@@ -128,7 +128,7 @@ extern "C" int stitch_job_create(stitch_ctx *ctx, const stitch_job_desc *desc, s
   *out = nullptr;
   if (desc->canvas_w == 0 || desc->canvas_h == 0) return fail(ctx, STITCH_E_INVALID, "Invalid dimensions: %ux%u", desc->canvas_w, desc->canvas_h);
   if (desc->out_bit_depth != 8 && desc->out_bit_depth != 16) return fail(ctx, STITCH_E_INVALID, "out_bit_depth must be 8 or 16");
-  if (desc->out_kind > STITCH_OUT_JPEG_ENTROPY) return fail(ctx, STITCH_E_INVALID, "unknown out_kind %u", desc->out_kind);
+  if (desc->out_kind > STITCH_OUT_PNG_DEFLATE) return fail(ctx, STITCH_E_INVALID, "unknown out_kind %u", desc->out_kind);
   if (desc->out_kind == STITCH_OUT_JPEG_ENTROPY) {
     if (desc->out_bit_depth != 8) return fail(ctx, STITCH_E_INVALID, "JPEG output requires 8-bit RGBA");
     if (desc->jpeg_quality < 1 || desc->jpeg_quality > 100)
@@ -169,6 +169,8 @@ extern "C" void stitch_job_destroy(stitch_job *job) {
   dev_free(ctx, job->d_streams); dev_free(ctx, job->d_a7);
   dev_free(ctx, job->d_slow); dev_free(ctx, job->d_units); dev_free(ctx, job->d_uprog);
   dev_free(ctx, job->d_canvas); dev_free(ctx, job->d_out); dev_free(ctx, job->d_sync); dev_free(ctx, job->d_plans); dev_free(ctx, job->d_ctab);
+  dev_free(ctx, job->d_defl); dev_free(ctx, job->d_defl_scratch);
+  if (job->h_defl) cudaFreeHost(job->h_defl);
   for (auto &q : job->d_jpeg) dev_free(ctx, q);
   if (job->h_jpeg_totals) cudaFreeHost(job->h_jpeg_totals);
   cudaStreamSynchronize(ctx->stream);
@@ -587,7 +589,7 @@ static void bg_words(const stitch_job_desc &d, uint32_t &lo, uint32_t &hi) {
 static int render_rows(stitch_job *job, uint32_t a, uint32_t b, uint8_t *d_rows, uint32_t *launches, cudaEvent_t ev_decoded) {
   stitch_ctx *ctx = job->ctx;
   const stitch_job_desc &jd = job->desc;
-  const bool png = jd.out_kind == STITCH_OUT_PNG_FILTERED;
+  const bool png = jd.out_kind == STITCH_OUT_PNG_FILTERED || jd.out_kind == STITCH_OUT_PNG_DEFLATE;
   const size_t row_bytes = (size_t)jd.canvas_w * job->bpp;
   const size_t pitch16 = round_up(row_bytes, 16);
   const uint32_t n_rows = b - a;
@@ -690,9 +692,10 @@ extern "C" int stitch_job_run_band(stitch_job *job, uint32_t y0, uint32_t y1, ui
     return fail(ctx, STITCH_E_INVALID, "JPEG bands must start on a multiple of 8 rows and end on one or at the canvas bottom");
   const size_t row_bytes = (size_t)jd.canvas_w * job->bpp;
   const uint32_t n_rows = y1 - y0;
-  const bool png = jd.out_kind == STITCH_OUT_PNG_FILTERED;
+  const bool deflate = jd.out_kind == STITCH_OUT_PNG_DEFLATE;
+  const bool png = jd.out_kind == STITCH_OUT_PNG_FILTERED || deflate;
   const size_t host_row = row_bytes + (png ? 1 : 0);
-  if (out && !jpeg && cap < host_row * n_rows) return fail(ctx, STITCH_E_CAPACITY, "output buffer too small: need %zu bytes", host_row * n_rows);
+  if (out && !jpeg && !deflate && cap < host_row * n_rows) return fail(ctx, STITCH_E_CAPACITY, "output buffer too small: need %zu bytes", host_row * n_rows);
   size_t jpeg_bytes = 0;
   const size_t pitch16 = round_up(row_bytes, 16);
 
@@ -743,7 +746,7 @@ extern "C" int stitch_job_run_band(stitch_job *job, uint32_t y0, uint32_t y1, ui
     // own stream while chunk k+1 is computed and while later tiles are still coming up (add_tile queued
     // them on the upload stream), so the bus is busy in both directions and the kernels hide behind it.
     uint32_t chunk = n_rows;
-    if (out) {
+    if (out && !deflate) {
       size_t chunk_bytes = (size_t)64 << 20;
       if (const char *e = getenv("STITCH_CHUNK_BYTES")) chunk_bytes = std::max<size_t>(1, strtoull(e, nullptr, 10));  // tuning / tests
       const size_t want = chunk_bytes / std::max<size_t>(host_row, 1);
@@ -755,18 +758,35 @@ extern "C" int stitch_job_run_band(stitch_job *job, uint32_t y0, uint32_t y1, ui
       uint8_t *d_rows = job->d_out + (size_t)(a - y0) * job->out_pitch;
       if ((rc = render_rows(job, a, b, d_rows, &launches, first ? ctx->ev[2] : nullptr))) return rc;
       first = false;
-      if (out) {
+      if (out && !deflate) {
         CK(cudaEventRecord(ctx->ev_chunk, ctx->stream));
         CK(cudaStreamWaitEvent(ctx->down, ctx->ev_chunk, 0));
         CK(cudaMemcpy2DAsync(out + (size_t)(a - y0) * host_row, host_row, d_rows + job->out_lead, job->out_pitch, host_row,
                              b - a, cudaMemcpyDeviceToHost, ctx->down));
       }
     }
+    if (deflate) {  // 8(f).1: the band leaves the device compressed
+      size_t zbytes = 0;
+      uint32_t adler = 1;
+      if ((rc = stitch_deflate_band(job, n_rows, host_row, &zbytes, &adler, &launches))) return rc;
+      CK(cudaEventRecord(ctx->ev[3], ctx->stream));
+      if (out) {
+        const size_t need = sizeof(stitch_deflate_band_info) + zbytes;
+        if (cap < need) return fail(ctx, STITCH_E_CAPACITY, "output buffer too small: need %zu bytes", need);
+        stitch_deflate_band_info info;
+        memset(&info, 0, sizeof info);
+        info.n_bytes = zbytes; info.n_raw = (uint64_t)host_row * n_rows; info.adler = adler;
+        memcpy(out, &info, sizeof info);
+        CK(cudaMemcpyAsync(out + sizeof info, job->d_defl, zbytes, cudaMemcpyDeviceToHost, ctx->stream));
+        if (out_len) *out_len = need;
+      }
+    } else {
     CK(cudaEventRecord(ctx->ev[3], ctx->stream));
     if (out) {
       CK(cudaEventRecord(ctx->ev_down, ctx->down));
       CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_down, 0));
       if (out_len) *out_len = host_row * n_rows;
+    }
     }
   }
   CK(cudaEventRecord(ctx->ev[4], ctx->stream));

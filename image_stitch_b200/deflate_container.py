@@ -1,0 +1,51 @@
+"""zlib framing around the deflate blocks that libstitch_b200 produces on the device
+(STITCH_OUT_PNG_DEFLATE): the role of StreamingDeflator's output side (src/streaming-deflate.ts:130-185).
+
+Every band is a run of complete, byte-aligned, non-final deflate blocks, so the stream is
+  78 01 | band | band | ... | 01 00 00 FF FF | Adler-32 (big endian)
+with the Adler-32 of all raw rows combined from the per-band values (RFC 1950; zlib's adler32_combine).
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _native
+
+ZLIB_HEADER = b"\x78\x01"            # deflate, 32 KiB window, no preset dictionary, check bits
+FINAL_BLOCK = b"\x01\x00\x00\xff\xff"  # BFINAL = 1, stored, zero bytes
+_M = 65521
+_INFO = C.sizeof(_native.DeflateBandInfo)
+
+
+def adler32_combine(adler1: int, adler2: int, len2: int) -> int:
+    """Adler-32 of A+B from adler32(A), adler32(B) and len(B)."""
+    a1, b1 = adler1 & 0xFFFF, adler1 >> 16
+    a2, b2 = adler2 & 0xFFFF, adler2 >> 16
+    a = (a1 + a2 - 1) % _M
+    b = (b1 + b2 + (len2 % _M) * (a1 - 1)) % _M
+    return (b << 16) | a
+
+
+class DeflateBandSplicer:
+    """Joins the per-band results of stitch_job_run_band (STITCH_OUT_PNG_DEFLATE), in ascending row order."""
+
+    def __init__(self) -> None:
+        self.adler = 1
+        self.raw_bytes = 0
+        self.bytes_out = 0
+
+    def push(self, band) -> bytes:
+        data = memoryview(np.ascontiguousarray(band)).cast("B")
+        info = _native.DeflateBandInfo.from_buffer_copy(bytes(data[:_INFO]))
+        body = bytes(data[_INFO:_INFO + info.n_bytes])
+        if len(body) != info.n_bytes:
+            raise _native.StitchError(_native.E_STATE, "deflate band header does not match its payload")
+        self.adler = adler32_combine(self.adler, info.adler, info.n_raw)
+        self.raw_bytes += info.n_raw
+        self.bytes_out += len(body)
+        return body
+
+    def finish(self) -> bytes:
+        return FINAL_BLOCK + self.adler.to_bytes(4, "big")

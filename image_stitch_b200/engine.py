@@ -60,6 +60,7 @@ class JobPlan:
     headers: List[PngHeader]
     placements: List[TilePlacement]
     warnings: List[str] = field(default_factory=list)
+    device_deflate: bool = False  # PNG only: bands leave the device as deflate blocks
 
 
 _ctx_lock = threading.Lock()
@@ -207,7 +208,8 @@ class BandRunner:
     def __init__(self, plan: JobPlan, sources: Dict[int, TileSource], device: int, y0: int, y1: int):
         self.plan, self.y0, self.y1 = plan, y0, y1
         self.ctx = get_context(device)
-        kind = _native.OUT_JPEG_ENTROPY if plan.output_format == "jpeg" else _native.OUT_PNG_FILTERED
+        kind = _native.OUT_JPEG_ENTROPY if plan.output_format == "jpeg" else (
+            _native.OUT_PNG_DEFLATE if plan.device_deflate else _native.OUT_PNG_FILTERED)
         self.job = _native.Job(self.ctx, plan.canvas_w, plan.canvas_h, plan.out_bit_depth, kind, plan.alpha_blend,
                                plan.background, plan.jpeg_quality, band=(y0, y1))
         halo0 = max(0, y0 - 1)

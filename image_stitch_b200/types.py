@@ -101,6 +101,9 @@ class ConcatOptions:
     # additive (not in the reference): which CUDA devices run the row bands
     devices: Optional[Sequence[int]] = None
     band_rows: Optional[int] = None
+    # additive: DEFLATE the filtered rows on the device; the IDAT bytes then differ from the
+    # host's zlib output but inflate to the same rows
+    device_deflate: bool = False
 
     @staticmethod
     def coerce(options: Union["ConcatOptions", dict]) -> "ConcatOptions":
@@ -110,11 +113,13 @@ class ConcatOptions:
             known = {
                 "inputs", "layout", "decoder_options", "decoders", "output_format", "jpeg_quality",
                 "background_color", "enable_alpha_blending", "on_progress", "devices", "band_rows",
+                "device_deflate",
             }
             camel = {
                 "decoderOptions": "decoder_options", "outputFormat": "output_format",
                 "jpegQuality": "jpeg_quality", "backgroundColor": "background_color",
                 "enableAlphaBlending": "enable_alpha_blending", "onProgress": "on_progress",
+                "deviceDeflate": "device_deflate",
             }
             kw = {}
             for k, v in dict(options).items():

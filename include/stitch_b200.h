@@ -48,7 +48,10 @@ typedef enum stitch_status {
 typedef enum stitch_out_kind {
   STITCH_OUT_PNG_FILTERED = 0, /* rows of [filter byte + W*bpp]: filterScanline src/png-filter.ts:148-181 */
   STITCH_OUT_RAW_RGBA = 1,     /* composited rows W*bpp: generateRawScanlines src/image-concat-core.ts:691-831 */
-  STITCH_OUT_JPEG_ENTROPY = 2  /* entropy-coded MCU rows: StreamingJpegEncoder.encode_strip, src/jpeg-encoder.ts:155-166 */
+  STITCH_OUT_JPEG_ENTROPY = 2, /* entropy-coded MCU rows: StreamingJpegEncoder.encode_strip, src/jpeg-encoder.ts:155-166 */
+  STITCH_OUT_PNG_DEFLATE = 3   /* the filtered rows of kind 0, DEFLATE-compressed on the device: what
+                                  StreamingDeflator.push/flush emit (src/streaming-deflate.ts:130-185), as
+                                  byte-aligned non-final blocks; inflates to the same rows, bytes differ from pako's */
 } stitch_out_kind;
 
 typedef struct stitch_ctx stitch_ctx;
@@ -101,6 +104,17 @@ typedef struct stitch_timings {
  * byte-aligned run of complete entropy segments, each followed by its RSTm
  * marker (none after the image's last MCU row): bands are spliced by plain
  * concatenation in ascending row order, then EOI. */
+/* DEFLATE band result header (STITCH_OUT_PNG_DEFLATE), followed by n_bytes of complete, byte-aligned,
+ * non-final deflate blocks.  The host writes the zlib header (78 01), the bands in ascending row order, the
+ * final empty block (01 00 00 FF FF) and the big-endian Adler-32 of all raw rows, combining the per-band
+ * values with adler32_combine (RFC 1950). */
+typedef struct stitch_deflate_band_info {
+  uint64_t n_bytes;   /* compressed bytes that follow */
+  uint64_t n_raw;     /* raw bytes they inflate to: (y1-y0) * (1 + W*bpp) */
+  uint32_t adler;     /* Adler-32 of those raw bytes alone */
+  uint32_t reserved;
+} stitch_deflate_band_info;
+
 typedef struct stitch_jpeg_band_info {
   uint64_t n_bits;     /* 8 * payload bytes that follow this header (stuffing and RST markers included) */
   int32_t last_dc[3];  /* always 0: every restart segment starts from zero DC predictors */
@@ -158,6 +172,8 @@ int stitch_job_invalidate(stitch_job *job);
  *      RAW  (y1-y0) rows of W*bpp
  *      JPEG stitch_jpeg_band_info followed by the band's entropy bytes
  *           (y0 % 8 == 0; y1 % 8 == 0 or y1 == canvas_h)
+ *      DEFLATE stitch_deflate_band_info followed by the band's deflate blocks
+ *           (cap: at most (y1-y0)*(1+W*bpp) * 1.001 + 1 KiB)
  *  out == NULL: the result stays on the device (stitch_job_band_device).
  * The PNG predictor row for y0 > 0 is recomputed on the device (1-row halo).
  * With a host destination a PNG / RAW band is produced in chunks of about
