@@ -268,7 +268,7 @@ class Job:
         row = self.canvas_w * self.bpp + (1 if self.out_kind in (OUT_PNG_FILTERED, OUT_PNG_DEFLATE) else 0)
         if self.out_kind == OUT_PNG_DEFLATE:   # worst case: every 32 KiB block stored, 10 bytes of framing each
             raw = row * (y1 - y0)
-            return C.sizeof(DeflateBandInfo) + raw + (raw // 32768 + 1) * 10 + 64
+            return C.sizeof(DeflateBandInfo) + raw + (raw // 32768 + 1) * 10 + (raw // (1 << 20) + 2) * 16 + 64
         if self.out_kind == OUT_JPEG_ENTROPY:
             # worst case of baseline Huffman coding plus the band header
             mcus = ((self.canvas_w + 7) // 8) * ((y1 - y0 + 7) // 8)

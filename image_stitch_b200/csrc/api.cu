@@ -169,7 +169,8 @@ extern "C" void stitch_job_destroy(stitch_job *job) {
   dev_free(ctx, job->d_streams); dev_free(ctx, job->d_a7);
   dev_free(ctx, job->d_slow); dev_free(ctx, job->d_units); dev_free(ctx, job->d_uprog);
   dev_free(ctx, job->d_canvas); dev_free(ctx, job->d_out); dev_free(ctx, job->d_sync); dev_free(ctx, job->d_plans); dev_free(ctx, job->d_ctab);
-  dev_free(ctx, job->d_defl); dev_free(ctx, job->d_defl_scratch);
+  dev_free(ctx, job->d_defl); dev_free(ctx, job->d_defl_b); dev_free(ctx, job->d_defl_scratch);
+  for (auto &e : job->ev_defl) if (e) cudaEventDestroy(e);
   if (job->h_defl) cudaFreeHost(job->h_defl);
   for (auto &q : job->d_jpeg) dev_free(ctx, q);
   if (job->h_jpeg_totals) cudaFreeHost(job->h_jpeg_totals);
@@ -576,6 +577,15 @@ static int ensure_buffer(stitch_ctx *ctx, uint8_t **p, size_t *have, size_t need
 
 int stitch_ensure_buffer(stitch_ctx *ctx, uint8_t **p, size_t *have, size_t need) { return ensure_buffer(ctx, p, have, need); }
 
+// Adler-32 of A+B from adler32(A), adler32(B), len(B) (zlib's adler32_combine)
+static uint32_t adler32_combine(uint32_t adler1, uint32_t adler2, uint64_t len2) {
+  const uint64_t M = 65521;
+  const uint64_t a1 = adler1 & 0xffffu, b1 = adler1 >> 16, a2 = adler2 & 0xffffu, b2 = adler2 >> 16;
+  const uint64_t a = (a1 + a2 + M - 1) % M;
+  const uint64_t b = (b1 + b2 + (len2 % M) * ((a1 + M - 1) % M)) % M;
+  return (uint32_t)((b << 16) | a);
+}
+
 static uint32_t native_fmt(uint32_t out_bit_depth) { return out_bit_depth == 16 ? (uint32_t)FMT_RGBA16 : (uint32_t)FMT_RGBA8; }
 
 static void bg_words(const stitch_job_desc &d, uint32_t &lo, uint32_t &hi) {
@@ -746,39 +756,57 @@ extern "C" int stitch_job_run_band(stitch_job *job, uint32_t y0, uint32_t y1, ui
     // own stream while chunk k+1 is computed and while later tiles are still coming up (add_tile queued
     // them on the upload stream), so the bus is busy in both directions and the kernels hide behind it.
     uint32_t chunk = n_rows;
-    if (out && !deflate) {
+    if (out) {
       size_t chunk_bytes = (size_t)64 << 20;
       if (const char *e = getenv("STITCH_CHUNK_BYTES")) chunk_bytes = std::max<size_t>(1, strtoull(e, nullptr, 10));  // tuning / tests
       const size_t want = chunk_bytes / std::max<size_t>(host_row, 1);
       chunk = (uint32_t)std::min<size_t>(n_rows, std::max<size_t>(16, want / 16 * 16));
     }
     bool first = true;
+    uint32_t n_chunks = 0, z_adler = 1;
+    size_t z_total = 0;
     for (uint32_t a = y0; a < y1; a += chunk) {
       const uint32_t b = (uint32_t)std::min<uint64_t>((uint64_t)a + chunk, y1);
       uint8_t *d_rows = job->d_out + (size_t)(a - y0) * job->out_pitch;
       if ((rc = render_rows(job, a, b, d_rows, &launches, first ? ctx->ev[2] : nullptr))) return rc;
       first = false;
-      if (out && !deflate) {
+      if (deflate) {
+        // 8(f).1: the chunk leaves the device compressed.  Two device buffers take turns, so chunk k goes
+        // down the bus while chunk k+1 is rendered and compressed.
+        const uint32_t k = n_chunks++ & 1u;
+        uint8_t **zbuf = k ? &job->d_defl_b : &job->d_defl;
+        size_t *zcap = k ? &job->defl_b_bytes : &job->defl_bytes;
+        if (job->ev_defl[k]) CK(cudaStreamWaitEvent(ctx->stream, job->ev_defl[k], 0));  // its last download is over
+        if ((rc = ensure_buffer(ctx, zbuf, zcap, stitch_deflate_bound(host_row * (size_t)(b - a))))) return rc;
+        size_t zbytes = 0;
+        uint32_t adler = 1;
+        if ((rc = stitch_deflate_band(job, d_rows, b - a, host_row, *zbuf, &zbytes, &adler, &launches))) return rc;
+        z_adler = adler32_combine(z_adler, adler, (uint64_t)host_row * (b - a));
+        if (out) {
+          if (cap < sizeof(stitch_deflate_band_info) + z_total + zbytes)
+            return fail(ctx, STITCH_E_CAPACITY, "output buffer too small: need more than %zu bytes", sizeof(stitch_deflate_band_info) + z_total + zbytes);
+          CK(cudaMemcpyAsync(out + sizeof(stitch_deflate_band_info) + z_total, *zbuf, zbytes, cudaMemcpyDeviceToHost, ctx->down));
+          if (!job->ev_defl[k]) CK(cudaEventCreateWithFlags(&job->ev_defl[k], cudaEventDisableTiming));
+          CK(cudaEventRecord(job->ev_defl[k], ctx->down));
+        }
+        z_total += zbytes;
+      } else if (out) {
         CK(cudaEventRecord(ctx->ev_chunk, ctx->stream));
         CK(cudaStreamWaitEvent(ctx->down, ctx->ev_chunk, 0));
         CK(cudaMemcpy2DAsync(out + (size_t)(a - y0) * host_row, host_row, d_rows + job->out_lead, job->out_pitch, host_row,
                              b - a, cudaMemcpyDeviceToHost, ctx->down));
       }
     }
-    if (deflate) {  // 8(f).1: the band leaves the device compressed
-      size_t zbytes = 0;
-      uint32_t adler = 1;
-      if ((rc = stitch_deflate_band(job, n_rows, host_row, &zbytes, &adler, &launches))) return rc;
+    if (deflate) {
       CK(cudaEventRecord(ctx->ev[3], ctx->stream));
       if (out) {
-        const size_t need = sizeof(stitch_deflate_band_info) + zbytes;
-        if (cap < need) return fail(ctx, STITCH_E_CAPACITY, "output buffer too small: need %zu bytes", need);
+        CK(cudaEventRecord(ctx->ev_down, ctx->down));
+        CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_down, 0));
         stitch_deflate_band_info info;
         memset(&info, 0, sizeof info);
-        info.n_bytes = zbytes; info.n_raw = (uint64_t)host_row * n_rows; info.adler = adler;
+        info.n_bytes = z_total; info.n_raw = (uint64_t)host_row * n_rows; info.adler = z_adler;
         memcpy(out, &info, sizeof info);
-        CK(cudaMemcpyAsync(out + sizeof info, job->d_defl, zbytes, cudaMemcpyDeviceToHost, ctx->stream));
-        if (out_len) *out_len = need;
+        if (out_len) *out_len = sizeof info + z_total;
       }
     } else {
     CK(cudaEventRecord(ctx->ev[3], ctx->stream));

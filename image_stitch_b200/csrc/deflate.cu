@@ -324,19 +324,19 @@ __global__ void __launch_bounds__(DT) deflate_encode_kernel(const BandView v, co
 
 }  // namespace
 
-// Compresses the band that stitch_job_run_band just rendered into job->d_out (PNG layout).  The compressed
-// bytes land in job->d_defl; *out_bytes and *adler describe them.  Two small D2H reads.
-int stitch_deflate_band(stitch_job *job, uint32_t n_rows, size_t host_row, size_t *out_bytes, uint32_t *adler, uint32_t *launches) {
+// Compresses n_rows filtered rows that start at d_rows (row pitch job->out_pitch, filter byte at out_lead)
+// into d_dst.  *out_bytes and *adler describe the result.  Ends with one small D2H read and a stream sync:
+// the caller needs the size on the host to move the bytes on.
+int stitch_deflate_band(stitch_job *job, const uint8_t *d_rows, uint32_t n_rows, size_t host_row, uint8_t *d_dst,
+                        size_t *out_bytes, uint32_t *adler, uint32_t *launches) {
   stitch_ctx *ctx = job->ctx;
   int rc;
   BandView v;
-  v.base = job->d_out + job->out_lead; v.pitch = job->out_pitch; v.row_bytes = (uint32_t)host_row;
+  v.base = d_rows + job->out_lead; v.pitch = job->out_pitch; v.row_bytes = (uint32_t)host_row;
   v.total = (unsigned long long)host_row * n_rows;
   const uint32_t n_blocks = (uint32_t)((v.total + DB - 1) / DB);
   const size_t scratch = (size_t)n_blocks * (TAB * 4 + 4 + 8 + 8) + 64;
   if ((rc = stitch_ensure_buffer(ctx, &job->d_defl_scratch, &job->defl_scratch_bytes, scratch))) return rc;
-  const size_t worst = (size_t)v.total + (size_t)n_blocks * 10 + 64;  // every block stored
-  if ((rc = stitch_ensure_buffer(ctx, &job->d_defl, &job->defl_bytes, worst))) return rc;
   if (!job->h_defl) STITCH_CK(cudaHostAlloc((void **)&job->h_defl, 16, cudaHostAllocDefault));
   unsigned long long *offsets = reinterpret_cast<unsigned long long *>(job->d_defl_scratch);
   unsigned long long *result = offsets + n_blocks;
@@ -352,7 +352,7 @@ int stitch_deflate_band(stitch_job *job, uint32_t n_rows, size_t host_row, size_
   STITCH_CK(cudaGetLastError());
   deflate_scan_kernel<<<1, 1024, 0, ctx->stream>>>(sizes, adler_parts, n_blocks, v.total, offsets, result);
   STITCH_CK(cudaGetLastError());
-  deflate_encode_kernel<<<n_blocks, DT, sizeof(EncSmem), ctx->stream>>>(v, tabs, sizes, offsets, job->d_defl);
+  deflate_encode_kernel<<<n_blocks, DT, sizeof(EncSmem), ctx->stream>>>(v, tabs, sizes, offsets, d_dst);
   STITCH_CK(cudaGetLastError());
   STITCH_CK(cudaMemcpyAsync(job->h_defl, result, 16, cudaMemcpyDeviceToHost, ctx->stream));
   STITCH_CK(cudaStreamSynchronize(ctx->stream));
@@ -361,3 +361,6 @@ int stitch_deflate_band(stitch_job *job, uint32_t n_rows, size_t host_row, size_
   if (launches) *launches += 3;
   return STITCH_OK;
 }
+
+// worst case of stitch_deflate_band's output: every block stored
+size_t stitch_deflate_bound(size_t raw_bytes) { return raw_bytes + (raw_bytes / DB + 1) * 10 + 64; }

@@ -61,7 +61,9 @@ struct stitch_job {
   bool force_two_pass = false;
   // band buffers
   uint8_t *d_plans = nullptr; size_t plans_bytes = 0;  // fused kernel: per-unit plan records
-  uint8_t *d_defl = nullptr; size_t defl_bytes = 0;    // deflate: compressed band
+  uint8_t *d_defl = nullptr; size_t defl_bytes = 0;    // deflate: compressed band / chunk (two buffers, used in turn)
+  uint8_t *d_defl_b = nullptr; size_t defl_b_bytes = 0;
+  cudaEvent_t ev_defl[2] = {nullptr, nullptr};         // the download of buffer i has finished
   uint8_t *d_defl_scratch = nullptr; size_t defl_scratch_bytes = 0;
   unsigned long long *h_defl = nullptr;                // pinned: {bytes, adler}
   uint8_t *d_ctab = nullptr; size_t ctab_bytes = 0;    // canvas-as-one-tile tables: DevTile | bin_start[2] | bin_tiles[1]
@@ -94,6 +96,8 @@ int stitch_ensure_buffer(stitch_ctx *ctx, uint8_t **p, size_t *have, size_t need
 
 // jpeg.cu: kernel (d) over composited RGBA8 rows [y0,y1) held at `canvas` (row y0 first).  Leaves the
 // entropy-coded bytes in job->d_out and their count in *out_bytes (stream synchronised once inside).
-int stitch_deflate_band(stitch_job *job, uint32_t n_rows, size_t host_row, size_t *out_bytes, uint32_t *adler, uint32_t *launches);
+int stitch_deflate_band(stitch_job *job, const uint8_t *d_rows, uint32_t n_rows, size_t host_row, uint8_t *d_dst,
+                        size_t *out_bytes, uint32_t *adler, uint32_t *launches);
+size_t stitch_deflate_bound(size_t raw_bytes);
 int stitch_jpeg_encode_band(stitch_job *job, uint32_t y0, uint32_t y1, const uint8_t *canvas, size_t canvas_pitch,
                             size_t *out_bytes, uint32_t *launches);

@@ -111,3 +111,14 @@ def test_c2_band_ratio_and_rate(ctx, capsys):
     with capsys.disabled():
         print(f"\n[deflate] {len(rows) / 1e6:.1f} MB -> {len(z) / 1e6:.1f} MB (ratio {len(rows) / len(z):.2f}); "
               f"composite+filter+deflate {tm['compose_ms']:.3f} ms on the device")
+
+
+def test_chunked_download_of_deflate_bands(ctx, monkeypatch):
+    """Host destination: the band is rendered, compressed and downloaded chunk by chunk (two device buffers
+    taking turns); the chunks' blocks and Adler-32 values must join into one valid stream."""
+    rng = np.random.default_rng(31)
+    w, h = 600, 555
+    pix = synth.smooth_rgba8(rng, w, h, "uniform")
+    monkeypatch.setenv("STITCH_CHUNK_BYTES", "100000")   # ~41 rows per chunk -> 14 chunks
+    rows, z = _both(ctx, pix, w, h, [(0, 300), (300, h)])
+    assert zlib.decompress(z) == rows
