@@ -74,17 +74,29 @@ __device__ __forceinline__ uint4 tmem_ld4(uint32_t taddr) {
   return v;
 }
 
+// sat(|a| - |b|) on two lanes: 1 where |a| > |b|, else 0 (the operands are integers).  A comparison that
+// runs on the FMA pipe (HADD2.SAT) instead of the half-rate ALU pipe (HSET2), which is the one this kernel fills.
+__device__ __forceinline__ __half2 abs_gt_h2(__half2 a, __half2 b) {
+  uint32_t r;
+  asm("{ .reg .b32 ta, tb;\n\t"
+      "abs.f16x2 ta, %1;\n\t"
+      "abs.f16x2 tb, %2;\n\t"
+      "sub.sat.f16x2 %0, ta, tb; }" : "=r"(r) : "r"(*reinterpret_cast<uint32_t *>(&a)), "r"(*reinterpret_cast<uint32_t *>(&b)));
+  return *reinterpret_cast<__half2 *>(&r);
+}
+
 // Paeth-filtered bytes of two lanes: low byte of (x - paeth(a,b,c) + 1280) in each half.
+// png-filter.ts:16-25: a if pa <= pb && pa <= pc, else b if pb <= pc, else c.
 __device__ __forceinline__ __half2 paeth_resid_h2(__half2 x, __half2 a, __half2 b, __half2 c) {
   const __half2 d1 = __hsub2(b, c);   // p - a
   const __half2 d2 = __hsub2(a, c);   // p - b
   const __half2 s = __hadd2(d1, d2);  // p - c
-  const __half2 pb = __habs2(d2), pc = __habs2(s);
-  const __half2 t1 = __hle2(pb, pc);                        // pb <= pc
-  const __half2 t2 = __hle2(__habs2(d1), __hmin2(pb, pc));  // pa <= pb && pa <= pc
-  const __half2 pk1 = __hfma2(t1, d1, c);                   // t1 ? b : c
-  const __half2 w = __hadd2(__hsub2(x, pk1), __float2half2_rn(1280.f));
-  return __hfma2(t2, __hsub2(pk1, a), w);                   // x - (t2 ? a : pk1) + 1280, exact in [1025,1535]
+  const __half2 u = abs_gt_h2(d2, s);                       // pb > pc: c beats b
+  const __half2 m = __hmin2(__habs2(d2), __habs2(s));
+  const __half2 v = abs_gt_h2(d1, m);                       // pa > min(pb, pc): not a
+  const __half2 pk1 = __hfma2(__hneg2(u), d1, b);           // u ? c : b
+  const __half2 sel = __hfma2(v, __hsub2(pk1, a), a);       // v ? pk1 : a
+  return __hadd2(__hsub2(x, sel), __float2half2_rn(1280.f));  // exact, in [1025, 1535]
 }
 
 // ---- generic compositor: one 16-byte quad of canvas row y ------------------------
@@ -418,52 +430,58 @@ __device__ __forceinline__ uint32_t unit_wait(const FusedParams &p, const UnitRe
   return my_ft;
 }
 
+// Winners of rows 0..FU_R-1 (lane r holds row r's), 3 bits each, as a warp-uniform word.
+__device__ __forceinline__ uint32_t pack_winners(const uint32_t my_ft, const uint32_t lane) {
+  return __reduce_or_sync(0xffffffffu, lane < (uint32_t)FU_R ? my_ft << (3u * lane) : 0u);
+}
+
 // ---- phase B, part 2: rows [r0, r1) of the unit: the winner's bytes, one 128-bit store per lane per row ----
+// ftpack: the winners of the unit's rows, 3 bits each, the same in every lane (so every branch is uniform).
 template <int BPW>
 __device__ __forceinline__ void unit_emit(const FusedParams &p, const UnitRef &ref, const uint32_t *stash,
-                                          const uint32_t pf_taddr, const uint32_t lane, const uint32_t my_ft, const int r0,
-                                          const int r1) {
+                                          const uint32_t pf_taddr, const uint32_t lane, const uint32_t my_ft,
+                                          const uint32_t ftpack, const int r0, const int r1) {
   const uint32_t *raw = stash, *lcs = stash + FU_RAW_WORDS;
   const int wmax = (int)p.canvas_w * BPW;
   const int qw = (int)ref.seg * FU_SW + 4 * (int)lane;
   uint8_t *orow = p.out + (size_t)(ref.ya + r0 - (int)p.y_begin) * p.out_pitch + p.lead;
-  const uint32_t *cur_row = raw + (r0 + 1) * FU_SW + 4 * lane, *lcs_row = lcs + 2 * (r0 + 1);
-  uint32_t pf_row = pf_taddr + 4u * (uint32_t)r0;
-  const bool whole = qw + 4 <= wmax;
-  for (int r = r0; r < r1; r++, orow += p.out_pitch, cur_row += FU_SW, pf_row += 4, lcs_row += 2) {
-    const uint32_t ft = __shfl_sync(0xffffffffu, my_ft, r);
-    if (ref.seg == 0u && lane == 0u) orow[0] = (uint8_t)ft;
+  // the filter-type bytes of the rows: lane r holds row r's
+  if (ref.seg == 0u && (int)lane >= r0 && (int)lane < r1) orow[(size_t)((int)lane - r0) * p.out_pitch] = (uint8_t)my_ft;
+  uint8_t *odat = orow + 1 + 4 * (size_t)qw;
+  const uint32_t *cur_row = raw + (r0 + 1) * FU_SW + 4 * lane;
+  const bool full = ((int)ref.seg + 1) * FU_SW <= wmax;  // every lane stores a whole quad
+  for (int r = r0; r < r1; r++, odat += p.out_pitch, cur_row += FU_SW) {
+    const uint32_t ft = (ftpack >> (3 * r)) & 7u;
     uint4 o;
     if (ft == 4u) {
-      o = tmem_ld4(pf_row);
+      o = tmem_ld4(pf_taddr + 4u * (uint32_t)r);
     } else {
-      const uint4 cur = *reinterpret_cast<const uint4 *>(cur_row);
-      o = cur;
-      if (ft == 2u) {
-        const uint4 upq = *reinterpret_cast<const uint4 *>(cur_row - FU_SW);
-        o = make_uint4(sub4(cur.x, upq.x), sub4(cur.y, upq.y), sub4(cur.z, upq.z), sub4(cur.w, upq.w));
-      } else if (ft != 0u) {
-        uint32_t c0 = BPW == 2 ? __shfl_up_sync(0xffffffffu, cur.z, 1) : 0u;
-        uint32_t c1 = __shfl_up_sync(0xffffffffu, cur.w, 1);
-        if (lane == 0u) { c0 = lcs_row[0]; c1 = lcs_row[1]; }
-        const uint32_t a0 = BPW == 1 ? c1 : c0, a1 = BPW == 1 ? cur.x : c1;
-        const uint32_t a2 = BPW == 1 ? cur.y : cur.x, a3 = BPW == 1 ? cur.z : cur.y;
-        if (ft == 1u) {
-          o = make_uint4(sub4(cur.x, a0), sub4(cur.y, a1), sub4(cur.z, a2), sub4(cur.w, a3));
+      o = *reinterpret_cast<const uint4 *>(cur_row);
+      if (ft != 0u) {
+        uint4 pr;  // the predictor bytes
+        if (ft == 2u) {
+          pr = *reinterpret_cast<const uint4 *>(cur_row - FU_SW);
         } else {
-          const uint4 upq = *reinterpret_cast<const uint4 *>(cur_row - FU_SW);
-          o = make_uint4(sub4(cur.x, avg4(a0, upq.x)), sub4(cur.y, avg4(a1, upq.y)), sub4(cur.z, avg4(a2, upq.z)),
-                         sub4(cur.w, avg4(a3, upq.w)));
+          uint32_t c0 = BPW == 2 ? __shfl_up_sync(0xffffffffu, o.z, 1) : 0u;
+          uint32_t c1 = __shfl_up_sync(0xffffffffu, o.w, 1);
+          if (lane == 0u) { c0 = lcs[2 * (r + 1)]; c1 = lcs[2 * (r + 1) + 1]; }
+          pr = BPW == 1 ? make_uint4(c1, o.x, o.y, o.z) : make_uint4(c0, c1, o.x, o.y);
+          if (ft == 3u) {
+            const uint4 upq = *reinterpret_cast<const uint4 *>(cur_row - FU_SW);
+            pr = make_uint4(avg4(pr.x, upq.x), avg4(pr.y, upq.y), avg4(pr.z, upq.z), avg4(pr.w, upq.w));
+          }
         }
+        o = make_uint4(sub4(o.x, pr.x), sub4(o.y, pr.y), sub4(o.z, pr.z), sub4(o.w, pr.w));
       }
     }
-    uint32_t *odat = reinterpret_cast<uint32_t *>(orow + 1) + qw;
-    if (whole) {
+    if (full) {
       *reinterpret_cast<uint4 *>(odat) = o;
     } else if (qw < wmax) {
-      odat[0] = o.x;
-      if (qw + 1 < wmax) odat[1] = o.y;
-      if (qw + 2 < wmax) odat[2] = o.z;
+      uint32_t *od = reinterpret_cast<uint32_t *>(odat);
+      od[0] = o.x;
+      if (qw + 1 < wmax) od[1] = o.y;
+      if (qw + 2 < wmax) od[2] = o.z;
+      if (qw + 3 < wmax) od[3] = o.w;
     }
   }
 }
@@ -506,7 +524,10 @@ __global__ void __launch_bounds__(FU_WARPS * 32, 1) fused_kernel(const FusedPara
   const uint32_t n_warps = gridDim.x * FU_WARPS;
   uint32_t lmask[5];  // lane f keeps candidate f's row sum
 #pragma unroll
-  for (int f = 0; f < 5; f++) lmask[f] = lane == (uint32_t)f ? 0xffffffffu : 0u;
+  for (int f = 0; f < 5; f++) {
+    lmask[f] = lane == (uint32_t)f ? 0xffffffffu : 0u;
+    asm volatile("" : "+r"(lmask[f]));  // keep them as registers: one LOP3 per sum instead of ISETP + SEL + move
+  }
 
   uint32_t u = blockIdx.x * FU_WARPS + warp;  // first unit: the warp's own index; tickets continue from n_warps
   if (u < n_units) {
@@ -519,15 +540,16 @@ __global__ void __launch_bounds__(FU_WARPS * 32, 1) fused_kernel(const FusedPara
       unit_sweep<BPW>(p, plan, cur_stash, cur_pf, lane, lmask);
       uint32_t ft = 0u;
       if (have_prev) ft = unit_wait(p, prev, lane);
+      const uint32_t ftpack = pack_winners(ft, lane);
       uint32_t t = 0u;
       if (lane == 0u) t = atomicAdd(p.ticket, 1u);
       const int half = prev.nrows >> 1;
-      if (have_prev) unit_emit<BPW>(p, prev, prev_stash, prev_pf, lane, ft, 0, half);
+      if (have_prev) unit_emit<BPW>(p, prev, prev_stash, prev_pf, lane, ft, ftpack, 0, half);
       u = n_warps + __shfl_sync(0xffffffffu, t, 0);
       const bool more = u < n_units;
       PlanRaw raw_next;
       if (more) raw_next = plan_fetch(p, u);
-      if (have_prev) unit_emit<BPW>(p, prev, prev_stash, prev_pf, lane, ft, half, prev.nrows);
+      if (have_prev) unit_emit<BPW>(p, prev, prev_stash, prev_pf, lane, ft, ftpack, half, prev.nrows);
       __syncwarp();  // prev_stash is free again
       prev.seg = plan.seg; prev.ya = plan.ya; prev.nrows = plan.nrows;
       have_prev = true;
@@ -538,7 +560,7 @@ __global__ void __launch_bounds__(FU_WARPS * 32, 1) fused_kernel(const FusedPara
       unit_load<BPW>(p, plan, cur_stash, lane);
     }
     const uint32_t ft = unit_wait(p, prev, lane);
-    unit_emit<BPW>(p, prev, prev_stash, prev_pf, lane, ft, 0, prev.nrows);
+    unit_emit<BPW>(p, prev, prev_stash, prev_pf, lane, ft, pack_winners(ft, lane), 0, prev.nrows);
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
