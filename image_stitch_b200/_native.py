@@ -64,7 +64,7 @@ class Timings(C.Structure):
 
 
 class DeflateBandInfo(C.Structure):
-    _fields_ = [("n_bytes", C.c_uint64), ("n_raw", C.c_uint64), ("adler", C.c_uint32), ("reserved", C.c_uint32)]
+    _fields_ = [("n_bytes", C.c_uint64), ("n_raw", C.c_uint64), ("adler", C.c_uint32), ("crc32", C.c_uint32)]
 
 
 class JpegBandInfo(C.Structure):

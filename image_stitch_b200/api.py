@@ -100,12 +100,14 @@ class StreamingConcatenator:
         scanline_size = plan.canvas_w * bpp + 1
         if plan.device_deflate:
             # the device already produced deflate blocks: one IDAT per band, zlib framing around them
-            from .deflate_container import ZLIB_HEADER, DeflateBandSplicer
+            # (the chunk CRC comes from the device's CRC-32 of the band: no host pass over the bytes)
+            from .deflate_container import ZLIB_HEADER, DeflateBandSplicer, idat_chunk
             splicer = DeflateBandSplicer()
             head = ZLIB_HEADER
             for y0, y1, data, tm in engine.run_plan(plan, sources, self.options.devices, self.options.band_rows, on_band):
                 self.last_timings.append(tm)
-                yield serialize_chunk(create_chunk("IDAT", head + splicer.push(data)))
+                body = splicer.push(data)
+                yield idat_chunk(head, body, splicer.last_crc32)
                 head = b""
             yield serialize_chunk(create_chunk("IDAT", head + splicer.finish()))
             yield serialize_chunk(create_iend())

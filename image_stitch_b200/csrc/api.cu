@@ -763,7 +763,7 @@ extern "C" int stitch_job_run_band(stitch_job *job, uint32_t y0, uint32_t y1, ui
       chunk = (uint32_t)std::min<size_t>(n_rows, std::max<size_t>(16, want / 16 * 16));
     }
     bool first = true;
-    uint32_t n_chunks = 0, z_adler = 1;
+    uint32_t n_chunks = 0, z_adler = 1, z_crc_raw = 0;
     size_t z_total = 0;
     for (uint32_t a = y0; a < y1; a += chunk) {
       const uint32_t b = (uint32_t)std::min<uint64_t>((uint64_t)a + chunk, y1);
@@ -779,9 +779,10 @@ extern "C" int stitch_job_run_band(stitch_job *job, uint32_t y0, uint32_t y1, ui
         if (job->ev_defl[k]) CK(cudaStreamWaitEvent(ctx->stream, job->ev_defl[k], 0));  // its last download is over
         if ((rc = ensure_buffer(ctx, zbuf, zcap, stitch_deflate_bound(host_row * (size_t)(b - a))))) return rc;
         size_t zbytes = 0;
-        uint32_t adler = 1;
-        if ((rc = stitch_deflate_band(job, d_rows, b - a, host_row, *zbuf, &zbytes, &adler, &launches))) return rc;
+        uint32_t adler = 1, crc_raw = 0;
+        if ((rc = stitch_deflate_band(job, d_rows, b - a, host_row, *zbuf, &zbytes, &adler, &crc_raw, &launches))) return rc;
         z_adler = adler32_combine(z_adler, adler, (uint64_t)host_row * (b - a));
+        z_crc_raw = stitch_crc_raw_concat(z_crc_raw, crc_raw, zbytes);
         if (out) {
           if (cap < sizeof(stitch_deflate_band_info) + z_total + zbytes)
             return fail(ctx, STITCH_E_CAPACITY, "output buffer too small: need more than %zu bytes", sizeof(stitch_deflate_band_info) + z_total + zbytes);
@@ -805,6 +806,7 @@ extern "C" int stitch_job_run_band(stitch_job *job, uint32_t y0, uint32_t y1, ui
         stitch_deflate_band_info info;
         memset(&info, 0, sizeof info);
         info.n_bytes = z_total; info.n_raw = (uint64_t)host_row * n_rows; info.adler = z_adler;
+        info.crc32 = stitch_crc_finish(z_crc_raw, z_total);
         memcpy(out, &info, sizeof info);
         if (out_len) *out_len = sizeof info + z_total;
       }

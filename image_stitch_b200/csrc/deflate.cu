@@ -228,6 +228,8 @@ __global__ void __launch_bounds__(1024) deflate_scan_kernel(const uint32_t *size
     b = (total % ADLER_M + b) % ADLER_M;
     result[0] = s_base;
     result[1] = (b << 16) | a;
+    result[2] = 0;  // CRC-32 remainder, accumulated by crc32_kernel
+    result[3] = 0;
   }
 }
 
@@ -322,25 +324,128 @@ __global__ void __launch_bounds__(DT) deflate_encode_kernel(const BandView v, co
   for (uint32_t i = t; i < size; i += DT) out[i] = ob[i];
 }
 
+
+// ---- CRC-32 of the compressed bytes (the IDAT chunk's check value, src/png-writer.ts:12-30, src/utils.ts:18-24) ----
+// The register update is linear over GF(2): state' = state * x^(8 len) + R(M), with R(M) the remainder computed
+// from a zero state.  So every 128-byte slice gets its own R by table lookups, a CTA folds its 256 slices in a
+// tree (multiply the left half by x^(8 * its distance to the end), add), one thread moves the CTA's value to
+// the end of the buffer the same way and XORs it into the result.  Bits are reflected as in zlib: bit 31 is
+// x^0, multiplying by x is a right shift with the polynomial folded in.
+constexpr uint32_t CRC_POLY = 0xedb88320u;
+constexpr int CRC_SLICE = 128;               // bytes per thread
+constexpr int CRC_CTA = DT * CRC_SLICE;      // 32 KiB per CTA
+constexpr int CRC_POWS = 48;                 // x^(8 * 2^j), j < 48
+
+struct CrcTables {
+  uint32_t t[4][256];       // slicing-by-4
+  uint32_t pow8[CRC_POWS];  // x^(8 * 2^j) mod P
+};
+__device__ CrcTables g_crc;
+
+__host__ __device__ inline uint32_t crc_mulmod(uint32_t a, uint32_t b) {
+  uint32_t p = 0;
+  for (int j = 0; j < 32; j++) {  // a's coefficient of x^j sits in bit 31 - j
+    if ((a >> (31 - j)) & 1u) p ^= b;
+    b = (b >> 1) ^ ((b & 1u) ? CRC_POLY : 0u);  // b * x
+  }
+  return p;
+}
+// x^(8 n) mod P from the table of x^(8 * 2^j)
+__host__ __device__ inline uint32_t crc_xpow8(const uint32_t *pow8, unsigned long long n) {
+  uint32_t p = 0x80000000u;  // 1
+  for (int j = 0; n != 0 && j < CRC_POWS; j++, n >>= 1)
+    if (n & 1ull) p = crc_mulmod(p, pow8[j]);
+  return p;
+}
+
+// result[0] = number of bytes (written by the scan kernel), result[2] ^= R(dst[0 .. n))
+__global__ void __launch_bounds__(DT) crc32_kernel(const uint8_t *dst, unsigned long long *result) {
+  __shared__ uint32_t tab[4][256];
+  __shared__ uint32_t vals[DT];
+  const unsigned long long n = result[0];
+  const unsigned long long c0 = (unsigned long long)blockIdx.x * CRC_CTA;
+  if (c0 >= n) return;
+  const uint32_t t = threadIdx.x;
+  for (uint32_t i = t; i < 1024u; i += DT) (&tab[0][0])[i] = (&g_crc.t[0][0])[i];
+  __syncthreads();
+  const unsigned long long avail = n - c0;
+  const bool full = avail >= (unsigned long long)CRC_CTA;
+  uint32_t c = 0u;
+  if (full) {
+    const uint4 *q = reinterpret_cast<const uint4 *>(dst + c0 + (size_t)t * CRC_SLICE);
+#pragma unroll
+    for (int k = 0; k < CRC_SLICE / 16; k++) {
+      const uint4 w = q[k];
+      const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+      for (int i = 0; i < 4; i++) {
+        c ^= ww[i];
+        c = tab[3][c & 0xffu] ^ tab[2][(c >> 8) & 0xffu] ^ tab[1][(c >> 16) & 0xffu] ^ tab[0][c >> 24];
+      }
+    }
+  } else {
+    // the tail: right-aligned in the CTA's window (leading zeros leave a zero state unchanged), byte by byte
+    const long long first = (long long)t * CRC_SLICE - ((long long)CRC_CTA - (long long)avail);
+    for (int k = 0; k < CRC_SLICE; k++) {
+      const long long o = first + k;
+      if (o >= 0) c = tab[0][(c ^ dst[c0 + (unsigned long long)o]) & 0xffu] ^ (c >> 8);
+    }
+  }
+  vals[t] = c;
+  __syncthreads();
+#pragma unroll 1
+  for (int k = 0; k < 8; k++) {  // slices 2^k apart: the left one is 128 * 2^k bytes further from the end
+    const uint32_t stride = 1u << k;
+    if ((t & (2u * stride - 1u)) == 0u) vals[t] = crc_mulmod(vals[t], g_crc.pow8[7 + k]) ^ vals[t + stride];
+    __syncthreads();
+  }
+  if (t == 0u) {
+    const unsigned long long after = full ? n - c0 - (unsigned long long)CRC_CTA : 0ull;
+    const uint32_t v = crc_mulmod(vals[0], crc_xpow8(g_crc.pow8, after));
+    atomicXor(reinterpret_cast<unsigned int *>(result + 2), v);
+  }
+}
+
+CrcTables g_crc_host;
+bool g_crc_ready = false;
+
+void crc_tables_init() {
+  CrcTables &h = g_crc_host;
+  for (uint32_t b = 0; b < 256; b++) {
+    uint32_t c = b;
+    for (int k = 0; k < 8; k++) c = (c >> 1) ^ ((c & 1u) ? CRC_POLY : 0u);
+    h.t[0][b] = c;
+  }
+  for (uint32_t b = 0; b < 256; b++)
+    for (int k = 1; k < 4; k++) h.t[k][b] = h.t[0][h.t[k - 1][b] & 0xffu] ^ (h.t[k - 1][b] >> 8);
+  uint32_t p = 0x80000000u >> 8;  // x^8
+  for (int j = 0; j < CRC_POWS; j++) { h.pow8[j] = p; p = crc_mulmod(p, p); }
+}
+
 }  // namespace
 
 // Compresses n_rows filtered rows that start at d_rows (row pitch job->out_pitch, filter byte at out_lead)
 // into d_dst.  *out_bytes and *adler describe the result.  Ends with one small D2H read and a stream sync:
 // the caller needs the size on the host to move the bytes on.
 int stitch_deflate_band(stitch_job *job, const uint8_t *d_rows, uint32_t n_rows, size_t host_row, uint8_t *d_dst,
-                        size_t *out_bytes, uint32_t *adler, uint32_t *launches) {
+                        size_t *out_bytes, uint32_t *adler, uint32_t *crc_raw, uint32_t *launches) {
   stitch_ctx *ctx = job->ctx;
   int rc;
   BandView v;
   v.base = d_rows + job->out_lead; v.pitch = job->out_pitch; v.row_bytes = (uint32_t)host_row;
   v.total = (unsigned long long)host_row * n_rows;
   const uint32_t n_blocks = (uint32_t)((v.total + DB - 1) / DB);
-  const size_t scratch = (size_t)n_blocks * (TAB * 4 + 4 + 8 + 8) + 64;
+  const size_t scratch = (size_t)n_blocks * (TAB * 4 + 4 + 8 + 8) + 96;
+  if (!g_crc_ready) {
+    crc_tables_init();
+    STITCH_CK(cudaMemcpyToSymbol(g_crc, &g_crc_host, sizeof(CrcTables)));
+    g_crc_ready = true;
+  }
   if ((rc = stitch_ensure_buffer(ctx, &job->d_defl_scratch, &job->defl_scratch_bytes, scratch))) return rc;
-  if (!job->h_defl) STITCH_CK(cudaHostAlloc((void **)&job->h_defl, 16, cudaHostAllocDefault));
+  if (!job->h_defl) STITCH_CK(cudaHostAlloc((void **)&job->h_defl, 32, cudaHostAllocDefault));
   unsigned long long *offsets = reinterpret_cast<unsigned long long *>(job->d_defl_scratch);
-  unsigned long long *result = offsets + n_blocks;
-  uint32_t *adler_parts = reinterpret_cast<uint32_t *>(result + 2);
+  unsigned long long *result = offsets + n_blocks;  // [0] bytes, [1] adler, [2] crc remainder, [3] spare
+  uint32_t *adler_parts = reinterpret_cast<uint32_t *>(result + 4);
   uint32_t *sizes = adler_parts + 2 * (size_t)n_blocks;
   uint32_t *tabs = sizes + n_blocks;
   static bool attr_set = false;
@@ -354,12 +459,27 @@ int stitch_deflate_band(stitch_job *job, const uint8_t *d_rows, uint32_t n_rows,
   STITCH_CK(cudaGetLastError());
   deflate_encode_kernel<<<n_blocks, DT, sizeof(EncSmem), ctx->stream>>>(v, tabs, sizes, offsets, d_dst);
   STITCH_CK(cudaGetLastError());
-  STITCH_CK(cudaMemcpyAsync(job->h_defl, result, 16, cudaMemcpyDeviceToHost, ctx->stream));
+  // CRC-32 remainder of the compressed bytes (they are still in L2)
+  const size_t bound = stitch_deflate_bound((size_t)v.total);
+  crc32_kernel<<<(unsigned)((bound + CRC_CTA - 1) / CRC_CTA), DT, 0, ctx->stream>>>(d_dst, result);
+  STITCH_CK(cudaGetLastError());
+  STITCH_CK(cudaMemcpyAsync(job->h_defl, result, 24, cudaMemcpyDeviceToHost, ctx->stream));
   STITCH_CK(cudaStreamSynchronize(ctx->stream));
   *out_bytes = (size_t)job->h_defl[0];
   *adler = (uint32_t)job->h_defl[1];
-  if (launches) *launches += 3;
+  *crc_raw = (uint32_t)job->h_defl[2];
+  if (launches) *launches += 4;
   return STITCH_OK;
+}
+
+// R(A || B) from R(A), R(B) and len(B); and the standard CRC-32 (zlib.crc32) of n bytes from their remainder R.
+uint32_t stitch_crc_raw_concat(uint32_t ra, uint32_t rb, uint64_t len_b) {
+  if (!g_crc_ready) { crc_tables_init(); }
+  return crc_mulmod(ra, crc_xpow8(g_crc_host.pow8, len_b)) ^ rb;
+}
+uint32_t stitch_crc_finish(uint32_t raw, uint64_t n) {
+  if (!g_crc_ready) { crc_tables_init(); }
+  return raw ^ crc_mulmod(0xffffffffu, crc_xpow8(g_crc_host.pow8, n)) ^ 0xffffffffu;
 }
 
 // worst case of stitch_deflate_band's output: every block stored

@@ -96,8 +96,12 @@ int stitch_ensure_buffer(stitch_ctx *ctx, uint8_t **p, size_t *have, size_t need
 
 // jpeg.cu: kernel (d) over composited RGBA8 rows [y0,y1) held at `canvas` (row y0 first).  Leaves the
 // entropy-coded bytes in job->d_out and their count in *out_bytes (stream synchronised once inside).
+// deflate.cu: filtered rows -> deflate blocks at d_dst; *crc_raw is the CRC-32 remainder of those bytes from a zero
+// register (chunks concatenate with stitch_crc_raw_concat, stitch_crc_finish turns the total into zlib's crc32)
 int stitch_deflate_band(stitch_job *job, const uint8_t *d_rows, uint32_t n_rows, size_t host_row, uint8_t *d_dst,
-                        size_t *out_bytes, uint32_t *adler, uint32_t *launches);
+                        size_t *out_bytes, uint32_t *adler, uint32_t *crc_raw, uint32_t *launches);
 size_t stitch_deflate_bound(size_t raw_bytes);
+uint32_t stitch_crc_raw_concat(uint32_t ra, uint32_t rb, uint64_t len_b);
+uint32_t stitch_crc_finish(uint32_t raw, uint64_t n);
 int stitch_jpeg_encode_band(stitch_job *job, uint32_t y0, uint32_t y1, const uint8_t *canvas, size_t canvas_pitch,
                             size_t *out_bytes, uint32_t *launches);

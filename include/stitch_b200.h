@@ -107,12 +107,15 @@ typedef struct stitch_timings {
 /* DEFLATE band result header (STITCH_OUT_PNG_DEFLATE), followed by n_bytes of complete, byte-aligned,
  * non-final deflate blocks.  The host writes the zlib header (78 01), the bands in ascending row order, the
  * final empty block (01 00 00 FF FF) and the big-endian Adler-32 of all raw rows, combining the per-band
- * values with adler32_combine (RFC 1950). */
+ * values with adler32_combine (RFC 1950).  crc32 is the CRC-32 (zlib's crc32) of the n_bytes compressed bytes,
+ * computed on the device, so that the IDAT chunk's check value (src/png-writer.ts:12-30, src/utils.ts:18-24:
+ * CRC over the chunk type and data) is crc32_combine(crc32("IDAT" + prefix), crc32, n_bytes) without a host
+ * pass over the data. */
 typedef struct stitch_deflate_band_info {
   uint64_t n_bytes;   /* compressed bytes that follow */
   uint64_t n_raw;     /* raw bytes they inflate to: (y1-y0) * (1 + W*bpp) */
   uint32_t adler;     /* Adler-32 of those raw bytes alone */
-  uint32_t reserved;
+  uint32_t crc32;     /* CRC-32 of the n_bytes compressed bytes alone */
 } stitch_deflate_band_info;
 
 typedef struct stitch_jpeg_band_info {

@@ -28,7 +28,10 @@ def _both(ctx, pix, w, h, bands, out_bd=8):
         job.add_tile(pix.reshape(-1), width=w, height=h, bit_depth=out_bd, color_type=6, filtered=0)
         for a, b in bands:
             data, _ = job.run_band(a, b)
-            z += sp.push(data)
+            body = sp.push(data)
+            # the device's CRC-32 of the band's compressed bytes is what zlib computes over them on the host
+            assert sp.last_crc32 == zlib.crc32(body), (a, b, len(body))
+            z += body
     z += sp.finish()
     assert sp.raw_bytes == len(rows)
     return rows, z
@@ -105,7 +108,9 @@ def test_c2_band_ratio_and_rate(ctx, capsys):
         job.run_band(0, tile)
         data, tm = job.run_band(0, tile)
     sp = DeflateBandSplicer()
-    z = ZLIB_HEADER + sp.push(data) + sp.finish()
+    body = sp.push(data)
+    assert sp.last_crc32 == zlib.crc32(body)   # ~35 MB: several hundred CTAs of the CRC kernel and its tail
+    z = ZLIB_HEADER + body + sp.finish()
     rows = zlib.decompress(z)
     assert len(rows) == tile * (tile * 16 * 4 + 1)
     with capsys.disabled():
