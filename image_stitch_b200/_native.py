@@ -13,8 +13,8 @@ from typing import Optional
 _LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libstitch_b200.so")
 
 STITCH_OK = 0
-E_INVALID, E_CUDA, E_NOMEM, E_FILTER, E_COLOR, E_TRUNCATED, E_STATE, E_CAPACITY, E_NODEVICE = (
-    -1, -2, -3, -4, -5, -6, -7, -8, -10)
+E_INVALID, E_CUDA, E_NOMEM, E_FILTER, E_COLOR, E_TRUNCATED, E_STATE, E_CAPACITY, E_INFLATE, E_NODEVICE = (
+    -1, -2, -3, -4, -5, -6, -7, -8, -9, -10)
 OUT_PNG_FILTERED, OUT_RAW_RGBA, OUT_JPEG_ENTROPY, OUT_PNG_DEFLATE = 0, 1, 2, 3
 
 EXPORTS = [
@@ -22,6 +22,7 @@ EXPORTS = [
     "stitch_last_error", "stitch_job_create", "stitch_job_destroy", "stitch_job_add_tile",
     "stitch_job_add_tile_device", "stitch_job_decode", "stitch_job_invalidate", "stitch_job_run_band", "stitch_job_band_device",
     "stitch_job_status", "stitch_decode_image", "stitch_filter_rows", "stitch_jpeg_header",
+    "stitch_job_inflate", "stitch_inflate",
 ]
 
 
@@ -105,6 +106,8 @@ def load() -> C.CDLL:
     lib.stitch_decode_image.argtypes = [vp, C.POINTER(TileDesc), vp, sz, vp, sz, C.POINTER(sz)]
     lib.stitch_filter_rows.argtypes = [vp, vp, vp, C.c_uint32, sz, C.c_uint32, vp, sz]
     lib.stitch_jpeg_header.argtypes = [C.c_uint32, C.c_uint32, C.c_uint32, vp, sz, C.POINTER(sz)]
+    lib.stitch_job_inflate.argtypes = [vp, C.c_int, C.POINTER(Timings)]
+    lib.stitch_inflate.argtypes = [vp, vp, sz, vp, sz, C.POINTER(sz)]
     for name in EXPORTS:  # every symbol include/stitch_b200.h declares must be exported
         getattr(lib, name)
     _lib = lib
@@ -187,6 +190,16 @@ class Context:
         self.check(rc)
         return out[: n.value]
 
+    def inflate(self, zdata, capacity: int):
+        """Inflate alone: one zlib stream -> at most `capacity` bytes (numpy uint8)."""
+        import numpy as np
+        zdata = bytes(zdata) if isinstance(zdata, memoryview) else zdata
+        out = np.empty(max(1, capacity), dtype=np.uint8)
+        n = C.c_size_t()
+        rc = self.lib.stitch_inflate(self.handle, _addr(zdata), len(zdata), _addr(out), capacity, C.byref(n))
+        self.check(rc)
+        return out[: n.value]
+
     def filter_rows(self, rows, prev_row, n_rows, row_bytes, bpp):
         """Kernel (c) alone.  Returns n_rows*(1+row_bytes) bytes."""
         import numpy as np
@@ -258,6 +271,12 @@ class Job:
     def decode(self, force: bool = False) -> dict:
         t = Timings()
         self.ctx.check(self.lib.stitch_job_decode(self.handle, 1 if force else 0, C.byref(t)))
+        return t.as_dict()
+
+    def inflate(self, force: bool = False) -> dict:
+        """Inflates the tiles that were added as zlib streams (filtered=2); timings of that step alone."""
+        t = Timings()
+        self.ctx.check(self.lib.stitch_job_inflate(self.handle, 1 if force else 0, C.byref(t)))
         return t.as_dict()
 
     def invalidate(self) -> None:

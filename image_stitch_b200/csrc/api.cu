@@ -156,8 +156,9 @@ static void free_tile(stitch_ctx *ctx, TileRec &t) {
   }
   if (t.d_pix && t.d_pix != t.d_src) dev_free(ctx, t.d_pix);
   if (t.d_src && !t.src_external) dev_free(ctx, t.d_src);
+  if (t.d_z && !t.z_external) dev_free(ctx, t.d_z);
   dev_free(ctx, t.d_pass);
-  t.d_pix = t.d_src = t.d_pass = nullptr;
+  t.d_pix = t.d_src = t.d_pass = t.d_z = nullptr;
 }
 
 extern "C" void stitch_job_destroy(stitch_job *job) {
@@ -170,6 +171,8 @@ extern "C" void stitch_job_destroy(stitch_job *job) {
   dev_free(ctx, job->d_slow); dev_free(ctx, job->d_units); dev_free(ctx, job->d_uprog);
   dev_free(ctx, job->d_canvas); dev_free(ctx, job->d_out); dev_free(ctx, job->d_sync); dev_free(ctx, job->d_plans); dev_free(ctx, job->d_ctab);
   dev_free(ctx, job->d_defl); dev_free(ctx, job->d_defl_b); dev_free(ctx, job->d_defl_scratch);
+  dev_free(ctx, job->d_inf); dev_free(ctx, job->d_infres);
+  if (job->h_infres) cudaFreeHost(job->h_infres);
   for (auto &e : job->ev_defl) if (e) cudaEventDestroy(e);
   if (job->h_defl) cudaFreeHost(job->h_defl);
   for (auto &q : job->d_jpeg) dev_free(ctx, q);
@@ -276,28 +279,56 @@ static int prepare_tile(stitch_ctx *ctx, stitch_job *job, TileRec &t, uint32_t t
   return STITCH_OK;
 }
 
+// Bytes of the inflated IDAT stream a descriptor promises: filter byte + row for every row of the image
+// (png-decoder.ts:92) or of every non-empty Adam7 pass (adam7.ts:61-107).  0 for descriptors prepare_tile rejects.
+static size_t inflated_len(const stitch_tile_desc &d) {
+  const int spp = samples_per_pixel(d.color_type);
+  if (spp < 0 || d.color_type == 3 || src_fmt(d.color_type, d.bit_depth) == FMT_INVALID || !d.width || !d.height) return 0;
+  if (!d.interlace) return (scanline_bytes(d.width, d.bit_depth, d.color_type) + 1) * (size_t)d.height;
+  size_t total = 0;
+  for (int p = 0; p < 7; p++) {
+    const uint32_t pw = a7_extent(d.width, A7_XS[p], A7_DX[p]), ph = a7_extent(d.height, A7_YS[p], A7_DY[p]);
+    if (!pw || !ph) continue;
+    total += (size_t)ph * (1 + (size_t)(((uint64_t)pw * d.bit_depth * spp + 7) / 8));
+  }
+  return total;
+}
+
 static int add_tile_common(stitch_job *job, const stitch_tile_desc *tile, const uint8_t *host, const void *dev, size_t len) {
   if (!job || !tile || (!host && !dev && len)) return STITCH_E_INVALID;
   stitch_ctx *ctx = job->ctx;
   cudaSetDevice(ctx->device);
+  if (tile->filtered > 2u) return fail(ctx, STITCH_E_INVALID, "tile.filtered must be 0, 1 or 2");
+  const bool z = tile->filtered == 2u;  // 8f.2: `data` is the zlib stream; the inflated stream is made on the device
   TileRec t;
   t.d = *tile;
-  t.src_len = len;
-  if (dev) {
-    t.d_src = (uint8_t *)dev;
-    t.src_external = true;
+  if (z) {
+    t.d.filtered = 1;
+    t.src_len = inflated_len(*tile);
+    t.z_len = len;
+    t.inflated = false;
+    if (len >= (1ull << 32) || t.src_len >= (1ull << 32)) return fail(ctx, STITCH_E_INVALID, "zlib streams of 4 GiB and more are not supported");
+    if (dev) { t.d_z = (uint8_t *)dev; t.z_external = true; }
+    else CK(cudaMallocAsync((void **)&t.d_z, round_up(len, 16) + 32, ctx->up));
+    CK(cudaMallocAsync((void **)&t.d_src, round_up(t.src_len, 16) + 32, ctx->up));
   } else {
-    // +32: the unfilter kernel may read a few bytes past a row with vector loads.  Allocated in the order of
-    // the upload stream, where the bytes are written; ctx->stream sees it through the tile's upload event.
-    CK(cudaMallocAsync((void **)&t.d_src, round_up(len, 16) + 32, ctx->up));
+    t.src_len = len;
+    if (dev) {
+      t.d_src = (uint8_t *)dev;
+      t.src_external = true;
+    } else {
+      // +32: the unfilter kernel may read a few bytes past a row with vector loads.  Allocated in the order of
+      // the upload stream, where the bytes are written; ctx->stream sees it through the tile's upload event.
+      CK(cudaMallocAsync((void **)&t.d_src, round_up(len, 16) + 32, ctx->up));
+    }
   }
   int rc = prepare_tile(ctx, job, t, (uint32_t)job->tiles.size());
   if (rc) { free_tile(ctx, t); return rc; }
   if (host && len) {
-    cudaError_t e = cudaMemcpyAsync(t.d_src, host, len, cudaMemcpyHostToDevice, ctx->up);
+    cudaError_t e = cudaMemcpyAsync(z ? t.d_z : t.d_src, host, len, cudaMemcpyHostToDevice, ctx->up);
     if (e != cudaSuccess) { free_tile(ctx, t); return fail(ctx, STITCH_E_CUDA, "H2D failed: %s", cudaGetErrorString(e)); }
   }
-  if (!dev) {
+  if (!dev || z) {  // also orders the allocation of an inflate target made on the upload stream
     cudaError_t e = cudaEventCreateWithFlags(&t.up_event, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventRecord(t.up_event, ctx->up);
     if (e != cudaSuccess) { free_tile(ctx, t); return fail(ctx, STITCH_E_CUDA, "H2D failed: %s", cudaGetErrorString(e)); }
@@ -336,8 +367,45 @@ static int reset_status(stitch_ctx *ctx) {
   return STITCH_OK;
 }
 
+// Results of the inflate launches since the last check (stream synchronised by the caller): zlib's message
+// the way the reference reports it (`Inflate error: ${msg}`, streaming-inflate.ts:60-62), or the row-count
+// errors of png-decoder.ts:209-211 / adam7.ts:79-82 when the stream ends early.
+static int check_inflate(stitch_ctx *ctx, stitch_job *job) {
+  int rc = STITCH_OK;
+  for (uint32_t idx : job->inf_pending) {
+    if (rc) break;
+    const InfResult &r = job->h_infres[idx];
+    const TileRec &t = job->tiles[idx];
+    if (r.status) {
+      job->status = STITCH_E_INFLATE;
+      rc = fail(ctx, STITCH_E_INFLATE, "Inflate error: %s", inflate_message(r.status));
+    } else if (r.out_len < t.src_len) {
+      job->status = STITCH_E_TRUNCATED;
+      const size_t rb = scanline_bytes(t.d.width, t.d.bit_depth, t.d.color_type);
+      if (!t.d.interlace) rc = fail(ctx, STITCH_E_TRUNCATED, "Expected %u scanlines, decoded %zu", t.d.height, (size_t)r.out_len / (rb + 1));
+      else {
+        const int spp = samples_per_pixel(t.d.color_type);
+        size_t off = 0;
+        for (int p = 0; p < 7 && !rc; p++) {
+          const uint32_t pw = a7_extent(t.d.width, A7_XS[p], A7_DX[p]), ph = a7_extent(t.d.height, A7_YS[p], A7_DY[p]);
+          if (!pw || !ph) continue;
+          const size_t line = 1 + (size_t)(((uint64_t)pw * t.d.bit_depth * spp + 7) / 8);
+          for (uint32_t y = 0; y < ph; y++, off += line)
+            if (off + line > r.out_len) { rc = fail(ctx, STITCH_E_TRUNCATED, "Unexpected end of decompressed data at pass %d, line %u", p + 1, y); break; }
+        }
+      }
+    }
+  }
+  job->inf_pending.clear();
+  return rc;
+}
+
 // Reads the device error word (stream must be synchronised by the caller).
 static int check_status(stitch_ctx *ctx, stitch_job *job) {
+  if (job && !job->inf_pending.empty()) {
+    const int rc = check_inflate(ctx, job);
+    if (rc) return rc;
+  }
   const unsigned long long e = ctx->h_status->first_error;
   if (e == ~0ull) return STITCH_OK;
   const uint32_t ft = (uint32_t)(e & 0xffu);
@@ -358,11 +426,55 @@ static int wait_uploads(stitch_job *job, uint32_t ya, uint32_t yb) {
   return STITCH_OK;
 }
 
+// 8f.2: inflates, one warp per stream, the zlib tiles that touch canvas rows [ya, yb) and are not inflated yet
+// (all of them again with `force`).  Results are read by check_status after the caller's next synchronisation.
+static int inflate_tiles(stitch_job *job, int force, uint32_t *launches, uint32_t ya = 0, uint32_t yb = 0xffffffffu) {
+  stitch_ctx *ctx = job->ctx;
+  std::vector<InfStream> v;
+  for (uint32_t i = 0; i < job->tiles.size(); i++) {
+    TileRec &t = job->tiles[i];
+    if (!t.d_z || (t.inflated && !force)) continue;
+    if (t.d.vis_h && ((int64_t)t.d.dst_y + t.d.vis_h <= (int64_t)ya || (int64_t)t.d.dst_y >= (int64_t)yb)) continue;
+    InfStream s{};
+    s.src = t.d_z; s.dst = t.d_src; s.src_len = (uint32_t)t.z_len; s.dst_cap = (uint32_t)t.src_len; s.slot = i;
+    v.push_back(s);
+    t.inflated = true;
+    t.decoded = false;
+  }
+  if (v.empty()) return STITCH_OK;
+  int rc = upload_array(ctx, v, &job->d_inf, &job->inf_cap);
+  if (rc) return rc;
+  const size_t n = job->tiles.size();
+  if (n > job->infres_cap) {
+    dev_free(ctx, job->d_infres); job->d_infres = nullptr; job->infres_cap = 0;
+    if ((rc = dev_alloc(ctx, (void **)&job->d_infres, n * sizeof(InfResult)))) return rc;
+    job->infres_cap = n;
+  }
+  if (n > job->h_infres_cap) {
+    InfResult *h = nullptr;
+    CK(cudaHostAlloc((void **)&h, n * sizeof(InfResult), cudaHostAllocDefault));
+    if (job->h_infres) {  // results that are still to be checked live in the old mirror until the next sync copies them again
+      CK(cudaStreamSynchronize(ctx->stream));
+      memcpy(h, job->h_infres, job->h_infres_cap * sizeof(InfResult));
+      cudaFreeHost(job->h_infres);
+    }
+    job->h_infres = h; job->h_infres_cap = n;
+  }
+  CK(launch_inflate(job->d_inf, job->d_infres, (uint32_t)v.size(), ctx->stream));
+  if (launches) *launches += 2;
+  for (auto &s : v) {
+    CK(cudaMemcpyAsync(job->h_infres + s.slot, job->d_infres + s.slot, sizeof(InfResult), cudaMemcpyDeviceToHost, ctx->stream));
+    job->inf_pending.push_back(s.slot);
+  }
+  return STITCH_OK;
+}
+
 // Unfilters (and de-interlaces) the tiles that touch canvas rows [ya, yb) and are not decoded yet.
 static int decode_tiles(stitch_job *job, int force, uint32_t *launches, uint32_t ya = 0, uint32_t yb = 0xffffffffu) {
   stitch_ctx *ctx = job->ctx;
   int wrc = wait_uploads(job, ya, yb);
   if (wrc) return wrc;
+  if ((wrc = inflate_tiles(job, 0, launches, ya, yb))) return wrc;
   std::vector<UnfStream> streams;
   std::vector<A7Image> a7;
   uint32_t a7_max_rb = 0, a7_max_h = 0;
@@ -443,6 +555,62 @@ static int decode_tiles(stitch_job *job, int force, uint32_t *launches, uint32_t
     if (launches) (*launches)++;
   }
   return STITCH_OK;
+}
+
+extern "C" int stitch_job_inflate(stitch_job *job, int force, stitch_timings *t) {
+  if (!job) return STITCH_E_INVALID;
+  stitch_ctx *ctx = job->ctx;
+  cudaSetDevice(ctx->device);
+  uint32_t launches = 0;
+  int rc = wait_uploads(job, 0, 0xffffffffu);
+  if (rc) return rc;
+  if ((rc = reset_status(ctx))) return rc;
+  CK(cudaEventRecord(ctx->ev[0], ctx->stream));
+  if ((rc = inflate_tiles(job, force, &launches))) return rc;
+  CK(cudaEventRecord(ctx->ev[1], ctx->stream));
+  CK(cudaMemcpyAsync(ctx->h_status, ctx->d_status, sizeof(DevStatus), cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  if (t) {
+    memset(t, 0, sizeof *t);
+    cudaEventElapsedTime(&t->decode_ms, ctx->ev[0], ctx->ev[1]);
+    t->total_ms = t->decode_ms;
+    t->launches = launches;
+  }
+  return check_status(ctx, job);
+}
+
+extern "C" int stitch_inflate(stitch_ctx *ctx, const uint8_t *zdata, size_t zlen, uint8_t *out, size_t cap, size_t *out_len) {
+  if (!ctx || (!zdata && zlen) || (!out && cap)) return STITCH_E_INVALID;
+  if (out_len) *out_len = 0;
+  if (zlen >= (1ull << 32) || cap >= (1ull << 32)) return fail(ctx, STITCH_E_INVALID, "zlib streams of 4 GiB and more are not supported");
+  cudaSetDevice(ctx->device);
+  uint8_t *d_z = nullptr, *d_o = nullptr;
+  InfStream *d_s = nullptr;
+  InfResult *d_r = nullptr;
+  int rc = dev_alloc(ctx, (void **)&d_z, round_up(zlen, 16) + 32);
+  if (!rc) rc = dev_alloc(ctx, (void **)&d_o, round_up(cap, 16) + 32);
+  if (!rc) rc = dev_alloc(ctx, (void **)&d_s, sizeof(InfStream));
+  if (!rc) rc = dev_alloc(ctx, (void **)&d_r, sizeof(InfResult));
+  InfResult r{};
+  if (!rc) {
+    InfStream s{};
+    s.src = d_z; s.dst = d_o; s.src_len = (uint32_t)zlen; s.dst_cap = (uint32_t)cap; s.slot = 0;
+    cudaError_t e = zlen ? cudaMemcpyAsync(d_z, zdata, zlen, cudaMemcpyHostToDevice, ctx->stream) : cudaSuccess;
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_s, &s, sizeof s, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) e = launch_inflate(d_s, d_r, 1, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(&r, d_r, sizeof r, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    if (e == cudaSuccess && r.status == 0 && r.out_len) {
+      e = cudaMemcpyAsync(out, d_o, r.out_len, cudaMemcpyDeviceToHost, ctx->stream);
+      if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    }
+    if (e != cudaSuccess) rc = fail(ctx, STITCH_E_CUDA, "inflate failed: %s", cudaGetErrorString(e));
+  }
+  dev_free(ctx, d_z); dev_free(ctx, d_o); dev_free(ctx, d_s); dev_free(ctx, d_r);
+  if (rc) return rc;
+  if (r.status) return fail(ctx, STITCH_E_INFLATE, "Inflate error: %s", inflate_message(r.status));
+  if (out_len) *out_len = r.out_len;
+  return (r.flags & 1u) ? fail(ctx, STITCH_E_CAPACITY, "output buffer too small") : STITCH_OK;
 }
 
 extern "C" int stitch_job_invalidate(stitch_job *job) {

@@ -1,0 +1,556 @@
+// inflate.cu -- SURVEY.md 8(f).2: the zlib streams of the input PNGs (concatenated IDAT payloads) are inflated
+// on the device, so that tiles cross the bus compressed and the host's inflate (src/streaming-inflate.ts:23-76,
+// src/decoders/png-decoder.ts:63-229 up to the point where rows are unfiltered) disappears.  The result is the
+// inflated, still filtered stream that kernel (a) starts from, written straight into the tile's device buffer.
+//
+// DEFLATE decoding is serial inside a stream (a code's position depends on every code before it), so the
+// parallelism is across tiles: ONE WARP PER STREAM.  Inside the warp the bit reader and the Huffman walk run
+// redundantly in all 32 lanes (identical registers, broadcast shared-memory reads, no divergence), so every
+// lane knows every symbol without a shuffle: literals are stored by lanes 0..2, a match is copied by the lanes
+// below its length, straight into a shared-memory ring that holds the last 32 KiB of output and is written out
+// in 512-byte units.
+//
+//   tables   per dynamic block, built by the warp in shared memory: canonical code from the code lengths
+//            (count by length, stable rank by __match_any), an 11-bit single-symbol table filled symbol-parallel,
+//            then an 11-bit MULTI-LITERAL table made from it by lookups: an entry carries up to three
+//            literals when their codes fit in the index (filtered PNG rows are nearly all literals with 4-9 bit
+//            codes, so one shared-memory round trip of the serial chain yields 2+ bytes); codes longer than the
+//            index take a canonical bit-by-bit walk (count/first-code, RFC 1951 3.2.2)
+//   checks   everything zlib's inflate checks, with zlib's messages (what pako reports through
+//            `Inflate error: ${msg}`, streaming-inflate.ts:60-62): header, block type, stored lengths, code-length
+//            sets (over-subscribed / incomplete), missing end-of-block, invalid codes, distance too far back, and
+//            the Adler-32 trailer (a second, data-parallel kernel over the inflated bytes)
+//
+// Format references: RFC 1950, RFC 1951.
+#include "job.h"
+
+#include <cstring>
+
+namespace stitch {
+namespace {
+
+constexpr int TB = 11;                 // literal/length table index bits
+constexpr int TD = 9;                  // distance table index bits
+constexpr int INF_WARPS = 4;           // streams per CTA
+// The last 32 KiB of output (the farthest a match may reach) live in a per-warp shared-memory ring, so a match
+// copy never waits for L2; the ring is longer than that by a flush unit and a match, so nothing that is still to be
+// read or written out is overwritten.  Global memory is written from the ring, 512 bytes (one uint4 per lane) at a time.
+constexpr uint32_t WIN = 32768u + 1024u;
+static_assert(WIN % 16u == 0u && WIN >= 32768u + 512u + 258u + 16u, "ring: granule-aligned, a flush unit and a match of slack");
+constexpr uint32_t FULL = 0xffffffffu;
+constexpr uint32_t E_LONG = 0x30u;     // entry kind 3: code longer than the index, or no code at all
+
+// entry (literal/length table): bits 0-3 code bits consumed, 4-5 kind (0 literals, 1 length, 2 end of block,
+// 3 long/invalid); literals: 6-7 count, 8-31 up to three bytes; length: 8-11 extra bits, 16-24 base
+// entry (distance table): bits 0-3 code bits, 4-5 kind (0 ok, 3 long/invalid), 8-11 extra bits, 16-31 base
+__constant__ uint16_t c_lbase[31] = {3, 4, 5, 6, 7, 8, 9, 10, 11, 13, 15, 17, 19, 23, 27, 31, 35, 43, 51, 59, 67, 83, 99,
+                                     115, 131, 163, 195, 227, 258, 0, 0};
+__constant__ uint8_t c_lext[31] = {0, 0, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 2, 2, 2, 2, 3, 3, 3, 3, 4, 4, 4, 4, 5, 5, 5, 5, 0, 0, 0};
+__constant__ uint16_t c_dbase[32] = {1, 2, 3, 4, 5, 7, 9, 13, 17, 25, 33, 49, 65, 97, 129, 193, 257, 385, 513, 769, 1025,
+                                     1537, 2049, 3073, 4097, 6145, 8193, 12289, 16385, 24577, 0, 0};
+__constant__ uint8_t c_dext[32] = {0, 0, 0, 0, 1, 1, 2, 2, 3, 3, 4, 4, 5, 5, 6, 6, 7, 7, 8, 8, 9, 9, 10, 10, 11, 11, 12, 12, 13, 13, 0, 0};
+__constant__ uint8_t c_clorder[19] = {16, 17, 18, 0, 8, 7, 9, 6, 10, 5, 11, 4, 12, 3, 13, 2, 14, 1, 15};
+
+struct Canon {            // one canonical Huffman code (RFC 1951 3.2.2)
+  uint32_t cnt[16];       // codes per length
+  uint32_t offs[17];      // index of the first symbol of a length in `sym`
+  uint32_t next[16];      // first code of a length
+};
+
+struct WarpSmem {
+  uint32_t lt[1 << TB];
+  uint32_t dt[1 << TD];
+  uint16_t l1[1 << TB];
+  uint16_t lsym[288], dsym[32];
+  Canon lc, dc;
+  uint8_t lens[320];      // literal/length code lengths, then the distance code lengths
+  uint8_t clt[128];       // code-length code: symbol | bits << 5
+  uint32_t pad[3];
+  __align__(16) uint8_t win[WIN];
+};
+static_assert(sizeof(WarpSmem) % 16 == 0, "rings must stay 16-byte aligned");
+
+// ring -> global, whole 512-byte units below `upto` (all of it with `all`); granules may run past `upto` into
+// the 16 bytes of slack every destination buffer has
+__device__ __forceinline__ void ring_flush(const uint8_t *win, uint8_t *dst, uint32_t &flushed, uint32_t upto, bool all, uint32_t lane) {
+  while (flushed + 512u <= upto) {
+    const uint32_t g = flushed + 16u * lane;
+    *reinterpret_cast<uint4 *>(dst + g) = *reinterpret_cast<const uint4 *>(win + g % WIN);
+    flushed += 512u;
+  }
+  if (all && flushed < upto) {
+    const uint32_t g = flushed + 16u * lane;
+    if (g < upto) *reinterpret_cast<uint4 *>(dst + g) = *reinterpret_cast<const uint4 *>(win + g % WIN);
+    flushed = upto;
+  }
+}
+
+// ---- bit reader: identical in every lane ------------------------------------------------------------------
+struct Bits {
+  const uint32_t *w;
+  uint32_t last;   // index of the last readable word
+  uint32_t wi;     // index of the next word to fetch
+  uint32_t nx;     // fetched, not yet in bb
+  unsigned long long bb;
+  uint32_t bc;
+
+  __device__ __forceinline__ void init(const uint8_t *src, uint32_t src_len, uint32_t byte_off) {
+    w = reinterpret_cast<const uint32_t *>(src);
+    last = src_len ? (src_len - 1u) >> 2 : 0u;
+    const uint32_t k = byte_off >> 2, sh = 8u * (byte_off & 3u);
+    bb = (unsigned long long)(__ldg(w + min(k, last)) >> sh);
+    bc = 32u - sh;
+    nx = __ldg(w + min(k + 1u, last));
+    wi = k + 2u;
+  }
+  // at least 33 valid bits afterwards
+  __device__ __forceinline__ void refill() {
+    if (bc <= 32u) {
+      bb |= (unsigned long long)nx << bc;
+      bc += 32u;
+      nx = __ldg(w + min(wi, last));
+      wi++;
+    }
+  }
+  __device__ __forceinline__ uint32_t peek(uint32_t n) const { return (uint32_t)bb & ((1u << n) - 1u); }
+  __device__ __forceinline__ void drop(uint32_t n) { bb >>= n; bc -= n; }
+  __device__ __forceinline__ uint32_t take(uint32_t n) { const uint32_t v = peek(n); drop(n); return v; }
+  __device__ __forceinline__ unsigned long long consumed_bits() const { return (unsigned long long)(wi - 1u) * 32ull - bc; }
+};
+
+// Bit-by-bit canonical walk (codes are packed most significant bit first, RFC 1951 3.1.1).  Returns the symbol
+// and its length, or -1 when no code of up to 15 bits matches (incomplete code).
+__device__ __forceinline__ int canon_walk(uint32_t bits, const Canon &c, const uint16_t *sym, uint32_t &len_out) {
+  int code = 0, first = 0, index = 0;
+  for (uint32_t len = 1; len <= 15u; len++) {
+    code |= (int)(bits & 1u);
+    bits >>= 1;
+    const int count = (int)c.cnt[len];
+    if (code - count < first) { len_out = len; return sym[index + (code - first)]; }
+    index += count; first += count;
+    first <<= 1; code <<= 1;
+  }
+  return -1;
+}
+
+// Warp-wide: counts, validity (zlib inftrees.c: over-subscribed or incomplete sets are rejected, except an
+// incomplete distance/length set that consists of a single code... zlib allows that for distances only),
+// offsets, first codes, symbols sorted by (length, symbol).  Returns 0 ok, 1 over-subscribed, 2 incomplete.
+__device__ int canon_build(const uint8_t *lens, uint32_t n, Canon &c, uint16_t *sym, uint32_t lane) {
+  if (lane < 16u) c.cnt[lane] = 0u;
+  __syncwarp();
+  for (uint32_t i = lane; i < n; i += 32u) atomicAdd(&c.cnt[lens[i]], 1u);
+  __syncwarp();
+  int left = 1, bad = 0;
+  uint32_t off = 0, code = 0;
+  for (uint32_t len = 1; len <= 15u; len++) {   // redundantly in every lane (broadcast reads)
+    const uint32_t k = c.cnt[len];
+    left = (left << 1) - (int)k;
+    if (left < 0) bad = 1;
+    code = (code + (len > 1u ? c.cnt[len - 1u] : 0u)) << 1;
+    if (lane == 0u) { c.offs[len] = off; c.next[len] = code; }
+    off += k;
+  }
+  if (lane == 0u) { c.offs[16] = off; c.offs[0] = 0u; }
+  __syncwarp();
+  if (bad) return 1;
+  // stable ranks inside chunks of 32 symbols; running offsets in registers of the lanes 1..15 (lane L owns length L)
+  uint32_t run = lane >= 1u && lane <= 15u ? c.offs[lane] : 0u;
+  for (uint32_t base = 0; base < n; base += 32u) {
+    const uint32_t i = base + lane;
+    const uint32_t l = i < n ? lens[i] : 0u;
+    const uint32_t peers = __match_any_sync(FULL, l);
+    const uint32_t rank = __popc(peers & ((1u << lane) - 1u));
+    const uint32_t start = __shfl_sync(FULL, run, l);   // lane l holds the running offset of length l
+    if (l) sym[start + rank] = (uint16_t)i;
+    // lane L adds the number of symbols of length L seen in this chunk
+    uint32_t add = 0;
+    for (uint32_t L = 1; L <= 15u; L++) {
+      const uint32_t m = __ballot_sync(FULL, l == L);
+      if (lane == L) add = __popc(m);
+    }
+    run += add;
+  }
+  __syncwarp();
+  return left > 0 ? 2 : 0;
+}
+
+// Symbol-parallel fill of a single-symbol table with `bits` index bits: `put(index, symbol, length)`.
+template <class Put>
+__device__ __forceinline__ void canon_fill(const Canon &c, const uint16_t *sym, const uint8_t *lens, int bits, uint32_t lane, Put put) {
+  // symbols with at least 32 replicas: the warp shares each symbol's replicas
+  const int wide = bits - 5;
+  const uint32_t n_wide = wide >= 1 ? c.offs[wide + 1] : 0u;
+  for (uint32_t i = 0; i < n_wide; i++) {
+    const uint32_t s = sym[i], L = lens[s];
+    const uint32_t code = c.next[L] + (i - c.offs[L]);
+    const uint32_t r = __brev(code) >> (32u - L);
+    for (uint32_t k = lane; k < (1u << (bits - L)); k += 32u) put(r | (k << L), s, L);
+  }
+  const uint32_t n_all = c.offs[bits + 1];
+  for (uint32_t i = n_wide + lane; i < n_all; i += 32u) {
+    const uint32_t s = sym[i], L = lens[s];
+    const uint32_t code = c.next[L] + (i - c.offs[L]);
+    const uint32_t r = __brev(code) >> (32u - L);
+    for (uint32_t k = 0; k < (1u << (bits - L)); k++) put(r | (k << L), s, L);
+  }
+}
+
+// Tables of one block from sm.lens[0..nlen) and sm.lens[nlen..nlen+ndist).  Returns 0 or an InfStatus.
+__device__ int build_tables(WarpSmem &sm, uint32_t nlen, uint32_t ndist, uint32_t lane) {
+  int rc = canon_build(sm.lens, nlen, sm.lc, sm.lsym, lane);
+  // zlib (inftrees.c): an incomplete set is accepted only when it is a single one-bit code, or no code at all
+  // (a block without matches has no distance code; the end-of-block check has already excluded the literal side)
+  if (rc == 1 || (rc == 2 && !(sm.lc.offs[16] == 1u && sm.lc.cnt[1] == 1u))) return INF_E_LITLEN_SET;
+  rc = canon_build(sm.lens + nlen, ndist, sm.dc, sm.dsym, lane);
+  if (rc == 1 || (rc == 2 && !(sm.dc.offs[16] == 0u || (sm.dc.offs[16] == 1u && sm.dc.cnt[1] == 1u)))) return INF_E_DIST_SET;
+  for (uint32_t i = lane; i < (1u << TB); i += 32u) sm.l1[i] = 0;
+  for (uint32_t i = lane; i < (1u << TD); i += 32u) sm.dt[i] = E_LONG;
+  __syncwarp();
+  uint16_t *l1 = sm.l1;
+  canon_fill(sm.lc, sm.lsym, sm.lens, TB, lane, [l1](uint32_t idx, uint32_t s, uint32_t L) { l1[idx] = (uint16_t)(L | (s << 4)); });
+  uint32_t *dt = sm.dt;
+  canon_fill(sm.dc, sm.dsym, sm.lens + nlen, TD, lane, [dt](uint32_t idx, uint32_t s, uint32_t L) {
+    dt[idx] = s < 30u ? (L | ((uint32_t)c_dext[s] << 8) | ((uint32_t)c_dbase[s] << 16)) : E_LONG;
+  });
+  __syncwarp();
+  // multi-literal table from the single-symbol one
+  for (uint32_t idx = lane; idx < (1u << TB); idx += 32u) {
+    const uint32_t e1 = l1[idx];
+    uint32_t e = E_LONG;
+    if (e1) {
+      const uint32_t L1 = e1 & 15u, s1 = e1 >> 4;
+      if (s1 < 256u) {
+        uint32_t nb = L1, cnt = 1u, lits = s1;
+        const uint32_t e2 = l1[idx >> nb];
+        if (e2 && (e2 >> 4) < 256u && nb + (e2 & 15u) <= (uint32_t)TB) {
+          lits |= (e2 >> 4) << 8; nb += e2 & 15u; cnt = 2u;
+          const uint32_t e3 = l1[idx >> nb];
+          if (e3 && (e3 >> 4) < 256u && nb + (e3 & 15u) <= (uint32_t)TB) { lits |= (e3 >> 4) << 16; nb += e3 & 15u; cnt = 3u; }
+        }
+        e = nb | (cnt << 6) | (lits << 8);
+      } else if (s1 == 256u) {
+        e = L1 | 0x20u;
+      } else if (s1 < 286u) {
+        e = L1 | 0x10u | ((uint32_t)c_lext[s1 - 257u] << 8) | ((uint32_t)c_lbase[s1 - 257u] << 16);
+      }
+    }
+    sm.lt[idx] = e;
+  }
+  __syncwarp();
+  return 0;
+}
+
+// Dynamic block header (RFC 1951 3.2.7): code lengths into sm.lens.  Uniform in all lanes.
+__device__ int read_dynamic_header(WarpSmem &sm, Bits &br, uint32_t lane, uint32_t &nlen, uint32_t &ndist) {
+  br.refill();
+  nlen = br.take(5) + 257u;
+  ndist = br.take(5) + 1u;
+  const uint32_t ncode = br.take(4) + 4u;
+  if (nlen > 286u || ndist > 30u) return INF_E_TOO_MANY;
+  uint8_t *cl = sm.lens + 300;  // 19 code-length code lengths live in the tail of lens for a moment
+  if (lane < 19u) cl[lane] = 0;
+  __syncwarp();
+  for (uint32_t i = 0; i < ncode; i++) {
+    br.refill();
+    const uint32_t v = br.take(3);
+    if (lane == 0u) cl[c_clorder[i]] = (uint8_t)v;
+  }
+  __syncwarp();
+  // the code-length code: counts and first codes redundantly per lane, 7-bit table filled by the symbols' lanes
+  uint32_t cnt[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  for (uint32_t i = 0; i < 19u; i++) cnt[cl[i]]++;
+  int left = 1;
+  uint32_t next[8], code = 0;
+  next[0] = 0;
+  for (uint32_t len = 1; len <= 7u; len++) {
+    left = (left << 1) - (int)cnt[len];
+    if (left < 0) return INF_E_CODE_LENGTHS;
+    code = (code + (len > 1u ? cnt[len - 1u] : 0u)) << 1;
+    next[len] = code;
+  }
+  if (left > 0) return INF_E_CODE_LENGTHS;  // zlib: incomplete code-length code is an error (type CODES)
+  for (uint32_t i = lane; i < 128u; i += 32u) sm.clt[i] = 0;
+  __syncwarp();
+  if (lane < 19u) {
+    const uint32_t L = cl[lane];
+    if (L) {
+      uint32_t c = next[L];
+      for (uint32_t j = 0; j < lane; j++) c += cl[j] == L ? 1u : 0u;
+      const uint32_t r = __brev(c) >> (32u - L);
+      for (uint32_t k = 0; k < (1u << (7u - L)); k++) sm.clt[r | (k << L)] = (uint8_t)(lane | (L << 5));
+    }
+  }
+  __syncwarp();
+  // the nlen + ndist code lengths, run-length coded
+  const uint32_t total = nlen + ndist;
+  uint32_t i = 0, prev = 0;
+  while (i < total) {
+    br.refill();
+    const uint32_t e = sm.clt[br.peek(7)];
+    if (e == 0u) return INF_E_CODE_LENGTHS;
+    br.drop(e >> 5);
+    const uint32_t s = e & 31u;
+    if (s < 16u) {
+      if (lane == 0u) sm.lens[i] = (uint8_t)s;
+      prev = s; i++;
+    } else {
+      uint32_t rep, val = 0;
+      if (s == 16u) {
+        if (i == 0u) return INF_E_BIT_REPEAT;
+        val = prev; rep = 3u + br.take(2);
+      } else if (s == 17u) rep = 3u + br.take(3);
+      else rep = 11u + br.take(7);
+      if (i + rep > total) return INF_E_BIT_REPEAT;
+      if (lane < rep) sm.lens[i + lane] = (uint8_t)val;
+      if (lane + 32u < rep) sm.lens[i + lane + 32u] = (uint8_t)val;
+      if (lane + 64u < rep) sm.lens[i + lane + 64u] = (uint8_t)val;
+      if (lane + 96u < rep) sm.lens[i + lane + 96u] = (uint8_t)val;
+      if (lane + 128u < rep) sm.lens[i + lane + 128u] = (uint8_t)val;
+      prev = val; i += rep;
+    }
+  }
+  __syncwarp();
+  if (sm.lens[256] == 0) return INF_E_NO_EOB;
+  return 0;
+}
+
+__global__ void __launch_bounds__(INF_WARPS * 32) inflate_kernel(const InfStream *streams, InfResult *results, uint32_t n_streams) {
+  extern __shared__ __align__(16) unsigned char inf_smem_raw[];
+  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  const uint32_t sid = blockIdx.x * INF_WARPS + warp;
+  if (sid >= n_streams) return;
+  WarpSmem &sm = reinterpret_cast<WarpSmem *>(inf_smem_raw)[warp];
+  const InfStream st = streams[sid];
+  uint8_t *dst = st.dst;
+  uint8_t *win = sm.win;
+  const uint32_t cap = st.dst_cap;
+  uint32_t pos = 0, flushed = 0, wpos = 0;  // wpos: pos modulo the ring
+  int err = 0;
+  uint32_t adler_stored = 0, flags = 0;
+  Bits br;
+
+  if (st.src_len < 2u) { err = INF_E_EOF; goto done; }
+  br.init(st.src, st.src_len, 0u);
+  {
+    const uint32_t cmf = br.take(8), flg = br.take(8);
+    if (((cmf << 8) | flg) % 31u) { err = INF_E_HEADER; goto done; }
+    if ((cmf & 15u) != 8u) { err = INF_E_METHOD; goto done; }
+    if ((cmf >> 4) > 7u) { err = INF_E_WINDOW; goto done; }
+    if (flg & 0x20u) { err = INF_E_DICT; goto done; }
+  }
+  for (;;) {  // blocks
+    br.refill();
+    const uint32_t bfinal = br.take(1), btype = br.take(2);
+    if (btype == 3u) { err = INF_E_BLOCK_TYPE; goto done; }
+    if (btype == 0u) {
+      br.drop(br.bc & 7u);
+      br.refill();
+      const uint32_t len = br.take(16);
+      br.refill();
+      const uint32_t nlen = br.take(16);
+      if ((len ^ 0xffffu) != nlen) { err = INF_E_STORED; goto done; }
+      const unsigned long long at = br.consumed_bits() >> 3;
+      if (at + len > st.src_len) { err = INF_E_EOF; goto done; }
+      const uint8_t *s = st.src + at;
+      for (uint32_t done = 0; done < len;) {   // through the ring, a piece at a time (later matches may reach back into it)
+        const uint32_t n = min(len - done, 4096u);
+        for (uint32_t j = lane; j < n; j += 32u) win[(pos + j) % WIN] = __ldg(s + done + j);
+        pos += n; done += n;
+        __syncwarp();
+        ring_flush(win, dst, flushed, min(pos, cap), false, lane);
+        __syncwarp();
+      }
+      wpos = pos % WIN;
+      br.init(st.src, st.src_len, (uint32_t)at + len);
+    } else {
+      if (btype == 1u) {
+        for (uint32_t i = lane; i < 288u; i += 32u) sm.lens[i] = i < 144u ? 8 : i < 256u ? 9 : i < 280u ? 7 : 8;
+        sm.lens[288 + lane] = 5;  // 32 distance codes of 5 bits (30 and 31 never valid)
+        __syncwarp();
+        err = build_tables(sm, 288u, 32u, lane);
+      } else {
+        uint32_t nlen, ndist;
+        err = read_dynamic_header(sm, br, lane, nlen, ndist);
+        if (!err) err = build_tables(sm, nlen, ndist, lane);
+      }
+      if (err) goto done;
+      // ---- symbols of the block: every lane walks the same codes; output goes to the ring as it is decoded ----
+      bool eob = false;
+      while (!eob) {
+        br.refill();
+        const uint32_t e = sm.lt[br.peek(TB)];
+        uint32_t kind = (e >> 4) & 3u;
+        uint32_t lits = e >> 8, cnt = (e >> 6) & 3u, lbase = e >> 16, lext = (e >> 8) & 15u;
+        if (kind == 3u) {  // a code longer than TB bits (rare symbols), or none
+          uint32_t L;
+          const int sy = canon_walk((uint32_t)br.bb, sm.lc, sm.lsym, L);
+          if (sy < 0 || sy >= 286) { err = INF_E_LITLEN_CODE; break; }
+          br.drop(L);
+          if (sy < 256) { kind = 0u; lits = (uint32_t)sy; cnt = 1u; }
+          else if (sy == 256) kind = 2u;
+          else { kind = 1u; lbase = c_lbase[sy - 257]; lext = c_lext[sy - 257]; }
+        } else {
+          br.drop(e & 15u);
+        }
+        if (kind == 0u) {  // one to three literals: lanes 0..2 store them
+          if (lane < cnt) {
+            uint32_t q = wpos + lane;
+            q = q >= WIN ? q - WIN : q;
+            win[q] = (uint8_t)(lits >> (8u * lane));
+          }
+          pos += cnt; wpos += cnt;
+        } else if (kind == 2u) {
+          eob = true;
+        } else {
+          const uint32_t len = lbase + br.take(lext);
+          br.refill();
+          const uint32_t d = sm.dt[br.peek(TD)];
+          uint32_t dbase = d >> 16, dext = (d >> 8) & 15u;
+          if ((d & 0x30u) == 0x30u) {
+            uint32_t L;
+            const int sy = canon_walk((uint32_t)br.bb, sm.dc, sm.dsym, L);
+            if (sy < 0 || sy >= 30) { err = INF_E_DIST_CODE; break; }
+            br.drop(L);
+            dbase = c_dbase[sy]; dext = c_dext[sy];
+          } else {
+            br.drop(d & 15u);
+          }
+          const uint32_t dist = dbase + br.take(dext);
+          if (dist > pos) { err = INF_E_FAR; break; }
+          const uint32_t s0 = wpos >= dist ? wpos - dist : wpos + WIN - dist;
+          __syncwarp();  // the bytes this match copies may have been stored by other lanes
+          if (dist >= len) {
+            for (uint32_t j = lane; j < len; j += 32u) {
+              uint32_t sj = s0 + j, dj = wpos + j;
+              sj = sj >= WIN ? sj - WIN : sj;
+              dj = dj >= WIN ? dj - WIN : dj;
+              win[dj] = win[sj];
+            }
+          } else {       // the match overlaps its own output: a pattern of period `dist`
+            for (uint32_t j = lane; j < len; j += 32u) {
+              uint32_t sj = s0 + j % dist, dj = wpos + j;
+              sj = sj >= WIN ? sj - WIN : sj;
+              dj = dj >= WIN ? dj - WIN : dj;
+              win[dj] = win[sj];
+            }
+          }
+          pos += len; wpos += len;
+        }
+        wpos = wpos >= WIN ? wpos - WIN : wpos;
+        if (pos - flushed >= 512u || eob) {
+          __syncwarp();
+          ring_flush(win, dst, flushed, min(pos, cap), false, lane);
+          if (br.consumed_bits() > 8ull * st.src_len) { err = INF_E_EOF; break; }
+          if (pos > cap) { flags |= 1u; break; }  // more than the caller asked for: the rest is not needed
+        }
+      }
+      if (err || (flags & 1u)) goto done;
+    }
+    if (br.consumed_bits() > 8ull * st.src_len) { err = INF_E_EOF; goto done; }
+    if (bfinal) break;
+    if (pos > cap) { flags |= 1u; goto done; }
+  }
+  {  // Adler-32 trailer (RFC 1950), big-endian, on the next byte boundary
+    const unsigned long long at = (br.consumed_bits() + 7ull) >> 3;
+    if (at + 4ull > st.src_len) { err = INF_E_EOF; goto done; }
+    const uint8_t *t = st.src + at;
+    adler_stored = ((uint32_t)__ldg(t) << 24) | ((uint32_t)__ldg(t + 1) << 16) | ((uint32_t)__ldg(t + 2) << 8) | __ldg(t + 3);
+    flags |= 2u;  // trailer read: the Adler kernel compares
+  }
+done:
+  __syncwarp();
+  ring_flush(win, dst, flushed, min(pos, cap), true, lane);
+  if (lane == 0u) {
+    InfResult r;
+    r.status = (uint32_t)err; r.out_len = pos < cap ? pos : cap; r.adler_stored = adler_stored; r.flags = flags;
+    results[st.slot] = r;
+  }
+}
+
+// Adler-32 of every inflated stream against its trailer: one CTA per stream.  For bytes d[0..N):
+// s1 = 1 + sum d[i], s2 = N + sum (N - i) d[i]  (mod 65521).
+constexpr uint32_t ADLER_MOD = 65521u;
+__global__ void __launch_bounds__(256) inflate_adler_kernel(const InfStream *streams, InfResult *results) {
+  const uint32_t sid = blockIdx.x, slot = streams[sid].slot;
+  const InfResult r = results[slot];
+  if (r.status != 0u || (r.flags & 2u) == 0u || (r.flags & 1u) != 0u) return;
+  const uint8_t *d = streams[sid].dst;
+  const uint32_t N = r.out_len;
+  unsigned long long s1 = 0, s2 = 0;
+  const uint32_t n16 = N / 16u;
+  const uint4 *q = reinterpret_cast<const uint4 *>(d);   // tile buffers are 16-byte aligned
+  for (uint32_t k = threadIdx.x; k < n16; k += blockDim.x) {
+    const uint4 v = q[k];
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    uint32_t a = 0, b = 0;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const uint32_t b0 = w[j] & 255u, b1 = (w[j] >> 8) & 255u, b2 = (w[j] >> 16) & 255u, b3 = w[j] >> 24;
+      a += b0 + b1 + b2 + b3;
+      b += (16u - 4u * j) * b0 + (15u - 4u * j) * b1 + (14u - 4u * j) * b2 + (13u - 4u * j) * b3;
+    }
+    const uint32_t m = (N - 16u * k - 16u) % ADLER_MOD;
+    s1 += a;
+    s2 += (unsigned long long)m * a + b;
+    if ((k / blockDim.x & 1023u) == 1023u) s2 %= ADLER_MOD;
+  }
+  if (threadIdx.x == 0) {
+    for (uint32_t i = n16 * 16u; i < N; i++) { s1 += d[i]; s2 += (unsigned long long)(N - i) * d[i]; }
+  }
+  s1 %= ADLER_MOD; s2 %= ADLER_MOD;
+  __shared__ unsigned long long sh1[256], sh2[256];
+  sh1[threadIdx.x] = s1; sh2[threadIdx.x] = s2;
+  __syncthreads();
+  for (uint32_t s = 128; s > 0; s >>= 1) {
+    if (threadIdx.x < s) { sh1[threadIdx.x] += sh1[threadIdx.x + s]; sh2[threadIdx.x] += sh2[threadIdx.x + s]; }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    const uint32_t a = (uint32_t)((1ull + sh1[0]) % ADLER_MOD), b = (uint32_t)((N % ADLER_MOD + sh2[0]) % ADLER_MOD);
+    if (((b << 16) | a) != r.adler_stored) results[slot].status = INF_E_DATA_CHECK;
+  }
+}
+
+}  // namespace
+
+cudaError_t launch_inflate(const InfStream *d_streams, InfResult *d_results, uint32_t n_streams, cudaStream_t st) {
+  if (!n_streams) return cudaSuccess;
+  static bool attr = false;
+  const size_t smem = sizeof(WarpSmem) * INF_WARPS;
+  if (!attr) {
+    cudaError_t e = cudaFuncSetAttribute(inflate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    attr = true;
+  }
+  inflate_kernel<<<(n_streams + INF_WARPS - 1) / INF_WARPS, INF_WARPS * 32, smem, st>>>(d_streams, d_results, n_streams);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  inflate_adler_kernel<<<n_streams, 256, 0, st>>>(d_streams, d_results);
+  return cudaGetLastError();
+}
+
+const char *inflate_message(uint32_t status) {
+  switch (status) {   // zlib's own texts (inflate.c, inftrees.c), which pako passes through
+    case INF_E_HEADER: return "incorrect header check";
+    case INF_E_METHOD: return "unknown compression method";
+    case INF_E_WINDOW: return "invalid window size";
+    case INF_E_DICT: return "need dictionary";
+    case INF_E_BLOCK_TYPE: return "invalid block type";
+    case INF_E_STORED: return "invalid stored block lengths";
+    case INF_E_TOO_MANY: return "too many length or distance symbols";
+    case INF_E_CODE_LENGTHS: return "invalid code lengths set";
+    case INF_E_BIT_REPEAT: return "invalid bit length repeat";
+    case INF_E_NO_EOB: return "invalid code -- missing end-of-block";
+    case INF_E_LITLEN_SET: return "invalid literal/lengths set";
+    case INF_E_DIST_SET: return "invalid distances set";
+    case INF_E_LITLEN_CODE: return "invalid literal/length code";
+    case INF_E_DIST_CODE: return "invalid distance code";
+    case INF_E_FAR: return "invalid distance too far back";
+    case INF_E_DATA_CHECK: return "incorrect data check";
+    case INF_E_EOF: return "unexpected end of file";
+    default: return "unknown inflate error";
+  }
+}
+
+}  // namespace stitch

@@ -35,6 +35,10 @@ struct TileRec {
   bool has_a7 = false;
   stitch::A7Image a7;
   bool decoded = false;
+  uint8_t *d_z = nullptr;     // zlib stream as uploaded (descriptor said filtered == 2); d_src is its inflate target
+  bool z_external = false;
+  size_t z_len = 0;
+  bool inflated = true;       // false: d_src is still to be produced from d_z (inflate.cu)
   cudaEvent_t up_event = nullptr;  // recorded on ctx->up after the tile's bytes were queued
   bool up_waited = true;           // ctx->stream already waits for up_event
 };
@@ -57,6 +61,11 @@ struct stitch_job {
   uint32_t seam_epoch = 0;                                   // tag of the last decode that used the mailbox
   stitch::A7Image *d_a7 = nullptr; size_t a7_cap = 0;
   uint32_t bins_x = 0, bins_y = 0, bin_w_log2 = 9, bin_h_log2 = 4, bin_y_origin = 0;
+  // inflate (8f.2): stream table, one result slot per tile, pinned mirror, tiles whose result is not checked yet
+  stitch::InfStream *d_inf = nullptr; size_t inf_cap = 0;
+  stitch::InfResult *d_infres = nullptr; size_t infres_cap = 0;
+  stitch::InfResult *h_infres = nullptr; size_t h_infres_cap = 0;
+  std::vector<uint32_t> inf_pending;
   uint32_t *d_sync = nullptr; size_t sync_words = 0;   // fused kernel: rowsum | band_done | ticket
   bool force_two_pass = false;
   // band buffers

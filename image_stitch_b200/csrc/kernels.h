@@ -75,4 +75,27 @@ cudaError_t launch_adam7_gather(const A7Image *d_images, uint32_t n_images, uint
 cudaError_t launch_compose(const ComposeParams &p, bool out16, cudaStream_t st);
 cudaError_t launch_filter_rows(const FilterParams &p, cudaStream_t st);
 
+// inflate.cu: one zlib stream (concatenated IDAT payloads of one PNG) per warp.
+struct InfStream {
+  const uint8_t *src;   // zlib stream, 4-byte aligned, readable up to src_len rounded up to 4
+  uint8_t *dst;         // inflated bytes, 16-byte aligned, writable up to dst_cap rounded up to 16
+  uint32_t src_len;
+  uint32_t dst_cap;     // bytes the caller wants: decoding stops there
+  uint32_t slot;        // index of this stream's InfResult
+  uint32_t pad;
+};
+struct InfResult {
+  uint32_t status;        // 0 or InfStatus
+  uint32_t out_len;       // bytes written (<= dst_cap)
+  uint32_t adler_stored;  // the stream's trailer
+  uint32_t flags;         // bit 0: stopped at dst_cap before the stream ended; bit 1: trailer read
+};
+enum InfStatus : uint32_t {
+  INF_OK = 0, INF_E_HEADER, INF_E_METHOD, INF_E_WINDOW, INF_E_DICT, INF_E_BLOCK_TYPE, INF_E_STORED, INF_E_TOO_MANY,
+  INF_E_CODE_LENGTHS, INF_E_BIT_REPEAT, INF_E_NO_EOB, INF_E_LITLEN_SET, INF_E_DIST_SET, INF_E_LITLEN_CODE,
+  INF_E_DIST_CODE, INF_E_FAR, INF_E_DATA_CHECK, INF_E_EOF
+};
+cudaError_t launch_inflate(const InfStream *d_streams, InfResult *d_results, uint32_t n_streams, cudaStream_t st);
+const char *inflate_message(uint32_t status);
+
 }  // namespace stitch

@@ -42,6 +42,7 @@ typedef enum stitch_status {
                               "Unexpected end of decompressed data at pass P, line L" src/adam7.ts:80-82 */
   STITCH_E_STATE = -7,     /* call order violated */
   STITCH_E_CAPACITY = -8,  /* caller buffer too small */
+  STITCH_E_INFLATE = -9,   /* "Inflate error: <zlib message>"   src/streaming-inflate.ts:60-62, :69-71 */
   STITCH_E_NODEVICE = -10  /* no CUDA device: there is no CPU fallback */
 } stitch_status;
 
@@ -80,7 +81,10 @@ typedef struct stitch_tile_desc {
   uint32_t color_type;           /* 0,2,4,6 (3 = palette raises STITCH_E_COLOR like the reference) */
   uint32_t interlace;            /* 1: Adam7 stream, src/adam7.ts:52-110 */
   uint32_t filtered;             /* 1: data = inflated IDAT stream with filter bytes (src/decoders/png-decoder.ts:63-229)
-                                    0: data = dense unfiltered rows (foreign ImageDecoder.scanlines()) */
+                                    0: data = dense unfiltered rows (foreign ImageDecoder.scanlines())
+                                    2: data = the zlib stream itself (the concatenated IDAT payloads,
+                                       src/png-parser.ts / png-decoder.ts:100-117 before createDecompressionStream):
+                                       inflated on the device, then treated like 1 */
   int32_t dst_x, dst_y;          /* clipped top-left on the canvas, >= 0 */
   uint32_t src_off_x, src_off_y; /* ClippedImageInfo.sourceOffsetX/Y */
   uint32_t vis_w, vis_h;         /* visible size after clipping */
@@ -159,6 +163,14 @@ int stitch_job_add_tile_device(stitch_job *job, const stitch_tile_desc *tile, co
  * unless `force` is set (bench: re-run with inputs resident in HBM). */
 int stitch_job_decode(stitch_job *job, int force, stitch_timings *t);
 
+/* SURVEY 8f.2, the step before kernel (a): inflates every tile that was added as a zlib stream
+ * (filtered == 2) and is not inflated yet -- all of them again with `force` -- one warp per stream, and checks
+ * the Adler-32 trailers.  What createDecompressionStream('deflate') / pako.Inflate do on the host
+ * (src/streaming-inflate.ts:23-76).  stitch_job_decode / stitch_job_run_band call it on their own for the
+ * tiles they need; this entry point exists for timing the step alone.  Failures: STITCH_E_INFLATE with
+ * zlib's message, STITCH_E_TRUNCATED when the stream holds fewer rows than the header promises. */
+int stitch_job_inflate(stitch_job *job, int force, stitch_timings *t);
+
 /* Forgets that the job's tiles were decoded (no device work): the next
  * stitch_job_run_band unfilters again what its rows need, in the same stream
  * submission as the composite -- one synchronisation per band instead of two.
@@ -200,6 +212,10 @@ int stitch_job_status(stitch_job *job);
  * (what ImageDecoder.scanlines() yields, src/decoders/types.ts:55-61). */
 int stitch_decode_image(stitch_ctx *ctx, const stitch_tile_desc *tile, const uint8_t *data, size_t len,
                         uint8_t *out, size_t cap, size_t *out_len);
+
+/* Inflate alone: one zlib stream (RFC 1950) -> at most cap bytes.  STITCH_E_CAPACITY when the stream holds
+ * more (out is filled, *out_len == cap). */
+int stitch_inflate(stitch_ctx *ctx, const uint8_t *zdata, size_t zlen, uint8_t *out, size_t cap, size_t *out_len);
 
 /* Kernel (c) alone: filterScanline over `rows` rows of `row_bytes` bytes.
  * prev_row (may be NULL) is the raw row above rows[0]. out: rows*(1+row_bytes). */
