@@ -71,7 +71,7 @@ class StreamingConcatenator:
             sources: Dict[int, TileSource] = {}
             for idx in needed:
                 try:
-                    sources[idx] = engine.read_tile_source(decoders[idx], headers[idx], idx)
+                    sources[idx] = engine.read_tile_source(decoders[idx], headers[idx], idx, bool(opts.device_inflate))
                 except StitchFailure:
                     raise
                 except Exception as e:  # decoder failures surface as stitch errors (:21-28)

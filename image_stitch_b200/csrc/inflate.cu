@@ -31,12 +31,23 @@ namespace {
 
 constexpr int TB = 11;                 // literal/length table index bits
 constexpr int TD = 9;                  // distance table index bits
-constexpr int INF_WARPS = 4;           // streams per CTA
+constexpr int INF_WARPS = 3;           // streams per CTA
+// Speculative lane-parallel Huffman walk: a window of 32 x SUBBITS code bits is cut into 32 subsequences, one
+// per lane; a lane keeps at most SUBCAP symbol records of its subsequence.
+constexpr uint32_t SUBBITS = 256u;
+constexpr uint32_t SUBCAP = 64u;
+constexpr uint32_t LANE_OUT = 96u;       // a lane stops once its records produce this many bytes (a match may add 257 more)
+constexpr uint32_t RES = 0xffffu;        // src[]: this byte of the window is final
+constexpr uint32_t ZWORDS = 32u * SUBBITS / 32u + 16u;   // staged code words: the window, its 127-bit lead-in, a symbol of overrun, one word of look-ahead
+constexpr uint32_t MAX_ROUNDS = 8u;
+constexpr uint32_t F_EOB = 1u << 8, F_ERR = 1u << 9;
 // The last 32 KiB of output (the farthest a match may reach) live in a per-warp shared-memory ring, so a match
-// copy never waits for L2; the ring is longer than that by a flush unit and a match, so nothing that is still to be
-// read or written out is overwritten.  Global memory is written from the ring, 512 bytes (one uint4 per lane) at a time.
-constexpr uint32_t WIN = 32768u + 1024u;
-static_assert(WIN % 16u == 0u && WIN >= 32768u + 512u + 258u + 16u, "ring: granule-aligned, a flush unit and a match of slack");
+// copy never waits for L2; the ring is longer than that by one window's output and a flush unit, so nothing that is
+// still to be read or written out is overwritten.  Global memory is written from the ring, 512 bytes (one uint4 per
+// lane) at a time.
+constexpr uint32_t OUTCAP = 4096u;   // most output bytes one window of subsequences may produce
+constexpr uint32_t WIN = 32768u + OUTCAP + 512u;
+static_assert(WIN % 16u == 0u, "ring: granule-aligned");
 constexpr uint32_t FULL = 0xffffffffu;
 constexpr uint32_t E_LONG = 0x30u;     // entry kind 3: code longer than the index, or no code at all
 
@@ -66,6 +77,9 @@ struct WarpSmem {
   uint8_t lens[320];      // literal/length code lengths, then the distance code lengths
   uint8_t clt[128];       // code-length code: symbol | bits << 5
   uint32_t pad[3];
+  __align__(16) uint32_t zw[ZWORDS];        // code words of the current window
+  uint32_t q[SUBCAP * 32u];                 // symbol records, record k of lane i at q[k * 32 + i]
+  uint16_t src[OUTCAP];                     // per output byte of the window: RES, or the window byte it copies
   __align__(16) uint8_t win[WIN];
 };
 static_assert(sizeof(WarpSmem) % 16 == 0, "rings must stay 16-byte aligned");
@@ -315,6 +329,82 @@ __device__ int read_dynamic_header(WarpSmem &sm, Bits &br, uint32_t lane, uint32
   return 0;
 }
 
+
+// ---- lane-private bit reader over the staged window ---------------------------------------------------------
+struct LaneBits {
+  const uint32_t *zw;
+  uint32_t wi;
+  unsigned long long bb;
+  uint32_t bc;
+  __device__ __forceinline__ void init(const uint32_t *z, uint32_t rel_bit) {
+    zw = z;
+    wi = rel_bit >> 5;
+    const uint32_t sh = rel_bit & 31u;
+    bb = (unsigned long long)(zw[wi] >> sh);
+    bc = 32u - sh;
+    wi++;
+  }
+  __device__ __forceinline__ void refill() {
+    if (bc <= 32u) { bb |= (unsigned long long)zw[wi] << bc; bc += 32u; wi++; }
+  }
+  __device__ __forceinline__ uint32_t peek(uint32_t n) const { return (uint32_t)bb & ((1u << n) - 1u); }
+  __device__ __forceinline__ void drop(uint32_t n) { bb >>= n; bc -= n; }
+  __device__ __forceinline__ uint32_t take(uint32_t n) { const uint32_t v = peek(n); drop(n); return v; }
+  __device__ __forceinline__ uint32_t pos() const { return wi * 32u - bc; }
+};
+
+// One lane walks the codes from window bit `start` until it reaches `limit`, the end of the block, an invalid code,
+// or SUBCAP records.  Records: literals = count << 24 | up to three bytes; match = 1 << 31 | (length - 3) << 15 |
+// (distance - 1).  Returns the bit after the last symbol taken; `n_flag` = records | F_EOB | F_ERR | status << 16.
+__device__ __forceinline__ uint32_t walk_sub(WarpSmem &sm, uint32_t start, uint32_t limit, uint32_t lane, uint32_t &n_flag, uint32_t &n_out) {
+  LaneBits lb;
+  lb.init(sm.zw, start);
+  uint32_t n = 0, flag = 0, out = 0;
+  uint32_t *q = sm.q + lane;
+  while (lb.pos() < limit && n < SUBCAP && out < LANE_OUT) {
+    lb.refill();
+    const uint32_t e = sm.lt[lb.peek(TB)];
+    uint32_t kind = (e >> 4) & 3u;
+    uint32_t rec = ((e >> 6) & 3u) << 24 | (e >> 8), lbase = e >> 16, lext = (e >> 8) & 15u, add = (e >> 6) & 3u;
+    if (kind == 3u) {
+      uint32_t L;
+      const int sy = canon_walk((uint32_t)lb.bb, sm.lc, sm.lsym, L);
+      if (sy < 0 || sy >= 286) { flag = F_ERR | ((uint32_t)INF_E_LITLEN_CODE << 16); break; }
+      lb.drop(L);
+      if (sy < 256) { kind = 0u; rec = (1u << 24) | (uint32_t)sy; add = 1u; }
+      else if (sy == 256) kind = 2u;
+      else { kind = 1u; lbase = c_lbase[sy - 257]; lext = c_lext[sy - 257]; }
+    } else {
+      lb.drop(e & 15u);
+    }
+    if (kind == 2u) { flag = F_EOB; break; }
+    if (kind == 1u) {
+      const uint32_t len = lbase + lb.take(lext);
+      lb.refill();
+      const uint32_t d = sm.dt[lb.peek(TD)];
+      uint32_t dbase = d >> 16, dext = (d >> 8) & 15u;
+      if ((d & 0x30u) == 0x30u) {
+        uint32_t L;
+        const int sy = canon_walk((uint32_t)lb.bb, sm.dc, sm.dsym, L);
+        if (sy < 0 || sy >= 30) { flag = F_ERR | ((uint32_t)INF_E_DIST_CODE << 16); break; }
+        lb.drop(L);
+        dbase = c_dbase[sy]; dext = c_dext[sy];
+      } else {
+        lb.drop(d & 15u);
+      }
+      const uint32_t dist = dbase + lb.take(dext);
+      rec = (1u << 31) | ((len - 3u) << 15) | (dist - 1u);
+      add = len;
+    }
+    q[n * 32u] = rec;
+    n++;
+    out += add;
+  }
+  n_flag = n | flag;
+  n_out = out;
+  return lb.pos();
+}
+
 __global__ void __launch_bounds__(INF_WARPS * 32) inflate_kernel(const InfStream *streams, InfResult *results, uint32_t n_streams) {
   extern __shared__ __align__(16) unsigned char inf_smem_raw[];
   const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
@@ -375,77 +465,142 @@ __global__ void __launch_bounds__(INF_WARPS * 32) inflate_kernel(const InfStream
         if (!err) err = build_tables(sm, nlen, ndist, lane);
       }
       if (err) goto done;
-      // ---- symbols of the block: every lane walks the same codes; output goes to the ring as it is decoded ----
+      // ---- symbols of the block, a window of 32 subsequences at a time ----
+      // Lane i walks the codes of subsequence i from a guessed start (a multiple of SUBBITS; lane 0's start is
+      // exact).  Huffman codes resynchronise: a walk that starts off a code boundary usually falls onto real
+      // boundaries before its subsequence ends, so its END is right although its start was not.  Each round,
+      // the lanes whose start differs from their left neighbour's end walk again from that end; when no start
+      // changes any more every lane's records are the true symbols (by induction from lane 0).  After MAX_ROUNDS
+      // the consistent prefix of lanes is used and the next window starts where it ended.  The records are then
+      // applied in order by the whole warp (literals by lanes 0..2, a match by the lanes below its length).
+      unsigned long long bitpos = br.consumed_bits();
       bool eob = false;
+      const uint32_t last_gran = (st.src_len - 1u) >> 4;
       while (!eob) {
-        br.refill();
-        const uint32_t e = sm.lt[br.peek(TB)];
-        uint32_t kind = (e >> 4) & 3u;
-        uint32_t lits = e >> 8, cnt = (e >> 6) & 3u, lbase = e >> 16, lext = (e >> 8) & 15u;
-        if (kind == 3u) {  // a code longer than TB bits (rare symbols), or none
-          uint32_t L;
-          const int sy = canon_walk((uint32_t)br.bb, sm.lc, sm.lsym, L);
-          if (sy < 0 || sy >= 286) { err = INF_E_LITLEN_CODE; break; }
-          br.drop(L);
-          if (sy < 256) { kind = 0u; lits = (uint32_t)sy; cnt = 1u; }
-          else if (sy == 256) kind = 2u;
-          else { kind = 1u; lbase = c_lbase[sy - 257]; lext = c_lext[sy - 257]; }
-        } else {
-          br.drop(e & 15u);
-        }
-        if (kind == 0u) {  // one to three literals: lanes 0..2 store them
-          if (lane < cnt) {
-            uint32_t q = wpos + lane;
-            q = q >= WIN ? q - WIN : q;
-            win[q] = (uint8_t)(lits >> (8u * lane));
-          }
-          pos += cnt; wpos += cnt;
-        } else if (kind == 2u) {
-          eob = true;
-        } else {
-          const uint32_t len = lbase + br.take(lext);
-          br.refill();
-          const uint32_t d = sm.dt[br.peek(TD)];
-          uint32_t dbase = d >> 16, dext = (d >> 8) & 15u;
-          if ((d & 0x30u) == 0x30u) {
-            uint32_t L;
-            const int sy = canon_walk((uint32_t)br.bb, sm.dc, sm.dsym, L);
-            if (sy < 0 || sy >= 30) { err = INF_E_DIST_CODE; break; }
-            br.drop(L);
-            dbase = c_dbase[sy]; dext = c_dext[sy];
-          } else {
-            br.drop(d & 15u);
-          }
-          const uint32_t dist = dbase + br.take(dext);
-          if (dist > pos) { err = INF_E_FAR; break; }
-          const uint32_t s0 = wpos >= dist ? wpos - dist : wpos + WIN - dist;
-          __syncwarp();  // the bytes this match copies may have been stored by other lanes
-          if (dist >= len) {
-            for (uint32_t j = lane; j < len; j += 32u) {
-              uint32_t sj = s0 + j, dj = wpos + j;
-              sj = sj >= WIN ? sj - WIN : sj;
-              dj = dj >= WIN ? dj - WIN : dj;
-              win[dj] = win[sj];
-            }
-          } else {       // the match overlaps its own output: a pattern of period `dist`
-            for (uint32_t j = lane; j < len; j += 32u) {
-              uint32_t sj = s0 + j % dist, dj = wpos + j;
-              sj = sj >= WIN ? sj - WIN : sj;
-              dj = dj >= WIN ? dj - WIN : dj;
-              win[dj] = win[sj];
-            }
-          }
-          pos += len; wpos += len;
-        }
-        wpos = wpos >= WIN ? wpos - WIN : wpos;
-        if (pos - flushed >= 512u || eob) {
+        const uint32_t a0 = (uint32_t)(bitpos >> 7);         // 16-byte granule the window starts in
+        const uint32_t rel0 = (uint32_t)(bitpos & 127ull);
+        for (uint32_t t = lane; t < ZWORDS / 4u; t += 32u)
+          reinterpret_cast<uint4 *>(sm.zw)[t] = __ldg(reinterpret_cast<const uint4 *>(st.src) + min(a0 + t, last_gran));
+        __syncwarp();
+        uint32_t start = rel0 + lane * SUBBITS;
+        const uint32_t limit = rel0 + (lane + 1u) * SUBBITS;
+        uint32_t end = 0, n_flag = 0, n_out = 0;
+        bool walk = true;
+        uint32_t bad = 0;   // lanes whose start is not their left neighbour's end
+        for (uint32_t round = 0;; round++) {
+          if (walk) end = walk_sub(sm, start, limit, lane, n_flag, n_out);
           __syncwarp();
-          ring_flush(win, dst, flushed, min(pos, cap), false, lane);
-          if (br.consumed_bits() > 8ull * st.src_len) { err = INF_E_EOF; break; }
-          if (pos > cap) { flags |= 1u; break; }  // more than the caller asked for: the rest is not needed
+          const uint32_t left_end = __shfl_up_sync(FULL, end, 1);
+          const uint32_t left_flag = __shfl_up_sync(FULL, n_flag, 1);
+          // nothing follows a subsequence that ended the block or failed: lanes to its right are not part of the chain
+          const bool chained = lane > 0u && (left_flag & (F_EOB | F_ERR)) == 0u;
+          walk = chained && start != left_end;
+          bad = __ballot_sync(FULL, walk);
+          if (bad == 0u || round + 1u >= MAX_ROUNDS) break;
+          if (walk) start = left_end;
         }
+        // lanes of the chain: up to the first stop (inclusive) and before the first inconsistent start
+        const uint32_t stops = __ballot_sync(FULL, (n_flag & (F_EOB | F_ERR)) != 0u);
+        uint32_t n_lanes = bad ? (uint32_t)__ffs(bad) - 1u : 32u;
+        if (stops) n_lanes = min(n_lanes, (uint32_t)__ffs(stops));
+        // ---- apply: every lane of the chain writes its own records' bytes; copies from bytes that another lane is
+        // producing in this same window are left as pointers and resolved afterwards by pointer jumping ----
+        uint32_t off = n_out;   // inclusive scan of the lanes' output sizes
+#pragma unroll
+        for (uint32_t d = 1; d < 32u; d <<= 1) {
+          const uint32_t v = __shfl_up_sync(FULL, off, d);
+          if (lane >= d) off += v;
+        }
+        n_lanes = min(n_lanes, (uint32_t)__popc(__ballot_sync(FULL, off <= OUTCAP)));  // sizes are positive sums: a prefix of lanes
+        const uint32_t total = __shfl_sync(FULL, off, n_lanes - 1u);
+        off -= n_out;
+        uint16_t *src = sm.src;
+        bool far = false;
+        if (lane < n_lanes) {
+          const uint32_t ni = n_flag & 0xffu;
+          uint32_t o = off;
+          for (uint32_t k = 0; k < ni; k++) {
+            const uint32_t r = sm.q[k * 32u + lane];
+            if ((int)r >= 0) {
+              const uint32_t cnt = r >> 24;
+              for (uint32_t t = 0; t < cnt; t++, o++) {
+                uint32_t sl = wpos + o;
+                sl = sl >= WIN ? sl - WIN : sl;
+                win[sl] = (uint8_t)(r >> (8u * t));
+                src[o] = (uint16_t)RES;
+              }
+            } else {
+              const uint32_t len = ((r >> 15) & 0xffu) + 3u, dist = (r & 0x7fffu) + 1u;
+              far = far || dist > pos + o;
+              for (uint32_t t = 0; t < len; t++, o++) {
+                uint32_t sl = wpos + o;
+                sl = sl >= WIN ? sl - WIN : sl;
+                const int rel = (int)o - (int)dist;
+                if (rel < 0) {                       // history: final
+                  int hs = (int)wpos + rel;
+                  hs = hs < 0 ? hs + (int)WIN : hs;
+                  win[sl] = win[hs];
+                  src[o] = (uint16_t)RES;
+                } else if ((uint32_t)rel >= off) {   // a byte this lane made itself: final, or a pointer to follow
+                  const uint32_t p = src[rel];
+                  if (p == RES) {
+                    uint32_t ps = wpos + (uint32_t)rel;
+                    ps = ps >= WIN ? ps - WIN : ps;
+                    win[sl] = win[ps];
+                  }
+                  src[o] = (uint16_t)p;
+                } else {
+                  src[o] = (uint16_t)rel;            // another lane's byte
+                }
+              }
+            }
+          }
+        }
+        if (__any_sync(FULL, far)) { err = INF_E_FAR; break; }
+        __syncwarp();
+        for (;;) {   // pointer jumping: a pointer always leads to a lower lane's region, so at most 5 rounds
+          bool open = false;
+          for (uint32_t x0 = 0; x0 < total; x0 += 32u) {
+            const uint32_t x = x0 + lane;
+            const uint32_t p = x < total ? src[x] : RES;
+            const uint32_t pp = p == RES ? 0u : p;
+            const uint32_t qn = src[pp];
+            uint32_t ps = wpos + pp;
+            ps = ps >= WIN ? ps - WIN : ps;
+            const uint8_t v = win[ps];
+            __syncwarp();
+            if (p != RES) {
+              if (qn == RES) {
+                uint32_t sl = wpos + x;
+                sl = sl >= WIN ? sl - WIN : sl;
+                win[sl] = v;
+                src[x] = (uint16_t)RES;
+              } else {
+                src[x] = (uint16_t)qn;
+                open = true;
+              }
+            }
+            __syncwarp();
+          }
+          if (!__any_sync(FULL, open)) break;
+        }
+        pos += total; wpos += total;
+        if (wpos >= WIN) wpos -= WIN;
+        ring_flush(win, dst, flushed, min(pos, cap), false, lane);
+        if (err) break;
+        const uint32_t last_flag = __shfl_sync(FULL, n_flag, n_lanes - 1u);
+        bitpos = ((unsigned long long)a0 << 7) + __shfl_sync(FULL, end, n_lanes - 1u);
+        if (last_flag & F_ERR) { err = (int)(last_flag >> 16); break; }
+        eob = (last_flag & F_EOB) != 0u;
+        if (bitpos > 8ull * st.src_len) { err = INF_E_EOF; break; }
+        if (pos > cap) { flags |= 1u; break; }  // more than the caller asked for: the rest is not needed
+        __syncwarp();
       }
+      __syncwarp();
+      ring_flush(win, dst, flushed, min(pos, cap), false, lane);
       if (err || (flags & 1u)) goto done;
+      br.init(st.src, st.src_len, (uint32_t)(bitpos >> 3));
+      br.drop((uint32_t)(bitpos & 7ull));
     }
     if (br.consumed_bits() > 8ull * st.src_len) { err = INF_E_EOF; goto done; }
     if (bfinal) break;

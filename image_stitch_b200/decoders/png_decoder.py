@@ -12,7 +12,7 @@ from __future__ import annotations
 
 from typing import Iterator, Optional, Tuple
 
-from ..png_container import read_png, parse_png_header, scanline_bytes
+from ..png_container import extract_idat, parse_png_chunks, read_png, parse_png_header, scanline_bytes
 from ..types import ImageHeader, PngHeader
 
 _CHANNELS = {0: 1, 2: 3, 3: 3, 4: 2, 6: 4}  # palette reported as 3 channels: png-decoder.ts:32-34
@@ -61,6 +61,13 @@ class PngBufferDecoder:
             self._header = header
             self._inflated = stream
         return self.png_header(), self._inflated
+
+    def deflated(self) -> Tuple[PngHeader, bytes]:
+        """The zlib stream itself (IDAT payloads concatenated, png-decoder.ts:100-117 before the
+        decompression stream): with the `device_inflate` option the GPU path starts here."""
+        chunks = parse_png_chunks(self._bytes())
+        self._header = parse_png_header(self._bytes())
+        return self._header, extract_idat(chunks)
 
     def scanlines(self) -> Iterator[bytes]:
         from .. import engine

@@ -160,10 +160,13 @@ class TileSource:
     interlace: int
 
 
-def read_tile_source(decoder, declared: PngHeader, image_idx: int) -> TileSource:
+def read_tile_source(decoder, declared: PngHeader, image_idx: int, device_inflate: bool = False) -> TileSource:
     """Fetches one input's pixel bytes.  Decoders offering ``inflated()`` hand over the
     still-filtered stream (GPU unfilter); any other ImageDecoder is drained
     through scanlines() with the reference's row checks (image-concat-core.ts:427-448)."""
+    if device_inflate and hasattr(decoder, "deflated"):
+        hdr, zstream = decoder.deflated()      # filtered == 2: the device inflates (SURVEY.md 8f.2)
+        return TileSource(hdr, zstream, 2, 1 if hdr.interlace_method == 1 else 0)
     if hasattr(decoder, "inflated"):
         hdr, stream = decoder.inflated()
         return TileSource(hdr, stream, 1, 1 if hdr.interlace_method == 1 else 0)

@@ -104,6 +104,9 @@ class ConcatOptions:
     # additive: DEFLATE the filtered rows on the device; the IDAT bytes then differ from the
     # host's zlib output but inflate to the same rows
     device_deflate: bool = False
+    # additive: PNG inputs cross the bus as their zlib streams and are inflated on the device;
+    # same pixels, and zlib's error messages when a stream is corrupt
+    device_inflate: bool = False
 
     @staticmethod
     def coerce(options: Union["ConcatOptions", dict]) -> "ConcatOptions":
@@ -113,13 +116,13 @@ class ConcatOptions:
             known = {
                 "inputs", "layout", "decoder_options", "decoders", "output_format", "jpeg_quality",
                 "background_color", "enable_alpha_blending", "on_progress", "devices", "band_rows",
-                "device_deflate",
+                "device_deflate", "device_inflate",
             }
             camel = {
                 "decoderOptions": "decoder_options", "outputFormat": "output_format",
                 "jpegQuality": "jpeg_quality", "backgroundColor": "background_color",
                 "enableAlphaBlending": "enable_alpha_blending", "onProgress": "on_progress",
-                "deviceDeflate": "device_deflate",
+                "deviceDeflate": "device_deflate", "deviceInflate": "device_inflate",
             }
             kw = {}
             for k, v in dict(options).items():

@@ -203,3 +203,42 @@ def test_job_reports_inflate_and_row_count_errors(ctx):
             job.run_band(0, T)
         assert e.value.code == _native.E_TRUNCATED
         assert str(e.value) == f"Expected {T} scanlines, decoded 10"     # png-decoder.ts:209-211
+
+
+# ---- through the public API ---------------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("opts", [
+    {"layout": {"columns": 3}},
+    {"layout": {"width": 100}},
+    {"layout": {"columns": 2}, "output_format": "jpeg", "jpeg_quality": 90},
+    {"layout": {"columns": 3}, "device_deflate": True},
+])
+def test_concat_to_buffer_with_device_inflate(opts):
+    names = ["basn2c08", "basn0g08", "basn6a08", "basi4a08", "basn2c16", "basi0g16", "basn0g01", "basi6a16"]
+    ins = [H.suite_bytes(n) for n in names]
+    want = stitch.concat_to_buffer(dict(opts, inputs=ins))
+    got = stitch.concat_to_buffer(dict(opts, inputs=ins, device_inflate=True))
+    if opts.get("output_format") == "jpeg":
+        assert got == want
+    else:
+        assert read_png(got) == read_png(want)      # same header, same filtered rows (deflate bytes may differ)
+
+
+def test_positioned_with_device_inflate_and_corrupt_input():
+    pos = [{"x": 0, "y": 0, "source": H.suite_bytes("basn2c08")}, {"x": 10, "y": 6, "source": H.suite_bytes("basi6a08")}]
+    want = stitch.concat_to_buffer({"inputs": pos, "layout": {}})
+    got = stitch.concat_to_buffer({"inputs": pos, "layout": {}, "deviceInflate": True})
+    assert read_png(got) == read_png(want)
+    # corrupt the zlib stream inside the container (chunk CRC fixed up): the reference reports pako's message
+    from image_stitch_b200.png_container import build_png, create_chunk
+    chunks = parse_png_chunks(H.suite_bytes("basn6a08"))
+    out = []
+    for c in chunks:
+        if c.type == "IDAT":
+            d = bytearray(c.data)
+            d[len(d) // 2] ^= 0xff
+            c = create_chunk("IDAT", bytes(d))
+        out.append(c)
+    with pytest.raises(Exception) as e:
+        stitch.concat_to_buffer({"inputs": [build_png(out)], "layout": {"columns": 1}, "device_inflate": True})
+    assert "Failed to stitch images" in str(e.value) and ("Inflate error" in str(e.value) or "scanlines" in str(e.value))
