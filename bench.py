@@ -371,10 +371,50 @@ def run_ours(args, rank: int, world: int, local_rank: int):
     torch.cuda.synchronize(dev)
     e2e_z_s = time.perf_counter() - t0
 
-    times = torch.tensor([ms_total, e2e_s * 1e3, e2e_z_s * 1e3], dtype=torch.float64, device=dev)
+    # ---- and with INFLATE on the device as well: zlib streams up the bus, deflate blocks down ---
+    import zlib
+    z_distinct = [zlib.compress(bytes(tiles[k][1]), 6) for k in range(N_DISTINCT)]
+    host_zin = []
+    for zd in z_distinct:
+        t = torch.empty(len(zd), dtype=torch.uint8, pin_memory=True)
+        t.copy_(torch.frombuffer(bytearray(zd), dtype=torch.uint8))
+        host_zin.append(t)
+    zin_bytes = sum(len(z_distinct[k % N_DISTINCT]) for k in range(n_tiles))
+
+    def add_zlib_tiles(j):
+        k = 0
+        for r in range(GRID):
+            for c in range(GRID):
+                zt = host_zin[k % N_DISTINCT]
+                j.add_tile(zt, length=zt.numel(), width=TILE, height=TILE, bit_depth=8, color_type=6, interlace=0,
+                           filtered=2, dst_x=c * TILE, dst_y=rank * CANVAS + r * TILE, z_index=0,
+                           image_idx=rank * GRID * GRID + k)
+                k += 1
+
+    def step_e2e_codec():
+        j = _native.Job(ctx, CANVAS, canvas_h, 8, _native.OUT_PNG_DEFLATE, False, bytes(4), band=(y0, y1))
+        add_zlib_tiles(j)
+        out, tm = j.run_band(y0, y1, out=host_z)
+        j.close()
+        return tm
+
+    step_e2e_codec()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        step_e2e_codec()
+    torch.cuda.synchronize(dev)
+    e2e_c_s = time.perf_counter() - t0
+    # the inflate kernel alone, inputs resident
+    with _native.Job(ctx, CANVAS, canvas_h, 8, _native.OUT_PNG_FILTERED, False, bytes(4), band=(y0, y1)) as ij:
+        add_zlib_tiles(ij)
+        ij.inflate()
+        inf_ms = min(ij.inflate(force=True)["decode_ms"] for _ in range(3))
+
+    times = torch.tensor([ms_total, e2e_s * 1e3, e2e_z_s * 1e3, e2e_c_s * 1e3, inf_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
-    ms_total, e2e_ms, e2e_z_ms = float(times[0]), float(times[1]), float(times[2])
+    ms_total, e2e_ms, e2e_z_ms, e2e_c_ms, inf_ms = (float(times[i]) for i in range(5))
 
     if rank != 0:
         ctx.close()
@@ -402,6 +442,12 @@ def run_ours(args, rank: int, world: int, local_rank: int):
                                "ms_per_step": e2e_z_ms / e2e_steps, "ratio": out_row * CANVAS / max(1, z_len),
                                "note": "same step, output as zlib-compatible deflate blocks made on the device "
                                        "(STITCH_OUT_PNG_DEFLATE); not the headline e2e, which stays filtered scanlines"},
+        "e2e_device_codec": {"value": px_step / (e2e_c_ms / e2e_steps / 1e3), "unit": "MPix/s",
+                             "h2d_bytes_per_step": zin_bytes * world, "d2h_bytes_per_step": z_len * world,
+                             "ms_per_step": e2e_c_ms / e2e_steps,
+                             "note": "same step with the tiles uploaded as their zlib streams (host zlib level 6) and "
+                                     "inflated on the device (filtered = 2, SURVEY 8f.2), output deflated on the device: "
+                                     "compressed bytes both ways; not the headline e2e"},
         "gpu_launches": value_launches,
         "roofline": {"bound": "hbm", "kernel": "composite+filter-select (kernels b+c)", "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": achieved / peak, "traffic": profiled_traffic_bytes(), "peak_source": peak_src,
@@ -409,7 +455,10 @@ def run_ours(args, rank: int, world: int, local_rank: int):
                      "algorithmic_bytes_per_launch": alg_bytes, "avg_ms": cmp_avg,
                      "frac_of_8TBps": achieved / 8000.0},
         "kernels": {"unfilter": {"avg_ms": dec_avg, "achieved_GBps": unf_achieved, "frac": unf_achieved / peak},
-                    "compose_filter": {"avg_ms": cmp_avg, "achieved_GBps": achieved, "frac": achieved / peak}},
+                    "compose_filter": {"avg_ms": cmp_avg, "achieved_GBps": achieved, "frac": achieved / peak},
+                    "inflate": {"avg_ms": inf_ms, "inflated_GBps": n_tiles * stream_len / (inf_ms / 1e3) / 1e9,
+                                "streams": n_tiles, "note": "one warp per zlib stream; serial inside a stream, "
+                                "so bounded by the warp's instruction latency, not by HBM"}},
     }
     if not args.no_cpu_baseline:
         threads = cpu_threads(args)

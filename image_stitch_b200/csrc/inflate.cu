@@ -31,12 +31,12 @@ namespace {
 
 constexpr int TB = 11;                 // literal/length table index bits
 constexpr int TD = 9;                  // distance table index bits
-constexpr int INF_WARPS = 3;           // streams per CTA
+constexpr int INF_WARPS = 2;           // streams per CTA
 // Speculative lane-parallel Huffman walk: a window of 32 x SUBBITS code bits is cut into 32 subsequences, one
 // per lane; a lane keeps at most SUBCAP symbol records of its subsequence.
-constexpr uint32_t SUBBITS = 256u;
-constexpr uint32_t SUBCAP = 64u;
-constexpr uint32_t LANE_OUT = 96u;       // a lane stops once its records produce this many bytes (a match may add 257 more)
+constexpr uint32_t SUBBITS = 512u;
+constexpr uint32_t SUBCAP = 96u;
+constexpr uint32_t LANE_OUT = 224u;      // a lane stops once its records produce this many bytes (a match may add 257 more)
 constexpr uint32_t RES = 0xffffu;        // src[]: this byte of the window is final
 constexpr uint32_t ZWORDS = 32u * SUBBITS / 32u + 16u;   // staged code words: the window, its 127-bit lead-in, a symbol of overrun, one word of look-ahead
 constexpr uint32_t MAX_ROUNDS = 8u;
@@ -45,7 +45,7 @@ constexpr uint32_t F_EOB = 1u << 8, F_ERR = 1u << 9;
 // copy never waits for L2; the ring is longer than that by one window's output and a flush unit, so nothing that is
 // still to be read or written out is overwritten.  Global memory is written from the ring, 512 bytes (one uint4 per
 // lane) at a time.
-constexpr uint32_t OUTCAP = 4096u;   // most output bytes one window of subsequences may produce
+constexpr uint32_t OUTCAP = 8192u;   // most output bytes one window of subsequences may produce
 constexpr uint32_t WIN = 32768u + OUTCAP + 512u;
 static_assert(WIN % 16u == 0u, "ring: granule-aligned");
 constexpr uint32_t FULL = 0xffffffffu;
