@@ -31,7 +31,7 @@ namespace {
 
 constexpr int TB = 11;                 // literal/length table index bits
 constexpr int TD = 9;                  // distance table index bits
-constexpr int INF_WARPS = 2;           // streams per CTA
+constexpr int INF_STREAMS = 2;         // streams per CTA, two warps each: one walks the codes, one produces the bytes
 // Speculative lane-parallel Huffman walk: a window of 32 x SUBBITS code bits is cut into 32 subsequences, one
 // per lane; a lane keeps at most SUBCAP symbol records of its subsequence.
 constexpr uint32_t SUBBITS = 512u;
@@ -68,6 +68,15 @@ struct Canon {            // one canonical Huffman code (RFC 1951 3.2.2)
   uint32_t next[16];      // first code of a length
 };
 
+// One message from the warp that walks the codes to the warp that produces the bytes.
+enum MsgKind : uint32_t { MSG_WINDOW = 0, MSG_STORED = 1, MSG_END = 2 };
+struct Msg {
+  uint32_t kind;
+  uint32_t n_lanes, total;   // WINDOW: lanes of the chain, bytes they produce
+  uint32_t a, b, c;          // STORED: byte offset in the stream, length.  END: status, Adler-32 trailer, flags
+  uint32_t n[32], off[32];   // WINDOW: records and first output byte of every lane
+};
+
 struct WarpSmem {
   uint32_t lt[1 << TB];
   uint32_t dt[1 << TD];
@@ -78,7 +87,8 @@ struct WarpSmem {
   uint8_t clt[128];       // code-length code: symbol | bits << 5
   uint32_t pad[3];
   __align__(16) uint32_t zw[ZWORDS];        // code words of the current window
-  uint32_t q[SUBCAP * 32u];                 // symbol records, record k of lane i at q[k * 32 + i]
+  uint32_t q[2][SUBCAP * 32u];              // symbol records (two windows in flight), record k of lane i at q[.][k * 32 + i]
+  Msg msg[2];                               // what the walking warp hands to the applying warp with them
   uint16_t src[OUTCAP];                     // per output byte of the window: RES, or the window byte it copies
   __align__(16) uint8_t win[WIN];
 };
@@ -356,69 +366,88 @@ struct LaneBits {
 // One lane walks the codes from window bit `start` until it reaches `limit`, the end of the block, an invalid code,
 // or SUBCAP records.  Records: literals = count << 24 | up to three bytes; match = 1 << 31 | (length - 3) << 15 |
 // (distance - 1).  Returns the bit after the last symbol taken; `n_flag` = records | F_EOB | F_ERR | status << 16.
-__device__ __forceinline__ uint32_t walk_sub(WarpSmem &sm, uint32_t start, uint32_t limit, uint32_t lane, uint32_t &n_flag, uint32_t &n_out) {
+// `mask`: the lanes that walk in this round.  They step together: the loop condition is a vote, so the lanes meet
+// again at every symbol instead of each running its own copy of the loop.
+__device__ __forceinline__ uint32_t walk_sub(WarpSmem &sm, uint32_t *qbuf, uint32_t start, uint32_t limit, uint32_t lane, uint32_t mask,
+                                             uint32_t &n_flag, uint32_t &n_out) {
   LaneBits lb;
   lb.init(sm.zw, start);
   uint32_t n = 0, flag = 0, out = 0;
-  uint32_t *q = sm.q + lane;
-  while (lb.pos() < limit && n < SUBCAP && out < LANE_OUT) {
-    lb.refill();
-    const uint32_t e = sm.lt[lb.peek(TB)];
-    uint32_t kind = (e >> 4) & 3u;
-    uint32_t rec = ((e >> 6) & 3u) << 24 | (e >> 8), lbase = e >> 16, lext = (e >> 8) & 15u, add = (e >> 6) & 3u;
-    if (kind == 3u) {
-      uint32_t L;
-      const int sy = canon_walk((uint32_t)lb.bb, sm.lc, sm.lsym, L);
-      if (sy < 0 || sy >= 286) { flag = F_ERR | ((uint32_t)INF_E_LITLEN_CODE << 16); break; }
-      lb.drop(L);
-      if (sy < 256) { kind = 0u; rec = (1u << 24) | (uint32_t)sy; add = 1u; }
-      else if (sy == 256) kind = 2u;
-      else { kind = 1u; lbase = c_lbase[sy - 257]; lext = c_lext[sy - 257]; }
-    } else {
-      lb.drop(e & 15u);
-    }
-    if (kind == 2u) { flag = F_EOB; break; }
-    if (kind == 1u) {
-      const uint32_t len = lbase + lb.take(lext);
+  uint32_t *q = qbuf + lane;
+  bool live = true;
+  for (;;) {
+    live = live && lb.pos() < limit && n < SUBCAP && out < LANE_OUT;
+    if (!__any_sync(mask, live)) break;
+    if (live) {
       lb.refill();
-      const uint32_t d = sm.dt[lb.peek(TD)];
-      uint32_t dbase = d >> 16, dext = (d >> 8) & 15u;
-      if ((d & 0x30u) == 0x30u) {
-        uint32_t L;
-        const int sy = canon_walk((uint32_t)lb.bb, sm.dc, sm.dsym, L);
-        if (sy < 0 || sy >= 30) { flag = F_ERR | ((uint32_t)INF_E_DIST_CODE << 16); break; }
-        lb.drop(L);
-        dbase = c_dbase[sy]; dext = c_dext[sy];
+      const uint32_t e = sm.lt[lb.peek(TB)];
+      uint32_t kind = (e >> 4) & 3u;
+      uint32_t rec = ((e >> 6) & 3u) << 24 | (e >> 8), lbase = e >> 16, lext = (e >> 8) & 15u, add = (e >> 6) & 3u;
+      if (kind == 3u) {
+        uint32_t L = 0;
+        const int sy = canon_walk((uint32_t)lb.bb, sm.lc, sm.lsym, L);
+        if (sy < 0 || sy >= 286) { flag = F_ERR | ((uint32_t)INF_E_LITLEN_CODE << 16); live = false; }
+        else {
+          lb.drop(L);
+          if (sy < 256) { kind = 0u; rec = (1u << 24) | (uint32_t)sy; add = 1u; }
+          else if (sy == 256) kind = 2u;
+          else { kind = 1u; lbase = c_lbase[sy - 257]; lext = c_lext[sy - 257]; }
+        }
       } else {
-        lb.drop(d & 15u);
+        lb.drop(e & 15u);
       }
-      const uint32_t dist = dbase + lb.take(dext);
-      rec = (1u << 31) | ((len - 3u) << 15) | (dist - 1u);
-      add = len;
+      if (live && kind == 2u) { flag = F_EOB; live = false; }
+      if (live && kind == 1u) {
+        const uint32_t len = lbase + lb.take(lext);
+        lb.refill();
+        const uint32_t d = sm.dt[lb.peek(TD)];
+        uint32_t dbase = d >> 16, dext = (d >> 8) & 15u;
+        if ((d & 0x30u) == 0x30u) {
+          uint32_t L = 0;
+          const int sy = canon_walk((uint32_t)lb.bb, sm.dc, sm.dsym, L);
+          if (sy < 0 || sy >= 30) { flag = F_ERR | ((uint32_t)INF_E_DIST_CODE << 16); live = false; }
+          else { lb.drop(L); dbase = c_dbase[sy]; dext = c_dext[sy]; }
+        } else {
+          lb.drop(d & 15u);
+        }
+        const uint32_t dist = dbase + lb.take(dext);
+        rec = (1u << 31) | ((len - 3u) << 15) | (dist - 1u);
+        add = len;
+      }
+      if (live) {
+        q[n * 32u] = rec;
+        n++;
+        out += add;
+      }
     }
-    q[n * 32u] = rec;
-    n++;
-    out += add;
   }
   n_flag = n | flag;
   n_out = out;
   return lb.pos();
 }
 
-__global__ void __launch_bounds__(INF_WARPS * 32) inflate_kernel(const InfStream *streams, InfResult *results, uint32_t n_streams) {
-  extern __shared__ __align__(16) unsigned char inf_smem_raw[];
-  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-  const uint32_t sid = blockIdx.x * INF_WARPS + warp;
-  if (sid >= n_streams) return;
-  WarpSmem &sm = reinterpret_cast<WarpSmem *>(inf_smem_raw)[warp];
-  const InfStream st = streams[sid];
-  uint8_t *dst = st.dst;
-  uint8_t *win = sm.win;
+// ---- two warps per stream ---------------------------------------------------------------------------------------
+// The WALKER reads headers, builds tables and walks the codes of a window into records; the APPLIER turns the
+// records of the window before into bytes (ring, pointer jumping, HBM) meanwhile.  They meet at four named
+// barriers per stream (slot s of 2: FULL_s "records are there", EMPTY_s "slot may be refilled"); a barrier counts 64
+// threads, 32 that arrive and go on and 32 that wait.
+__device__ __forceinline__ void bar_wait(uint32_t id) { asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory"); }
+__device__ __forceinline__ void bar_signal(uint32_t id) { asm volatile("bar.arrive %0, 64;" ::"r"(id) : "memory"); }
+
+struct Link {
+  uint32_t full0, empty0;   // barrier ids of slot 0; slot 1 is +1
+  uint32_t slot;
+};
+
+__device__ void walker(WarpSmem &sm, const InfStream &st, Link lk, const uint32_t lane) {
   const uint32_t cap = st.dst_cap;
-  uint32_t pos = 0, flushed = 0, wpos = 0;  // wpos: pos modulo the ring
+  unsigned long long opos = 0;   // bytes produced so far (the applier's `pos` after it has caught up)
   int err = 0;
   uint32_t adler_stored = 0, flags = 0;
   Bits br;
+  // every message: wait until the slot is free, fill it, hand it over
+  auto acquire = [&]() -> Msg & { bar_wait(lk.empty0 + lk.slot); return sm.msg[lk.slot]; };
+  auto publish = [&]() { __syncwarp(); bar_signal(lk.full0 + lk.slot); lk.slot ^= 1u; };
 
   if (st.src_len < 2u) { err = INF_E_EOF; goto done; }
   br.init(st.src, st.src_len, 0u);
@@ -442,16 +471,10 @@ __global__ void __launch_bounds__(INF_WARPS * 32) inflate_kernel(const InfStream
       if ((len ^ 0xffffu) != nlen) { err = INF_E_STORED; goto done; }
       const unsigned long long at = br.consumed_bits() >> 3;
       if (at + len > st.src_len) { err = INF_E_EOF; goto done; }
-      const uint8_t *s = st.src + at;
-      for (uint32_t done = 0; done < len;) {   // through the ring, a piece at a time (later matches may reach back into it)
-        const uint32_t n = min(len - done, 4096u);
-        for (uint32_t j = lane; j < n; j += 32u) win[(pos + j) % WIN] = __ldg(s + done + j);
-        pos += n; done += n;
-        __syncwarp();
-        ring_flush(win, dst, flushed, min(pos, cap), false, lane);
-        __syncwarp();
-      }
-      wpos = pos % WIN;
+      Msg &m = acquire();
+      if (lane == 0u) { m.kind = MSG_STORED; m.a = (uint32_t)at; m.b = len; }
+      publish();
+      opos += len;
       br.init(st.src, st.src_len, (uint32_t)at + len);
     } else {
       if (btype == 1u) {
@@ -471,8 +494,7 @@ __global__ void __launch_bounds__(INF_WARPS * 32) inflate_kernel(const InfStream
       // boundaries before its subsequence ends, so its END is right although its start was not.  Each round,
       // the lanes whose start differs from their left neighbour's end walk again from that end; when no start
       // changes any more every lane's records are the true symbols (by induction from lane 0).  After MAX_ROUNDS
-      // the consistent prefix of lanes is used and the next window starts where it ended.  The records are then
-      // applied in order by the whole warp (literals by lanes 0..2, a match by the lanes below its length).
+      // the consistent prefix of lanes is used and the next window starts where it ended.
       unsigned long long bitpos = br.consumed_bits();
       bool eob = false;
       const uint32_t last_gran = (st.src_len - 1u) >> 4;
@@ -481,6 +503,8 @@ __global__ void __launch_bounds__(INF_WARPS * 32) inflate_kernel(const InfStream
         const uint32_t rel0 = (uint32_t)(bitpos & 127ull);
         for (uint32_t t = lane; t < ZWORDS / 4u; t += 32u)
           reinterpret_cast<uint4 *>(sm.zw)[t] = __ldg(reinterpret_cast<const uint4 *>(st.src) + min(a0 + t, last_gran));
+        Msg &m = acquire();    // also orders the staging stores before the walks
+        uint32_t *qbuf = sm.q[lk.slot];
         __syncwarp();
         uint32_t start = rel0 + lane * SUBBITS;
         const uint32_t limit = rel0 + (lane + 1u) * SUBBITS;
@@ -488,7 +512,7 @@ __global__ void __launch_bounds__(INF_WARPS * 32) inflate_kernel(const InfStream
         bool walk = true;
         uint32_t bad = 0;   // lanes whose start is not their left neighbour's end
         for (uint32_t round = 0;; round++) {
-          if (walk) end = walk_sub(sm, start, limit, lane, n_flag, n_out);
+          if (walk) end = walk_sub(sm, qbuf, start, limit, lane, round ? bad : FULL, n_flag, n_out);
           __syncwarp();
           const uint32_t left_end = __shfl_up_sync(FULL, end, 1);
           const uint32_t left_flag = __shfl_up_sync(FULL, n_flag, 1);
@@ -503,8 +527,6 @@ __global__ void __launch_bounds__(INF_WARPS * 32) inflate_kernel(const InfStream
         const uint32_t stops = __ballot_sync(FULL, (n_flag & (F_EOB | F_ERR)) != 0u);
         uint32_t n_lanes = bad ? (uint32_t)__ffs(bad) - 1u : 32u;
         if (stops) n_lanes = min(n_lanes, (uint32_t)__ffs(stops));
-        // ---- apply: every lane of the chain writes its own records' bytes; copies from bytes that another lane is
-        // producing in this same window are left as pointers and resolved afterwards by pointer jumping ----
         uint32_t off = n_out;   // inclusive scan of the lanes' output sizes
 #pragma unroll
         for (uint32_t d = 1; d < 32u; d <<= 1) {
@@ -513,98 +535,25 @@ __global__ void __launch_bounds__(INF_WARPS * 32) inflate_kernel(const InfStream
         }
         n_lanes = min(n_lanes, (uint32_t)__popc(__ballot_sync(FULL, off <= OUTCAP)));  // sizes are positive sums: a prefix of lanes
         const uint32_t total = __shfl_sync(FULL, off, n_lanes - 1u);
-        off -= n_out;
-        uint16_t *src = sm.src;
-        bool far = false;
-        if (lane < n_lanes) {
-          const uint32_t ni = n_flag & 0xffu;
-          uint32_t o = off;
-          for (uint32_t k = 0; k < ni; k++) {
-            const uint32_t r = sm.q[k * 32u + lane];
-            if ((int)r >= 0) {
-              const uint32_t cnt = r >> 24;
-              for (uint32_t t = 0; t < cnt; t++, o++) {
-                uint32_t sl = wpos + o;
-                sl = sl >= WIN ? sl - WIN : sl;
-                win[sl] = (uint8_t)(r >> (8u * t));
-                src[o] = (uint16_t)RES;
-              }
-            } else {
-              const uint32_t len = ((r >> 15) & 0xffu) + 3u, dist = (r & 0x7fffu) + 1u;
-              far = far || dist > pos + o;
-              for (uint32_t t = 0; t < len; t++, o++) {
-                uint32_t sl = wpos + o;
-                sl = sl >= WIN ? sl - WIN : sl;
-                const int rel = (int)o - (int)dist;
-                if (rel < 0) {                       // history: final
-                  int hs = (int)wpos + rel;
-                  hs = hs < 0 ? hs + (int)WIN : hs;
-                  win[sl] = win[hs];
-                  src[o] = (uint16_t)RES;
-                } else if ((uint32_t)rel >= off) {   // a byte this lane made itself: final, or a pointer to follow
-                  const uint32_t p = src[rel];
-                  if (p == RES) {
-                    uint32_t ps = wpos + (uint32_t)rel;
-                    ps = ps >= WIN ? ps - WIN : ps;
-                    win[sl] = win[ps];
-                  }
-                  src[o] = (uint16_t)p;
-                } else {
-                  src[o] = (uint16_t)rel;            // another lane's byte
-                }
-              }
-            }
-          }
-        }
-        if (__any_sync(FULL, far)) { err = INF_E_FAR; break; }
-        __syncwarp();
-        for (;;) {   // pointer jumping: a pointer always leads to a lower lane's region, so at most 5 rounds
-          bool open = false;
-          for (uint32_t x0 = 0; x0 < total; x0 += 32u) {
-            const uint32_t x = x0 + lane;
-            const uint32_t p = x < total ? src[x] : RES;
-            const uint32_t pp = p == RES ? 0u : p;
-            const uint32_t qn = src[pp];
-            uint32_t ps = wpos + pp;
-            ps = ps >= WIN ? ps - WIN : ps;
-            const uint8_t v = win[ps];
-            __syncwarp();
-            if (p != RES) {
-              if (qn == RES) {
-                uint32_t sl = wpos + x;
-                sl = sl >= WIN ? sl - WIN : sl;
-                win[sl] = v;
-                src[x] = (uint16_t)RES;
-              } else {
-                src[x] = (uint16_t)qn;
-                open = true;
-              }
-            }
-            __syncwarp();
-          }
-          if (!__any_sync(FULL, open)) break;
-        }
-        pos += total; wpos += total;
-        if (wpos >= WIN) wpos -= WIN;
-        ring_flush(win, dst, flushed, min(pos, cap), false, lane);
-        if (err) break;
+        m.n[lane] = n_flag & 0xffu;
+        m.off[lane] = off - n_out;
+        if (lane == 0u) { m.kind = MSG_WINDOW; m.n_lanes = n_lanes; m.total = total; }
+        publish();
+        opos += total;
         const uint32_t last_flag = __shfl_sync(FULL, n_flag, n_lanes - 1u);
         bitpos = ((unsigned long long)a0 << 7) + __shfl_sync(FULL, end, n_lanes - 1u);
         if (last_flag & F_ERR) { err = (int)(last_flag >> 16); break; }
         eob = (last_flag & F_EOB) != 0u;
         if (bitpos > 8ull * st.src_len) { err = INF_E_EOF; break; }
-        if (pos > cap) { flags |= 1u; break; }  // more than the caller asked for: the rest is not needed
-        __syncwarp();
+        if (opos > cap) { flags |= 1u; break; }  // more than the caller asked for: the rest is not needed
       }
-      __syncwarp();
-      ring_flush(win, dst, flushed, min(pos, cap), false, lane);
       if (err || (flags & 1u)) goto done;
       br.init(st.src, st.src_len, (uint32_t)(bitpos >> 3));
       br.drop((uint32_t)(bitpos & 7ull));
     }
     if (br.consumed_bits() > 8ull * st.src_len) { err = INF_E_EOF; goto done; }
     if (bfinal) break;
-    if (pos > cap) { flags |= 1u; goto done; }
+    if (opos > cap) { flags |= 1u; goto done; }
   }
   {  // Adler-32 trailer (RFC 1950), big-endian, on the next byte boundary
     const unsigned long long at = (br.consumed_bits() + 7ull) >> 3;
@@ -614,13 +563,146 @@ __global__ void __launch_bounds__(INF_WARPS * 32) inflate_kernel(const InfStream
     flags |= 2u;  // trailer read: the Adler kernel compares
   }
 done:
+  Msg &m = acquire();
+  if (lane == 0u) { m.kind = MSG_END; m.a = (uint32_t)err; m.b = adler_stored; m.c = flags; }
+  publish();
+}
+
+__device__ void applier(WarpSmem &sm, const InfStream &st, InfResult *results, Link lk, const uint32_t lane) {
+  uint8_t *dst = st.dst;
+  uint8_t *win = sm.win;
+  uint16_t *src = sm.src;
+  const uint32_t cap = st.dst_cap;
+  uint32_t pos = 0, flushed = 0, wpos = 0;  // wpos: pos modulo the ring
+  uint32_t err = 0, end_status = 0, adler_stored = 0, flags = 0;
+  bar_signal(lk.empty0);       // both slots start empty
+  bar_signal(lk.empty0 + 1u);
+  for (;;) {
+    bar_wait(lk.full0 + lk.slot);
+    const Msg &m = sm.msg[lk.slot];
+    const uint32_t kind = m.kind;
+    if (kind == MSG_END) { end_status = m.a; adler_stored = m.b; flags = m.c; break; }
+    if (kind == MSG_STORED) {
+      const uint8_t *s = st.src + m.a;
+      const uint32_t len = m.b;
+      bar_signal(lk.empty0 + lk.slot);
+      lk.slot ^= 1u;
+      if (err) continue;
+      for (uint32_t done = 0; done < len;) {   // through the ring, a piece at a time (later matches may reach back into it)
+        const uint32_t n = min(len - done, 4096u);
+        for (uint32_t j = lane; j < n; j += 32u) win[(pos + j) % WIN] = __ldg(s + done + j);
+        pos += n; done += n;
+        __syncwarp();
+        ring_flush(win, dst, flushed, min(pos, cap), false, lane);
+        __syncwarp();
+      }
+      wpos = pos % WIN;
+      continue;
+    }
+    // ---- a window: every lane of the chain writes its own records' bytes; copies from bytes that another lane is
+    // producing in this same window are left as pointers and resolved afterwards by pointer jumping ----
+    const uint32_t n_lanes = m.n_lanes, total = m.total;
+    const uint32_t off = m.off[lane], ni = m.n[lane];
+    const uint32_t *q = sm.q[lk.slot];
+    bool far = false;
+    {
+      uint32_t o = off;
+      const uint32_t my_n = lane < n_lanes && !err ? ni : 0u;
+      for (uint32_t k = 0; __any_sync(FULL, k < my_n); k++) {   // a vote per record: the lanes stay in step
+        if (k >= my_n) continue;
+        const uint32_t r = q[k * 32u + lane];
+        if ((int)r >= 0) {
+          const uint32_t cnt = r >> 24;
+          for (uint32_t t = 0; t < cnt; t++, o++) {
+            uint32_t sl = wpos + o;
+            sl = sl >= WIN ? sl - WIN : sl;
+            win[sl] = (uint8_t)(r >> (8u * t));
+            src[o] = (uint16_t)RES;
+          }
+        } else {
+          const uint32_t len = ((r >> 15) & 0xffu) + 3u, dist = (r & 0x7fffu) + 1u;
+          far = far || dist > pos + o;
+          for (uint32_t t = 0; t < len; t++, o++) {
+            uint32_t sl = wpos + o;
+            sl = sl >= WIN ? sl - WIN : sl;
+            const int rel = (int)o - (int)dist;
+            if (rel < 0) {                       // history: final
+              int hs = (int)wpos + rel;
+              hs = hs < 0 ? hs + (int)WIN : hs;
+              win[sl] = win[hs];
+              src[o] = (uint16_t)RES;
+            } else if ((uint32_t)rel >= off) {   // a byte this lane made itself: final, or a pointer to follow
+              const uint32_t p = src[rel];
+              if (p == RES) {
+                uint32_t ps = wpos + (uint32_t)rel;
+                ps = ps >= WIN ? ps - WIN : ps;
+                win[sl] = win[ps];
+              }
+              src[o] = (uint16_t)p;
+            } else {
+              src[o] = (uint16_t)rel;            // another lane's byte
+            }
+          }
+        }
+      }
+    }
+    __syncwarp();
+    bar_signal(lk.empty0 + lk.slot);   // the records are consumed: the walker may refill the slot
+    lk.slot ^= 1u;
+    if (err) continue;
+    if (__any_sync(FULL, far)) { err = INF_E_FAR; continue; }
+    for (;;) {   // pointer jumping: a pointer always leads to a lower lane's region, so at most 5 rounds
+      bool open = false;
+      for (uint32_t x0 = 0; x0 < total; x0 += 32u) {
+        const uint32_t x = x0 + lane;
+        const uint32_t p = x < total ? src[x] : RES;
+        const uint32_t pp = p == RES ? 0u : p;
+        const uint32_t qn = src[pp];
+        uint32_t ps = wpos + pp;
+        ps = ps >= WIN ? ps - WIN : ps;
+        const uint8_t v = win[ps];
+        __syncwarp();
+        if (p != RES) {
+          if (qn == RES) {
+            uint32_t sl = wpos + x;
+            sl = sl >= WIN ? sl - WIN : sl;
+            win[sl] = v;
+            src[x] = (uint16_t)RES;
+          } else {
+            src[x] = (uint16_t)qn;
+            open = true;
+          }
+        }
+        __syncwarp();
+      }
+      if (!__any_sync(FULL, open)) break;
+    }
+    pos += total; wpos += total;
+    if (wpos >= WIN) wpos -= WIN;
+    ring_flush(win, dst, flushed, min(pos, cap), false, lane);
+  }
   __syncwarp();
   ring_flush(win, dst, flushed, min(pos, cap), true, lane);
   if (lane == 0u) {
     InfResult r;
-    r.status = (uint32_t)err; r.out_len = pos < cap ? pos : cap; r.adler_stored = adler_stored; r.flags = flags;
+    r.status = err ? err : end_status; r.out_len = pos < cap ? pos : cap; r.adler_stored = adler_stored;
+    r.flags = err ? 0u : flags;
     results[st.slot] = r;
   }
+}
+
+__global__ void __launch_bounds__(INF_STREAMS * 64) inflate_kernel(const InfStream *streams, InfResult *results, uint32_t n_streams) {
+  extern __shared__ __align__(16) unsigned char inf_smem_raw[];
+  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  const uint32_t pair = warp >> 1;
+  const uint32_t sid = blockIdx.x * INF_STREAMS + pair;
+  if (sid >= n_streams) return;
+  WarpSmem &sm = reinterpret_cast<WarpSmem *>(inf_smem_raw)[pair];
+  const InfStream st = streams[sid];
+  Link lk;
+  lk.full0 = 1u + 4u * pair; lk.empty0 = 3u + 4u * pair; lk.slot = 0u;   // barrier 0 is __syncthreads'
+  if (warp & 1u) applier(sm, st, results, lk, lane);
+  else walker(sm, st, lk, lane);
 }
 
 // Adler-32 of every inflated stream against its trailer: one CTA per stream.  For bytes d[0..N):
@@ -672,13 +754,13 @@ __global__ void __launch_bounds__(256) inflate_adler_kernel(const InfStream *str
 cudaError_t launch_inflate(const InfStream *d_streams, InfResult *d_results, uint32_t n_streams, cudaStream_t st) {
   if (!n_streams) return cudaSuccess;
   static bool attr = false;
-  const size_t smem = sizeof(WarpSmem) * INF_WARPS;
+  const size_t smem = sizeof(WarpSmem) * INF_STREAMS;
   if (!attr) {
     cudaError_t e = cudaFuncSetAttribute(inflate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     attr = true;
   }
-  inflate_kernel<<<(n_streams + INF_WARPS - 1) / INF_WARPS, INF_WARPS * 32, smem, st>>>(d_streams, d_results, n_streams);
+  inflate_kernel<<<(n_streams + INF_STREAMS - 1) / INF_STREAMS, INF_STREAMS * 64, smem, st>>>(d_streams, d_results, n_streams);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   inflate_adler_kernel<<<n_streams, 256, 0, st>>>(d_streams, d_results);
