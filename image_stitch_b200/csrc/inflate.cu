@@ -4,11 +4,17 @@
 // inflated, still filtered stream that kernel (a) starts from, written straight into the tile's device buffer.
 //
 // DEFLATE decoding is serial inside a stream (a code's position depends on every code before it), so the
-// parallelism is across tiles: ONE WARP PER STREAM.  Inside the warp the bit reader and the Huffman walk run
-// redundantly in all 32 lanes (identical registers, broadcast shared-memory reads, no divergence), so every
-// lane knows every symbol without a shuffle: literals are stored by lanes 0..2, a match is copied by the lanes
-// below its length, straight into a shared-memory ring that holds the last 32 KiB of output and is written out
-// in 512-byte units.
+// parallelism across tiles is one stream per warp PAIR, and the work inside a stream is made parallel by
+// speculation:
+//
+//   walk     a window of 32 x 512 code bits is cut into 32 subsequences; lane i walks subsequence i from a guessed
+//            start and keeps its symbols as records.  Huffman codes resynchronise, so the walk usually ends on a true
+//            code boundary; lanes whose start differs from their left neighbour's end walk again until nothing
+//            changes (exact by induction from lane 0), else the consistent prefix of lanes is taken
+//   apply    every lane writes its own records' bytes into a shared-memory ring holding the last 32 KiB of output;
+//            copies from bytes another lane produces in the same window stay 16-bit pointers, resolved for all bytes
+//            in parallel by pointer jumping; the ring goes to HBM in 16-byte granules per lane
+//   pipeline the first warp of the pair walks window w+1 while the second applies window w (named barriers)
 //
 //   tables   per dynamic block, built by the warp in shared memory: canonical code from the code lengths
 //            (count by length, stable rank by __match_any), an 11-bit single-symbol table filled symbol-parallel,
@@ -36,6 +42,9 @@ constexpr int INF_STREAMS = 2;         // streams per CTA, two warps each: one w
 // per lane; a lane keeps at most SUBCAP symbol records of its subsequence.
 constexpr uint32_t SUBBITS = 512u;
 constexpr uint32_t SUBCAP = 96u;
+constexpr uint32_t QHEAD = 16u;          // record rows in front of a lane's list: a re-walked prefix may be longer than the one it replaces
+constexpr uint32_t QROWS = SUBCAP + QHEAD;
+constexpr uint32_t TQCAP = 32u;          // records of a re-walk kept aside until it meets the old walk
 constexpr uint32_t LANE_OUT = 224u;      // a lane stops once its records produce this many bytes (a match may add 257 more)
 constexpr uint32_t RES = 0xffffu;        // src[]: this byte of the window is final
 constexpr uint32_t ZWORDS = 32u * SUBBITS / 32u + 16u;   // staged code words: the window, its 127-bit lead-in, a symbol of overrun, one word of look-ahead
@@ -75,6 +84,7 @@ struct Msg {
   uint32_t n_lanes, total;   // WINDOW: lanes of the chain, bytes they produce
   uint32_t a, b, c;          // STORED: byte offset in the stream, length.  END: status, Adler-32 trailer, flags
   uint32_t n[32], off[32];   // WINDOW: records and first output byte of every lane
+  uint32_t base[32];         // WINDOW: row of the lane's first record
 };
 
 struct WarpSmem {
@@ -87,12 +97,14 @@ struct WarpSmem {
   uint8_t clt[128];       // code-length code: symbol | bits << 5
   uint32_t pad[3];
   __align__(16) uint32_t zw[ZWORDS];        // code words of the current window
-  uint32_t q[2][SUBCAP * 32u];              // symbol records (two windows in flight), record k of lane i at q[.][k * 32 + i]
+  uint32_t q[2][QROWS * 32u];               // symbol records (two windows in flight), record k of lane i at q[.][(base_i + k) * 32 + i]
+  uint16_t bpos[SUBCAP * 32u];              // first walk of the window: the bit each record starts at
   Msg msg[2];                               // what the walking warp hands to the applying warp with them
   uint16_t src[OUTCAP];                     // per output byte of the window: RES, or the window byte it copies
   __align__(16) uint8_t win[WIN];
 };
 static_assert(sizeof(WarpSmem) % 16 == 0, "rings must stay 16-byte aligned");
+static_assert(TQCAP * 32u * 4u <= sizeof(uint16_t) * (1u << TB), "the re-walk records borrow the single-symbol table, which only the table build uses");
 
 // ring -> global, whole 512-byte units below `upto` (all of it with `all`); granules may run past `upto` into
 // the 16 bytes of slack every destination buffer has
@@ -366,62 +378,129 @@ struct LaneBits {
 // One lane walks the codes from window bit `start` until it reaches `limit`, the end of the block, an invalid code,
 // or SUBCAP records.  Records: literals = count << 24 | up to three bytes; match = 1 << 31 | (length - 3) << 15 |
 // (distance - 1).  Returns the bit after the last symbol taken; `n_flag` = records | F_EOB | F_ERR | status << 16.
+// One symbol at the lane's position: 0 = a record (literals or a match) and the bytes it makes, 1 = end of block,
+// 2 = invalid code (`flag` says which).
+__device__ __forceinline__ uint32_t walk_one(WarpSmem &sm, LaneBits &lb, uint32_t &rec, uint32_t &add, uint32_t &flag) {
+  lb.refill();
+  const uint32_t e = sm.lt[lb.peek(TB)];
+  uint32_t kind = (e >> 4) & 3u;
+  uint32_t lbase = e >> 16, lext = (e >> 8) & 15u;
+  rec = ((e >> 6) & 3u) << 24 | (e >> 8);
+  add = (e >> 6) & 3u;
+  if (kind == 3u) {
+    uint32_t L = 0;
+    const int sy = canon_walk((uint32_t)lb.bb, sm.lc, sm.lsym, L);
+    if (sy < 0 || sy >= 286) { flag = F_ERR | ((uint32_t)INF_E_LITLEN_CODE << 16); return 2u; }
+    lb.drop(L);
+    if (sy < 256) { kind = 0u; rec = (1u << 24) | (uint32_t)sy; add = 1u; }
+    else if (sy == 256) kind = 2u;
+    else { kind = 1u; lbase = c_lbase[sy - 257]; lext = c_lext[sy - 257]; }
+  } else {
+    lb.drop(e & 15u);
+  }
+  if (kind == 2u) { flag = F_EOB; return 1u; }
+  if (kind == 1u) {
+    const uint32_t len = lbase + lb.take(lext);
+    lb.refill();
+    const uint32_t d = sm.dt[lb.peek(TD)];
+    uint32_t dbase = d >> 16, dext = (d >> 8) & 15u;
+    if ((d & 0x30u) == 0x30u) {
+      uint32_t L = 0;
+      const int sy = canon_walk((uint32_t)lb.bb, sm.dc, sm.dsym, L);
+      if (sy < 0 || sy >= 30) { flag = F_ERR | ((uint32_t)INF_E_DIST_CODE << 16); return 2u; }
+      lb.drop(L);
+      dbase = c_dbase[sy]; dext = c_dext[sy];
+    } else {
+      lb.drop(d & 15u);
+    }
+    const uint32_t dist = dbase + lb.take(dext);
+    rec = (1u << 31) | ((len - 3u) << 15) | (dist - 1u);
+    add = len;
+  }
+  return 0u;
+}
+
+__device__ __forceinline__ uint32_t rec_bytes(uint32_t rec) { return (int)rec >= 0 ? rec >> 24 : ((rec >> 15) & 0xffu) + 3u; }
+
 // `mask`: the lanes that walk in this round.  They step together: the loop condition is a vote, so the lanes meet
-// again at every symbol instead of each running its own copy of the loop.
+// again at every symbol instead of each running its own copy of the loop.  `first`: the window's first walk, which
+// also notes where every record starts.
 __device__ __forceinline__ uint32_t walk_sub(WarpSmem &sm, uint32_t *qbuf, uint32_t start, uint32_t limit, uint32_t lane, uint32_t mask,
-                                             uint32_t &n_flag, uint32_t &n_out) {
+                                             bool first, uint32_t &n_flag, uint32_t &n_out) {
   LaneBits lb;
   lb.init(sm.zw, start);
   uint32_t n = 0, flag = 0, out = 0;
-  uint32_t *q = qbuf + lane;
+  uint32_t *q = qbuf + QHEAD * 32u + lane;
+  uint16_t *bp = sm.bpos + lane;
   bool live = true;
   for (;;) {
-    live = live && lb.pos() < limit && n < SUBCAP && out < LANE_OUT;
+    const uint32_t at = lb.pos();
+    live = live && at < limit && n < SUBCAP && out < LANE_OUT;
     if (!__any_sync(mask, live)) break;
     if (live) {
-      lb.refill();
-      const uint32_t e = sm.lt[lb.peek(TB)];
-      uint32_t kind = (e >> 4) & 3u;
-      uint32_t rec = ((e >> 6) & 3u) << 24 | (e >> 8), lbase = e >> 16, lext = (e >> 8) & 15u, add = (e >> 6) & 3u;
-      if (kind == 3u) {
-        uint32_t L = 0;
-        const int sy = canon_walk((uint32_t)lb.bb, sm.lc, sm.lsym, L);
-        if (sy < 0 || sy >= 286) { flag = F_ERR | ((uint32_t)INF_E_LITLEN_CODE << 16); live = false; }
-        else {
-          lb.drop(L);
-          if (sy < 256) { kind = 0u; rec = (1u << 24) | (uint32_t)sy; add = 1u; }
-          else if (sy == 256) kind = 2u;
-          else { kind = 1u; lbase = c_lbase[sy - 257]; lext = c_lext[sy - 257]; }
-        }
-      } else {
-        lb.drop(e & 15u);
-      }
-      if (live && kind == 2u) { flag = F_EOB; live = false; }
-      if (live && kind == 1u) {
-        const uint32_t len = lbase + lb.take(lext);
-        lb.refill();
-        const uint32_t d = sm.dt[lb.peek(TD)];
-        uint32_t dbase = d >> 16, dext = (d >> 8) & 15u;
-        if ((d & 0x30u) == 0x30u) {
-          uint32_t L = 0;
-          const int sy = canon_walk((uint32_t)lb.bb, sm.dc, sm.dsym, L);
-          if (sy < 0 || sy >= 30) { flag = F_ERR | ((uint32_t)INF_E_DIST_CODE << 16); live = false; }
-          else { lb.drop(L); dbase = c_dbase[sy]; dext = c_dext[sy]; }
-        } else {
-          lb.drop(d & 15u);
-        }
-        const uint32_t dist = dbase + lb.take(dext);
-        rec = (1u << 31) | ((len - 3u) << 15) | (dist - 1u);
-        add = len;
-      }
-      if (live) {
+      uint32_t rec, add;
+      if (walk_one(sm, lb, rec, add, flag)) live = false;
+      else {
         q[n * 32u] = rec;
+        if (first) bp[n * 32u] = (uint16_t)at;
         n++;
         out += add;
       }
     }
   }
   n_flag = n | flag;
+  n_out = out;
+  return lb.pos();
+}
+
+// The window's second walk: from the true start, and only until it steps on a bit where a record of the first
+// walk starts -- from there on the two walks are the same walk.  The new records wait in `tq` (the first walk's
+// are still needed) and are then put in front of the old tail; `base` is the row the merged list starts at.
+// In: n_flag / n_out / end of the first walk.  Out: those of the merged list.
+__device__ __forceinline__ uint32_t walk_again(WarpSmem &sm, uint32_t *qbuf, uint32_t start, uint32_t limit, uint32_t lane, uint32_t mask,
+                                               uint32_t old_end, uint32_t &n_flag, uint32_t &n_out, uint32_t &base) {
+  LaneBits lb;
+  lb.init(sm.zw, start);
+  const uint32_t n_old = n_flag & 0xffu;
+  uint32_t m = 0, flag = 0, out = 0, j = 0;
+  uint32_t *q = qbuf + lane;
+  uint32_t *tq = reinterpret_cast<uint32_t *>(sm.l1) + lane;
+  const uint16_t *bp = sm.bpos + lane;
+  bool live = true, met = false, direct = false;   // direct: too many new records to keep aside, the old walk is given up
+  for (;;) {
+    const uint32_t at = lb.pos();
+    live = live && at < limit && m < SUBCAP && out < LANE_OUT;
+    if (live && !direct) {
+      while (j < n_old && bp[j * 32u] < at) j++;
+      if (j < n_old && bp[j * 32u] == at && m <= j + QHEAD) { met = true; live = false; }
+    }
+    if (!__any_sync(mask, live)) break;
+    if (live) {
+      uint32_t rec, add;
+      if (walk_one(sm, lb, rec, add, flag)) live = false;
+      else {
+        if (!direct && m == TQCAP) {
+          for (uint32_t t = 0; t < m; t++) q[(QHEAD + t) * 32u] = tq[t * 32u];
+          direct = true;
+        }
+        if (direct) q[(QHEAD + m) * 32u] = rec; else tq[m * 32u] = rec;
+        m++;
+        out += add;
+      }
+    }
+  }
+  if (met) {
+    uint32_t before = 0;   // bytes of the old records that the new ones replace
+    for (uint32_t k = 0; k < j; k++) before += rec_bytes(q[(QHEAD + k) * 32u]);
+    base = QHEAD + j - m;
+    for (uint32_t t = 0; t < m; t++) q[(base + t) * 32u] = tq[t * 32u];
+    n_flag = (m + n_old - j) | (n_flag & ~0xffu);
+    n_out = out + n_out - before;
+    return old_end;
+  }
+  if (!direct) for (uint32_t t = 0; t < m; t++) q[(QHEAD + t) * 32u] = tq[t * 32u];
+  base = QHEAD;
+  n_flag = m | flag;
   n_out = out;
   return lb.pos();
 }
@@ -508,11 +587,14 @@ __device__ void walker(WarpSmem &sm, const InfStream &st, Link lk, const uint32_
         __syncwarp();
         uint32_t start = rel0 + lane * SUBBITS;
         const uint32_t limit = rel0 + (lane + 1u) * SUBBITS;
-        uint32_t end = 0, n_flag = 0, n_out = 0;
+        uint32_t end = 0, n_flag = 0, n_out = 0, base = QHEAD;
         bool walk = true;
         uint32_t bad = 0;   // lanes whose start is not their left neighbour's end
         for (uint32_t round = 0;; round++) {
-          if (walk) end = walk_sub(sm, qbuf, start, limit, lane, round ? bad : FULL, n_flag, n_out);
+          if (walk) {
+            if (round == 1u) end = walk_again(sm, qbuf, start, limit, lane, bad, end, n_flag, n_out, base);
+            else { end = walk_sub(sm, qbuf, start, limit, lane, round ? bad : FULL, round == 0u, n_flag, n_out); base = QHEAD; }
+          }
           __syncwarp();
           const uint32_t left_end = __shfl_up_sync(FULL, end, 1);
           const uint32_t left_flag = __shfl_up_sync(FULL, n_flag, 1);
@@ -537,6 +619,7 @@ __device__ void walker(WarpSmem &sm, const InfStream &st, Link lk, const uint32_
         const uint32_t total = __shfl_sync(FULL, off, n_lanes - 1u);
         m.n[lane] = n_flag & 0xffu;
         m.off[lane] = off - n_out;
+        m.base[lane] = base;
         if (lane == 0u) { m.kind = MSG_WINDOW; m.n_lanes = n_lanes; m.total = total; }
         publish();
         opos += total;
@@ -602,7 +685,7 @@ __device__ void applier(WarpSmem &sm, const InfStream &st, InfResult *results, L
     // ---- a window: every lane of the chain writes its own records' bytes; copies from bytes that another lane is
     // producing in this same window are left as pointers and resolved afterwards by pointer jumping ----
     const uint32_t n_lanes = m.n_lanes, total = m.total;
-    const uint32_t off = m.off[lane], ni = m.n[lane];
+    const uint32_t off = m.off[lane], ni = m.n[lane], base = m.base[lane];
     const uint32_t *q = sm.q[lk.slot];
     bool far = false;
     {
@@ -610,7 +693,7 @@ __device__ void applier(WarpSmem &sm, const InfStream &st, InfResult *results, L
       const uint32_t my_n = lane < n_lanes && !err ? ni : 0u;
       for (uint32_t k = 0; __any_sync(FULL, k < my_n); k++) {   // a vote per record: the lanes stay in step
         if (k >= my_n) continue;
-        const uint32_t r = q[k * 32u + lane];
+        const uint32_t r = q[(base + k) * 32u + lane];
         if ((int)r >= 0) {
           const uint32_t cnt = r >> 24;
           for (uint32_t t = 0; t < cnt; t++, o++) {
