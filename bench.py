@@ -48,7 +48,7 @@ WORKLOAD_CONFIG = {
 }
 
 
-def profiled_traffic_bytes(summary="profiles/r1b_prof_fused_r1i.summary.csv"):
+def profiled_traffic_bytes(summary="profiles/r1c_prof_fused.summary.csv"):
     """dram__bytes_read.sum + dram__bytes_write.sum of the composite+filter kernel from the committed
     `ncu --set full` capture of this same workload (one launch).  None when the summary is missing."""
     path = os.path.join(os.path.dirname(os.path.abspath(__file__)), summary)
@@ -451,7 +451,7 @@ def run_ours(args, rank: int, world: int, local_rank: int):
         "gpu_launches": value_launches,
         "roofline": {"bound": "hbm", "kernel": "composite+filter-select (kernels b+c)", "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": achieved / peak, "traffic": profiled_traffic_bytes(), "peak_source": peak_src,
-                     "traffic_source": "profiles/r1b_prof_fused_r1i.summary.csv (ncu --set full, one launch, bytes)",
+                     "traffic_source": "profiles/r1c_prof_fused.summary.csv (ncu --set full, one launch, bytes)",
                      "algorithmic_bytes_per_launch": alg_bytes, "avg_ms": cmp_avg,
                      "frac_of_8TBps": achieved / 8000.0},
         "kernels": {"unfilter": {"avg_ms": dec_avg, "achieved_GBps": unf_achieved, "frac": unf_achieved / peak},
