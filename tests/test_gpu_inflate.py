@@ -185,6 +185,34 @@ def test_job_with_many_zlib_tiles_equals_inflated_tiles(ctx):
     assert outs[0] == outs[1]
 
 
+def test_c2_size_job_from_zlib_streams(ctx):
+    """BASELINE config 2 at full size with every tile entering as its zlib stream: the 16384 x 16384 band is
+    byte-identical to the one made from host-inflated streams, and inflating again gives the same bytes."""
+    import hashlib
+    grid, tile, canvas = 16, 1024, 16384
+    rng = np.random.default_rng(2)
+    streams = [bytes(synth.encode_filtered(synth.smooth_rgba8(rng, tile, tile, "opaque"), 4)) for _ in range(4)]
+    zs = [_z(st, lvl) for st, lvl in zip(streams, (6, 1, 9, 6))]
+    which = lambda r, c: (r * 5 + c * 3) % 4
+    out = np.empty(canvas * (canvas * 4 + 1), np.uint8)
+    digests = []
+    for mode in (1, 2):
+        with _native.Job(ctx, canvas, canvas, 8, _native.OUT_PNG_FILTERED, False, bytes(4)) as job:
+            for r in range(grid):
+                for c in range(grid):
+                    k = which(r, c)
+                    job.add_tile(streams[k] if mode == 1 else zs[k], width=tile, height=tile, bit_depth=8, color_type=6,
+                                 filtered=mode, dst_x=c * tile, dst_y=r * tile, image_idx=r * grid + c)
+            got, _ = job.run_band(0, canvas, out=out)
+            digests.append(hashlib.sha256(memoryview(got)).hexdigest())
+            if mode == 2:
+                job.inflate(force=True)          # every stream again, in place
+                job.invalidate()
+                got, _ = job.run_band(0, canvas, out=out)
+                digests.append(hashlib.sha256(memoryview(got)).hexdigest())
+    assert digests[0] == digests[1] == digests[2]
+
+
 def test_job_reports_inflate_and_row_count_errors(ctx):
     rng = np.random.default_rng(10)
     T = 64
