@@ -58,6 +58,67 @@ static void dev_free(stitch_ctx *ctx, void *p) {
   if (p) cudaFreeAsync(p, ctx->stream);
 }
 
+// ---- small tables and fills without the copy engines (see stitch_ctx::h_arena) ------------------------------------
+__global__ void copy_words_kernel(uint32_t *dst, const uint32_t *src, size_t n) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) dst[i] = src[i];
+}
+__global__ void fill_words_kernel(uint32_t *dst, uint32_t v, size_t n) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) dst[i] = v;
+}
+// Rows of `row_bytes` bytes at src + r * pitch  ->  the same rows back to back (the host's layout, whose rows of
+// 1 + W*bpp bytes have no alignment), four bytes per thread.
+__global__ void pack_rows_kernel(uint32_t *dst, const uint8_t *src, size_t pitch, uint32_t row_bytes, size_t n_words, size_t total) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_words; i += (size_t)gridDim.x * blockDim.x) {
+    const size_t o = i * 4;
+    size_t r = o / row_bytes;
+    uint32_t c = (uint32_t)(o - r * row_bytes), w = 0;
+    const uint8_t *p = src + r * pitch;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      if (o + k < total) w |= (uint32_t)p[c] << (8 * k);
+      if (++c == row_bytes) { c = 0; p += pitch; }
+    }
+    dst[i] = w;
+  }
+}
+static constexpr size_t ARENA_BYTES = (size_t)32 << 20;
+
+int stitch_upload_small(stitch_ctx *ctx, void *d_dst, const void *src, size_t bytes) {
+  if (!bytes) return STITCH_OK;
+  const size_t need = round_up(bytes, 16);
+  if ((bytes & 3u) || !ctx->h_arena || ctx->arena_used + need > ctx->arena_cap) {   // too large for the arena: the copy engine after all
+    CK(cudaMemcpyAsync(d_dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    return STITCH_OK;
+  }
+  uint8_t *stage = ctx->h_arena + ctx->arena_used;   // pinned host memory is addressable from kernels (unified addressing)
+  ctx->arena_used += need;
+  memcpy(stage, src, bytes);
+  const size_t n = bytes / 4;
+  const unsigned blocks = (unsigned)std::min<size_t>((n + 255) / 256, 1024);
+  copy_words_kernel<<<blocks, 256, 0, ctx->stream>>>((uint32_t *)d_dst, (const uint32_t *)stage, n);
+  CK(cudaGetLastError());
+  return STITCH_OK;
+}
+
+int stitch_fill_words(stitch_ctx *ctx, void *d_dst, uint32_t value, size_t bytes) {
+  const size_t n = bytes / 4;
+  if (!n) return STITCH_OK;
+  const unsigned blocks = (unsigned)std::min<size_t>((n + 255) / 256, 2048);
+  fill_words_kernel<<<blocks, 256, 0, ctx->stream>>>((uint32_t *)d_dst, value, n);
+  CK(cudaGetLastError());
+  return STITCH_OK;
+}
+
+int stitch_download_small(stitch_ctx *ctx, void *h_pinned_dst, const void *d_src, size_t bytes) {
+  const size_t n = bytes / 4;
+  if (!n) return STITCH_OK;
+  copy_words_kernel<<<(unsigned)std::min<size_t>((n + 255) / 256, 64), 256, 0, ctx->stream>>>((uint32_t *)h_pinned_dst, (const uint32_t *)d_src, n);
+  CK(cudaGetLastError());
+  return STITCH_OK;
+}
+
+void stitch_arena_reset(stitch_ctx *ctx) { ctx->arena_used = 0; }
+
 // ---------------------------------------------------------------------------
 extern "C" int stitch_abi_version(void) { return STITCH_ABI_VERSION; }
 
@@ -91,6 +152,8 @@ extern "C" int stitch_ctx_create(int device_id, stitch_ctx **out) {
   cudaMalloc((void **)&ctx->d_status, sizeof(DevStatus));
   cudaHostAlloc((void **)&ctx->h_status, sizeof(DevStatus), cudaHostAllocDefault);
   if (!ctx->d_status || !ctx->h_status) { delete ctx; return STITCH_E_NOMEM; }
+  if (cudaHostAlloc((void **)&ctx->h_arena, ARENA_BYTES, cudaHostAllocDefault) == cudaSuccess) ctx->arena_cap = ARENA_BYTES;
+  else { ctx->h_arena = nullptr; cudaGetLastError(); }
   *out = ctx;
   return STITCH_OK;
 }
@@ -106,6 +169,7 @@ extern "C" void stitch_ctx_destroy(stitch_ctx *ctx) {
   cudaStreamDestroy(ctx->up); cudaStreamDestroy(ctx->down);
   if (ctx->d_status) cudaFree(ctx->d_status);
   if (ctx->h_status) cudaFreeHost(ctx->h_status);
+  if (ctx->h_arena) cudaFreeHost(ctx->h_arena);
   if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
 }
@@ -172,6 +236,8 @@ extern "C" void stitch_job_destroy(stitch_job *job) {
   dev_free(ctx, job->d_canvas); dev_free(ctx, job->d_out); dev_free(ctx, job->d_sync); dev_free(ctx, job->d_plans); dev_free(ctx, job->d_ctab);
   dev_free(ctx, job->d_defl); dev_free(ctx, job->d_defl_b); dev_free(ctx, job->d_defl_scratch);
   dev_free(ctx, job->d_inf); dev_free(ctx, job->d_infres);
+  dev_free(ctx, job->d_pack[0]); dev_free(ctx, job->d_pack[1]);
+  for (auto &e : job->ev_pack) if (e) cudaEventDestroy(e);
   if (job->h_infres) cudaFreeHost(job->h_infres);
   for (auto &e : job->ev_defl) if (e) cudaEventDestroy(e);
   if (job->h_defl) cudaFreeHost(job->h_defl);
@@ -358,13 +424,13 @@ static int upload_array(stitch_ctx *ctx, const std::vector<T> &v, T **d_ptr, siz
     if (rc) return rc;
     *cap = v.size();
   }
-  if (!v.empty()) CK(cudaMemcpyAsync(*d_ptr, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
+  static_assert(sizeof(T) % 4 == 0, "tables are copied word by word");
+  if (!v.empty()) return stitch_upload_small(ctx, *d_ptr, v.data(), v.size() * sizeof(T));
   return STITCH_OK;
 }
 
 static int reset_status(stitch_ctx *ctx) {
-  CK(cudaMemsetAsync(ctx->d_status, 0xff, sizeof(DevStatus), ctx->stream));
-  return STITCH_OK;
+  return stitch_fill_words(ctx, ctx->d_status, 0xffffffffu, sizeof(DevStatus));
 }
 
 // Results of the inflate launches since the last check (stream synchronised by the caller): zlib's message
@@ -462,10 +528,10 @@ static int inflate_tiles(stitch_job *job, int force, uint32_t *launches, uint32_
   }
   CK(launch_inflate(job->d_inf, job->d_infres, (uint32_t)v.size(), ctx->stream));
   if (launches) *launches += 2;
-  for (auto &s : v) {
-    CK(cudaMemcpyAsync(job->h_infres + s.slot, job->d_infres + s.slot, sizeof(InfResult), cudaMemcpyDeviceToHost, ctx->stream));
-    job->inf_pending.push_back(s.slot);
-  }
+  // the results of this launch lie between its first and last slot (tiles are visited in order)
+  if ((rc = stitch_download_small(ctx, job->h_infres + v.front().slot, job->d_infres + v.front().slot,
+                                  (size_t)(v.back().slot - v.front().slot + 1) * sizeof(InfResult)))) return rc;
+  for (auto &s : v) job->inf_pending.push_back(s.slot);
   return STITCH_OK;
 }
 
@@ -528,13 +594,13 @@ static int decode_tiles(stitch_job *job, int force, uint32_t *launches, uint32_t
       dev_free(ctx, job->d_uprog); job->d_uprog = nullptr; job->uprog_cap = 0;
       if ((rc = dev_alloc(ctx, (void **)&job->d_uprog, bytes))) return rc;
       job->uprog_cap = bytes;
-      CK(cudaMemsetAsync(job->d_uprog, 0, bytes, ctx->stream));  // tags of a fresh mailbox: epoch 0 = never written
+      if ((rc = stitch_fill_words(ctx, job->d_uprog, 0u, bytes))) return rc;  // tags of a fresh mailbox: epoch 0 = never written
     }
     if (++job->seam_epoch == 0u) {  // 2^32 decodes later the tags would repeat: start over
-      CK(cudaMemsetAsync(job->d_uprog, 0, job->uprog_cap, ctx->stream));
+      if ((rc = stitch_fill_words(ctx, job->d_uprog, 0u, job->uprog_cap))) return rc;
       job->seam_epoch = 1u;
     }
-    CK(cudaMemsetAsync(job->d_uprog, 0, 4, ctx->stream));  // ticket
+    if ((rc = stitch_fill_words(ctx, job->d_uprog, 0u, 4))) return rc;  // ticket
     uint32_t uniform_bpp = fast[0].bpp;
     for (auto &s : fast) if (s.bpp != uniform_bpp) uniform_bpp = 0;
     CK(launch_unfilter_wave(job->d_streams, job->d_units, job->n_fast_units, job->d_uprog + 256, job->seam_epoch,
@@ -561,6 +627,7 @@ extern "C" int stitch_job_inflate(stitch_job *job, int force, stitch_timings *t)
   if (!job) return STITCH_E_INVALID;
   stitch_ctx *ctx = job->ctx;
   cudaSetDevice(ctx->device);
+  if (ctx->arena_used) { cudaStreamSynchronize(ctx->stream); stitch_arena_reset(ctx); }  // an earlier call left early
   uint32_t launches = 0;
   int rc = wait_uploads(job, 0, 0xffffffffu);
   if (rc) return rc;
@@ -570,6 +637,7 @@ extern "C" int stitch_job_inflate(stitch_job *job, int force, stitch_timings *t)
   CK(cudaEventRecord(ctx->ev[1], ctx->stream));
   CK(cudaMemcpyAsync(ctx->h_status, ctx->d_status, sizeof(DevStatus), cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));
+  stitch_arena_reset(ctx);
   if (t) {
     memset(t, 0, sizeof *t);
     cudaEventElapsedTime(&t->decode_ms, ctx->ev[0], ctx->ev[1]);
@@ -623,6 +691,7 @@ extern "C" int stitch_job_decode(stitch_job *job, int force, stitch_timings *t) 
   if (!job) return STITCH_E_INVALID;
   stitch_ctx *ctx = job->ctx;
   cudaSetDevice(ctx->device);
+  if (ctx->arena_used) { cudaStreamSynchronize(ctx->stream); stitch_arena_reset(ctx); }  // an earlier call left early
   uint32_t launches = 0;
   int rc = reset_status(ctx);
   if (rc) return rc;
@@ -632,6 +701,7 @@ extern "C" int stitch_job_decode(stitch_job *job, int force, stitch_timings *t) 
   CK(cudaEventRecord(ctx->ev[1], ctx->stream));
   CK(cudaMemcpyAsync(ctx->h_status, ctx->d_status, sizeof(DevStatus), cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));
+  stitch_arena_reset(ctx);
   if (t) {
     memset(t, 0, sizeof *t);
     cudaEventElapsedTime(&t->decode_ms, ctx->ev[0], ctx->ev[1]);
@@ -721,9 +791,10 @@ static int finalize_job(stitch_job *job) {
   if ((rc = dev_alloc(ctx, (void **)&job->d_tiles, dt.size() * sizeof(DevTile)))) return rc;
   if ((rc = dev_alloc(ctx, (void **)&job->d_bin_start, start.size() * sizeof(uint32_t)))) return rc;
   if ((rc = dev_alloc(ctx, (void **)&job->d_bin_tiles, list.size() * sizeof(uint32_t)))) return rc;
-  if (!dt.empty()) CK(cudaMemcpyAsync(job->d_tiles, dt.data(), dt.size() * sizeof(DevTile), cudaMemcpyHostToDevice, ctx->stream));
-  CK(cudaMemcpyAsync(job->d_bin_start, start.data(), start.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
-  CK(cudaMemcpyAsync(job->d_bin_tiles, list.data(), list.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+  static_assert(sizeof(DevTile) % 4 == 0, "tables are copied word by word");
+  if ((rc = stitch_upload_small(ctx, job->d_tiles, dt.data(), dt.size() * sizeof(DevTile)))) return rc;
+  if ((rc = stitch_upload_small(ctx, job->d_bin_start, start.data(), start.size() * sizeof(uint32_t)))) return rc;
+  if ((rc = stitch_upload_small(ctx, job->d_bin_tiles, list.data(), list.size() * sizeof(uint32_t)))) return rc;
   // the host vectors are pageable: the async copies above have already staged them
   CK(cudaStreamSynchronize(ctx->stream));
   job->finalized = true;
@@ -797,7 +868,7 @@ static int render_rows(stitch_job *job, uint32_t a, uint32_t b, uint8_t *d_rows,
       if ((rc = dev_alloc(ctx, (void **)&job->d_sync, words * 4))) return rc;
       job->sync_words = words;
     }
-    CK(cudaMemsetAsync(job->d_sync, 0, words * 4, ctx->stream));
+    if ((rc = stitch_fill_words(ctx, job->d_sync, 0u, words * 4))) return rc;
     FusedParams fp{};
     fp.tiles = job->d_tiles; fp.bin_start = job->d_bin_start; fp.bin_tiles = job->d_bin_tiles;
     fp.bins_x = job->bins_x; fp.canvas_w = jd.canvas_w; fp.y_begin = a; fp.y_end = b; fp.band0 = band0;
@@ -828,7 +899,8 @@ static int render_rows(stitch_job *job, uint32_t a, uint32_t b, uint8_t *d_rows,
       tab.t.x0 = 0; tab.t.y0 = (int32_t)ys; tab.t.x1 = (int32_t)jd.canvas_w; tab.t.y1 = (int32_t)b;
       tab.t.opaque = 1;
       tab.bin_start[1] = 1;
-      CK(cudaMemcpyAsync(job->d_ctab, &tab, sizeof tab, cudaMemcpyHostToDevice, ctx->stream));  // pageable: staged on return
+      static_assert(sizeof tab % 4 == 0, "tables are copied word by word");
+      if ((rc = stitch_upload_small(ctx, job->d_ctab, &tab, sizeof tab))) return rc;  // staged on return
       fp.tiles = reinterpret_cast<const DevTile *>(job->d_ctab);
       fp.bin_start = reinterpret_cast<const uint32_t *>(job->d_ctab + offsetof(decltype(tab), bin_start));
       fp.bin_tiles = reinterpret_cast<const uint32_t *>(job->d_ctab + offsetof(decltype(tab), bin_tiles));
@@ -856,12 +928,27 @@ static int render_rows(stitch_job *job, uint32_t a, uint32_t b, uint8_t *d_rows,
   return STITCH_OK;
 }
 
+// Device -> host on the download stream, in pieces the size of the job's tile uploads.  The link is shared copy
+// by copy: while uploads of one tile each are still in flight, downloads of the same size get their half of it,
+// larger ones crowd the uploads out and smaller ones are crowded out themselves (tools/bus_bidir.py).
+static int download_pieces(stitch_job *job, uint8_t *host, const uint8_t *dev, size_t bytes) {
+  stitch_ctx *ctx = job->ctx;
+  size_t piece = bytes, up_bytes = 0, up_n = 0;
+  for (const auto &t : job->tiles) if (t.up_event) { up_bytes += t.d_z ? t.z_len : t.src_len; up_n++; }
+  if (up_n) piece = std::max<size_t>(up_bytes / up_n, (size_t)1 << 20);
+  if (const char *e = getenv("STITCH_DOWN_PIECE")) piece = std::max<size_t>(4096, strtoull(e, nullptr, 10));  // tuning
+  for (size_t o = 0; o < bytes; o += piece)
+    CK(cudaMemcpyAsync(host + o, dev + o, std::min(piece, bytes - o), cudaMemcpyDeviceToHost, ctx->down));
+  return STITCH_OK;
+}
+
 extern "C" int stitch_job_run_band(stitch_job *job, uint32_t y0, uint32_t y1, uint8_t *out, size_t cap,
                                    size_t *out_len, stitch_timings *tm) {
   if (!job) return STITCH_E_INVALID;
   stitch_ctx *ctx = job->ctx;
   const stitch_job_desc &jd = job->desc;
   cudaSetDevice(ctx->device);
+  if (ctx->arena_used) { cudaStreamSynchronize(ctx->stream); stitch_arena_reset(ctx); }  // an earlier call left early
   if (out_len) *out_len = 0;
   if (y0 >= y1 || y0 < jd.band_y0 || y1 > jd.band_y1)
     return fail(ctx, STITCH_E_INVALID, "rows [%u,%u) are outside the job's band [%u,%u)", y0, y1, jd.band_y0, jd.band_y1);
@@ -941,11 +1028,17 @@ extern "C" int stitch_job_run_band(stitch_job *job, uint32_t y0, uint32_t y1, ui
     bool first = true;
     uint32_t n_chunks = 0, z_adler = 1, z_crc_raw = 0;
     size_t z_total = 0;
+    // STITCH_TRACE=1: when every chunk was rendered and when it had left the device, on stderr (debugging aid)
+    const bool trace = getenv("STITCH_TRACE") != nullptr;
+    std::vector<cudaEvent_t> tr_render, tr_down;
+    cudaEvent_t tr_up = nullptr;
+    if (trace) { cudaEventCreate(&tr_up); cudaEventRecord(tr_up, ctx->up); }
     for (uint32_t a = y0; a < y1; a += chunk) {
       const uint32_t b = (uint32_t)std::min<uint64_t>((uint64_t)a + chunk, y1);
       uint8_t *d_rows = job->d_out + (size_t)(a - y0) * job->out_pitch;
       if ((rc = render_rows(job, a, b, d_rows, &launches, first ? ctx->ev[2] : nullptr))) return rc;
       first = false;
+      if (trace) { cudaEvent_t e; cudaEventCreate(&e); cudaEventRecord(e, ctx->stream); tr_render.push_back(e); }
       if (deflate) {
         // 8(f).1: the chunk leaves the device compressed.  Two device buffers take turns, so chunk k goes
         // down the bus while chunk k+1 is rendered and compressed.
@@ -962,17 +1055,53 @@ extern "C" int stitch_job_run_band(stitch_job *job, uint32_t y0, uint32_t y1, ui
         if (out) {
           if (cap < sizeof(stitch_deflate_band_info) + z_total + zbytes)
             return fail(ctx, STITCH_E_CAPACITY, "output buffer too small: need more than %zu bytes", sizeof(stitch_deflate_band_info) + z_total + zbytes);
-          CK(cudaMemcpyAsync(out + sizeof(stitch_deflate_band_info) + z_total, *zbuf, zbytes, cudaMemcpyDeviceToHost, ctx->down));
+          if ((rc = download_pieces(job, out + sizeof(stitch_deflate_band_info) + z_total, *zbuf, zbytes))) return rc;
           if (!job->ev_defl[k]) CK(cudaEventCreateWithFlags(&job->ev_defl[k], cudaEventDisableTiming));
           CK(cudaEventRecord(job->ev_defl[k], ctx->down));
         }
         z_total += zbytes;
+      } else if (out && png) {
+        // the filtered rows are packed on the device (the host rows have no padding) and leave as flat copies,
+        // cut to the size of the tile uploads they share the link with (download_pieces)
+        const uint32_t k = n_chunks++ & 1u;
+        const size_t bytes = host_row * (size_t)(b - a);
+        if (job->ev_pack[k]) CK(cudaStreamWaitEvent(ctx->stream, job->ev_pack[k], 0));  // its last download is over
+        if ((rc = ensure_buffer(ctx, &job->d_pack[k], &job->pack_bytes[k], round_up(bytes, 16)))) return rc;
+        const size_t n_words = (bytes + 3) / 4;
+        pack_rows_kernel<<<(unsigned)std::min<size_t>((n_words + 255) / 256, 148 * 16), 256, 0, ctx->stream>>>(
+            (uint32_t *)job->d_pack[k], d_rows + job->out_lead, job->out_pitch, (uint32_t)host_row, n_words, bytes);
+        CK(cudaGetLastError());
+        launches += 1;
+        CK(cudaEventRecord(ctx->ev_chunk, ctx->stream));
+        CK(cudaStreamWaitEvent(ctx->down, ctx->ev_chunk, 0));
+        // The link is shared copy by copy: with uploads of one tile each still in flight, downloads of the same
+        // size get their half of it, larger ones crowd the uploads out and smaller ones are crowded out themselves.
+        if ((rc = download_pieces(job, out + (size_t)(a - y0) * host_row, job->d_pack[k], bytes))) return rc;
+        if (!job->ev_pack[k]) CK(cudaEventCreateWithFlags(&job->ev_pack[k], cudaEventDisableTiming));
+        CK(cudaEventRecord(job->ev_pack[k], ctx->down));
+        if (trace) { cudaEvent_t e; cudaEventCreate(&e); cudaEventRecord(e, ctx->down); tr_down.push_back(e); }
       } else if (out) {
         CK(cudaEventRecord(ctx->ev_chunk, ctx->stream));
         CK(cudaStreamWaitEvent(ctx->down, ctx->ev_chunk, 0));
         CK(cudaMemcpy2DAsync(out + (size_t)(a - y0) * host_row, host_row, d_rows + job->out_lead, job->out_pitch, host_row,
                              b - a, cudaMemcpyDeviceToHost, ctx->down));
+        if (trace) { cudaEvent_t e; cudaEventCreate(&e); cudaEventRecord(e, ctx->down); tr_down.push_back(e); }
       }
+    }
+    if (trace) {
+      cudaStreamSynchronize(ctx->stream); cudaStreamSynchronize(ctx->down); cudaStreamSynchronize(ctx->up);
+      float ms = 0;
+      cudaEventElapsedTime(&ms, ctx->ev[0], tr_up);
+      fprintf(stderr, "[stitch trace] uploads queued before run_band finished at %.2f ms\n", ms);
+      for (size_t i = 0; i < tr_render.size(); i++) {
+        float r = 0, d = 0;
+        cudaEventElapsedTime(&r, ctx->ev[0], tr_render[i]);
+        if (i < tr_down.size()) cudaEventElapsedTime(&d, ctx->ev[0], tr_down[i]);
+        fprintf(stderr, "[stitch trace] chunk %zu rendered %.2f ms, downloaded %.2f ms\n", i, r, d);
+      }
+      for (auto e : tr_render) cudaEventDestroy(e);
+      for (auto e : tr_down) cudaEventDestroy(e);
+      cudaEventDestroy(tr_up);
     }
     if (deflate) {
       CK(cudaEventRecord(ctx->ev[3], ctx->stream));
@@ -998,6 +1127,7 @@ extern "C" int stitch_job_run_band(stitch_job *job, uint32_t y0, uint32_t y1, ui
   CK(cudaEventRecord(ctx->ev[4], ctx->stream));
   CK(cudaMemcpyAsync(ctx->h_status, ctx->d_status, sizeof(DevStatus), cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));
+  stitch_arena_reset(ctx);
   job->last_y0 = y0; job->last_y1 = y1;
   if (tm) {
     // decode_ms covers the first chunk's decode only when the band is produced in several chunks

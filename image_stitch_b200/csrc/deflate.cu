@@ -463,7 +463,7 @@ int stitch_deflate_band(stitch_job *job, const uint8_t *d_rows, uint32_t n_rows,
   const size_t bound = stitch_deflate_bound((size_t)v.total);
   crc32_kernel<<<(unsigned)((bound + CRC_CTA - 1) / CRC_CTA), DT, 0, ctx->stream>>>(d_dst, result);
   STITCH_CK(cudaGetLastError());
-  STITCH_CK(cudaMemcpyAsync(job->h_defl, result, 24, cudaMemcpyDeviceToHost, ctx->stream));
+  if ((rc = stitch_download_small(ctx, job->h_defl, result, 24))) return rc;   // by a kernel: not behind the downloads in flight
   STITCH_CK(cudaStreamSynchronize(ctx->stream));
   *out_bytes = (size_t)job->h_defl[0];
   *adler = (uint32_t)job->h_defl[1];

@@ -19,6 +19,10 @@ struct stitch_ctx {
   // chunks on `down`; ordering is by events (one per tile, one per chunk).
   cudaStream_t up = nullptr, down = nullptr;
   cudaEvent_t ev_chunk = nullptr, ev_down = nullptr;
+  // Small host tables (tile lists, chain tables, bins) reach the device through this pinned arena and a copy
+  // KERNEL, not through cudaMemcpyAsync: the host-to-device copy engine serves its queue in order, and a job's
+  // tile uploads (hundreds of MB, queued by add_tile) would hold a 1 KB table back until they are all through.
+  uint8_t *h_arena = nullptr; size_t arena_cap = 0, arena_used = 0;
   stitch::DevStatus *d_status = nullptr;   // device error word
   stitch::DevStatus *h_status = nullptr;   // pinned mirror
 };
@@ -72,6 +76,8 @@ struct stitch_job {
   uint8_t *d_plans = nullptr; size_t plans_bytes = 0;  // fused kernel: per-unit plan records
   uint8_t *d_defl = nullptr; size_t defl_bytes = 0;    // deflate: compressed band / chunk (two buffers, used in turn)
   uint8_t *d_defl_b = nullptr; size_t defl_b_bytes = 0;
+  uint8_t *d_pack[2] = {nullptr, nullptr}; size_t pack_bytes[2] = {0, 0};   // PNG rows of a chunk without row padding: one flat download
+  cudaEvent_t ev_pack[2] = {nullptr, nullptr};                                // the download of d_pack[i] has finished
   cudaEvent_t ev_defl[2] = {nullptr, nullptr};         // the download of buffer i has finished
   uint8_t *d_defl_scratch = nullptr; size_t defl_scratch_bytes = 0;
   unsigned long long *h_defl = nullptr;                // pinned: {bytes, adler}
@@ -94,6 +100,13 @@ int stitch_fail(stitch_ctx *ctx, int code, const char *fmt, ...);
 int stitch_dev_alloc(stitch_ctx *ctx, void **p, size_t bytes);
 void stitch_dev_free(stitch_ctx *ctx, void *p);
 int stitch_ensure_buffer(stitch_ctx *ctx, uint8_t **p, size_t *have, size_t need);
+// dst <- src (host, any memory) / dst <- 32-bit value, on ctx->stream, without the copy engines.  bytes % 4 == 0.
+int stitch_upload_small(stitch_ctx *ctx, void *d_dst, const void *src, size_t bytes);
+int stitch_fill_words(stitch_ctx *ctx, void *d_dst, uint32_t value, size_t bytes);
+// pinned host memory <- device, written by a kernel (a few words: sizes, check values, status), so that the read-back
+// does not queue behind the band downloads on the device-to-host copy engine.  Valid after a stream synchronisation.
+int stitch_download_small(stitch_ctx *ctx, void *h_pinned_dst, const void *d_src, size_t bytes);
+void stitch_arena_reset(stitch_ctx *ctx);   // after a stream synchronisation: the staged tables have been read
 
 #define STITCH_CK(call)                                                                        \
   do {                                                                                         \

@@ -535,7 +535,7 @@ int stitch_jpeg_encode_band(stitch_job *job, uint32_t y0, uint32_t y1, const uin
   const size_t uwords = (ubytes + 3) / 4 + 2;
   if ((rc = stitch_ensure_buffer(ctx, &job->d_jpeg[3], &job->jpeg_cap[3], uwords * 4))) return rc;
   if ((rc = stitch_ensure_buffer(ctx, &job->d_out, &job->out_bytes, 2 * ubytes + 2 * (size_t)g.mrows + 64))) return rc;
-  STITCH_CK(cudaMemsetAsync(job->d_jpeg[3], 0, uwords * 4, ctx->stream));
+  { int frc = stitch_fill_words(ctx, job->d_jpeg[3], 0u, (size_t)uwords * 4); if (frc) return frc; }
   {
     const size_t want = (n_blk + 255) / 256;
     const uint32_t grid = (uint32_t)(want < 148u * 16u ? want : 148u * 16u);
