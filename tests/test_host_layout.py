@@ -120,3 +120,32 @@ def test_split_rows_alignment():
     assert parts[0][0] == 0 and parts[-1][1] == 1000
     assert all(a % 8 == 0 for a, _ in parts) and all(p[1] == q[0] for p, q in zip(parts, parts[1:]))
     assert engine.split_rows(0, 5, 8) == [(0, 5)]
+
+
+def test_device_codec_options_and_deflated_source():
+    """Additive options and the decoder method that hands over the zlib stream itself."""
+    import zlib
+    from image_stitch_b200 import engine
+    from image_stitch_b200.decoders.png_decoder import PngBufferDecoder
+    from image_stitch_b200.types import ConcatOptions
+    o = ConcatOptions.coerce({"inputs": [b""], "layout": {"columns": 1}, "deviceInflate": True, "deviceDeflate": True})
+    assert o.device_inflate is True and o.device_deflate is True
+    assert ConcatOptions.coerce({"inputs": [b""], "layout": {"columns": 1}}).device_inflate is False
+    with pytest.raises(TypeError):
+        ConcatOptions.coerce({"inputs": [], "device_unflate": True})
+    data = H.suite_bytes("basi6a08")
+    dec = PngBufferDecoder(data)
+    hdr, z = dec.deflated()
+    hdr2, inflated = dec.inflated()
+    assert (hdr.width, hdr.height, hdr.interlace_method) == (32, 32, 1) and hdr == hdr2
+    assert zlib.decompress(z) == inflated                      # the stream the device inflates is the IDAT payload
+    src = engine.read_tile_source(dec, hdr, 0, device_inflate=True)
+    assert (src.filtered, src.interlace, bytes(src.data)) == (2, 1, z)
+    src = engine.read_tile_source(dec, hdr, 0)
+    assert (src.filtered, bytes(src.data)) == (1, inflated)
+
+    class Foreign:  # a decoder without deflated(): the option falls back to scanlines()
+        def scanlines(self):
+            return iter([bytes(hdr.width * 4)] * hdr.height)
+    src = engine.read_tile_source(Foreign(), hdr, 0, device_inflate=True)
+    assert src.filtered == 0 and len(src.data) == hdr.width * 4 * hdr.height
