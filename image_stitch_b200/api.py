@@ -101,13 +101,13 @@ class StreamingConcatenator:
         if plan.device_deflate:
             # the device already produced deflate blocks: one IDAT per band, zlib framing around them
             # (the chunk CRC comes from the device's CRC-32 of the band: no host pass over the bytes)
-            from .deflate_container import ZLIB_HEADER, DeflateBandSplicer, idat_chunk
+            from .deflate_container import ZLIB_HEADER, DeflateBandSplicer, idat_parts
             splicer = DeflateBandSplicer()
             head = ZLIB_HEADER
             for y0, y1, data, tm in engine.run_plan(plan, sources, self.options.devices, self.options.band_rows, on_band):
                 self.last_timings.append(tm)
-                body = splicer.push(data)
-                yield idat_chunk(head, body, splicer.last_crc32)
+                body = splicer.push(data, copy=False)      # a view: every band has its own buffer
+                yield from idat_parts(head, body, splicer.last_crc32)
                 head = b""
             yield serialize_chunk(create_chunk("IDAT", head + splicer.finish()))
             yield serialize_chunk(create_iend())

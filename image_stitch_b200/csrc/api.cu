@@ -969,6 +969,14 @@ extern "C" int stitch_job_run_band(stitch_job *job, uint32_t y0, uint32_t y1, ui
   if (rc) return rc;
   CK(cudaEventRecord(ctx->ev[0], ctx->stream));
   CK(cudaEventRecord(ctx->ev[1], ctx->stream));
+  // zlib tiles: a stream takes as long to inflate alone as among hundreds (a warp pair each), so every tile of
+  // the JOB that is still compressed is inflated in ONE launch, ahead of the first band that needs any of them
+  for (auto &t : job->tiles)
+    if (t.d_z && !t.inflated) {
+      if ((rc = wait_uploads(job, 0, 0xffffffffu))) return rc;
+      if ((rc = inflate_tiles(job, 0, &launches))) return rc;
+      break;
+    }
   if (jpeg) {
     if ((rc = decode_tiles(job, 0, &launches, y0, y1))) return rc;
     CK(cudaEventRecord(ctx->ev[2], ctx->stream));
@@ -1017,14 +1025,6 @@ extern "C" int stitch_job_run_band(stitch_job *job, uint32_t y0, uint32_t y1, ui
       const size_t want = chunk_bytes / std::max<size_t>(host_row, 1);
       chunk = (uint32_t)std::min<size_t>(n_rows, std::max<size_t>(16, want / 16 * 16));
     }
-    // zlib tiles: a stream takes as long to inflate alone as among hundreds (one warp each), so every tile of the
-    // band is inflated in ONE launch up front instead of chunk by chunk
-    for (auto &t : job->tiles)
-      if (t.d_z && !t.inflated) {
-        if ((rc = wait_uploads(job, y0 ? y0 - 1 : 0, y1))) return rc;
-        if ((rc = inflate_tiles(job, 0, &launches, y0 ? y0 - 1 : 0, y1))) return rc;
-        break;
-      }
     bool first = true;
     uint32_t n_chunks = 0, z_adler = 1, z_crc_raw = 0;
     size_t z_total = 0;

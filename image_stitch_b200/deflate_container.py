@@ -65,6 +65,16 @@ def idat_chunk(prefix: bytes, body: bytes, body_crc: int, suffix: bytes = b"") -
     return b"".join((n.to_bytes(4, "big"), b"IDAT", prefix, body, suffix, crc.to_bytes(4, "big")))
 
 
+def idat_parts(prefix: bytes, body, body_crc: int, suffix: bytes = b""):
+    """The same chunk as (head, body, tail) without copying the body (hundreds of MB per band): the stream yields the
+    three parts one after the other."""
+    crc = crc32_combine(zlib.crc32(b"IDAT" + prefix), body_crc, len(body))
+    if suffix:
+        crc = crc32_combine(crc, zlib.crc32(suffix), len(suffix))
+    n = len(prefix) + len(body) + len(suffix)
+    return n.to_bytes(4, "big") + b"IDAT" + prefix, body, suffix + crc.to_bytes(4, "big")
+
+
 class DeflateBandSplicer:
     """Joins the per-band results of stitch_job_run_band (STITCH_OUT_PNG_DEFLATE), in ascending row order."""
 
@@ -74,10 +84,13 @@ class DeflateBandSplicer:
         self.bytes_out = 0
         self.last_crc32 = 0   # CRC-32 of the body push() returned last (computed on the device)
 
-    def push(self, band) -> bytes:
+    def push(self, band, copy: bool = True):
+        """The band's deflate blocks; with copy=False a view into `band` (which must then stay alive and unchanged)."""
         data = memoryview(np.ascontiguousarray(band)).cast("B")
         info = _native.DeflateBandInfo.from_buffer_copy(bytes(data[:_INFO]))
-        body = bytes(data[_INFO:_INFO + info.n_bytes])
+        body = data[_INFO:_INFO + info.n_bytes]
+        if copy:
+            body = bytes(body)
         if len(body) != info.n_bytes:
             raise _native.StitchError(_native.E_STATE, "deflate band header does not match its payload")
         self.adler = adler32_combine(self.adler, info.adler, info.n_raw)

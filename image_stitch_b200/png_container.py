@@ -70,7 +70,7 @@ def parse_png_chunks(data) -> List[PngChunk]:
         (crc,) = struct.unpack_from(">I", data, off)
         off += 4
         name = ctype.decode("latin-1")
-        if png_crc32(ctype + body) != crc:
+        if zlib.crc32(body, zlib.crc32(ctype)) & 0xFFFFFFFF != crc:   # CRC over type + data, without joining them
             raise ValueError(f"CRC mismatch for chunk {name}")
         chunks.append(PngChunk(length, name, body, crc))
     return chunks
