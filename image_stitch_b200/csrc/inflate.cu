@@ -7,7 +7,7 @@
 // parallelism across tiles is one stream per warp PAIR, and the work inside a stream is made parallel by
 // speculation:
 //
-//   walk     a window of 32 x 512 code bits is cut into 32 subsequences; lane i walks subsequence i from a guessed
+//   walk     a window of 32 x 768 code bits is cut into 32 subsequences; lane i walks subsequence i from a guessed
 //            start and keeps its symbols as records.  Huffman codes resynchronise, so the walk usually ends on a true
 //            code boundary; lanes whose start differs from their left neighbour's end walk again until nothing
 //            changes (exact by induction from lane 0), else the consistent prefix of lanes is taken
@@ -40,12 +40,12 @@ constexpr int TD = 9;                  // distance table index bits
 constexpr int INF_STREAMS = 2;         // streams per CTA, two warps each: one walks the codes, one produces the bytes
 // Speculative lane-parallel Huffman walk: a window of 32 x SUBBITS code bits is cut into 32 subsequences, one
 // per lane; a lane keeps at most SUBCAP symbol records of its subsequence.
-constexpr uint32_t SUBBITS = 512u;
+constexpr uint32_t SUBBITS = 768u;
 constexpr uint32_t SUBCAP = 96u;
 constexpr uint32_t QHEAD = 16u;          // record rows in front of a lane's list: a re-walked prefix may be longer than the one it replaces
 constexpr uint32_t QROWS = SUBCAP + QHEAD;
 constexpr uint32_t TQCAP = 32u;          // records of a re-walk kept aside until it meets the old walk
-constexpr uint32_t LANE_OUT = 224u;      // a lane stops once its records produce this many bytes (a match may add 257 more)
+constexpr uint32_t LANE_OUT = 256u;      // a lane stops once its records produce this many bytes (a match may add 257 more)
 constexpr uint32_t RES = 0xffffu;        // src[]: this byte of the window is final
 constexpr uint32_t ZWORDS = 32u * SUBBITS / 32u + 16u;   // staged code words: the window, its 127-bit lead-in, a symbol of overrun, one word of look-ahead
 constexpr uint32_t MAX_ROUNDS = 8u;
