@@ -97,6 +97,7 @@ int stitch_upload_small(stitch_ctx *ctx, void *d_dst, const void *src, size_t by
   const unsigned blocks = (unsigned)std::min<size_t>((n + 255) / 256, 1024);
   copy_words_kernel<<<blocks, 256, 0, ctx->stream>>>((uint32_t *)d_dst, (const uint32_t *)stage, n);
   CK(cudaGetLastError());
+  ctx->aux_launches++;
   return STITCH_OK;
 }
 
@@ -106,6 +107,7 @@ int stitch_fill_words(stitch_ctx *ctx, void *d_dst, uint32_t value, size_t bytes
   const unsigned blocks = (unsigned)std::min<size_t>((n + 255) / 256, 2048);
   fill_words_kernel<<<blocks, 256, 0, ctx->stream>>>((uint32_t *)d_dst, value, n);
   CK(cudaGetLastError());
+  ctx->aux_launches++;
   return STITCH_OK;
 }
 
@@ -114,6 +116,7 @@ int stitch_download_small(stitch_ctx *ctx, void *h_pinned_dst, const void *d_src
   if (!n) return STITCH_OK;
   copy_words_kernel<<<(unsigned)std::min<size_t>((n + 255) / 256, 64), 256, 0, ctx->stream>>>((uint32_t *)h_pinned_dst, (const uint32_t *)d_src, n);
   CK(cudaGetLastError());
+  ctx->aux_launches++;
   return STITCH_OK;
 }
 
@@ -628,6 +631,7 @@ extern "C" int stitch_job_inflate(stitch_job *job, int force, stitch_timings *t)
   stitch_ctx *ctx = job->ctx;
   cudaSetDevice(ctx->device);
   if (ctx->arena_used) { cudaStreamSynchronize(ctx->stream); stitch_arena_reset(ctx); }  // an earlier call left early
+  ctx->aux_launches = 0;
   uint32_t launches = 0;
   int rc = wait_uploads(job, 0, 0xffffffffu);
   if (rc) return rc;
@@ -642,7 +646,7 @@ extern "C" int stitch_job_inflate(stitch_job *job, int force, stitch_timings *t)
     memset(t, 0, sizeof *t);
     cudaEventElapsedTime(&t->decode_ms, ctx->ev[0], ctx->ev[1]);
     t->total_ms = t->decode_ms;
-    t->launches = launches;
+    t->launches = launches + ctx->aux_launches;
   }
   return check_status(ctx, job);
 }
@@ -692,6 +696,7 @@ extern "C" int stitch_job_decode(stitch_job *job, int force, stitch_timings *t) 
   stitch_ctx *ctx = job->ctx;
   cudaSetDevice(ctx->device);
   if (ctx->arena_used) { cudaStreamSynchronize(ctx->stream); stitch_arena_reset(ctx); }  // an earlier call left early
+  ctx->aux_launches = 0;
   uint32_t launches = 0;
   int rc = reset_status(ctx);
   if (rc) return rc;
@@ -706,7 +711,7 @@ extern "C" int stitch_job_decode(stitch_job *job, int force, stitch_timings *t) 
     memset(t, 0, sizeof *t);
     cudaEventElapsedTime(&t->decode_ms, ctx->ev[0], ctx->ev[1]);
     t->total_ms = t->decode_ms;
-    t->launches = launches;
+    t->launches = launches + ctx->aux_launches;
   }
   return check_status(ctx, job);
 }
@@ -949,6 +954,7 @@ extern "C" int stitch_job_run_band(stitch_job *job, uint32_t y0, uint32_t y1, ui
   const stitch_job_desc &jd = job->desc;
   cudaSetDevice(ctx->device);
   if (ctx->arena_used) { cudaStreamSynchronize(ctx->stream); stitch_arena_reset(ctx); }  // an earlier call left early
+  ctx->aux_launches = 0;
   if (out_len) *out_len = 0;
   if (y0 >= y1 || y0 < jd.band_y0 || y1 > jd.band_y1)
     return fail(ctx, STITCH_E_INVALID, "rows [%u,%u) are outside the job's band [%u,%u)", y0, y1, jd.band_y0, jd.band_y1);
@@ -1137,7 +1143,7 @@ extern "C" int stitch_job_run_band(stitch_job *job, uint32_t y0, uint32_t y1, ui
     cudaEventElapsedTime(&tm->compose_ms, ctx->ev[2], ctx->ev[3]);
     cudaEventElapsedTime(&tm->d2h_ms, ctx->ev[3], ctx->ev[4]);
     cudaEventElapsedTime(&tm->total_ms, ctx->ev[0], ctx->ev[4]);
-    tm->launches = launches;
+    tm->launches = launches + ctx->aux_launches;
   }
   return check_status(ctx, job);
 }

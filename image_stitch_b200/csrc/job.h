@@ -23,6 +23,7 @@ struct stitch_ctx {
   // KERNEL, not through cudaMemcpyAsync: the host-to-device copy engine serves its queue in order, and a job's
   // tile uploads (hundreds of MB, queued by add_tile) would hold a 1 KB table back until they are all through.
   uint8_t *h_arena = nullptr; size_t arena_cap = 0, arena_used = 0;
+  uint32_t aux_launches = 0;   // copy / fill kernels launched since the current API call began (they count as launches)
   stitch::DevStatus *d_status = nullptr;   // device error word
   stitch::DevStatus *h_status = nullptr;   // pinned mirror
 };
