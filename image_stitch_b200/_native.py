@@ -20,7 +20,7 @@ OUT_PNG_FILTERED, OUT_RAW_RGBA, OUT_JPEG_ENTROPY, OUT_PNG_DEFLATE = 0, 1, 2, 3
 EXPORTS = [
     "stitch_abi_version", "stitch_ctx_create", "stitch_ctx_destroy", "stitch_ctx_set_stream",
     "stitch_last_error", "stitch_job_create", "stitch_job_destroy", "stitch_job_add_tile",
-    "stitch_job_add_tile_device", "stitch_job_decode", "stitch_job_invalidate", "stitch_job_run_band", "stitch_job_band_device",
+    "stitch_job_add_tile_device", "stitch_job_add_tile_palette", "stitch_job_decode", "stitch_job_invalidate", "stitch_job_run_band", "stitch_job_band_device",
     "stitch_job_status", "stitch_decode_image", "stitch_filter_rows", "stitch_jpeg_header",
     "stitch_job_inflate", "stitch_inflate",
 ]
@@ -98,6 +98,7 @@ def load() -> C.CDLL:
     lib.stitch_job_destroy.restype = None
     lib.stitch_job_add_tile.argtypes = [vp, C.POINTER(TileDesc), vp, sz]
     lib.stitch_job_add_tile_device.argtypes = [vp, C.POINTER(TileDesc), vp, sz]
+    lib.stitch_job_add_tile_palette.argtypes = [vp, C.POINTER(TileDesc), vp, sz, vp, sz, vp, sz]
     lib.stitch_job_decode.argtypes = [vp, C.c_int, C.POINTER(Timings)]
     lib.stitch_job_invalidate.argtypes = [vp]
     lib.stitch_job_run_band.argtypes = [vp, C.c_uint32, C.c_uint32, vp, sz, C.POINTER(sz), C.POINTER(Timings)]
@@ -254,7 +255,7 @@ class Job:
 
     def add_tile(self, data, *, width, height, bit_depth, color_type, interlace=0, filtered=1, dst_x=0, dst_y=0,
                  src_off_x=0, src_off_y=0, vis_w=None, vis_h=None, z_index=0, image_idx=0, device_ptr=None,
-                 length=None) -> None:
+                 length=None, plte=None, trns=b"") -> None:
         td = TileDesc(width=width, height=height, bit_depth=bit_depth, color_type=color_type, interlace=interlace,
                       filtered=filtered, dst_x=dst_x, dst_y=dst_y, src_off_x=src_off_x, src_off_y=src_off_y,
                       vis_w=width if vis_w is None else vis_w, vis_h=height if vis_h is None else vis_h,
@@ -265,7 +266,12 @@ class Job:
             if isinstance(data, memoryview):
                 data = bytes(data)
             n = len(data) if length is None else length
-            rc = self.lib.stitch_job_add_tile(self.handle, C.byref(td), _addr(data), n)
+            if plte is not None:   # 8f.4 extension: colour type 3 with its PLTE / tRNS chunk bodies
+                plte, trns = bytes(plte), bytes(trns or b"")
+                rc = self.lib.stitch_job_add_tile_palette(self.handle, C.byref(td), _addr(data), n, _addr(plte), len(plte),
+                                                          _addr(trns) if trns else None, len(trns))
+            else:
+                rc = self.lib.stitch_job_add_tile(self.handle, C.byref(td), _addr(data), n)
         self.ctx.check(rc)
 
     def decode(self, force: bool = False) -> dict:

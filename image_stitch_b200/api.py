@@ -71,7 +71,8 @@ class StreamingConcatenator:
             sources: Dict[int, TileSource] = {}
             for idx in needed:
                 try:
-                    sources[idx] = engine.read_tile_source(decoders[idx], headers[idx], idx, bool(opts.device_inflate))
+                    sources[idx] = engine.read_tile_source(decoders[idx], headers[idx], idx, bool(opts.device_inflate),
+                                                                bool(opts.expand_palette))
                 except StitchFailure:
                     raise
                 except Exception as e:  # decoder failures surface as stitch errors (:21-28)

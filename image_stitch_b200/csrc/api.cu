@@ -225,7 +225,8 @@ static void free_tile(stitch_ctx *ctx, TileRec &t) {
   if (t.d_src && !t.src_external) dev_free(ctx, t.d_src);
   if (t.d_z && !t.z_external) dev_free(ctx, t.d_z);
   dev_free(ctx, t.d_pass);
-  t.d_pix = t.d_src = t.d_pass = t.d_z = nullptr;
+  if (t.d_idx && t.d_idx != t.d_src) dev_free(ctx, t.d_idx);
+  t.d_pix = t.d_src = t.d_pass = t.d_z = t.d_idx = nullptr;
 }
 
 extern "C" void stitch_job_destroy(stitch_job *job) {
@@ -234,7 +235,7 @@ extern "C" void stitch_job_destroy(stitch_job *job) {
   cudaSetDevice(ctx->device);
   for (auto &t : job->tiles) free_tile(ctx, t);
   dev_free(ctx, job->d_tiles); dev_free(ctx, job->d_bin_start); dev_free(ctx, job->d_bin_tiles);
-  dev_free(ctx, job->d_streams); dev_free(ctx, job->d_a7);
+  dev_free(ctx, job->d_streams); dev_free(ctx, job->d_a7); dev_free(ctx, job->d_pal);
   dev_free(ctx, job->d_slow); dev_free(ctx, job->d_units); dev_free(ctx, job->d_uprog);
   dev_free(ctx, job->d_canvas); dev_free(ctx, job->d_out); dev_free(ctx, job->d_sync); dev_free(ctx, job->d_plans); dev_free(ctx, job->d_ctab);
   dev_free(ctx, job->d_defl); dev_free(ctx, job->d_defl_b); dev_free(ctx, job->d_defl_scratch);
@@ -257,13 +258,20 @@ static uint32_t a7_extent(uint32_t dim, int start, int step) {
   return (int64_t)dim <= start ? 0u : (uint32_t)(((int64_t)dim - start + step - 1) / step);
 }
 
+// Colour type / bit depth pairs the path takes: the reference's (common.cuh src_fmt), and colour type 3 only
+// for a tile that came with its palette (stitch_job_add_tile_palette, the 8f.4 extension).
+static bool format_ok(const stitch_tile_desc &d, bool has_pal) {
+  if (d.color_type == 3) return has_pal && (d.bit_depth == 1 || d.bit_depth == 2 || d.bit_depth == 4 || d.bit_depth == 8);
+  return samples_per_pixel(d.color_type) > 0 && src_fmt(d.color_type, d.bit_depth) != FMT_INVALID;
+}
+
 // Validates the descriptor and stream length the way the reference does while
 // reading, and prepares the unfilter chains.  d_src must already be set.
 static int prepare_tile(stitch_ctx *ctx, stitch_job *job, TileRec &t, uint32_t tile_no) {
   const stitch_tile_desc &d = t.d;
   const int spp = samples_per_pixel(d.color_type);
-  if (spp < 0 || d.color_type == 3 || src_fmt(d.color_type, d.bit_depth) == FMT_INVALID) {
-    if (d.color_type == 3 || spp < 0)  // pixel-ops.ts:609-611 (palette reaches convertScanline and throws)
+  if (!format_ok(d, t.has_pal)) {
+    if ((d.color_type == 3 && !t.has_pal) || spp < 0)  // pixel-ops.ts:609-611 (palette reaches convertScanline and throws)
       return fail(ctx, STITCH_E_COLOR, "Unsupported source color type: %u", d.color_type);
     return fail(ctx, STITCH_E_INVALID, "Unsupported bit depth %u for color type %u", d.bit_depth, d.color_type);
   }
@@ -276,26 +284,50 @@ static int prepare_tile(stitch_ctx *ctx, stitch_job *job, TileRec &t, uint32_t t
   }
   const size_t rb = scanline_bytes(d.width, d.bit_depth, d.color_type);
   const uint32_t fbpp = (uint32_t)((spp * d.bit_depth + 7) / 8);
-  if (rb >= (1ull << 31)) return fail(ctx, STITCH_E_INVALID, "tile row too large");
+  if (rb >= (1ull << 31) || (t.has_pal && d.width >= (1u << 29))) return fail(ctx, STITCH_E_INVALID, "tile row too large");
   t.streams.clear();
   t.has_a7 = false;
+  // the plane the unfilter chains (and the Adam7 gather) write: the pixels themselves, or palette indices
+  uint8_t *plane = nullptr;
+  uint32_t plane_pitch = (uint32_t)round_up(rb, 16);
+  auto alloc_planes = [&]() -> int {
+    int rc = STITCH_OK;
+    if (t.has_pal) {
+      t.pitch = (uint32_t)round_up((size_t)d.width * 4u, 16);
+      t.idx_pitch = plane_pitch;
+      if (d.filtered && (rc = dev_alloc(ctx, (void **)&t.d_idx, (size_t)plane_pitch * d.height))) return rc;
+      plane = t.d_idx;
+    } else {
+      t.pitch = plane_pitch;
+    }
+    if ((rc = dev_alloc(ctx, (void **)&t.d_pix, (size_t)t.pitch * d.height))) return rc;
+    if (!t.has_pal) plane = t.d_pix;
+    return rc;
+  };
   if (!d.filtered) {
     if (t.src_len < rb * d.height)  // image-concat-core.ts:427-448 (decoder ended early / wrong row length)
       return fail(ctx, STITCH_E_TRUNCATED, "Expected %u scanlines, decoded %zu", d.height, rb ? t.src_len / rb : 0);
+    if (t.has_pal) {  // raw index rows: only the expansion is left to do
+      plane_pitch = (uint32_t)rb;
+      int rc = alloc_planes();
+      if (rc) return rc;
+      t.d_idx = t.d_src;
+      t.decoded = false;
+      return STITCH_OK;
+    }
     t.d_pix = t.d_src;
     t.pitch = (uint32_t)rb;
     t.decoded = true;
     return STITCH_OK;
   }
-  t.pitch = (uint32_t)round_up(rb, 16);
   if (!d.interlace) {
     if (t.src_len < (rb + 1) * (size_t)d.height)  // png-decoder.ts:209-211
       return fail(ctx, STITCH_E_TRUNCATED, "Expected %u scanlines, decoded %zu", d.height, t.src_len / (rb + 1));
-    int rc = dev_alloc(ctx, (void **)&t.d_pix, (size_t)t.pitch * d.height);
+    int rc = alloc_planes();
     if (rc) return rc;
     UnfStream s{};
-    s.src = t.d_src; s.dst = t.d_pix; s.src_stride = (uint32_t)rb + 1; s.row_bytes = (uint32_t)rb;
-    s.dst_pitch = t.pitch; s.rows = d.height; s.bpp = fbpp; s.last_row_bytes = (uint32_t)rb;
+    s.src = t.d_src; s.dst = plane; s.src_stride = (uint32_t)rb + 1; s.row_bytes = (uint32_t)rb;
+    s.dst_pitch = plane_pitch; s.rows = d.height; s.bpp = fbpp; s.last_row_bytes = (uint32_t)rb;
     s.tile = tile_no; s.pass = 0;
     s.src_end = t.d_src + round_up(t.src_len, 16);
     t.streams.push_back(s);
@@ -328,8 +360,7 @@ static int prepare_tile(stitch_ctx *ctx, stitch_job *job, TileRec &t, uint32_t t
   }
   int rc = dev_alloc(ctx, (void **)&t.d_pass, scratch + 16);
   if (rc) return rc;
-  rc = dev_alloc(ctx, (void **)&t.d_pix, (size_t)t.pitch * d.height);
-  if (rc) return rc;
+  if ((rc = alloc_planes())) return rc;
   memset(&t.a7, 0, sizeof t.a7);
   for (int p = 0; p < 7; p++) {
     t.a7.pass_pix[p] = t.d_pass + pass_scr[p];
@@ -342,7 +373,7 @@ static int prepare_tile(stitch_ctx *ctx, stitch_job *job, TileRec &t, uint32_t t
     s.src_end = t.d_src + round_up(t.src_len, 16);
     t.streams.push_back(s);
   }
-  t.a7.dst = t.d_pix; t.a7.dst_pitch = t.pitch; t.a7.width = d.width; t.a7.height = d.height;
+  t.a7.dst = plane; t.a7.dst_pitch = plane_pitch; t.a7.width = d.width; t.a7.height = d.height;
   t.a7.bit_depth = d.bit_depth; t.a7.bpp = fbpp; t.a7.row_bytes = (uint32_t)rb;
   t.has_a7 = true;
   return STITCH_OK;
@@ -350,9 +381,9 @@ static int prepare_tile(stitch_ctx *ctx, stitch_job *job, TileRec &t, uint32_t t
 
 // Bytes of the inflated IDAT stream a descriptor promises: filter byte + row for every row of the image
 // (png-decoder.ts:92) or of every non-empty Adam7 pass (adam7.ts:61-107).  0 for descriptors prepare_tile rejects.
-static size_t inflated_len(const stitch_tile_desc &d) {
+static size_t inflated_len(const stitch_tile_desc &d, bool has_pal) {
   const int spp = samples_per_pixel(d.color_type);
-  if (spp < 0 || d.color_type == 3 || src_fmt(d.color_type, d.bit_depth) == FMT_INVALID || !d.width || !d.height) return 0;
+  if (!format_ok(d, has_pal) || !d.width || !d.height) return 0;
   if (!d.interlace) return (scanline_bytes(d.width, d.bit_depth, d.color_type) + 1) * (size_t)d.height;
   size_t total = 0;
   for (int p = 0; p < 7; p++) {
@@ -363,7 +394,8 @@ static size_t inflated_len(const stitch_tile_desc &d) {
   return total;
 }
 
-static int add_tile_common(stitch_job *job, const stitch_tile_desc *tile, const uint8_t *host, const void *dev, size_t len) {
+static int add_tile_common(stitch_job *job, const stitch_tile_desc *tile, const uint8_t *host, const void *dev, size_t len,
+                           const uint32_t *pal = nullptr, bool pal_opaque = true) {
   if (!job || !tile || (!host && !dev && len)) return STITCH_E_INVALID;
   stitch_ctx *ctx = job->ctx;
   cudaSetDevice(ctx->device);
@@ -371,9 +403,14 @@ static int add_tile_common(stitch_job *job, const stitch_tile_desc *tile, const 
   const bool z = tile->filtered == 2u;  // 8f.2: `data` is the zlib stream; the inflated stream is made on the device
   TileRec t;
   t.d = *tile;
+  if (pal) {
+    t.has_pal = true;
+    t.pal_opaque = pal_opaque;
+    memcpy(t.pal, pal, sizeof t.pal);
+  }
   if (z) {
     t.d.filtered = 1;
-    t.src_len = inflated_len(*tile);
+    t.src_len = inflated_len(*tile, t.has_pal);
     t.z_len = len;
     t.inflated = false;
     if (len >= (1ull << 32) || t.src_len >= (1ull << 32)) return fail(ctx, STITCH_E_INVALID, "zlib streams of 4 GiB and more are not supported");
@@ -410,6 +447,26 @@ static int add_tile_common(stitch_job *job, const stitch_tile_desc *tile, const 
 
 extern "C" int stitch_job_add_tile(stitch_job *job, const stitch_tile_desc *tile, const uint8_t *data, size_t len) {
   return add_tile_common(job, tile, data, nullptr, len);
+}
+// 8f.4 extension: a colour type 3 tile with its PLTE (3 bytes per entry) and tRNS (1 byte per entry) chunk bodies.
+extern "C" int stitch_job_add_tile_palette(stitch_job *job, const stitch_tile_desc *tile, const uint8_t *data, size_t len,
+                                           const uint8_t *plte, size_t plte_len, const uint8_t *trns, size_t trns_len) {
+  if (!job || !tile) return STITCH_E_INVALID;
+  stitch_ctx *ctx = job->ctx;
+  if (tile->color_type != 3) return fail(ctx, STITCH_E_INVALID, "a palette was given for color type %u", tile->color_type);
+  if (!plte || plte_len == 0 || plte_len % 3 != 0 || plte_len > 768)  // PNG specification 11.2.3
+    return fail(ctx, STITCH_E_INVALID, "PLTE must hold 1 to 256 entries of 3 bytes, got %zu bytes", plte_len);
+  if ((!trns && trns_len) || trns_len > plte_len / 3)              // 11.3.2.1
+    return fail(ctx, STITCH_E_INVALID, "tRNS holds %zu entries, PLTE %zu", trns_len, plte_len / 3);
+  uint32_t pal[256];
+  bool opaque = true;
+  for (size_t i = 0; i < 256; i++) {
+    uint32_t v = 0xFF000000u;
+    if (i < plte_len / 3) v |= (uint32_t)plte[3 * i] | ((uint32_t)plte[3 * i + 1] << 8) | ((uint32_t)plte[3 * i + 2] << 16);
+    if (i < trns_len) { v = (v & 0x00FFFFFFu) | ((uint32_t)trns[i] << 24); opaque = opaque && trns[i] == 255; }
+    pal[i] = v;
+  }
+  return add_tile_common(job, tile, data, nullptr, len, pal, opaque);
 }
 extern "C" int stitch_job_add_tile_device(stitch_job *job, const stitch_tile_desc *tile, const void *device_data, size_t len) {
   if (((uintptr_t)device_data & 15u) != 0) return fail(job ? job->ctx : nullptr, STITCH_E_INVALID, "device_data must be 16-byte aligned");
@@ -546,9 +603,10 @@ static int decode_tiles(stitch_job *job, int force, uint32_t *launches, uint32_t
   if ((wrc = inflate_tiles(job, 0, launches, ya, yb))) return wrc;
   std::vector<UnfStream> streams;
   std::vector<A7Image> a7;
-  uint32_t a7_max_rb = 0, a7_max_h = 0;
+  std::vector<PalImage> pal;
+  uint32_t a7_max_rb = 0, a7_max_h = 0, pal_max_w = 0, pal_max_h = 0;
   for (auto &t : job->tiles) {
-    if (!t.d.filtered) continue;
+    if (!t.d.filtered && !t.has_pal) continue;
     if (t.decoded && !force) continue;
     if (t.d.vis_h && ((int64_t)t.d.dst_y + t.d.vis_h <= (int64_t)ya || (int64_t)t.d.dst_y >= (int64_t)yb)) continue;
     for (auto &s : t.streams) streams.push_back(s);
@@ -557,9 +615,26 @@ static int decode_tiles(stitch_job *job, int force, uint32_t *launches, uint32_t
       a7_max_rb = std::max(a7_max_rb, t.a7.row_bytes);
       a7_max_h = std::max(a7_max_h, t.a7.height);
     }
+    if (t.has_pal) {
+      PalImage pi{};
+      pi.idx = t.d_idx; pi.dst = t.d_pix; pi.idx_pitch = t.idx_pitch; pi.dst_pitch = t.pitch;
+      pi.width = t.d.width; pi.height = t.d.height; pi.bit_depth = t.d.bit_depth;
+      memcpy(pi.pal, t.pal, sizeof pi.pal);
+      pal.push_back(pi);
+      pal_max_w = std::max(pal_max_w, t.d.width);
+      pal_max_h = std::max(pal_max_h, t.d.height);
+    }
     t.decoded = true;
   }
-  if (streams.empty()) return STITCH_OK;
+  auto expand_palettes = [&]() -> int {  // after the index planes are whole
+    if (pal.empty()) return STITCH_OK;
+    int rc = upload_array(ctx, pal, &job->d_pal, &job->pal_cap);
+    if (rc) return rc;
+    CK(launch_expand_palette(job->d_pal, (uint32_t)pal.size(), pal_max_w, pal_max_h, ctx->stream));
+    if (launches) (*launches)++;
+    return STITCH_OK;
+  };
+  if (streams.empty()) return expand_palettes();
   // Chains whose final row is cut short (Adam7 slice semantics, adam7.ts:87-88) keep the legacy kernel;
   // everything else runs on the wavefront kernel, one unit per 32-row group, handed out group-major so
   // that all chains advance together and a unit's predecessor is always already running.
@@ -623,7 +698,7 @@ static int decode_tiles(stitch_job *job, int force, uint32_t *launches, uint32_t
     CK(launch_adam7_gather(job->d_a7, (uint32_t)a7.size(), a7_max_rb, a7_max_h, ctx->stream));
     if (launches) (*launches)++;
   }
-  return STITCH_OK;
+  return expand_palettes();
 }
 
 extern "C" int stitch_job_inflate(stitch_job *job, int force, stitch_timings *t) {
@@ -733,10 +808,10 @@ static int finalize_job(stitch_job *job) {
   for (size_t k = 0; k < order.size(); k++) {
     const TileRec &t = job->tiles[order[k]];
     DevTile &o = dt[k];
-    o.pix = t.d_pix; o.pitch = t.pitch; o.fmt = src_fmt(t.d.color_type, t.d.bit_depth);
+    o.pix = t.d_pix; o.pitch = t.pitch; o.fmt = t.has_pal ? (uint32_t)FMT_RGBA8 : src_fmt(t.d.color_type, t.d.bit_depth);
     o.x0 = t.d.dst_x; o.y0 = t.d.dst_y; o.x1 = t.d.dst_x + (int32_t)t.d.vis_w; o.y1 = t.d.dst_y + (int32_t)t.d.vis_h;
     o.sx0 = (int32_t)t.d.src_off_x; o.sy0 = (int32_t)t.d.src_off_y;
-    o.opaque = (t.d.color_type == 0 || t.d.color_type == 2) ? 1u : 0u;
+    o.opaque = t.has_pal ? (t.pal_opaque ? 1u : 0u) : (t.d.color_type == 0 || t.d.color_type == 2) ? 1u : 0u;
     o.pad = 0;
   }
   // Bins are the fused kernel's items (absolute grid: FB_R rows x FB_SWW words).  A bin also lists

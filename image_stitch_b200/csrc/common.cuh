@@ -73,6 +73,16 @@ struct A7Image {
   uint32_t row_bytes;
 };
 
+// One colour type 3 image for expand_palette_kernel (8f.4 extension; the reference throws on palette input).
+struct PalImage {
+  const uint8_t *idx;   // dense rows of palette indices, MSB first below 8 bits
+  uint8_t *dst;         // RGBA8 rows
+  uint32_t idx_pitch, dst_pitch;
+  uint32_t width, height;
+  uint32_t bit_depth, pad;
+  uint32_t pal[256];    // RGBA8 in memory order
+};
+
 // device error word: 0 = none, else (kind<<56 | tile<<24 | row/aux)
 struct DevStatus {
   unsigned long long first_error;

@@ -233,6 +233,34 @@ __global__ void __launch_bounds__(256) adam7_gather_kernel(const A7Image *images
   }
 }
 
+// ---- palette expansion (an extension: pixel-ops.ts:609-611 throws on colour type 3) ---------
+// PNG specification, colour type 3: RGB from PLTE[index], alpha from tRNS[index] or 255.  The host has merged
+// both into one 256-entry RGBA table; a block keeps it in shared memory, a thread expands four pixels into one
+// 16-byte store.  Reads 1 B (or less) and writes 4 B per pixel.
+__global__ void __launch_bounds__(256) expand_palette_kernel(const PalImage *__restrict__ images) {
+  const PalImage &im = images[blockIdx.z];
+  __shared__ uint32_t pal[256];
+  pal[threadIdx.x] = im.pal[threadIdx.x];
+  __syncthreads();
+  const uint32_t x0 = (blockIdx.x * 256u + threadIdx.x) * 4u;
+  if (x0 >= im.width) return;
+  const uint32_t bd = im.bit_depth, mask = (1u << bd) - 1u;
+  for (uint32_t y = blockIdx.y; y < im.height; y += gridDim.y) {
+    const uint8_t *row = im.idx + (size_t)y * im.idx_pitch;
+    uint32_t px[4];
+#pragma unroll
+    for (uint32_t k = 0; k < 4u; k++) {
+      const uint32_t x = x0 + k < im.width ? x0 + k : im.width - 1u;
+      const uint32_t bit = x * bd;
+      px[k] = pal[(row[bit >> 3] >> (8u - (bit & 7u) - bd)) & mask];
+    }
+    uint8_t *o = im.dst + (size_t)y * im.dst_pitch + (size_t)x0 * 4u;
+    if (x0 + 4u <= im.width) *reinterpret_cast<uint4 *>(o) = make_uint4(px[0], px[1], px[2], px[3]);
+    else
+      for (uint32_t k = 0; x0 + k < im.width; k++) reinterpret_cast<uint32_t *>(o)[k] = px[k];
+  }
+}
+
 // ---- host launchers ---------------------------------------------------------
 
 cudaError_t launch_unfilter(const UnfStream *d_streams, uint32_t n_streams, DevStatus *d_status, cudaStream_t st) {
@@ -246,6 +274,14 @@ cudaError_t launch_adam7_gather(const A7Image *d_images, uint32_t n_images, uint
   if (n_images == 0) return cudaSuccess;
   dim3 grid((max_row_bytes + 255u) / 256u, max_height < 1024u ? (max_height ? max_height : 1u) : 1024u, n_images);
   adam7_gather_kernel<<<grid, 256, 0, st>>>(d_images);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_expand_palette(const PalImage *d_images, uint32_t n_images, uint32_t max_width, uint32_t max_height,
+                                  cudaStream_t st) {
+  if (n_images == 0) return cudaSuccess;
+  dim3 grid((max_width + 1023u) / 1024u, max_height < 1024u ? (max_height ? max_height : 1u) : 1024u, n_images);
+  expand_palette_kernel<<<grid, 256, 0, st>>>(d_images);
   return cudaGetLastError();
 }
 

@@ -44,6 +44,11 @@ struct TileRec {
   bool z_external = false;
   size_t z_len = 0;
   bool inflated = true;       // false: d_src is still to be produced from d_z (inflate.cu)
+  // 8f.4 extension (colour type 3): the unfilter chains write the index plane d_idx, expand_palette_kernel makes d_pix (RGBA8)
+  bool has_pal = false, pal_opaque = true;
+  uint8_t *d_idx = nullptr;   // == d_src for filtered == 0
+  uint32_t idx_pitch = 0;
+  uint32_t pal[256];          // RGBA8 in memory order; entries past PLTE are opaque black
   cudaEvent_t up_event = nullptr;  // recorded on ctx->up after the tile's bytes were queued
   bool up_waited = true;           // ctx->stream already waits for up_event
 };
@@ -65,6 +70,7 @@ struct stitch_job {
   uint32_t n_fast_units = 0;
   uint32_t seam_epoch = 0;                                   // tag of the last decode that used the mailbox
   stitch::A7Image *d_a7 = nullptr; size_t a7_cap = 0;
+  stitch::PalImage *d_pal = nullptr; size_t pal_cap = 0;
   uint32_t bins_x = 0, bins_y = 0, bin_w_log2 = 9, bin_h_log2 = 4, bin_y_origin = 0;
   // inflate (8f.2): stream table, one result slot per tile, pinned mirror, tiles whose result is not checked yet
   stitch::InfStream *d_inf = nullptr; size_t inf_cap = 0;

@@ -72,6 +72,8 @@ cudaError_t launch_unfilter_wave(const UnfStream *d_streams, const UnfUnit *d_un
                                  uint32_t uniform_bpp /* 0 = mixed */, cudaStream_t st);
 cudaError_t launch_adam7_gather(const A7Image *d_images, uint32_t n_images, uint32_t max_row_bytes,
                                 uint32_t max_height, cudaStream_t st);
+cudaError_t launch_expand_palette(const PalImage *d_images, uint32_t n_images, uint32_t max_width, uint32_t max_height,
+                                  cudaStream_t st);
 cudaError_t launch_compose(const ComposeParams &p, bool out16, cudaStream_t st);
 cudaError_t launch_filter_rows(const FilterParams &p, cudaStream_t st);
 

@@ -69,6 +69,19 @@ class PngBufferDecoder:
         self._header = parse_png_header(self._bytes())
         return self._header, extract_idat(chunks)
 
+    def palette(self) -> Tuple[Optional[bytes], bytes]:
+        """(PLTE body, tRNS body) of a colour type 3 file, for the `expand_palette` extension (SURVEY.md 8f.4);
+        the reference never reads these chunks."""
+        plte, trns = None, b""
+        for c in parse_png_chunks(self._bytes()):
+            if c.type == "PLTE" and plte is None:
+                plte = bytes(c.data)
+            elif c.type == "tRNS":
+                trns = bytes(c.data)
+            elif c.type == "IDAT":
+                break
+        return plte, trns
+
     def scanlines(self) -> Iterator[bytes]:
         from .. import engine
         header, stream = self.inflated()

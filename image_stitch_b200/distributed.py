@@ -106,7 +106,7 @@ def stitch_rank_band(options, render: Optional[BandRenderer] = None):
         if y1 <= y0:
             return plan, (y0, y1), b""
         needed = sorted({p.image_idx for p in placements_for_band(plan, y0, y1)})
-        sources = {i: engine.read_tile_source(decoders[i], headers[i], i, bool(opts.device_inflate)) for i in needed}
+        sources = {i: engine.read_tile_source(decoders[i], headers[i], i, bool(opts.device_inflate), bool(opts.expand_palette)) for i in needed}
         band = (render or gpu_band)(plan, sources, y0, y1)
         return plan, (y0, y1), band
     finally:

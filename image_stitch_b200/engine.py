@@ -158,18 +158,28 @@ class TileSource:
     data: object          # bytes-like
     filtered: int
     interlace: int
+    plte: Optional[bytes] = None   # expand_palette extension: chunk bodies of a colour type 3 input
+    trns: bytes = b""
 
 
-def read_tile_source(decoder, declared: PngHeader, image_idx: int, device_inflate: bool = False) -> TileSource:
+def read_tile_source(decoder, declared: PngHeader, image_idx: int, device_inflate: bool = False,
+                     expand_palette: bool = False) -> TileSource:
     """Fetches one input's pixel bytes.  Decoders offering ``inflated()`` hand over the
     still-filtered stream (GPU unfilter); any other ImageDecoder is drained
     through scanlines() with the reference's row checks (image-concat-core.ts:427-448)."""
+    def with_palette(src: TileSource) -> TileSource:
+        if expand_palette and src.header.color_type == 3 and hasattr(decoder, "palette"):
+            src.plte, src.trns = decoder.palette()
+            if src.plte is None:
+                raise StitchFailure(f"input #{image_idx + 1} has colour type 3 but no PLTE chunk")
+        return src
+
     if device_inflate and hasattr(decoder, "deflated"):
         hdr, zstream = decoder.deflated()      # filtered == 2: the device inflates (SURVEY.md 8f.2)
-        return TileSource(hdr, zstream, 2, 1 if hdr.interlace_method == 1 else 0)
+        return with_palette(TileSource(hdr, zstream, 2, 1 if hdr.interlace_method == 1 else 0))
     if hasattr(decoder, "inflated"):
         hdr, stream = decoder.inflated()
-        return TileSource(hdr, stream, 1, 1 if hdr.interlace_method == 1 else 0)
+        return with_palette(TileSource(hdr, stream, 1, 1 if hdr.interlace_method == 1 else 0))
     expected = scanline_bytes(declared.width, declared.bit_depth, declared.color_type)
     rows = []
     for n, row in enumerate(decoder.scanlines()):
@@ -223,7 +233,8 @@ class BandRunner:
                 self.job.add_tile(s.data, width=s.header.width, height=s.header.height, bit_depth=s.header.bit_depth,
                                   color_type=s.header.color_type, interlace=s.interlace, filtered=s.filtered,
                                   dst_x=p.dst_x, dst_y=p.dst_y, src_off_x=p.src_off_x, src_off_y=p.src_off_y,
-                                  vis_w=p.vis_w, vis_h=p.vis_h, z_index=p.z_index, image_idx=p.image_idx)
+                                  vis_w=p.vis_w, vis_h=p.vis_h, z_index=p.z_index, image_idx=p.image_idx,
+                                  plte=s.plte, trns=s.trns)
                 self.tiles.append(p)
 
     def run(self, a: int, b: int):

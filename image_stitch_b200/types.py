@@ -107,6 +107,9 @@ class ConcatOptions:
     # additive: PNG inputs cross the bus as their zlib streams and are inflated on the device;
     # same pixels, and zlib's error messages when a stream is corrupt
     device_inflate: bool = False
+    # additive, BEYOND the reference: colour type 3 inputs are expanded through PLTE/tRNS on the
+    # device.  Off by default: the reference fails with `Unsupported source color type: 3`, and so does this build
+    expand_palette: bool = False
 
     @staticmethod
     def coerce(options: Union["ConcatOptions", dict]) -> "ConcatOptions":
@@ -116,13 +119,14 @@ class ConcatOptions:
             known = {
                 "inputs", "layout", "decoder_options", "decoders", "output_format", "jpeg_quality",
                 "background_color", "enable_alpha_blending", "on_progress", "devices", "band_rows",
-                "device_deflate", "device_inflate",
+                "device_deflate", "device_inflate", "expand_palette",
             }
             camel = {
                 "decoderOptions": "decoder_options", "outputFormat": "output_format",
                 "jpegQuality": "jpeg_quality", "backgroundColor": "background_color",
                 "enableAlphaBlending": "enable_alpha_blending", "onProgress": "on_progress",
                 "deviceDeflate": "device_deflate", "deviceInflate": "device_inflate",
+                "expandPalette": "expand_palette",
             }
             kw = {}
             for k, v in dict(options).items():

@@ -154,6 +154,16 @@ void stitch_job_destroy(stitch_job *job);
  * validated on the device by stitch_job_decode. */
 int stitch_job_add_tile(stitch_job *job, const stitch_tile_desc *tile, const uint8_t *data, size_t len);
 
+/* EXTENSION, beyond the reference: a colour type 3 tile together with the bodies of its PLTE
+ * (3 bytes per entry, 1..256 entries) and tRNS (1 alpha byte per entry, may be NULL/0) chunks.  The reference
+ * has no such path -- convertScanline throws `Unsupported source color type: 3` (pixel-ops.ts:609-611), which
+ * is what stitch_job_add_tile keeps returning for colour type 3.  Here the index plane (bit depth 1, 2, 4, 8;
+ * filtered 0, 1 or 2; interlaced or not) is decoded by kernel (a) and expanded to RGBA8 on the device as the PNG
+ * specification defines: RGB = PLTE[i], A = tRNS[i] or 255; an index past the end of PLTE gives opaque black.
+ * Checked against the third-party pngsuite/json goldens, not against the reference. */
+int stitch_job_add_tile_palette(stitch_job *job, const stitch_tile_desc *tile, const uint8_t *data, size_t len,
+                                const uint8_t *plte, size_t plte_len, const uint8_t *trns, size_t trns_len);
+
 /* Same, but `device_data` already lives in this ctx's device memory (16-byte
  * aligned, stays valid and unmodified until the job is destroyed). */
 int stitch_job_add_tile_device(stitch_job *job, const stitch_tile_desc *tile, const void *device_data, size_t len);

@@ -264,6 +264,25 @@ uint32_t orc_scale_sample(uint32_t value, int from_bits, int to_bits) {
 
 static uint32_t be16(const uint8_t *p) { return ((uint32_t)p[0] << 8) | p[1]; }
 
+/* Extension (see oracle.h): colour type 3 -> RGBA8 per the PNG specification. */
+void orc_expand_palette_scanline(const uint8_t *src, uint32_t width, int bit_depth, const uint8_t *plte,
+                                 size_t plte_len, const uint8_t *trns, size_t trns_len, uint8_t *dst) {
+  const size_t entries = plte_len / 3;
+  const uint32_t mask = (1u << bit_depth) - 1u;
+  uint32_t x;
+  for (x = 0; x < width; x++) {
+    const size_t bit = (size_t)x * (size_t)bit_depth;
+    const uint32_t idx = (src[bit >> 3] >> (8 - (int)(bit & 7) - bit_depth)) & mask;
+    uint8_t *o = dst + (size_t)x * 4;
+    if (idx < entries) {
+      o[0] = plte[idx * 3]; o[1] = plte[idx * 3 + 1]; o[2] = plte[idx * 3 + 2];
+    } else {
+      o[0] = o[1] = o[2] = 0;
+    }
+    o[3] = idx < trns_len ? trns[idx] : 255;
+  }
+}
+
 /* pixel-ops.ts:496-633 */
 int orc_convert_scanline(const uint8_t *src, uint32_t width, int sbd, int sct,
                          int tbd, int tct, uint8_t *dst) {

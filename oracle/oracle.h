@@ -80,6 +80,14 @@ uint32_t orc_scale_sample(uint32_t value, int from_bits, int to_bits);
 int orc_convert_scanline(const uint8_t *src, uint32_t width, int src_bit_depth, int src_color_type,
                          int tgt_bit_depth, int tgt_color_type, uint8_t *dst);
 
+/* EXTENSION, beyond the reference: the reference throws `Unsupported source color type: 3`
+ * (pixel-ops.ts:609-611); this expands one row of palette indices (bit depth 1, 2, 4 or 8, MSB first like
+ * pixel-ops.ts:540-552 reads sub-byte gray) to RGBA8 the way the PNG specification defines colour type 3:
+ * RGB from PLTE entry i, alpha from tRNS entry i where present, else 255; an index past the end of PLTE gives
+ * opaque black.  Not a parity claim: pinned by the third-party pngsuite/json goldens of the 63 palette files. */
+void orc_expand_palette_scanline(const uint8_t *src, uint32_t width, int bit_depth, const uint8_t *plte,
+                                 size_t plte_len, const uint8_t *trns, size_t trns_len, uint8_t *dst);
+
 /* pixel-ops.ts:646-736 */
 void orc_composite_scanline(uint8_t *dest, const uint8_t *source, uint32_t start_x,
                             uint32_t source_width, int bytes_per_pixel, int use_alpha_blending);

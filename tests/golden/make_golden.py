@@ -7,6 +7,8 @@ What is copied are FIXTURES, not reference source code:
   * expected-outputs/example1..5.png   genuine reference outputs
         (tests/utils/fixtures/expected-outputs, recipes in tests/utils/generate-expected-outputs.js:29-106)
   * pngsuite_rgba.npz           the lunapaint/pngsuite JSON goldens (pngsuite/json/*.json) as arrays
+  * pngsuite_palette_rgba.npz   the same for the colour type 3 files: the reference throws on those, the goldens pin
+                                the palette EXTENSION and nothing else
 """
 import json
 import os
@@ -39,7 +41,7 @@ def main():
     for n in sorted(os.listdir(exp_src)):
         shutil.copyfile(os.path.join(exp_src, n), os.path.join(exp_dst, n))
     # JSON goldens: flat [r,g,b,a,...]; 8-bit values for <=8-bit sources, 16-bit values for 16-bit sources.
-    arrays = {}
+    arrays, palette = {}, {}
     jdir = os.path.join(REF, "pngsuite", "json")
     for n in names:
         stem = n[:-4]
@@ -47,17 +49,17 @@ def main():
         if not os.path.exists(jp):
             continue
         w, h, bd, ct, _, _, _ = png_ihdr(os.path.join(png_src, n))
-        if ct == 3:
-            continue  # the reference throws on palette images
         with open(jp) as f:
             vals = json.load(f)
         a = np.asarray(vals, dtype=np.uint16 if bd == 16 else np.uint8)
         if a.size != w * h * 4:
             print("skip (size)", stem, a.size, w, h)
             continue
-        arrays[stem] = a.reshape(h, w, 4)
+        # the reference throws on palette images: kept apart from the parity goldens
+        (palette if ct == 3 else arrays)[stem] = a.reshape(h, w, 4)
     np.savez_compressed(os.path.join(HERE, "pngsuite_rgba.npz"), **arrays)
-    print(f"{len(names)} PNGs, {len(arrays)} JSON goldens")
+    np.savez_compressed(os.path.join(HERE, "pngsuite_palette_rgba.npz"), **palette)
+    print(f"{len(names)} PNGs, {len(arrays)} JSON goldens, {len(palette)} palette goldens (extension)")
 
 
 if __name__ == "__main__":

@@ -47,6 +47,10 @@ def oracle_plan(options):
         if hasattr(dec, "inflated"):
             h, stream = dec.inflated()
             pix = orc.decode_scanlines(stream, h.width, h.height, h.bit_depth, h.color_type, h.interlace_method)
+            if h.color_type == 3 and opts.expand_palette:   # extension (oracle.h): the tile enters as RGBA8
+                plte, trns = dec.palette()
+                pix = orc.expand_palette(pix, h.width, h.height, h.bit_depth, plte, trns).reshape(-1)
+                h = PngHeader(h.width, h.height, 8, 6, h.compression_method, h.filter_method, h.interlace_method)
         else:
             h = headers[p.image_idx]
             pix = np.frombuffer(b"".join(dec.scanlines()), np.uint8)

@@ -53,6 +53,8 @@ def lib() -> C.CDLL:
         l.orc_scale_sample.argtypes = [C.c_uint32, C.c_int, C.c_int]
         l.orc_scale_sample.restype = C.c_uint32
         l.orc_convert_scanline.argtypes = [vp, C.c_uint32, C.c_int, C.c_int, C.c_int, C.c_int, vp]
+        l.orc_expand_palette_scanline.argtypes = [vp, C.c_uint32, C.c_int, vp, sz, vp, sz, vp]
+        l.orc_expand_palette_scanline.restype = None
         l.orc_composite_scanline.argtypes = [vp, vp, C.c_uint32, C.c_uint32, C.c_int, C.c_int]
         l.orc_composite_scanline.restype = None
         l.orc_render_rows.argtypes = [C.c_uint32, C.c_uint32, C.c_int, vp, C.c_int, C.POINTER(OrcTile), sz,
@@ -146,6 +148,18 @@ def convert_scanline(src, width, sbd, sct, tbd, tct):
     if sbd == tbd and sct == tct:
         return out[: len(s)]
     return out[: width * (8 if tbd == 16 else 4)]
+
+
+def expand_palette(pix, w, h, bd, plte, trns=b""):
+    """Extension (oracle.h): h rows of palette indices -> (h, w*4) RGBA8."""
+    n = scanline_bytes(w, bd, 3)
+    src = _u8(pix)
+    p, t = _u8(plte), _u8(trns if trns else b"\0")
+    out = np.zeros((h, w * 4), np.uint8)
+    for y in range(h):
+        row = np.ascontiguousarray(src[y * n:(y + 1) * n])
+        lib().orc_expand_palette_scanline(_p(row), w, bd, _p(p), len(plte), _p(t), len(trns) if trns else 0, _p(out[y]))
+    return out
 
 
 def composite_scanline(dest, source, start_x, source_width, bpp, blend):

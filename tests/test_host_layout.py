@@ -149,3 +149,24 @@ def test_device_codec_options_and_deflated_source():
             return iter([bytes(hdr.width * 4)] * hdr.height)
     src = engine.read_tile_source(Foreign(), hdr, 0, device_inflate=True)
     assert src.filtered == 0 and len(src.data) == hdr.width * 4 * hdr.height
+
+
+def test_expand_palette_option_and_source():
+    from image_stitch_b200 import engine
+    from image_stitch_b200.decoders.png_decoder import PngBufferDecoder
+    from image_stitch_b200.layout import image_header_to_png_header
+    o = ConcatOptions.coerce({"inputs": [b""], "layout": {"columns": 1}, "expandPalette": True})
+    assert o.expand_palette is True
+    assert ConcatOptions.coerce({"inputs": [b""], "layout": {"columns": 1}}).expand_palette is False
+    png = H.suite_bytes("tbbn3p08")
+    dec = PngBufferDecoder(png)
+    hdr = image_header_to_png_header(dec.get_header())
+    plte, trns = dec.palette()
+    assert len(plte) % 3 == 0 and 0 < len(trns) <= len(plte) // 3
+    src = engine.read_tile_source(dec, hdr, 0, expand_palette=True)
+    assert src.header.color_type == 3 and src.plte == plte and src.trns == trns and src.filtered == 1
+    src = engine.read_tile_source(dec, hdr, 0, device_inflate=True, expand_palette=True)
+    assert src.filtered == 2 and src.plte == plte
+    assert engine.read_tile_source(dec, hdr, 0).plte is None            # default: the reference's error follows
+    dec2 = PngBufferDecoder(H.suite_bytes("basn2c08"))
+    assert engine.read_tile_source(dec2, image_header_to_png_header(dec2.get_header()), 0, expand_palette=True).plte is None

@@ -64,3 +64,22 @@ def test_oracle_matches_pngsuite_json(stem):
     else:
         got_v = got.reshape(hdr.height, hdr.width, 4)
     assert np.array_equal(got_v, want)
+
+
+def _palette_cases():
+    return sorted(np.load(H.GOLDEN + "/pngsuite_palette_rgba.npz").files)
+
+
+@pytest.mark.parametrize("stem", _palette_cases())
+def test_oracle_palette_extension_matches_pngsuite_json(stem):
+    """The palette expansion is an extension (the reference throws on colour type 3): its oracle
+    restates the PNG specification and is pinned by the third-party goldens only."""
+    from image_stitch_b200.decoders.png_decoder import PngBufferDecoder
+    want = np.load(H.GOLDEN + "/pngsuite_palette_rgba.npz")[stem]
+    png = H.suite_bytes(stem)
+    hdr, stream = H.inflated_idat(png)
+    assert hdr.color_type == 3
+    plte, trns = PngBufferDecoder(png).palette()
+    idx = orc.decode_scanlines(stream, hdr.width, hdr.height, hdr.bit_depth, 3, hdr.interlace_method)
+    got = orc.expand_palette(idx, hdr.width, hdr.height, hdr.bit_depth, plte, trns)
+    assert np.array_equal(got.reshape(want.shape), want)
