@@ -129,9 +129,12 @@ def _addr(buf) -> int:
         return C.cast(C.c_char_p(buf), C.c_void_p).value or 0
     if isinstance(buf, (bytearray, memoryview)):
         mv = memoryview(buf)
-        if mv.readonly:
-            raise TypeError("read-only memoryview: pass bytes, bytearray or a numpy array")
-        return C.addressof(C.c_uint8.from_buffer(mv)) if len(mv) else 0
+        if not len(mv):
+            return 0
+        if mv.readonly:   # e.g. a chunk body inside a PNG file's bytes: numpy gives the address without a copy
+            import numpy as np
+            return np.frombuffer(mv, np.uint8).__array_interface__["data"][0]
+        return C.addressof(C.c_uint8.from_buffer(mv))
     return C.addressof(buf)
 
 
@@ -263,9 +266,9 @@ class Job:
         if device_ptr is not None:
             rc = self.lib.stitch_job_add_tile_device(self.handle, C.byref(td), C.c_void_p(device_ptr), length)
         else:
-            if isinstance(data, memoryview):
+            if isinstance(data, memoryview) and not data.c_contiguous:
                 data = bytes(data)
-            n = len(data) if length is None else length
+            n = (data.nbytes if isinstance(data, memoryview) else len(data)) if length is None else length
             if plte is not None:   # 8f.4 extension: colour type 3 with its PLTE / tRNS chunk bodies
                 plte, trns = bytes(plte), bytes(trns or b"")
                 rc = self.lib.stitch_job_add_tile_palette(self.handle, C.byref(td), _addr(data), n, _addr(plte), len(plte),

@@ -13,6 +13,7 @@ through libstitch_b200.
 from __future__ import annotations
 
 import io
+import os
 import zlib
 from typing import Dict, Iterator, List, Optional, Union
 
@@ -22,6 +23,7 @@ from . import engine
 from ._native import StitchError
 from .decoders.decoder_factory import create_decoders
 from .decoders.plugin_registry import get_default_decoder_plugins
+from .decoders.png_decoder import PngBufferDecoder
 from .engine import JobPlan, StitchFailure, TileSource
 from .layout import image_header_to_png_header
 from .png_container import PNG_SIGNATURE, create_chunk, create_iend, create_ihdr, serialize_chunk
@@ -69,14 +71,29 @@ class StreamingConcatenator:
             self.plan = plan
             needed = sorted({p.image_idx for p in plan.placements})
             sources: Dict[int, TileSource] = {}
-            for idx in needed:
+
+            def read(idx: int) -> TileSource:
                 try:
-                    sources[idx] = engine.read_tile_source(decoders[idx], headers[idx], idx, bool(opts.device_inflate),
-                                                                bool(opts.expand_palette))
+                    return engine.read_tile_source(decoders[idx], headers[idx], idx, bool(opts.device_inflate),
+                                                   bool(opts.expand_palette))
                 except StitchFailure:
                     raise
                 except Exception as e:  # decoder failures surface as stitch errors (:21-28)
                     raise StitchFailure(f"unable to read input #{idx + 1}: {e}", e) from e
+
+            # The built-in PNG decoders spend their time in zlib (chunk CRC, host inflate), which releases the GIL:
+            # they are read on a few threads.  Foreign decoders are drained one after the other, as the reference
+            # does.  Errors surface in input order either way.
+            threaded = [i for i in needed if isinstance(decoders[i], PngBufferDecoder)]
+            if len(threaded) > 1:
+                from concurrent.futures import ThreadPoolExecutor
+                with ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 1, len(threaded))) as pool:
+                    futures = {i: pool.submit(read, i) for i in threaded}
+                    for idx in needed:
+                        sources[idx] = futures[idx].result() if idx in futures else read(idx)
+            else:
+                for idx in needed:
+                    sources[idx] = read(idx)
             on_band = self._progress(plan, len(inputs))
             try:
                 if plan.output_format == "jpeg":

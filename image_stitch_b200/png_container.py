@@ -50,8 +50,11 @@ def scanline_bytes(width: int, bit_depth: int, color_type: int) -> int:
 
 
 def parse_png_chunks(data) -> List[PngChunk]:
-    """src/png-parser.ts:17-86 -- same error strings."""
-    data = bytes(data)
+    """src/png-parser.ts:17-86 -- same error strings.  Bodies of 64 KiB and more (IDAT of a large tile) are views
+    into `data`, not copies."""
+    if not isinstance(data, (bytes, memoryview)):
+        data = bytes(data)
+    view = memoryview(data)
     if not is_png_signature(data):
         raise ValueError("Invalid PNG signature")
     off = 8
@@ -61,11 +64,11 @@ def parse_png_chunks(data) -> List[PngChunk]:
         if off + 12 > n:
             raise ValueError("Incomplete PNG chunk")
         (length,) = struct.unpack_from(">I", data, off)
-        ctype = data[off + 4: off + 8]
+        ctype = bytes(view[off + 4: off + 8])
         off += 8
         if off + length + 4 > n:
             raise ValueError("Incomplete PNG chunk data")
-        body = data[off: off + length]
+        body = view[off: off + length] if length >= 65536 else bytes(view[off: off + length])
         off += length
         (crc,) = struct.unpack_from(">I", data, off)
         off += 4
@@ -107,7 +110,8 @@ def parse_png_header(data) -> PngHeader:
 
 
 def extract_idat(chunks: List[PngChunk]) -> bytes:
-    return b"".join(c.data for c in chunks if c.type == "IDAT")
+    parts = [c.data for c in chunks if c.type == "IDAT"]
+    return parts[0] if len(parts) == 1 else b"".join(parts)   # one IDAT: the chunk body itself, no copy
 
 
 def inflate_idat(compressed: bytes) -> bytes:
@@ -138,7 +142,7 @@ def create_chunk(ctype: str, data: bytes) -> PngChunk:
 
 def serialize_chunk(chunk: PngChunk) -> bytes:
     """src/png-writer.ts:35-56"""
-    return struct.pack(">I", chunk.length) + chunk.type.encode("latin-1") + chunk.data + struct.pack(">I", chunk.crc)
+    return struct.pack(">I", chunk.length) + chunk.type.encode("latin-1") + bytes(chunk.data) + struct.pack(">I", chunk.crc)
 
 
 def create_ihdr(header: PngHeader) -> PngChunk:

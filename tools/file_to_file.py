@@ -7,8 +7,9 @@ import image_stitch_b200 as stitch
 from image_stitch_b200 import synth
 from image_stitch_b200.png_container import PNG_SIGNATURE, PngHeader, create_chunk, create_ihdr, create_iend, read_png, serialize_chunk
 
-G = int(sys.argv[1]) if len(sys.argv) > 1 else 8
-T = int(sys.argv[2]) if len(sys.argv) > 2 else 1024
+_pos = [a for a in sys.argv[1:] if not a.startswith("--")]
+G = int(_pos[0]) if len(_pos) > 0 else 8
+T = int(_pos[1]) if len(_pos) > 1 else 1024
 rng = np.random.default_rng(2)
 files = []
 for i in range(4):
