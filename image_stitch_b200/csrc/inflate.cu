@@ -50,6 +50,7 @@ constexpr uint32_t RES = 0xffffu;        // src[]: this byte of the window is fi
 constexpr uint32_t ZWORDS = 32u * SUBBITS / 32u + 16u;   // staged code words: the window, its 127-bit lead-in, a symbol of overrun, one word of look-ahead
 constexpr uint32_t MAX_ROUNDS = 8u;
 constexpr uint32_t F_EOB = 1u << 8, F_ERR = 1u << 9;
+constexpr uint32_t F_WIDE = 1u << 10;   // a merged record list that makes more than 512 bytes: its lane is left to the next window
 // The last 32 KiB of output (the farthest a match may reach) live in a per-warp shared-memory ring, so a match
 // copy never waits for L2; the ring is longer than that by one window's output and a flush unit, so nothing that is
 // still to be read or written out is overwritten.  Global memory is written from the ring, 512 bytes (one uint4 per
@@ -100,7 +101,7 @@ struct WarpSmem {
   uint32_t q[2][QROWS * 32u];               // symbol records (two windows in flight), record k of lane i at q[.][(base_i + k) * 32 + i]
   uint16_t bpos[SUBCAP * 32u];              // first walk of the window: the bit each record starts at
   Msg msg[2];                               // what the walking warp hands to the applying warp with them
-  uint16_t src[OUTCAP];                     // per output byte of the window: RES, or the window byte it copies
+  __align__(16) uint16_t src[OUTCAP];       // per output byte of the window: RES, or the window byte it copies
   __align__(16) uint8_t win[WIN];
 };
 static_assert(sizeof(WarpSmem) % 16 == 0, "rings must stay 16-byte aligned");
@@ -425,18 +426,21 @@ __device__ __forceinline__ uint32_t rec_bytes(uint32_t rec) { return (int)rec >=
 // `mask`: the lanes that walk in this round.  They step together: the loop condition is a vote, so the lanes meet
 // again at every symbol instead of each running its own copy of the loop.  `first`: the window's first walk, which
 // also notes where every record starts.
-__device__ __forceinline__ uint32_t walk_sub(WarpSmem &sm, uint32_t *qbuf, uint32_t start, uint32_t limit, uint32_t lane, uint32_t mask,
-                                             bool first, uint32_t &n_flag, uint32_t &n_out) {
+// Every lane of the warp calls (the votes are full-warp votes); only the `active` ones walk.  (A step that does
+// one table lookup -- literal/length OR distance, as a two-state machine -- was measured: cheaper per step, but the
+// steps of a round are then max over lanes of symbols + matches, and the round got 25 % slower.)
+__device__ __forceinline__ uint32_t walk_sub(WarpSmem &sm, uint32_t *qbuf, uint32_t start, uint32_t limit, uint32_t lane, bool active,
+                                             bool first, uint32_t old_end, uint32_t &n_flag, uint32_t &n_out) {
   LaneBits lb;
   lb.init(sm.zw, start);
   uint32_t n = 0, flag = 0, out = 0;
   uint32_t *q = qbuf + QHEAD * 32u + lane;
   uint16_t *bp = sm.bpos + lane;
-  bool live = true;
+  bool live = active;
   for (;;) {
     const uint32_t at = lb.pos();
     live = live && at < limit && n < SUBCAP && out < LANE_OUT;
-    if (!__any_sync(mask, live)) break;
+    if (!__any_sync(FULL, live)) break;
     if (live) {
       uint32_t rec, add;
       if (walk_one(sm, lb, rec, add, flag)) live = false;
@@ -448,6 +452,7 @@ __device__ __forceinline__ uint32_t walk_sub(WarpSmem &sm, uint32_t *qbuf, uint3
       }
     }
   }
+  if (!active) return old_end;
   n_flag = n | flag;
   n_out = out;
   return lb.pos();
@@ -457,24 +462,26 @@ __device__ __forceinline__ uint32_t walk_sub(WarpSmem &sm, uint32_t *qbuf, uint3
 // walk starts -- from there on the two walks are the same walk.  The new records wait in `tq` (the first walk's
 // are still needed) and are then put in front of the old tail; `base` is the row the merged list starts at.
 // In: n_flag / n_out / end of the first walk.  Out: those of the merged list.
-__device__ __forceinline__ uint32_t walk_again(WarpSmem &sm, uint32_t *qbuf, uint32_t start, uint32_t limit, uint32_t lane, uint32_t mask,
+__device__ __forceinline__ uint32_t walk_again(WarpSmem &sm, uint32_t *qbuf, uint32_t start, uint32_t limit, uint32_t lane, bool active,
                                                uint32_t old_end, uint32_t &n_flag, uint32_t &n_out, uint32_t &base) {
   LaneBits lb;
   lb.init(sm.zw, start);
   const uint32_t n_old = n_flag & 0xffu;
-  uint32_t m = 0, flag = 0, out = 0, j = 0;
+  uint32_t m = 0, flag = 0, out = 0, j = 0, state = 0, plen = 0;
   uint32_t *q = qbuf + lane;
   uint32_t *tq = reinterpret_cast<uint32_t *>(sm.l1) + lane;
   const uint16_t *bp = sm.bpos + lane;
-  bool live = true, met = false, direct = false;   // direct: too many new records to keep aside, the old walk is given up
+  bool live = active, met = false, direct = false;   // direct: too many new records to keep aside, the old walk is given up
   for (;;) {
-    const uint32_t at = lb.pos();
-    live = live && at < limit && m < SUBCAP && out < LANE_OUT;
-    if (live && !direct) {
-      while (j < n_old && bp[j * 32u] < at) j++;
-      if (j < n_old && bp[j * 32u] == at && m <= j + QHEAD) { met = true; live = false; }
+    {
+      const uint32_t at = lb.pos();
+      live = live && at < limit && m < SUBCAP && out < LANE_OUT;
+      if (live && !direct) {
+        while (j < n_old && bp[j * 32u] < at) j++;
+        if (j < n_old && bp[j * 32u] == at && m <= j + QHEAD) { met = true; live = false; }
+      }
     }
-    if (!__any_sync(mask, live)) break;
+    if (!__any_sync(FULL, live)) break;
     if (live) {
       uint32_t rec, add;
       if (walk_one(sm, lb, rec, add, flag)) live = false;
@@ -489,6 +496,7 @@ __device__ __forceinline__ uint32_t walk_again(WarpSmem &sm, uint32_t *qbuf, uin
       }
     }
   }
+  if (!active) return old_end;
   if (met) {
     uint32_t before = 0;   // bytes of the old records that the new ones replace
     for (uint32_t k = 0; k < j; k++) before += rec_bytes(q[(QHEAD + k) * 32u]);
@@ -496,6 +504,7 @@ __device__ __forceinline__ uint32_t walk_again(WarpSmem &sm, uint32_t *qbuf, uin
     for (uint32_t t = 0; t < m; t++) q[(base + t) * 32u] = tq[t * 32u];
     n_flag = (m + n_old - j) | (n_flag & ~0xffu);
     n_out = out + n_out - before;
+    if (n_out > 512u) n_flag |= F_WIDE;   // the applier packs a match's offset inside its lane into 9 bits
     return old_end;
   }
   if (!direct) for (uint32_t t = 0; t < m; t++) q[(QHEAD + t) * 32u] = tq[t * 32u];
@@ -591,9 +600,10 @@ __device__ void walker(WarpSmem &sm, const InfStream &st, Link lk, const uint32_
         bool walk = true;
         uint32_t bad = 0;   // lanes whose start is not their left neighbour's end
         for (uint32_t round = 0;; round++) {
-          if (walk) {
-            if (round == 1u) end = walk_again(sm, qbuf, start, limit, lane, bad, end, n_flag, n_out, base);
-            else { end = walk_sub(sm, qbuf, start, limit, lane, round ? bad : FULL, round == 0u, n_flag, n_out); base = QHEAD; }
+          if (round == 1u) end = walk_again(sm, qbuf, start, limit, lane, walk, end, n_flag, n_out, base);
+          else {
+            end = walk_sub(sm, qbuf, start, limit, lane, walk, round == 0u, end, n_flag, n_out);
+            if (walk) base = QHEAD;
           }
           __syncwarp();
           const uint32_t left_end = __shfl_up_sync(FULL, end, 1);
@@ -609,6 +619,8 @@ __device__ void walker(WarpSmem &sm, const InfStream &st, Link lk, const uint32_
         const uint32_t stops = __ballot_sync(FULL, (n_flag & (F_EOB | F_ERR)) != 0u);
         uint32_t n_lanes = bad ? (uint32_t)__ffs(bad) - 1u : 32u;
         if (stops) n_lanes = min(n_lanes, (uint32_t)__ffs(stops));
+        const uint32_t wide = __ballot_sync(FULL, (n_flag & F_WIDE) != 0u);   // never lane 0: it does not walk twice
+        if (wide) n_lanes = min(n_lanes, (uint32_t)__ffs(wide) - 1u);
         uint32_t off = n_out;   // inclusive scan of the lanes' output sizes
 #pragma unroll
         for (uint32_t d = 1; d < 32u; d <<= 1) {
@@ -682,48 +694,65 @@ __device__ void applier(WarpSmem &sm, const InfStream &st, InfResult *results, L
       wpos = pos % WIN;
       continue;
     }
-    // ---- a window: every lane of the chain writes its own records' bytes; copies from bytes that another lane is
-    // producing in this same window are left as pointers and resolved afterwards by pointer jumping ----
+    // ---- a window ----
+    // Every byte of the window starts out final.  Pass L: every lane of the chain writes the literals of its own
+    // records and moves its matches, with the offset they write to, to the head of its own record column.  Pass M:
+    // the matches, in order.  (One pass over the records would run the match code in every step in which any lane
+    // has a match -- nearly all of them -- although a lane has only a handful.)  A match that copies from bytes
+    // another lane is producing in this same window leaves 16-bit pointers, resolved afterwards by pointer jumping.
     const uint32_t n_lanes = m.n_lanes, total = m.total;
     const uint32_t off = m.off[lane], ni = m.n[lane], base = m.base[lane];
-    const uint32_t *q = sm.q[lk.slot];
+    uint32_t *col = sm.q[lk.slot] + base * 32u + lane;
     bool far = false;
+    uint32_t plo = OUTCAP, phi = 0;   // the pointers this lane leaves lie in [plo, phi)
+    for (uint32_t t = lane; t * 8u < total; t += 32u) reinterpret_cast<uint4 *>(src)[t] = make_uint4(~0u, ~0u, ~0u, ~0u);
+    __syncwarp();
     {
-      uint32_t o = off;
+      uint32_t o = off, nm = 0;
       const uint32_t my_n = lane < n_lanes && !err ? ni : 0u;
       for (uint32_t k = 0; __any_sync(FULL, k < my_n); k++) {   // a vote per record: the lanes stay in step
         if (k >= my_n) continue;
-        const uint32_t r = q[(base + k) * 32u + lane];
+        const uint32_t r = col[k * 32u];
         if ((int)r >= 0) {
           const uint32_t cnt = r >> 24;
-          for (uint32_t t = 0; t < cnt; t++, o++) {
-            uint32_t sl = wpos + o;
-            sl = sl >= WIN ? sl - WIN : sl;
-            win[sl] = (uint8_t)(r >> (8u * t));
-            src[o] = (uint16_t)RES;
-          }
+          uint32_t sl = wpos + o;
+          sl = sl >= WIN ? sl - WIN : sl;
+          win[sl] = (uint8_t)r;
+          if (cnt > 1u) { sl = sl + 1u == WIN ? 0u : sl + 1u; win[sl] = (uint8_t)(r >> 8); }
+          if (cnt > 2u) { sl = sl + 1u == WIN ? 0u : sl + 1u; win[sl] = (uint8_t)(r >> 16); }
+          o += cnt;
         } else {
-          const uint32_t len = ((r >> 15) & 0xffu) + 3u, dist = (r & 0x7fffu) + 1u;
-          far = far || dist > pos + o;
-          for (uint32_t t = 0; t < len; t++, o++) {
-            uint32_t sl = wpos + o;
-            sl = sl >= WIN ? sl - WIN : sl;
-            const int rel = (int)o - (int)dist;
-            if (rel < 0) {                       // history: final
-              int hs = (int)wpos + rel;
-              hs = hs < 0 ? hs + (int)WIN : hs;
-              win[sl] = win[hs];
-              src[o] = (uint16_t)RES;
-            } else if ((uint32_t)rel >= off) {   // a byte this lane made itself: final, or a pointer to follow
-              const uint32_t p = src[rel];
-              if (p == RES) {
-                uint32_t ps = wpos + (uint32_t)rel;
-                ps = ps >= WIN ? ps - WIN : ps;
-                win[sl] = win[ps];
-              }
-              src[o] = (uint16_t)p;
+          const uint32_t orel = o - off;   // < 512: records start below LANE_OUT, merged lists are kept below by the walker
+          far = far || orel >= 512u;
+          col[nm * 32u] = (r << 9) | (orel & 511u);   // (length - 3) << 24 | (distance - 1) << 9 | offset; slot nm <= k is consumed
+          nm++;
+          o += ((r >> 15) & 0xffu) + 3u;
+        }
+      }
+      for (uint32_t i = 0; __any_sync(FULL, i < nm); i++) {
+        if (i >= nm) continue;
+        const uint32_t c = col[i * 32u];
+        const uint32_t len = (c >> 24) + 3u, dist = ((c >> 9) & 0x7fffu) + 1u;
+        o = off + (c & 511u);
+        far = far || dist > pos + o;
+        for (uint32_t t = 0; t < len; t++, o++) {
+          uint32_t sl = wpos + o;
+          sl = sl >= WIN ? sl - WIN : sl;
+          const int rel = (int)o - (int)dist;
+          if (rel < 0) {                       // history: final
+            int hs = (int)wpos + rel;
+            hs = hs < 0 ? hs + (int)WIN : hs;
+            win[sl] = win[hs];
+          } else {
+            // a byte this lane made itself is final or a pointer to follow; another lane's byte is pointed to
+            const uint32_t p = (uint32_t)rel >= off ? src[rel] : (uint32_t)rel;
+            if (p == RES) {
+              uint32_t ps = wpos + (uint32_t)rel;
+              ps = ps >= WIN ? ps - WIN : ps;
+              win[sl] = win[ps];
             } else {
-              src[o] = (uint16_t)rel;            // another lane's byte
+              src[o] = (uint16_t)p;
+              plo = min(plo, o); phi = max(phi, o + 1u);
             }
           }
         }
@@ -734,11 +763,13 @@ __device__ void applier(WarpSmem &sm, const InfStream &st, InfResult *results, L
     lk.slot ^= 1u;
     if (err) continue;
     if (__any_sync(FULL, far)) { err = INF_E_FAR; continue; }
-    for (;;) {   // pointer jumping: a pointer always leads to a lower lane's region, so at most 5 rounds
+    plo = __reduce_min_sync(FULL, plo) & ~31u;
+    phi = __reduce_max_sync(FULL, phi);
+    while (plo < phi) {   // pointer jumping: a pointer always leads to a lower lane's region, so at most 5 rounds
       bool open = false;
-      for (uint32_t x0 = 0; x0 < total; x0 += 32u) {
+      for (uint32_t x0 = plo; x0 < phi; x0 += 32u) {
         const uint32_t x = x0 + lane;
-        const uint32_t p = x < total ? src[x] : RES;
+        const uint32_t p = x < phi ? src[x] : RES;
         const uint32_t pp = p == RES ? 0u : p;
         const uint32_t qn = src[pp];
         uint32_t ps = wpos + pp;
