@@ -57,6 +57,38 @@ def test_strategies_match_zlib(ctx, strategy):
         _check(ctx, raw, _z(raw, 6, strategy))
 
 
+def _lz_mix(rng, n, alphabet, p_copy, max_dist, max_len):
+    """Bytes made like an LZ77 stream: literals from a small alphabet, copies at random distances and lengths (short
+    distances give overlapping copies and chains of copies of copies inside one window of the device's walk)."""
+    out = bytearray(rng.integers(0, alphabet, 64, dtype=np.uint8).tobytes())
+    while len(out) < n:
+        if rng.random() < p_copy:
+            d = int(rng.integers(1, min(max_dist, len(out)) + 1))
+            ln = int(rng.integers(3, max_len + 1))
+            for _ in range(ln):
+                out.append(out[-d])
+        else:
+            out += rng.integers(0, alphabet, int(rng.integers(1, 12)), dtype=np.uint8).tobytes()
+    return bytes(out[:n])
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_random_lz_mixes_match_zlib(ctx, seed):
+    """Copies of copies at every distance scale: inside a lane's own bytes, across lanes of one window, across
+    windows, near the 32 KiB limit; matches from 3 to 258 bytes; alphabets from 2 symbols (three literals per table
+    entry) to 256 (long codes)."""
+    rng = np.random.default_rng(1000 + seed)
+    alphabet = [2, 4, 16, 64, 256, 256][seed % 6]
+    p_copy = [0.05, 0.3, 0.6, 0.9][seed % 4]
+    max_dist = [4, 40, 300, 3000, 32768, 32768][(seed // 2) % 6]
+    max_len = [4, 12, 64, 258][(seed // 3) % 4]
+    raw = _lz_mix(rng, 60_000 + 7919 * seed, alphabet, p_copy, max_dist, max_len)
+    for level in (1, 6, 9):
+        _check(ctx, raw, _z(raw, level))
+    _check(ctx, raw, _z(raw, 6, zlib.Z_FIXED))
+    _check(ctx, raw, _z(raw, 9, zlib.Z_DEFAULT_STRATEGY, 15, 1))   # memLevel 1: a new block every ~128 symbols
+
+
 def test_small_window_and_memlevel(ctx):
     rng = np.random.default_rng(5)
     raw = _corpus(rng)["filtered_rows"]
