@@ -458,16 +458,23 @@ __device__ __forceinline__ uint32_t walk_sub(WarpSmem &sm, uint32_t *qbuf, uint3
   return lb.pos();
 }
 
-// The window's second walk: from the true start, and only until it steps on a bit where a record of the first
-// walk starts -- from there on the two walks are the same walk.  The new records wait in `tq` (the first walk's
-// are still needed) and are then put in front of the old tail; `base` is the row the merged list starts at.
-// In: n_flag / n_out / end of the first walk.  Out: those of the merged list.
+// What a lane keeps of its FIRST walk of the window, for the walks that follow: the records in rows QHEAD.. of its
+// column with the bit each starts at (bpos), of which those from `valid` on are still in place.
+struct FirstWalk {
+  uint32_t n, out, flag, end;   // records, bytes they make, F_EOB / F_ERR | status, bit after the last symbol
+  uint32_t valid;               // records below this index have been overwritten by an earlier merge
+};
+
+// A later walk of the window: from the lane's corrected start, and only until it steps on a bit where a (still
+// intact) record of the first walk starts -- from there on the two walks are the same walk.  The new records wait in
+// `tq` and are then put in front of the old tail; `base` is the row the merged list starts at.  A walk that never
+// meets the first one replaces it (and the lane has no first walk to meet any more).
 __device__ __forceinline__ uint32_t walk_again(WarpSmem &sm, uint32_t *qbuf, uint32_t start, uint32_t limit, uint32_t lane, bool active,
-                                               uint32_t old_end, uint32_t &n_flag, uint32_t &n_out, uint32_t &base) {
+                                               FirstWalk &fw, uint32_t old_end, uint32_t &n_flag, uint32_t &n_out, uint32_t &base) {
   LaneBits lb;
   lb.init(sm.zw, start);
-  const uint32_t n_old = n_flag & 0xffu;
-  uint32_t m = 0, flag = 0, out = 0, j = 0, state = 0, plen = 0;
+  const uint32_t n_old = fw.n;
+  uint32_t m = 0, flag = 0, out = 0, j = fw.valid;
   uint32_t *q = qbuf + lane;
   uint32_t *tq = reinterpret_cast<uint32_t *>(sm.l1) + lane;
   const uint16_t *bp = sm.bpos + lane;
@@ -498,16 +505,26 @@ __device__ __forceinline__ uint32_t walk_again(WarpSmem &sm, uint32_t *qbuf, uin
   }
   if (!active) return old_end;
   if (met) {
-    uint32_t before = 0;   // bytes of the old records that the new ones replace
-    for (uint32_t k = 0; k < j; k++) before += rec_bytes(q[(QHEAD + k) * 32u]);
+    uint32_t tail;   // bytes of the first walk's records from j on
+    if (fw.valid == 0u) {
+      uint32_t before = 0;
+      for (uint32_t k = 0; k < j; k++) before += rec_bytes(q[(QHEAD + k) * 32u]);
+      tail = fw.out - before;
+    } else {
+      tail = 0;
+      for (uint32_t k = j; k < n_old; k++) tail += rec_bytes(q[(QHEAD + k) * 32u]);
+    }
     base = QHEAD + j - m;
     for (uint32_t t = 0; t < m; t++) q[(base + t) * 32u] = tq[t * 32u];
-    n_flag = (m + n_old - j) | (n_flag & ~0xffu);
-    n_out = out + n_out - before;
+    fw.valid = j;
+    n_flag = (m + n_old - j) | fw.flag;
+    n_out = out + tail;
     if (n_out > 512u) n_flag |= F_WIDE;   // the applier packs a match's offset inside its lane into 9 bits
-    return old_end;
+    return fw.end;
   }
   if (!direct) for (uint32_t t = 0; t < m; t++) q[(QHEAD + t) * 32u] = tq[t * 32u];
+  fw.n = 0u;   // the first walk's records are gone
+  fw.valid = 0u;
   base = QHEAD;
   n_flag = m | flag;
   n_out = out;
@@ -598,12 +615,14 @@ __device__ void walker(WarpSmem &sm, const InfStream &st, Link lk, const uint32_
         const uint32_t limit = rel0 + (lane + 1u) * SUBBITS;
         uint32_t end = 0, n_flag = 0, n_out = 0, base = QHEAD;
         bool walk = true;
+        FirstWalk fw;
         uint32_t bad = 0;   // lanes whose start is not their left neighbour's end
         for (uint32_t round = 0;; round++) {
-          if (round == 1u) end = walk_again(sm, qbuf, start, limit, lane, walk, end, n_flag, n_out, base);
-          else {
-            end = walk_sub(sm, qbuf, start, limit, lane, walk, round == 0u, end, n_flag, n_out);
-            if (walk) base = QHEAD;
+          if (round == 0u) {
+            end = walk_sub(sm, qbuf, start, limit, lane, true, true, end, n_flag, n_out);
+            fw.n = n_flag & 0xffu; fw.out = n_out; fw.flag = n_flag & ~0xffu; fw.end = end; fw.valid = 0u;
+          } else {
+            end = walk_again(sm, qbuf, start, limit, lane, walk, fw, end, n_flag, n_out, base);
           }
           __syncwarp();
           const uint32_t left_end = __shfl_up_sync(FULL, end, 1);
