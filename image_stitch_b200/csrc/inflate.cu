@@ -382,42 +382,37 @@ struct LaneBits {
 // One symbol at the lane's position: 0 = a record (literals or a match) and the bytes it makes, 1 = end of block,
 // 2 = invalid code (`flag` says which).
 __device__ __forceinline__ uint32_t walk_one(WarpSmem &sm, LaneBits &lb, uint32_t &rec, uint32_t &add, uint32_t &flag) {
+  // Written without branches on the symbol's kind: the lanes of a warp step together, and with 32 of them some lane
+  // has a match in nearly every step, so the distance lookup is paid anyway -- selects are cheaper than the two
+  // diverging paths.  Only codes longer than the table index branch off.
   lb.refill();
-  const uint32_t e = sm.lt[lb.peek(TB)];
-  uint32_t kind = (e >> 4) & 3u;
-  uint32_t lbase = e >> 16, lext = (e >> 8) & 15u;
-  rec = ((e >> 6) & 3u) << 24 | (e >> 8);
-  add = (e >> 6) & 3u;
-  if (kind == 3u) {
+  uint32_t e = sm.lt[lb.peek(TB)];
+  if ((e & E_LONG) == E_LONG) {
     uint32_t L = 0;
     const int sy = canon_walk((uint32_t)lb.bb, sm.lc, sm.lsym, L);
     if (sy < 0 || sy >= 286) { flag = F_ERR | ((uint32_t)INF_E_LITLEN_CODE << 16); return 2u; }
-    lb.drop(L);
-    if (sy < 256) { kind = 0u; rec = (1u << 24) | (uint32_t)sy; add = 1u; }
-    else if (sy == 256) kind = 2u;
-    else { kind = 1u; lbase = c_lbase[sy - 257]; lext = c_lext[sy - 257]; }
-  } else {
-    lb.drop(e & 15u);
+    if (sy < 256) e = L | (1u << 6) | ((uint32_t)sy << 8);
+    else if (sy == 256) e = L | 0x20u;
+    else e = L | 0x10u | ((uint32_t)c_lext[sy - 257] << 8) | ((uint32_t)c_lbase[sy - 257] << 16);
   }
+  lb.drop(e & 15u);
+  const uint32_t kind = (e >> 4) & 3u;
+  const bool is_len = kind == 1u;
+  const uint32_t len = (e >> 16) + lb.take(is_len ? (e >> 8) & 15u : 0u);
+  lb.refill();
+  uint32_t d = sm.dt[lb.peek(TD)];
+  if (is_len && (d & E_LONG) == E_LONG) {
+    uint32_t L = 0;
+    const int sy = canon_walk((uint32_t)lb.bb, sm.dc, sm.dsym, L);
+    if (sy < 0 || sy >= 30) { flag = F_ERR | ((uint32_t)INF_E_DIST_CODE << 16); return 2u; }
+    d = L | ((uint32_t)c_dext[sy] << 8) | ((uint32_t)c_dbase[sy] << 16);
+  }
+  lb.drop(is_len ? d & 15u : 0u);
+  const uint32_t dist = (d >> 16) + lb.take(is_len ? (d >> 8) & 15u : 0u);
+  const uint32_t cnt = (e >> 6) & 3u;
+  rec = is_len ? (1u << 31) | ((len - 3u) << 15) | (dist - 1u) : (cnt << 24) | (e >> 8);
+  add = is_len ? len : cnt;
   if (kind == 2u) { flag = F_EOB; return 1u; }
-  if (kind == 1u) {
-    const uint32_t len = lbase + lb.take(lext);
-    lb.refill();
-    const uint32_t d = sm.dt[lb.peek(TD)];
-    uint32_t dbase = d >> 16, dext = (d >> 8) & 15u;
-    if ((d & 0x30u) == 0x30u) {
-      uint32_t L = 0;
-      const int sy = canon_walk((uint32_t)lb.bb, sm.dc, sm.dsym, L);
-      if (sy < 0 || sy >= 30) { flag = F_ERR | ((uint32_t)INF_E_DIST_CODE << 16); return 2u; }
-      lb.drop(L);
-      dbase = c_dbase[sy]; dext = c_dext[sy];
-    } else {
-      lb.drop(d & 15u);
-    }
-    const uint32_t dist = dbase + lb.take(dext);
-    rec = (1u << 31) | ((len - 3u) << 15) | (dist - 1u);
-    add = len;
-  }
   return 0u;
 }
 
