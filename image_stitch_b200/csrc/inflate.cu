@@ -381,13 +381,14 @@ struct LaneBits {
 // (distance - 1).  Returns the bit after the last symbol taken; `n_flag` = records | F_EOB | F_ERR | status << 16.
 // One symbol at the lane's position: 0 = a record (literals or a match) and the bytes it makes, 1 = end of block,
 // 2 = invalid code (`flag` says which).
-__device__ __forceinline__ uint32_t walk_one(WarpSmem &sm, LaneBits &lb, uint32_t &rec, uint32_t &add, uint32_t &flag) {
+__device__ __forceinline__ uint32_t walk_one(WarpSmem &sm, LaneBits &lb, const bool live, uint32_t &rec, uint32_t &add, uint32_t &flag) {
   // Written without branches on the symbol's kind: the lanes of a warp step together, and with 32 of them some lane
   // has a match in nearly every step, so the distance lookup is paid anyway -- selects are cheaper than the two
-  // diverging paths.  Only codes longer than the table index branch off.
+  // diverging paths.  Only codes longer than the table index branch off.  A lane that is not `live` goes through
+  // the same instructions and takes no bits.
   lb.refill();
   uint32_t e = sm.lt[lb.peek(TB)];
-  if ((e & E_LONG) == E_LONG) {
+  if (live && (e & E_LONG) == E_LONG) {
     uint32_t L = 0;
     const int sy = canon_walk((uint32_t)lb.bb, sm.lc, sm.lsym, L);
     if (sy < 0 || sy >= 286) { flag = F_ERR | ((uint32_t)INF_E_LITLEN_CODE << 16); return 2u; }
@@ -395,9 +396,9 @@ __device__ __forceinline__ uint32_t walk_one(WarpSmem &sm, LaneBits &lb, uint32_
     else if (sy == 256) e = L | 0x20u;
     else e = L | 0x10u | ((uint32_t)c_lext[sy - 257] << 8) | ((uint32_t)c_lbase[sy - 257] << 16);
   }
-  lb.drop(e & 15u);
+  lb.drop(live ? e & 15u : 0u);
   const uint32_t kind = (e >> 4) & 3u;
-  const bool is_len = kind == 1u;
+  const bool is_len = live && kind == 1u;
   const uint32_t len = (e >> 16) + lb.take(is_len ? (e >> 8) & 15u : 0u);
   lb.refill();
   uint32_t d = sm.dt[lb.peek(TD)];
@@ -412,7 +413,7 @@ __device__ __forceinline__ uint32_t walk_one(WarpSmem &sm, LaneBits &lb, uint32_
   const uint32_t cnt = (e >> 6) & 3u;
   rec = is_len ? (1u << 31) | ((len - 3u) << 15) | (dist - 1u) : (cnt << 24) | (e >> 8);
   add = is_len ? len : cnt;
-  if (kind == 2u) { flag = F_EOB; return 1u; }
+  if (live && kind == 2u) { flag = F_EOB; return 1u; }
   return 0u;
 }
 
@@ -436,16 +437,14 @@ __device__ __forceinline__ uint32_t walk_sub(WarpSmem &sm, uint32_t *qbuf, uint3
     const uint32_t at = lb.pos();
     live = live && at < limit && n < SUBCAP && out < LANE_OUT;
     if (!__any_sync(FULL, live)) break;
+    uint32_t rec, add;
+    live = walk_one(sm, lb, live, rec, add, flag) == 0u && live;
     if (live) {
-      uint32_t rec, add;
-      if (walk_one(sm, lb, rec, add, flag)) live = false;
-      else {
-        q[n * 32u] = rec;
-        if (first) bp[n * 32u] = (uint16_t)at;
-        n++;
-        out += add;
-      }
+      q[n * 32u] = rec;
+      if (first) bp[n * 32u] = (uint16_t)at;
     }
+    n += live ? 1u : 0u;
+    out += live ? add : 0u;
   }
   if (!active) return old_end;
   n_flag = n | flag;
@@ -479,24 +478,25 @@ __device__ __forceinline__ uint32_t walk_again(WarpSmem &sm, uint32_t *qbuf, uin
       const uint32_t at = lb.pos();
       live = live && at < limit && m < SUBCAP && out < LANE_OUT;
       if (live && !direct) {
-        while (j < n_old && bp[j * 32u] < at) j++;
+        // both walks move forward: j follows by at most two records a step (once the walks have met they advance a
+        // record a step each, so a j that lags catches up and the meeting is seen a little later at worst)
+        j += j < n_old && bp[j * 32u] < at ? 1u : 0u;
+        j += j < n_old && bp[j * 32u] < at ? 1u : 0u;
         if (j < n_old && bp[j * 32u] == at && m <= j + QHEAD) { met = true; live = false; }
       }
     }
     if (!__any_sync(FULL, live)) break;
+    uint32_t rec, add;
+    live = walk_one(sm, lb, live, rec, add, flag) == 0u && live;
     if (live) {
-      uint32_t rec, add;
-      if (walk_one(sm, lb, rec, add, flag)) live = false;
-      else {
-        if (!direct && m == TQCAP) {
-          for (uint32_t t = 0; t < m; t++) q[(QHEAD + t) * 32u] = tq[t * 32u];
-          direct = true;
-        }
-        if (direct) q[(QHEAD + m) * 32u] = rec; else tq[m * 32u] = rec;
-        m++;
-        out += add;
+      if (!direct && m == TQCAP) {
+        for (uint32_t t = 0; t < m; t++) q[(QHEAD + t) * 32u] = tq[t * 32u];
+        direct = true;
       }
+      *(direct ? q + (QHEAD + m) * 32u : tq + m * 32u) = rec;
     }
+    m += live ? 1u : 0u;
+    out += live ? add : 0u;
   }
   if (!active) return old_end;
   if (met) {
