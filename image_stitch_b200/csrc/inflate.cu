@@ -354,26 +354,14 @@ __device__ int read_dynamic_header(WarpSmem &sm, Bits &br, uint32_t lane, uint32
 
 
 // ---- lane-private bit reader over the staged window ---------------------------------------------------------
+// A lane's place in the staged code words: just the bit position.  Every symbol fetches the 64 bits from there
+// (three shared-memory words, two funnel shifts) -- fewer dependent instructions per symbol than keeping a shifting
+// bit buffer up to date, and the dependent chain is what a single walking warp is bound by.
 struct LaneBits {
   const uint32_t *zw;
-  uint32_t wi;
-  unsigned long long bb;
-  uint32_t bc;
-  __device__ __forceinline__ void init(const uint32_t *z, uint32_t rel_bit) {
-    zw = z;
-    wi = rel_bit >> 5;
-    const uint32_t sh = rel_bit & 31u;
-    bb = (unsigned long long)(zw[wi] >> sh);
-    bc = 32u - sh;
-    wi++;
-  }
-  __device__ __forceinline__ void refill() {
-    if (bc <= 32u) { bb |= (unsigned long long)zw[wi] << bc; bc += 32u; wi++; }
-  }
-  __device__ __forceinline__ uint32_t peek(uint32_t n) const { return (uint32_t)bb & ((1u << n) - 1u); }
-  __device__ __forceinline__ void drop(uint32_t n) { bb >>= n; bc -= n; }
-  __device__ __forceinline__ uint32_t take(uint32_t n) { const uint32_t v = peek(n); drop(n); return v; }
-  __device__ __forceinline__ uint32_t pos() const { return wi * 32u - bc; }
+  uint32_t p;
+  __device__ __forceinline__ void init(const uint32_t *z, uint32_t rel_bit) { zw = z; p = rel_bit; }
+  __device__ __forceinline__ uint32_t pos() const { return p; }
 };
 
 // One lane walks the codes from window bit `start` until it reaches `limit`, the end of the block, an invalid code,
@@ -386,33 +374,37 @@ __device__ __forceinline__ uint32_t walk_one(WarpSmem &sm, LaneBits &lb, const b
   // has a match in nearly every step, so the distance lookup is paid anyway -- selects are cheaper than the two
   // diverging paths.  Only codes longer than the table index branch off.  A lane that is not `live` goes through
   // the same instructions and takes no bits.
-  lb.refill();
-  uint32_t e = sm.lt[lb.peek(TB)];
+  const uint32_t wi = lb.p >> 5, sh = lb.p & 31u;
+  const uint32_t w0 = lb.zw[wi], w1 = lb.zw[wi + 1u], w2 = lb.zw[wi + 2u];
+  const uint32_t lo = __funnelshift_r(w0, w1, sh), hi = __funnelshift_r(w1, w2, sh);   // the 64 bits from p on
+  uint32_t e = sm.lt[lo & ((1u << TB) - 1u)];
   if (live && (e & E_LONG) == E_LONG) {
     uint32_t L = 0;
-    const int sy = canon_walk((uint32_t)lb.bb, sm.lc, sm.lsym, L);
+    const int sy = canon_walk(lo, sm.lc, sm.lsym, L);
     if (sy < 0 || sy >= 286) { flag = F_ERR | ((uint32_t)INF_E_LITLEN_CODE << 16); return 2u; }
     if (sy < 256) e = L | (1u << 6) | ((uint32_t)sy << 8);
     else if (sy == 256) e = L | 0x20u;
     else e = L | 0x10u | ((uint32_t)c_lext[sy - 257] << 8) | ((uint32_t)c_lbase[sy - 257] << 16);
   }
-  lb.drop(live ? e & 15u : 0u);
-  const uint32_t kind = (e >> 4) & 3u;
+  const uint32_t nb = e & 15u, kind = (e >> 4) & 3u;
   const bool is_len = live && kind == 1u;
-  const uint32_t len = (e >> 16) + lb.take(is_len ? (e >> 8) & 15u : 0u);
-  lb.refill();
-  uint32_t d = sm.dt[lb.peek(TD)];
+  const uint32_t lext = is_len ? (e >> 8) & 15u : 0u;
+  const uint32_t len = (e >> 16) + ((lo >> nb) & ((1u << lext) - 1u));    // code <= 15 bits, extra <= 5
+  const uint32_t k = nb + lext;
+  const uint32_t dbits = __funnelshift_r(lo, hi, k);                      // the 32 bits after the length
+  uint32_t d = sm.dt[dbits & ((1u << TD) - 1u)];
   if (is_len && (d & E_LONG) == E_LONG) {
     uint32_t L = 0;
-    const int sy = canon_walk((uint32_t)lb.bb, sm.dc, sm.dsym, L);
+    const int sy = canon_walk(dbits, sm.dc, sm.dsym, L);
     if (sy < 0 || sy >= 30) { flag = F_ERR | ((uint32_t)INF_E_DIST_CODE << 16); return 2u; }
     d = L | ((uint32_t)c_dext[sy] << 8) | ((uint32_t)c_dbase[sy] << 16);
   }
-  lb.drop(is_len ? d & 15u : 0u);
-  const uint32_t dist = (d >> 16) + lb.take(is_len ? (d >> 8) & 15u : 0u);
+  const uint32_t dn = d & 15u, dext = (d >> 8) & 15u;
+  const uint32_t dist = (d >> 16) + ((dbits >> dn) & ((1u << dext) - 1u));  // code <= 15 bits, extra <= 13
   const uint32_t cnt = (e >> 6) & 3u;
   rec = is_len ? (1u << 31) | ((len - 3u) << 15) | (dist - 1u) : (cnt << 24) | (e >> 8);
   add = is_len ? len : cnt;
+  lb.p += live ? (is_len ? k + dn + dext : nb) : 0u;
   if (live && kind == 2u) { flag = F_EOB; return 1u; }
   return 0u;
 }
