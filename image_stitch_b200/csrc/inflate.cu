@@ -741,27 +741,25 @@ __device__ void applier(WarpSmem &sm, const InfStream &st, InfResult *results, L
         const uint32_t len = (c >> 24) + 3u, dist = ((c >> 9) & 0x7fffu) + 1u;
         o = off + (c & 511u);
         far = far || dist > pos + o;
-        for (uint32_t t = 0; t < len; t++, o++) {
-          uint32_t sl = wpos + o;
-          sl = sl >= WIN ? sl - WIN : sl;
-          const int rel = (int)o - (int)dist;
-          if (rel < 0) {                       // history: final
-            int hs = (int)wpos + rel;
-            hs = hs < 0 ? hs + (int)WIN : hs;
-            win[sl] = win[hs];
-          } else {
-            // a byte this lane made itself is final or a pointer to follow; another lane's byte is pointed to
-            const uint32_t p = (uint32_t)rel >= off ? src[rel] : (uint32_t)rel;
-            if (p == RES) {
-              uint32_t ps = wpos + (uint32_t)rel;
-              ps = ps >= WIN ? ps - WIN : ps;
-              win[sl] = win[ps];
-            } else {
-              src[o] = (uint16_t)p;
-              plo = min(plo, o); phi = max(phi, o + 1u);
-            }
-          }
+        // The byte copied lies `dist` back in the ring whether it is history or was made in this window.  History is
+        // final; a byte this lane made itself is final or a pointer to follow; another lane's byte is pointed to.
+        const uint32_t o0 = o;
+        int rel = (int)o - (int)dist;
+        uint32_t sl = wpos + o;
+        sl = sl >= WIN ? sl - WIN : sl;
+        int sp = (int)wpos + rel;
+        sp = sp < 0 ? sp + (int)WIN : sp >= (int)WIN ? sp - (int)WIN : sp;
+        bool left = false;   // pointers left behind
+        for (uint32_t t = 0; t < len; t++) {
+          uint32_t p = rel < 0 ? RES : (uint32_t)rel;
+          if (rel >= (int)off) p = src[rel];
+          if (p == RES) win[sl] = win[sp];
+          else { src[o] = (uint16_t)p; left = true; }
+          o++; rel++;
+          sl = sl + 1u == WIN ? 0u : sl + 1u;
+          sp = sp + 1 == (int)WIN ? 0 : sp + 1;
         }
+        if (left) { plo = min(plo, o0); phi = max(phi, o); }
       }
     }
     __syncwarp();
@@ -776,6 +774,7 @@ __device__ void applier(WarpSmem &sm, const InfStream &st, InfResult *results, L
       for (uint32_t x0 = plo; x0 < phi; x0 += 32u) {
         const uint32_t x = x0 + lane;
         const uint32_t p = x < phi ? src[x] : RES;
+        if (!__any_sync(FULL, p != RES)) continue;   // most of the window holds no pointer
         const uint32_t pp = p == RES ? 0u : p;
         const uint32_t qn = src[pp];
         uint32_t ps = wpos + pp;
