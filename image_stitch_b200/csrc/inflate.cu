@@ -770,7 +770,7 @@ __device__ void applier(WarpSmem &sm, const InfStream &st, InfResult *results, L
     plo = __reduce_min_sync(FULL, plo) & ~31u;
     phi = __reduce_max_sync(FULL, phi);
     while (plo < phi) {   // pointer jumping: a pointer always leads to a lower lane's region, so at most 5 rounds
-      bool open = false;
+      uint32_t olo = OUTCAP, ohi = 0;   // the pointers still open after this round
       for (uint32_t x0 = plo; x0 < phi; x0 += 32u) {
         const uint32_t x = x0 + lane;
         const uint32_t p = x < phi ? src[x] : RES;
@@ -789,12 +789,13 @@ __device__ void applier(WarpSmem &sm, const InfStream &st, InfResult *results, L
             src[x] = (uint16_t)RES;
           } else {
             src[x] = (uint16_t)qn;
-            open = true;
+            olo = min(olo, x); ohi = x + 1u;
           }
         }
         __syncwarp();
       }
-      if (!__any_sync(FULL, open)) break;
+      plo = __reduce_min_sync(FULL, olo) & ~31u;
+      phi = __reduce_max_sync(FULL, ohi);
     }
     pos += total; wpos += total;
     if (wpos >= WIN) wpos -= WIN;
