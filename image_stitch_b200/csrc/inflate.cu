@@ -595,6 +595,10 @@ __device__ void walker(WarpSmem &sm, const InfStream &st, Link lk, const uint32_
         const uint32_t rel0 = (uint32_t)(bitpos & 127ull);
         for (uint32_t t = lane; t < ZWORDS / 4u; t += 32u)
           reinterpret_cast<uint4 *>(sm.zw)[t] = __ldg(reinterpret_cast<const uint4 *>(st.src) + min(a0 + t, last_gran));
+        {  // the window after this one most likely starts 32 subsequences on: have its words in L1 by then
+          const uint32_t g = min(a0 + 32u * SUBBITS / 128u + 8u * lane, last_gran);
+          if (lane < ZWORDS / 32u + 1u) asm volatile("prefetch.global.L1 [%0];" ::"l"(reinterpret_cast<const uint4 *>(st.src) + g));
+        }
         Msg &m = acquire();    // also orders the staging stores before the walks
         uint32_t *qbuf = sm.q[lk.slot];
         __syncwarp();
