@@ -721,23 +721,21 @@ __device__ void applier(WarpSmem &sm, const InfStream &st, InfResult *results, L
       uint32_t o = off, nm = 0;
       const uint32_t my_n = lane < n_lanes && !err ? ni : 0u;
       for (uint32_t k = 0; __any_sync(FULL, k < my_n); k++) {   // a vote per record: the lanes stay in step
-        if (k >= my_n) continue;
-        const uint32_t r = col[k * 32u];
-        if ((int)r >= 0) {
-          const uint32_t cnt = r >> 24;
-          uint32_t sl = wpos + o;
-          sl = sl >= WIN ? sl - WIN : sl;
-          win[sl] = (uint8_t)r;
-          if (cnt > 1u) { sl = sl + 1u == WIN ? 0u : sl + 1u; win[sl] = (uint8_t)(r >> 8); }
-          if (cnt > 2u) { sl = sl + 1u == WIN ? 0u : sl + 1u; win[sl] = (uint8_t)(r >> 16); }
-          o += cnt;
-        } else {
-          const uint32_t orel = o - off;   // < 512: records start below LANE_OUT, merged lists are kept below by the walker
-          far = far || orel >= 512u;
-          col[nm * 32u] = (r << 9) | (orel & 511u);   // (length - 3) << 24 | (distance - 1) << 9 | offset; slot nm <= k is consumed
-          nm++;
-          o += ((r >> 15) & 0xffu) + 3u;
-        }
+        const bool on = k < my_n;            // selects and predicated stores, no diverging paths
+        const uint32_t r = on ? col[k * 32u] : 0u;
+        const bool lit = on && (int)r >= 0, mat = on && (int)r < 0;
+        const uint32_t cnt = r >> 24;
+        uint32_t s0 = wpos + o;
+        s0 = s0 >= WIN ? s0 - WIN : s0;
+        const uint32_t s1 = s0 + 1u == WIN ? 0u : s0 + 1u, s2 = s1 + 1u == WIN ? 0u : s1 + 1u;
+        if (lit) win[s0] = (uint8_t)r;
+        if (lit && cnt > 1u) win[s1] = (uint8_t)(r >> 8);
+        if (lit && cnt > 2u) win[s2] = (uint8_t)(r >> 16);
+        const uint32_t orel = o - off;   // < 512: records start below LANE_OUT, merged lists are kept below by the walker
+        far = far || (mat && orel >= 512u);
+        if (mat) col[nm * 32u] = (r << 9) | (orel & 511u);   // (length - 3) << 24 | (distance - 1) << 9 | offset; slot nm <= k is consumed
+        nm += mat ? 1u : 0u;
+        o += lit ? cnt : mat ? ((r >> 15) & 0xffu) + 3u : 0u;
       }
       for (uint32_t i = 0; __any_sync(FULL, i < nm); i++) {
         if (i >= nm) continue;
@@ -775,25 +773,36 @@ __device__ void applier(WarpSmem &sm, const InfStream &st, InfResult *results, L
     phi = __reduce_max_sync(FULL, phi);
     while (plo < phi) {   // pointer jumping: a pointer always leads to a lower lane's region, so at most 5 rounds
       uint32_t olo = OUTCAP, ohi = 0;   // the pointers still open after this round
-      for (uint32_t x0 = plo; x0 < phi; x0 += 32u) {
-        const uint32_t x = x0 + lane;
-        const uint32_t p = x < phi ? src[x] : RES;
-        if (!__any_sync(FULL, p != RES)) continue;   // most of the window holds no pointer
-        const uint32_t pp = p == RES ? 0u : p;
-        const uint32_t qn = src[pp];
-        uint32_t ps = wpos + pp;
-        ps = ps >= WIN ? ps - WIN : ps;
-        const uint8_t v = win[ps];
+      for (uint32_t x0 = plo; x0 < phi; x0 += 64u) {   // two groups of 32 a step: their loads overlap
+        uint32_t x[2], p[2], qn[2];
+        uint8_t v[2];
+#pragma unroll
+        for (int g = 0; g < 2; g++) {
+          x[g] = x0 + 32u * g + lane;
+          p[g] = x[g] < phi ? src[x[g]] : RES;
+        }
+        if (!__any_sync(FULL, p[0] != RES || p[1] != RES)) continue;   // no pointer here
+#pragma unroll
+        for (int g = 0; g < 2; g++) {
+          const uint32_t pp = p[g] == RES ? 0u : p[g];
+          qn[g] = src[pp];
+          uint32_t ps = wpos + pp;
+          ps = ps >= WIN ? ps - WIN : ps;
+          v[g] = win[ps];
+        }
         __syncwarp();
-        if (p != RES) {
-          if (qn == RES) {
-            uint32_t sl = wpos + x;
-            sl = sl >= WIN ? sl - WIN : sl;
-            win[sl] = v;
-            src[x] = (uint16_t)RES;
-          } else {
-            src[x] = (uint16_t)qn;
-            olo = min(olo, x); ohi = x + 1u;
+#pragma unroll
+        for (int g = 0; g < 2; g++) {
+          if (p[g] != RES) {
+            if (qn[g] == RES) {
+              uint32_t sl = wpos + x[g];
+              sl = sl >= WIN ? sl - WIN : sl;
+              win[sl] = v[g];
+              src[x[g]] = (uint16_t)RES;
+            } else {
+              src[x[g]] = (uint16_t)qn[g];
+              olo = min(olo, x[g]); ohi = max(ohi, x[g] + 1u);
+            }
           }
         }
         __syncwarp();
