@@ -44,7 +44,6 @@ constexpr uint32_t SUBBITS = 768u;
 constexpr uint32_t SUBCAP = 96u;
 constexpr uint32_t QHEAD = 16u;          // record rows in front of a lane's list: a re-walked prefix may be longer than the one it replaces
 constexpr uint32_t QROWS = SUBCAP + QHEAD;
-constexpr uint32_t TQCAP = 32u;          // records of a re-walk kept aside until it meets the old walk
 constexpr uint32_t LANE_OUT = 256u;      // a lane stops once its records produce this many bytes (a match may add 257 more)
 constexpr uint32_t RES = 0xffffu;        // src[]: this byte of the window is final
 constexpr uint32_t ZWORDS = 32u * SUBBITS / 32u + 16u;   // staged code words: the window, its 127-bit lead-in, a symbol of overrun, one word of look-ahead
@@ -105,7 +104,6 @@ struct WarpSmem {
   __align__(16) uint8_t win[WIN];
 };
 static_assert(sizeof(WarpSmem) % 16 == 0, "rings must stay 16-byte aligned");
-static_assert(TQCAP * 32u * 4u <= sizeof(uint16_t) * (1u << TB), "the re-walk records borrow the single-symbol table, which only the table build uses");
 
 // ring -> global, whole 512-byte units below `upto` (all of it with `all`); granules may run past `upto` into
 // the 16 bytes of slack every destination buffer has
@@ -452,8 +450,8 @@ struct FirstWalk {
 };
 
 // A later walk of the window: from the lane's corrected start, and only until it steps on a bit where a (still
-// intact) record of the first walk starts -- from there on the two walks are the same walk.  The new records wait in
-// `tq` and are then put in front of the old tail; `base` is the row the merged list starts at.  A walk that never
+// intact) record of the first walk starts -- from there on the two walks are the same walk.  The new records are
+// then moved in front of the old tail; `base` is the row the merged list starts at.  A walk that never
 // meets the first one replaces it (and the lane has no first walk to meet any more).
 __device__ __forceinline__ uint32_t walk_again(WarpSmem &sm, uint32_t *qbuf, uint32_t start, uint32_t limit, uint32_t lane, bool active,
                                                FirstWalk &fw, uint32_t old_end, uint32_t &n_flag, uint32_t &n_out, uint32_t &base) {
@@ -462,57 +460,46 @@ __device__ __forceinline__ uint32_t walk_again(WarpSmem &sm, uint32_t *qbuf, uin
   const uint32_t n_old = fw.n;
   uint32_t m = 0, flag = 0, out = 0, j = fw.valid;
   uint32_t *q = qbuf + lane;
-  uint32_t *tq = reinterpret_cast<uint32_t *>(sm.l1) + lane;
   const uint16_t *bp = sm.bpos + lane;
-  bool live = active, met = false, direct = false;   // direct: too many new records to keep aside, the old walk is given up
+  // The new records go to rows 0.. of the lane's column, the first walk's live in rows QHEAD..: the first walk's
+  // record j is still needed as long as the new walk has not passed it, so row m may be written while m < QHEAD + j.
+  // A new walk that makes so many more records than the old one gives up meeting it (`alone`).
+  bool live = active, met = false, alone = false;
   for (;;) {
     {
       const uint32_t at = lb.pos();
       live = live && at < limit && m < SUBCAP && out < LANE_OUT;
-      if (live && !direct) {
+      if (live && !alone) {
         // both walks move forward: j follows by at most two records a step (once the walks have met they advance a
         // record a step each, so a j that lags catches up and the meeting is seen a little later at worst)
         j += j < n_old && bp[j * 32u] < at ? 1u : 0u;
         j += j < n_old && bp[j * 32u] < at ? 1u : 0u;
-        if (j < n_old && bp[j * 32u] == at && m <= j + QHEAD) { met = true; live = false; }
+        if (j < n_old && bp[j * 32u] == at) { met = true; live = false; }
+        alone = m >= QHEAD + j;
       }
     }
     if (!__any_sync(FULL, live)) break;
     uint32_t rec, add;
     live = walk_one(sm, lb, live, rec, add, flag) == 0u && live;
-    if (live) {
-      if (!direct && m == TQCAP) {
-        for (uint32_t t = 0; t < m; t++) q[(QHEAD + t) * 32u] = tq[t * 32u];
-        direct = true;
-      }
-      *(direct ? q + (QHEAD + m) * 32u : tq + m * 32u) = rec;
-    }
+    if (live) q[m * 32u] = rec;
     m += live ? 1u : 0u;
     out += live ? add : 0u;
   }
   if (!active) return old_end;
   if (met) {
-    uint32_t tail;   // bytes of the first walk's records from j on
-    if (fw.valid == 0u) {
-      uint32_t before = 0;
-      for (uint32_t k = 0; k < j; k++) before += rec_bytes(q[(QHEAD + k) * 32u]);
-      tail = fw.out - before;
-    } else {
-      tail = 0;
-      for (uint32_t k = j; k < n_old; k++) tail += rec_bytes(q[(QHEAD + k) * 32u]);
-    }
-    base = QHEAD + j - m;
-    for (uint32_t t = 0; t < m; t++) q[(base + t) * 32u] = tq[t * 32u];
+    uint32_t tail = 0;   // bytes of the first walk's records from j on (those rows are untouched)
+    for (uint32_t k = j; k < n_old; k++) tail += rec_bytes(q[(QHEAD + k) * 32u]);
+    base = QHEAD + j - m;   // m <= QHEAD + j: every row was written under that condition
+    if (base) for (uint32_t t = m; t-- > 0u;) q[(base + t) * 32u] = q[t * 32u];
     fw.valid = j;
     n_flag = (m + n_old - j) | fw.flag;
     n_out = out + tail;
     if (n_out > 512u) n_flag |= F_WIDE;   // the applier packs a match's offset inside its lane into 9 bits
     return fw.end;
   }
-  if (!direct) for (uint32_t t = 0; t < m; t++) q[(QHEAD + t) * 32u] = tq[t * 32u];
   fw.n = 0u;   // the first walk's records are gone
   fw.valid = 0u;
-  base = QHEAD;
+  base = 0u;
   n_flag = m | flag;
   n_out = out;
   return lb.pos();
