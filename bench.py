@@ -225,8 +225,9 @@ def run_reference(args, rank: int, world: int):
         "impl": "reference", "metric": "composited output MPix/s", "value": value, "unit": "MPix/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": total / args.steps * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": dict(WORKLOAD_CONFIG, note="CPU restatement of the TypeScript reference (oracle/, C, -O2) on the host "
-                                             "cores; no JS runtime on this box; each step is a bounded sample"),
+        "config": dict(WORKLOAD_CONFIG),   # identical to the GPU arm's config (the driver compares them)
+        "note": "CPU restatement of the TypeScript reference (oracle/, C, -O2) on the host cores; no JS runtime on this "
+                "box; each step is a bounded sample",
         "cpu_baseline": {"value": value, "unit": "MPix/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "MPix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
