@@ -22,7 +22,7 @@ EXPORTS = [
     "stitch_last_error", "stitch_job_create", "stitch_job_destroy", "stitch_job_add_tile",
     "stitch_job_add_tile_device", "stitch_job_add_tile_palette", "stitch_job_decode", "stitch_job_invalidate", "stitch_job_run_band", "stitch_job_band_device",
     "stitch_job_status", "stitch_decode_image", "stitch_filter_rows", "stitch_jpeg_header",
-    "stitch_job_inflate", "stitch_inflate",
+    "stitch_job_inflate", "stitch_inflate", "stitch_filter_rows_noalloc",
 ]
 
 
@@ -109,6 +109,7 @@ def load() -> C.CDLL:
     lib.stitch_jpeg_header.argtypes = [C.c_uint32, C.c_uint32, C.c_uint32, vp, sz, C.POINTER(sz)]
     lib.stitch_job_inflate.argtypes = [vp, C.c_int, C.POINTER(Timings)]
     lib.stitch_inflate.argtypes = [vp, vp, sz, vp, sz, C.POINTER(sz)]
+    lib.stitch_filter_rows_noalloc.argtypes = [vp, vp, sz, vp, C.c_uint32, sz, C.c_uint32, vp, sz]
     for name in EXPORTS:  # every symbol include/stitch_b200.h declares must be exported
         getattr(lib, name)
     _lib = lib
@@ -213,6 +214,13 @@ class Context:
         rc = self.lib.stitch_filter_rows(self.handle, _addr(rows), _addr(prev), n_rows, row_bytes, bpp, _addr(out), out.size)
         self.check(rc)
         return out
+
+
+    def filter_rows_noalloc(self, d_rows: int, in_pitch: int, d_prev_row: int, n_rows: int, row_bytes: int, bpp: int,
+                            d_out: int, out_pitch: int) -> None:
+        """Kernel (c) with DEVICE pointers and the library's static scratch: allocates nothing (operators' addition)."""
+        self.check(self.lib.stitch_filter_rows_noalloc(self.handle, C.c_void_p(d_rows), in_pitch, C.c_void_p(d_prev_row or None),
+                                                       n_rows, row_bytes, bpp, C.c_void_p(d_out), out_pitch))
 
 
 class Job:

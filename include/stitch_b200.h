@@ -232,6 +232,20 @@ int stitch_inflate(stitch_ctx *ctx, const uint8_t *zdata, size_t zlen, uint8_t *
 int stitch_filter_rows(stitch_ctx *ctx, const uint8_t *rows, const uint8_t *prev_row, uint32_t n_rows,
                        size_t row_bytes, uint32_t bpp, uint8_t *out, size_t cap);
 
+/* Kernel (c) again, for callers that cannot allocate device memory (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Same result as stitch_filter_rows, but d_rows / d_prev_row / d_out are DEVICE pointers the caller
+ * owns (row r of the input at d_rows + r*in_pitch; of the output at d_out + r*out_pitch: filter-type byte, then
+ * row_bytes filtered bytes; d_prev_row may be NULL), and the kernels' scratch -- five 64-bit cost sums per row --
+ * is a static 1 MiB __device__ array inside the library, so the call performs no cudaMalloc/cudaFree/pool
+ * allocation.  Limits: n_rows <= STITCH_NOALLOC_MAX_ROWS and row_bytes <= STITCH_NOALLOC_MAX_ROW_BYTES per call
+ * (STITCH_E_CAPACITY beyond).  All calls on one GPU share the array: the call clears what it uses, runs on the
+ * context's stream and returns after synchronising it; calls that overlap on the same GPU race. */
+#define STITCH_NOALLOC_MAX_ROWS 16384u
+#define STITCH_NOALLOC_MAX_ROW_BYTES (1u << 25)
+int stitch_filter_rows_noalloc(stitch_ctx *ctx, const uint8_t *d_rows, size_t in_pitch, const uint8_t *d_prev_row,
+                               uint32_t n_rows, size_t row_bytes, uint32_t bpp, uint8_t *d_out, size_t out_pitch);
+
 /* ---- JPEG container helpers (host side of src/jpeg-encoder.ts) ------------ */
 
 /* Writes SOI + JFIF APP0 + DQT + SOF0 + DHT + SOS for the encoder definition in
