@@ -240,6 +240,7 @@ extern "C" void stitch_job_destroy(stitch_job *job) {
   dev_free(ctx, job->d_canvas); dev_free(ctx, job->d_out); dev_free(ctx, job->d_sync); dev_free(ctx, job->d_plans); dev_free(ctx, job->d_ctab);
   dev_free(ctx, job->d_defl); dev_free(ctx, job->d_defl_b); dev_free(ctx, job->d_defl_scratch);
   dev_free(ctx, job->d_inf); dev_free(ctx, job->d_infres);
+  dev_free(ctx, job->d_maps); dev_free(ctx, job->d_ivs); dev_free(ctx, job->d_col_start); dev_free(ctx, job->d_lists); dev_free(ctx, job->d_bgrow);
   dev_free(ctx, job->d_pack[0]); dev_free(ctx, job->d_pack[1]);
   for (auto &e : job->ev_pack) if (e) cudaEventDestroy(e);
   if (job->h_infres) cudaFreeHost(job->h_infres);
@@ -875,6 +876,14 @@ static int finalize_job(stitch_job *job) {
   if ((rc = stitch_upload_small(ctx, job->d_tiles, dt.data(), dt.size() * sizeof(DevTile)))) return rc;
   if ((rc = stitch_upload_small(ctx, job->d_bin_start, start.data(), start.size() * sizeof(uint32_t)))) return rc;
   if ((rc = stitch_upload_small(ctx, job->d_bin_tiles, list.data(), list.size() * sizeof(uint32_t)))) return rc;
+  if (jd.out_kind == STITCH_OUT_PNG_FILTERED || jd.out_kind == STITCH_OUT_PNG_DEFLATE) {
+    std::vector<uint32_t> src_words(order.size()), src_rows(order.size());
+    for (size_t k = 0; k < order.size(); k++) {
+      src_words[k] = job->tiles[order[k]].d.width * (job->bpp / 4);
+      src_rows[k] = job->tiles[order[k]].d.height;
+    }
+    if ((rc = stitch_build_strip_plan(job, dt, src_words, src_rows))) return rc;
+  }
   // the host vectors are pageable: the async copies above have already staged them
   CK(cudaStreamSynchronize(ctx->stream));
   job->finalized = true;
@@ -957,6 +966,22 @@ static int render_rows(stitch_job *job, uint32_t a, uint32_t b, uint8_t *d_rows,
     bg_words(jd, fp.bg_lo, fp.bg_hi);
     fp.rowsum = reinterpret_cast<unsigned long long *>(job->d_sync); fp.ticket = job->d_sync + (size_t)n_rows * 16;
     fp.out = d_rows; fp.out_pitch = job->out_pitch; fp.lead = (uint32_t)job->out_lead;
+    static const bool use_strip = getenv("STITCH_STRIP") != nullptr;   // opt-in until its parity run is green
+    if (job->strip_ok && use_strip) {
+      StripParams sp{};
+      sp.tiles = job->d_tiles; sp.maps = job->d_maps; sp.ivs = reinterpret_cast<const StripIv *>(job->d_ivs);
+      sp.col_start = reinterpret_cast<const uint32_t *>(job->d_col_start); sp.lists = reinterpret_cast<const uint32_t *>(job->d_lists);
+      sp.bg_row = reinterpret_cast<const uint8_t *>(job->d_bgrow);
+      sp.canvas_w = jd.canvas_w; sp.y_begin = a; sp.y_end = b; sp.ncol = job->strip_ncol; sp.alpha_blend = jd.alpha_blend;
+      bg_words(jd, sp.bg_lo, sp.bg_hi);
+      sp.rowsum = reinterpret_cast<unsigned long long *>(job->d_sync);
+      sp.out = d_rows; sp.out_pitch = job->out_pitch; sp.lead = (uint32_t)job->out_lead;
+      static const int q_env = getenv("STITCH_STRIP_Q") ? atoi(getenv("STITCH_STRIP_Q")) : 0;   // tuning
+      const cudaError_t se = launch_strip(sp, jd.out_bit_depth == 16, q_env, ctx->device, ctx->sm_count, ctx->stream);
+      if (se == cudaSuccess) { *launches += 1; return STITCH_OK; }
+      if (se != cudaErrorInvalidConfiguration) CK(se);
+      cudaGetLastError();
+    }
     if ((rc = ensure_buffer(ctx, &job->d_plans, &job->plans_bytes, fused_plan_bytes(fp.n_bands * fp.nseg)))) return rc;
     fp.plans = job->d_plans;
     // How many of the band's bins need the generic compositor?  Few: one fused pass straight from the tiles.

@@ -79,6 +79,10 @@ struct stitch_job {
   std::vector<uint32_t> inf_pending;
   uint32_t *d_sync = nullptr; size_t sync_words = 0;   // fused kernel: rowsum | band_done | ticket
   bool force_two_pass = false;
+  // strip.cu: TMA tensor maps (one per tile), per-box-column interval plan, background row
+  void *d_maps = nullptr, *d_ivs = nullptr, *d_col_start = nullptr, *d_lists = nullptr, *d_bgrow = nullptr;
+  uint32_t strip_ncol = 0;
+  bool strip_ok = false;
   // band buffers
   uint8_t *d_plans = nullptr; size_t plans_bytes = 0;  // fused kernel: per-unit plan records
   uint8_t *d_defl = nullptr; size_t defl_bytes = 0;    // deflate: compressed band / chunk (two buffers, used in turn)
@@ -132,5 +136,8 @@ int stitch_deflate_band(stitch_job *job, const uint8_t *d_rows, uint32_t n_rows,
 size_t stitch_deflate_bound(size_t raw_bytes);
 uint32_t stitch_crc_raw_concat(uint32_t ra, uint32_t rb, uint64_t len_b);
 uint32_t stitch_crc_finish(uint32_t raw, uint64_t n);
+// strip_plan.cu: interval plan + tensor maps for strip.cu; dt = the tiles back to front as uploaded to d_tiles
+int stitch_build_strip_plan(stitch_job *job, const std::vector<stitch::DevTile> &dt, const std::vector<uint32_t> &src_words,
+                            const std::vector<uint32_t> &src_rows);
 int stitch_jpeg_encode_band(stitch_job *job, uint32_t y0, uint32_t y1, const uint8_t *canvas, size_t canvas_pitch,
                             size_t *out_bytes, uint32_t *launches);

@@ -64,6 +64,45 @@ uint32_t fused_words_per_seg();
 uint32_t fused_unit_rows();
 uint32_t fused_unit_words();
 
+// Row-pipelined composite + filter-select (strip.cu), kernels (b)+(c) of north_star with TMA-staged row bands.
+// A canvas row is cut into BOX columns of 256 words (1 KiB).  For every box column the host lists the y-intervals
+// over which the set of tiles touching the column does not change (StripIv) and what a box row of that interval
+// is made of:
+//   SK_DIRECT  one native-format tile covers the box and overwrites what is below: one 2-D TMA box load
+//   SK_BG      no tile: a bulk copy of the background row
+//   SK_COMP    anything else: normalise + alpha-over by the CTA's warps over the interval's tile list
+struct StripIv {
+  uint32_t y_end;             // exclusive canvas row where the interval ends
+  uint32_t kind;              // StripKind
+  uint32_t tile;              // SK_DIRECT: index into tiles / maps
+  int32_t cw, cy;             // SK_DIRECT: the box's first word is word cw of source row (y + cy)
+  uint32_t list_off, n_list;  // SK_COMP: tiles touching the column in this interval, back to front (into lists)
+  uint32_t pad;
+};
+enum StripKind : uint32_t { SK_BG = 0, SK_DIRECT = 1, SK_COMP = 2 };
+struct StripParams {
+  const DevTile *tiles;
+  const void *maps;           // one 128-byte CUtensorMap per tile: 32-bit words, box 256 x 1
+  const StripIv *ivs;
+  const uint32_t *col_start;  // [ncol + 1]: intervals of box column c are ivs[col_start[c] .. col_start[c + 1])
+  const uint32_t *lists;
+  const uint8_t *bg_row;      // 1 KiB of background pixels, 16-byte aligned
+  uint32_t canvas_w;
+  uint32_t y_begin, y_end;    // canvas rows to produce
+  uint32_t nsx, nry, ncol;    // column strips x row ranges (one CTA each); box columns of the canvas
+  uint32_t rows_per_range;
+  uint32_t alpha_blend;
+  uint32_t bg_lo, bg_hi;
+  unsigned long long *rowsum; // [(y_end - y_begin)][8], zeroed: low half = cost sum, high half = warps arrived
+  uint8_t *out;               // row r: filter byte at out + r*out_pitch + lead
+  size_t out_pitch;
+  uint32_t lead;
+};
+uint32_t strip_box_words();
+// q = 0: the launcher picks the quads per thread.  cudaErrorInvalidConfiguration: the row is too wide for one
+// resident grid (the caller falls back to composite-then-filter).
+cudaError_t launch_strip(StripParams p, bool out16, int q, int device, int sm_count, cudaStream_t st);
+
 cudaError_t launch_unfilter(const UnfStream *d_streams, uint32_t n_streams, DevStatus *d_status, cudaStream_t st);
 // d_seam: mailbox of unfilter_wave_seam_bytes() per chain, zeroed once; epoch: a value never used with it before (> 0).
 size_t unfilter_wave_seam_bytes(uint32_t rows, uint32_t row_bytes);
