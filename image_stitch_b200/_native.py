@@ -23,6 +23,7 @@ EXPORTS = [
     "stitch_job_add_tile_device", "stitch_job_add_tile_palette", "stitch_job_decode", "stitch_job_invalidate", "stitch_job_run_band", "stitch_job_band_device",
     "stitch_job_status", "stitch_decode_image", "stitch_filter_rows", "stitch_jpeg_header",
     "stitch_job_inflate", "stitch_inflate", "stitch_filter_rows_noalloc",
+    "stitch_selftest_blend", "stitch_selftest_blend8_samples",
 ]
 
 
@@ -109,6 +110,8 @@ def load() -> C.CDLL:
     lib.stitch_jpeg_header.argtypes = [C.c_uint32, C.c_uint32, C.c_uint32, vp, sz, C.POINTER(sz)]
     lib.stitch_job_inflate.argtypes = [vp, C.c_int, C.POINTER(Timings)]
     lib.stitch_inflate.argtypes = [vp, vp, sz, vp, sz, C.POINTER(sz)]
+    lib.stitch_selftest_blend.argtypes = [vp, C.c_uint32, C.c_uint64, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(C.c_uint32)]
+    lib.stitch_selftest_blend8_samples.argtypes = [vp, C.c_uint32, C.c_uint32, vp]
     lib.stitch_filter_rows_noalloc.argtypes = [vp, vp, sz, vp, C.c_uint32, sz, C.c_uint32, vp, sz]
     for name in EXPORTS:  # every symbol include/stitch_b200.h declares must be exported
         getattr(lib, name)
@@ -215,6 +218,18 @@ class Context:
         self.check(rc)
         return out
 
+
+    def selftest_blend(self, mode: int, amount: int = 0):
+        """(checked, mismatches, first offending tuple) of the device-side blend proof (stitch_selftest_blend)."""
+        chk, bad, first = C.c_uint64(), C.c_uint64(), (C.c_uint32 * 4)()
+        self.check(self.lib.stitch_selftest_blend(self.handle, mode, amount, C.byref(chk), C.byref(bad), first))
+        return chk.value, bad.value, tuple(first)
+
+    def selftest_blend8_samples(self, n: int, seed: int = 1):
+        import numpy as np
+        out = np.empty((n, 3), dtype=np.uint32)
+        self.check(self.lib.stitch_selftest_blend8_samples(self.handle, n, seed, _addr(out)))
+        return out
 
     def filter_rows_noalloc(self, d_rows: int, in_pitch: int, d_prev_row: int, n_rows: int, row_bytes: int, bpp: int,
                             d_out: int, out_pitch: int) -> None:

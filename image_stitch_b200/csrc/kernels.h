@@ -70,16 +70,20 @@ uint32_t fused_unit_words();
 // is made of:
 //   SK_DIRECT  one native-format tile covers the box and overwrites what is below: one 2-D TMA box load
 //   SK_BG      no tile: a bulk copy of the background row
+//   SK_SHIFT   the same, but the box starts at a source byte that is not a multiple of 16 (a tiled TMA load faults
+//              on such a start coordinate -- measured on B200), or the tile's pitch / width rule TMA out: the
+//              producer warp copies the box with 4-byte cp.async completing on the same mbarrier
 //   SK_COMP    anything else: normalise + alpha-over by the CTA's warps over the interval's tile list
 struct StripIv {
   uint32_t y_end;             // exclusive canvas row where the interval ends
   uint32_t kind;              // StripKind
-  uint32_t tile;              // SK_DIRECT: index into tiles / maps
-  int32_t cw, cy;             // SK_DIRECT: the box's first word is word cw of source row (y + cy)
+  uint32_t tile;              // SK_DIRECT, SK_SHIFT: index into tiles / maps
+  int32_t cw, cy;             // SK_DIRECT, SK_SHIFT: the box's first word is word cw of source row (y + cy)
   uint32_t list_off, n_list;  // SK_COMP: tiles touching the column in this interval, back to front (into lists)
+                              // SK_SHIFT: list_off = words of the box that exist in the source row (<= 256)
   uint32_t pad;
 };
-enum StripKind : uint32_t { SK_BG = 0, SK_DIRECT = 1, SK_COMP = 2 };
+enum StripKind : uint32_t { SK_BG = 0, SK_DIRECT = 1, SK_COMP = 2, SK_SHIFT = 3 };
 struct StripParams {
   const DevTile *tiles;
   const void *maps;           // one 128-byte CUtensorMap per tile: 32-bit words, box 256 x 1

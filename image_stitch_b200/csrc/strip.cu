@@ -65,6 +65,16 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
 __device__ __forceinline__ void mbar_arrive_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {   // no arrival: only more bytes to wait for
+  asm volatile("mbarrier.expect_tx.relaxed.cta.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+// arrives once all cp.async copies this thread has issued so far have landed (at once if there are none)
+__device__ __forceinline__ void mbar_arrive_after_cp_async(uint32_t bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void cp_async4(uint32_t dst, const void *src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+}
 __device__ __forceinline__ bool mbar_try(uint32_t bar, uint32_t parity) {
   uint32_t ok;
   asm volatile(
@@ -151,12 +161,18 @@ struct IvCursor {
   uint32_t idx, end_idx;   // current interval, one past the column's last
   uint32_t y_end, kind, tile, list_off, n_list;
   int32_t cw, cy;
+  const uint8_t *pix;      // SK_DIRECT, SK_SHIFT: the tile's rows
+  uint32_t pitch;
 };
 __device__ __forceinline__ void iv_load(const StripParams &p, IvCursor &c) {
   const uint4 *q = reinterpret_cast<const uint4 *>(p.ivs + c.idx);
   const uint4 a = __ldg(q), b = __ldg(q + 1);
   c.y_end = a.x; c.kind = a.y; c.tile = a.z; c.cw = (int32_t)a.w;
   c.cy = (int32_t)b.x; c.list_off = b.y; c.n_list = b.z;
+  if (c.kind == SK_DIRECT || c.kind == SK_SHIFT) {
+    const DevTile *t = p.tiles + c.tile;
+    c.pix = t->pix; c.pitch = t->pitch;
+  }
 }
 __device__ __forceinline__ void iv_open(const StripParams &p, IvCursor &c, uint32_t col) {
   c.idx = __ldg(p.col_start + col); c.end_idx = __ldg(p.col_start + col + 1);
@@ -171,9 +187,8 @@ template <int BPW>
 __device__ __forceinline__ uint2 halo_pixel(const StripParams &p, IvCursor &hc, const uint32_t ch, const int y) {
   if (y < 0) return make_uint2(0u, 0u);
   iv_seek(p, hc, y);
-  if (hc.kind == SK_DIRECT) {
-    const DevTile &t = p.tiles[hc.tile];
-    const uint32_t *src = reinterpret_cast<const uint32_t *>(t.pix + (size_t)(y + hc.cy) * t.pitch) + (hc.cw + SK_BOX - BPW);
+  if (hc.kind == SK_DIRECT || hc.kind == SK_SHIFT) {
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(hc.pix + (size_t)(y + hc.cy) * hc.pitch) + (hc.cw + SK_BOX - BPW);
     return BPW == 2 ? make_uint2(__ldg(src), __ldg(src + 1)) : make_uint2(0u, __ldg(src));
   }
   if (hc.kind == SK_COMP) {
@@ -209,24 +224,37 @@ __device__ __forceinline__ void strip_producer(const StripParams &p, const uint3
       if (BPW == 2) sts32(row - 8u, halo.x);
       sts32(row - 4u, halo.y);
     }
-    bool comp = false;
+    bool comp = false, shift = false;
+    const uint8_t *sp = nullptr;   // SK_SHIFT: first byte of the box in the source row
     if (has_col && y >= 0) {
       iv_seek(p, bc, y);
       const uint32_t dst = row + lane * (SK_BOX * 4);
       if (bc.kind == SK_DIRECT) {
-        mbar_arrive_tx(full, SK_BOX * 4);
+        mbar_expect_tx(full, SK_BOX * 4);
         tma_box_2d(dst, reinterpret_cast<const uint8_t *>(p.maps) + (size_t)bc.tile * 128u, bc.cw, y + bc.cy, full);
       } else if (bc.kind == SK_BG) {
-        mbar_arrive_tx(full, SK_BOX * 4);
+        mbar_expect_tx(full, SK_BOX * 4);
         bulk_copy(dst, p.bg_row, SK_BOX * 4, full);
+      } else if (bc.kind == SK_SHIFT) {
+        shift = true;
+        sp = bc.pix + (size_t)(y + bc.cy) * bc.pitch + (size_t)bc.cw * 4u;
       } else {
         comp = true;
         sts32(plan + lane * 4u, bc.idx);
-        mbar_arrive(full);
       }
-    } else {
-      mbar_arrive(full);   // no box, or the zero row above the canvas (the consumers write it)
     }
+    // boxes whose source is not 16-byte aligned: the whole warp copies them word by word, asynchronously
+    for (uint32_t m = __ballot_sync(0xffffffffu, shift); m; m &= m - 1u) {
+      const int b = __ffs((int)m) - 1;
+      const unsigned long long spb = __shfl_sync(0xffffffffu, (unsigned long long)sp, b);
+      const uint32_t nw = __shfl_sync(0xffffffffu, bc.list_off, b);
+      const uint32_t dstb = row + (uint32_t)b * (SK_BOX * 4) + lane * 4u;
+      const uint8_t *srcb = reinterpret_cast<const uint8_t *>(spb) + lane * 4u;
+#pragma unroll
+      for (int i = 0; i < SK_BOX / 32; i++)
+        if (lane + 32u * i < nw) cp_async4(dstb + 128u * i, srcb + 128 * i);
+    }
+    mbar_arrive_after_cp_async(full);   // every lane arrives once per row: when its copies, if any, have landed
     const uint32_t mask = __ballot_sync(0xffffffffu, comp);
     if (lane == 0u) sts32(plan + 32u * 4u, mask);
     mbar_arrive(bar_plan + 8u * slot);
@@ -340,6 +368,7 @@ __device__ __forceinline__ void strip_emit(const StripParams &p, const uint32_t 
     const int qw = xw0 + 4 * (int)j;
     uint4 o;
     if (ft == 4u) {
+      __syncwarp();   // tcgen05.ld is .sync.aligned: the partial stores of the quad before may have split the warp
       o = tmem_ld4(taddr + 4u * i);
     } else {
       o = lds128(a);

@@ -112,11 +112,16 @@ int stitch_build_strip_plan(stitch_job *job, const std::vector<DevTile> &dt, con
       } else {
         const DevTile &t = dt[cur.back()];
         const bool top_covers = (!jd.alpha_blend || t.opaque) && t.x0 <= X0 && t.x1 >= X1;
-        if (top_covers && direct_ok[cur.back()]) {
-          iv.kind = SK_DIRECT;
+        if (top_covers && t.fmt == native) {
           iv.tile = cur.back();
           iv.cw = (int32_t)((X0 - t.x0 + t.sx0) * (int32_t)bpw);
           iv.cy = t.sy0 - t.y0;
+          // a tiled TMA load needs its start coordinate on a 16-byte boundary (it faults otherwise: measured)
+          if (direct_ok[cur.back()] && (iv.cw & 3) == 0) iv.kind = SK_DIRECT;
+          else {
+            iv.kind = SK_SHIFT;
+            iv.list_off = std::min<uint32_t>(strip_box_words(), src_words[cur.back()] - (uint32_t)iv.cw);
+          }
         } else {
           iv.kind = SK_COMP;
           iv.n_list = (uint32_t)cur.size();
@@ -128,7 +133,7 @@ int stitch_build_strip_plan(stitch_job *job, const std::vector<DevTile> &dt, con
         StripIv &pv = ivs.back();
         if (pv.kind == iv.kind) {
           if (iv.kind == SK_BG) merged = true;
-          else if (iv.kind == SK_DIRECT) merged = pv.tile == iv.tile;
+          else if (iv.kind == SK_DIRECT || iv.kind == SK_SHIFT) merged = pv.tile == iv.tile;
           else merged = prev_list_len == cur.size() && std::equal(cur.begin(), cur.end(), lists.begin() + (ptrdiff_t)prev_list_begin);
         }
         if (merged) pv.y_end = iv.y_end;

@@ -246,6 +246,16 @@ int stitch_filter_rows(stitch_ctx *ctx, const uint8_t *rows, const uint8_t *prev
 int stitch_filter_rows_noalloc(stitch_ctx *ctx, const uint8_t *d_rows, size_t in_pitch, const uint8_t *d_prev_row,
                                uint32_t n_rows, size_t row_bytes, uint32_t bpp, uint8_t *d_out, size_t out_pitch);
 
+/* Device-side proof of the alpha-over fast path (compositeScanline, src/pixel-ops.ts:646-736): compares the
+ * library's blend with the literal f64 arithmetic of the reference ON THE DEVICE.  mode 0: 8-bit, every
+ * (srcAlpha, dstAlpha, src, dst) -- 2^32 tuples (amount = k > 1 checks every k-th (sA, dA, s) only); mode 1:
+ * 16-bit, `amount` hashed samples (0 = 2^28) including every alpha within 8 of the thresholds 65529 and 7.
+ * first[4] receives one offending tuple.  stitch_selftest_blend8_samples returns n triples {dst, src, blended}
+ * of hashed pixels for a host-side check against another implementation.  Test infrastructure. */
+int stitch_selftest_blend(stitch_ctx *ctx, uint32_t mode, uint64_t amount, uint64_t *checked, uint64_t *mismatches,
+                          uint32_t first[4]);
+int stitch_selftest_blend8_samples(stitch_ctx *ctx, uint32_t n, uint32_t seed, uint32_t *out_triples);
+
 /* ---- JPEG container helpers (host side of src/jpeg-encoder.ts) ------------ */
 
 /* Writes SOI + JFIF APP0 + DQT + SOF0 + DHT + SOS for the encoder definition in
