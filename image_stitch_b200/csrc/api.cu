@@ -966,8 +966,10 @@ static int render_rows(stitch_job *job, uint32_t a, uint32_t b, uint8_t *d_rows,
     bg_words(jd, fp.bg_lo, fp.bg_hi);
     fp.rowsum = reinterpret_cast<unsigned long long *>(job->d_sync); fp.ticket = job->d_sync + (size_t)n_rows * 16;
     fp.out = d_rows; fp.out_pitch = job->out_pitch; fp.lead = (uint32_t)job->out_lead;
-    static const bool use_strip = getenv("STITCH_STRIP") != nullptr;   // opt-in until its parity run is green
-    if (job->strip_ok && use_strip) {
+    // STITCH_STRIP=1 selects the row-pipelined kernel (strip.cu: parity-green, slower than the unit kernel on
+    // B200 -- DESIGN.md section 3d); read at every call so that tests can run both in one process
+    const char *strip_env = getenv("STITCH_STRIP");
+    if (job->strip_ok && strip_env && strip_env[0] == '1') {
       StripParams sp{};
       sp.tiles = job->d_tiles; sp.maps = job->d_maps; sp.ivs = reinterpret_cast<const StripIv *>(job->d_ivs);
       sp.col_start = reinterpret_cast<const uint32_t *>(job->d_col_start); sp.lists = reinterpret_cast<const uint32_t *>(job->d_lists);

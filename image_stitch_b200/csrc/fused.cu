@@ -159,6 +159,15 @@ __device__ __forceinline__ UnitPlan unit_plan(const FusedParams &p, const uint32
         pl.fast_src = src; pl.fast_pitch = pitch;
         pl.halo_fast = ty0 <= ya - 1;
         pl.left_fast = tx0 <= X0 - 1;
+        // The predictor row ya-1 and the pixel column X0-1 lie outside the unit: a tile ABOVE this one in z order
+        // that ends exactly at the unit's top or left edge does not touch the unit (it was skipped above) but is
+        // what the canvas shows there, so the copies straight out of this tile would be wrong.
+        for (int q = k + 1; q < (int)n_list && (pl.halo_fast || pl.left_fast); q++) {
+          const DevTile &h = p.tiles[__ldg(list + q)];
+          if (h.x0 >= h.x1 || h.y0 >= h.y1) continue;
+          if (h.y0 <= ya - 1 && h.y1 > ya - 1 && h.x0 < X1 && h.x1 > X0) pl.halo_fast = false;
+          if (h.x0 <= X0 - 1 && h.x1 > X0 - 1 && h.y0 < yb && h.y1 > ya - 1) pl.left_fast = false;
+        }
       }
     }
     break;

@@ -86,7 +86,7 @@ struct StripIv {
 enum StripKind : uint32_t { SK_BG = 0, SK_DIRECT = 1, SK_COMP = 2, SK_SHIFT = 3 };
 struct StripParams {
   const DevTile *tiles;
-  const void *maps;           // one 128-byte CUtensorMap per tile: 32-bit words, box 256 x 1
+  const void *maps;           // two 128-byte CUtensorMaps per tile (32-bit words): box 128 x 1 row, box 128 x 4 rows
   const StripIv *ivs;
   const uint32_t *col_start;  // [ncol + 1]: intervals of box column c are ivs[col_start[c] .. col_start[c + 1])
   const uint32_t *lists;

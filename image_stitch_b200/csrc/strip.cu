@@ -1,57 +1,49 @@
 // strip.cu -- kernels (b)+(c) in ONE pass over HBM, row-pipelined: normalise + composite the tiles under a
 // canvas row (src/image-concat-core.ts:404-545, :551-685; src/pixel-ops.ts:496-736), compute the five PNG filter
-// costs (src/png-filter.ts:148-181), agree on the row's winner across every CTA that shares the row, write the
+// costs (src/png-filter.ts:148-181), agree on the row's winner across all the warps that share the row, write the
 // filtered scanline.  HBM traffic: every visible tile pixel read once, every output byte written once.
 //
-// Decomposition.  Rows [y_begin, y_end) are cut into nry row RANGES, a canvas row into nsx column STRIPS of
-// SW = Q * 2048 words; CTA (sx, ry) walks down its strip of its range one row at a time.  A CTA is 16 consumer
-// warps and one producer warp around a ring of NSLOT row slots in shared memory:
+// Decomposition.  A canvas row is cut into COLUMNS of 128 words (one 16-byte quad per lane), the rows
+// [y_begin, y_end) into nry RANGES; warp (column, range) walks down its column one row at a time and is its own
+// producer and consumer around a private ring of 16 row slots in shared memory (4 stages of 4 rows):
 //
-//   producer   per row: waits until the slot is free; lane b owns box b (1 KiB) of the strip row and issues what
-//              the host's plan says for it -- a 2-D TMA box load straight from the one tile that covers it (any
-//              pixel alignment: the tensor map does the address arithmetic), a bulk copy of the background row,
-//              or nothing: boxes that need compositing are flagged for the consumers.  Lane 0 also fetches the
-//              pixel left of the strip.  Loads complete on the slot's "full" mbarrier.
-//   consumers  per row y: (1) composite the flagged boxes of row y+1 (normalise + alpha-over per 16-byte quad),
-//              arrive on its "full" barrier; (2) wait for row y and sweep it: thread t owns quads t, t+512, ... of
-//              the strip row, the row above is carried unpacked in registers, costs of None/Sub/Up/Average on
-//              packed bytes (VABSDIFF4), Paeth two bytes at a time in half2, its residual parked in TENSOR MEMORY;
-//              (3) publish the warp's five partial sums with one red.global.add.u64 each (the high half counts
-//              arrivals, so the sums need no fence and no flag); (4) read row y-1's sums -- complete once every
-//              warp of every strip has swept y-1, which they did while this warp swept y --, pick the winner
-//              (first minimum: None, Sub, Up, Average, Paeth) and emit row y-1: Paeth from tensor memory, the
-//              others recomputed from the raw rows still in the ring; (5) release row y-2's slot.
+//   stage in   lane 0 issues, per row, what the host's plan says for the column: a 2-D TMA box load (128 words x 1
+//              row) straight from the one tile that covers it, or a bulk copy of the background row; a column whose
+//              source is not 16-byte aligned (a tiled TMA load faults on such a start coordinate) is copied by all
+//              lanes with 4-byte cp.async; a column that needs compositing (tile edges, overlap, blending, foreign
+//              formats) is composed by the warp, one quad per lane.  The pixel left of the column comes separately
+//              (4-byte cp.async by lane 0).  Everything completes on the stage's mbarrier.
+//   sweep      row y: the row above is carried unpacked in registers; costs of None/Sub/Up/Average on packed bytes
+//              (VABSDIFF4), Paeth two bytes at a time in half2, its residual parked in TENSOR MEMORY; five warp sums
+//              leave with one red.global.add.u64 each (the high half counts arrivals: no fence, no flag)
+//   emit       row y-LAG: its sums are complete once every column of the range has swept it -- which they did while
+//              this warp swept the LAG rows since --, winner = first minimum (None, Sub, Up, Average, Paeth);
+//              Paeth comes from tensor memory, the others are recomputed from the raw rows still in the ring
 //
-// Every CTA of the grid must be resident (the CTAs of a range wait for one another's sums): cooperative launch.
-// No wait cycle can form: the sums of row r need every strip to have swept r, which needs row r's slot, which is
-// free once row r-NSLOT+... was emitted, which needs the sums of an EARLIER row: induction on the row index.
+// Warps wait for one another only through the row sums, LAG rows late; every warp of the grid must be resident
+// (cooperative launch).  No wait cycle can form: a warp blocks only in the wait for the sums of row r, and every
+// warp reaches the sweep of row r without waiting for anything but rows before r.
 #include "common.cuh"
 #include "kernels.h"
 #include "filter_math.cuh"
 
 namespace stitch {
 
-static constexpr int SK_WARPS = 16;                      // consumer warps
-static constexpr int SK_CONS = SK_WARPS * 32;            // consumer threads
-static constexpr int SK_THREADS = SK_CONS + 32;          // + the producer warp
-static constexpr int SK_BOX = 256;                       // words per TMA box (1 KiB)
-static constexpr int SK_NSLOT = 5;                       // rows y-2 .. y+2
-static constexpr int SK_LEAD = 128;                      // bytes ahead of a slot's row; the pixel left of the strip ends at +128
-
-template <int Q> struct SKGeo {
-  static constexpr int SW = Q * SK_CONS * 4;             // words per strip row
-  static constexpr int NB = SW / SK_BOX;                 // boxes per strip row (8 Q)
-  static constexpr int SLOT_BYTES = SK_LEAD + SW * 4;
-  static constexpr int OFF_BAR = SK_NSLOT * SLOT_BYTES;  // full[NSLOT] | empty[NSLOT] | planned[NSLOT]
-  static constexpr int OFF_PLAN = OFF_BAR + 3 * SK_NSLOT * 8 + 8;   // per slot: 32 interval indices + mask (+ pad)
-  static constexpr int PLAN_WORDS = 36;
-  static constexpr int OFF_TMEM = OFF_PLAN + SK_NSLOT * PLAN_WORDS * 4;
-  static constexpr int SMEM = OFF_TMEM + 16;
-  static constexpr int TMEM_COLS = Q * 32 < 32 ? 32 : Q * 32;       // 4 warp groups x 2 rows x Q quads x 4 words
-  static_assert(NB <= 32, "one producer lane per box");
-  static_assert((TMEM_COLS & (TMEM_COLS - 1)) == 0 && TMEM_COLS <= 512, "tensor memory columns: a power of two");
-  static_assert(SLOT_BYTES % 128 == 0, "TMA destinations are 128-byte aligned");
-};
+static constexpr int SK_WARPS = 16;                      // warps per CTA (one CTA per SM)
+static constexpr int SK_THREADS = SK_WARPS * 32;
+static constexpr int SK_BOX = 128;                       // words per column = per TMA box (512 bytes)
+static constexpr int SK_RING = 16;                       // row slots per warp
+static constexpr int SK_SROWS = 4;                       // rows per stage
+static constexpr int SK_NST = SK_RING / SK_SROWS;        // stages
+static constexpr int SK_TROWS = 2 * SK_SROWS;            // rows of Paeth residuals in tensor memory: the group swept and the one before
+static constexpr int SK_W_ROWS = SK_RING * SK_BOX * 4;   // per-warp shared memory: rows | left pixels | stage barriers
+static constexpr int SK_W_HALO = SK_W_ROWS;              //   left pixel of row slot r: 8 bytes at + 8 r (words c0, c1)
+static constexpr int SK_W_BAR = SK_W_HALO + SK_RING * 8;
+static constexpr int SK_W_BYTES = (SK_W_BAR + SK_NST * 8 + 127) / 128 * 128;
+static constexpr int SK_SMEM = SK_WARPS * SK_W_BYTES + 16;          // + tensor-memory base address
+static constexpr int SK_TMEM_COLS = 256;                 // >= (SK_WARPS / 4) x TROWS x 4 words
+static_assert((SK_WARPS / 4) * SK_TROWS * 4 <= SK_TMEM_COLS && SK_WARPS % 4 == 0, "tensor memory layout");
+static_assert(SK_NST == 4 && SK_SROWS == 4, "the group schedule below: sweep g, emit g-1, refill the stage of g-2 with g+2");
 
 uint32_t strip_box_words() { return SK_BOX; }
 
@@ -182,246 +174,229 @@ __device__ __forceinline__ void iv_seek(const StripParams &p, IvCursor &c, int y
   while ((uint32_t)y >= c.y_end && c.idx + 1u < c.end_idx) { c.idx++; iv_load(p, c); }
 }
 
-// The pixel left of the strip in row y (the last pixel of box column `ch`): c0 = word -2 (8-byte pixels), c1 = word -1.
+__device__ __forceinline__ void cp_async8(uint32_t dst, const void *src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src) : "memory");
+}
+
+// The cursors live in shared memory between stage issues (12 words each), so that they hold no registers
+// while the warp sweeps.
+__device__ __forceinline__ void cur_save(uint32_t a, const IvCursor &c) {
+  sts128(a, make_uint4(c.idx, c.end_idx, c.y_end, c.kind));
+  sts128(a + 16u, make_uint4(c.tile, c.list_off, c.n_list, (uint32_t)c.cw));
+  const unsigned long long px = reinterpret_cast<unsigned long long>(c.pix);
+  sts128(a + 32u, make_uint4((uint32_t)c.cy, c.pitch, (uint32_t)px, (uint32_t)(px >> 32)));
+}
+__device__ __forceinline__ void cur_load(uint32_t a, IvCursor &c) {
+  const uint4 x = lds128(a), y = lds128(a + 16u), z = lds128(a + 32u);
+  c.idx = x.x; c.end_idx = x.y; c.y_end = x.z; c.kind = x.w;
+  c.tile = y.x; c.list_off = y.y; c.n_list = y.z; c.cw = (int32_t)y.w;
+  c.cy = (int32_t)z.x; c.pitch = z.y;
+  c.pix = reinterpret_cast<const uint8_t *>(((unsigned long long)z.w << 32) | z.z);
+}
+
+// Shared-memory addresses of one warp's private area.
+struct WarpSm {
+  uint32_t rows, halo, bar, cur;   // cur: two saved cursors (the column's, the left neighbour's)
+};
+
+// The pixel left of the column in row y -> the slot's halo words (c0 at +0, c1 at +4).  One lane.
 template <int BPW>
-__device__ __forceinline__ uint2 halo_pixel(const StripParams &p, IvCursor &hc, const uint32_t ch, const int y) {
-  if (y < 0) return make_uint2(0u, 0u);
+__device__ __forceinline__ void halo_issue(const StripParams &p, IvCursor &hc, const bool has_left, const uint32_t col,
+                                           const int y, const uint32_t halo) {
+  if (!has_left || y < 0) { sts32(halo, 0u); sts32(halo + 4u, 0u); return; }
   iv_seek(p, hc, y);
   if (hc.kind == SK_DIRECT || hc.kind == SK_SHIFT) {
-    const uint32_t *src = reinterpret_cast<const uint32_t *>(hc.pix + (size_t)(y + hc.cy) * hc.pitch) + (hc.cw + SK_BOX - BPW);
-    return BPW == 2 ? make_uint2(__ldg(src), __ldg(src + 1)) : make_uint2(0u, __ldg(src));
-  }
-  if (hc.kind == SK_COMP) {
-    const uint4 v = strip_compose_quad<BPW>(compose_ctx(p), p.lists + hc.list_off, hc.n_list, (int)(ch * SK_BOX + SK_BOX - 4), y);
-    return make_uint2(v.z, v.w);
-  }
-  return BPW == 2 ? make_uint2(p.bg_lo, p.bg_hi) : make_uint2(0u, p.bg_lo);
-}
-
-// ---- producer warp: rows ya-1 .. yb-1 of the strip into the ring ------------------------------------------------
-template <int BPW, int Q>
-__device__ __forceinline__ void strip_producer(const StripParams &p, const uint32_t smem, const uint32_t lane,
-                                               const uint32_t sx, const int ya, const int n_k) {
-  using G = SKGeo<Q>;
-  const uint32_t bar_full = smem + G::OFF_BAR, bar_empty = bar_full + 8 * SK_NSLOT, bar_plan = bar_empty + 8 * SK_NSLOT;
-  const uint32_t col = sx * G::NB + lane;
-  const bool has_col = lane < (uint32_t)G::NB && col < p.ncol;
-  IvCursor bc{}, hc{};
-  if (has_col) iv_open(p, bc, col);
-  const bool has_halo = lane == 0u && sx > 0u;
-  const uint32_t ch = sx * G::NB - 1u;
-  if (has_halo) iv_open(p, hc, ch);
-  uint2 halo = make_uint2(0u, 0u);
-  if (has_halo) halo = halo_pixel<BPW>(p, hc, ch, ya - 1);
-  for (int k = 0; k < n_k; k++) {
-    const int y = ya - 1 + k;
-    const uint32_t slot = (uint32_t)k % SK_NSLOT, it = (uint32_t)k / SK_NSLOT;
-    if (k >= SK_NSLOT) mbar_wait(bar_empty + 8u * slot, (it & 1u) ^ 1u);   // the row that used the slot was emitted
-    const uint32_t row = smem + slot * G::SLOT_BYTES + SK_LEAD;
-    const uint32_t full = bar_full + 8u * slot;
-    const uint32_t plan = smem + G::OFF_PLAN + slot * (G::PLAN_WORDS * 4);
-    if (lane == 0u) {   // the pixel left of the strip (fetched one row ahead)
-      if (BPW == 2) sts32(row - 8u, halo.x);
-      sts32(row - 4u, halo.y);
-    }
-    bool comp = false, shift = false;
-    const uint8_t *sp = nullptr;   // SK_SHIFT: first byte of the box in the source row
-    if (has_col && y >= 0) {
-      iv_seek(p, bc, y);
-      const uint32_t dst = row + lane * (SK_BOX * 4);
-      if (bc.kind == SK_DIRECT) {
-        mbar_expect_tx(full, SK_BOX * 4);
-        tma_box_2d(dst, reinterpret_cast<const uint8_t *>(p.maps) + (size_t)bc.tile * 128u, bc.cw, y + bc.cy, full);
-      } else if (bc.kind == SK_BG) {
-        mbar_expect_tx(full, SK_BOX * 4);
-        bulk_copy(dst, p.bg_row, SK_BOX * 4, full);
-      } else if (bc.kind == SK_SHIFT) {
-        shift = true;
-        sp = bc.pix + (size_t)(y + bc.cy) * bc.pitch + (size_t)bc.cw * 4u;
-      } else {
-        comp = true;
-        sts32(plan + lane * 4u, bc.idx);
-      }
-    }
-    // boxes whose source is not 16-byte aligned: the whole warp copies them word by word, asynchronously
-    for (uint32_t m = __ballot_sync(0xffffffffu, shift); m; m &= m - 1u) {
-      const int b = __ffs((int)m) - 1;
-      const unsigned long long spb = __shfl_sync(0xffffffffu, (unsigned long long)sp, b);
-      const uint32_t nw = __shfl_sync(0xffffffffu, bc.list_off, b);
-      const uint32_t dstb = row + (uint32_t)b * (SK_BOX * 4) + lane * 4u;
-      const uint8_t *srcb = reinterpret_cast<const uint8_t *>(spb) + lane * 4u;
-#pragma unroll
-      for (int i = 0; i < SK_BOX / 32; i++)
-        if (lane + 32u * i < nw) cp_async4(dstb + 128u * i, srcb + 128 * i);
-    }
-    mbar_arrive_after_cp_async(full);   // every lane arrives once per row: when its copies, if any, have landed
-    const uint32_t mask = __ballot_sync(0xffffffffu, comp);
-    if (lane == 0u) sts32(plan + 32u * 4u, mask);
-    mbar_arrive(bar_plan + 8u * slot);
-    if (has_halo && k + 1 < n_k) halo = halo_pixel<BPW>(p, hc, ch, y + 1);
-  }
-}
-
-// ---- consumers: their share of the compositing of ring entry k (row ya-1+k) --------------------------------------
-template <int BPW, int Q>
-__device__ __forceinline__ void strip_compose_share(const StripParams &p, const uint32_t smem, const uint32_t tid,
-                                                    const uint32_t sx, const int ya, const int k) {
-  using G = SKGeo<Q>;
-  const uint32_t bar_full = smem + G::OFF_BAR, bar_plan = bar_full + 16 * SK_NSLOT;
-  const int y = ya - 1 + k;
-  const uint32_t slot = (uint32_t)k % SK_NSLOT, it = (uint32_t)k / SK_NSLOT;
-  const uint32_t row = smem + slot * G::SLOT_BYTES + SK_LEAD;
-  const uint32_t plan = smem + G::OFF_PLAN + slot * (G::PLAN_WORDS * 4);
-  mbar_wait(bar_plan + 8u * slot, it & 1u);   // the slot is free and the producer has said what it does not load
-  if (y < 0) {   // previousLine === null: zeros
-#pragma unroll
-    for (int i = 0; i < Q; i++) sts128(row + 16u * (tid + SK_CONS * i), make_uint4(0u, 0u, 0u, 0u));
+    const uint8_t *src = hc.pix + (size_t)(y + hc.cy) * hc.pitch + (size_t)(hc.cw + SK_BOX - BPW) * 4u;
+    if (BPW == 2) cp_async8(halo, src); else cp_async4(halo + 4u, src);
+  } else if (hc.kind == SK_COMP) {
+    const uint4 v = strip_compose_quad<BPW>(compose_ctx(p), p.lists + hc.list_off, hc.n_list, (int)(col * SK_BOX - 4u), y);
+    sts32(halo, v.z); sts32(halo + 4u, v.w);
   } else {
-    const uint32_t mask = lds32(plan + 32u * 4u);
-    if (mask) {
-#pragma unroll
-      for (int i = 0; i < Q; i++) {
-        const uint32_t b = (tid >> 6) + 8u * i;
-        if ((mask >> b) & 1u) {   // uniform for the warp: a box is two warps wide
-          const StripIv &iv = p.ivs[lds32(plan + b * 4u)];
-          const uint32_t j = tid + SK_CONS * i;
-          const uint4 v = strip_compose_quad<BPW>(compose_ctx(p), p.lists + iv.list_off, iv.n_list, (int)(sx * G::SW + 4u * j), y);
-          sts128(row + 16u * j, v);
+    sts32(halo, BPW == 2 ? p.bg_lo : 0u); sts32(halo + 4u, BPW == 2 ? p.bg_hi : p.bg_lo);
+  }
+}
+
+// Ring entries 4j .. 4j+3 (rows ya-1+k) of the warp's column into their slots; completes on the stage's mbarrier.
+// Lanes 0..3 fetch the left pixels of the four rows, each with its own copy of the left neighbour's cursor.
+template <int BPW>
+__device__ __forceinline__ void issue_stage(const StripParams &p, const WarpSm ws, const uint32_t lane, const uint32_t col,
+                                            const int ya, const int n_k, const int j) {
+  const int k0 = j * SK_SROWS;
+  if (k0 >= n_k) return;
+  const int y0 = ya - 1 + k0;
+  const int n_r = min(SK_SROWS, n_k - k0);   // rows of the stage that exist
+  IvCursor bc;
+  cur_load(ws.cur, bc);
+  const uint32_t bar = ws.bar + 8u * ((uint32_t)j & (SK_NST - 1));
+  const uint32_t slot0 = (uint32_t)k0 & (SK_RING - 1);
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // our reads of these slots, then bulk writes into them
+  if ((int)lane < n_r) {
+    IvCursor hc;
+    const bool has_left = col > 0u;
+    if (has_left) cur_load(ws.cur + 48u, hc);
+    halo_issue<BPW>(p, hc, has_left, col, y0 + (int)lane, ws.halo + 8u * (slot0 + lane));
+    if ((int)lane == n_r - 1 && has_left) cur_save(ws.cur + 48u, hc);   // the furthest one
+  }
+  if (y0 >= 0) iv_seek(p, bc, y0);
+  if (y0 >= 0 && bc.kind == SK_DIRECT && (uint32_t)(y0 + n_r - 1) < bc.y_end) {
+    // the whole stage lies in one tile: one box of 128 words x 4 rows (rows past the range or the tile are never read)
+    if (lane == 0u) {
+      mbar_expect_tx(bar, SK_SROWS * SK_BOX * 4);
+      tma_box_2d(ws.rows + slot0 * (SK_BOX * 4), reinterpret_cast<const uint8_t *>(p.maps) + (size_t)bc.tile * 256u + 128u, bc.cw, y0 + bc.cy, bar);
+    }
+  } else {
+#pragma unroll 1
+    for (int r = 0; r < n_r; r++) {
+      const int y = y0 + r;
+      const uint32_t row = ws.rows + (slot0 + (uint32_t)r) * (SK_BOX * 4);
+      if (y < 0) {   // previousLine === null: zeros
+        sts128(row + 16u * lane, make_uint4(0u, 0u, 0u, 0u));
+        continue;
+      }
+      iv_seek(p, bc, y);
+      if (bc.kind == SK_DIRECT) {
+        if (lane == 0u) {
+          mbar_expect_tx(bar, SK_BOX * 4);
+          tma_box_2d(row, reinterpret_cast<const uint8_t *>(p.maps) + (size_t)bc.tile * 256u, bc.cw, y + bc.cy, bar);
         }
+      } else if (bc.kind == SK_BG) {
+        if (lane == 0u) {
+          mbar_expect_tx(bar, SK_BOX * 4);
+          bulk_copy(row, p.bg_row, SK_BOX * 4, bar);
+        }
+      } else if (bc.kind == SK_SHIFT) {
+        const uint8_t *src = bc.pix + (size_t)(y + bc.cy) * bc.pitch + (size_t)bc.cw * 4u + 16u * lane;
+#pragma unroll
+        for (int i = 0; i < 4; i++)
+          if (4u * lane + i < bc.list_off) cp_async4(row + 16u * lane + 4u * i, src + 4 * i);
+      } else {
+        const uint4 v = strip_compose_quad<BPW>(compose_ctx(p), p.lists + bc.list_off, bc.n_list, (int)(col * SK_BOX + 4u * lane), y);
+        sts128(row + 16u * lane, v);
       }
     }
   }
   __syncwarp();
-  if ((tid & 31u) == 0u) mbar_arrive(bar_full + 8u * slot);
+  mbar_arrive_after_cp_async(bar);   // every lane once per stage: when its own copies, if any, have landed
+  cur_save(ws.cur, bc);              // (all lanes hold the same cursor: same value, same address)
 }
 
-// Winner of row r (first minimum in the order None, Sub, Up, Average, Paeth; png-filter.ts:174) once all `total`
-// warps have added their sums.  pre: lane f's word as read earlier (count in the high half).
-__device__ __forceinline__ uint32_t strip_winner(const StripParams &p, const int r, const uint32_t lane,
-                                                 const uint32_t total, unsigned long long w) {
-  const unsigned long long *rs = p.rowsum + (size_t)(r - (int)p.y_begin) * 8 + (lane < 5u ? lane : 0u);
+// Winners of the SK_SROWS ring entries k0 .. k0+3 (first minimum in the order None, Sub, Up, Average, Paeth;
+// png-filter.ts:174) once all `total` columns have added their sums: lane 8 r + f holds word f of row r.  Returns
+// the winners packed 3 bits per row, the same in every lane.  pre: the lane's word as read earlier.
+__device__ __forceinline__ uint32_t strip_winners(const StripParams &p, const int y0, const int k0, const int n_k,
+                                                  const uint32_t lane, const uint32_t total, unsigned long long w) {
+  const uint32_t r = lane >> 3, f = lane & 7u;
+  const bool mine = f < 5u && k0 + (int)r >= 1 && k0 + (int)r < n_k;   // entry 0 is the predictor row: never emitted
+  const unsigned long long *rs = p.rowsum + (size_t)(y0 + (int)r - (int)p.y_begin) * 8 + f;
   for (;;) {
-    const bool ok = lane >= 5u || (uint32_t)(w >> 32) == total;
+    const bool ok = !mine || (uint32_t)(w >> 32) == total;
     if (__all_sync(0xffffffffu, ok)) break;
-    __nanosleep(40);
-    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(w) : "l"(rs) : "memory");
+#ifdef SK_EXPERIMENT_NOWAIT
+    break;
+#endif
+    __nanosleep(100);
+    if (mine) asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(w) : "l"(rs) : "memory");
   }
-  const uint32_t key = lane < 5u ? (((uint32_t)w << 3) | lane) : 0xffffffffu;
-  return __reduce_min_sync(0xffffffffu, key) & 7u;
+  uint32_t key = mine ? (((uint32_t)w << 3) | f) : 0xffffffffu;
+  key = min(key, __shfl_xor_sync(0xffffffffu, key, 1));
+  key = min(key, __shfl_xor_sync(0xffffffffu, key, 2));
+  key = min(key, __shfl_xor_sync(0xffffffffu, key, 4));
+  return __reduce_or_sync(0xffffffffu, f == 0u ? (key & 7u) << (3u * r) : 0u);
 }
 
 // The row above, as the sweep of the next row needs it.
-template <int Q> struct RowCarry {
-  uint4 raw[Q];     // the thread's quads, packed
-  H4 hb[Q][4];      // ... unpacked to half2 (1024 + byte)
-  H4 hl[Q][2];      // the two words left of each quad, unpacked ([0] only for 8-byte pixels)
+struct RowCarry {
+  uint4 raw;     // the lane's quad, packed
+  H4 hb[4];      // ... unpacked to half2 (1024 + byte)
+  H4 hl[2];      // the two words left of the quad, unpacked ([0] only for 8-byte pixels)
 };
 
-template <int BPW, int Q>
-__device__ __forceinline__ void carry_init(RowCarry<Q> &c, const uint32_t row, const uint32_t tid) {
-#pragma unroll
-  for (int i = 0; i < Q; i++) {
-    const uint32_t a = row + 16u * (tid + SK_CONS * i);
-    c.raw[i] = lds128(a);
-    c.hb[i][0] = unpack_h4(c.raw[i].x); c.hb[i][1] = unpack_h4(c.raw[i].y);
-    c.hb[i][2] = unpack_h4(c.raw[i].z); c.hb[i][3] = unpack_h4(c.raw[i].w);
-    if (BPW == 2) c.hl[i][0] = unpack_h4(lds32(a - 8u));
-    c.hl[i][1] = unpack_h4(lds32(a - 4u));
+// The two words left of the lane's quad: the lane to the left has them; lane 0 reads the slot's halo words.
+template <int BPW>
+__device__ __forceinline__ void left_words(const uint4 q, const uint32_t halo, const uint32_t lane, uint32_t &c0, uint32_t &c1) {
+  c0 = BPW == 2 ? __shfl_up_sync(0xffffffffu, q.z, 1) : 0u;
+  c1 = __shfl_up_sync(0xffffffffu, q.w, 1);
+  if (lane == 0u) {
+    if (BPW == 2) c0 = lds32(halo);
+    c1 = lds32(halo + 4u);
   }
 }
 
 // Sweep of one row: `ab` = the row above (in), `cu` = this row (out).  Adds the warp's sums to the row's words.
-template <int BPW, int Q>
-__device__ __forceinline__ void strip_sweep(const StripParams &p, const RowCarry<Q> &ab, RowCarry<Q> &cu, const uint32_t row,
-                                            const uint32_t tid, const int xw0, const int wmax, const bool guard,
-                                            const uint32_t taddr, const int y, const uint32_t (&lmask)[5]) {
+template <int BPW>
+__device__ __forceinline__ void strip_sweep(const StripParams &p, const RowCarry &ab, RowCarry &cu, const uint32_t row,
+                                            const uint32_t halo, const uint32_t lane, const int qw, const int wmax,
+                                            const bool guard, const uint32_t taddr, const int y, const uint32_t (&lmask)[5]) {
   uint32_t s[5] = {0u, 0u, 0u, 0u, 0u};
-#pragma unroll
-  for (int i = 0; i < Q; i++) {
-    const uint32_t j = tid + SK_CONS * i, a = row + 16u * j;
-    const uint4 cur = lds128(a);
-    const uint32_t lc1 = lds32(a - 4u);
-    const uint32_t lc0 = BPW == 2 ? lds32(a - 8u) : 0u;
-    const int qw = xw0 + 4 * (int)j;
-    if (guard) sweep_quad<BPW, true>(cur, lc0, lc1, ab.raw[i], ab.hb[i], ab.hl[i], cu.hb[i], cu.hl[i], qw, wmax, taddr + 4u * i, s);
-    else sweep_quad<BPW, false>(cur, lc0, lc1, ab.raw[i], ab.hb[i], ab.hl[i], cu.hb[i], cu.hl[i], qw, wmax, taddr + 4u * i, s);
-    cu.raw[i] = cur;
-  }
+  const uint4 cur = lds128(row);
+  uint32_t lc0, lc1;
+  left_words<BPW>(cur, halo, lane, lc0, lc1);
+  if (guard) sweep_quad<BPW, true>(cur, lc0, lc1, ab.raw, ab.hb, ab.hl, cu.hb, cu.hl, qw, wmax, taddr, s);
+  else sweep_quad<BPW, false>(cur, lc0, lc1, ab.raw, ab.hb, ab.hl, cu.hb, cu.hl, qw, wmax, taddr, s);
+  cu.raw = cur;
   uint32_t v = 0u;
 #pragma unroll
   for (int f = 0; f < 5; f++) v |= __reduce_add_sync(0xffffffffu, s[f]) & lmask[f];
-  const uint32_t lane = tid & 31u;
   if (lane < 5u) atomicAdd(p.rowsum + (size_t)(y - (int)p.y_begin) * 8 + lane, (1ull << 32) | (unsigned long long)v);
-  asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
 }
 
-// Row y with winner ft: the filtered bytes, one 128-bit store per quad.  cur/up: the row and the row above in the ring.
-template <int BPW, int Q>
+// Row y with winner ft: the filtered bytes, one 128-bit store per lane.  cur/up: the row and the row above in the ring.
+template <int BPW>
 __device__ __forceinline__ void strip_emit(const StripParams &p, const uint32_t ft, const int y, const uint32_t cur_row,
-                                           const uint32_t up_row, const uint32_t taddr, const uint32_t tid, const uint32_t sx,
-                                           const int xw0, const int wmax) {
+                                           const uint32_t up_row, const uint32_t halo, const uint32_t taddr,
+                                           const uint32_t lane, const uint32_t col, const int qw, const int wmax) {
   uint8_t *orow = p.out + (size_t)(y - (int)p.y_begin) * p.out_pitch + p.lead;
-  if (sx == 0u && tid == 0u) orow[0] = (uint8_t)ft;
-#pragma unroll
-  for (int i = 0; i < Q; i++) {
-    const uint32_t j = tid + SK_CONS * i, a = cur_row + 16u * j, b = up_row + 16u * j;
-    const int qw = xw0 + 4 * (int)j;
-    uint4 o;
-    if (ft == 4u) {
-      __syncwarp();   // tcgen05.ld is .sync.aligned: the partial stores of the quad before may have split the warp
-      o = tmem_ld4(taddr + 4u * i);
-    } else {
-      o = lds128(a);
-      if (ft != 0u) {
-        uint4 pr;
-        if (ft == 2u) {
-          pr = lds128(b);
-        } else {
-          const uint32_t c1 = lds32(a - 4u);
-          pr = BPW == 1 ? make_uint4(c1, o.x, o.y, o.z) : make_uint4(lds32(a - 8u), c1, o.x, o.y);
-          if (ft == 3u) {
-            const uint4 upq = lds128(b);
-            pr = make_uint4(avg4(pr.x, upq.x), avg4(pr.y, upq.y), avg4(pr.z, upq.z), avg4(pr.w, upq.w));
-          }
+  if (col == 0u && lane == 0u) orow[0] = (uint8_t)ft;
+  uint4 o;
+  if (ft == 4u) {
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");   // the row's residuals were stored LAG rows ago
+    o = tmem_ld4(taddr);
+  } else {
+    o = lds128(cur_row);
+    if (ft != 0u) {
+      uint4 pr;
+      if (ft == 2u) {
+        pr = lds128(up_row);
+      } else {
+        uint32_t c0, c1;
+        left_words<BPW>(o, halo, lane, c0, c1);
+        pr = BPW == 1 ? make_uint4(c1, o.x, o.y, o.z) : make_uint4(c0, c1, o.x, o.y);
+        if (ft == 3u) {
+          const uint4 upq = lds128(up_row);
+          pr = make_uint4(avg4(pr.x, upq.x), avg4(pr.y, upq.y), avg4(pr.z, upq.z), avg4(pr.w, upq.w));
         }
-        o = make_uint4(sub4(o.x, pr.x), sub4(o.y, pr.y), sub4(o.z, pr.z), sub4(o.w, pr.w));
       }
-    }
-    uint8_t *od = orow + 1 + 4 * (size_t)qw;
-    if (qw + 4 <= wmax) {
-      *reinterpret_cast<uint4 *>(od) = o;
-    } else if (qw < wmax) {
-      uint32_t *ow = reinterpret_cast<uint32_t *>(od);
-      ow[0] = o.x;
-      if (qw + 1 < wmax) ow[1] = o.y;
-      if (qw + 2 < wmax) ow[2] = o.z;
+      o = make_uint4(sub4(o.x, pr.x), sub4(o.y, pr.y), sub4(o.z, pr.z), sub4(o.w, pr.w));
     }
   }
+  uint8_t *od = orow + 1 + 4 * (size_t)qw;
+  if (qw + 4 <= wmax) {
+    *reinterpret_cast<uint4 *>(od) = o;
+  } else if (qw < wmax) {
+    uint32_t *ow = reinterpret_cast<uint32_t *>(od);
+    ow[0] = o.x;
+    if (qw + 1 < wmax) ow[1] = o.y;
+    if (qw + 2 < wmax) ow[2] = o.z;
+  }
+  __syncwarp();   // the partial stores may have split the warp; what follows is .sync.aligned
 }
 
-template <int BPW, int Q>
+template <int BPW>
 __global__ void __launch_bounds__(SK_THREADS, 1) strip_kernel(const StripParams p) {
-  using G = SKGeo<Q>;
   extern __shared__ __align__(128) uint8_t sk_smem[];
   const uint32_t smem = (uint32_t)__cvta_generic_to_shared(sk_smem);
-  const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31u;
-  const uint32_t ry = blockIdx.x / p.nsx, sx = blockIdx.x - ry * p.nsx;
-  const int ya = (int)(p.y_begin + ry * p.rows_per_range);
-  const int yb = (int)min(p.y_end, (uint32_t)ya + p.rows_per_range);
-  const int n_k = yb - ya + 1;   // ring entries: rows ya-1 .. yb-1
-  const uint32_t bar_full = smem + G::OFF_BAR, bar_empty = bar_full + 8 * SK_NSLOT, bar_plan = bar_empty + 8 * SK_NSLOT;
-  if (tid == 0u) {
-    for (int s = 0; s < SK_NSLOT; s++) {
-      mbar_init(bar_full + 8u * s, 32u + SK_WARPS);   // every producer lane + every consumer warp
-      mbar_init(bar_empty + 8u * s, SK_WARPS);
-      mbar_init(bar_plan + 8u * s, 32u);
-    }
+  const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+  WarpSm ws;
+  ws.rows = smem + warp * SK_W_BYTES; ws.halo = ws.rows + SK_W_HALO; ws.bar = ws.rows + SK_W_BAR;
+  ws.cur = smem + SK_WARPS * SK_W_BYTES + 16u + warp * 96u;
+  const uint32_t tmem_slot = smem + SK_WARPS * SK_W_BYTES;
+  if (lane == 0u) {
+    for (int s = 0; s < SK_NST; s++) mbar_init(ws.bar + 8u * s, 32u);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
-  const uint32_t tmem_slot = smem + G::OFF_TMEM;
   if (warp == 0u) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(G::TMEM_COLS) : "memory");
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(SK_TMEM_COLS) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -429,99 +404,124 @@ __global__ void __launch_bounds__(SK_THREADS, 1) strip_kernel(const StripParams 
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem_base = lds32(tmem_slot);
 
-  if (warp == (uint32_t)SK_WARPS) {
-    strip_producer<BPW, Q>(p, smem, lane, sx, ya, n_k);
-  } else {
-    const int xw0 = (int)(sx * G::SW), wmax = (int)p.canvas_w * BPW;
-    const bool guard = xw0 + G::SW > wmax;
-    const uint32_t total = p.nsx * SK_WARPS;
-    // tensor memory: lane quarter warp % 4; column block (warp / 4, row parity)
-    const uint32_t tm = tmem_base + (((warp & 3u) * 32u) << 16) + (warp >> 2) * (2u * Q * 4u);
+  // consecutive warps take consecutive columns of one range
+  const uint32_t wid = blockIdx.x * SK_WARPS + warp;
+  const uint32_t ry = wid / p.ncol, col = wid - ry * p.ncol;
+  if (ry < p.nry) {
+    const int ya = (int)(p.y_begin + ry * p.rows_per_range);
+    const int yb = (int)min(p.y_end, (uint32_t)ya + p.rows_per_range);
+    const int n_k = yb - ya + 1;   // ring entries: rows ya-1 .. yb-1
+    const int qw = (int)(col * SK_BOX + 4u * lane), wmax = (int)p.canvas_w * BPW;
+    const bool guard = (int)(col * SK_BOX) + SK_BOX > wmax;
+    const uint32_t total = p.ncol;
+    // tensor memory: lane quarter warp % 4, column block warp / 4, one 4-word row per ring entry mod TROWS
+    const uint32_t tm = tmem_base + (((warp & 3u) * 32u) << 16) + (warp >> 2) * (SK_TROWS * 4u);
     uint32_t lmask[5];
 #pragma unroll
     for (int f = 0; f < 5; f++) {
       lmask[f] = lane == (uint32_t)f ? 0xffffffffu : 0u;
       asm volatile("" : "+r"(lmask[f]));
     }
-    auto slot_row = [&](int k) { return smem + ((uint32_t)k % SK_NSLOT) * G::SLOT_BYTES + SK_LEAD; };
-    auto wait_full = [&](int k) { mbar_wait(bar_full + 8u * ((uint32_t)k % SK_NSLOT), ((uint32_t)k / SK_NSLOT) & 1u); };
-    auto poll = [&](int r) {
+    {  // the cursors start at the columns' first intervals
+      IvCursor c;
+      iv_open(p, c, col);
+      cur_save(ws.cur, c);
+      if (lane == 0u && col > 0u) { iv_open(p, c, col - 1u); cur_save(ws.cur + 48u, c); }
+      __syncwarp();
+    }
+    auto row_addr = [&](int k) { return ws.rows + ((uint32_t)k & (SK_RING - 1)) * (SK_BOX * 4) + 16u * lane; };
+    auto halo_addr = [&](int k) { return ws.halo + ((uint32_t)k & (SK_RING - 1)) * 8u; };
+    auto tm_row = [&](int k) { return tm + ((uint32_t)k & (SK_TROWS - 1)) * 4u; };
+    auto wait_stage = [&](int j) { mbar_wait(ws.bar + 8u * ((uint32_t)j & (SK_NST - 1)), ((uint32_t)j / SK_NST) & 1u); };
+    // lane 8 r + f reads word f of the sums of ring entry k0 + r
+    auto poll = [&](int k0) {
       unsigned long long w = 0ull;
-      if (lane < 5u) asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(w) : "l"(p.rowsum + (size_t)(r - (int)p.y_begin) * 8 + lane) : "memory");
+      const int k = k0 + (int)(lane >> 3);
+      if ((lane & 7u) < 5u && k >= 1 && k < n_k)
+        asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(w) : "l"(p.rowsum + (size_t)(ya - 1 + k - (int)p.y_begin) * 8 + (lane & 7u)) : "memory");
       return w;
     };
-    // one step of the pipeline for ring entry k (row y = ya-1+k), k >= 1
-    auto step = [&](int k, const RowCarry<Q> &ab, RowCarry<Q> &cu) {
-      const int y = ya - 1 + k;
-      if (k + 1 < n_k) strip_compose_share<BPW, Q>(p, smem, tid, sx, ya, k + 1);
-      unsigned long long pre = 0ull;
-      if (k >= 2) pre = poll(y - 1);
-      wait_full(k);
-      strip_sweep<BPW, Q>(p, ab, cu, slot_row(k), tid, xw0, wmax, guard, tm + (uint32_t)(k & 1) * (Q * 4u), y, lmask);
-      if (k >= 2) {
-        const uint32_t ft = strip_winner(p, y - 1, lane, total, pre);
-        strip_emit<BPW, Q>(p, ft, y - 1, slot_row(k - 1), slot_row(k - 2), tm + (uint32_t)((k - 1) & 1) * (Q * 4u), tid, sx, xw0, wmax);
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // our reads of the slot, then the producer's bulk writes
-        __syncwarp();
-        if (lane == 0u) mbar_arrive(bar_empty + 8u * ((uint32_t)(k - 2) % SK_NSLOT));
+    auto sweep = [&](int k, const RowCarry &ab, RowCarry &cu) {
+      strip_sweep<BPW>(p, ab, cu, row_addr(k), halo_addr(k), lane, qw, wmax, guard, tm_row(k), ya - 1 + k, lmask);
+    };
+    auto emit_group = [&](int g, unsigned long long pre) {   // ring entries 4g .. 4g+3
+      const int k0 = g * SK_SROWS;
+      const uint32_t ftpack = strip_winners(p, ya - 1 + k0, k0, n_k, lane, total, pre);
+#pragma unroll
+      for (int r = 0; r < SK_SROWS; r++) {
+        const int k = k0 + r;
+        if (k >= 1 && k < n_k)
+          strip_emit<BPW>(p, (ftpack >> (3 * r)) & 7u, ya - 1 + k, row_addr(k), row_addr(k - 1), halo_addr(k), tm_row(k), lane, col, qw, wmax);
       }
     };
-    strip_compose_share<BPW, Q>(p, smem, tid, sx, ya, 0);
-    strip_compose_share<BPW, Q>(p, smem, tid, sx, ya, 1);
-    RowCarry<Q> ca, cb;
-    wait_full(0);
-    carry_init<BPW, Q>(ca, slot_row(0), tid);
-    int k = 1;
-    for (; k + 1 < n_k; k += 2) {
-      step(k, ca, cb);
-      step(k + 1, cb, ca);
+    for (int j = 0; j < SK_NST - 1; j++) issue_stage<BPW>(p, ws, lane, col, ya, n_k, j);   // stages 0, 1, 2
+    RowCarry ca, cb;
+    wait_stage(0);
+    {
+      ca.raw = lds128(row_addr(0));
+      ca.hb[0] = unpack_h4(ca.raw.x); ca.hb[1] = unpack_h4(ca.raw.y); ca.hb[2] = unpack_h4(ca.raw.z); ca.hb[3] = unpack_h4(ca.raw.w);
+      uint32_t c0, c1;
+      left_words<BPW>(ca.raw, halo_addr(0), lane, c0, c1);
+      ca.hl[0] = unpack_h4(c0); ca.hl[1] = unpack_h4(c1);
     }
-    if (k < n_k) { step(k, ca, cb); k++; }
-    {  // the last row
-      const int y = ya - 1 + (n_k - 1);
-      const uint32_t ft = strip_winner(p, y, lane, total, poll(y));
-      strip_emit<BPW, Q>(p, ft, y, slot_row(n_k - 1), slot_row(n_k - 2), tm + (uint32_t)((n_k - 1) & 1) * (Q * 4u), tid, sx, xw0, wmax);
+    // Group g = ring entries 4g .. 4g+3.  Per iteration: sweep group g, emit group g-1 (its sums have had a group's
+    // time to complete), then refill the stage of group g-2 -- nothing reads it any more -- with group g+2.
+    const int n_g = (n_k + SK_SROWS - 1) / SK_SROWS;
+    for (int g = 0; g < n_g; g++) {
+      const int k0 = g * SK_SROWS;
+      if (g > 0) wait_stage(g);
+      unsigned long long pre = 0ull;
+      if (k0 + 3 < n_k) {   // a whole group: straight-line
+        if (g > 0) sweep(k0, ca, cb); else cb = ca;
+        sweep(k0 + 1, cb, ca);
+        sweep(k0 + 2, ca, cb);
+        if (g > 0) pre = poll(k0 - SK_SROWS);   // read late (the others have had three rows' time), used after one more row
+        sweep(k0 + 3, cb, ca);
+      } else {
+        for (int k = k0 > 0 ? k0 : 1; k < n_k; k++) { sweep(k, ca, cb); ca = cb; }
+        if (g > 0) pre = poll(k0 - SK_SROWS);
+      }
+      if (g > 0) emit_group(g - 1, pre);
+      if (g > 0) issue_stage<BPW>(p, ws, lane, col, ya, n_k, g + 2);
     }
+    emit_group(n_g - 1, poll((n_g - 1) * SK_SROWS));
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   if (warp == 0u) {
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(G::TMEM_COLS) : "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(SK_TMEM_COLS) : "memory");
   }
 }
 
-template <int BPW, int Q>
+template <int BPW>
 static cudaError_t launch_strip_t(StripParams &p, int sm_count, cudaStream_t st) {
-  using G = SKGeo<Q>;
   const uint32_t row_words = p.canvas_w * BPW, n_rows = p.y_end - p.y_begin;
-  p.nsx = (row_words + G::SW - 1) / G::SW;
-  cudaError_t e = cudaFuncSetAttribute(strip_kernel<BPW, Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM);   // per device: set at every launch
+  const int smem_bytes = SK_SMEM + SK_WARPS * 96;
+  p.ncol = (row_words + SK_BOX - 1) / SK_BOX;
+  p.nsx = p.ncol;
+  cudaError_t e = cudaFuncSetAttribute(strip_kernel<BPW>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);   // per device: at every launch
   if (e != cudaSuccess) return e;
   int occ = 0;
-  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, strip_kernel<BPW, Q>, SK_THREADS, G::SMEM);
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, strip_kernel<BPW>, SK_THREADS, smem_bytes);
   if (e != cudaSuccess) return e;
   if (occ < 1) return cudaErrorLaunchOutOfResources;
-  const uint32_t resident = (uint32_t)sm_count;   // one CTA per SM: a CTA owns its SM's tensor-memory columns
-  if (p.nsx > resident) return cudaErrorInvalidConfiguration;
-  uint32_t nry = resident / p.nsx;
+  const uint32_t resident = (uint32_t)sm_count * SK_WARPS;   // one CTA per SM (it owns the SM's tensor-memory columns)
+  if (p.ncol > resident) return cudaErrorInvalidConfiguration;
+  uint32_t nry = resident / p.ncol;
   if (nry > n_rows) nry = n_rows;
   p.rows_per_range = (n_rows + nry - 1) / nry;
   p.nry = (n_rows + p.rows_per_range - 1) / p.rows_per_range;   // no empty range
+  const uint32_t ctas = (p.ncol * p.nry + SK_WARPS - 1) / SK_WARPS;
   void *args[] = {&p};
-  return cudaLaunchCooperativeKernel((const void *)strip_kernel<BPW, Q>, dim3(p.nsx * p.nry), dim3(SK_THREADS), args, G::SMEM, st);
+  return cudaLaunchCooperativeKernel((const void *)strip_kernel<BPW>, dim3(ctas), dim3(SK_THREADS), args, (size_t)smem_bytes, st);
 }
 
 cudaError_t launch_strip(StripParams p, bool out16, int q, int device, int sm_count, cudaStream_t st) {
-  (void)device;
+  (void)device; (void)q;
   const uint32_t row_words = p.canvas_w * (out16 ? 2u : 1u);
   if (p.y_end <= p.y_begin || row_words == 0u) return cudaSuccess;
   if ((size_t)row_words * 4 >= ((size_t)1 << 22)) return cudaErrorInvalidConfiguration;   // cost sums must stay below 2^29
-  if (q == 0) {   // wide rows: two quads per thread (half the strips, half the per-row overhead per quad)
-    const uint32_t s1 = (row_words + 2047u) / 2048u, s2 = (row_words + 4095u) / 4096u;
-    q = (s2 >= 2u && s2 * 2u <= s1 + (s1 + 9u) / 10u) ? 2 : 1;
-  }
-  if (out16) return q == 2 ? launch_strip_t<2, 2>(p, sm_count, st) : launch_strip_t<2, 1>(p, sm_count, st);
-  return q == 2 ? launch_strip_t<1, 2>(p, sm_count, st) : launch_strip_t<1, 1>(p, sm_count, st);
+  return out16 ? launch_strip_t<2>(p, sm_count, st) : launch_strip_t<1>(p, sm_count, st);
 }
 
 }  // namespace stitch

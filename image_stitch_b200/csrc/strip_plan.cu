@@ -30,14 +30,14 @@ static EncodeTiledFn encode_tiled_fn() {
   return fn;
 }
 
-// Rows of 32-bit words, box 256 words x 1 row; elements outside the tile read as zero.
-static bool encode_tile_map(const DevTile &t, uint32_t words_per_row, uint32_t rows, CUtensorMap *out) {
+// Rows of 32-bit words, box of one column (128 words) x box_rows rows; elements outside the tile read as zero.
+static bool encode_tile_map(const DevTile &t, uint32_t words_per_row, uint32_t rows, uint32_t box_rows, CUtensorMap *out) {
   EncodeTiledFn fn = encode_tiled_fn();
   if (!fn) return false;
   if ((reinterpret_cast<uintptr_t>(t.pix) & 15u) || (t.pitch & 15u) || !words_per_row || !rows) return false;
   const cuuint64_t dims[2] = {words_per_row, rows};
   const cuuint64_t strides[1] = {t.pitch};
-  const cuuint32_t box[2] = {strip_box_words(), 1};
+  const cuuint32_t box[2] = {strip_box_words(), box_rows};
   const cuuint32_t estr[2] = {1, 1};
   return fn(out, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, const_cast<uint8_t *>(t.pix), dims, strides, box, estr,
             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -64,11 +64,13 @@ int stitch_build_strip_plan(stitch_job *job, const std::vector<DevTile> &dt, con
   const uint32_t native = jd.out_bit_depth == 16 ? (uint32_t)FMT_RGBA16 : (uint32_t)FMT_RGBA8;
   job->strip_ok = false;
 
-  std::vector<CUtensorMap> maps(std::max<size_t>(dt.size(), 1));
+  std::vector<CUtensorMap> maps(std::max<size_t>(2 * dt.size(), 1));   // per tile: box of 1 row, box of 4 rows
   std::vector<uint8_t> direct_ok(dt.size(), 0);
   for (size_t k = 0; k < dt.size(); k++) {
-    memset(&maps[k], 0, sizeof(CUtensorMap));
-    direct_ok[k] = dt[k].fmt == native && src_words[k] >= strip_box_words() && encode_tile_map(dt[k], src_words[k], src_rows[k], &maps[k]);
+    memset(&maps[2 * k], 0, 2 * sizeof(CUtensorMap));
+    direct_ok[k] = dt[k].fmt == native && src_words[k] >= strip_box_words() &&
+                   encode_tile_map(dt[k], src_words[k], src_rows[k], 1, &maps[2 * k]) &&
+                   encode_tile_map(dt[k], src_words[k], src_rows[k], 4, &maps[2 * k + 1]);
   }
 
   std::vector<std::vector<uint32_t>> col_tiles(ncol);

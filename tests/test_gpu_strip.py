@@ -1,4 +1,4 @@
-"""Row-pipelined composite+filter kernel (csrc/strip.cu) against the oracle, bit-exact, on canvases wide enough
+"""The composite+filter kernels (csrc/fused.cu and the row-pipelined csrc/strip.cu) against the oracle, bit-exact, on canvases wide enough
 for several column strips and TMA boxes: direct tile boxes at arbitrary pixel offsets, background boxes,
 composited boxes (tile edges, blending, foreign formats), the pixel handed across a strip seam, overlays whose
 edges sit on 8-row / 128-pixel boundaries (the unit kernel took its predictor row from the wrong
@@ -11,6 +11,17 @@ import oracle_py as orc
 from image_stitch_b200 import _native, synth
 
 pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(params=["unit", "strip"], autouse=True)
+def kernel(request, monkeypatch):
+    """Every case runs through both composite+filter kernels: the default unit kernel (csrc/fused.cu) and the
+    row-pipelined one (csrc/strip.cu, STITCH_STRIP=1; the library reads the variable at every call)."""
+    if request.param == "strip":
+        monkeypatch.setenv("STITCH_STRIP", "1")
+    else:
+        monkeypatch.delenv("STITCH_STRIP", raising=False)
+    return request.param
 
 
 def _tile(rng, w, h, alpha, x, y, z, idx, canvas_w, canvas_h, bit_depth=8, color_type=6):
