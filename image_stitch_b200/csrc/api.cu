@@ -866,17 +866,9 @@ static int finalize_job(stitch_job *job) {
     }
     job->busy_bins[by + 1] = job->busy_bins[by] + busy;
   }
-  dev_free(ctx, job->d_tiles); dev_free(ctx, job->d_bin_start); dev_free(ctx, job->d_bin_tiles);
-  job->d_tiles = nullptr; job->d_bin_start = nullptr; job->d_bin_tiles = nullptr;
   int rc;
-  if ((rc = dev_alloc(ctx, (void **)&job->d_tiles, dt.size() * sizeof(DevTile)))) return rc;
-  if ((rc = dev_alloc(ctx, (void **)&job->d_bin_start, start.size() * sizeof(uint32_t)))) return rc;
-  if ((rc = dev_alloc(ctx, (void **)&job->d_bin_tiles, list.size() * sizeof(uint32_t)))) return rc;
-  static_assert(sizeof(DevTile) % 4 == 0, "tables are copied word by word");
-  if ((rc = stitch_upload_small(ctx, job->d_tiles, dt.data(), dt.size() * sizeof(DevTile)))) return rc;
-  if ((rc = stitch_upload_small(ctx, job->d_bin_start, start.data(), start.size() * sizeof(uint32_t)))) return rc;
-  if ((rc = stitch_upload_small(ctx, job->d_bin_tiles, list.data(), list.size() * sizeof(uint32_t)))) return rc;
   if (jd.out_kind == STITCH_OUT_PNG_FILTERED || jd.out_kind == STITCH_OUT_PNG_DEFLATE) {
+    // tensor maps of the tiles (dt[k].pad <- valid) and the interval plan of strip.cu, ahead of the tile table's upload
     std::vector<uint32_t> src_words(order.size()), src_rows(order.size());
     for (size_t k = 0; k < order.size(); k++) {
       src_words[k] = job->tiles[order[k]].d.width * (job->bpp / 4);
@@ -884,6 +876,15 @@ static int finalize_job(stitch_job *job) {
     }
     if ((rc = stitch_build_strip_plan(job, dt, src_words, src_rows))) return rc;
   }
+  dev_free(ctx, job->d_tiles); dev_free(ctx, job->d_bin_start); dev_free(ctx, job->d_bin_tiles);
+  job->d_tiles = nullptr; job->d_bin_start = nullptr; job->d_bin_tiles = nullptr;
+  if ((rc = dev_alloc(ctx, (void **)&job->d_tiles, dt.size() * sizeof(DevTile)))) return rc;
+  if ((rc = dev_alloc(ctx, (void **)&job->d_bin_start, start.size() * sizeof(uint32_t)))) return rc;
+  if ((rc = dev_alloc(ctx, (void **)&job->d_bin_tiles, list.size() * sizeof(uint32_t)))) return rc;
+  static_assert(sizeof(DevTile) % 4 == 0, "tables are copied word by word");
+  if ((rc = stitch_upload_small(ctx, job->d_tiles, dt.data(), dt.size() * sizeof(DevTile)))) return rc;
+  if ((rc = stitch_upload_small(ctx, job->d_bin_start, start.data(), start.size() * sizeof(uint32_t)))) return rc;
+  if ((rc = stitch_upload_small(ctx, job->d_bin_tiles, list.data(), list.size() * sizeof(uint32_t)))) return rc;
   // the host vectors are pageable: the async copies above have already staged them
   CK(cudaStreamSynchronize(ctx->stream));
   job->finalized = true;
@@ -966,6 +967,7 @@ static int render_rows(stitch_job *job, uint32_t a, uint32_t b, uint8_t *d_rows,
     bg_words(jd, fp.bg_lo, fp.bg_hi);
     fp.rowsum = reinterpret_cast<unsigned long long *>(job->d_sync); fp.ticket = job->d_sync + (size_t)n_rows * 16;
     fp.out = d_rows; fp.out_pitch = job->out_pitch; fp.lead = (uint32_t)job->out_lead;
+    fp.maps = job->strip_ok ? job->d_maps : nullptr;
     // STITCH_STRIP=1 selects the row-pipelined kernel (strip.cu: parity-green, slower than the unit kernel on
     // B200 -- DESIGN.md section 3d); read at every call so that tests can run both in one process
     const char *strip_env = getenv("STITCH_STRIP");
@@ -998,17 +1000,19 @@ static int render_rows(stitch_job *job, uint32_t a, uint32_t b, uint8_t *d_rows,
       const uint32_t ys = a ? a - 1 : 0;
       job->canvas_pitch = pitch16;
       if ((rc = ensure_buffer(ctx, &job->d_canvas, &job->canvas_bytes, pitch16 * (size_t)(b - ys)))) return rc;
-      if ((rc = ensure_buffer(ctx, &job->d_ctab, &job->ctab_bytes, 256))) return rc;
+      if ((rc = ensure_buffer(ctx, &job->d_ctab, &job->ctab_bytes, 1024))) return rc;
       CK(launch_compose_canvas(fp, jd.out_bit_depth == 16, job->d_canvas, pitch16, ys, b, ctx->stream));
-      struct { DevTile t; uint32_t pad[4]; uint32_t bin_start[2]; uint32_t bin_tiles[2]; } tab;
+      struct { uint8_t maps[384]; DevTile t; uint32_t pad[4]; uint32_t bin_start[2]; uint32_t bin_tiles[2]; } tab;   // maps first: 128-byte aligned
       memset(&tab, 0, sizeof tab);
       tab.t.pix = job->d_canvas; tab.t.pitch = (uint32_t)pitch16; tab.t.fmt = native_fmt(jd.out_bit_depth);
       tab.t.x0 = 0; tab.t.y0 = (int32_t)ys; tab.t.x1 = (int32_t)jd.canvas_w; tab.t.y1 = (int32_t)b;
       tab.t.opaque = 1;
+      tab.t.pad = stitch_encode_tile_maps(tab.t, (uint32_t)(pitch16 / 4), b - ys, tab.maps) ? 1u : 0u;   // the canvas as a TMA source
       tab.bin_start[1] = 1;
       static_assert(sizeof tab % 4 == 0, "tables are copied word by word");
       if ((rc = stitch_upload_small(ctx, job->d_ctab, &tab, sizeof tab))) return rc;  // staged on return
-      fp.tiles = reinterpret_cast<const DevTile *>(job->d_ctab);
+      fp.tiles = reinterpret_cast<const DevTile *>(job->d_ctab + offsetof(decltype(tab), t));
+      fp.maps = job->d_ctab;
       fp.bin_start = reinterpret_cast<const uint32_t *>(job->d_ctab + offsetof(decltype(tab), bin_start));
       fp.bin_tiles = reinterpret_cast<const uint32_t *>(job->d_ctab + offsetof(decltype(tab), bin_tiles));
       fp.single_bin = 1; fp.alpha_blend = 0;

@@ -35,7 +35,7 @@ struct DevTile {
   int32_t x1, y1;      // exclusive bottom-right on the canvas
   int32_t sx0, sy0;    // source pixel that lands on (x0,y0): sourceOffsetX/Y
   uint32_t opaque;     // 1: every pixel has alpha == max (no alpha channel, or verified by decode)
-  uint32_t pad;
+  uint32_t pad;        // 1: the tile has valid TMA tensor maps (strip_plan.cu), 0: none
 };
 
 // One dependency chain for kernel (a): a non-interlaced image or one Adam7 pass.

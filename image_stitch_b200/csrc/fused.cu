@@ -29,6 +29,7 @@
 #include "common.cuh"
 #include "kernels.h"
 #include "filter_math.cuh"
+#include "async_copy.cuh"
 
 namespace stitch {
 
@@ -40,9 +41,9 @@ static constexpr int FU_SW = 128;                    // words per unit row
 static constexpr int FU_WARPS = 20;                  // workers per CTA (one CTA per SM)
 static constexpr int FU_RAW_WORDS = (FU_R + 1) * FU_SW;  // row 0 = predictor row above the unit
 static constexpr int FU_LC_WORDS = ((FU_R + 1) * 2 + 3) / 4 * 4;  // two words left of every row
-static constexpr int FU_WARP_WORDS = FU_RAW_WORDS + FU_LC_WORDS;
+static constexpr int FU_WARP_WORDS = (FU_RAW_WORDS + FU_LC_WORDS + 31) / 32 * 32;  // stashes start on 128-byte boundaries (TMA destinations)
 static constexpr int FU_SLOTS = 2;                   // stashes per warp
-static constexpr size_t FU_CTA_SMEM = (size_t)FU_WARPS * FU_SLOTS * FU_WARP_WORDS * 4 + 16;  // + TMEM base address
+static constexpr size_t FU_CTA_SMEM = (size_t)FU_WARPS * FU_SLOTS * FU_WARP_WORDS * 4 + 16 + FU_WARPS * FU_SLOTS * 8;  // + TMEM base address + one mbarrier per stash
 // The Paeth residuals of a unit (FU_R rows x 16 bytes per lane) wait for the row winners in TENSOR MEMORY:
 // lane l of warp w owns TMEM lane 32 (w % 4) + l (a warp reaches only that quarter), warps w / 4 = 0..3 use
 // disjoint column ranges, one unit takes FU_R * 4 columns.  This is plain scratch use of
@@ -119,6 +120,9 @@ struct UnitPlan {
   const uint8_t *fast_src;  // tile byte that lands on (X0, ya) when the unit is a plain window of one tile
   uint32_t fast_pitch;
   bool halo_fast, left_fast;
+  bool tma_ok;              // the covering tile has tensor maps
+  uint32_t tile;            // the covering tile (index into tiles / maps)
+  int32_t c0, c1;           // TMA coordinates of the predictor row's first word: word in the source row, source row
 };
 
 // Rows and columns of unit u (pure arithmetic).
@@ -143,7 +147,7 @@ __device__ __forceinline__ UnitPlan unit_plan(const FusedParams &p, const uint32
   const uint32_t *list = p.bin_tiles + b0;
   pl.list = list; pl.n_list = n_list;
   const int X0 = xw0 / BPW, X1 = min((int)p.canvas_w, (xw0 + FU_SW) / BPW);  // unit's pixel columns
-  pl.fast_src = nullptr; pl.fast_pitch = 0; pl.halo_fast = false; pl.left_fast = false;
+  pl.fast_src = nullptr; pl.fast_pitch = 0; pl.halo_fast = false; pl.left_fast = false; pl.tma_ok = false; pl.tile = 0; pl.c0 = 0; pl.c1 = 0;
   for (int k = (int)n_list - 1; k >= 0; k--) {
     const DevTile &t = p.tiles[__ldg(list + k)];
     const int tx0 = t.x0, ty0 = t.y0, tx1 = t.x1, ty1 = t.y1;
@@ -157,6 +161,9 @@ __device__ __forceinline__ UnitPlan unit_plan(const FusedParams &p, const uint32
       const uint8_t *src = t.pix + (size_t)(ya - ty0 + t.sy0) * pitch + (size_t)(X0 - tx0 + t.sx0) * (4u * BPW);
       if (((reinterpret_cast<uintptr_t>(src) | pitch) & 15u) == 0) {
         pl.fast_src = src; pl.fast_pitch = pitch;
+        pl.tile = __ldg(list + k);
+        pl.tma_ok = t.pad != 0u && p.maps != nullptr;
+        pl.c0 = (X0 - tx0 + t.sx0) * BPW; pl.c1 = ya - 1 - ty0 + t.sy0;
         pl.halo_fast = ty0 <= ya - 1;
         pl.left_fast = tx0 <= X0 - 1;
         // The predictor row ya-1 and the pixel column X0-1 lie outside the unit: a tile ABOVE this one in z order
@@ -182,9 +189,9 @@ struct __align__(16) PlanRec {
   const uint8_t *fast_src;
   uint32_t fast_pitch;
   uint32_t list_off;   // into bin_tiles
-  uint32_t n_list;
-  uint32_t flags;      // bit 0 halo_fast, bit 1 left_fast
-  uint32_t pad[2];
+  uint32_t n_flags;    // n_list << 3 | bit 0 halo_fast | bit 1 left_fast | bit 2 tma_ok
+  uint32_t tile;
+  int32_t c0, c1;      // see UnitPlan
 };
 static_assert(sizeof(PlanRec) == 32, "two 16-byte loads per record");
 
@@ -195,9 +202,9 @@ __global__ void fused_plan_kernel(const FusedParams p, PlanRec *recs, const uint
   const UnitPlan pl = unit_plan<BPW>(p, u);
   PlanRec r;
   r.fast_src = pl.fast_src; r.fast_pitch = pl.fast_pitch;
-  r.list_off = (uint32_t)(pl.list - p.bin_tiles); r.n_list = pl.n_list;
-  r.flags = (pl.halo_fast ? 1u : 0u) | (pl.left_fast ? 2u : 0u);
-  r.pad[0] = r.pad[1] = 0u;
+  r.list_off = (uint32_t)(pl.list - p.bin_tiles);
+  r.n_flags = (pl.n_list << 3) | (pl.halo_fast ? 1u : 0u) | (pl.left_fast ? 2u : 0u) | (pl.tma_ok ? 4u : 0u);
+  r.tile = pl.tile; r.c0 = pl.c0; r.c1 = pl.c1;
   recs[u] = r;
 }
 
@@ -214,21 +221,35 @@ __device__ __forceinline__ UnitPlan plan_make(const FusedParams &p, const uint32
   pl.fast_src = reinterpret_cast<const uint8_t *>(((unsigned long long)r.a.y << 32) | r.a.x);
   pl.fast_pitch = r.a.z;
   pl.list = p.bin_tiles + r.a.w;
-  pl.n_list = r.b.x;
-  pl.halo_fast = (r.b.y & 1u) != 0u;
-  pl.left_fast = (r.b.y & 2u) != 0u;
+  pl.n_list = r.b.x >> 3;
+  pl.tma_ok = (r.b.x & 4u) != 0u;
+  pl.halo_fast = (r.b.x & 1u) != 0u;
+  pl.left_fast = (r.b.x & 2u) != 0u;
+  pl.tile = r.b.y; pl.c0 = (int32_t)r.b.z; pl.c1 = (int32_t)r.b.w;
   return pl;
 }
 
 // ---- phase A: raw stash <- composited pixels of rows ya-1 .. yb-1 (cp.async left in flight) ----
 template <int BPW>
-__device__ __forceinline__ void unit_load(const FusedParams &p, const UnitPlan &pl, uint32_t *stash, const uint32_t lane) {
+__device__ __forceinline__ bool unit_load(const FusedParams &p, const UnitPlan &pl, uint32_t *stash, const uint32_t bar,
+                                          const uint32_t lane) {
   uint32_t *raw = stash, *lcs = stash + FU_RAW_WORDS;
   const int wmax = (int)p.canvas_w * BPW;  // words per canvas row
   const int ya = pl.ya, nrows = pl.nrows, xw0 = pl.xw0, qw = xw0 + 4 * (int)lane;
   const uint8_t *fast_src = pl.fast_src;
   const uint32_t fast_pitch = pl.fast_pitch;
-  {
+  // A plain window of one tile, predictor row included: ONE 2-D TMA box (128 words x 9 rows) from the tile's tensor
+  // map, issued by lane 0, completing on the stash's mbarrier.  (Rows past the unit and words past the canvas or
+  // the tile are loaded or zero-filled and never used.)
+  const bool tma = pl.tma_ok && pl.halo_fast && ya > 0;
+  if (tma) {
+    if (lane == 0u) {
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the emit's reads of this stash, then the bulk write
+      mbar_arrive_tx(bar, (FU_R + 1) * FU_SW * 4);
+      tma_box_2d((uint32_t)__cvta_generic_to_shared(raw), reinterpret_cast<const uint8_t *>(p.maps) + (size_t)pl.tile * 384u + 256u,
+                 pl.c0, pl.c1, bar);
+    }
+  } else {
     uint32_t *dst = raw + 4 * lane;
     const bool inside = qw < wmax;
     // predictor row
@@ -264,17 +285,20 @@ __device__ __forceinline__ void unit_load(const FusedParams &p, const UnitPlan &
     lcs[lane * 2 + 1] = c1;
   }
   asm volatile("cp.async.commit_group;" ::: "memory");
+  return tma;
 }
 
 // ---- sweep: filter costs of every row, Paeth residuals into the stash, partial sums published ----
 template <int BPW>
 __device__ __forceinline__ void unit_sweep(const FusedParams &p, const UnitPlan &pl, uint32_t *stash, const uint32_t pf_taddr,
-                                           const uint32_t lane, const uint32_t (&lmask)[5]) {
+                                           const uint32_t lane, const uint32_t (&lmask)[5], const bool tma, const uint32_t bar,
+                                           const uint32_t parity) {
   uint32_t *raw = stash, *lcs = stash + FU_RAW_WORDS;
   const int wmax = (int)p.canvas_w * BPW;
   const int nrows = pl.nrows, qw = pl.xw0 + 4 * (int)lane;
   const bool guard = pl.xw0 + FU_SW > wmax;
   asm volatile("cp.async.wait_group 0;" ::: "memory");
+  if (tma) mbar_wait(bar, parity);
   __syncwarp();
   uint4 up = *reinterpret_cast<const uint4 *>(raw + 4 * lane);
   uint32_t l0 = __shfl_up_sync(0xffffffffu, up.z, 1), l1 = __shfl_up_sync(0xffffffffu, up.w, 1);
@@ -410,6 +434,14 @@ __global__ void __launch_bounds__(FU_WARPS * 32, 1) fused_kernel(const FusedPara
   uint32_t *cur_stash = fu_smem + warp * (FU_SLOTS * FU_WARP_WORDS), *prev_stash = cur_stash + FU_WARP_WORDS;
   // tensor memory for the residual stash: warp 0 allocates for the CTA, every warp uses its own lane quarter
   uint32_t *tmem_slot = fu_smem + FU_WARPS * FU_SLOTS * FU_WARP_WORDS;
+  // one mbarrier per stash: the unit's TMA box completes on it
+  uint32_t cur_bar = (uint32_t)__cvta_generic_to_shared(tmem_slot) + 16u + warp * (FU_SLOTS * 8u), prev_bar = cur_bar + 8u;
+  uint32_t cur_par = 0u, prev_par = 0u;
+  if (lane == 0u) {
+    mbar_init(cur_bar, 1u); mbar_init(prev_bar, 1u);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
   if (warp == 0u) {
     const uint32_t sa = (uint32_t)__cvta_generic_to_shared(tmem_slot);
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(sa), "n"(FU_TMEM_COLS) : "memory");
@@ -434,12 +466,13 @@ __global__ void __launch_bounds__(FU_WARPS * 32, 1) fused_kernel(const FusedPara
   uint32_t u = blockIdx.x * FU_WARPS + warp;  // first unit: the warp's own index; tickets continue from n_warps
   if (u < n_units) {
     UnitPlan plan = plan_make(p, u, plan_fetch(p, u));
-    unit_load<BPW>(p, plan, cur_stash, lane);
+    bool cur_tma = unit_load<BPW>(p, plan, cur_stash, cur_bar, lane);
     UnitRef prev;
     prev.seg = 0; prev.ya = 0; prev.nrows = 0;
     bool have_prev = false;
     for (;;) {
-      unit_sweep<BPW>(p, plan, cur_stash, cur_pf, lane, lmask);
+      unit_sweep<BPW>(p, plan, cur_stash, cur_pf, lane, lmask, cur_tma, cur_bar, cur_par);
+      if (cur_tma) cur_par ^= 1u;
       uint32_t ft = 0u;
       if (have_prev) ft = unit_wait(p, prev, lane);
       const uint32_t ftpack = pack_winners(ft, lane);
@@ -457,9 +490,11 @@ __global__ void __launch_bounds__(FU_WARPS * 32, 1) fused_kernel(const FusedPara
       have_prev = true;
       { uint32_t *sw = cur_stash; cur_stash = prev_stash; prev_stash = sw; }
       { const uint32_t sw = cur_pf; cur_pf = prev_pf; prev_pf = sw; }
+      { const uint32_t sw = cur_bar; cur_bar = prev_bar; prev_bar = sw; }
+      { const uint32_t sw = cur_par; cur_par = prev_par; prev_par = sw; }
       if (!more) break;
       plan = plan_make(p, u, raw_next);
-      unit_load<BPW>(p, plan, cur_stash, lane);
+      cur_tma = unit_load<BPW>(p, plan, cur_stash, cur_bar, lane);
     }
     const uint32_t ft = unit_wait(p, prev, lane);
     unit_emit<BPW>(p, prev, prev_stash, prev_pf, lane, ft, pack_winners(ft, lane), 0, prev.nrows);

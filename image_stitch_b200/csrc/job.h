@@ -137,7 +137,8 @@ size_t stitch_deflate_bound(size_t raw_bytes);
 uint32_t stitch_crc_raw_concat(uint32_t ra, uint32_t rb, uint64_t len_b);
 uint32_t stitch_crc_finish(uint32_t raw, uint64_t n);
 // strip_plan.cu: interval plan + tensor maps for strip.cu; dt = the tiles back to front as uploaded to d_tiles
-int stitch_build_strip_plan(stitch_job *job, const std::vector<stitch::DevTile> &dt, const std::vector<uint32_t> &src_words,
+int stitch_build_strip_plan(stitch_job *job, std::vector<stitch::DevTile> &dt, const std::vector<uint32_t> &src_words,
                             const std::vector<uint32_t> &src_rows);
+bool stitch_encode_tile_maps(const stitch::DevTile &t, uint32_t words_per_row, uint32_t rows, void *out3);
 int stitch_jpeg_encode_band(stitch_job *job, uint32_t y0, uint32_t y1, const uint8_t *canvas, size_t canvas_pitch,
                             size_t *out_bytes, uint32_t *launches);

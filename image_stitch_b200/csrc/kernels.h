@@ -51,6 +51,7 @@ struct FusedParams {
   uint32_t *ticket;           // zeroed
   void *plans;                // fused_plan_bytes(n_bands * nseg) of scratch: per-unit plan records
   uint32_t single_bin;        // 1: bin_start/bin_tiles describe one bin that covers the whole canvas
+  const void *maps;           // per tile three 128-byte CUtensorMaps (boxes of 1, 4 and 9 rows of 128 words), or nullptr
   uint8_t *out;               // row r: filter byte at out + r*out_pitch + lead
   size_t out_pitch;
   uint32_t lead;
@@ -86,7 +87,7 @@ struct StripIv {
 enum StripKind : uint32_t { SK_BG = 0, SK_DIRECT = 1, SK_COMP = 2, SK_SHIFT = 3 };
 struct StripParams {
   const DevTile *tiles;
-  const void *maps;           // two 128-byte CUtensorMaps per tile (32-bit words): box 128 x 1 row, box 128 x 4 rows
+  const void *maps;           // three 128-byte CUtensorMaps per tile (32-bit words): boxes of 128 words x 1, 4, 9 rows
   const StripIv *ivs;
   const uint32_t *col_start;  // [ncol + 1]: intervals of box column c are ivs[col_start[c] .. col_start[c + 1])
   const uint32_t *lists;

@@ -26,6 +26,7 @@
 #include "common.cuh"
 #include "kernels.h"
 #include "filter_math.cuh"
+#include "async_copy.cuh"
 
 namespace stitch {
 
@@ -46,62 +47,6 @@ static_assert((SK_WARPS / 4) * SK_TROWS * 4 <= SK_TMEM_COLS && SK_WARPS % 4 == 0
 static_assert(SK_NST == 4 && SK_SROWS == 4, "the group schedule below: sweep g, emit g-1, refill the stage of g-2 with g+2");
 
 uint32_t strip_box_words() { return SK_BOX; }
-
-// ---- mbarrier / TMA / shared-memory primitives (shared::cta addresses as 32-bit) ------------------------------
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {   // no arrival: only more bytes to wait for
-  asm volatile("mbarrier.expect_tx.relaxed.cta.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-// arrives once all cp.async copies this thread has issued so far have landed (at once if there are none)
-__device__ __forceinline__ void mbar_arrive_after_cp_async(uint32_t bar) {
-  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void cp_async4(uint32_t dst, const void *src) {
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
-}
-__device__ __forceinline__ bool mbar_try(uint32_t bar, uint32_t parity) {
-  uint32_t ok;
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-      "selp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
-  return ok != 0u;
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  while (!mbar_try(bar, parity)) {}
-}
-__device__ __forceinline__ void tma_box_2d(uint32_t dst, const void *map, int c0, int c1, uint32_t bar) {
-  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-               ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar) : "memory");
-}
-__device__ __forceinline__ void bulk_copy(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-               ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
-}
-__device__ __forceinline__ uint4 lds128(uint32_t a) {
-  uint4 v;
-  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a) : "memory");
-  return v;
-}
-__device__ __forceinline__ uint32_t lds32(uint32_t a) {
-  uint32_t v;
-  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
-  return v;
-}
-__device__ __forceinline__ void sts128(uint32_t a, const uint4 v) {
-  asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
-}
-__device__ __forceinline__ void sts32(uint32_t a, uint32_t v) {
-  asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory");
-}
 
 // one out-of-line copy of the generic compositor per kernel (it carries the f64 blend); what it reads of the
 // kernel's parameters travels by value, so that the parameter block is not copied to the stack
@@ -242,7 +187,7 @@ __device__ __forceinline__ void issue_stage(const StripParams &p, const WarpSm w
     // the whole stage lies in one tile: one box of 128 words x 4 rows (rows past the range or the tile are never read)
     if (lane == 0u) {
       mbar_expect_tx(bar, SK_SROWS * SK_BOX * 4);
-      tma_box_2d(ws.rows + slot0 * (SK_BOX * 4), reinterpret_cast<const uint8_t *>(p.maps) + (size_t)bc.tile * 256u + 128u, bc.cw, y0 + bc.cy, bar);
+      tma_box_2d(ws.rows + slot0 * (SK_BOX * 4), reinterpret_cast<const uint8_t *>(p.maps) + (size_t)bc.tile * 384u + 128u, bc.cw, y0 + bc.cy, bar);
     }
   } else {
 #pragma unroll 1
@@ -257,7 +202,7 @@ __device__ __forceinline__ void issue_stage(const StripParams &p, const WarpSm w
       if (bc.kind == SK_DIRECT) {
         if (lane == 0u) {
           mbar_expect_tx(bar, SK_BOX * 4);
-          tma_box_2d(row, reinterpret_cast<const uint8_t *>(p.maps) + (size_t)bc.tile * 256u, bc.cw, y + bc.cy, bar);
+          tma_box_2d(row, reinterpret_cast<const uint8_t *>(p.maps) + (size_t)bc.tile * 384u, bc.cw, y + bc.cy, bar);
         }
       } else if (bc.kind == SK_BG) {
         if (lane == 0u) {

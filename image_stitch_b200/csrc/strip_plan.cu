@@ -44,6 +44,14 @@ static bool encode_tile_map(const DevTile &t, uint32_t words_per_row, uint32_t r
             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// Three maps (1, 4, 9 rows) for one tile into out[3]; false when the tile cannot be a TMA source.
+bool stitch_encode_tile_maps(const DevTile &t, uint32_t words_per_row, uint32_t rows, void *out) {
+  static_assert(sizeof(CUtensorMap) == 128, "one 128-byte descriptor");
+  CUtensorMap *m = static_cast<CUtensorMap *>(out);
+  return words_per_row >= strip_box_words() && encode_tile_map(t, words_per_row, rows, 1, m) &&
+         encode_tile_map(t, words_per_row, rows, 4, m + 1) && encode_tile_map(t, words_per_row, rows, 9, m + 2);
+}
+
 template <class T>
 static int upload_vec(stitch_ctx *ctx, const std::vector<T> &v, void **d_ptr) {
   stitch_dev_free(ctx, *d_ptr);
@@ -54,8 +62,9 @@ static int upload_vec(stitch_ctx *ctx, const std::vector<T> &v, void **d_ptr) {
   return v.empty() ? STITCH_OK : stitch_upload_small(ctx, *d_ptr, v.data(), v.size() * sizeof(T));
 }
 
-// dt: the job's tiles back to front (as uploaded to job->d_tiles); src_words/src_rows: each tile's full size.
-int stitch_build_strip_plan(stitch_job *job, const std::vector<DevTile> &dt, const std::vector<uint32_t> &src_words,
+// dt: the job's tiles back to front (uploaded to job->d_tiles AFTER this call: dt[k].pad receives "has valid tensor
+// maps"); src_words/src_rows: each tile's full size.
+int stitch_build_strip_plan(stitch_job *job, std::vector<DevTile> &dt, const std::vector<uint32_t> &src_words,
                             const std::vector<uint32_t> &src_rows) {
   stitch_ctx *ctx = job->ctx;
   const stitch_job_desc &jd = job->desc;
@@ -64,13 +73,15 @@ int stitch_build_strip_plan(stitch_job *job, const std::vector<DevTile> &dt, con
   const uint32_t native = jd.out_bit_depth == 16 ? (uint32_t)FMT_RGBA16 : (uint32_t)FMT_RGBA8;
   job->strip_ok = false;
 
-  std::vector<CUtensorMap> maps(std::max<size_t>(2 * dt.size(), 1));   // per tile: box of 1 row, box of 4 rows
+  std::vector<CUtensorMap> maps(std::max<size_t>(3 * dt.size(), 1));   // per tile: boxes of 1, 4 and 9 rows
   std::vector<uint8_t> direct_ok(dt.size(), 0);
   for (size_t k = 0; k < dt.size(); k++) {
-    memset(&maps[2 * k], 0, 2 * sizeof(CUtensorMap));
+    memset(&maps[3 * k], 0, 3 * sizeof(CUtensorMap));
     direct_ok[k] = dt[k].fmt == native && src_words[k] >= strip_box_words() &&
-                   encode_tile_map(dt[k], src_words[k], src_rows[k], 1, &maps[2 * k]) &&
-                   encode_tile_map(dt[k], src_words[k], src_rows[k], 4, &maps[2 * k + 1]);
+                   encode_tile_map(dt[k], src_words[k], src_rows[k], 1, &maps[3 * k]) &&
+                   encode_tile_map(dt[k], src_words[k], src_rows[k], 4, &maps[3 * k + 1]) &&
+                   encode_tile_map(dt[k], src_words[k], src_rows[k], 9, &maps[3 * k + 2]);
+    dt[k].pad = direct_ok[k];   // the kernels may use the tile's maps
   }
 
   std::vector<std::vector<uint32_t>> col_tiles(ncol);
