@@ -36,33 +36,59 @@ TILE = 1024
 GRID = 16
 CANVAS = TILE * GRID            # 16384
 N_DISTINCT = 8                  # distinct tile contents (re-used cyclically; every tile has its own device buffer)
+C3_CANVAS, C3_TILE, C3_SIDE = 32768, 2048, 16
 ALG_BYTES_PER_PX = 8.0          # fused composite+filter: read 4*coverage(=1) + write 4
 UNF_BYTES_PER_PX = 8.0          # unfilter: read 4 + write 4 per tile pixel
 
 
 WORKLOAD_CONFIG = {
-    "workload": "C2: 16x16 grid of 1024x1024 RGBA8 tiles (inflated filtered streams) -> 16384x16384 "
-                "filtered PNG scanlines per GPU; N GPUs = N row bands of one 16384x(16384*N) canvas",
+    "workload": "C2: 16x16 grid of 1024x1024 RGBA8 tiles (inflated filtered streams, a random PNG filter type per "
+                "tile row) -> 16384x16384 filtered PNG scanlines per GPU; N GPUs = N row bands of ONE 16384x(16384*N) "
+                "canvas (band k also uploads and unfilters the 16 tiles above it: its first row's predictor is their last row)",
     "l2": "inputs (1.07 GB) and outputs (1.07 GB) per step exceed the 126 MB L2; no flush needed",
-    "step": "unfilter(256 tiles) + composite + filter-select",
+    "step": "unfilter(256 tiles, + 16 halo tiles on ranks > 0) + composite + filter-select",
 }
 
 
-def profiled_traffic_bytes(summary="profiles/r1c_prof_fused.summary.csv"):
-    """dram__bytes_read.sum + dram__bytes_write.sum of the composite+filter kernel from the committed
-    `ncu --set full` capture of this same workload (one launch).  None when the summary is missing."""
-    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), summary)
-    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
-    got = {}
+def profiled_traffic_bytes(*summaries, scale: float = 1.0):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the profiled kernel(s) from committed `ncu --set full`
+    captures of this same workload (one launch each), times `scale`.  None when a summary is missing."""
+    summaries = summaries or ("profiles/r2_prof_fused.summary.csv",)
+    unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    total = 0.0
+    for summary in summaries:
+        path = os.path.join(os.path.dirname(os.path.abspath(__file__)), summary)
+        got = {}
+        try:
+            with open(path) as f:
+                for line in f:
+                    parts = line.strip().split(",")
+                    if len(parts) == 3 and parts[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum") and parts[0] not in got:
+                        got[parts[0]] = float(parts[2]) * unit.get(parts[1], 1.0)
+        except OSError:
+            return None
+        if len(got) != 2:
+            return None
+        total += sum(got.values())
+    return total * scale
+
+
+def e2e_floor(world: int, h2d_per_gpu: float, d2h_per_gpu: float, e2e_ms: float):
+    """What plain pinned copies achieve on this class of node with `world` GPUs copying both ways at once
+    (tools/bus_scaling.py, committed as profiles/r2_bus_scaling.jsonl: the node's host side delivers 50-65 GB/s
+    per direction in total, however many GPUs share it), and how close the e2e step comes to it."""
+    path = os.path.join(ROOT, "profiles", "r2_bus_scaling.jsonl")
     try:
-        with open(path) as f:
-            for line in f:
-                parts = line.strip().split(",")
-                if len(parts) == 3 and parts[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum") and parts[0] not in got:
-                    got[parts[0]] = float(parts[2]) * scale.get(parts[1], 1.0)
+        rows = [json.loads(l) for l in open(path) if l.strip()]
     except OSError:
         return None
-    return sum(got.values()) if len(got) == 2 else None
+    row = next((r for r in rows if r["n_gpus"] == world), None)
+    if row is None:
+        return None
+    rate = row["both"]["per_gpu_GBps_per_direction"] * 1e9
+    floor_ms = max(h2d_per_gpu, d2h_per_gpu) / rate * 1e3
+    return {"floor_ms_per_step": floor_ms, "e2e_over_floor": e2e_ms / floor_ms, "node_GBps_per_direction_both_ways": row["both"]["aggregate_GBps_per_direction"],
+            "source": "profiles/r2_bus_scaling.jsonl (plain cudaMemcpyAsync, 1 GiB per direction per GPU, all GPUs at once, slowest rank)"}
 
 
 def parse_args():
@@ -78,15 +104,41 @@ def parse_args():
     return ap.parse_args()
 
 
-def make_tiles(seed: int):
-    """N_DISTINCT synthetic tiles -> (raw pixels [h, w*4], inflated filtered stream)."""
+def make_tiles(seed: int, force: int = 5):
+    """N_DISTINCT synthetic tiles -> (raw pixels [h, w*4], inflated filtered stream).
+    force: the PNG filter type of the tile rows (synth.encode_filtered): 5 = a random type per row (the headline:
+    every unfilter path in one stream), 4 = Paeth everywhere, -1 = the min-sum heuristic (Sub + Average on these tiles)."""
     from image_stitch_b200 import synth
     rng = np.random.default_rng(seed)
     out = []
     for _ in range(N_DISTINCT):
         pix = synth.smooth_rgba8(rng, TILE, TILE, "opaque")
-        out.append((pix, synth.encode_filtered(pix, 4)))
+        out.append((pix, synth.encode_filtered(pix, 4, force, rng)))
     return out
+
+
+class _DevBuf:
+    """A device pointer as a __cuda_array_interface__ object (for torch.as_tensor)."""
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+
+def band_hash(job, y0: int, dev):
+    """Two position-weighted sums over the filtered rows of the band the job rendered last (device side, rows
+    without their padding): equal bands <=> equal hashes for any single-byte error; used to compare a band rendered
+    by its own rank with the same rows of the whole canvas rendered by rank 0."""
+    import torch
+    ptr, pitch, lead, rb = job.band_device()
+    rows = job.last_rows
+    flat = torch.as_tensor(_DevBuf(ptr, pitch * rows), device=dev)
+    h1 = h2 = 0
+    for a in range(0, rows, 2048):
+        x = flat[a * pitch:(min(rows, a + 2048)) * pitch].view(-1, pitch)[:, lead:lead + rb]
+        rs = x.sum(dim=1, dtype=torch.int64)
+        cs = x.sum(dim=0, dtype=torch.int64)
+        h1 += int((rs * (torch.arange(rs.numel(), device=dev, dtype=torch.int64) + (y0 + a + 1))).sum().item()) & ((1 << 62) - 1)
+        h2 += int((cs * (torch.arange(cs.numel(), device=dev, dtype=torch.int64) + 1)).sum().item()) & ((1 << 62) - 1)
+    return [h1 & ((1 << 62) - 1), h2 & ((1 << 62) - 1)]
 
 
 class ClockSampler:
@@ -238,20 +290,164 @@ def run_reference(args, rank: int, world: int):
 # ---------------------------------------------------------------------------
 # GPU arm
 # ---------------------------------------------------------------------------
-def add_band_tiles(job, streams, rank: int, device_ptrs=None):
-    """The 256 tiles under this rank's row band of the 16384 x (16384*N) canvas."""
+def add_band_tiles(job, streams, rank: int, device_ptrs=None, filtered: int = 1):
+    """The tiles this rank's row band of the 16384 x (16384*N) canvas needs: the 256 under it and, for rank > 0,
+    the 16 of the grid row above it (streams[256:272]) -- the band's first row is filtered against their last row,
+    which the rank recomputes instead of receiving.  streams: host buffers (or just lengths with
+    device_ptrs)."""
     y_base = rank * CANVAS
-    k = 0
-    for r in range(GRID):
-        for c in range(GRID):
-            s = streams[k]
-            kw = dict(width=TILE, height=TILE, bit_depth=8, color_type=6, interlace=0, filtered=1, dst_x=c * TILE,
-                      dst_y=y_base + r * TILE, z_index=0, image_idx=rank * GRID * GRID + k)
-            if device_ptrs is not None:
-                job.add_tile(None, device_ptr=device_ptrs[k], length=len(s), **kw)
-            else:
-                job.add_tile(s, length=len(s), **kw)
-            k += 1
+    places = [(r, c) for r in range(GRID) for c in range(GRID)]
+    if rank > 0:
+        places += [(-1, c) for c in range(GRID)]
+    for k, (r, c) in enumerate(places):
+        s = streams[k]
+        idx = rank * GRID * GRID + k if r >= 0 else (rank - 1) * GRID * GRID + (GRID - 1) * GRID + c
+        kw = dict(width=TILE, height=TILE, bit_depth=8, color_type=6, interlace=0, filtered=filtered, dst_x=c * TILE,
+                  dst_y=y_base + r * TILE, z_index=0, image_idx=idx)
+        if device_ptrs is not None:
+            job.add_tile(None, device_ptr=device_ptrs[k], length=len(s), **kw)
+        else:
+            job.add_tile(s, length=len(s), **kw)
+
+
+def tile_index(rank: int, k: int) -> int:
+    """Which of the rank's N_DISTINCT tile contents grid position k of band `rank` shows."""
+    return k % N_DISTINCT
+
+
+# ---------------------------------------------------------------------------
+# Sections of the GPU arm beside the headline workload
+# ---------------------------------------------------------------------------
+def _c3_setup(dev, need):
+    """Device buffers (one per tile: nothing is shared, so nothing is served from L2 by accident) for the C3 tiles
+    in `need`, filled from four distinct synthetic tiles."""
+    import torch
+    from image_stitch_b200 import synth
+    rng = np.random.default_rng(33)
+    raws = [torch.from_numpy(synth.smooth_rgba8(rng, C3_TILE, C3_TILE, k).reshape(-1)).to(dev) for k in synth.C3_CONTENT]
+    return {t["image_idx"]: raws[t["content"]].clone() for t in need}
+
+
+def _c3_job(ctx, layout, bufs, blend: bool, band):
+    from image_stitch_b200 import _native
+    job = _native.Job(ctx, C3_CANVAS, C3_CANVAS, 8, _native.OUT_PNG_FILTERED, blend, bytes([255, 255, 255, 128]), band=band)
+    for t in layout:
+        if t["image_idx"] in bufs and t["vis_w"] and t["vis_h"]:
+            b = bufs[t["image_idx"]]
+            job.add_tile(None, device_ptr=b.data_ptr(), length=b.numel(), width=C3_TILE, height=C3_TILE, bit_depth=8, color_type=6,
+                         filtered=0, dst_x=t["dst_x"], dst_y=t["dst_y"], src_off_x=t["src_off_x"], src_off_y=t["src_off_y"],
+                         vis_w=t["vis_w"], vis_h=t["vis_h"], z_index=t["z_index"], image_idx=t["image_idx"])
+    return job
+
+
+def c3_section(ctx, dev, rank: int, world: int, barrier):
+    """Composite + filter-select of this rank's band of the C3 canvas, blending on and off (device-timed, inputs
+    resident): ms per band, and the band's hash for the seam check."""
+    from image_stitch_b200 import synth
+    layout = synth.c3_layout(np.random.default_rng(3), C3_CANVAS, C3_SIDE, C3_TILE)
+    y0, y1 = rank * C3_CANVAS // world, (rank + 1) * C3_CANVAS // world
+    need = [t for t in layout if t["vis_h"] and t["dst_y"] < y1 and t["dst_y"] + t["vis_h"] > max(0, y0 - 1)]
+    bufs = _c3_setup(dev, need)
+    out = {"tiles": len(need)}
+    for blend in (True, False):
+        job = _c3_job(ctx, layout, bufs, blend, (y0, y1))
+        for _ in range(2):
+            job.run_band(y0, y1, download=False)
+        barrier()
+        ms = [job.run_band(y0, y1, download=False)[1]["compose_ms"] for _ in range(3)]
+        barrier()
+        out["blend_ms" if blend else "noblend_ms"] = float(np.mean(ms))
+        if blend:
+            out["hash"] = band_hash(job, y0, dev)
+        job.close()
+    del bufs
+    return out
+
+
+def c3_full_check(ctx, dev, world: int, hashes) -> bool:
+    """Rank 0: the whole C3 canvas as one job, band by band, against the hashes of the ranks' own bands."""
+    from image_stitch_b200 import synth
+    layout = synth.c3_layout(np.random.default_rng(3), C3_CANVAS, C3_SIDE, C3_TILE)
+    bufs = _c3_setup(dev, [t for t in layout if t["vis_h"]])
+    job = _c3_job(ctx, layout, bufs, True, (0, C3_CANVAS))
+    ok = True
+    for k in range(world):
+        a, b = k * C3_CANVAS // world, (k + 1) * C3_CANVAS // world
+        job.run_band(a, b, download=False)
+        ok = ok and band_hash(job, a, dev) == list(hashes[k])
+    job.close()
+    return bool(ok)
+
+
+def seam_check_c2(ctx, dev, world: int, hashes) -> bool:
+    """Rank 0: the whole 16384 x (16384 * world) mosaic as one job (every rank's 256 tiles, no halo tiles), band by
+    band, against the hashes of the bands the ranks rendered alone from their tiles plus the 16 halo tiles."""
+    from image_stitch_b200 import _native
+    job = _native.Job(ctx, CANVAS, CANVAS * world, 8, _native.OUT_PNG_FILTERED, False, bytes(4))
+    keep = []
+    for k in range(world):
+        tk = make_tiles(2 + k)
+        keep.append(tk)
+        for i in range(GRID * GRID):
+            st = tk[i % N_DISTINCT][1]
+            job.add_tile(st, length=len(st), width=TILE, height=TILE, bit_depth=8, color_type=6, interlace=0, filtered=1,
+                         dst_x=(i % GRID) * TILE, dst_y=k * CANVAS + (i // GRID) * TILE, z_index=0, image_idx=k * GRID * GRID + i)
+    ok = True
+    for k in range(world):
+        job.run_band(k * CANVAS, (k + 1) * CANVAS, download=False)
+        ok = ok and band_hash(job, k * CANVAS, dev) == list(hashes[k])
+    job.close()
+    return bool(ok)
+
+
+def unfilter_variants(ctx, dev, peak: float):
+    """Kernel (a) alone on the 256 tiles of C2 by filter type of the tile rows (SURVEY.md 8d asks for per-filter
+    figures): Paeth everywhere, and what the reference's own heuristic picks for these tiles (Sub + Average)."""
+    import torch
+    from image_stitch_b200 import _native
+    out = {}
+    for name, force in (("paeth", 4), ("heuristic_sub_average", -1)):
+        tv = make_tiles(2, force)
+        dev_in = torch.stack([torch.from_numpy(tv[k % N_DISTINCT][1]) for k in range(GRID * GRID)]).to(dev)
+        with _native.Job(ctx, CANVAS, CANVAS, 8, _native.OUT_PNG_FILTERED, False, bytes(4)) as job:
+            add_band_tiles(job, [dev_in[k] for k in range(GRID * GRID)], 0, [dev_in[k].data_ptr() for k in range(GRID * GRID)])
+            job.decode(force=True)
+            ms = min(job.decode(force=True)["decode_ms"] for _ in range(4))
+        gbs = UNF_BYTES_PER_PX * CANVAS * CANVAS / (ms / 1e3) / 1e9
+        out[name] = {"avg_ms": ms, "achieved_GBps": gbs, "frac": gbs / peak}
+        del dev_in
+    return out
+
+
+def jpeg_section(ctx, dev, peak: float):
+    """Kernel (d): a 16x16 mosaic of 2048^2 opaque tiles -> 32768^2 baseline JPEG, q = 90, restart interval of one MCU
+    row (BASELINE C5's 65536^2 exceeds SOF0's 16-bit size fields, so it cannot be a JPEG)."""
+    import torch
+    from image_stitch_b200 import _native, synth
+    rng = np.random.default_rng(5)
+    raws = [torch.from_numpy(synth.smooth_rgba8(rng, C3_TILE, C3_TILE, "opaque").reshape(-1)).to(dev) for _ in range(4)]
+    bufs = [raws[i % 4].clone() for i in range(C3_SIDE * C3_SIDE)]
+    res = {"workload": "16x16 mosaic of 2048x2048 RGBA8 tiles -> 32768x32768 baseline JPEG (4:4:4, q=90, DRI = one MCU row)"}
+    with _native.Job(ctx, C3_CANVAS, C3_CANVAS, 8, _native.OUT_JPEG_ENTROPY, False, bytes(4), jpeg_quality=90) as job:
+        for i, b in enumerate(bufs):
+            job.add_tile(None, device_ptr=b.data_ptr(), length=b.numel(), width=C3_TILE, height=C3_TILE, bit_depth=8, color_type=6,
+                         filtered=0, dst_x=(i % C3_SIDE) * C3_TILE, dst_y=(i // C3_SIDE) * C3_TILE, image_idx=i)
+        job.run_band(0, C3_CANVAS, download=False)
+        ms = [job.run_band(0, C3_CANVAS, download=False)[1]["compose_ms"] for _ in range(3)]
+        _, _, _, n_bytes = job.band_device()
+        host = torch.empty(n_bytes + 64, dtype=torch.uint8, pin_memory=True)
+        t0 = time.perf_counter()
+        out, _ = job.run_band(0, C3_CANVAS, out=host)
+        d2h_ms = (time.perf_counter() - t0) * 1e3
+    px = C3_CANVAS * C3_CANVAS
+    avg = float(np.mean(ms))
+    alg = 4.0 * px + n_bytes
+    res.update({"avg_ms": avg, "value_MPix_s": px / 1e6 / (avg / 1e3), "entropy_bytes": int(n_bytes), "bits_per_pixel": 8.0 * n_bytes / px,
+                "roofline": {"bound": "hbm", "algorithmic_bytes": alg, "achieved_GBps": alg / (avg / 1e3) / 1e9,
+                             "frac": alg / (avg / 1e3) / 1e9 / peak,
+                             "note": "composite to a canvas + colour/FDCT/quantise + code lengths + bit packing + stuffing; algorithmic = 4 B/px read + entropy bytes written"},
+                "with_d2h_of_the_entropy_bytes_ms": d2h_ms})
+    return res
 
 
 def run_ours(args, rank: int, world: int, local_rank: int):
@@ -264,16 +460,23 @@ def run_ours(args, rank: int, world: int, local_rank: int):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     tiles = make_tiles(2 + rank)
-    n_tiles = GRID * GRID
+    tiles_above = make_tiles(2 + rank - 1) if rank > 0 else None
+    n_own = GRID * GRID
+    n_tiles = n_own + (GRID if rank > 0 else 0)      # + the halo tiles (grid row above the band)
     stream_len = TILE * (TILE * 4 + 1)
     canvas_h = CANVAS * world
     y0, y1 = rank * CANVAS, (rank + 1) * CANVAS
     out_row = CANVAS * 4 + 1
 
+    def content(k: int):
+        """(tile set, index) shown at position k of this rank's tile list (add_band_tiles order)."""
+        return (tiles, k % N_DISTINCT) if k < n_own else (tiles_above, ((GRID - 1) * GRID + (k - n_own)) % N_DISTINCT)
+
     # pinned host copies of every tile stream (e2e source) and of the output band (e2e sink)
     host_in = torch.empty((n_tiles, stream_len), dtype=torch.uint8, pin_memory=True)
     for k in range(n_tiles):
-        host_in[k].copy_(torch.from_numpy(tiles[k % N_DISTINCT][1]))
+        ts_, i_ = content(k)
+        host_in[k].copy_(torch.from_numpy(ts_[i_][1]))
     host_out = torch.empty(out_row * CANVAS, dtype=torch.uint8, pin_memory=True)
     host_streams = [host_in[k] for k in range(n_tiles)]
 
@@ -328,6 +531,7 @@ def run_ours(args, rank: int, world: int, local_rank: int):
     torch.cuda.synchronize(dev)
     clocks = sampler.stop()
     ms_total = e0.elapsed_time(e1)
+    my_hash = band_hash(job, y0, dev)     # this rank's band, rendered from its own tiles + halo tiles
     job.close()
 
     # ---- e2e: host buffers in, host buffer out, every step --------------------------------
@@ -374,27 +578,21 @@ def run_ours(args, rank: int, world: int, local_rank: int):
 
     # ---- and with INFLATE on the device as well: zlib streams up the bus, deflate blocks down ---
     import zlib
-    z_distinct = [zlib.compress(bytes(tiles[k][1]), 6) for k in range(N_DISTINCT)]
-    host_zin = []
-    for zd in z_distinct:
-        t = torch.empty(len(zd), dtype=torch.uint8, pin_memory=True)
-        t.copy_(torch.frombuffer(bytearray(zd), dtype=torch.uint8))
-        host_zin.append(t)
-    zin_bytes = sum(len(z_distinct[k % N_DISTINCT]) for k in range(n_tiles))
-
-    def add_zlib_tiles(j):
-        k = 0
-        for r in range(GRID):
-            for c in range(GRID):
-                zt = host_zin[k % N_DISTINCT]
-                j.add_tile(zt, length=zt.numel(), width=TILE, height=TILE, bit_depth=8, color_type=6, interlace=0,
-                           filtered=2, dst_x=c * TILE, dst_y=rank * CANVAS + r * TILE, z_index=0,
-                           image_idx=rank * GRID * GRID + k)
-                k += 1
+    z_sets = {id(tiles): [zlib.compress(bytes(tiles[k][1]), 6) for k in range(N_DISTINCT)]}
+    if tiles_above is not None:
+        z_sets[id(tiles_above)] = [zlib.compress(bytes(tiles_above[k][1]), 6) for k in range(N_DISTINCT)]
+    pinned_z = {}
+    for key, zs in z_sets.items():
+        for i_, zd in enumerate(zs):
+            t = torch.empty(len(zd), dtype=torch.uint8, pin_memory=True)
+            t.copy_(torch.frombuffer(bytearray(zd), dtype=torch.uint8))
+            pinned_z[(key, i_)] = t
+    host_zin = [pinned_z[(id(content(k)[0]), content(k)[1])] for k in range(n_tiles)]
+    zin_bytes = sum(t.numel() for t in host_zin)
 
     def step_e2e_codec():
         j = _native.Job(ctx, CANVAS, canvas_h, 8, _native.OUT_PNG_DEFLATE, False, bytes(4), band=(y0, y1))
-        add_zlib_tiles(j)
+        add_band_tiles(j, host_zin, rank, filtered=2)
         out, tm = j.run_band(y0, y1, out=host_z)
         j.close()
         return tm
@@ -408,18 +606,32 @@ def run_ours(args, rank: int, world: int, local_rank: int):
     e2e_c_s = time.perf_counter() - t0
     # the inflate kernel alone, inputs resident
     with _native.Job(ctx, CANVAS, canvas_h, 8, _native.OUT_PNG_FILTERED, False, bytes(4), band=(y0, y1)) as ij:
-        add_zlib_tiles(ij)
+        add_band_tiles(ij, host_zin, rank, filtered=2)
         ij.inflate()
         inf_ms = min(ij.inflate(force=True)["decode_ms"] for _ in range(3))
+    del dev_in
+    # ---- C3 (north_star's target shape), strong-scaled: ONE 32768^2 canvas of 256 positioned 2048^2 tiles, zIndex
+    #      alpha blending, cut into `world` row bands; a rank uploads the tiles that touch its band or the row above it
+    c3 = c3_section(ctx, dev, rank, world, barrier)
 
-    times = torch.tensor([ms_total, e2e_s * 1e3, e2e_z_s * 1e3, e2e_c_s * 1e3, inf_ms], dtype=torch.float64, device=dev)
+    times = torch.tensor([ms_total, e2e_s * 1e3, e2e_z_s * 1e3, e2e_c_s * 1e3, inf_ms, c3["blend_ms"], c3["noblend_ms"]],
+                         dtype=torch.float64, device=dev)
+    hashes = [None] * world
+    c3_hashes = [None] * world
     if world > 1:
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
-    ms_total, e2e_ms, e2e_z_ms, e2e_c_ms, inf_ms = (float(times[i]) for i in range(5))
+        dist.all_gather_object(hashes, my_hash)
+        dist.all_gather_object(c3_hashes, c3["hash"])
+    ms_total, e2e_ms, e2e_z_ms, e2e_c_ms, inf_ms, c3_blend_ms, c3_noblend_ms = (float(times[i]) for i in range(7))
 
     if rank != 0:
         ctx.close()
         return
+    seam = None
+    if world > 1:   # the whole canvas as ONE job on this GPU: every band must hash like the rank that rendered it alone
+        seam = {"c2_bands_equal": seam_check_c2(ctx, dev, world, hashes), "c3_bands_equal": c3_full_check(ctx, dev, world, c3_hashes),
+                "method": "rank 0 renders the whole canvas as one job (no halo tiles, no bands) and compares position-weighted "
+                          "row/column sums of each band's filtered bytes with those of the rank that rendered the band alone"}
     px_step = CANVAS * CANVAS * world / 1e6       # MPix per step, all ranks
     ms_step = ms_total / args.steps
     value = px_step / (ms_step / 1e3)
@@ -428,18 +640,21 @@ def run_ours(args, rank: int, world: int, local_rank: int):
     cmp_avg, dec_avg = float(np.mean(cmp_ms)), float(np.mean(dec_ms))
     alg_bytes = ALG_BYTES_PER_PX * CANVAS * CANVAS
     achieved = alg_bytes / (cmp_avg / 1e3) / 1e9
-    unf_achieved = UNF_BYTES_PER_PX * CANVAS * CANVAS / (dec_avg / 1e3) / 1e9
+    unf_achieved = UNF_BYTES_PER_PX * n_tiles * TILE * TILE / (dec_avg / 1e3) / 1e9
+    h2d_all = (world * n_own + (world - 1) * GRID) * stream_len
+    c3_px = C3_CANVAS * C3_CANVAS
+    c3_alg = 8.0 * c3_px       # 4 B/px x coverage 1.0 read + 4 B/px written
     line = {
         "metric": "composited output MPix/s", "value": value, "unit": "MPix/s", "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": dict(WORKLOAD_CONFIG),
         "clocks": clocks,
-        "e2e": {"value": e2e_value, "unit": "MPix/s", "h2d_bytes_per_step": n_tiles * stream_len * world,
+        "e2e": {"value": e2e_value, "unit": "MPix/s", "h2d_bytes_per_step": h2d_all,
                 "d2h_bytes_per_step": out_row * CANVAS * world, "ms_per_step": e2e_ms / e2e_steps,
                 "last_step_device_ms": e2e_tm},
         "e2e_device_deflate": {"value": px_step / (e2e_z_ms / e2e_steps / 1e3), "unit": "MPix/s",
-                               "h2d_bytes_per_step": n_tiles * stream_len * world, "d2h_bytes_per_step": z_len * world,
+                               "h2d_bytes_per_step": h2d_all, "d2h_bytes_per_step": z_len * world,
                                "ms_per_step": e2e_z_ms / e2e_steps, "ratio": out_row * CANVAS / max(1, z_len),
                                "note": "same step, output as zlib-compatible deflate blocks made on the device "
                                        "(STITCH_OUT_PNG_DEFLATE); not the headline e2e, which stays filtered scanlines"},
@@ -449,18 +664,35 @@ def run_ours(args, rank: int, world: int, local_rank: int):
                              "note": "same step with the tiles uploaded as their zlib streams (host zlib level 6) and "
                                      "inflated on the device (filtered = 2, SURVEY 8f.2), output deflated on the device: "
                                      "compressed bytes both ways; not the headline e2e"},
+        "e2e_floor": e2e_floor(world, h2d_all / world, out_row * CANVAS, e2e_ms / e2e_steps),
         "gpu_launches": value_launches,
-        "roofline": {"bound": "hbm", "kernel": "composite+filter-select (kernels b+c)", "achieved": achieved, "peak": peak,
+        "roofline": {"bound": "hbm", "kernel": "composite+filter-select (kernels b+c), C2", "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": achieved / peak, "traffic": profiled_traffic_bytes(), "peak_source": peak_src,
-                     "traffic_source": "profiles/r1c_prof_fused.summary.csv (ncu --set full, one launch, bytes)",
+                     "traffic_source": "profiles/r2_prof_fused.summary.csv (ncu --set full of this kernel on this workload, one launch, bytes)",
                      "algorithmic_bytes_per_launch": alg_bytes, "avg_ms": cmp_avg,
                      "frac_of_8TBps": achieved / 8000.0},
-        "kernels": {"unfilter": {"avg_ms": dec_avg, "achieved_GBps": unf_achieved, "frac": unf_achieved / peak},
+        "roofline_c3": {"bound": "hbm", "kernel": "composite + filter-select on C3 (composite to a canvas in HBM, then the unit kernel reads it back)",
+                        "workload": "C3: 256 positioned overlapping 2048x2048 RGBA8 tiles (half opaque, a quarter alpha 1..254, a quarter 0/255 "
+                                    "masks), zIndex alpha blending, 32768x32768 canvas, background #FFFFFF80; every tile has its own buffer",
+                        "avg_ms": c3_blend_ms, "achieved": c3_alg / (c3_blend_ms / 1e3) / 1e9, "peak": peak, "unit": "GB/s",
+                        "frac": c3_alg / (c3_blend_ms / 1e3) / 1e9 / peak, "value_MPix_s": c3_px / 1e6 / (c3_blend_ms / 1e3),
+                        "algorithmic_bytes_per_launch": c3_alg, "traffic": profiled_traffic_bytes("profiles/r2_prof_c3_compose.summary.csv", "profiles/r2_prof_c3_filter.summary.csv", scale=8.0),
+                        "traffic_source": "8 x (compose_canvas_kernel + fused_kernel of one 4096-row band), profiles/r2_prof_c3_*.summary.csv",
+                        "blending_off": {"avg_ms": c3_noblend_ms, "frac": c3_alg / (c3_noblend_ms / 1e3) / 1e9 / peak,
+                                         "value_MPix_s": c3_px / 1e6 / (c3_noblend_ms / 1e3)},
+                        "scaling": "strong: the one canvas is cut into n_gpus row bands, max over ranks", "rows_per_gpu": C3_CANVAS // world},
+        "kernels": {"unfilter": {"avg_ms": dec_avg, "achieved_GBps": unf_achieved, "frac": unf_achieved / peak, "tiles": n_tiles,
+                                 "filter_types": "random per row"},
                     "compose_filter": {"avg_ms": cmp_avg, "achieved_GBps": achieved, "frac": achieved / peak},
                     "inflate": {"avg_ms": inf_ms, "inflated_GBps": n_tiles * stream_len / (inf_ms / 1e3) / 1e9,
-                                "streams": n_tiles, "note": "one warp per zlib stream; serial inside a stream, "
-                                "so bounded by the warp's instruction latency, not by HBM"}},
+                                "streams": n_tiles, "note": "a warp pair per zlib stream; serial inside a stream, "
+                                "so bounded by the warps' instruction latency, not by HBM"}},
     }
+    if seam is not None:
+        line["seam_check"] = seam
+    if world == 1:
+        line["kernels"]["unfilter_variants"] = unfilter_variants(ctx, dev, peak)
+        line["jpeg"] = jpeg_section(ctx, dev, peak)
     if not args.no_cpu_baseline:
         threads = cpu_threads(args)
         _, dt1 = cpu_sample(tiles, args.cpu_sample_rows, threads)
@@ -476,6 +708,7 @@ def run_ours(args, rank: int, world: int, local_rank: int):
         line["host_codec"] = host_codec_rates(tiles)
     print(json.dumps(line), flush=True)
     ctx.close()
+
 
 
 def main():

@@ -260,6 +260,7 @@ class Job:
         self.out_kind = out_kind
         self.canvas_w, self.canvas_h = canvas_w, canvas_h
         self._keep = []
+        self.last_rows = 0
 
     def close(self) -> None:
         if self.handle:
@@ -339,6 +340,7 @@ class Job:
         else:
             rc = self.lib.stitch_job_run_band(self.handle, y0, y1, None, 0, C.byref(n), C.byref(t))
         self.ctx.check(rc)
+        self.last_rows = y1 - y0
         res = out[: n.value] if download else None
         return res, t.as_dict()
 

@@ -52,3 +52,25 @@ def encode_filtered(pix: np.ndarray, bpp: int, force: int = -1, rng=None) -> np.
     stack = np.stack(cands)               # [5, h, n]
     out[:, 1:] = stack[best, np.arange(h)]
     return out.reshape(-1)
+
+
+def c3_layout(rng, canvas: int, n_side: int, tile: int):
+    """n_side^2 tiles at uniform random positions in [-256, canvas - tile + 256] (about a tenth
+    are clipped), zIndex a random permutation with 16 deliberate duplicates (imageIdx breaks the tie).  Tile i shows
+    content i % 4 of (opaque, opaque, alpha uniform in 1..254, alpha a 0/255 mask): half of the tiles opaque, a
+    quarter translucent, a quarter masked.  Returns placement dicts (no pixels; key "content")."""
+    n = n_side * n_side
+    z = rng.permutation(n)
+    z[rng.choice(n, 16, replace=False)] = z[rng.choice(n, 16, replace=False)]
+    tiles = []
+    for i in range(n):
+        x = int(rng.integers(-256, canvas - tile + 257))
+        y = int(rng.integers(-256, canvas - tile + 257))
+        left, top, right, bottom = max(0, x), max(0, y), min(canvas, x + tile), min(canvas, y + tile)
+        tiles.append(dict(width=tile, height=tile, bit_depth=8, color_type=6, content=i % 4, dst_x=left, dst_y=top,
+                          src_off_x=left - x, src_off_y=top - y, vis_w=right - left, vis_h=bottom - top,
+                          z_index=int(z[i]), image_idx=i))
+    return tiles
+
+
+C3_CONTENT = ("opaque", "opaque", "uniform", "binary")

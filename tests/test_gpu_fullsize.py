@@ -51,21 +51,11 @@ def test_c2_grid_16k_sampled_bands_and_round_trip(ctx):
 
 
 def _c3_tiles(rng, canvas, n_side, tile):
-    """n_side^2 tiles at uniform random positions in [-256, canvas - tile + 256] (about a tenth
-    are clipped), zIndex a random permutation with 16 deliberate duplicates (imageIdx breaks the tie), half of
-    the tiles opaque, a quarter with alpha uniform in 1..254, a quarter with a 0/255 mask."""
-    n = n_side * n_side
-    raws = [synth.smooth_rgba8(rng, tile, tile, k) for k in ("opaque", "opaque", "uniform", "binary")]
-    z = rng.permutation(n)
-    z[rng.choice(n, 16, replace=False)] = z[rng.choice(n, 16, replace=False)]
-    tiles = []
-    for i in range(n):
-        x = int(rng.integers(-256, canvas - tile + 257))
-        y = int(rng.integers(-256, canvas - tile + 257))
-        left, top, right, bottom = max(0, x), max(0, y), min(canvas, x + tile), min(canvas, y + tile)
-        tiles.append(dict(width=tile, height=tile, bit_depth=8, color_type=6, pixels=raws[i % 4], dst_x=left, dst_y=top,
-                          src_off_x=left - x, src_off_y=top - y, vis_w=right - left, vis_h=bottom - top,
-                          z_index=int(z[i]), image_idx=i))
+    """SURVEY.md 8d, C3 (layout: image_stitch_b200.synth.c3_layout, shared with bench.py), with pixels."""
+    raws = [synth.smooth_rgba8(rng, tile, tile, k) for k in synth.C3_CONTENT]
+    tiles = synth.c3_layout(rng, canvas, n_side, tile)
+    for t in tiles:
+        t["pixels"] = raws[t["content"]]
     return tiles
 
 
