@@ -299,6 +299,7 @@ class Job:
                                                           _addr(trns) if trns else None, len(trns))
             else:
                 rc = self.lib.stitch_job_add_tile(self.handle, C.byref(td), _addr(data), n)
+            self._keep.append(data)   # a pinned source is copied asynchronously: it must outlive the upload (until close)
         self.ctx.check(rc)
 
     def decode(self, force: bool = False) -> dict:

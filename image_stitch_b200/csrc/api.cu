@@ -1053,9 +1053,26 @@ static int download_pieces(stitch_job *job, uint8_t *host, const uint8_t *dev, s
   return STITCH_OK;
 }
 
+static int run_band_impl(stitch_job *job, uint32_t y0, uint32_t y1, uint8_t *out, size_t cap, size_t *out_len, stitch_timings *tm);
+
 extern "C" int stitch_job_run_band(stitch_job *job, uint32_t y0, uint32_t y1, uint8_t *out, size_t cap,
                                    size_t *out_len, stitch_timings *tm) {
   if (!job) return STITCH_E_INVALID;
+  const int rc = run_band_impl(job, y0, y1, out, cap, out_len, tm);
+  if (rc != STITCH_OK) {
+    // An error exit may leave earlier chunks' downloads in flight towards the caller's buffer, kernels queued and
+    // staged tables unread: drain all three streams before the caller may free anything.
+    stitch_ctx *ctx = job->ctx;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->down);
+    cudaStreamSynchronize(ctx->stream);
+    cudaGetLastError();
+    stitch_arena_reset(ctx);
+  }
+  return rc;
+}
+
+static int run_band_impl(stitch_job *job, uint32_t y0, uint32_t y1, uint8_t *out, size_t cap, size_t *out_len, stitch_timings *tm) {
   stitch_ctx *ctx = job->ctx;
   const stitch_job_desc &jd = job->desc;
   cudaSetDevice(ctx->device);

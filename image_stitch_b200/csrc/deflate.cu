@@ -407,9 +407,8 @@ __global__ void __launch_bounds__(DT) crc32_kernel(const uint8_t *dst, unsigned 
 }
 
 CrcTables g_crc_host;
-bool g_crc_ready = false;
 
-void crc_tables_init() {
+static void crc_tables_fill() {
   CrcTables &h = g_crc_host;
   for (uint32_t b = 0; b < 256; b++) {
     uint32_t c = b;
@@ -420,6 +419,10 @@ void crc_tables_init() {
     for (int k = 1; k < 4; k++) h.t[k][b] = h.t[0][h.t[k - 1][b] & 0xffu] ^ (h.t[k - 1][b] >> 8);
   uint32_t p = 0x80000000u >> 8;  // x^8
   for (int j = 0; j < CRC_POWS; j++) { h.pow8[j] = p; p = crc_mulmod(p, p); }
+}
+void crc_tables_init() {   // host tables: once per process, whichever thread comes first
+  static std::once_flag flag;
+  std::call_once(flag, crc_tables_fill);
 }
 
 }  // namespace
@@ -436,10 +439,14 @@ int stitch_deflate_band(stitch_job *job, const uint8_t *d_rows, uint32_t n_rows,
   v.total = (unsigned long long)host_row * n_rows;
   const uint32_t n_blocks = (uint32_t)((v.total + DB - 1) / DB);
   const size_t scratch = (size_t)n_blocks * (TAB * 4 + 4 + 8 + 8) + 96;
-  if (!g_crc_ready) {
-    crc_tables_init();
-    STITCH_CK(cudaMemcpyToSymbol(g_crc, &g_crc_host, sizeof(CrcTables)));
-    g_crc_ready = true;
+  {  // the CRC tables are a __device__ symbol and the encoder's shared memory an attribute: both per device
+    static PerDevice once;
+    int unused = 0;
+    STITCH_CK(once.get(&unused, [](int *) {
+      crc_tables_init();
+      cudaError_t e = cudaMemcpyToSymbol(g_crc, &g_crc_host, sizeof(CrcTables));
+      return e != cudaSuccess ? e : cudaFuncSetAttribute(deflate_encode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(EncSmem));
+    }));
   }
   if ((rc = stitch_ensure_buffer(ctx, &job->d_defl_scratch, &job->defl_scratch_bytes, scratch))) return rc;
   if (!job->h_defl) STITCH_CK(cudaHostAlloc((void **)&job->h_defl, 32, cudaHostAllocDefault));
@@ -448,11 +455,6 @@ int stitch_deflate_band(stitch_job *job, const uint8_t *d_rows, uint32_t n_rows,
   uint32_t *adler_parts = reinterpret_cast<uint32_t *>(result + 4);
   uint32_t *sizes = adler_parts + 2 * (size_t)n_blocks;
   uint32_t *tabs = sizes + n_blocks;
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaFuncSetAttribute(deflate_encode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(EncSmem));
-    attr_set = true;
-  }
   deflate_plan_kernel<<<n_blocks, DT, 0, ctx->stream>>>(v, tabs, sizes, adler_parts);
   STITCH_CK(cudaGetLastError());
   deflate_scan_kernel<<<1, 1024, 0, ctx->stream>>>(sizes, adler_parts, n_blocks, v.total, offsets, result);
@@ -474,11 +476,11 @@ int stitch_deflate_band(stitch_job *job, const uint8_t *d_rows, uint32_t n_rows,
 
 // R(A || B) from R(A), R(B) and len(B); and the standard CRC-32 (zlib.crc32) of n bytes from their remainder R.
 uint32_t stitch_crc_raw_concat(uint32_t ra, uint32_t rb, uint64_t len_b) {
-  if (!g_crc_ready) { crc_tables_init(); }
+  crc_tables_init();
   return crc_mulmod(ra, crc_xpow8(g_crc_host.pow8, len_b)) ^ rb;
 }
 uint32_t stitch_crc_finish(uint32_t raw, uint64_t n) {
-  if (!g_crc_ready) { crc_tables_init(); }
+  crc_tables_init();
   return raw ^ crc_mulmod(0xffffffffu, crc_xpow8(g_crc_host.pow8, n)) ^ 0xffffffffu;
 }
 

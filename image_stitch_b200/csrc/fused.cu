@@ -545,14 +545,17 @@ cudaError_t launch_compose_canvas(const FusedParams &p, bool out16, uint8_t *can
 size_t fused_plan_bytes(uint32_t n_units) { return (size_t)n_units * sizeof(PlanRec); }
 
 cudaError_t launch_fused(const FusedParams &p, bool out16, int sm_count, cudaStream_t st) {
-  static int occ8 = -1, occ16 = -1;
-  if (occ8 < 0) {
-    cudaFuncSetAttribute(fused_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FU_CTA_SMEM);
-    cudaFuncSetAttribute(fused_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FU_CTA_SMEM);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ8, fused_kernel<1>, FU_WARPS * 32, FU_CTA_SMEM);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ16, fused_kernel<2>, FU_WARPS * 32, FU_CTA_SMEM);
-  }
-  int occ = out16 ? occ16 : occ8;
+  static PerDevice once8, once16;   // shared-memory opt-in and occupancy, per device
+  int occ = 0;
+  cudaError_t pe = out16 ? once16.get(&occ, [](int *v) {
+                               cudaError_t e = cudaFuncSetAttribute(fused_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FU_CTA_SMEM);
+                               return e != cudaSuccess ? e : cudaOccupancyMaxActiveBlocksPerMultiprocessor(v, fused_kernel<2>, FU_WARPS * 32, FU_CTA_SMEM);
+                             })
+                         : once8.get(&occ, [](int *v) {
+                               cudaError_t e = cudaFuncSetAttribute(fused_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FU_CTA_SMEM);
+                               return e != cudaSuccess ? e : cudaOccupancyMaxActiveBlocksPerMultiprocessor(v, fused_kernel<1>, FU_WARPS * 32, FU_CTA_SMEM);
+                             });
+  if (pe != cudaSuccess) return pe;
   if (occ < 1) return cudaErrorLaunchOutOfResources;
   if (occ > FU_MAX_CTAS) occ = FU_MAX_CTAS;
   const uint32_t n_units = p.n_bands * p.nseg;

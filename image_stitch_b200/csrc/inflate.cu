@@ -873,13 +873,13 @@ __global__ void __launch_bounds__(256) inflate_adler_kernel(const InfStream *str
 
 cudaError_t launch_inflate(const InfStream *d_streams, InfResult *d_results, uint32_t n_streams, cudaStream_t st) {
   if (!n_streams) return cudaSuccess;
-  static bool attr = false;
+  static PerDevice once;   // shared-memory opt-in, per device
   const size_t smem = sizeof(WarpSmem) * INF_STREAMS;
-  if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(inflate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    attr = true;
-  }
+  int unused = 0;
+  const cudaError_t pe = once.get(&unused, [smem](int *) {
+    return cudaFuncSetAttribute(inflate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  });
+  if (pe != cudaSuccess) return pe;
   inflate_kernel<<<(n_streams + INF_STREAMS - 1) / INF_STREAMS, INF_STREAMS * 64, smem, st>>>(d_streams, d_results, n_streams);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;

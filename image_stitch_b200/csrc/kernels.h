@@ -2,8 +2,35 @@
 #pragma once
 #include "common.cuh"
 
+#include <mutex>
+
 struct stitch_job;
 struct stitch_timings;
+
+namespace stitch {
+// cudaFuncSetAttribute, occupancy figures and __device__/__constant__ symbols are PER DEVICE: one-time set-up is
+// remembered per device (a process may drive several: ConcatOptions.devices, one stitch_ctx per device), under a
+// lock because the contexts' threads launch concurrently.  value_plus_1[dev] == 0: not done yet on that device.
+struct PerDevice {
+  std::mutex mu;
+  int value_plus_1[64] = {};
+  template <class F>   // F: cudaError_t(int *value), run once per device with that device current
+  cudaError_t get(int *value, F init) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(mu);
+    if (!value_plus_1[dev]) {
+      int v = 0;
+      if ((e = init(&v)) != cudaSuccess) return e;
+      value_plus_1[dev] = v + 1;
+    }
+    *value = value_plus_1[dev] - 1;
+    return cudaSuccess;
+  }
+};
+}  // namespace stitch
 
 namespace stitch {
 

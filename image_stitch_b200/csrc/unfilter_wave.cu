@@ -487,11 +487,13 @@ __global__ void __launch_bounds__(UW_WARPS * 32, 4)
 
 template <int KBPP>
 static cudaError_t launch_uw(const UwParams &p, int sm_count, cudaStream_t st) {
-  static int occ = -1;
-  if (occ < 0) {
-    cudaFuncSetAttribute(unfilter_wave_kernel<KBPP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)UW_CTA_SMEM);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, unfilter_wave_kernel<KBPP>, UW_WARPS * 32, UW_CTA_SMEM);
-  }
+  static PerDevice once;   // one per instantiation: shared-memory opt-in and occupancy, per device
+  int occ = 0;
+  const cudaError_t pe = once.get(&occ, [](int *v) {
+    cudaError_t e = cudaFuncSetAttribute(unfilter_wave_kernel<KBPP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)UW_CTA_SMEM);
+    return e != cudaSuccess ? e : cudaOccupancyMaxActiveBlocksPerMultiprocessor(v, unfilter_wave_kernel<KBPP>, UW_WARPS * 32, UW_CTA_SMEM);
+  });
+  if (pe != cudaSuccess) return pe;
   if (occ < 1) return cudaErrorLaunchOutOfResources;
   // Residency is not needed for correctness (see "schedule" above); the grid is sized to it for balance.
   const uint32_t resident = (uint32_t)(occ * sm_count);

@@ -3,9 +3,11 @@
 encodes rows [y0_k, y1_k) from the tiles that intersect them (plus the one
 predictor row above, recomputed rather than exchanged) and the bands are
 handed, in ascending order, to the container writer on rank 0.  The only
-communication is that final hand-off (a gather of byte strings), which stands
-in for "D2H into pinned buffers, consumed in order" when ranks are separate
-processes.
+communication is that final hand-off: a gather TO RANK 0 ONLY of container-ready
+pieces (every rank deflates its own band, or passes on the device's deflate
+blocks) over a host-memory (gloo) group -- no NCCL collective, no padding --,
+which stands in for "D2H into pinned buffers, consumed in order" when ranks are
+separate processes.
 
 Launch with ``torchrun --nproc-per-node N`` (backend nccl on GPUs; the host
 logic is exercised on CPU with gloo in tests/test_distributed_gloo.py).
@@ -38,8 +40,13 @@ def placements_for_band(plan: JobPlan, y0: int, y1: int) -> List[TilePlacement]:
     return [p for p in plan.placements if p.dst_y < y1 and p.dst_y + p.vis_h > halo0]
 
 
-def gpu_band(plan: JobPlan, sources: Dict[int, TileSource], y0: int, y1: int, device: Optional[int] = None) -> bytes:
-    """Default renderer: libstitch_b200 on this rank's device."""
+IDAT_PIECE = 8 << 20   # bytes of compressed data per IDAT chunk written by rank 0
+
+
+def gpu_band(plan: JobPlan, sources: Dict[int, TileSource], y0: int, y1: int, device: Optional[int] = None):
+    """Default renderer: libstitch_b200 on this rank's device.  Returns the band's rows as the device left them:
+    filtered scanlines (bytes), JPEG entropy segments (bytes), or -- with device_deflate -- a list of
+    (deflate blocks, crc32 of them, adler32, raw length) per chunk."""
     runner = engine.BandRunner(plan, sources, engine.default_device() if device is None else device, y0, y1)
     try:
         step = engine.default_band_rows(plan)
@@ -49,40 +56,92 @@ def gpu_band(plan: JobPlan, sources: Dict[int, TileSource], y0: int, y1: int, de
             if plan.output_format == "jpeg":
                 from .jpeg_container import JpegBandSplicer
                 parts.append(JpegBandSplicer().push(data))
+            elif plan.device_deflate:
+                from .deflate_container import DeflateBandSplicer
+                sp = DeflateBandSplicer()
+                body = sp.push(data)
+                parts.append((body, sp.last_crc32, sp.adler, sp.raw_bytes))
             else:
                 parts.append(np.ascontiguousarray(data).tobytes())
-        return b"".join(parts)
+        return parts if plan.device_deflate and plan.output_format != "jpeg" else b"".join(parts)
     finally:
         runner.close()
 
 
-def gather_bytes(local: bytes, dst: int = 0) -> Optional[List[bytes]]:
-    """Variable-length gather to `dst` over the default process group (gloo or nccl)."""
-    import torch
+def band_to_pieces(plan: JobPlan, band) -> dict:
+    """What a rank hands to rank 0: container-ready pieces of ITS rows, so that rank 0 only frames and writes.
+    PNG: raw deflate data ending on a byte boundary (sync flush), so that the ranks' pieces concatenate into one
+    zlib stream, with the Adler-32 and length of the rows they encode -- every rank deflates its own band (level 6,
+    like streaming-deflate.ts:57-66) in parallel, or passes on the device's deflate blocks with the device's CRC-32.
+    JPEG: the band's entropy-coded segments (restart intervals make them concatenate)."""
+    if plan.output_format == "jpeg":
+        return {"kind": "jpeg", "pieces": [bytes(band)] if band else []}
+    if isinstance(band, list):   # device deflate: (blocks, crc32, adler32, raw length) per chunk
+        from .deflate_container import adler32_combine
+        adler, raw = 1, 0
+        for _, _, a, n in band:
+            adler = adler32_combine(adler, a, n)
+            raw += n
+        return {"kind": "deflate", "pieces": [bytes(b) for b, _, _, _ in band], "crcs": [c for _, c, _, _ in band], "adler": adler, "raw": raw}
+    raw = bytes(band)
+    if not raw:
+        return {"kind": "deflate", "pieces": [], "crcs": None, "adler": 1, "raw": 0}
+    co = zlib.compressobj(6, zlib.DEFLATED, -15)
+    z = co.compress(raw) + co.flush(zlib.Z_SYNC_FLUSH)
+    return {"kind": "deflate", "pieces": [z[o:o + IDAT_PIECE] for o in range(0, len(z), IDAT_PIECE)], "crcs": None,
+            "adler": zlib.adler32(raw), "raw": len(raw)}
+
+
+_host_group = None
+
+
+def host_group():
+    """The process group the hand-off to rank 0 uses: host memory to host memory (gloo), whatever the default
+    backend is -- the bands are already in host memory and no GPU should see them again."""
+    global _host_group
+    import torch.distributed as dist
+    if dist.get_backend() == "gloo":
+        return None
+    if _host_group is None:
+        _host_group = dist.new_group(backend="gloo")
+    return _host_group
+
+
+def gather_pieces(local, dst: int = 0) -> Optional[list]:
+    """Gather of one object per rank to `dst` ONLY, in rank order (= ascending rows): no padding, no copy to the other
+    ranks, no NCCL."""
     import torch.distributed as dist
     world, rank = dist.get_world_size(), dist.get_rank()
-    dev = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend() == "nccl" else torch.device("cpu")
-    sizes = [torch.zeros(1, dtype=torch.int64, device=dev) for _ in range(world)]
-    dist.all_gather(sizes, torch.tensor([len(local)], dtype=torch.int64, device=dev))
-    cap = max(1, int(max(int(s.item()) for s in sizes)))
-    buf = torch.zeros(cap, dtype=torch.uint8, device=dev)
-    if local:
-        buf[: len(local)] = torch.frombuffer(bytearray(local), dtype=torch.uint8).to(dev)
-    out = [torch.zeros(cap, dtype=torch.uint8, device=dev) for _ in range(world)]
-    dist.all_gather(out, buf)   # all_gather works on both backends; only dst keeps the result
-    if rank != dst:
-        return None
-    return [out[r][: int(sizes[r].item())].cpu().numpy().tobytes() for r in range(world)]
+    out = [None] * world if rank == dst else None
+    dist.gather_object(local, out, dst=dst, group=host_group())
+    return out
 
 
-def write_container(plan: JobPlan, bands: List[bytes]) -> bytes:
-    """Rank 0: bands (ascending rows) -> PNG or JPEG file, like api.StreamingConcatenator."""
+def gather_bytes(local: bytes, dst: int = 0) -> Optional[List[bytes]]:
+    """Variable-length gather of byte strings to `dst` (see gather_pieces)."""
+    return gather_pieces(bytes(local), dst)
+
+
+def write_container(plan: JobPlan, parts: List[dict]) -> bytes:
+    """Rank 0: the ranks' pieces (ascending rows) -> PNG or JPEG file, like api.StreamingConcatenator: several IDAT
+    chunks (a chunk holds at most 2^31 - 1 bytes), one zlib stream whose Adler-32 is combined from the ranks'."""
     if plan.output_format == "jpeg":
         from .jpeg_container import EOI, jpeg_header
-        return jpeg_header(plan.canvas_w, plan.canvas_h, plan.jpeg_quality) + b"".join(bands) + EOI
-    ihdr = serialize_chunk(create_ihdr(PngHeader(plan.canvas_w, plan.canvas_h, plan.out_bit_depth, plan.out_color_type, 0, 0, 0)))
-    idat = serialize_chunk(create_chunk("IDAT", zlib.compress(b"".join(bands), 6)))
-    return PNG_SIGNATURE + ihdr + idat + serialize_chunk(create_iend())
+        return jpeg_header(plan.canvas_w, plan.canvas_h, plan.jpeg_quality) + b"".join(b"".join(p["pieces"]) for p in parts) + EOI
+    from .deflate_container import FINAL_BLOCK, ZLIB_HEADER, adler32_combine, idat_chunk
+    out = [PNG_SIGNATURE, serialize_chunk(create_ihdr(PngHeader(plan.canvas_w, plan.canvas_h, plan.out_bit_depth, plan.out_color_type, 0, 0, 0)))]
+    head, adler = ZLIB_HEADER, 1
+    for p in parts:
+        adler = adler32_combine(adler, p["adler"], p["raw"])
+        for i, piece in enumerate(p["pieces"]):
+            if p["crcs"] is not None:   # the device's CRC-32 of the piece: the chunk CRC needs no pass over the bytes
+                out.append(idat_chunk(head, piece, p["crcs"][i]))
+            else:
+                out.append(serialize_chunk(create_chunk("IDAT", head + piece)))
+            head = b""
+    out.append(serialize_chunk(create_chunk("IDAT", head + FINAL_BLOCK + adler.to_bytes(4, "big"))))
+    out.append(serialize_chunk(create_iend()))
+    return b"".join(out)
 
 
 def stitch_rank_band(options, render: Optional[BandRenderer] = None):
@@ -102,6 +161,7 @@ def stitch_rank_band(options, render: Optional[BandRenderer] = None):
     try:
         headers = [image_header_to_png_header(d.get_header()) for d in decoders]
         plan = engine.plan_job(opts, inputs, headers, logger=lambda m: None)
+        plan.device_deflate = bool(opts.device_deflate) and plan.output_format != "jpeg"
         y0, y1 = rank_rows(plan.canvas_h, world)[rank]
         if y1 <= y0:
             return plan, (y0, y1), b""
@@ -120,7 +180,7 @@ def stitch_rank_band(options, render: Optional[BandRenderer] = None):
 def concat_to_buffer_distributed(options, render: Optional[BandRenderer] = None) -> Optional[bytes]:
     """concatToBuffer over all ranks of the default process group: the file on rank 0, None elsewhere."""
     plan, _, band = stitch_rank_band(options, render)
-    bands = gather_bytes(band, 0)
-    if bands is None:
+    parts = gather_pieces(band_to_pieces(plan, band), 0)
+    if parts is None:
         return None
-    return write_container(plan, bands)
+    return write_container(plan, parts)

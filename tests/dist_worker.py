@@ -34,6 +34,9 @@ def oracle_band(plan, sources, y0, y1):
 def main():
     case, out_path = sys.argv[1], sys.argv[2]
     dist.init_process_group("gloo")
+    if os.environ.get("STITCH_DIST_GPU"):
+        import torch
+        os.environ["STITCH_B200_DEVICE"] = str(int(os.environ.get("LOCAL_RANK", "0")) % max(1, torch.cuda.device_count()))
     ins = [H.suite_bytes(n) for n in ("basn2c08", "basn6a08", "basn0g08", "basn4a08", "basi6a08", "basn2c08")]
     if case == "grid_png":
         opts = {"inputs": ins, "layout": {"columns": 2}}
@@ -41,7 +44,20 @@ def main():
         opts = {"inputs": [{"x": 7 * i, "y": 13 * i, "source": s} for i, s in enumerate(ins)], "layout": {}}
     else:
         opts = {"inputs": ins, "layout": {"columns": 2}, "output_format": "jpeg", "jpeg_quality": 90}
-    plan, (y0, y1), band = D.stitch_rank_band(opts, oracle_band)
+    render = None if os.environ.get("STITCH_DIST_GPU") else oracle_band   # GPU test: the product's own gpu_band
+    if os.environ.get("STITCH_DIST_DEVICE_DEFLATE"):
+        opts["device_deflate"] = True
+    if os.environ.get("STITCH_DIST_FILE"):   # the whole product path: pieces -> rank 0 -> container
+        data = D.concat_to_buffer_distributed(opts, render)
+        if dist.get_rank() == 0:
+            with open(out_path, "wb") as f:
+                f.write(data)
+            with open(out_path + ".json", "w") as f:
+                json.dump({}, f)
+        dist.barrier()
+        dist.destroy_process_group()
+        return
+    plan, (y0, y1), band = D.stitch_rank_band(opts, render)
     bands = D.gather_bytes(band, 0)
     if dist.get_rank() == 0:
         with open(out_path, "wb") as f:

@@ -23,13 +23,15 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _run(case, world, tmp_path):
+def _run(case, world, tmp_path, extra_env=None, gpu=False):
     out = str(tmp_path / f"{case}_{world}.bin")
     port = _free_port()
     procs = []
     for r in range(world):
         env = dict(os.environ, RANK=str(r), WORLD_SIZE=str(world), LOCAL_RANK=str(r), MASTER_ADDR="127.0.0.1",
-                   MASTER_PORT=str(port), CUDA_VISIBLE_DEVICES="")
+                   MASTER_PORT=str(port), **(extra_env or {}))
+        if not gpu:
+            env["CUDA_VISIBLE_DEVICES"] = ""
         procs.append(subprocess.Popen([sys.executable, os.path.join(HERE, "dist_worker.py"), case, out], env=env,
                                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT))
     for p in procs:
@@ -81,3 +83,25 @@ def test_rank_rows_properties():
                 if b > a:
                     assert a % 8 == 0 and (b % 8 == 0 or b == h)
                     prev = b
+
+
+@pytest.mark.parametrize("case", ["grid_png", "positioned_png"])
+def test_whole_file_through_rank0(case, tmp_path):
+    """concat_to_buffer_distributed: every rank deflates its own band (sync-flushed raw deflate), rank 0 frames the
+    pieces into IDAT chunks with the combined Adler-32: the file must be a valid PNG of the whole canvas."""
+    from image_stitch_b200.png_container import read_png
+    data, _ = _run(case, 3, tmp_path, {"STITCH_DIST_FILE": "1"})
+    opts = ({"inputs": _inputs(), "layout": {"columns": 2}} if case == "grid_png" else
+            {"inputs": [{"x": 7 * i, "y": 13 * i, "source": s} for i, s in enumerate(_inputs())], "layout": {}})
+    _, want = H.oracle_stitch_rows(opts)
+    header, rows = read_png(data)   # checks every chunk CRC and the zlib trailer
+    assert rows == want.tobytes()
+    assert data.count(b"IDAT") >= 3
+
+
+def test_whole_jpeg_through_rank0(tmp_path):
+    data, _ = _run("jpeg", 2, tmp_path, {"STITCH_DIST_FILE": "1"})
+    opts = {"inputs": _inputs(), "layout": {"columns": 2}}
+    plan, raw = H.oracle_stitch_rows(opts, out_kind=1)
+    w, h = plan.canvas_w, plan.canvas_h
+    assert data == orc.jpeg_file(np.frombuffer(raw, np.uint8).reshape(h, w * 4), w, h, 90)
