@@ -867,7 +867,7 @@ static int finalize_job(stitch_job *job) {
     job->busy_bins[by + 1] = job->busy_bins[by] + busy;
   }
   int rc;
-  if (jd.out_kind == STITCH_OUT_PNG_FILTERED || jd.out_kind == STITCH_OUT_PNG_DEFLATE) {
+  {
     // tensor maps of the tiles (dt[k].pad <- valid) and the interval plan of strip.cu, ahead of the tile table's upload
     std::vector<uint32_t> src_words(order.size()), src_rows(order.size());
     for (size_t k = 0; k < order.size(); k++) {
@@ -923,6 +923,17 @@ static void bg_words(const stitch_job_desc &d, uint32_t &lo, uint32_t &hi) {
   if (d.out_bit_depth != 16) hi = 0;
 }
 
+static StripParams strip_params(const stitch_job *job) {
+  const stitch_job_desc &jd = job->desc;
+  StripParams sp{};
+  sp.tiles = job->d_tiles; sp.maps = job->d_maps; sp.ivs = reinterpret_cast<const StripIv *>(job->d_ivs);
+  sp.col_start = reinterpret_cast<const uint32_t *>(job->d_col_start); sp.lists = reinterpret_cast<const uint32_t *>(job->d_lists);
+  sp.bg_row = reinterpret_cast<const uint8_t *>(job->d_bgrow);
+  sp.canvas_w = jd.canvas_w; sp.ncol = job->strip_ncol; sp.alpha_blend = jd.alpha_blend;
+  bg_words(jd, sp.bg_lo, sp.bg_hi);
+  return sp;
+}
+
 // Rows [a, b) of a PNG-filtered or raw band into d_rows (row pitch job->out_pitch): decode the tiles the rows
 // need, composite, filter.  Everything is queued on ctx->stream; nothing is waited for.
 static int render_rows(stitch_job *job, uint32_t a, uint32_t b, uint8_t *d_rows, uint32_t *launches, cudaEvent_t ev_decoded) {
@@ -972,12 +983,8 @@ static int render_rows(stitch_job *job, uint32_t a, uint32_t b, uint8_t *d_rows,
     // B200 -- DESIGN.md section 3d); read at every call so that tests can run both in one process
     const char *strip_env = getenv("STITCH_STRIP");
     if (job->strip_ok && strip_env && strip_env[0] == '1') {
-      StripParams sp{};
-      sp.tiles = job->d_tiles; sp.maps = job->d_maps; sp.ivs = reinterpret_cast<const StripIv *>(job->d_ivs);
-      sp.col_start = reinterpret_cast<const uint32_t *>(job->d_col_start); sp.lists = reinterpret_cast<const uint32_t *>(job->d_lists);
-      sp.bg_row = reinterpret_cast<const uint8_t *>(job->d_bgrow);
-      sp.canvas_w = jd.canvas_w; sp.y_begin = a; sp.y_end = b; sp.ncol = job->strip_ncol; sp.alpha_blend = jd.alpha_blend;
-      bg_words(jd, sp.bg_lo, sp.bg_hi);
+      StripParams sp = strip_params(job);
+      sp.y_begin = a; sp.y_end = b;
       sp.rowsum = reinterpret_cast<unsigned long long *>(job->d_sync);
       sp.out = d_rows; sp.out_pitch = job->out_pitch; sp.lead = (uint32_t)job->out_lead;
       static const int q_env = getenv("STITCH_STRIP_Q") ? atoi(getenv("STITCH_STRIP_Q")) : 0;   // tuning
@@ -1001,7 +1008,8 @@ static int render_rows(stitch_job *job, uint32_t a, uint32_t b, uint8_t *d_rows,
       job->canvas_pitch = pitch16;
       if ((rc = ensure_buffer(ctx, &job->d_canvas, &job->canvas_bytes, pitch16 * (size_t)(b - ys)))) return rc;
       if ((rc = ensure_buffer(ctx, &job->d_ctab, &job->ctab_bytes, 1024))) return rc;
-      CK(launch_compose_canvas(fp, jd.out_bit_depth == 16, job->d_canvas, pitch16, ys, b, ctx->stream));
+      if (job->strip_ok) CK(launch_compose_plan(strip_params(job), jd.out_bit_depth == 16, job->d_canvas, pitch16, ys, b, ctx->stream));
+      else CK(launch_compose_canvas(fp, jd.out_bit_depth == 16, job->d_canvas, pitch16, ys, b, ctx->stream));
       struct { uint8_t maps[384]; DevTile t; uint32_t pad[4]; uint32_t bin_start[2]; uint32_t bin_tiles[2]; } tab;   // maps first: 128-byte aligned
       memset(&tab, 0, sizeof tab);
       tab.t.pix = job->d_canvas; tab.t.pitch = (uint32_t)pitch16; tab.t.fmt = native_fmt(jd.out_bit_depth);
@@ -1123,7 +1131,8 @@ static int run_band_impl(stitch_job *job, uint32_t y0, uint32_t y1, uint8_t *out
       fq.tiles = job->d_tiles; fq.bin_start = job->d_bin_start; fq.bin_tiles = job->d_bin_tiles;
       fq.bins_x = job->bins_x; fq.canvas_w = jd.canvas_w; fq.alpha_blend = jd.alpha_blend;
       bg_words(jd, fq.bg_lo, fq.bg_hi);
-      CK(launch_compose_canvas(fq, false, job->d_canvas, pitch16, y0, y1, ctx->stream));
+      if (job->strip_ok) CK(launch_compose_plan(strip_params(job), false, job->d_canvas, pitch16, y0, y1, ctx->stream));
+      else CK(launch_compose_canvas(fq, false, job->d_canvas, pitch16, y0, y1, ctx->stream));
     }
     launches += 1;
     if ((rc = stitch_jpeg_encode_band(job, y0, y1, job->d_canvas, pitch16, &jpeg_bytes, &launches))) return rc;

@@ -109,7 +109,7 @@ struct StripIv {
   int32_t cw, cy;             // SK_DIRECT, SK_SHIFT: the box's first word is word cw of source row (y + cy)
   uint32_t list_off, n_list;  // SK_COMP: tiles touching the column in this interval, back to front (into lists)
                               // SK_SHIFT: list_off = words of the box that exist in the source row (<= 256)
-  uint32_t pad;
+  uint32_t pad;               // SK_COMP: 1 = every tile of the list is in the output's format and spans the whole column
 };
 enum StripKind : uint32_t { SK_BG = 0, SK_DIRECT = 1, SK_COMP = 2, SK_SHIFT = 3 };
 struct StripParams {
@@ -134,6 +134,8 @@ uint32_t strip_box_words();
 // q = 0: the launcher picks the quads per thread.  cudaErrorInvalidConfiguration: the row is too wide for one
 // resident grid (the caller falls back to composite-then-filter).
 cudaError_t launch_strip(StripParams p, bool out16, int q, int device, int sm_count, cudaStream_t st);
+// Normalise + composite rows [ys, ye) into a dense canvas in HBM, driven by the same interval plan (strip.cu).
+cudaError_t launch_compose_plan(StripParams p, bool out16, uint8_t *canvas, size_t pitch, uint32_t ys, uint32_t ye, cudaStream_t st);
 
 cudaError_t launch_unfilter(const UnfStream *d_streams, uint32_t n_streams, DevStatus *d_status, cudaStream_t st);
 // d_seam: mailbox of unfilter_wave_seam_bytes() per chain, zeroed once; epoch: a value never used with it before (> 0).

@@ -96,7 +96,7 @@ __device__ __forceinline__ void sweep_quad(const uint4 cur, const uint32_t lc0, 
 // ---- the host's plan, walked downwards ---------------------------------------------------------------------
 struct IvCursor {
   uint32_t idx, end_idx;   // current interval, one past the column's last
-  uint32_t y_end, kind, tile, list_off, n_list;
+  uint32_t y_end, kind, tile, list_off, n_list, flags;
   int32_t cw, cy;
   const uint8_t *pix;      // SK_DIRECT, SK_SHIFT: the tile's rows
   uint32_t pitch;
@@ -105,7 +105,7 @@ __device__ __forceinline__ void iv_load(const StripParams &p, IvCursor &c) {
   const uint4 *q = reinterpret_cast<const uint4 *>(p.ivs + c.idx);
   const uint4 a = __ldg(q), b = __ldg(q + 1);
   c.y_end = a.x; c.kind = a.y; c.tile = a.z; c.cw = (int32_t)a.w;
-  c.cy = (int32_t)b.x; c.list_off = b.y; c.n_list = b.z;
+  c.cy = (int32_t)b.x; c.list_off = b.y; c.n_list = b.z; c.flags = b.w;
   if (c.kind == SK_DIRECT || c.kind == SK_SHIFT) {
     const DevTile *t = p.tiles + c.tile;
     c.pix = t->pix; c.pitch = t->pitch;
@@ -436,6 +436,95 @@ __global__ void __launch_bounds__(SK_THREADS, 1) strip_kernel(const StripParams 
   if (warp == 0u) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(SK_TMEM_COLS) : "memory");
   }
+}
+
+// ---- plan-driven compositor: rows [ys, ye) of the canvas into HBM ----------------------------------------------
+// Used when a band goes "via canvas" (many composited boxes) and for the JPEG feed.  A warp owns one 128-word column
+// over CP_ROWS rows, so the plan's interval makes the kind of work warp-uniform: a background column is a stream of
+// constant stores, a column inside one tile a copy (16-byte loads when the source is aligned, else word loads), a
+// column whose layers all span it in the output's format blends layer after layer without per-pixel tests, and only
+// columns with tile edges or foreign formats walk their -- short, exact -- tile list per quad.
+static constexpr int CP_ROWS = 16;
+
+template <int BPW>
+__global__ void __launch_bounds__(128) compose_plan_kernel(const StripParams p, uint8_t *canvas, const size_t pitch,
+                                                           const uint32_t ys, const uint32_t ye) {
+  const uint32_t lane = threadIdx.x, col = blockIdx.x;
+  const uint32_t y0 = ys + (blockIdx.y * blockDim.y + threadIdx.y) * CP_ROWS;
+  if (y0 >= ye) return;
+  const uint32_t y1 = min(ye, y0 + CP_ROWS);
+  const int wmax = (int)p.canvas_w * BPW, qw = (int)(col * SK_BOX + 4u * lane);
+  if (qw >= wmax) return;
+  // the column's interval that holds row y0: binary search over y_end
+  IvCursor c;
+  c.idx = __ldg(p.col_start + col); c.end_idx = __ldg(p.col_start + col + 1);
+  {
+    uint32_t lo = c.idx, hi = c.end_idx - 1u;
+    while (lo < hi) {
+      const uint32_t mid = (lo + hi) >> 1;
+      if (__ldg(&p.ivs[mid].y_end) > y0) hi = mid; else lo = mid + 1u;
+    }
+    c.idx = lo;
+  }
+  iv_load(p, c);
+  const ComposeCtx cc = compose_ctx(p);
+  uint8_t *dst = canvas + (size_t)(y0 - ys) * pitch + (size_t)qw * 4u;
+  const bool partial = qw + 4 > wmax;   // the canvas ends inside this quad: words past it are written as zeros
+  for (uint32_t y = y0; y < y1; y++, dst += pitch) {
+    iv_seek(p, c, (int)y);
+    uint4 v;
+    if (c.kind == SK_BG) {
+      v = BPW == 2 ? make_uint4(p.bg_lo, p.bg_hi, p.bg_lo, p.bg_hi) : make_uint4(p.bg_lo, p.bg_lo, p.bg_lo, p.bg_lo);
+    } else if (c.kind == SK_DIRECT) {
+      v = __ldg(reinterpret_cast<const uint4 *>(c.pix + (size_t)((int)y + c.cy) * c.pitch + (size_t)c.cw * 4u) + lane);
+    } else if (c.kind == SK_SHIFT) {
+      const uint32_t *src = reinterpret_cast<const uint32_t *>(c.pix + (size_t)((int)y + c.cy) * c.pitch) + c.cw + 4 * (int)lane;
+      const uint32_t n = c.list_off > 4u * lane ? c.list_off - 4u * lane : 0u;   // words of the quad that exist in the source row
+      v.x = n > 0u ? __ldg(src) : 0u; v.y = n > 1u ? __ldg(src + 1) : 0u; v.z = n > 2u ? __ldg(src + 2) : 0u; v.w = n > 3u ? __ldg(src + 3) : 0u;
+    } else if (c.flags & 1u) {
+      // every layer spans the column in the output's format: background, then layer after layer, no per-pixel tests
+      v = BPW == 2 ? make_uint4(p.bg_lo, p.bg_hi, p.bg_lo, p.bg_hi) : make_uint4(p.bg_lo, p.bg_lo, p.bg_lo, p.bg_lo);
+      for (uint32_t k = 0; k < c.n_list; k++) {
+        const DevTile *t = p.tiles + __ldg(p.lists + c.list_off + k);
+        const uint32_t *src = reinterpret_cast<const uint32_t *>(t->pix + (size_t)((int)y - t->y0 + t->sy0) * t->pitch) +
+                              ((int)(col * (SK_BOX / BPW)) - t->x0 + t->sx0) * BPW + 4 * (int)lane;
+        uint4 s;
+        if (partial) {   // the canvas (and possibly the tile's row) ends inside this quad: no loads past it
+          s.x = __ldg(src); s.y = qw + 1 < wmax ? __ldg(src + 1) : 0u; s.z = qw + 2 < wmax ? __ldg(src + 2) : 0u; s.w = 0u;
+        } else if ((reinterpret_cast<uintptr_t>(src) & 15u) == 0) {
+          s = __ldg(reinterpret_cast<const uint4 *>(src));
+        } else {
+          s.x = __ldg(src); s.y = __ldg(src + 1); s.z = __ldg(src + 2); s.w = __ldg(src + 3);
+        }
+        if (p.alpha_blend == 0u || t->opaque) v = s;
+        else if (BPW == 1) v = make_uint4(blend8(v.x, s.x), blend8(v.y, s.y), blend8(v.z, s.z), blend8(v.w, s.w));
+        else {
+          const uint2 a = blend16(make_uint2(v.x, v.y), make_uint2(s.x, s.y)), b = blend16(make_uint2(v.z, v.w), make_uint2(s.z, s.w));
+          v = make_uint4(a.x, a.y, b.x, b.y);
+        }
+      }
+    } else {
+      v = compose_quad<BPW>(cc, p.lists + c.list_off, c.n_list, qw, (int)y);
+    }
+    if (partial) {
+      if (qw + 1 >= wmax) v.y = 0u;
+      if (qw + 2 >= wmax) v.z = 0u;
+      if (qw + 3 >= wmax) v.w = 0u;
+    }
+    *reinterpret_cast<uint4 *>(dst) = v;
+  }
+}
+
+cudaError_t launch_compose_plan(StripParams p, bool out16, uint8_t *canvas, size_t pitch, uint32_t ys, uint32_t ye, cudaStream_t st) {
+  if (ye <= ys) return cudaSuccess;
+  const uint32_t row_words = p.canvas_w * (out16 ? 2u : 1u);
+  const uint32_t ncol = (row_words + SK_BOX - 1) / SK_BOX;
+  const uint32_t chunks = (ye - ys + CP_ROWS - 1) / CP_ROWS;
+  const dim3 block(32, 4), grid(ncol, (chunks + 3u) / 4u);
+  if (grid.y > 65535u) return cudaErrorInvalidConfiguration;
+  if (out16) compose_plan_kernel<2><<<grid, block, 0, st>>>(p, canvas, pitch, ys, ye);
+  else compose_plan_kernel<1><<<grid, block, 0, st>>>(p, canvas, pitch, ys, ye);
+  return cudaGetLastError();
 }
 
 template <int BPW>

@@ -138,6 +138,9 @@ int stitch_build_strip_plan(stitch_job *job, std::vector<DevTile> &dt, const std
         } else {
           iv.kind = SK_COMP;
           iv.n_list = (uint32_t)cur.size();
+          bool simple = true;   // every layer is in the output's own format and spans the whole column: no per-pixel tests
+          for (uint32_t k : cur) simple = simple && dt[k].fmt == native && dt[k].x0 <= X0 && dt[k].x1 >= X1 && (dt[k].pitch & 3u) == 0;
+          iv.pad = simple ? 1u : 0u;
         }
       }
       // merge with the interval above when it asks for the same thing
