@@ -280,19 +280,32 @@ __device__ __forceinline__ uint32_t blend8(uint32_t dst, uint32_t src) {
   if (sa == 255u) return src;  // srcAlpha >= 0.9999 <=> 255   (:707-711)
   if (sa == 0u) return dst;    // srcAlpha > 0.0001 fails only for 0 (:712, :732)
   const uint32_t da = dst >> 24;
-  const uint32_t k1 = 255u * sa, k2 = da * (255u - sa), D = k1 + k2, D2 = 2u * D;   // D >= 255
-  const float r = __frcp_rn((float)D2);
+  if (da == 255u) {
+    // over an opaque pixel N / D = X / 255 with X = s sa + d (255 - sa): round half up = floor((2 X + 255) / 510), and
+    // 2 X + 255 is odd, so there is no tie; the result is opaque (D = 255^2)
+    // Red and blue travel in the 16-bit halves of one word (X <= 255^2 fits), and
+    // floor((2 X + 255) / 510) = floor((X + 127) / 255) = (Y + 1 + (Y >> 8)) >> 8 with Y = X + 127 <= 65152.
+    const uint32_t na = 255u - sa;
+    const uint32_t rb = (src & 0x00FF00FFu) * sa + (dst & 0x00FF00FFu) * na + 0x007F007Fu;
+    const uint32_t g = ((src >> 8) & 0xFFu) * sa + ((dst >> 8) & 0xFFu) * na + 0x7Fu;
+    const uint32_t out = 0xFF000000u | (((rb + 0x00010001u + ((rb >> 8) & 0x00FF00FFu)) >> 8) & 0x00FF00FFu) |
+                         (((g + 1u + (g >> 8)) >> 8) << 8);
+    return out;
+  }
+  const uint32_t k1 = 255u * sa, k2 = da * (255u - sa), D = k1 + k2, D2 = 2u * D;   // 255 <= D <= 65025
+  // M + 1/2 < 2^32 / D2 < M + 3: floor(T M / 2^32) is floor(T / D2) or one less for every T < 2^27 (the reciprocal
+  // of the exactly converted D2 is within 2^-24 of the true one, the truncation takes less than one more)
+  const uint32_t M = (uint32_t)(__frcp_rn((float)D2) * 4294967296.f) - 1u;
   uint32_t out = ((D2 + 255u) / 510u) << 24;
   bool tie = false;
 #pragma unroll
   for (int c = 0; c < 3; c++) {
     const uint32_t s = (src >> (8 * c)) & 0xFFu, d = (dst >> (8 * c)) & 0xFFu;
     const uint32_t T = 2u * (s * k1 + d * k2) + D;           // 2 N + D < 2^27
-    uint32_t q = (uint32_t)((float)T * r);                    // floor(T / D2) give or take one
-    int rem = (int)T - (int)(q * D2);
-    if (rem < 0) { q--; rem += (int)D2; }
-    else if (rem >= (int)D2) { q++; rem -= (int)D2; }
-    tie = tie || rem == 0;
+    uint32_t q = __umulhi(T, M);
+    uint32_t rem = T - q * D2;                                // in [0, 2 D2)
+    if (rem >= D2) { q++; rem -= D2; }
+    tie = tie || rem == 0u;
     out |= q << (8 * c);
   }
   if (tie) return blend8_exact(dst, src);

@@ -60,6 +60,13 @@ __device__ __forceinline__ void fu_cp_async16(void *smem, const void *gmem) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gmem) : "memory");
 }
 
+__device__ __forceinline__ void fu_cp_async4(uint32_t sa, const void *gmem) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void fu_cp_async16s(uint32_t sa, const void *gmem) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gmem) : "memory");
+}
+
 // One row of the sweep.  GUARD: the unit reaches past the right edge of the canvas.
 // hb/hlu: the row above, unpacked (input); hx/hlc: this row, unpacked (output, becomes the next row's hb/hlu).
 template <int BPW, bool GUARD>
@@ -123,12 +130,14 @@ struct UnitPlan {
   bool tma_ok;              // the covering tile has tensor maps
   uint32_t tile;            // the covering tile (index into tiles / maps)
   int32_t c0, c1;           // TMA coordinates of the predictor row's first word: word in the source row, source row
+  uint32_t iv, iv_left;     // plan mode: the intervals of the unit's column and of the column left of it that hold row max(ya - 1, 0)
+  uint32_t u, src_kind;     // plan mode: index of the unit's record; 4 = one TMA box from the tile, 8 = background only, 0 = prepared rows
 };
 
 // Rows and columns of unit u (pure arithmetic).
-__device__ __forceinline__ void unit_geom(const FusedParams &p, const uint32_t u, UnitPlan &pl) {
+__device__ __forceinline__ void unit_geom(const FusedParams &p, const uint32_t u, UnitPlan &pl, const uint32_t seg_of_rec = 0xffffffffu) {
   const uint32_t band = u / p.nseg;
-  pl.seg = u - band * p.nseg;
+  pl.seg = seg_of_rec != 0xffffffffu ? seg_of_rec : u - band * p.nseg;   // plan mode deals a band's units out of order
   const uint32_t band_abs = p.band0 + band;
   const int ya = max((int)p.y_begin, (int)(band_abs * FU_R));
   const int yb = min((int)p.y_end, (int)((band_abs + 1) * FU_R));
@@ -208,6 +217,7 @@ __global__ void fused_plan_kernel(const FusedParams p, PlanRec *recs, const uint
   recs[u] = r;
 }
 
+enum : uint32_t { PK_TMA = 4u, PK_BG = 8u, PK_COPY = 16u, PK_LEFT = 32u };   // plan mode: flags of a record, see unit_class()
 struct PlanRaw { uint4 a, b; };
 __device__ __forceinline__ PlanRaw plan_fetch(const FusedParams &p, const uint32_t u) {
   const uint4 *q = reinterpret_cast<const uint4 *>(reinterpret_cast<const PlanRec *>(p.plans) + u);
@@ -215,9 +225,20 @@ __device__ __forceinline__ PlanRaw plan_fetch(const FusedParams &p, const uint32
   r.a = __ldg(q); r.b = __ldg(q + 1);
   return r;
 }
+template <bool PLAN>
 __device__ __forceinline__ UnitPlan plan_make(const FusedParams &p, const uint32_t u, const PlanRaw &r) {
   UnitPlan pl;
+  if (PLAN) {   // see the record layout above unit_class()
+    unit_geom(p, u, pl, r.a.z);
+    pl.iv = 0; pl.iv_left = 0; pl.u = u; pl.src_kind = r.b.x;
+    pl.fast_src = reinterpret_cast<const uint8_t *>(((unsigned long long)r.a.y << 32) | r.a.x);   // PK_COPY, PK_LEFT
+    pl.fast_pitch = r.a.w; pl.list = nullptr; pl.n_list = 0;
+    pl.tma_ok = (r.b.x & PK_TMA) != 0u; pl.halo_fast = pl.tma_ok; pl.left_fast = (r.b.x & PK_LEFT) != 0u;
+    pl.tile = r.b.y; pl.c0 = (int32_t)r.b.z; pl.c1 = (int32_t)r.b.w;
+    return pl;
+  }
   unit_geom(p, u, pl);
+  pl.iv = 0; pl.iv_left = 0; pl.u = u; pl.src_kind = 0;
   pl.fast_src = reinterpret_cast<const uint8_t *>(((unsigned long long)r.a.y << 32) | r.a.x);
   pl.fast_pitch = r.a.z;
   pl.list = p.bin_tiles + r.a.w;
@@ -229,8 +250,325 @@ __device__ __forceinline__ UnitPlan plan_make(const FusedParams &p, const uint32
   return pl;
 }
 
-// ---- phase A: raw stash <- composited pixels of rows ya-1 .. yb-1 (cp.async left in flight) ----
+// ---- plan mode: the host's interval plan (strip_plan.cu) instead of bins --------------------------------------
+// A unit is one 128-word column of the plan.  Three kernels: fused_plan_iv_kernel classifies the units of a band
+// (one CTA per band) and writes their records; fused_prep_kernel (a warp per unit) normalises and composites the
+// rows of the units that are not a plain window of one tile, and the left pixels that cannot be copied from the
+// unit's own tile, into scratch; the fused kernel then gets every unit by one bulk copy (or a few cp.async) and
+// every unit costs it the same -- nobody waits for a warp that is still blending.
+//
+// Record of unit u (32 bytes, as two uint4 a, b); b.x = flags:
+//   PK_TMA     the unit and its predictor row are a window of one tile that has tensor maps: b.y = tile,
+//              b.z, b.w = box coordinates
+//   PK_COPY    the same without tensor maps or with a source offset that is not a multiple of 16 bytes (a tiled TMA
+//              load faults on it): the lanes copy the window with cp.async; a.x, a.y = address of the window's
+//              first word, a.w = pitch
+//   PK_BG      background only: filled by the lanes
+//   none       prepared rows: one bulk copy of the unit's slot in unit_rows
+//   PK_LEFT    the pixel left of the unit comes from the same source (the tile's row, or background); with PK_TMA,
+//              a.x, a.y, a.w are then as for PK_COPY.  Otherwise it is read from unit_left.
+// a.z = the unit's column.  Where a.x, a.y hold no address they are the intervals of the unit's column and of the
+// column left of it that hold the predictor row (for the prepare kernel); PK_COPY keeps the latter in b.y.
+
+static constexpr int FU_PREP_WORDS = (FU_R + 1) * FU_SW;   // a unit's slot of prepared rows
+static constexpr int FU_LEFT_WORDS = (FU_R + 1) * 2;       // a unit's left pixels
+static constexpr int FP_ROWS = 1;           // prepare kernel: rows per task
+static constexpr uint32_t FP_LEFT = 15u;   // prepare kernel: a task is unit << 4 | part; parts 0 .. (FU_R + 1) / rows - 1 are rows, FP_LEFT the left pixels
+
+struct IvCur {
+  uint32_t idx, end_idx;
+  uint32_t y_end, kind, tile, list_off, n_list, flags;
+  int32_t cw, cy;
+  const uint8_t *pix;   // SK_DIRECT, SK_SHIFT: the tile's rows
+  uint32_t pitch;
+};
+__device__ __forceinline__ void iv_load(const FusedParams &p, IvCur &c) {
+  const uint4 *q = reinterpret_cast<const uint4 *>(p.ivs) + 2u * c.idx;
+  const uint4 a = __ldg(q), b = __ldg(q + 1);
+  c.y_end = a.x; c.kind = a.y; c.tile = a.z; c.cw = (int32_t)a.w;
+  c.cy = (int32_t)b.x; c.list_off = b.y; c.n_list = b.z; c.flags = b.w;
+  if (c.kind == SK_DIRECT || c.kind == SK_SHIFT) {
+    const DevTile *t = p.tiles + c.tile;
+    c.pix = t->pix; c.pitch = t->pitch;
+  }
+}
+__device__ __forceinline__ void iv_seek(const FusedParams &p, IvCur &c, int y) {
+  while ((uint32_t)y >= c.y_end && c.idx + 1u < c.end_idx) { c.idx++; iv_load(p, c); }
+}
+// index of the interval of column col that holds row y
+__device__ __forceinline__ uint32_t iv_find(const FusedParams &p, uint32_t col, uint32_t y) {
+  uint32_t lo = __ldg(p.col_start + col), hi = __ldg(p.col_start + col + 1) - 1u;
+  while (lo < hi) {
+    const uint32_t mid = (lo + hi) >> 1;
+    if (__ldg(reinterpret_cast<const uint32_t *>(p.ivs) + 8u * mid) > y) hi = mid; else lo = mid + 1u;
+  }
+  return lo;
+}
+
+// The record of the unit (column seg, rows [ya, yb)); returns its class for the dealing order:
+// 0: some row is composited, 1: prepared from copies and background, 2: needs no preparation.
+__device__ __forceinline__ uint32_t unit_class(const FusedParams &p, uint32_t seg, int ya, int yb, PlanRaw &r) {
+  const uint32_t y_first = (uint32_t)max(ya - 1, 0);
+  IvCur c;
+  c.idx = iv_find(p, seg, y_first); c.end_idx = __ldg(p.col_start + seg + 1);
+  iv_load(p, c);
+  const uint32_t iv_left = seg ? iv_find(p, seg - 1u, y_first) : 0u;
+  r.a = make_uint4(c.idx, iv_left, seg, 0u);
+  r.b = make_uint4(0u, 0u, 0u, 0u);
+  const bool whole = c.y_end >= (uint32_t)yb;   // one interval holds the predictor row and the unit
+  // does the column left of the unit show the same source in these rows?  (column 0: the pixel is 0, read from unit_left)
+  bool left_same = false;
+  if (seg && whole) {
+    const uint4 *q = reinterpret_cast<const uint4 *>(p.ivs) + 2u * iv_left;
+    const uint4 la = __ldg(q);
+    left_same = la.x >= (uint32_t)yb && (c.kind == SK_BG ? la.y == SK_BG
+                                                           : (la.y == SK_DIRECT || la.y == SK_SHIFT) && la.z == c.tile);
+  }
+  if (whole && c.kind == SK_BG) {
+    r.b.x = PK_BG | (left_same ? PK_LEFT : 0u);
+    return 2u;
+  }
+  if (whole && ya > 0 && (c.kind == SK_DIRECT || c.kind == SK_SHIFT) && c.list_off == (uint32_t)FU_SW) {
+    const unsigned long long src = reinterpret_cast<unsigned long long>(c.pix + (size_t)(ya - 1 + c.cy) * c.pitch) + 4ull * (unsigned)c.cw;
+    if (c.kind == SK_DIRECT && p.maps != nullptr && p.tiles[c.tile].pad != 0u) {
+      r.b = make_uint4(PK_TMA, c.tile, (uint32_t)c.cw, (uint32_t)(ya - 1 + c.cy));
+      if (left_same) { r.a.x = (uint32_t)src; r.a.y = (uint32_t)(src >> 32); r.a.w = c.pitch; r.b.x |= PK_LEFT; }
+    } else {
+      r.a.x = (uint32_t)src; r.a.y = (uint32_t)(src >> 32); r.a.w = c.pitch;
+      r.b.x = PK_COPY | (left_same ? PK_LEFT : 0u); r.b.y = iv_left;
+    }
+    return 2u;
+  }
+  uint32_t cls = 1u;
+  for (;;) {
+    if (c.kind == SK_COMP) cls = 0u;
+    if (c.y_end >= (uint32_t)yb || c.idx + 1u >= c.end_idx) break;
+    c.idx++; iv_load(p, c);
+  }
+  return cls;
+}
+
 template <int BPW>
+__global__ void __launch_bounds__(256) fused_plan_iv_kernel(const FusedParams p, PlanRec *recs, const uint32_t FP_PARTS) {
+  __shared__ uint32_t cnt[4], pos[4], list_base;
+  const uint32_t band = blockIdx.x, band_abs = p.band0 + band;
+  const int ya = max((int)p.y_begin, (int)(band_abs * FU_R)), yb = min((int)p.y_end, (int)((band_abs + 1) * FU_R));
+  if (threadIdx.x < 4) { cnt[threadIdx.x] = 0; pos[threadIdx.x] = 0; }
+  __syncthreads();
+  // A band's units are dealt out in record order: those that need preparing go first (composited rows ahead of
+  // copied ones, then those that only need their left pixels), so that they form one range of the band's records.
+  PlanRaw r;
+  uint32_t cls0 = 0;   // this thread's first unit: classified once
+  for (uint32_t seg = threadIdx.x, i = 0; seg < p.nseg; seg += blockDim.x, i++) {
+    uint32_t cls = unit_class(p, seg, ya, yb, r);
+    if (cls == 2u && (r.b.x & PK_LEFT)) cls = 3u;
+    if (i == 0) cls0 = cls;
+    atomicAdd(&cnt[cls], 1u);
+  }
+  const PlanRaw r0 = r;
+  __syncthreads();
+  const uint32_t base[4] = {0u, cnt[0], cnt[0] + cnt[1], cnt[0] + cnt[1] + cnt[2]};
+  const uint32_t n_prep = base[3], first = band * p.nseg;
+  if (threadIdx.x == 0) {
+    const uint32_t nt = base[2] * (FP_PARTS + 1) + (n_prep - base[2]);
+    list_base = nt ? atomicAdd(p.prep_count, nt) : 0u;
+  }
+  uint4 *out = reinterpret_cast<uint4 *>(recs + first);
+  for (uint32_t seg = threadIdx.x, i = 0; seg < p.nseg; seg += blockDim.x, i++) {
+    uint32_t cls = cls0;
+    if (p.nseg > blockDim.x) {
+      cls = unit_class(p, seg, ya, yb, r);
+      if (cls == 2u && (r.b.x & PK_LEFT)) cls = 3u;
+    } else r = r0;
+    const uint32_t at = base[cls] + atomicAdd(&pos[cls], 1u);
+    out[2u * at] = r.a; out[2u * at + 1u] = r.b;
+  }
+  __syncthreads();
+  // tasks of the band: classes 0 and 1 (the first n_rows_units records) have FP_PARTS row parts and the left pixels,
+  // class 2 the left pixels only
+  const uint32_t n_rows_units = base[2], n_tasks = n_rows_units * (FP_PARTS + 1) + (n_prep - n_rows_units);
+  for (uint32_t j = threadIdx.x; j < n_tasks; j += blockDim.x) {
+    uint32_t task;
+    if (j < n_rows_units * (FP_PARTS + 1)) {
+      const uint32_t part = j % (FP_PARTS + 1);
+      task = ((first + j / (FP_PARTS + 1)) << 4) | (part == FP_PARTS ? FP_LEFT : part);
+    } else task = ((first + n_rows_units + (j - n_rows_units * (FP_PARTS + 1))) << 4) | FP_LEFT;
+    p.prep_list[list_base + j] = task;
+  }
+}
+
+struct FuCtx {   // what the generic compositor reads, by value (see compose_quad)
+  const DevTile *tiles;
+  uint32_t alpha_blend, bg_lo, bg_hi, canvas_w;
+};
+template <int BPW>
+static __device__ __noinline__ uint4 fu_compose_quad(const FuCtx c, const uint32_t *list, uint32_t n_list, int xw, int y) {
+  return compose_quad<BPW>(c, list, n_list, xw, y);
+}
+
+static constexpr int FP_LAYERS = 2;                        // layers of a row loaded together
+
+// One layer's words under this lane's quad: which of them the layer covers (bit j: word j), and their values.
+template <int BPW>
+__device__ __forceinline__ uint32_t layer_fetch(const DevTile *t, const int x, const int y, const int n_canvas, uint4 &s) {
+  constexpr int PX = 4 / BPW;
+  const int tx0 = t->x0, tx1 = t->x1;
+  uint32_t m = 0u;
+#pragma unroll
+  for (int i = 0; i < PX; i++)
+    if (x + i >= tx0 && x + i < tx1 && i * BPW < n_canvas) m |= (BPW == 2 ? 3u : 1u) << (i * BPW);
+  s = make_uint4(0u, 0u, 0u, 0u);
+  if (m) {
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(t->pix + (size_t)(y - t->y0 + t->sy0) * t->pitch) + (x - tx0 + t->sx0) * BPW;
+    if (m == 15u && (reinterpret_cast<uintptr_t>(src) & 15u) == 0) s = __ldg(reinterpret_cast<const uint4 *>(src));
+    else {
+      if (m & 1u) s.x = __ldg(src);
+      if (m & 2u) s.y = __ldg(src + 1);
+      if (m & 4u) s.z = __ldg(src + 2);
+      if (m & 8u) s.w = __ldg(src + 3);
+    }
+  }
+  return m;
+}
+// The blend of one layer into a quad: out of line, so that the kernel holds one copy of the arithmetic (with a
+// copy per layer and word the prepare kernel spent half its time waiting for instructions).
+template <int BPW>
+static __device__ __noinline__ uint4 layer_blend(uint4 v, const uint4 s, const uint32_t m) {
+  if (BPW == 1) {
+    if (m & 1u) v.x = blend8(v.x, s.x);
+    if (m & 2u) v.y = blend8(v.y, s.y);
+    if (m & 4u) v.z = blend8(v.z, s.z);
+    if (m & 8u) v.w = blend8(v.w, s.w);
+  } else {
+    if (m & 1u) { const uint2 a = blend16(make_uint2(v.x, v.y), make_uint2(s.x, s.y)); v.x = a.x; v.y = a.y; }
+    if (m & 4u) { const uint2 a = blend16(make_uint2(v.z, v.w), make_uint2(s.z, s.w)); v.z = a.x; v.w = a.y; }
+  }
+  return v;
+}
+template <int BPW>
+__device__ __forceinline__ void layer_apply(uint4 &v, const uint4 s, const uint32_t m, const bool overwrite) {
+  if (m == 0u) return;
+  if (overwrite) {
+    if (m & 1u) v.x = s.x;
+    if (m & 2u) v.y = s.y;
+    if (m & 4u) v.z = s.z;
+    if (m & 8u) v.w = s.w;
+  } else {
+    v = layer_blend<BPW>(v, s, m);
+  }
+}
+
+// Row y (>= 0) of the unit's column, composed from the interval c that holds it: one quad per lane.  All loads of
+// a row (up to FP_LAYERS layers at a time) are issued before the first blend.
+template <int BPW>
+__device__ __forceinline__ uint4 unit_compose_row(const FusedParams &p, const IvCur &c, const int xw0, const int y, const uint32_t lane) {
+  const int wmax = (int)p.canvas_w * BPW, qw = xw0 + 4 * (int)lane;
+  if (qw >= wmax) return make_uint4(0u, 0u, 0u, 0u);   // nothing right of the canvas
+  const int n_canvas = min(4, wmax - qw);               // words of this lane's quad that exist in the canvas
+  uint4 v = BPW == 2 ? make_uint4(p.bg_lo, p.bg_hi, p.bg_lo, p.bg_hi) : make_uint4(p.bg_lo, p.bg_lo, p.bg_lo, p.bg_lo);
+  if (c.kind == SK_DIRECT || c.kind == SK_SHIFT) {
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(c.pix + (size_t)(y + c.cy) * c.pitch) + c.cw + 4 * (int)lane;
+    const int n = min(n_canvas, (int)c.list_off - 4 * (int)lane);   // words that exist in the source row too
+    if (n == 4 && (reinterpret_cast<uintptr_t>(src) & 15u) == 0) v = __ldg(reinterpret_cast<const uint4 *>(src));
+    else { v.x = n > 0 ? __ldg(src) : 0u; v.y = n > 1 ? __ldg(src + 1) : 0u; v.z = n > 2 ? __ldg(src + 2) : 0u; v.w = n > 3 ? __ldg(src + 3) : 0u; }
+  } else if (c.kind == SK_COMP && (c.flags & 2u)) {
+    // every layer is in the output's format: word loads under a per-lane coverage mask
+    const int x = qw / BPW;
+    for (uint32_t k0 = 0; k0 < c.n_list; k0 += FP_LAYERS) {
+      uint4 s[FP_LAYERS];
+      uint32_t m[FP_LAYERS], ow = 0u;
+#pragma unroll
+      for (int k = 0; k < FP_LAYERS; k++) {
+        m[k] = 0u;
+        if (k0 + k < c.n_list) {
+          const DevTile *t = p.tiles + __ldg(p.lists + c.list_off + k0 + k);
+          if (p.alpha_blend == 0u || t->opaque) ow |= 1u << k;
+          m[k] = layer_fetch<BPW>(t, x, y, n_canvas, s[k]);
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < FP_LAYERS; k++) layer_apply<BPW>(v, s[k], m[k], (ow >> k) & 1u);
+    }
+  } else if (c.kind == SK_COMP) {
+    FuCtx cc;
+    cc.tiles = p.tiles; cc.alpha_blend = p.alpha_blend; cc.bg_lo = p.bg_lo; cc.bg_hi = p.bg_hi; cc.canvas_w = p.canvas_w;
+    v = fu_compose_quad<BPW>(cc, p.lists + c.list_off, c.n_list, qw, y);
+  }
+  if (n_canvas < 4) {
+    if (n_canvas < 2) v.y = 0u;
+    if (n_canvas < 3) v.z = 0u;
+    v.w = 0u;
+  }
+  return v;
+}
+
+// The pixel just left of the unit in rows ya-1 .. yb-1, through the plan of the column left of it (lane r: row
+// ya-1+r), into the unit's 2 (FU_R + 1) words of unit_left.
+template <int BPW>
+__device__ __forceinline__ void unit_left_plan(const FusedParams &p, const UnitPlan &pl, uint32_t *lcs, const uint32_t lane) {
+  if ((int)lane > pl.nrows) return;
+  const int y = pl.ya - 1 + (int)lane;
+  uint32_t c0 = 0u, c1 = 0u;
+  if (y >= 0 && pl.seg > 0u) {
+    IvCur h;
+    h.idx = pl.iv_left; h.end_idx = __ldg(p.col_start + pl.seg);
+    iv_load(p, h);
+    iv_seek(p, h, y);
+    if (h.kind == SK_BG) {
+      c1 = BPW == 2 ? p.bg_hi : p.bg_lo; c0 = p.bg_lo;
+    } else if (h.kind == SK_DIRECT || h.kind == SK_SHIFT) {
+      const uint32_t *lp = reinterpret_cast<const uint32_t *>(h.pix + (size_t)(y + h.cy) * h.pitch) + h.cw + FU_SW;
+      c1 = __ldg(lp - 1);
+      if (BPW == 2) c0 = __ldg(lp - 2);
+    } else {
+      FuCtx cc;
+      cc.tiles = p.tiles; cc.alpha_blend = p.alpha_blend; cc.bg_lo = p.bg_lo; cc.bg_hi = p.bg_hi; cc.canvas_w = p.canvas_w;
+      const uint4 v = fu_compose_quad<BPW>(cc, p.lists + h.list_off, h.n_list, pl.xw0 - 4, y);
+      c1 = v.w; c0 = v.z;
+    }
+  }
+  lcs[lane * 2] = BPW == 2 ? c0 : 0u;
+  lcs[lane * 2 + 1] = c1;
+}
+
+// The prepare kernel: a fixed grid of warps over the tasks the plan kernel listed.  A task is a unit and a part:
+// part k < FP_PARTS = rows ya-1+FP_ROWS k .. of the unit into its slot of unit_rows (FU_R + 1 rows of 128 words:
+// what the TMA box of a plain unit looks like), part FP_PARTS = the unit's left pixels.  Rows are split into parts
+// so that the machine is full of short, independent load chains.
+template <int BPW, int ROWS, int MINB>
+__global__ void __launch_bounds__(256, MINB) fused_prep_kernel(const FusedParams p) {
+  const uint32_t lane = threadIdx.x & 31u, n_warps = gridDim.x * (blockDim.x >> 5);
+  const uint32_t n_tasks = __ldg(p.prep_count);
+  for (uint32_t t = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); t < n_tasks; t += n_warps) {
+    const uint32_t task = __ldg(p.prep_list + t), u = task >> 4, part = task & 15u;
+    const PlanRaw r = plan_fetch(p, u);
+    const uint32_t flags = r.b.x;
+    UnitPlan pl;
+    unit_geom(p, u, pl, r.a.z);
+    if (part == FP_LEFT) {
+      pl.iv_left = (flags & PK_COPY) ? r.b.y : r.a.y;
+      unit_left_plan<BPW>(p, pl, p.unit_left + (size_t)u * FU_LEFT_WORDS, lane);
+      continue;
+    }
+    IvCur c;
+    c.idx = r.a.x; c.end_idx = __ldg(p.col_start + pl.seg + 1);
+    iv_load(p, c);
+    const int r0 = (int)part * ROWS, r1 = min(r0 + ROWS, pl.nrows + 1);
+    uint32_t *dst = p.unit_rows + (size_t)u * FU_PREP_WORDS + r0 * FU_SW + 4u * lane;
+    for (int rr = r0; rr < r1; rr++, dst += FU_SW) {
+      const int y = pl.ya - 1 + rr;
+      uint4 v = make_uint4(0u, 0u, 0u, 0u);   // previousLine === null above row 0
+      if (y >= 0) {
+        iv_seek(p, c, y);
+        v = unit_compose_row<BPW>(p, c, pl.xw0, y, lane);
+      }
+      *reinterpret_cast<uint4 *>(dst) = v;
+    }
+  }
+}
+
+// ---- phase A: raw stash <- composited pixels of rows ya-1 .. yb-1 (cp.async left in flight) ----
+template <int BPW, bool PLAN>
 __device__ __forceinline__ bool unit_load(const FusedParams &p, const UnitPlan &pl, uint32_t *stash, const uint32_t bar,
                                           const uint32_t lane) {
   uint32_t *raw = stash, *lcs = stash + FU_RAW_WORDS;
@@ -241,6 +579,60 @@ __device__ __forceinline__ bool unit_load(const FusedParams &p, const UnitPlan &
   // A plain window of one tile, predictor row included: ONE 2-D TMA box (128 words x 9 rows) from the tile's tensor
   // map, issued by lane 0, completing on the stash's mbarrier.  (Rows past the unit and words past the canvas or
   // the tile are loaded or zero-filled and never used.)
+  if (PLAN) {
+    // one TMA box of the unit's tile, one bulk copy of its prepared rows, cp.async by the lanes, or background
+    const uint32_t k = pl.src_kind;
+    const bool bulk = (k & (PK_BG | PK_COPY)) == 0u;
+    if (bulk) {
+      if (lane == 0u) {
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the emit's reads of this stash, then the bulk write
+        mbar_arrive_tx(bar, FU_PREP_WORDS * 4);
+        if (k & PK_TMA)
+          tma_box_2d((uint32_t)__cvta_generic_to_shared(raw), reinterpret_cast<const uint8_t *>(p.maps) + (size_t)pl.tile * 384u + 256u,
+                     pl.c0, pl.c1, bar);
+        else
+          bulk_copy((uint32_t)__cvta_generic_to_shared(raw), p.unit_rows + (size_t)pl.u * FU_PREP_WORDS, FU_PREP_WORDS * 4, bar);
+      }
+    } else if (k & PK_COPY) {
+      const uint8_t *src = fast_src + 16u * lane;
+      const uint32_t sa = (uint32_t)__cvta_generic_to_shared(raw + 4 * lane);
+      if (((reinterpret_cast<uintptr_t>(fast_src) | fast_pitch) & 15u) == 0) {
+        for (int rr = 0; rr <= nrows; rr++, src += fast_pitch) fu_cp_async16s(sa + (uint32_t)rr * (FU_SW * 4), src);
+      } else {
+        for (int rr = 0; rr <= nrows; rr++, src += fast_pitch) {
+#pragma unroll
+          for (int j = 0; j < 4; j++) fu_cp_async4(sa + (uint32_t)rr * (FU_SW * 4) + 4u * j, src + 4 * j);
+        }
+      }
+    } else {
+      uint4 v = make_uint4(0u, 0u, 0u, 0u);
+      if (qw < wmax) {
+        v = BPW == 2 ? make_uint4(p.bg_lo, p.bg_hi, p.bg_lo, p.bg_hi) : make_uint4(p.bg_lo, p.bg_lo, p.bg_lo, p.bg_lo);
+        if (qw + 1 >= wmax) v.y = 0u;
+        if (qw + 2 >= wmax) v.z = 0u;
+        if (qw + 3 >= wmax) v.w = 0u;
+      }
+      uint32_t *dst = raw + 4 * lane;
+      *reinterpret_cast<uint4 *>(dst) = ya == 0 ? make_uint4(0u, 0u, 0u, 0u) : v;   // previousLine === null
+      for (int rr = 0; rr < nrows; rr++) { dst += FU_SW; *reinterpret_cast<uint4 *>(dst) = v; }
+    }
+    if ((int)lane <= nrows) {   // the pixel left of the unit, rows ya-1 .. yb-1
+      const uint32_t sa = (uint32_t)__cvta_generic_to_shared(lcs + 2 * lane);
+      if (!(k & PK_LEFT)) {
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sa), "l"(p.unit_left + (size_t)pl.u * FU_LEFT_WORDS + 2 * lane) : "memory");
+      } else if (k & PK_BG) {
+        const bool none = ya == 0 && lane == 0u;
+        lcs[2 * lane] = none || BPW == 1 ? 0u : p.bg_lo;
+        lcs[2 * lane + 1] = none ? 0u : (BPW == 2 ? p.bg_hi : p.bg_lo);
+      } else {
+        const uint8_t *lp = fast_src + (size_t)lane * fast_pitch;
+        if (BPW == 2) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sa), "l"(lp - 8) : "memory");
+        else fu_cp_async4(sa + 4u, lp - 4);
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    return bulk;
+  }
   const bool tma = pl.tma_ok && pl.halo_fast && ya > 0;
   if (tma) {
     if (lane == 0u) {
@@ -427,7 +819,7 @@ __device__ __forceinline__ void unit_emit(const FusedParams &p, const UnitRef &r
 // (launch_fused checks it; the cooperative launch makes the whole grid resident).  So all of B is taken;
 // its units are swept (held by blocked or finished warps), B is complete, and the warps waiting for it
 // are not blocked after all.
-template <int BPW>
+template <int BPW, bool PLAN>
 __global__ void __launch_bounds__(FU_WARPS * 32, 1) fused_kernel(const FusedParams p) {
   extern __shared__ __align__(16) uint32_t fu_smem[];
   const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
@@ -465,8 +857,8 @@ __global__ void __launch_bounds__(FU_WARPS * 32, 1) fused_kernel(const FusedPara
 
   uint32_t u = blockIdx.x * FU_WARPS + warp;  // first unit: the warp's own index; tickets continue from n_warps
   if (u < n_units) {
-    UnitPlan plan = plan_make(p, u, plan_fetch(p, u));
-    bool cur_tma = unit_load<BPW>(p, plan, cur_stash, cur_bar, lane);
+    UnitPlan plan = plan_make<PLAN>(p, u, plan_fetch(p, u));
+    bool cur_tma = unit_load<BPW, PLAN>(p, plan, cur_stash, cur_bar, lane);
     UnitRef prev;
     prev.seg = 0; prev.ya = 0; prev.nrows = 0;
     bool have_prev = false;
@@ -493,8 +885,8 @@ __global__ void __launch_bounds__(FU_WARPS * 32, 1) fused_kernel(const FusedPara
       { const uint32_t sw = cur_bar; cur_bar = prev_bar; prev_bar = sw; }
       { const uint32_t sw = cur_par; cur_par = prev_par; prev_par = sw; }
       if (!more) break;
-      plan = plan_make(p, u, raw_next);
-      cur_tma = unit_load<BPW>(p, plan, cur_stash, cur_bar, lane);
+      plan = plan_make<PLAN>(p, u, raw_next);
+      cur_tma = unit_load<BPW, PLAN>(p, plan, cur_stash, cur_bar, lane);
     }
     const uint32_t ft = unit_wait(p, prev, lane);
     unit_emit<BPW>(p, prev, prev_stash, prev_pf, lane, ft, pack_winners(ft, lane), 0, prev.nrows);
@@ -543,18 +935,23 @@ cudaError_t launch_compose_canvas(const FusedParams &p, bool out16, uint8_t *can
 }
 
 size_t fused_plan_bytes(uint32_t n_units) { return (size_t)n_units * sizeof(PlanRec); }
+size_t fused_unit_rows_bytes(uint32_t n_units) { return (size_t)n_units * FU_PREP_WORDS * 4; }
+size_t fused_unit_left_bytes(uint32_t n_units) { return (size_t)n_units * (FU_LEFT_WORDS + FU_R + 2) * 4; }   // + the list of tasks
+
+template <int BPW, bool PLAN>
+static cudaError_t fused_occupancy(int *occ) {
+  static PerDevice once;   // shared-memory opt-in and occupancy, per device
+  return once.get(occ, [](int *v) {
+    cudaError_t e = cudaFuncSetAttribute(fused_kernel<BPW, PLAN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FU_CTA_SMEM);
+    return e != cudaSuccess ? e : cudaOccupancyMaxActiveBlocksPerMultiprocessor(v, fused_kernel<BPW, PLAN>, FU_WARPS * 32, FU_CTA_SMEM);
+  });
+}
 
 cudaError_t launch_fused(const FusedParams &p, bool out16, int sm_count, cudaStream_t st) {
-  static PerDevice once8, once16;   // shared-memory opt-in and occupancy, per device
+  const bool plan = p.ivs != nullptr;
   int occ = 0;
-  cudaError_t pe = out16 ? once16.get(&occ, [](int *v) {
-                               cudaError_t e = cudaFuncSetAttribute(fused_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FU_CTA_SMEM);
-                               return e != cudaSuccess ? e : cudaOccupancyMaxActiveBlocksPerMultiprocessor(v, fused_kernel<2>, FU_WARPS * 32, FU_CTA_SMEM);
-                             })
-                         : once8.get(&occ, [](int *v) {
-                               cudaError_t e = cudaFuncSetAttribute(fused_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FU_CTA_SMEM);
-                               return e != cudaSuccess ? e : cudaOccupancyMaxActiveBlocksPerMultiprocessor(v, fused_kernel<1>, FU_WARPS * 32, FU_CTA_SMEM);
-                             });
+  cudaError_t pe = out16 ? (plan ? fused_occupancy<2, true>(&occ) : fused_occupancy<2, false>(&occ))
+                         : (plan ? fused_occupancy<1, true>(&occ) : fused_occupancy<1, false>(&occ));
   if (pe != cudaSuccess) return pe;
   if (occ < 1) return cudaErrorLaunchOutOfResources;
   if (occ > FU_MAX_CTAS) occ = FU_MAX_CTAS;
@@ -564,15 +961,26 @@ cudaError_t launch_fused(const FusedParams &p, bool out16, int sm_count, cudaStr
   // wait-freedom needs 2 x warps > units per band (see fused_kernel); wider rows take the two-pass path
   if (2u * grid * FU_WARPS <= p.nseg) return cudaErrorInvalidConfiguration;
   PlanRec *recs = reinterpret_cast<PlanRec *>(p.plans);
-  if (out16) fused_plan_kernel<2><<<(n_units + 255u) / 256u, 256, 0, st>>>(p, recs, n_units);
-  else fused_plan_kernel<1><<<(n_units + 255u) / 256u, 256, 0, st>>>(p, recs, n_units);
+  if (plan) {
+    if (n_units >= (1u << 28)) return cudaErrorInvalidConfiguration;   // a task is unit << 4 | part
+    if (out16) fused_plan_iv_kernel<2><<<p.n_bands, 256, 0, st>>>(p, recs, (FU_R + 1) / FP_ROWS);
+    else fused_plan_iv_kernel<1><<<p.n_bands, 256, 0, st>>>(p, recs, (FU_R + 1) / FP_ROWS);
+    // a fixed grid of warps over the listed tasks (measured: 1 or 3 rows per task and 3 to 6 CTAs per SM all take the
+    // same time on C3 -- the kernel is bound by the blend arithmetic, not by occupancy)
+    if (out16) fused_prep_kernel<2, FP_ROWS, 4><<<sm_count * 4, 256, 0, st>>>(p);
+    else fused_prep_kernel<1, FP_ROWS, 4><<<sm_count * 4, 256, 0, st>>>(p);
+  } else {
+    if (out16) fused_plan_kernel<2><<<(n_units + 255u) / 256u, 256, 0, st>>>(p, recs, n_units);
+    else fused_plan_kernel<1><<<(n_units + 255u) / 256u, 256, 0, st>>>(p, recs, n_units);
+  }
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   // Cooperative launch: the runtime guarantees that every CTA of the grid is resident (or fails),
   // which the wait-freedom argument above fused_kernel relies on.
   FusedParams pp = p;
   void *args[] = {&pp};
-  const void *fn = out16 ? (const void *)fused_kernel<2> : (const void *)fused_kernel<1>;
+  const void *fn = out16 ? (plan ? (const void *)fused_kernel<2, true> : (const void *)fused_kernel<2, false>)
+                         : (plan ? (const void *)fused_kernel<1, true> : (const void *)fused_kernel<1, false>);
   return cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(FU_WARPS * 32), args, FU_CTA_SMEM, st);
 }
 

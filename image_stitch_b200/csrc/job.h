@@ -85,6 +85,7 @@ struct stitch_job {
   bool strip_ok = false;
   // band buffers
   uint8_t *d_plans = nullptr; size_t plans_bytes = 0;  // fused kernel: per-unit plan records
+  uint8_t *d_unit_left = nullptr; size_t unit_left_bytes = 0;  // fused kernel, plan mode: left pixels of every unit
   uint8_t *d_defl = nullptr; size_t defl_bytes = 0;    // deflate: compressed band / chunk (two buffers, used in turn)
   uint8_t *d_defl_b = nullptr; size_t defl_b_bytes = 0;
   uint8_t *d_pack[2] = {nullptr, nullptr}; size_t pack_bytes[2] = {0, 0};   // PNG rows of a chunk without row padding: one flat download

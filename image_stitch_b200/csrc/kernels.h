@@ -63,6 +63,7 @@ struct FilterParams {
 // Fused composite + filter-select (fused.cu).  Bins are FB_R rows x FB_SWW words; each bin's tile list
 // also holds tiles touching the row above / the pixel left of it.  Units (one per warp) are
 // fused_unit_rows() x fused_unit_words() and never straddle a bin.
+struct StripIv;
 struct FusedParams {
   const DevTile *tiles;
   const uint32_t *bin_start;
@@ -79,12 +80,24 @@ struct FusedParams {
   void *plans;                // fused_plan_bytes(n_bands * nseg) of scratch: per-unit plan records
   uint32_t single_bin;        // 1: bin_start/bin_tiles describe one bin that covers the whole canvas
   const void *maps;           // per tile three 128-byte CUtensorMaps (boxes of 1, 4 and 9 rows of 128 words), or nullptr
+  // The host's interval plan (strip_plan.cu), or nullptr.  With it the kernel needs no bins: a unit is one 128-word
+  // column of the plan, its rows are composed interval by interval (background / one tile / layers that all span
+  // the column / generic), and a band's units are dealt out most expensive first.
+  const StripIv *ivs;
+  const uint32_t *col_start;
+  const uint32_t *lists;
+  uint32_t *unit_rows;        // plan mode scratch: fused_unit_rows_bytes(n_units), prepared rows of the units that need them
+  uint32_t *unit_left;        // plan mode scratch: fused_unit_left_bytes(n_units), the pixels left of every unit | prep_list
+  uint32_t *prep_list;        // plan mode scratch (tail of unit_left's buffer): the prepare kernel's tasks
+  uint32_t *prep_count;       // zeroed: entries of prep_list
   uint8_t *out;               // row r: filter byte at out + r*out_pitch + lead
   size_t out_pitch;
   uint32_t lead;
 };
 cudaError_t launch_fused(const FusedParams &p, bool out16, int sm_count, cudaStream_t st);
 size_t fused_plan_bytes(uint32_t n_units);
+size_t fused_unit_rows_bytes(uint32_t n_units);
+size_t fused_unit_left_bytes(uint32_t n_units);
 cudaError_t launch_compose_canvas(const FusedParams &p, bool out16, uint8_t *canvas, size_t pitch, uint32_t ys,
                                   uint32_t ye, cudaStream_t st);
 uint32_t fused_rows_per_band();
@@ -108,8 +121,8 @@ struct StripIv {
   uint32_t tile;              // SK_DIRECT, SK_SHIFT: index into tiles / maps
   int32_t cw, cy;             // SK_DIRECT, SK_SHIFT: the box's first word is word cw of source row (y + cy)
   uint32_t list_off, n_list;  // SK_COMP: tiles touching the column in this interval, back to front (into lists)
-                              // SK_SHIFT: list_off = words of the box that exist in the source row (<= 256)
-  uint32_t pad;               // SK_COMP: 1 = every tile of the list is in the output's format and spans the whole column
+                              // SK_DIRECT, SK_SHIFT: list_off = words of the box that exist in the source row (<= 128)
+  uint32_t pad;               // SK_COMP: bit 1 = every tile of the list is in the output's format, bit 0 = and spans the whole column
 };
 enum StripKind : uint32_t { SK_BG = 0, SK_DIRECT = 1, SK_COMP = 2, SK_SHIFT = 3 };
 struct StripParams {

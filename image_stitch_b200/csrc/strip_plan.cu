@@ -130,17 +130,18 @@ int stitch_build_strip_plan(stitch_job *job, std::vector<DevTile> &dt, const std
           iv.cw = (int32_t)((X0 - t.x0 + t.sx0) * (int32_t)bpw);
           iv.cy = t.sy0 - t.y0;
           // a tiled TMA load needs its start coordinate on a 16-byte boundary (it faults otherwise: measured)
-          if (direct_ok[cur.back()] && (iv.cw & 3) == 0) iv.kind = SK_DIRECT;
-          else {
-            iv.kind = SK_SHIFT;
-            iv.list_off = std::min<uint32_t>(strip_box_words(), src_words[cur.back()] - (uint32_t)iv.cw);
-          }
+          iv.kind = direct_ok[cur.back()] && (iv.cw & 3) == 0 ? SK_DIRECT : SK_SHIFT;
+          iv.list_off = std::min<uint32_t>(strip_box_words(), src_words[cur.back()] - (uint32_t)iv.cw);
         } else {
           iv.kind = SK_COMP;
           iv.n_list = (uint32_t)cur.size();
-          bool simple = true;   // every layer is in the output's own format and spans the whole column: no per-pixel tests
-          for (uint32_t k : cur) simple = simple && dt[k].fmt == native && dt[k].x0 <= X0 && dt[k].x1 >= X1 && (dt[k].pitch & 3u) == 0;
-          iv.pad = simple ? 1u : 0u;
+          // bit 1: every layer is in the output's own format (word loads); bit 0: and spans the whole column (no per-pixel tests)
+          bool words = true, spans = true;
+          for (uint32_t k : cur) {
+            words = words && dt[k].fmt == native && (dt[k].pitch & 3u) == 0;
+            spans = spans && dt[k].x0 <= X0 && dt[k].x1 >= X1;
+          }
+          iv.pad = (words && spans ? 1u : 0u) | (words ? 2u : 0u);
         }
       }
       // merge with the interval above when it asks for the same thing

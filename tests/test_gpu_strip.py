@@ -13,14 +13,20 @@ from image_stitch_b200 import _native, synth
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(params=["unit", "strip"], autouse=True)
+@pytest.fixture(params=["unit", "unit_plan", "via_canvas", "strip"], autouse=True)
 def kernel(request, monkeypatch):
-    """Every case runs through both composite+filter kernels: the default unit kernel (csrc/fused.cu) and the
-    row-pipelined one (csrc/strip.cu, STITCH_STRIP=1; the library reads the variable at every call)."""
+    """Every case runs through every composite+filter route: the unit kernel (csrc/fused.cu) as the library picks
+    its mode, the unit kernel in plan mode for every band (STITCH_SINGLE_PASS=2), busy bands through the canvas
+    (STITCH_SINGLE_PASS=0), and the row-pipelined kernel (csrc/strip.cu, STITCH_STRIP=1).  The library reads the
+    variables at every call."""
+    monkeypatch.delenv("STITCH_STRIP", raising=False)
+    monkeypatch.delenv("STITCH_SINGLE_PASS", raising=False)
     if request.param == "strip":
         monkeypatch.setenv("STITCH_STRIP", "1")
-    else:
-        monkeypatch.delenv("STITCH_STRIP", raising=False)
+    elif request.param == "unit_plan":
+        monkeypatch.setenv("STITCH_SINGLE_PASS", "2")
+    elif request.param == "via_canvas":
+        monkeypatch.setenv("STITCH_SINGLE_PASS", "0")
     return request.param
 
 
