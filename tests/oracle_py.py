@@ -26,7 +26,7 @@ class OrcTile(C.Structure):
 
 
 def build(force: bool = False) -> str:
-    srcs = [os.path.join(_ORACLE_DIR, f) for f in ("oracle.c", "jpeg_oracle.c", "oracle.h", "Makefile")]
+    srcs = [os.path.join(_ORACLE_DIR, f) for f in ("oracle.c", "jpeg_oracle.c", "jpeg_decode_oracle.c", "oracle.h", "Makefile")]
     stale = not os.path.exists(_LIB) or any(os.path.getmtime(s) > os.path.getmtime(_LIB) for s in srcs if os.path.exists(s))
     if force or stale:
         subprocess.run(["make", "-C", _ORACLE_DIR, "-B" if force else "-s"], check=True, capture_output=True)
@@ -255,3 +255,39 @@ def jpeg_file(rgba, width, height, quality):
     """Whole JPEG file by the oracle: header + entropy segments + EOI."""
     r = np.ascontiguousarray(rgba, dtype=np.uint8).reshape(height, width * 4)
     return jpeg_header(width, height, quality) + jpeg_encode_rows(r, width, height, 0, height, quality) + b"\xff\xd9"
+
+
+# ---- JPEG decode (oracle/jpeg_decode_oracle.c) ----------------------------------------------
+def _jdec_setup():
+    l = lib()
+    if getattr(l, "_jdec_ready", False):
+        return l
+    vp, sz = C.c_void_p, C.c_size_t
+    l.jdec_info.argtypes = [vp, sz, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
+    l.jdec_info.restype = C.c_int
+    l.jdec_decode.argtypes = [vp, sz, vp, sz]
+    l.jdec_decode.restype = C.c_int
+    l.jdec_message.argtypes = [C.c_int]
+    l.jdec_message.restype = C.c_char_p
+    l._jdec_ready = True
+    return l
+
+
+class JpegDecodeError(Exception):
+    pass
+
+
+def jpeg_decode(data: bytes):
+    """Baseline JPEG -> (H, W, 4) RGBA8 or (H, W) gray8, as libjpeg-turbo's default path gives it; raises
+    JpegDecodeError with the decoder's message."""
+    l = _jdec_setup()
+    buf = np.frombuffer(bytes(data), dtype=np.uint8)
+    w, h, ch = C.c_uint32(), C.c_uint32(), C.c_uint32()
+    rc = l.jdec_info(_p(buf), buf.size, C.byref(w), C.byref(h), C.byref(ch))
+    if rc:
+        raise JpegDecodeError(l.jdec_message(rc).decode())
+    out = np.zeros(h.value * w.value * ch.value, dtype=np.uint8)
+    rc = l.jdec_decode(_p(buf), buf.size, _p(out), out.size)
+    if rc:
+        raise JpegDecodeError(l.jdec_message(rc).decode())
+    return out.reshape(h.value, w.value, 4) if ch.value == 4 else out.reshape(h.value, w.value)
