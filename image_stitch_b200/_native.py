@@ -13,6 +13,7 @@ from typing import Optional
 _LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libstitch_b200.so")
 
 STITCH_OK = 0
+E_JPEG = -11
 E_INVALID, E_CUDA, E_NOMEM, E_FILTER, E_COLOR, E_TRUNCATED, E_STATE, E_CAPACITY, E_INFLATE, E_NODEVICE = (
     -1, -2, -3, -4, -5, -6, -7, -8, -9, -10)
 OUT_PNG_FILTERED, OUT_RAW_RGBA, OUT_JPEG_ENTROPY, OUT_PNG_DEFLATE = 0, 1, 2, 3
@@ -24,6 +25,7 @@ EXPORTS = [
     "stitch_job_status", "stitch_decode_image", "stitch_filter_rows", "stitch_jpeg_header",
     "stitch_job_inflate", "stitch_inflate", "stitch_filter_rows_noalloc",
     "stitch_selftest_blend", "stitch_selftest_blend8_samples",
+    "stitch_jpeg_info", "stitch_job_add_tile_jpeg", "stitch_decode_jpeg",
 ]
 
 
@@ -107,6 +109,9 @@ def load() -> C.CDLL:
     lib.stitch_job_status.argtypes = [vp]
     lib.stitch_decode_image.argtypes = [vp, C.POINTER(TileDesc), vp, sz, vp, sz, C.POINTER(sz)]
     lib.stitch_filter_rows.argtypes = [vp, vp, vp, C.c_uint32, sz, C.c_uint32, vp, sz]
+    lib.stitch_jpeg_info.argtypes = [vp, vp, sz, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
+    lib.stitch_job_add_tile_jpeg.argtypes = [vp, C.POINTER(TileDesc), vp, sz]
+    lib.stitch_decode_jpeg.argtypes = [vp, vp, sz, vp, sz, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
     lib.stitch_jpeg_header.argtypes = [C.c_uint32, C.c_uint32, C.c_uint32, vp, sz, C.POINTER(sz)]
     lib.stitch_job_inflate.argtypes = [vp, C.c_int, C.POINTER(Timings)]
     lib.stitch_inflate.argtypes = [vp, vp, sz, vp, sz, C.POINTER(sz)]
@@ -197,6 +202,24 @@ class Context:
         rc = self.lib.stitch_decode_image(self.handle, C.byref(td), _addr(data), len(data), _addr(out), out.size, C.byref(n))
         self.check(rc)
         return out[: n.value]
+
+    def jpeg_info(self, data):
+        """(width, height, channels) of a JPEG file without decoding (parseJpegHeader, jpeg-decoder.ts:46-94)."""
+        data = bytes(data) if isinstance(data, memoryview) else data
+        w, h, ch = C.c_uint32(), C.c_uint32(), C.c_uint32()
+        self.check(self.lib.stitch_jpeg_info(self.handle, _addr(data), len(data), C.byref(w), C.byref(h), C.byref(ch)))
+        return w.value, h.value, ch.value
+
+    def decode_jpeg(self, data):
+        """The device JPEG decoder alone: (H, W, 4) RGBA8 or (H, W) gray8 (numpy uint8)."""
+        import numpy as np
+        data = bytes(data) if isinstance(data, memoryview) else data
+        w, h, ch = self.jpeg_info(data)
+        out = np.empty(max(1, w * h * ch), dtype=np.uint8)
+        rc = self.lib.stitch_decode_jpeg(self.handle, _addr(data), len(data), _addr(out), out.size, C.byref(C.c_uint32()),
+                                         C.byref(C.c_uint32()), C.byref(C.c_uint32()))
+        self.check(rc)
+        return out[: w * h * ch].reshape((h, w, 4) if ch == 4 else (h, w))
 
     def inflate(self, zdata, capacity: int):
         """Inflate alone: one zlib stream -> at most `capacity` bytes (numpy uint8)."""
@@ -301,6 +324,17 @@ class Job:
                 rc = self.lib.stitch_job_add_tile(self.handle, C.byref(td), _addr(data), n)
             self._keep.append(data)   # a pinned source is copied asynchronously: it must outlive the upload (until close)
         self.ctx.check(rc)
+
+    def add_tile_jpeg(self, data, *, dst_x=0, dst_y=0, src_off_x=0, src_off_y=0, vis_w=None, vis_h=None, z_index=0,
+                      image_idx=0) -> None:
+        """8f.4 extension: a baseline JPEG file as a tile, decoded on the device (csrc/jpeg_decode.cu)."""
+        data = bytes(data) if isinstance(data, (memoryview, bytearray)) else data
+        w, h, _ = self.ctx.jpeg_info(data)
+        td = TileDesc(width=w, height=h, bit_depth=8, color_type=6, interlace=0, filtered=0, dst_x=dst_x, dst_y=dst_y,
+                      src_off_x=src_off_x, src_off_y=src_off_y, vis_w=w if vis_w is None else vis_w,
+                      vis_h=h if vis_h is None else vis_h, z_index=z_index, image_idx=image_idx)
+        self.ctx.check(self.lib.stitch_job_add_tile_jpeg(self.handle, C.byref(td), _addr(data), len(data)))
+        self._keep.append(data)
 
     def decode(self, force: bool = False) -> dict:
         t = Timings()

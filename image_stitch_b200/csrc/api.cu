@@ -244,6 +244,7 @@ extern "C" void stitch_job_destroy(stitch_job *job) {
   dev_free(ctx, job->d_pack[0]); dev_free(ctx, job->d_pack[1]);
   for (auto &e : job->ev_pack) if (e) cudaEventDestroy(e);
   if (job->h_infres) cudaFreeHost(job->h_infres);
+  if (job->h_jdstat) cudaFreeHost(job->h_jdstat);
   for (auto &e : job->ev_defl) if (e) cudaEventDestroy(e);
   if (job->h_defl) cudaFreeHost(job->h_defl);
   for (auto &q : job->d_jpeg) dev_free(ctx, q);
@@ -396,7 +397,7 @@ static size_t inflated_len(const stitch_tile_desc &d, bool has_pal) {
 }
 
 static int add_tile_common(stitch_job *job, const stitch_tile_desc *tile, const uint8_t *host, const void *dev, size_t len,
-                           const uint32_t *pal = nullptr, bool pal_opaque = true) {
+                           const uint32_t *pal = nullptr, bool pal_opaque = true, bool own_dev = false) {
   if (!job || !tile || (!host && !dev && len)) return STITCH_E_INVALID;
   stitch_ctx *ctx = job->ctx;
   cudaSetDevice(ctx->device);
@@ -422,7 +423,7 @@ static int add_tile_common(stitch_job *job, const stitch_tile_desc *tile, const 
     t.src_len = len;
     if (dev) {
       t.d_src = (uint8_t *)dev;
-      t.src_external = true;
+      t.src_external = !own_dev;   // own_dev: rows a kernel chain on ctx->up is producing (a decoded JPEG tile)
     } else {
       // +32: the unfilter kernel may read a few bytes past a row with vector loads.  Allocated in the order of
       // the upload stream, where the bytes are written; ctx->stream sees it through the tile's upload event.
@@ -435,7 +436,7 @@ static int add_tile_common(stitch_job *job, const stitch_tile_desc *tile, const 
     cudaError_t e = cudaMemcpyAsync(z ? t.d_z : t.d_src, host, len, cudaMemcpyHostToDevice, ctx->up);
     if (e != cudaSuccess) { free_tile(ctx, t); return fail(ctx, STITCH_E_CUDA, "H2D failed: %s", cudaGetErrorString(e)); }
   }
-  if (!dev || z) {  // also orders the allocation of an inflate target made on the upload stream
+  if (!dev || z || own_dev) {  // also orders the allocation of an inflate target made on the upload stream
     cudaError_t e = cudaEventCreateWithFlags(&t.up_event, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventRecord(t.up_event, ctx->up);
     if (e != cudaSuccess) { free_tile(ctx, t); return fail(ctx, STITCH_E_CUDA, "H2D failed: %s", cudaGetErrorString(e)); }
@@ -468,6 +469,9 @@ extern "C" int stitch_job_add_tile_palette(stitch_job *job, const stitch_tile_de
     pal[i] = v;
   }
   return add_tile_common(job, tile, data, nullptr, len, pal, opaque);
+}
+int stitch_add_tile_produced(stitch_job *job, const stitch_tile_desc *tile, uint8_t *d_rows, size_t len) {
+  return add_tile_common(job, tile, nullptr, d_rows, len, nullptr, true, true);
 }
 extern "C" int stitch_job_add_tile_device(stitch_job *job, const stitch_tile_desc *tile, const void *device_data, size_t len) {
   if (((uintptr_t)device_data & 15u) != 0) return fail(job ? job->ctx : nullptr, STITCH_E_INVALID, "device_data must be 16-byte aligned");
@@ -531,6 +535,20 @@ static int check_inflate(stitch_ctx *ctx, stitch_job *job) {
 static int check_status(stitch_ctx *ctx, stitch_job *job) {
   if (job && !job->inf_pending.empty()) {
     const int rc = check_inflate(ctx, job);
+    if (rc) return rc;
+  }
+  if (job && !job->jd_pending.empty()) {   // JPEG tiles whose decode chain ctx->stream has waited for
+    size_t keep = 0;
+    int rc = STITCH_OK;
+    for (const auto &pr : job->jd_pending) {
+      if (pr.second < job->tiles.size() && !job->tiles[pr.second].up_waited) { job->jd_pending[keep++] = pr; continue; }
+      const uint32_t code = job->h_jdstat[pr.first];
+      if (code && !rc) {
+        job->status = STITCH_E_JPEG;
+        rc = fail(ctx, STITCH_E_JPEG, "%s", stitch_jpeg_decode_message(code));
+      }
+    }
+    job->jd_pending.resize(keep);
     if (rc) return rc;
   }
   const unsigned long long e = ctx->h_status->first_error;
@@ -1309,6 +1327,24 @@ extern "C" int stitch_job_band_device(stitch_job *job, void **ptr, size_t *pitch
   if (lead) *lead = job->out_lead;
   if (row_bytes) *row_bytes = job->out_row_bytes;
   return STITCH_OK;
+}
+
+int stitch_job_read_tile(stitch_job *job, uint32_t k, uint8_t *out, size_t cap) {
+  if (!job || !out || k >= job->tiles.size()) return STITCH_E_INVALID;
+  stitch_ctx *ctx = job->ctx;
+  cudaSetDevice(ctx->device);
+  TileRec &t = job->tiles[k];
+  if (!t.decoded || !t.d_pix) return fail(ctx, STITCH_E_STATE, "tile #%u is not decoded", k + 1);
+  const size_t rb = scanline_bytes(t.d.width, t.d.bit_depth, t.d.color_type);
+  if (cap < rb * t.d.height) return fail(ctx, STITCH_E_CAPACITY, "output buffer too small: need %zu bytes", rb * t.d.height);
+  if (!t.up_waited) { CK(cudaStreamWaitEvent(ctx->stream, t.up_event, 0)); t.up_waited = true; }
+  CK(cudaMemcpy2DAsync(out, rb, t.d_pix, t.pitch, rb, t.d.height, cudaMemcpyDeviceToHost, ctx->stream));
+  int rc = reset_status(ctx);
+  if (rc) return rc;
+  CK(cudaMemcpyAsync(ctx->h_status, ctx->d_status, sizeof(DevStatus), cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  stitch_arena_reset(ctx);
+  return check_status(ctx, job);
 }
 
 extern "C" int stitch_job_status(stitch_job *job) { return job ? job->status : STITCH_E_INVALID; }

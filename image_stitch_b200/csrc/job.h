@@ -5,6 +5,7 @@
 #include "kernels.h"
 
 #include <string>
+#include <utility>
 #include <vector>
 
 // ---------------------------------------------------------------------------
@@ -105,10 +106,19 @@ struct stitch_job {
   size_t jpeg_cap[5] = {0, 0, 0, 0, 0};
   unsigned long long *h_jpeg_totals = nullptr;  // pinned: [0] unstuffed bytes, [1] output bytes
   int jpeg_tables_quality = -1;
+  // JPEG tiles (jpeg_decode.cu): one pinned status word per tile, written by the tile's last decode kernel;
+  // jd_pending: (slot, tile) pairs not checked yet
+  uint32_t *h_jdstat = nullptr; size_t jdstat_cap = 0, jdstat_used = 0;
+  std::vector<std::pair<uint32_t, uint32_t>> jd_pending;
 };
 
 
 int stitch_fail(stitch_ctx *ctx, int code, const char *fmt, ...);
+// a tile whose dense rows a kernel chain on ctx->up is producing at d_rows (cudaMallocAsync'ed there; the job owns it)
+int stitch_add_tile_produced(stitch_job *job, const stitch_tile_desc *tile, uint8_t *d_rows, size_t len);
+// tile k's dense rows -> host (after its upload / decode chain), with the job's pending decode errors checked
+int stitch_job_read_tile(stitch_job *job, uint32_t k, uint8_t *out, size_t cap);
+const char *stitch_jpeg_decode_message(uint32_t code);
 int stitch_dev_alloc(stitch_ctx *ctx, void **p, size_t bytes);
 void stitch_dev_free(stitch_ctx *ctx, void *p);
 int stitch_ensure_buffer(stitch_ctx *ctx, uint8_t **p, size_t *have, size_t need);

@@ -3,6 +3,7 @@ from __future__ import annotations
 
 from typing import List, Optional
 
+from .jpeg_decoder import jpeg_decoder
 from .png_decoder import png_decoder
 
 _default: Optional[list] = None
@@ -11,7 +12,7 @@ _default: Optional[list] = None
 def get_default_decoder_plugins() -> List:
     global _default
     if not _default:
-        _default = [png_decoder]
+        _default = [png_decoder, jpeg_decoder]
     return _default
 
 

@@ -89,6 +89,11 @@ def decode_image(header: PngHeader, stream, device: Optional[int] = None):
                                             header.interlace_method, stream, filtered=1)
 
 
+def decode_jpeg(data, device: Optional[int] = None):
+    """The device JPEG decoder alone: (H, W, 4) RGBA8 or (H, W) gray8."""
+    return get_context(device).decode_jpeg(data)
+
+
 def collect_inputs(options: ConcatOptions) -> list:
     """stream() :929-949 -- arrays, iterables and async iterables are all accepted."""
     inputs = options.inputs
@@ -156,7 +161,7 @@ def plan_job(options: ConcatOptions, inputs: list, headers: List[PngHeader],
 class TileSource:
     header: PngHeader     # the header the pixel bytes follow (true PNG header for inflated streams)
     data: object          # bytes-like
-    filtered: int
+    filtered: int         # 0 dense rows, 1 inflated stream, 2 zlib stream, 3 JPEG file
     interlace: int
     plte: Optional[bytes] = None   # expand_palette extension: chunk bodies of a colour type 3 input
     trns: bytes = b""
@@ -174,6 +179,8 @@ def read_tile_source(decoder, declared: PngHeader, image_idx: int, device_inflat
                 raise StitchFailure(f"input #{image_idx + 1} has colour type 3 but no PLTE chunk")
         return src
 
+    if hasattr(decoder, "jpeg_file"):          # filtered == 3: the file itself, decoded on the device
+        return TileSource(declared, decoder.jpeg_file(), 3, 0)
     if device_inflate and hasattr(decoder, "deflated"):
         hdr, zstream = decoder.deflated()      # filtered == 2: the device inflates
         return with_palette(TileSource(hdr, zstream, 2, 1 if hdr.interlace_method == 1 else 0))
@@ -230,6 +237,11 @@ class BandRunner:
         for p in plan.placements:
             if p.dst_y < y1 and p.dst_y + p.vis_h > halo0:
                 s = sources[p.image_idx]
+                if s.filtered == 3:
+                    self.job.add_tile_jpeg(s.data, dst_x=p.dst_x, dst_y=p.dst_y, src_off_x=p.src_off_x, src_off_y=p.src_off_y,
+                                           vis_w=p.vis_w, vis_h=p.vis_h, z_index=p.z_index, image_idx=p.image_idx)
+                    self.tiles.append(p)
+                    continue
                 self.job.add_tile(s.data, width=s.header.width, height=s.header.height, bit_depth=s.header.bit_depth,
                                   color_type=s.header.color_type, interlace=s.interlace, filtered=s.filtered,
                                   dst_x=p.dst_x, dst_y=p.dst_y, src_off_x=p.src_off_x, src_off_y=p.src_off_y,

@@ -43,7 +43,9 @@ typedef enum stitch_status {
   STITCH_E_STATE = -7,     /* call order violated */
   STITCH_E_CAPACITY = -8,  /* caller buffer too small */
   STITCH_E_INFLATE = -9,   /* "Inflate error: <zlib message>"   src/streaming-inflate.ts:60-62, :69-71 */
-  STITCH_E_NODEVICE = -10  /* no CUDA device: there is no CPU fallback */
+  STITCH_E_NODEVICE = -10, /* no CUDA device: there is no CPU fallback */
+  STITCH_E_JPEG = -11      /* "Invalid JPEG: ..." src/decoders/jpeg-decoder.ts:49,74,93; "Unsupported JPEG: ..." for what the
+                              device decoder does not take (progressive, 12-bit, CMYK, unusual sampling) */
 } stitch_status;
 
 typedef enum stitch_out_kind {
@@ -215,6 +217,29 @@ int stitch_job_band_device(stitch_job *job, void **ptr, size_t *pitch, size_t *l
 
 /* First decode error seen on the device, in the reference's wording. */
 int stitch_job_status(stitch_job *job);
+
+/* ---- 8(f).4 extension: baseline JPEG tiles, decoded on the device ---------------------------------------------
+ * The reference decodes JPEG inputs on the host through sharp / jpeg-js / the browser (src/decoders/jpeg-decoder.ts:
+ * 196-281) and feeds RGBA8 (or gray8) rows to the same hot path; here the file crosses the bus as it is and
+ * libjpeg-turbo's default decode (what sharp gives on Node) is redone on the GPU: Huffman decoding per restart
+ * interval, jpeg_idct_islow, fancy chroma upsampling, fixed-point YCbCr -> RGB (csrc/jpeg_decode.cu).
+ * Accepted: SOF0 / SOF1, 8-bit, one interleaved scan, gray or YCbCr, luma sampling 1x1, 2x1, 2x2 with 1x1 chroma;
+ * anything else fails with STITCH_E_JPEG and a message that says what. */
+
+/* Dimensions and channel count (1 gray, 4 RGBA) without decoding: parseJpegHeader + getHeader,
+ * src/decoders/jpeg-decoder.ts:46-94, :298-315, same messages.  ctx may be NULL (no message text then). */
+int stitch_jpeg_info(stitch_ctx *ctx, const uint8_t *data, size_t len, uint32_t *width, uint32_t *height, uint32_t *channels);
+
+/* Adds the JPEG file `data` as a tile.  Of `tile` the placement fields are used (dst_x/y, src_off_x/y, vis_w/h,
+ * z_index, image_idx); width and height must be 0 or the frame's.  The file is parsed and queued for upload and
+ * decoding before the call returns; decode errors of the entropy-coded data surface at the first run_band that
+ * needs the tile (STITCH_E_JPEG).  At most 4096 JPEG tiles per job. */
+int stitch_job_add_tile_jpeg(stitch_job *job, const stitch_tile_desc *tile, const uint8_t *data, size_t len);
+
+/* The decoder alone: the whole image as dense rows, width * height * channels bytes (what JpegDecoder.scanlines()
+ * yields row by row, src/decoders/jpeg-decoder.ts:317-347). */
+int stitch_decode_jpeg(stitch_ctx *ctx, const uint8_t *data, size_t len, uint8_t *out, size_t cap, uint32_t *width,
+                       uint32_t *height, uint32_t *channels);
 
 /* ---- stand-alone pieces (unit-level parity) ------------------------------- */
 

@@ -51,6 +51,9 @@ def oracle_plan(options):
                 plte, trns = dec.palette()
                 pix = orc.expand_palette(pix, h.width, h.height, h.bit_depth, plte, trns).reshape(-1)
                 h = PngHeader(h.width, h.height, 8, 6, h.compression_method, h.filter_method, h.interlace_method)
+        elif hasattr(dec, "jpeg_file"):   # JPEG input: the oracle's own decoder (oracle/jpeg_decode_oracle.c)
+            h = headers[p.image_idx]
+            pix = orc.jpeg_decode(dec.jpeg_file()).reshape(-1)
         else:
             h = headers[p.image_idx]
             pix = np.frombuffer(b"".join(dec.scanlines()), np.uint8)
