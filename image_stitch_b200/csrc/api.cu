@@ -170,6 +170,8 @@ extern "C" void stitch_ctx_destroy(stitch_ctx *ctx) {
   for (auto &ev : ctx->ev) if (ev) cudaEventDestroy(ev);
   cudaEventDestroy(ctx->ev_chunk); cudaEventDestroy(ctx->ev_down);
   cudaStreamDestroy(ctx->up); cudaStreamDestroy(ctx->down);
+  for (cudaStream_t js : ctx->jd_streams) if (js) cudaStreamDestroy(js);
+  if (ctx->pinned_spare) cudaFreeHost(ctx->pinned_spare);
   if (ctx->d_status) cudaFree(ctx->d_status);
   if (ctx->h_status) cudaFreeHost(ctx->h_status);
   if (ctx->h_arena) cudaFreeHost(ctx->h_arena);
@@ -245,6 +247,12 @@ extern "C" void stitch_job_destroy(stitch_job *job) {
   for (auto &e : job->ev_pack) if (e) cudaEventDestroy(e);
   if (job->h_infres) cudaFreeHost(job->h_infres);
   if (job->h_jdstat) cudaFreeHost(job->h_jdstat);
+  if (!job->pinned.empty())   // copies out of the chunks may still be queued
+    for (cudaStream_t js : ctx->jd_streams) if (js) cudaStreamSynchronize(js);
+  for (auto &pc : job->pinned) {
+    if (!ctx->pinned_spare) { ctx->pinned_spare = pc.first; ctx->pinned_spare_cap = pc.second; }
+    else cudaFreeHost(pc.first);
+  }
   for (auto &e : job->ev_defl) if (e) cudaEventDestroy(e);
   if (job->h_defl) cudaFreeHost(job->h_defl);
   for (auto &q : job->d_jpeg) dev_free(ctx, q);
@@ -397,7 +405,7 @@ static size_t inflated_len(const stitch_tile_desc &d, bool has_pal) {
 }
 
 static int add_tile_common(stitch_job *job, const stitch_tile_desc *tile, const uint8_t *host, const void *dev, size_t len,
-                           const uint32_t *pal = nullptr, bool pal_opaque = true, bool own_dev = false) {
+                           const uint32_t *pal = nullptr, bool pal_opaque = true, bool own_dev = false, cudaStream_t produced_on = nullptr) {
   if (!job || !tile || (!host && !dev && len)) return STITCH_E_INVALID;
   stitch_ctx *ctx = job->ctx;
   cudaSetDevice(ctx->device);
@@ -438,7 +446,7 @@ static int add_tile_common(stitch_job *job, const stitch_tile_desc *tile, const 
   }
   if (!dev || z || own_dev) {  // also orders the allocation of an inflate target made on the upload stream
     cudaError_t e = cudaEventCreateWithFlags(&t.up_event, cudaEventDisableTiming);
-    if (e == cudaSuccess) e = cudaEventRecord(t.up_event, ctx->up);
+    if (e == cudaSuccess) e = cudaEventRecord(t.up_event, own_dev && produced_on ? produced_on : ctx->up);
     if (e != cudaSuccess) { free_tile(ctx, t); return fail(ctx, STITCH_E_CUDA, "H2D failed: %s", cudaGetErrorString(e)); }
     t.up_waited = false;
   }
@@ -470,8 +478,8 @@ extern "C" int stitch_job_add_tile_palette(stitch_job *job, const stitch_tile_de
   }
   return add_tile_common(job, tile, data, nullptr, len, pal, opaque);
 }
-int stitch_add_tile_produced(stitch_job *job, const stitch_tile_desc *tile, uint8_t *d_rows, size_t len) {
-  return add_tile_common(job, tile, nullptr, d_rows, len, nullptr, true, true);
+int stitch_add_tile_produced(stitch_job *job, const stitch_tile_desc *tile, uint8_t *d_rows, size_t len, cudaStream_t produced_on) {
+  return add_tile_common(job, tile, nullptr, d_rows, len, nullptr, true, true, produced_on);
 }
 extern "C" int stitch_job_add_tile_device(stitch_job *job, const stitch_tile_desc *tile, const void *device_data, size_t len) {
   if (((uintptr_t)device_data & 15u) != 0) return fail(job ? job->ctx : nullptr, STITCH_E_INVALID, "device_data must be 16-byte aligned");

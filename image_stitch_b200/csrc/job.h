@@ -27,6 +27,11 @@ struct stitch_ctx {
   uint32_t aux_launches = 0;   // copy / fill kernels launched since the current API call began (they count as launches)
   stitch::DevStatus *d_status = nullptr;   // device error word
   stitch::DevStatus *h_status = nullptr;   // pinned mirror
+  // one pinned staging chunk kept between jobs (jpeg_decode.cu: pinning 32 MB costs about 10 ms)
+  uint8_t *pinned_spare = nullptr; size_t pinned_spare_cap = 0;
+  // JPEG tiles are decoded on a few streams in turn, so that the small kernels of several tiles overlap
+  cudaStream_t jd_streams[4] = {};
+  uint32_t jd_next = 0;
 };
 
 struct TileRec {
@@ -110,12 +115,14 @@ struct stitch_job {
   // jd_pending: (slot, tile) pairs not checked yet
   uint32_t *h_jdstat = nullptr; size_t jdstat_cap = 0, jdstat_used = 0;
   std::vector<std::pair<uint32_t, uint32_t>> jd_pending;
+  std::vector<std::pair<uint8_t *, size_t>> pinned;   // pinned staging chunks (jpeg_decode.cu), bump-allocated
+  size_t pinned_used = 0;
 };
 
 
 int stitch_fail(stitch_ctx *ctx, int code, const char *fmt, ...);
-// a tile whose dense rows a kernel chain on ctx->up is producing at d_rows (cudaMallocAsync'ed there; the job owns it)
-int stitch_add_tile_produced(stitch_job *job, const stitch_tile_desc *tile, uint8_t *d_rows, size_t len);
+// a tile whose dense rows a kernel chain on stream `produced_on` is producing at d_rows (cudaMallocAsync'ed there; the job owns it)
+int stitch_add_tile_produced(stitch_job *job, const stitch_tile_desc *tile, uint8_t *d_rows, size_t len, cudaStream_t produced_on);
 // tile k's dense rows -> host (after its upload / decode chain), with the job's pending decode errors checked
 int stitch_job_read_tile(stitch_job *job, uint32_t k, uint8_t *out, size_t cap);
 const char *stitch_jpeg_decode_message(uint32_t code);

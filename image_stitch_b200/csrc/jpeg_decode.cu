@@ -14,9 +14,13 @@
 //   colour    one thread per 4 output pixels: h2v1 / h2v2 fancy upsampling (replication when the downsampled width is
 //             <= 2), context rows replicated at the image edges, YCbCr -> RGBA8; gray is copied
 //
-// Everything runs on the job's upload stream right behind the file's H2D copy; the tile's upload event covers it.
+// Everything runs on one of four decode streams of the context (taken in turn, so that the small kernels of several
+// tiles overlap) right behind the file's H2D copy; the tile's upload event is recorded there and covers it.
 #include "job.h"
+#include "kernels.h"
 
+#include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -47,7 +51,11 @@ const char *jd_message(uint32_t code) {
   }
 }
 
-constexpr int LOOK = 9;   // look-ahead bits of the Huffman tables
+constexpr int LOOK = 9;            // look-ahead bits of the Huffman tables
+constexpr uint32_t SUB_BITS = 1024;  // bits per subsequence of the speculative walk
+constexpr int SYNC_ROUNDS = 32;      // relaxation rounds before the serial decoder takes over (a settled walk skips the rest)
+constexpr uint32_t BAD = 0xffffffffu;
+constexpr uint32_t DC_CHUNK = 8;     // MCUs per chunk of the DC prefix sum
 
 struct JdHuff {
   uint16_t look[1 << LOOK];   // code bits << 8 | symbol for codes of up to LOOK bits, 0 for longer ones
@@ -63,13 +71,31 @@ struct JdComp {
   uint32_t block0;            // the component's first block in `coefs`
   uint32_t plane_off, stride; // its sample plane in `planes`
 };
+// One subsequence of the entropy-coded data: the symbols that START in [start_bit, end_bit) of its restart interval.
+struct JdSub {
+  uint32_t start_bit, end_bit;
+  uint32_t interval;
+  uint32_t first;             // 1: the interval's first subsequence -- its start state is exact
+};
+struct JdState {
+  uint32_t bp;                // bit position of the next symbol (BAD: the walk met an impossible code)
+  uint32_t pos;               // block within the MCU << 8 | zig-zag index of the next coefficient (0: the DC code is next)
+};
 struct JdImage {
-  const uint8_t *ecs;         // entropy-coded segment
-  uint32_t ecs_len;
+  const uint32_t *ecs;        // entropy-coded data with byte stuffing and restart markers removed (host), big-endian bit order
   uint32_t width, height, ncomp, hmax, vmax, mcus_x, mcus_y;
   uint32_t restart;           // MCUs per restart interval (the whole scan when the file has none)
-  uint32_t n_intervals;
-  const uint32_t *rst_off;    // byte offset in ecs of every interval's first byte
+  uint32_t n_intervals, n_subs, bpm;   // bpm: blocks per MCU
+  uint32_t mcu_comp[6], mcu_bx[6], mcu_by[6];   // block j of an MCU: component, block column / row inside the MCU
+  const uint32_t *int_bit;    // [n_intervals + 1] first bit of every interval (byte aligned), end of the data
+  const uint32_t *int_sub;    // [n_intervals + 1] first subsequence of every interval
+  const JdSub *subs;
+  JdState *st_in[2];          // start state of every subsequence, double-buffered by round parity
+  JdState *st_out;            // state after its last symbol
+  JdState *last_in;           // the start state st_out was walked from
+  uint32_t *nblk, *base;      // blocks completed inside the subsequence; sequence number of its first block
+  uint32_t *flags;            // [r] round r changed something; [SYNC_ROUNDS] 1 = the walk settled; [SYNC_ROUNDS + 1] grid barrier
+  int *dc_sum;                // [3][chunks] DC prefix sum scratch
   JdComp c[3];
   int16_t *coefs;             // 64 per block, natural order
   uint8_t *planes;
@@ -79,115 +105,279 @@ struct JdImage {
   JdHuff huff[6];             // component c: DC at 2 c, AC at 2 c + 1
 };
 
-__constant__ uint8_t c_natural[64] = {0,  1,  8,  16, 9,  2,  3,  10, 17, 24, 32, 25, 18, 11, 4,  5,  12, 19, 26, 33, 40, 48,
+__constant__ uint8_t c_natural[80] = {0,  1,  8,  16, 9,  2,  3,  10, 17, 24, 32, 25, 18, 11, 4,  5,  12, 19, 26, 33, 40, 48,
                                       41, 34, 27, 20, 13, 6,  7,  14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23,
-                                      30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
+                                      30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63,
+                                      63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63};
 const uint8_t h_natural[64] = {0,  1,  8,  16, 9,  2,  3,  10, 17, 24, 32, 25, 18, 11, 4,  5,  12, 19, 26, 33, 40, 48,
                                41, 34, 27, 20, 13, 6,  7,  14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23,
                                30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
 
 // ---- entropy decoding -----------------------------------------------------------------------------------------
-// MSB-first bit reader over one restart interval (T.81 F.2.2.5; a stuffed zero follows every 0xFF data byte, B.1.1.5).
-// At a marker or at the end of the data zeros are fed, as jdhuff.c does; `fed` counts them so that an interval that
-// used bits which are not there is reported.
-struct JdBits {
-  const uint8_t *p, *end;
-  unsigned long long acc;   // next bit at bit 63
-  int cnt, fed;
-  bool stop;
-  __device__ __forceinline__ void fill() {
-    while (cnt <= 48) {
-      unsigned long long byte = 0;
-      if (!stop && p < end) {
-        byte = *p;
-        if (byte == 0xffu) {
-          if (p + 1 < end && p[1] == 0u) p += 2;
-          else { stop = true; byte = 0; }
-        } else p++;
-      } else stop = true;
-      if (stop) fed += 8;
-      acc |= byte << (56 - cnt);
-      cnt += 8;
-    }
-  }
-  __device__ __forceinline__ uint32_t peek(int n) const { return (uint32_t)(acc >> (64 - n)); }
-  __device__ __forceinline__ void skip(int n) { acc <<= n; cnt -= n; }
-};
+// Huffman decoding is serial (a code's position depends on every code before it), and most files carry no restart
+// markers, so the parallelism inside an interval comes from speculation (the approach of Weissenberger & Schmidt,
+// "Accelerating JPEG decompression on GPUs"): the interval's bits are cut into subsequences of SUB_BITS; a thread
+// walks its subsequence from a guessed state (a block starting exactly there) and hands the state it ends in to the
+// next one.  Huffman-coded data resynchronises after a few symbols, so after a few rounds of "walk again from what
+// my predecessor ended in" nothing changes any more: that fixed point is the true decode, because the first
+// subsequence of every interval starts exact and every other start state is its predecessor's end state.  Then the
+// blocks a subsequence completes are counted, a prefix sum gives every subsequence its first block, and one more
+// walk writes the coefficients (DC differences; the predictions are a second prefix sum).  A file whose walk has not
+// settled after SYNC_ROUNDS rounds is decoded by one thread per restart interval instead.
 
-__device__ __forceinline__ int jd_decode(JdBits &b, const JdHuff &h) {
-  if (b.cnt < 16) b.fill();
-  const uint32_t e = h.look[b.peek(LOOK)];
-  if (e) { b.skip((int)(e >> 8)); return (int)(e & 0xffu); }
-  for (int l = LOOK + 1; l <= 16; l++) {
-    const int32_t code = (int32_t)b.peek(l);
-    if (h.maxcode[l] >= 0 && code <= h.maxcode[l] && code >= h.mincode[l]) {
-      b.skip(l);
-      return h.vals[h.valptr[l] + code - h.mincode[l]];
-    }
-  }
-  return -1;
+// The 32 bits that start at bit bp.
+__device__ __forceinline__ uint32_t jd_window(const uint32_t *ecs, const uint32_t bp) {
+  const uint32_t i = bp >> 5;
+  const uint32_t w0 = __byte_perm(__ldg(ecs + i), 0u, 0x0123), w1 = __byte_perm(__ldg(ecs + i + 1u), 0u, 0x0123);
+  return __funnelshift_l(w1, w0, bp & 31u);
 }
-__device__ __forceinline__ int jd_receive_extend(JdBits &b, int s) {   // F.2.2.1 RECEIVE + EXTEND
-  if (b.cnt < s) b.fill();
-  const uint32_t r = b.peek(s);
-  b.skip(s);
-  return r < (1u << (s - 1)) ? (int)r - (int)((1u << s) - 1u) : (int)r;
+__device__ __forceinline__ int jd_extend(const uint32_t r, const uint32_t s) {   // F.2.2.1 EXTEND
+  return r < (1u << (s - 1u)) ? (int)r - (int)((1u << s) - 1u) : (int)r;
+}
+__device__ __forceinline__ int16_t *jd_block(const JdImage &img, const uint32_t g, const uint32_t j) {
+  const uint32_t mcu = g / img.bpm, mx = mcu % img.mcus_x, my = mcu / img.mcus_x;
+  const JdComp &c = img.c[img.mcu_comp[j]];
+  return img.coefs + ((size_t)c.block0 + (size_t)(my * c.v + img.mcu_by[j]) * c.wb + (mx * c.h + img.mcu_bx[j])) * 64;
 }
 
-constexpr int JH_THREADS = 64;
+// Walks the symbols that start in [s.bp, limit): EMIT writes coefficients (DC as the difference, F.2.1.3), starting
+// with block sequence number g and never past g_end (the interval's padding follows its last block).  end_bit: the
+// interval's end.  Returns the state after the last symbol and the number of blocks completed; err != 0 (EMIT only):
+// the data is corrupt.  DC_ABS: the caller keeps the predictors (serial decoder).
+template <bool EMIT, bool DC_ABS>
+__device__ __forceinline__ JdState jd_walk(const JdImage &img, const JdHuff *sh, JdState s, const uint32_t limit, const uint32_t end_bit,
+                                           uint32_t g, const uint32_t g_end, uint32_t &nblk, uint32_t &err, int *pred) {
+  // what every symbol needs, in registers: blocks per MCU, the component of every block of an MCU (2 bits each), and
+  // a 64-bit window of the data that is topped up a word at a time (the next bit is bit 63)
+  const uint32_t *__restrict__ ecs = img.ecs;
+  const uint32_t bpm = img.bpm;
+  uint32_t comp_map = 0;
+  for (uint32_t j = 0; j < bpm; j++) comp_map |= img.mcu_comp[j] << (2u * j);
+  uint32_t bp = s.bp, bim = s.pos >> 8, k = s.pos & 0xffu;
+  uint32_t comp = (comp_map >> (2u * bim)) & 3u;
+  uint32_t wi = bp >> 5;
+  unsigned long long buf = (unsigned long long)__byte_perm(__ldg(ecs + wi), 0u, 0x0123) << (32u + (bp & 31u));
+  uint32_t have = 32u - (bp & 31u);
+  wi++;
+  nblk = 0;
+  int16_t *blk = nullptr;
+  if (EMIT && g < g_end) blk = jd_block(img, g, bim);
+  while (bp < limit) {
+    if (EMIT && g >= g_end) break;
+    if (have < 32u) {
+      buf |= (unsigned long long)__byte_perm(__ldg(ecs + wi), 0u, 0x0123) << (32u - have);
+      have += 32u; wi++;
+    }
+    const uint32_t w = (uint32_t)(buf >> 32);
+    const JdHuff &h = sh[2u * comp + (k ? 1u : 0u)];
+    const uint32_t e = h.look[w >> (32 - LOOK)];
+    uint32_t len = e >> 8, sym = e & 0xffu;
+    if (!e) {   // a code longer than the look-ahead: canonical walk
+      for (int l = LOOK + 1; l <= 16; l++) {
+        const int32_t code = (int32_t)(w >> (32 - l));
+        if (h.maxcode[l] >= 0 && code <= h.maxcode[l] && code >= h.mincode[l]) { len = (uint32_t)l; sym = h.vals[h.valptr[l] + code - h.mincode[l]]; break; }
+      }
+      if (!len) { if (EMIT) err = JD_E_HUFF; s.bp = BAD; return s; }
+    }
+    const uint32_t sbits = k ? (sym & 15u) : sym, total = len + sbits;
+    if (sbits > 15u) { if (EMIT) err = JD_E_HUFF; s.bp = BAD; return s; }
+    if (bp + total > end_bit) {   // the interval's padding (all ones: never a whole code), or data that ends early
+      if (EMIT) err = JD_E_TRUNCATED;
+      break;
+    }
+    const uint32_t vbits = sbits ? (w << len) >> (32u - sbits) : 0u;
+    bp += total; buf <<= total; have -= total;
+    if (k == 0u) {
+      if (EMIT) {
+        int v = sbits ? jd_extend(vbits, sbits) : 0;
+        if (DC_ABS) { pred[comp] += v; v = pred[comp]; }
+        blk[0] = (int16_t)v;
+      }
+      k = 1u;
+    } else if (sbits) {
+      k += sym >> 4;
+      if (k > 63u) { if (EMIT) err = JD_E_HUFF; s.bp = BAD; return s; }
+      if (EMIT) blk[c_natural[k]] = (int16_t)jd_extend(vbits, sbits);
+      k++;
+    } else {
+      k = (sym >> 4) == 15u ? k + 16u : 64u;
+    }
+    if (k >= 64u) {
+      k = 0u; nblk++; g++;
+      if (++bim == bpm) bim = 0u;
+      comp = (comp_map >> (2u * bim)) & 3u;
+      if (EMIT && g < g_end) blk = jd_block(img, g, bim);
+    }
+  }
+  s.bp = bp; s.pos = (bim << 8) | k;
+  return s;
+}
 
-__global__ void __launch_bounds__(JH_THREADS) jd_huff_kernel(const JdImage *img_p) {
-  __shared__ JdHuff sh[6];
-  const JdImage &img = *img_p;
-  {
-    const uint32_t n = img.ncomp * 2u * (uint32_t)(sizeof(JdHuff) / 4);
-    const uint32_t *src = reinterpret_cast<const uint32_t *>(img.huff);
-    uint32_t *dst = reinterpret_cast<uint32_t *>(sh);
-    for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) dst[i] = src[i];
+__device__ __forceinline__ void jd_load_tables(const JdImage &img, JdHuff *sh) {
+  const uint32_t n = img.ncomp * 2u * (uint32_t)(sizeof(JdHuff) / 4);
+  const uint32_t *src = reinterpret_cast<const uint32_t *>(img.huff);
+  uint32_t *dst = reinterpret_cast<uint32_t *>(sh);
+  for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) dst[i] = src[i];
+  __syncthreads();
+}
+
+constexpr int JH_THREADS = 128;
+
+// The relaxation rounds, in one resident grid (cooperative launch) with a grid barrier between rounds: in every
+// round each subsequence whose start state changed is walked again from the state its predecessor ended in.
+// Ends when a round changes nothing (flags[SYNC_ROUNDS] = 1) or after SYNC_ROUNDS rounds.
+__device__ __forceinline__ void jd_grid_barrier(uint32_t *counter, const uint32_t target) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    atomicAdd(counter, 1u);
+    while (*reinterpret_cast<volatile uint32_t *>(counter) < target) __nanosleep(64);
+    __threadfence();
   }
   __syncthreads();
-  const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-  if (k >= img.n_intervals) return;
-  const uint32_t total = img.mcus_x * img.mcus_y;
-  const uint32_t m0 = k * img.restart, m1 = min(total, m0 + img.restart);
-  JdBits b;
-  b.p = img.ecs + img.rst_off[k];
-  b.end = img.ecs + (k + 1u < img.n_intervals ? img.rst_off[k + 1u] - 2u : img.ecs_len);   // up to the next interval's marker
-  b.acc = 0; b.cnt = 0; b.fed = 0; b.stop = false;
-  int pred[3] = {0, 0, 0};
-  uint32_t err = 0;
-  uint32_t mx = m0 % img.mcus_x, my = m0 / img.mcus_x;
-  for (uint32_t m = m0; m < m1 && !err; m++) {
-    for (uint32_t i = 0; i < img.ncomp && !err; i++) {
-      const JdComp &c = img.c[i];
-      for (uint32_t v = 0; v < c.v && !err; v++) {
-        for (uint32_t hh = 0; hh < c.h; hh++) {
-          int16_t *blk = img.coefs + ((size_t)c.block0 + (size_t)(my * c.v + v) * c.wb + (mx * c.h + hh)) * 64;
-          int s = jd_decode(b, sh[2 * i]);
-          if (s < 0 || s > 15) { err = JD_E_HUFF; break; }
-          if (s) pred[i] += jd_receive_extend(b, s);
-          blk[0] = (int16_t)pred[i];
-          for (int kk = 1; kk < 64; kk++) {
-            s = jd_decode(b, sh[2 * i + 1]);
-            if (s < 0) { err = JD_E_HUFF; break; }
-            const int r = s >> 4;
-            s &= 15;
-            if (s) {
-              kk += r;
-              if (kk > 63) { err = JD_E_HUFF; break; }
-              blk[c_natural[kk]] = (int16_t)jd_receive_extend(b, s);
-            } else {
-              if (r != 15) break;
-              kk += 15;
-            }
-          }
-          if (err) break;
-        }
+}
+__global__ void __launch_bounds__(JH_THREADS) jd_sync_kernel(const JdImage *img_p) {
+  __shared__ JdHuff sh[6];
+  const JdImage &img = *img_p;
+  jd_load_tables(img, sh);
+  uint32_t *barrier = img.flags + SYNC_ROUNDS + 1;
+  for (uint32_t round = 0; round < (uint32_t)SYNC_ROUNDS; round++) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < img.n_subs; i += gridDim.x * blockDim.x) {
+      const JdSub sub = img.subs[i];
+      JdState in;
+      if (sub.first || round == 0u) { in.bp = sub.start_bit; in.pos = 0u; }   // exact / the guess: a block starts here
+      else {
+        in = img.st_in[round & 1u][i];
+        if (in.bp == BAD) { in.bp = sub.start_bit; in.pos = 0u; }
       }
+      const JdState before = img.st_out[i];
+      JdState out = before;
+      const JdState last = img.last_in[i];
+      if (round == 0u || last.bp != in.bp || last.pos != in.pos) {   // the same start gives the same walk: only changed starts are walked again
+        uint32_t nblk, err = 0;
+        out = jd_walk<false, false>(img, sh, in, sub.end_bit, img.int_bit[sub.interval + 1u], 0u, 0u, nblk, err, nullptr);
+        if (before.bp != out.bp || before.pos != out.pos || img.nblk[i] != nblk) img.flags[round] = 1u;
+        img.st_out[i] = out;
+        img.nblk[i] = nblk;
+        img.last_in[i] = in;
+      }
+      if (i + 1u < img.n_subs) img.st_in[(round + 1u) & 1u][i + 1u] = out;   // (the next interval's first subsequence ignores it)
     }
-    if (++mx == img.mcus_x) { mx = 0; my++; }
+    jd_grid_barrier(barrier, (round + 1u) * gridDim.x);
+    if (*reinterpret_cast<volatile uint32_t *>(img.flags + round) == 0u) {   // nothing changed: the walk has settled
+      if (blockIdx.x == 0 && threadIdx.x == 0) img.flags[SYNC_ROUNDS] = 1u;
+      return;
+    }
   }
-  if (!err && b.fed > b.cnt) err = JD_E_TRUNCATED;   // the interval used bits that are not there
+}
+
+// Per restart interval (one CTA): has the walk settled; first block of every subsequence; does the count add up.
+__global__ void __launch_bounds__(256) jd_scan_kernel(const JdImage *img_p) {
+  __shared__ uint32_t warp_sum[8], carry;
+  const JdImage &img = *img_p;
+  if (img.flags[SYNC_ROUNDS] == 0u) return;   // not settled: the serial decoder takes over
+  const uint32_t iv = blockIdx.x, s0 = img.int_sub[iv], s1 = img.int_sub[iv + 1u];
+  const uint32_t total = img.mcus_x * img.mcus_y, m0 = iv * img.restart, m1 = min(total, m0 + img.restart);
+  if (threadIdx.x == 0) carry = m0 * img.bpm;
+  __syncthreads();
+  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  for (uint32_t at = s0; at < s1; at += blockDim.x) {
+    const uint32_t i = at + threadIdx.x;
+    const uint32_t v = i < s1 ? img.nblk[i] : 0u;
+    uint32_t x = v;
+    for (int d = 1; d < 32; d <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, d); if ((int)lane >= d) x += y; }
+    if (lane == 31u) warp_sum[warp] = x;
+    __syncthreads();
+    uint32_t before = carry;
+    for (uint32_t w2 = 0; w2 < warp; w2++) before += warp_sum[w2];
+    if (i < s1) img.base[i] = before + x - v;
+    __syncthreads();
+    if (threadIdx.x == blockDim.x - 1u) carry = before + x;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0 && carry != m1 * img.bpm) atomicCAS(img.status, 0u, carry < m1 * img.bpm ? (uint32_t)JD_E_TRUNCATED : (uint32_t)JD_E_HUFF);
+}
+
+// The last walk: coefficients into HBM (DC differences).
+__global__ void __launch_bounds__(JH_THREADS) jd_emit_kernel(const JdImage *img_p) {
+  __shared__ JdHuff sh[6];
+  const JdImage &img = *img_p;
+  if (img.flags[SYNC_ROUNDS] == 0u) return;
+  jd_load_tables(img, sh);
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= img.n_subs) return;
+  const JdSub sub = img.subs[i];
+  JdState in;
+  if (sub.first) { in.bp = sub.start_bit; in.pos = 0u; }
+  else in = img.st_in[0][i];
+  if (in.bp == BAD) { atomicCAS(img.status, 0u, (uint32_t)JD_E_HUFF); return; }
+  const uint32_t total = img.mcus_x * img.mcus_y, m1 = min(total, (sub.interval + 1u) * img.restart);
+  uint32_t nblk, err = 0;
+  jd_walk<true, false>(img, sh, in, sub.end_bit, img.int_bit[sub.interval + 1u], img.base[i], m1 * img.bpm, nblk, err, nullptr);
+  if (err) atomicCAS(img.status, 0u, err);
+}
+
+// DC predictions (F.2.1.3.1: a running sum per component, restarting with every interval) as a prefix sum over chunks
+// of DC_CHUNK MCUs: chunk sums, their exclusive scan per interval, then the running sum inside every chunk.
+__device__ __forceinline__ void jd_chunk_range(const JdImage &img, const uint32_t chunk, uint32_t &m0, uint32_t &m1) {
+  const uint32_t cpi = (img.restart + DC_CHUNK - 1u) / DC_CHUNK, iv = chunk / cpi, piece = chunk - iv * cpi;
+  const uint32_t total = img.mcus_x * img.mcus_y, i0 = iv * img.restart, i1 = min(total, i0 + img.restart);
+  m0 = min(i1, i0 + piece * DC_CHUNK); m1 = min(i1, m0 + DC_CHUNK);
+}
+template <int PHASE>
+__global__ void __launch_bounds__(128) jd_dc_kernel(const JdImage *img_p, const uint32_t n_chunks) {
+  const JdImage &img = *img_p;
+  if (img.flags[SYNC_ROUNDS] == 0u) return;   // the serial decoder wrote the predictions itself
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t cpi = (img.restart + DC_CHUNK - 1u) / DC_CHUNK;
+  if (PHASE == 1) {   // one warp per interval and component: exclusive scan of its chunk sums
+    const uint32_t wid = t >> 5, lane = threadIdx.x & 31u;
+    if (wid >= img.n_intervals * img.ncomp) return;
+    const uint32_t iv = wid / img.ncomp, comp = wid - iv * img.ncomp;
+    int *sums = img.dc_sum + (size_t)comp * n_chunks + (size_t)iv * cpi;
+    int carry = 0;
+    for (uint32_t at = 0; at < cpi; at += 32u) {
+      const uint32_t p = at + lane;
+      const int v = p < cpi ? sums[p] : 0;
+      int x = v;
+      for (int d = 1; d < 32; d <<= 1) { const int y = __shfl_up_sync(0xffffffffu, x, d); if ((int)lane >= d) x += y; }
+      if (p < cpi) sums[p] = carry + x - v;
+      carry += __shfl_sync(0xffffffffu, x, 31);
+    }
+    return;
+  }
+  if (t >= n_chunks * img.ncomp) return;
+  const uint32_t chunk = t / img.ncomp, comp = t - chunk * img.ncomp;
+  uint32_t m0, m1;
+  jd_chunk_range(img, chunk, m0, m1);
+  int run = PHASE == 2 ? img.dc_sum[(size_t)comp * n_chunks + chunk] : 0;
+  for (uint32_t m = m0; m < m1; m++) {
+    for (uint32_t j = 0; j < img.bpm; j++) {
+      if (img.mcu_comp[j] != comp) continue;
+      int16_t *blk = jd_block(img, m * img.bpm, j);
+      run += blk[0];
+      if (PHASE == 2) blk[0] = (int16_t)run;
+    }
+  }
+  if (PHASE == 0) img.dc_sum[(size_t)comp * n_chunks + chunk] = run;
+}
+
+// The serial decoder: one thread per restart interval.  Runs only when the speculative walk did not settle.
+__global__ void __launch_bounds__(JH_THREADS) jd_serial_kernel(const JdImage *img_p) {
+  __shared__ JdHuff sh[6];
+  const JdImage &img = *img_p;
+  if (img.flags[SYNC_ROUNDS] != 0u) return;
+  jd_load_tables(img, sh);
+  const uint32_t iv = blockIdx.x * blockDim.x + threadIdx.x;
+  if (iv >= img.n_intervals) return;
+  const uint32_t total = img.mcus_x * img.mcus_y, m0 = iv * img.restart, m1 = min(total, m0 + img.restart);
+  JdState in;
+  in.bp = img.int_bit[iv]; in.pos = 0u;
+  int pred[3] = {0, 0, 0};
+  uint32_t nblk, err = 0;
+  const uint32_t end_bit = img.int_bit[iv + 1u];
+  jd_walk<true, true>(img, sh, in, end_bit, end_bit, m0 * img.bpm, m1 * img.bpm, nblk, err, pred);
+  if (!err && nblk != (m1 - m0) * img.bpm) err = JD_E_TRUNCATED;
   if (err) atomicCAS(img.status, 0u, err);
 }
 
@@ -306,8 +496,9 @@ struct HostFrame {
   uint16_t q[4][64] = {};
   bool qset[4] = {};
   HostHuff dc[4], ac[4];
-  size_t ecs_off = 0, ecs_len = 0;
-  std::vector<uint32_t> rst_off;   // interval starts within the segment
+  size_t ecs_off = 0;              // the entropy-coded segment starts here
+  uint32_t n_intervals = 0;
+  std::vector<uint32_t> int_byte;  // [n_intervals + 1] interval starts in the UNSTUFFED data, its length (unstuff())
 };
 
 void derive(const HostHuff &h, JdHuff &o) {
@@ -425,37 +616,45 @@ uint32_t parse(const uint8_t *d, size_t n, HostFrame &f, bool header_only) {
       f.mcus_x = (f.width + 8 * f.hmax - 1) / (8 * f.hmax);
       f.mcus_y = (f.height + 8 * f.vmax - 1) / (8 * f.vmax);
       f.ecs_off = o + len;
-      // the segment ends at the first marker that is neither a stuffed zero nor RSTn; RSTn start the intervals
       const uint32_t total = f.mcus_x * f.mcus_y;
-      const uint32_t per = f.restart ? f.restart : total;
-      const uint32_t n_int = (total + per - 1) / per;
-      f.rst_off.assign(1, 0u);
-      size_t e = f.ecs_off;
-      while (e < n) {
-        const uint8_t *ff = static_cast<const uint8_t *>(memchr(d + e, 0xff, n - e));
-        if (!ff) { e = n; break; }
-        e = (size_t)(ff - d);
-        if (e + 1 >= n) { e = n; break; }
-        const uint8_t mk = d[e + 1];
-        if (mk == 0x00) { e += 2; continue; }
-        if (mk == 0xff) { e += 1; continue; }
-        if (mk >= 0xd0 && mk <= 0xd7) {
-          if (f.rst_off.size() >= n_int || mk != 0xd0 + ((f.rst_off.size() - 1) & 7)) return JD_E_RST;
-          f.rst_off.push_back((uint32_t)(e + 2 - f.ecs_off));
-          e += 2;
-          continue;
-        }
-        break;   // EOI or another segment
-      }
-      f.ecs_len = e - f.ecs_off;
-      if (f.rst_off.size() != n_int) return f.restart && e < n ? JD_E_RST : JD_E_TRUNCATED;
-      if (f.ecs_len >= (1ull << 32)) return JD_E_TRUNCATED;
-      f.restart = per;
+      if (!f.restart) f.restart = total;
+      f.n_intervals = (total + f.restart - 1) / f.restart;
       return JD_OK;
     }
     o += len;
   }
   return have_sof ? JD_E_TRUNCATED : JD_E_NO_SOF;
+}
+
+// The entropy-coded segment without its framing (T.81 B.1.1.5: the zero after every 0xFF data byte; B.2.1: the RSTn
+// markers between restart intervals), copied to dst (capacity: the rest of the file).  The segment ends at the first
+// marker that is neither.  Fills f.int_byte.
+uint32_t unstuff(const uint8_t *d, size_t n, HostFrame &f, uint8_t *dst) {
+  f.int_byte.assign(1, 0u);
+  size_t e = f.ecs_off, out = 0;
+  while (e < n) {
+    const uint8_t *ff = static_cast<const uint8_t *>(memchr(d + e, 0xff, n - e));
+    const size_t stop = ff ? (size_t)(ff - d) : n;
+    memcpy(dst + out, d + e, stop - e);
+    out += stop - e;
+    e = stop;
+    if (e + 1 >= n) { e = n; break; }
+    const uint8_t mk = d[e + 1];
+    if (mk == 0x00) { dst[out++] = 0xff; e += 2; continue; }
+    if (mk == 0xff) { e += 1; continue; }   // fill byte
+    if (mk >= 0xd0 && mk <= 0xd7) {
+      if (f.int_byte.size() >= f.n_intervals || mk != 0xd0 + ((f.int_byte.size() - 1) & 7)) return JD_E_RST;
+      f.int_byte.push_back((uint32_t)out);
+      e += 2;
+      continue;
+    }
+    break;   // EOI or another segment
+  }
+  if (f.int_byte.size() != f.n_intervals) return f.n_intervals > 1 && e < n ? JD_E_RST : JD_E_TRUNCATED;
+  if (out >= (1ull << 28)) return JD_E_TRUNCATED;   // bit positions are 32-bit
+  f.int_byte.push_back((uint32_t)out);
+  memset(dst + out, 0, 8);   // the readers look one word ahead
+  return JD_OK;
 }
 
 }  // namespace
@@ -475,6 +674,26 @@ extern "C" int stitch_jpeg_info(stitch_ctx *ctx, const uint8_t *data, size_t len
   return STITCH_OK;
 }
 
+// Pinned staging memory of the job (files are unstuffed into it and copied from it asynchronously; pageable sources
+// would make every copy wait for the decode kernels queued before it).  Lives until the job is destroyed.
+static uint8_t *job_pinned(stitch_job *job, size_t bytes) {
+  bytes = (bytes + 255) & ~(size_t)255;
+  if (job->pinned.empty() || job->pinned_used + bytes > job->pinned.back().second) {
+    size_t cap = std::max<size_t>(bytes, (size_t)32 << 20);
+    void *p = nullptr;
+    stitch_ctx *ctx = job->ctx;
+    if (ctx->pinned_spare && ctx->pinned_spare_cap >= bytes) {   // the chunk the last job left behind
+      p = ctx->pinned_spare; cap = ctx->pinned_spare_cap;
+      ctx->pinned_spare = nullptr; ctx->pinned_spare_cap = 0;
+    } else if (cudaHostAlloc(&p, cap, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    job->pinned.push_back({static_cast<uint8_t *>(p), cap});
+    job->pinned_used = 0;
+  }
+  uint8_t *r = job->pinned.back().first + job->pinned_used;
+  job->pinned_used += bytes;
+  return r;
+}
+
 extern "C" int stitch_job_add_tile_jpeg(stitch_job *job, const stitch_tile_desc *tile, const uint8_t *data, size_t len) {
   if (!job || !tile || !data) return STITCH_E_INVALID;
   stitch_ctx *ctx = job->ctx;
@@ -485,14 +704,38 @@ extern "C" int stitch_job_add_tile_jpeg(stitch_job *job, const stitch_tile_desc 
   if ((tile->width && tile->width != f.width) || (tile->height && tile->height != f.height))
     return stitch_fail(ctx, STITCH_E_INVALID, "tile #%u: the descriptor says %ux%u, the JPEG frame %ux%u", tile->image_idx + 1,
                        tile->width, tile->height, f.width, f.height);
-  // the image's tables
-  std::vector<uint8_t> host(sizeof(JdImage));
-  JdImage &img = *reinterpret_cast<JdImage *>(host.data());
+  // host block (pinned): image tables | interval bits | interval subsequences | subsequences | unstuffed data
+  const size_t raw_cap = len - f.ecs_off + 16;
+  uint8_t *h_ecs = job_pinned(job, raw_cap);
+  if (!h_ecs) return stitch_fail(ctx, STITCH_E_NOMEM, "JPEG tile: no pinned staging memory");
+  const uint32_t ue = unstuff(data, len, f, h_ecs);
+  if (ue) return stitch_fail(ctx, STITCH_E_JPEG, "%s", jd_message(ue));
+  const uint32_t n_int = f.n_intervals;
+  const size_t ecs_bytes = ((size_t)f.int_byte[n_int] + 8 + 3) & ~(size_t)3;
+  std::vector<JdSub> subs;
+  std::vector<uint32_t> int_bit(n_int + 1), int_sub(n_int + 1);
+  static const uint32_t sub_bits = getenv("STITCH_JPEG_SUB_BITS") ? (uint32_t)std::max(64, atoi(getenv("STITCH_JPEG_SUB_BITS"))) : SUB_BITS;   // tuning
+  for (uint32_t iv = 0; iv < n_int; iv++) {
+    const uint32_t b0 = f.int_byte[iv] * 8u, b1 = f.int_byte[iv + 1] * 8u;
+    int_bit[iv] = b0;
+    int_sub[iv] = (uint32_t)subs.size();
+    uint32_t at = b0;
+    do {
+      JdSub sb;
+      sb.start_bit = at; sb.end_bit = std::min(b1, at + sub_bits); sb.interval = iv; sb.first = at == b0 ? 1u : 0u;
+      subs.push_back(sb);
+      at += sub_bits;
+    } while (at < b1);
+  }
+  int_bit[n_int] = f.int_byte[n_int] * 8u;
+  int_sub[n_int] = (uint32_t)subs.size();
+  const uint32_t n_subs = (uint32_t)subs.size();
+
+  size_t n_blocks = 0, plane_bytes = 0;
+  JdImage img;
   memset(&img, 0, sizeof img);
   img.width = f.width; img.height = f.height; img.ncomp = f.ncomp; img.hmax = f.hmax; img.vmax = f.vmax;
-  img.mcus_x = f.mcus_x; img.mcus_y = f.mcus_y; img.restart = f.restart; img.n_intervals = (uint32_t)f.rst_off.size();
-  img.ecs_len = (uint32_t)f.ecs_len;
-  size_t n_blocks = 0, plane_bytes = 0;
+  img.mcus_x = f.mcus_x; img.mcus_y = f.mcus_y; img.restart = f.restart; img.n_intervals = n_int; img.n_subs = n_subs;
   for (uint32_t i = 0; i < f.ncomp; i++) {
     JdComp &c = img.c[i];
     c.h = f.c[i].h; c.v = f.c[i].v;
@@ -504,10 +747,13 @@ extern "C" int stitch_job_add_tile_jpeg(stitch_job *job, const stitch_tile_desc 
     memcpy(img.q[i], f.q[f.c[i].tq], sizeof img.q[i]);
     derive(f.dc[f.c[i].td], img.huff[2 * i]);
     derive(f.ac[f.c[i].ta], img.huff[2 * i + 1]);
+    for (uint32_t v = 0; v < c.v; v++)
+      for (uint32_t hh = 0; hh < c.h; hh++) { img.mcu_comp[img.bpm] = i; img.mcu_bx[img.bpm] = hh; img.mcu_by[img.bpm] = v; img.bpm++; }
   }
   if (n_blocks >= (1u << 26) || plane_bytes >= (1ull << 32)) return stitch_fail(ctx, STITCH_E_INVALID, "JPEG tile too large");
   const uint32_t ch = f.ncomp == 1 ? 1u : 4u;
   const size_t out_bytes = (size_t)f.width * f.height * ch;
+  const uint32_t cpi = (f.restart + DC_CHUNK - 1) / DC_CHUNK, n_chunks = n_int * cpi;
   // status slot of this tile (pinned, written by the last kernel below)
   if (!job->h_jdstat) {
     STITCH_CK(cudaHostAlloc((void **)&job->h_jdstat, 4096 * sizeof(uint32_t), cudaHostAllocDefault));
@@ -517,51 +763,81 @@ extern "C" int stitch_job_add_tile_jpeg(stitch_job *job, const stitch_tile_desc 
   const uint32_t slot = (uint32_t)job->jdstat_used++;
   job->h_jdstat[slot] = 0;
 
-  cudaStream_t st = ctx->up;
-  uint8_t *d_out = nullptr, *d_ecs = nullptr, *d_planes = nullptr;
+  // device block: [uploaded: image | int_bit | int_sub | subs | data] [scratch: states, counts, flags, status, DC sums]
+  auto up16 = [](size_t x) { return (x + 15) & ~(size_t)15; };
+  const size_t o_img = 0, o_ibit = up16(sizeof(JdImage)), o_isub = o_ibit + up16((n_int + 1) * 4), o_subs = o_isub + up16((n_int + 1) * 4);
+  const size_t o_ecs = o_subs + up16((size_t)n_subs * sizeof(JdSub)), up_bytes = o_ecs + up16(ecs_bytes);
+  const size_t o_in0 = up_bytes, o_in1 = o_in0 + up16((size_t)n_subs * 8), o_out = o_in1 + up16((size_t)n_subs * 8);
+  const size_t o_last = o_out + up16((size_t)n_subs * 8);
+  const size_t o_nblk = o_last + up16((size_t)n_subs * 8), o_base = o_nblk + up16((size_t)n_subs * 4), o_flags = o_base + up16((size_t)n_subs * 4);
+  const size_t o_stat = o_flags + up16((SYNC_ROUNDS + 2) * 4), o_dc = o_stat + 16, dev_bytes = o_dc + up16((size_t)n_chunks * 3 * 4);
+  uint8_t *h_up = job_pinned(job, o_ecs);   // tables (the data is already pinned at h_ecs)
+  if (!h_up) return stitch_fail(ctx, STITCH_E_NOMEM, "JPEG tile: no pinned staging memory");
+
+  // the decode chains of successive tiles take turns on a few streams (each behind the uploads queued so far)
+  cudaStream_t &slot_stream = ctx->jd_streams[ctx->jd_next++ & 3u];
+  if (!slot_stream) STITCH_CK(cudaStreamCreateWithFlags(&slot_stream, cudaStreamNonBlocking));
+  cudaStream_t st = slot_stream;
+  uint8_t *d_out = nullptr, *d_blk = nullptr, *d_planes = nullptr;
   int16_t *d_coefs = nullptr;
-  uint32_t *d_rst = nullptr, *d_stat = nullptr;
-  JdImage *d_img = nullptr;
-  auto release = [&](bool all) {
-    if (d_ecs) cudaFreeAsync(d_ecs, st);
-    if (d_planes) cudaFreeAsync(d_planes, st);
-    if (d_coefs) cudaFreeAsync(d_coefs, st);
-    if (d_rst) cudaFreeAsync(d_rst, st);
-    if (d_stat) cudaFreeAsync(d_stat, st);
-    if (d_img) cudaFreeAsync(d_img, st);
-    if (all && d_out) cudaFreeAsync(d_out, st);
-  };
   cudaError_t e = cudaMallocAsync((void **)&d_out, out_bytes + 32, st);
-  if (e == cudaSuccess) e = cudaMallocAsync((void **)&d_ecs, f.ecs_len + 16, st);
+  if (e == cudaSuccess) e = cudaMallocAsync((void **)&d_blk, dev_bytes, st);
   if (e == cudaSuccess) e = cudaMallocAsync((void **)&d_planes, plane_bytes, st);
   if (e == cudaSuccess) e = cudaMallocAsync((void **)&d_coefs, n_blocks * 128, st);
-  if (e == cudaSuccess) e = cudaMallocAsync((void **)&d_rst, f.rst_off.size() * 4, st);
-  if (e == cudaSuccess) e = cudaMallocAsync((void **)&d_stat, 4, st);
-  if (e == cudaSuccess) e = cudaMallocAsync((void **)&d_img, sizeof(JdImage), st);
   if (e == cudaSuccess) {
-    img.ecs = d_ecs; img.rst_off = d_rst; img.coefs = d_coefs; img.planes = d_planes; img.out = d_out; img.status = d_stat;
-    e = cudaMemcpyAsync(d_ecs, data + f.ecs_off, f.ecs_len, cudaMemcpyHostToDevice, st);
+    img.ecs = reinterpret_cast<const uint32_t *>(d_blk + o_ecs);
+    img.int_bit = reinterpret_cast<const uint32_t *>(d_blk + o_ibit); img.int_sub = reinterpret_cast<const uint32_t *>(d_blk + o_isub);
+    img.subs = reinterpret_cast<const JdSub *>(d_blk + o_subs);
+    img.st_in[0] = reinterpret_cast<JdState *>(d_blk + o_in0); img.st_in[1] = reinterpret_cast<JdState *>(d_blk + o_in1);
+    img.st_out = reinterpret_cast<JdState *>(d_blk + o_out); img.last_in = reinterpret_cast<JdState *>(d_blk + o_last);
+    img.nblk = reinterpret_cast<uint32_t *>(d_blk + o_nblk); img.base = reinterpret_cast<uint32_t *>(d_blk + o_base);
+    img.flags = reinterpret_cast<uint32_t *>(d_blk + o_flags); img.status = reinterpret_cast<uint32_t *>(d_blk + o_stat);
+    img.dc_sum = reinterpret_cast<int *>(d_blk + o_dc);
+    img.coefs = d_coefs; img.planes = d_planes; img.out = d_out;
+    memcpy(h_up + o_img, &img, sizeof img);
+    memcpy(h_up + o_ibit, int_bit.data(), (n_int + 1) * 4);
+    memcpy(h_up + o_isub, int_sub.data(), (n_int + 1) * 4);
+    memcpy(h_up + o_subs, subs.data(), (size_t)n_subs * sizeof(JdSub));
+    e = cudaMemcpyAsync(d_blk, h_up, o_ecs, cudaMemcpyHostToDevice, st);
   }
-  // pageable sources: the runtime stages them before the call returns
-  if (e == cudaSuccess) e = cudaMemcpyAsync(d_rst, f.rst_off.data(), f.rst_off.size() * 4, cudaMemcpyHostToDevice, st);
-  if (e == cudaSuccess) e = cudaMemcpyAsync(d_img, &img, sizeof img, cudaMemcpyHostToDevice, st);
-  if (e == cudaSuccess) e = cudaMemsetAsync(d_stat, 0, 4, st);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(d_blk + o_ecs, h_ecs, ecs_bytes, cudaMemcpyHostToDevice, st);
+  if (e == cudaSuccess) e = cudaMemsetAsync(d_blk + o_out, 0xff, up16((size_t)n_subs * 8), st);                 // st_out: BAD
+  if (e == cudaSuccess) e = cudaMemsetAsync(d_blk + o_nblk, 0, o_dc - o_nblk, st);                              // counts, flags, status
   if (e == cudaSuccess) e = cudaMemsetAsync(d_coefs, 0, n_blocks * 128, st);
   if (e == cudaSuccess) {
-    jd_huff_kernel<<<(img.n_intervals + JH_THREADS - 1) / JH_THREADS, JH_THREADS, 0, st>>>(d_img);
+    const JdImage *d_img = reinterpret_cast<const JdImage *>(d_blk);
+    const unsigned sub_grid = (n_subs + JH_THREADS - 1) / JH_THREADS;
+    {
+      static PerDevice occ_once;
+      int occ = 0;
+      e = occ_once.get(&occ, [](int *v) { return cudaOccupancyMaxActiveBlocksPerMultiprocessor(v, jd_sync_kernel, JH_THREADS, 0); });
+      const unsigned resident = (unsigned)std::max(1, occ) * (unsigned)ctx->sm_count;
+      const JdImage *arg = d_img;
+      void *args[] = {(void *)&arg};
+      if (e == cudaSuccess)
+        e = cudaLaunchCooperativeKernel((const void *)jd_sync_kernel, dim3(std::min(sub_grid, resident)), dim3(JH_THREADS), args, 0, st);
+    }
+    jd_scan_kernel<<<n_int, 256, 0, st>>>(d_img);
+    jd_emit_kernel<<<sub_grid, JH_THREADS, 0, st>>>(d_img);
+    jd_dc_kernel<0><<<(n_chunks * f.ncomp + 127) / 128, 128, 0, st>>>(d_img, n_chunks);
+    jd_dc_kernel<1><<<(n_int * f.ncomp * 32 + 127) / 128, 128, 0, st>>>(d_img, n_chunks);
+    jd_dc_kernel<2><<<(n_chunks * f.ncomp + 127) / 128, 128, 0, st>>>(d_img, n_chunks);
+    jd_serial_kernel<<<(n_int + JH_THREADS - 1) / JH_THREADS, JH_THREADS, 0, st>>>(d_img);
     jd_idct_kernel<<<(unsigned)((n_blocks + 127) / 128), 128, 0, st>>>(d_img, (uint32_t)n_blocks);
     jd_color_kernel<<<dim3((f.width + 255) / 256, f.height), 256, 0, st>>>(d_img);
-    jd_status_out_kernel<<<1, 1, 0, st>>>(job->h_jdstat + slot, d_stat);
+    jd_status_out_kernel<<<1, 1, 0, st>>>(job->h_jdstat + slot, img.status);
     e = cudaGetLastError();
   }
+  if (d_blk) cudaFreeAsync(d_blk, st);
+  if (d_planes) cudaFreeAsync(d_planes, st);
+  if (d_coefs) cudaFreeAsync(d_coefs, st);
   if (e != cudaSuccess) {
-    release(true);
+    if (d_out) cudaFreeAsync(d_out, st);
     return stitch_fail(ctx, e == cudaErrorMemoryAllocation ? STITCH_E_NOMEM : STITCH_E_CUDA, "JPEG tile: %s", cudaGetErrorString(e));
   }
-  release(false);
   stitch_tile_desc d = *tile;
   d.width = f.width; d.height = f.height; d.bit_depth = 8; d.color_type = f.ncomp == 1 ? 0u : 6u; d.interlace = 0; d.filtered = 0;
-  const int rc = stitch_add_tile_produced(job, &d, d_out, out_bytes);
+  const int rc = stitch_add_tile_produced(job, &d, d_out, out_bytes, st);
   if (rc) { cudaFreeAsync(d_out, st); return rc; }
   job->jd_pending.push_back({slot, (uint32_t)job->tiles.size() - 1u});
   return STITCH_OK;
