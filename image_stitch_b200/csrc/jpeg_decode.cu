@@ -5,11 +5,14 @@
 // The arithmetic follows that published algorithm bit for bit; oracle/jpeg_decode_oracle.c is its CPU restatement,
 // pinned against libjpeg-turbo 3.1.4.1 (tests/golden/jpeg_decode), and tests/test_gpu_jpeg_decode.py compares the two.
 //
-//   host      marker segments (SOF0/SOF1, DQT, DHT, DRI, SOS) are parsed and the restart markers of the entropy-coded
-//             segment located while the file is still in host memory -- container work, like cutting a PNG into chunks
-//   entropy   one thread per restart interval (DC predictors restart there, T.81 F.2.1.3): 9-bit look-ahead tables in
-//             shared memory, canonical walk for longer codes; coefficients go to HBM de-zigzagged.  A file without
-//             restart markers is one interval, i.e. one thread: tiles then decode side by side, not inside a tile
+//   host      marker segments (SOF0/SOF1, DQT, DHT, DRI, SOS) are parsed and the entropy-coded segment is copied into
+//             pinned staging memory without its framing (the zero stuffed after every 0xFF data byte, the RSTn markers
+//             between restart intervals) -- container work, like cutting a PNG into chunks; no code is decoded
+//   entropy   speculative parallel Huffman walk inside every restart interval (see "entropy decoding" below):
+//             subsequences of 1024 bits, one thread each, relaxation rounds in one cooperative kernel until the
+//             hand-over states settle, a prefix sum for block positions, a last walk that writes the coefficients
+//             de-zigzagged, and a prefix sum for the DC predictions; 9-bit look-ahead tables in shared memory.  One
+//             thread per restart interval decodes the file only if the walk has not settled after 32 rounds
 //   IDCT      one thread per 8x8 block: dequantise + jpeg_idct_islow, samples into the component's plane
 //   colour    one thread per 4 output pixels: h2v1 / h2v2 fancy upsampling (replication when the downsampled width is
 //             <= 2), context rows replicated at the image edges, YCbCr -> RGBA8; gray is copied
@@ -714,7 +717,9 @@ extern "C" int stitch_job_add_tile_jpeg(stitch_job *job, const stitch_tile_desc 
   const size_t ecs_bytes = ((size_t)f.int_byte[n_int] + 8 + 3) & ~(size_t)3;
   std::vector<JdSub> subs;
   std::vector<uint32_t> int_bit(n_int + 1), int_sub(n_int + 1);
-  static const uint32_t sub_bits = getenv("STITCH_JPEG_SUB_BITS") ? (uint32_t)std::max(64, atoi(getenv("STITCH_JPEG_SUB_BITS"))) : SUB_BITS;   // tuning
+  // STITCH_JPEG_SUB_BITS: tuning and tests (tiny subsequences do not settle and exercise the serial decoder); read at every call
+  const char *sb_env = getenv("STITCH_JPEG_SUB_BITS");
+  const uint32_t sub_bits = sb_env ? (uint32_t)std::min(1 << 30, std::max(64, atoi(sb_env))) : SUB_BITS;
   for (uint32_t iv = 0; iv < n_int; iv++) {
     const uint32_t b0 = f.int_byte[iv] * 8u, b1 = f.int_byte[iv + 1] * 8u;
     int_bit[iv] = b0;

@@ -57,6 +57,16 @@ def test_larger_images_with_and_without_restart_intervals(ctx):
         assert np.array_equal(got, orc.jpeg_decode(buf.getvalue())), opts
 
 
+@pytest.mark.parametrize("sub_bits", ["64", "256", "4096", "1000000000"])
+def test_every_decoder_path_gives_the_same_pixels(ctx, monkeypatch, sub_bits):
+    """Subsequence length of the speculative walk: 64 bits never settles (the one-thread-per-interval decoder takes
+    over), 256 needs many rounds, 10^9 is one subsequence per restart interval."""
+    monkeypatch.setenv("STITCH_JPEG_SUB_BITS", sub_bits)
+    for name in ("c420_big_opt", "c420_big_rst", "g_big", "c422_rst1_opt", "c444_q100_opt", "c420_q1"):
+        data = _file(name)
+        assert np.array_equal(ctx.decode_jpeg(data), orc.jpeg_decode(data)), name
+
+
 def test_errors(ctx):
     with pytest.raises(_native.StitchError, match="Invalid JPEG: missing SOI marker"):
         ctx.decode_jpeg(b"\x89PNG\r\n\x1a\n0000")
