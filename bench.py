@@ -53,7 +53,7 @@ WORKLOAD_CONFIG = {
 def profiled_traffic_bytes(*summaries, scale: float = 1.0):
     """dram__bytes_read.sum + dram__bytes_write.sum of the profiled kernel(s) from committed `ncu --set full`
     captures of this same workload (one launch each), times `scale`.  None when a summary is missing."""
-    summaries = summaries or ("profiles/r2_prof_fused.summary.csv",)
+    summaries = summaries or ("profiles/r2c_prof_fused_c2.summary.csv",)
     unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
     total = 0.0
     for summary in summaries:
@@ -63,8 +63,8 @@ def profiled_traffic_bytes(*summaries, scale: float = 1.0):
             with open(path) as f:
                 for line in f:
                     parts = line.strip().split(",")
-                    if len(parts) == 3 and parts[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum") and parts[0] not in got:
-                        got[parts[0]] = float(parts[2]) * unit.get(parts[1], 1.0)
+                    if len(parts) == 3 and parts[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):   # every kernel of the capture
+                        got[parts[0]] = got.get(parts[0], 0.0) + float(parts[2]) * unit.get(parts[1], 1.0)
         except OSError:
             return None
         if len(got) != 2:
@@ -450,6 +450,44 @@ def jpeg_section(ctx, dev, peak: float):
     return res
 
 
+def jpeg_decode_section(ctx):
+    """16 baseline JPEG tiles of 2048^2 (4:2:0, q = 85, no restart markers: the common kind) decoded on the
+    device, composited and filtered -- wall time from the first add_tile_jpeg (host buffers, the files cross the bus
+    compressed) to the finished band on the device.  The files are made with Pillow when the box has it."""
+    import io
+    from image_stitch_b200 import _native, synth
+    try:
+        from PIL import Image
+    except ImportError:
+        return {"unavailable": "Pillow is not installed: no JPEG file to decode"}
+    tile, grid = C3_TILE, 4
+    pic = synth.smooth_rgba8(np.random.default_rng(8), tile, tile, "opaque").reshape(tile, tile, 4)[..., :3]
+    buf = io.BytesIO()
+    Image.fromarray(np.ascontiguousarray(pic), "RGB").save(buf, "JPEG", quality=85, subsampling=2)
+    data = buf.getvalue()
+    t0 = time.perf_counter()
+    Image.open(io.BytesIO(data)).load()
+    cpu_ms = (time.perf_counter() - t0) * 1e3
+    best = None
+    for _ in range(4):
+        with _native.Job(ctx, tile * grid, tile * grid, 8, _native.OUT_PNG_FILTERED, False, bytes(4)) as job:
+            t0 = time.perf_counter()
+            for k in range(grid * grid):
+                job.add_tile_jpeg(data, dst_x=(k % grid) * tile, dst_y=(k // grid) * tile, image_idx=k)
+            t1 = time.perf_counter()
+            _, tm = job.run_band(0, tile * grid, download=False)
+            t2 = time.perf_counter()
+        ms = ((t1 - t0) * 1e3, (t2 - t0) * 1e3, tm["compose_ms"])
+        best = ms if best is None or ms[1] < best[1] else best
+    px = grid * grid * tile * tile
+    return {"workload": f"{grid * grid} JPEG tiles of {tile}x{tile} (4:2:0, q=85, {len(data)} bytes each, no restart markers) -> "
+                        f"{tile * grid}x{tile * grid} filtered PNG scanlines",
+            "queued_ms": best[0], "wall_ms": best[1], "composite_filter_ms": best[2], "value_MPix_s": px / 1e6 / (best[1] / 1e3),
+            "h2d_bytes": len(data) * grid * grid, "libjpeg_turbo_one_core_ms_per_tile": cpu_ms,
+            "note": "wall clock around add_tile_jpeg x 16 + run_band (decode kernels are queued at add time on four streams); "
+                    "byte-exact against libjpeg-turbo (tests/test_gpu_jpeg_decode.py)"}
+
+
 def run_ours(args, rank: int, world: int, local_rank: int):
     import torch
     import torch.distributed as dist
@@ -668,18 +706,22 @@ def run_ours(args, rank: int, world: int, local_rank: int):
         "gpu_launches": value_launches,
         "roofline": {"bound": "hbm", "kernel": "composite+filter-select (kernels b+c), C2", "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": achieved / peak, "traffic": profiled_traffic_bytes(), "peak_source": peak_src,
-                     "traffic_source": "profiles/r2_prof_fused.summary.csv (ncu --set full of this kernel on this workload, one launch, bytes)",
+                     "traffic_source": "profiles/r2c_prof_fused_c2.summary.csv (ncu --set full of this kernel on this workload, one launch, bytes)",
                      "algorithmic_bytes_per_launch": alg_bytes, "avg_ms": cmp_avg,
                      "frac_of_8TBps": achieved / 8000.0},
-        "roofline_c3": {"bound": "hbm", "kernel": "composite + filter-select on C3 (composite to a canvas in HBM, then the unit kernel reads it back)",
+        "roofline_c3": {"bound": "hbm", "kernel": "composite + filter-select on C3; with blending: composite to a canvas in HBM, then the unit kernel "
+                                                  "reads it back; without: the unit kernel's plan mode (plan + prepare + fused, no canvas)",
                         "workload": "C3: 256 positioned overlapping 2048x2048 RGBA8 tiles (half opaque, a quarter alpha 1..254, a quarter 0/255 "
                                     "masks), zIndex alpha blending, 32768x32768 canvas, background #FFFFFF80; every tile has its own buffer",
                         "avg_ms": c3_blend_ms, "achieved": c3_alg / (c3_blend_ms / 1e3) / 1e9, "peak": peak, "unit": "GB/s",
                         "frac": c3_alg / (c3_blend_ms / 1e3) / 1e9 / peak, "value_MPix_s": c3_px / 1e6 / (c3_blend_ms / 1e3),
-                        "algorithmic_bytes_per_launch": c3_alg, "traffic": profiled_traffic_bytes("profiles/r2_prof_c3_compose.summary.csv", "profiles/r2_prof_c3_filter.summary.csv", scale=8.0),
-                        "traffic_source": "8 x (compose_canvas_kernel + fused_kernel of one 4096-row band), profiles/r2_prof_c3_*.summary.csv",
+                        "algorithmic_bytes_per_launch": c3_alg, "traffic": profiled_traffic_bytes("profiles/r2c_prof_c3_blend.summary.csv", scale=8.0),
+                        "traffic_source": "8 x (compose_plan_kernel + fused_kernel of one 4096-row band), profiles/r2c_prof_c3_blend.summary.csv",
                         "blending_off": {"avg_ms": c3_noblend_ms, "frac": c3_alg / (c3_noblend_ms / 1e3) / 1e9 / peak,
-                                         "value_MPix_s": c3_px / 1e6 / (c3_noblend_ms / 1e3)},
+                                         "value_MPix_s": c3_px / 1e6 / (c3_noblend_ms / 1e3),
+                                         "traffic": profiled_traffic_bytes("profiles/r2c_prof_c3_noblend.summary.csv", scale=8.0),
+                                         "traffic_source": "8 x (fused_plan_iv + fused_prep + fused_kernel of one 4096-row band), "
+                                                           "profiles/r2c_prof_c3_noblend.summary.csv"},
                         "scaling": "strong: the one canvas is cut into n_gpus row bands, max over ranks", "rows_per_gpu": C3_CANVAS // world},
         "kernels": {"unfilter": {"avg_ms": dec_avg, "achieved_GBps": unf_achieved, "frac": unf_achieved / peak, "tiles": n_tiles,
                                  "filter_types": "random per row"},
@@ -693,6 +735,7 @@ def run_ours(args, rank: int, world: int, local_rank: int):
     if world == 1:
         line["kernels"]["unfilter_variants"] = unfilter_variants(ctx, dev, peak)
         line["jpeg"] = jpeg_section(ctx, dev, peak)
+        line["jpeg_decode"] = jpeg_decode_section(ctx)
     if not args.no_cpu_baseline:
         threads = cpu_threads(args)
         _, dt1 = cpu_sample(tiles, args.cpu_sample_rows, threads)
