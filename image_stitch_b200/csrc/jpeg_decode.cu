@@ -11,7 +11,7 @@
 //   entropy   speculative parallel Huffman walk inside every restart interval (see "entropy decoding" below):
 //             subsequences of 1024 bits, one thread each, relaxation rounds in one cooperative kernel until the
 //             hand-over states settle, a prefix sum for block positions, a last walk that writes the coefficients
-//             de-zigzagged, and a prefix sum for the DC predictions; 9-bit look-ahead tables in shared memory.  One
+//             de-zigzagged, and a prefix sum for the DC predictions; 11-bit look-ahead tables in shared memory.  One
 //             thread per restart interval decodes the file only if the walk has not settled after 32 rounds
 //   IDCT      one thread per 8x8 block: dequantise + jpeg_idct_islow, samples into the component's plane
 //   colour    one thread per 4 output pixels: h2v1 / h2v2 fancy upsampling (replication when the downsampled width is
@@ -54,7 +54,7 @@ const char *jd_message(uint32_t code) {
   }
 }
 
-constexpr int LOOK = 9;            // look-ahead bits of the Huffman tables
+constexpr int LOOK = 11;           // look-ahead bits of the Huffman tables (longer codes are rare: out-of-line canonical walk)
 constexpr uint32_t SUB_BITS = 1024;  // bits per subsequence of the speculative walk
 constexpr int SYNC_ROUNDS = 32;      // relaxation rounds before the serial decoder takes over (a settled walk skips the rest)
 constexpr uint32_t BAD = 0xffffffffu;
@@ -143,6 +143,15 @@ __device__ __forceinline__ int16_t *jd_block(const JdImage &img, const uint32_t 
   return img.coefs + ((size_t)c.block0 + (size_t)(my * c.v + img.mcu_by[j]) * c.wb + (mx * c.h + img.mcu_bx[j])) * 64;
 }
 
+// Canonical walk (T.81 F.2.2.3) for codes longer than the look-ahead: code bits << 8 | symbol, 0 = no such code.
+static __device__ __noinline__ uint32_t jd_long_code(const JdHuff &h, const uint32_t w) {
+  for (int l = LOOK + 1; l <= 16; l++) {
+    const int32_t code = (int32_t)(w >> (32 - l));
+    if (h.maxcode[l] >= 0 && code <= h.maxcode[l] && code >= h.mincode[l]) return ((uint32_t)l << 8) | h.vals[h.valptr[l] + code - h.mincode[l]];
+  }
+  return 0u;
+}
+
 // Walks the symbols that start in [s.bp, limit): EMIT writes coefficients (DC as the difference, F.2.1.3), starting
 // with block sequence number g and never past g_end (the interval's padding follows its last block).  end_bit: the
 // interval's end.  Returns the state after the last symbol and the number of blocks completed; err != 0 (EMIT only):
@@ -175,11 +184,9 @@ __device__ __forceinline__ JdState jd_walk(const JdImage &img, const JdHuff *sh,
     const JdHuff &h = sh[2u * comp + (k ? 1u : 0u)];
     const uint32_t e = h.look[w >> (32 - LOOK)];
     uint32_t len = e >> 8, sym = e & 0xffu;
-    if (!e) {   // a code longer than the look-ahead: canonical walk
-      for (int l = LOOK + 1; l <= 16; l++) {
-        const int32_t code = (int32_t)(w >> (32 - l));
-        if (h.maxcode[l] >= 0 && code <= h.maxcode[l] && code >= h.mincode[l]) { len = (uint32_t)l; sym = h.vals[h.valptr[l] + code - h.mincode[l]]; break; }
-      }
+    if (!e) {   // a code longer than the look-ahead
+      const uint32_t e2 = jd_long_code(h, w);
+      len = e2 >> 8; sym = e2 & 0xffu;
       if (!len) { if (EMIT) err = JD_E_HUFF; s.bp = BAD; return s; }
     }
     const uint32_t sbits = k ? (sym & 15u) : sym, total = len + sbits;

@@ -59,20 +59,27 @@ def _c3_tiles(rng, canvas, n_side, tile):
     return tiles
 
 
-def test_c3_positioned_blend_32k_sampled_bands(ctx, capsys):
-    """256 positioned overlapping 2048x2048 RGBA8 tiles, zIndex alpha blending, 32768x32768 canvas."""
+@pytest.mark.parametrize("blend,route", [(True, None), (False, None), (True, "1"), (False, "0")])
+def test_c3_positioned_blend_32k_sampled_bands(ctx, capsys, monkeypatch, blend, route):
+    """256 positioned overlapping 2048x2048 RGBA8 tiles on a 32768x32768 canvas, with and without zIndex alpha
+    blending, on the route the library picks (blended: via the canvas; not blended: the unit kernel's plan mode) and on
+    the other one (STITCH_SINGLE_PASS=1 / 0)."""
+    if route is None:
+        monkeypatch.delenv("STITCH_SINGLE_PASS", raising=False)
+    else:
+        monkeypatch.setenv("STITCH_SINGLE_PASS", route)
     canvas, tile = 32768, 2048
     rng = np.random.default_rng(3)
     tiles = _c3_tiles(rng, canvas, 16, tile)
     bg = bytes([255, 255, 255, 128])
-    with _native.Job(ctx, canvas, canvas, 8, _native.OUT_PNG_FILTERED, True, bg) as job:
+    with _native.Job(ctx, canvas, canvas, 8, _native.OUT_PNG_FILTERED, blend, bg) as job:
         for t in tiles:
             job.add_tile(t["pixels"].reshape(-1), width=tile, height=tile, bit_depth=8, color_type=6, filtered=0,
                          dst_x=t["dst_x"], dst_y=t["dst_y"], src_off_x=t["src_off_x"], src_off_y=t["src_off_y"],
                          vis_w=t["vis_w"], vis_h=t["vis_h"], z_index=t["z_index"], image_idx=t["image_idx"])
         for a, b in ((0, 10), (2040, 2056), (16380, 16390), (32760, 32768)):
             got, _ = job.run_band(a, b)
-            want = orc.render_rows(canvas, canvas, 8, bg, True, tiles, a, b, 0)
+            want = orc.render_rows(canvas, canvas, 8, bg, blend, tiles, a, b, 0)
             assert np.array_equal(np.asarray(got), want), (a, b)
         # a large band equals its pieces (size-independent property), and gives a timing for DESIGN.md
         big, tm = job.run_band(4096, 8192)
@@ -83,7 +90,7 @@ def test_c3_positioned_blend_32k_sampled_bands(ctx, capsys):
         job.run_band(4096, 8192, download=False)          # scratch buffers grow to the band's size here
         _, tm = job.run_band(4096, 8192, download=False)
     with capsys.disabled():
-        print(f"\n[c3] 4096 rows x 32768 px, blending: compose+filter {tm['compose_ms']:.3f} ms "
+        print(f"\n[c3] 4096 rows x 32768 px, blending {blend}, STITCH_SINGLE_PASS {route}: compose+filter {tm['compose_ms']:.3f} ms "
               f"({4096 * 32768 / tm['compose_ms'] / 1e3:.0f} MPix/s)")
 
 
