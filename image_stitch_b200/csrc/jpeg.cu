@@ -23,6 +23,8 @@
 //   J7 stuff    CTA = one MCU row: byte stuffing, RSTm marker, final bytes
 #include "job.h"
 
+#include <cstdlib>
+
 #include <cstring>
 
 using namespace stitch;
@@ -137,64 +139,80 @@ struct JpegGeom {
   uint32_t rows_in_band;    // canvas rows held at `canvas`
 };
 
-__global__ void __launch_bounds__(128) jpeg_dct_kernel(const uint8_t *canvas, size_t pitch, JpegGeom g, int16_t *coefs,
-                                                       unsigned long long *nzmask) {
-  const uint32_t m = blockIdx.x * blockDim.x + threadIdx.x;  // MCU in the row
-  if (m >= g.mcus) return;
-  // The three components of an MCU are done by the same thread one after the other: the pixels come from
-  // HBM once, the second and third pass hit L1.
-  for (uint32_t it = blockIdx.y * 3u; it < g.mrows * 3u; it += (it % 3u == 2u) ? gridDim.y * 3u - 2u : 1u) {
-    const uint32_t mr = it / 3u, comp = it - mr * 3u;  // 0 Y, 1 Cb, 2 Cr
-    int d[64];
-#pragma unroll
-    for (int yy = 0; yy < 8; yy++) {
-      uint32_t y = g.y0 + mr * 8 + yy;
+// One CTA = 128 MCUs of one MCU row (8 canvas rows x 1024 pixels), one thread per MCU.  The 32 KB of pixels are staged
+// in shared memory by coalesced 16-byte cp.async (the threads' own reads are 32 bytes at a stride of 32: half-used
+// sectors, and the second and third component pass used to depend on L1 keeping them), then the three components of an
+// MCU are done by the same thread one after the other from there.
+static constexpr int JD_MCUS = 128;
+__global__ void __launch_bounds__(JD_MCUS, 6) jpeg_dct_kernel(const uint8_t *canvas, size_t pitch, JpegGeom g, int16_t *coefs,
+                                                              unsigned long long *nzmask) {
+  __shared__ __align__(16) uint8_t px_sm[8][JD_MCUS * 32];
+  const uint32_t m = blockIdx.x * JD_MCUS + threadIdx.x;  // MCU in the row
+  const uint32_t x0 = blockIdx.x * JD_MCUS * 8u;          // first pixel column of the CTA
+  const uint32_t px_here = min(g.width - x0, (uint32_t)JD_MCUS * 8u);   // pixels of the CTA's span that exist
+  for (uint32_t mr = blockIdx.y; mr < g.mrows; mr += gridDim.y) {
+    __syncthreads();   // the previous MCU row's reads are over
+    for (uint32_t c = threadIdx.x; c < 8u * (JD_MCUS * 32u / 16u); c += JD_MCUS) {
+      const uint32_t yy = c / (JD_MCUS * 2u), q = c % (JD_MCUS * 2u);   // row, 16-byte chunk (4 pixels) in the row
+      if (q * 4u >= px_here) continue;
+      uint32_t y = g.y0 + mr * 8u + yy;
       y = min(y, g.height - 1u) - g.y0;  // replicate the last image row below the bottom edge
-      const uint8_t *row = canvas + (size_t)y * pitch;
-      uint32_t px[8];
-      if (m * 8u + 8u <= g.width) {
-        const uint4 a = __ldg(reinterpret_cast<const uint4 *>(row + (size_t)m * 32)), b = __ldg(reinterpret_cast<const uint4 *>(row + (size_t)m * 32 + 16));
-        px[0] = a.x; px[1] = a.y; px[2] = a.z; px[3] = a.w; px[4] = b.x; px[5] = b.y; px[6] = b.z; px[7] = b.w;
-      } else {
+      const uint32_t sa = (uint32_t)__cvta_generic_to_shared(&px_sm[yy][q * 16u]);
+      const uint8_t *src = canvas + (size_t)y * pitch + (size_t)x0 * 4u + q * 16u;
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(src) : "memory");
+    }
+    asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+    if (m >= g.mcus) continue;
+    for (uint32_t comp = 0; comp < 3u; comp++) {  // 0 Y, 1 Cb, 2 Cr
+      int d[64];
+#pragma unroll
+      for (int yy = 0; yy < 8; yy++) {
+        uint32_t px[8];
+        if (m * 8u + 8u <= g.width) {
+          const uint4 a = *reinterpret_cast<const uint4 *>(&px_sm[yy][threadIdx.x * 32u]), b = *reinterpret_cast<const uint4 *>(&px_sm[yy][threadIdx.x * 32u + 16u]);
+          px[0] = a.x; px[1] = a.y; px[2] = a.z; px[3] = a.w; px[4] = b.x; px[5] = b.y; px[6] = b.z; px[7] = b.w;
+        } else {
+#pragma unroll
+          for (int xx = 0; xx < 8; xx++) {
+            const uint32_t x = min(m * 8u + xx, g.width - 1u);  // replicate the last column
+            px[xx] = *reinterpret_cast<const uint32_t *>(&px_sm[yy][(x - x0) * 4u]);
+          }
+        }
 #pragma unroll
         for (int xx = 0; xx < 8; xx++) {
-          const uint32_t x = min(m * 8u + xx, g.width - 1u);  // replicate the last column
-          px[xx] = *reinterpret_cast<const uint32_t *>(row + (size_t)x * 4);
+          const int r = px[xx] & 0xff, gg = (px[xx] >> 8) & 0xff, b = (px[xx] >> 16) & 0xff;  // alpha dropped
+          int v;
+          if (comp == 0) v = (19595 * r + 38470 * gg + 7471 * b + 32768) >> 16;
+          else if (comp == 1) v = (-11059 * r - 21709 * gg + 32768 * b + (128 << 16) + 32767) >> 16;
+          else v = (32768 * r - 27439 * gg - 5329 * b + (128 << 16) + 32767) >> 16;
+          d[yy * 8 + xx] = v - 128;
         }
       }
 #pragma unroll
-      for (int xx = 0; xx < 8; xx++) {
-        const int r = px[xx] & 0xff, gg = (px[xx] >> 8) & 0xff, b = (px[xx] >> 16) & 0xff;  // alpha dropped
-        int v;
-        if (comp == 0) v = (19595 * r + 38470 * gg + 7471 * b + 32768) >> 16;
-        else if (comp == 1) v = (-11059 * r - 21709 * gg + 32768 * b + (128 << 16) + 32767) >> 16;
-        else v = (32768 * r - 27439 * gg - 5329 * b + (128 << 16) + 32767) >> 16;
-        d[yy * 8 + xx] = v - 128;
+      for (int i = 0; i < 8; i++)
+        fdct_1d(d[8 * i], d[8 * i + 1], d[8 * i + 2], d[8 * i + 3], d[8 * i + 4], d[8 * i + 5], d[8 * i + 6], d[8 * i + 7], true);
+#pragma unroll
+      for (int i = 0; i < 8; i++)
+        fdct_1d(d[i], d[8 + i], d[16 + i], d[24 + i], d[32 + i], d[40 + i], d[48 + i], d[56 + i], false);
+      const int cls = comp ? 1 : 0;
+      uint32_t packed[32];
+      uint32_t nz_lo = 0u, nz_hi = 0u;  // bit k: AC coefficient k (zigzag order) is not zero
+#pragma unroll
+      for (int k = 0; k < 64; k++) {
+        const int c = d[zz_nat(k)];
+        const uint32_t q8 = c_q8[cls][k], n = (uint32_t)abs(c) + (q8 >> 1);
+        const int qv = (int)__umulhi(n, c_recip[cls][k]);
+        const uint32_t v16 = (uint32_t)(c < 0 ? -qv : qv) & 0xffffu;
+        if (k & 1) packed[k >> 1] |= v16 << 16; else packed[k >> 1] = v16;
+        if (k > 0 && qv != 0) { if (k < 32) nz_lo |= 1u << (k & 31); else nz_hi |= 1u << (k & 31); }
       }
+      const size_t blk_idx = ((size_t)mr * g.mcus + m) * 3 + comp;
+      nzmask[blk_idx] = ((unsigned long long)nz_hi << 32) | nz_lo;
+      uint4 *o = reinterpret_cast<uint4 *>(coefs + blk_idx * 64);
+#pragma unroll
+      for (int k = 0; k < 8; k++) o[k] = make_uint4(packed[4 * k], packed[4 * k + 1], packed[4 * k + 2], packed[4 * k + 3]);
     }
-#pragma unroll
-    for (int i = 0; i < 8; i++)
-      fdct_1d(d[8 * i], d[8 * i + 1], d[8 * i + 2], d[8 * i + 3], d[8 * i + 4], d[8 * i + 5], d[8 * i + 6], d[8 * i + 7], true);
-#pragma unroll
-    for (int i = 0; i < 8; i++)
-      fdct_1d(d[i], d[8 + i], d[16 + i], d[24 + i], d[32 + i], d[40 + i], d[48 + i], d[56 + i], false);
-    const int cls = comp ? 1 : 0;
-    uint32_t packed[32];
-    uint32_t nz_lo = 0u, nz_hi = 0u;  // bit k: AC coefficient k (zigzag order) is not zero
-#pragma unroll
-    for (int k = 0; k < 64; k++) {
-      const int c = d[zz_nat(k)];
-      const uint32_t q8 = c_q8[cls][k], n = (uint32_t)abs(c) + (q8 >> 1);
-      const int qv = (int)__umulhi(n, c_recip[cls][k]);
-      const uint32_t v16 = (uint32_t)(c < 0 ? -qv : qv) & 0xffffu;
-      if (k & 1) packed[k >> 1] |= v16 << 16; else packed[k >> 1] = v16;
-      if (k > 0 && qv != 0) { if (k < 32) nz_lo |= 1u << (k & 31); else nz_hi |= 1u << (k & 31); }
-    }
-    const size_t blk_idx = ((size_t)mr * g.mcus + m) * 3 + comp;
-    nzmask[blk_idx] = ((unsigned long long)nz_hi << 32) | nz_lo;
-    uint4 *o = reinterpret_cast<uint4 *>(coefs + blk_idx * 64);
-#pragma unroll
-    for (int k = 0; k < 8; k++) o[k] = make_uint4(packed[4 * k], packed[4 * k + 1], packed[4 * k + 2], packed[4 * k + 3]);
   }
 }
 
@@ -521,7 +539,7 @@ int stitch_jpeg_encode_band(stitch_job *job, uint32_t y0, uint32_t y1, const uin
 
   {
     dim3 grid((g.mcus + 127u) / 128u, g.mrows < 4096u ? g.mrows : 4096u);
-    jpeg_dct_kernel<<<grid, 128, 0, ctx->stream>>>(canvas, canvas_pitch, g, coefs, nzmask);
+    jpeg_dct_kernel<<<grid, JD_MCUS, 0, ctx->stream>>>(canvas, canvas_pitch, g, coefs, nzmask);
     STITCH_CK(cudaGetLastError());
   }
   const uint32_t row_grid = g.mrows < 148u * 8u ? g.mrows : 148u * 8u;
