@@ -168,6 +168,57 @@ napi_value AddTile(napi_env env, napi_callback_info info) {
   return nullptr;
 }
 
+// addTileJpeg(job, placement, file: Uint8Array): a baseline JPEG file as a tile, decoded on the device (SURVEY 8f.4;
+// replaces decodeJpeg + the row hand-over, src/decoders/jpeg-decoder.ts:239-281, :317-347).  Throws "Invalid JPEG: ..."
+// or "Unsupported JPEG: ..." (the caller then falls back to the reference's own decoders and addTile).
+napi_value AddTileJpeg(napi_env env, napi_callback_info info) {
+  size_t argc = 3;
+  napi_value argv[3];
+  NAPI_OK(napi_get_cb_info(env, info, &argc, argv, nullptr, nullptr));
+  Job *j = nullptr;
+  NAPI_OK(napi_get_value_external(env, argv[0], reinterpret_cast<void **>(&j)));
+  uint8_t *data = nullptr;
+  size_t len = 0;
+  if (!GetBytes(env, argv[2], &data, &len)) { napi_throw_type_error(env, nullptr, "addTileJpeg: file must be a Uint8Array"); return nullptr; }
+  stitch_tile_desc t;
+  std::memset(&t, 0, sizeof t);
+  uint32_t w = 0, h = 0, ch = 0;
+  int rc = stitch_jpeg_info(j->owner->ctx, data, len, &w, &h, &ch);
+  if (rc != STITCH_OK) return ThrowStitch(env, j->owner, rc);
+  GetI32(env, argv[1], "dstX", &t.dst_x);
+  GetI32(env, argv[1], "dstY", &t.dst_y);
+  GetU32(env, argv[1], "srcOffX", &t.src_off_x);
+  GetU32(env, argv[1], "srcOffY", &t.src_off_y);
+  GetU32(env, argv[1], "visW", &t.vis_w, w);
+  GetU32(env, argv[1], "visH", &t.vis_h, h);
+  GetI32(env, argv[1], "zIndex", &t.z_index);
+  GetU32(env, argv[1], "imageIdx", &t.image_idx);
+  rc = stitch_job_add_tile_jpeg(j->job, &t, data, len);
+  if (rc != STITCH_OK) return ThrowStitch(env, j->owner, rc);
+  return nullptr;
+}
+
+// jpegInfo(ctx, file) -> { width, height, channels }: parseJpegHeader + getHeader, src/decoders/jpeg-decoder.ts:46-94, :298-315
+napi_value JpegInfo(napi_env env, napi_callback_info info) {
+  size_t argc = 2;
+  napi_value argv[2];
+  NAPI_OK(napi_get_cb_info(env, info, &argc, argv, nullptr, nullptr));
+  Ctx *c = nullptr;
+  NAPI_OK(napi_get_value_external(env, argv[0], reinterpret_cast<void **>(&c)));
+  uint8_t *data = nullptr;
+  size_t len = 0;
+  if (!GetBytes(env, argv[1], &data, &len)) { napi_throw_type_error(env, nullptr, "jpegInfo: file must be a Uint8Array"); return nullptr; }
+  uint32_t w = 0, h = 0, ch = 0;
+  const int rc = stitch_jpeg_info(c->ctx, data, len, &w, &h, &ch);
+  if (rc != STITCH_OK) return ThrowStitch(env, c, rc);
+  napi_value obj, v;
+  NAPI_OK(napi_create_object(env, &obj));
+  NAPI_OK(napi_create_uint32(env, w, &v)); NAPI_OK(napi_set_named_property(env, obj, "width", v));
+  NAPI_OK(napi_create_uint32(env, h, &v)); NAPI_OK(napi_set_named_property(env, obj, "height", v));
+  NAPI_OK(napi_create_uint32(env, ch, &v)); NAPI_OK(napi_set_named_property(env, obj, "channels", v));
+  return obj;
+}
+
 // runBand(job, y0, y1, out: Uint8Array) -> Promise<number of bytes written>
 // The band is rendered on a libuv worker thread: the event loop is never blocked (calls on one job are
 // serialised by the host, which awaits bands in ascending y0 before feeding deflate).
@@ -267,6 +318,8 @@ napi_value Init(napi_env env, napi_value exports) {
       {"createContext", nullptr, CreateContext, nullptr, nullptr, nullptr, napi_default, nullptr},
       {"createJob", nullptr, CreateJob, nullptr, nullptr, nullptr, napi_default, nullptr},
       {"addTile", nullptr, AddTile, nullptr, nullptr, nullptr, napi_default, nullptr},
+      {"addTileJpeg", nullptr, AddTileJpeg, nullptr, nullptr, nullptr, napi_default, nullptr},
+      {"jpegInfo", nullptr, JpegInfo, nullptr, nullptr, nullptr, napi_default, nullptr},
       {"runBand", nullptr, RunBand, nullptr, nullptr, nullptr, napi_default, nullptr},
       {"jpegHeader", nullptr, JpegHeader, nullptr, nullptr, nullptr, napi_default, nullptr},
       {"destroyJob", nullptr, DestroyJob, nullptr, nullptr, nullptr, napi_default, nullptr},

@@ -20,6 +20,8 @@ export interface ImageDecoderLike {
   inflated?(): Promise<{ data: Uint8Array; header: PngHeader }>;
   /** Optional: the concatenated IDAT payloads (zlib stream): inflated on the device (filtered = 2). */
   deflated?(): Promise<{ data: Uint8Array; header: PngHeader }>;
+  /** Optional (JPEG decoders): the file itself -- decoded on the device by stitch_job_add_tile_jpeg. */
+  jpegFile?(): Uint8Array;
 }
 export interface PlacedTile {
   imageIdx: number; x: number; y: number;           // clipped top-left on the canvas (>= 0)
@@ -33,6 +35,8 @@ interface Native {
   createContext(device: number): unknown;
   createJob(ctx: unknown, desc: Record<string, unknown>): unknown;
   addTile(job: unknown, desc: Record<string, unknown>, data: Uint8Array, plte?: Uint8Array, trns?: Uint8Array): void;
+  addTileJpeg(job: unknown, placement: Record<string, unknown>, file: Uint8Array): void;
+  jpegInfo(ctx: unknown, file: Uint8Array): { width: number; height: number; channels: number };
   runBand(job: unknown, y0: number, y1: number, out: Uint8Array): Promise<number>;
   jpegHeader(width: number, height: number, quality: number): Uint8Array;
   destroyJob(job: unknown): void;
@@ -77,6 +81,15 @@ export class GpuStitchJob {
   /** Registers one input; errors carry the reference's messages (e.g. "Unsupported source color type: 3"). */
   async addTile(decoder: ImageDecoderLike, t: PlacedTile): Promise<void> {
     let data: Uint8Array; let header: PngHeader; let filtered = 0;
+    if (decoder.jpegFile) {   // a JPEG input: the file itself, decoded on the device (SURVEY 8f.4)
+      try {
+        native.addTileJpeg(this.job, { dstX: t.x, dstY: t.y, srcOffX: t.sourceOffsetX, srcOffY: t.sourceOffsetY,
+          visW: t.visibleWidth, visH: t.visibleHeight, zIndex: t.zIndex, imageIdx: t.imageIdx }, decoder.jpegFile());
+        return;
+      } catch (e) {   // progressive, 12-bit, CMYK ...: the reference's own decoders take it (raw rows below)
+        if (!String((e as Error).message).startsWith('Unsupported JPEG')) throw e;
+      }
+    }
     if (this.o.deviceInflate && decoder.deflated) { ({ data, header } = await decoder.deflated()); filtered = 2; }
     else if (decoder.inflated) { ({ data, header } = await decoder.inflated()); filtered = 1; }
     else {
