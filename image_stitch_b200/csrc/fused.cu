@@ -471,6 +471,23 @@ __device__ __forceinline__ uint4 unit_compose_row(const FusedParams &p, const Iv
     const int n = min(n_canvas, (int)c.list_off - 4 * (int)lane);   // words that exist in the source row too
     if (n == 4 && (reinterpret_cast<uintptr_t>(src) & 15u) == 0) v = __ldg(reinterpret_cast<const uint4 *>(src));
     else { v.x = n > 0 ? __ldg(src) : 0u; v.y = n > 1 ? __ldg(src + 1) : 0u; v.z = n > 2 ? __ldg(src + 2) : 0u; v.w = n > 3 ? __ldg(src + 3) : 0u; }
+  } else if (c.kind == SK_COMP && (c.flags & 1u)) {
+    // every layer spans the column in the output's format: layer after layer, no per-pixel tests
+    for (uint32_t k = 0; k < c.n_list; k++) {
+      const DevTile *t = p.tiles + __ldg(p.lists + c.list_off + k);
+      const uint32_t *src = reinterpret_cast<const uint32_t *>(t->pix + (size_t)(y - t->y0 + t->sy0) * t->pitch) +
+                            (xw0 / BPW - t->x0 + t->sx0) * BPW + 4 * (int)lane;
+      uint4 s;
+      if (n_canvas < 4) {   // the canvas (and possibly the tile's row) ends inside this quad: no loads past it
+        s.x = __ldg(src); s.y = n_canvas > 1 ? __ldg(src + 1) : 0u; s.z = n_canvas > 2 ? __ldg(src + 2) : 0u; s.w = 0u;
+      } else if ((reinterpret_cast<uintptr_t>(src) & 15u) == 0) {
+        s = __ldg(reinterpret_cast<const uint4 *>(src));
+      } else {
+        s.x = __ldg(src); s.y = __ldg(src + 1); s.z = __ldg(src + 2); s.w = __ldg(src + 3);
+      }
+      if (p.alpha_blend == 0u || t->opaque) v = s;
+      else v = layer_blend<BPW>(v, s, 15u);
+    }
   } else if (c.kind == SK_COMP && (c.flags & 2u)) {
     // every layer is in the output's format: word loads under a per-lane coverage mask
     const int x = qw / BPW;
