@@ -159,3 +159,16 @@ def test_decoder_plugin_contract():
     assert b"".join(rows) == orc.jpeg_decode(data).tobytes()
     g = JpegBufferDecoder(_file("g_q90"))
     assert g.get_header().channels == 1 and len(next(iter(g.scanlines()))) == 40
+
+
+import jpeg_variants as JV
+
+
+@pytest.mark.parametrize("name", sorted(JV.variants()))
+def test_marker_segment_variants(ctx, name, decoded):
+    data, same_as, err = JV.variants()[name]
+    if err:
+        with pytest.raises(_native.StitchError, match=err.replace("(", r"\(").replace(")", r"\)")):
+            ctx.decode_jpeg(data)
+    else:
+        assert np.array_equal(ctx.decode_jpeg(data)[..., :3], decoded[same_as])

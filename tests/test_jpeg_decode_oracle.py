@@ -60,3 +60,17 @@ def test_truncated_and_corrupt_streams():
     rst[k + 1] = 0xD5
     with pytest.raises(orc.JpegDecodeError, match="restart marker"):
         orc.jpeg_decode(bytes(rst))
+
+
+import jpeg_variants as JV
+
+
+@pytest.mark.parametrize("name", sorted(JV.variants()))
+def test_marker_segment_variants(name, decoded):
+    """Files that differ from a fixture in their marker segments only: same pixels, or the error that names the reason."""
+    data, same_as, err = JV.variants()[name]
+    if err:
+        with pytest.raises(orc.JpegDecodeError, match=err.replace("(", r"\(").replace(")", r"\)")):
+            orc.jpeg_decode(data)
+    else:
+        assert np.array_equal(orc.jpeg_decode(data)[..., :3], decoded[same_as])
