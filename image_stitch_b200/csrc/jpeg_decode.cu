@@ -189,35 +189,31 @@ __device__ __forceinline__ JdState jd_walk(const JdImage &img, const JdHuff *sh,
       len = e2 >> 8; sym = e2 & 0xffu;
       if (!len) { if (EMIT) err = JD_E_HUFF; s.bp = BAD; return s; }
     }
-    const uint32_t sbits = k ? (sym & 15u) : sym, total = len + sbits;
-    if (sbits > 15u) { if (EMIT) err = JD_E_HUFF; s.bp = BAD; return s; }
+    // One symbol, without branches on its kind (the 32 lanes of a warp sit at different kinds of symbol: with a branch
+    // per kind the warp pays for every kind at every step).
+    const bool isdc = k == 0u;
+    const uint32_t sbits = isdc ? sym : (sym & 15u), run = sym >> 4, total = len + sbits;
+    const uint32_t k_coef = isdc ? 0u : k + run;                       // the coefficient this symbol sets (when sbits != 0)
+    const uint32_t k_next = isdc ? 1u : (sbits ? k_coef + 1u : (run == 15u ? k + 16u : 64u));
+    if (sbits > 15u || (sbits && k_coef > 63u)) { if (EMIT) err = JD_E_HUFF; s.bp = BAD; return s; }
     if (bp + total > end_bit) {   // the interval's padding (all ones: never a whole code), or data that ends early
       if (EMIT) err = JD_E_TRUNCATED;
       break;
     }
-    const uint32_t vbits = sbits ? (w << len) >> (32u - sbits) : 0u;
+    if (EMIT) {
+      const uint32_t vbits = sbits ? (w << len) >> (32u - sbits) : 0u;
+      int v = sbits ? jd_extend(vbits, sbits) : 0;
+      if (DC_ABS && isdc) { pred[comp] += v; v = pred[comp]; }
+      if (isdc || sbits) blk[c_natural[k_coef]] = (int16_t)v;
+    }
     bp += total; buf <<= total; have -= total;
-    if (k == 0u) {
-      if (EMIT) {
-        int v = sbits ? jd_extend(vbits, sbits) : 0;
-        if (DC_ABS) { pred[comp] += v; v = pred[comp]; }
-        blk[0] = (int16_t)v;
-      }
-      k = 1u;
-    } else if (sbits) {
-      k += sym >> 4;
-      if (k > 63u) { if (EMIT) err = JD_E_HUFF; s.bp = BAD; return s; }
-      if (EMIT) blk[c_natural[k]] = (int16_t)jd_extend(vbits, sbits);
-      k++;
-    } else {
-      k = (sym >> 4) == 15u ? k + 16u : 64u;
-    }
-    if (k >= 64u) {
-      k = 0u; nblk++; g++;
-      if (++bim == bpm) bim = 0u;
-      comp = (comp_map >> (2u * bim)) & 3u;
-      if (EMIT && g < g_end) blk = jd_block(img, g, bim);
-    }
+    const bool done = k_next >= 64u;
+    k = done ? 0u : k_next;
+    nblk += done ? 1u : 0u;
+    g += done ? 1u : 0u;
+    bim = done ? (bim + 1u == bpm ? 0u : bim + 1u) : bim;
+    comp = (comp_map >> (2u * bim)) & 3u;
+    if (EMIT && done && g < g_end) blk = jd_block(img, g, bim);
   }
   s.bp = bp; s.pos = (bim << 8) | k;
   return s;
