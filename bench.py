@@ -53,7 +53,7 @@ WORKLOAD_CONFIG = {
 def profiled_traffic_bytes(*summaries, scale: float = 1.0):
     """dram__bytes_read.sum + dram__bytes_write.sum of the profiled kernel(s) from committed `ncu --set full`
     captures of this same workload (one launch each), times `scale`.  None when a summary is missing."""
-    summaries = summaries or ("profiles/r2c_prof_fused_c2.summary.csv",)
+    summaries = summaries or ("profiles/r2e_prof_fused_c2.summary.csv",)
     unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
     total = 0.0
     for summary in summaries:
@@ -706,7 +706,7 @@ def run_ours(args, rank: int, world: int, local_rank: int):
         "gpu_launches": value_launches,
         "roofline": {"bound": "hbm", "kernel": "composite+filter-select (kernels b+c), C2", "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": achieved / peak, "traffic": profiled_traffic_bytes(), "peak_source": peak_src,
-                     "traffic_source": "profiles/r2c_prof_fused_c2.summary.csv (ncu --set full of this kernel on this workload, one launch, bytes)",
+                     "traffic_source": "profiles/r2e_prof_fused_c2.summary.csv (ncu --set full of this kernel on this workload, one launch, bytes)",
                      "algorithmic_bytes_per_launch": alg_bytes, "avg_ms": cmp_avg,
                      "frac_of_8TBps": achieved / 8000.0},
         "roofline_c3": {"bound": "hbm", "kernel": "composite + filter-select on C3; with blending: composite to a canvas in HBM, then the unit kernel "
@@ -715,13 +715,13 @@ def run_ours(args, rank: int, world: int, local_rank: int):
                                     "masks), zIndex alpha blending, 32768x32768 canvas, background #FFFFFF80; every tile has its own buffer",
                         "avg_ms": c3_blend_ms, "achieved": c3_alg / (c3_blend_ms / 1e3) / 1e9, "peak": peak, "unit": "GB/s",
                         "frac": c3_alg / (c3_blend_ms / 1e3) / 1e9 / peak, "value_MPix_s": c3_px / 1e6 / (c3_blend_ms / 1e3),
-                        "algorithmic_bytes_per_launch": c3_alg, "traffic": profiled_traffic_bytes("profiles/r2c_prof_c3_blend.summary.csv", scale=8.0),
-                        "traffic_source": "8 x (compose_plan_kernel + fused_kernel of one 4096-row band), profiles/r2c_prof_c3_blend.summary.csv",
+                        "algorithmic_bytes_per_launch": c3_alg, "traffic": profiled_traffic_bytes("profiles/r2e_prof_c3_blend.summary.csv", scale=8.0),
+                        "traffic_source": "8 x (compose_plan_kernel + fused_kernel of one 4096-row band), profiles/r2e_prof_c3_blend.summary.csv",
                         "blending_off": {"avg_ms": c3_noblend_ms, "frac": c3_alg / (c3_noblend_ms / 1e3) / 1e9 / peak,
                                          "value_MPix_s": c3_px / 1e6 / (c3_noblend_ms / 1e3),
-                                         "traffic": profiled_traffic_bytes("profiles/r2c_prof_c3_noblend.summary.csv", scale=8.0),
+                                         "traffic": profiled_traffic_bytes("profiles/r2e_prof_c3_noblend.summary.csv", scale=8.0),
                                          "traffic_source": "8 x (fused_plan_iv + fused_prep + fused_kernel of one 4096-row band), "
-                                                           "profiles/r2c_prof_c3_noblend.summary.csv"},
+                                                           "profiles/r2e_prof_c3_noblend.summary.csv"},
                         "scaling": "strong: the one canvas is cut into n_gpus row bands, max over ranks", "rows_per_gpu": C3_CANVAS // world},
         "kernels": {"unfilter": {"avg_ms": dec_avg, "achieved_GBps": unf_achieved, "frac": unf_achieved / peak, "tiles": n_tiles,
                                  "filter_types": "random per row"},

@@ -38,7 +38,7 @@ static constexpr int FB_SWW = 512;  // bin width in 32-bit words
 
 static constexpr int FU_R = 8;                       // rows per unit
 static constexpr int FU_SW = 128;                    // words per unit row
-static constexpr int FU_WARPS = 20;                  // workers per CTA (one CTA per SM)
+static constexpr int FU_WARPS = 24;                  // workers per CTA (one CTA per SM): what 227 KB of shared memory hold; 80 registers each
 static constexpr int FU_RAW_WORDS = (FU_R + 1) * FU_SW;  // row 0 = predictor row above the unit
 static constexpr int FU_LC_WORDS = ((FU_R + 1) * 2 + 3) / 4 * 4;  // two words left of every row
 static constexpr int FU_WARP_WORDS = (FU_RAW_WORDS + FU_LC_WORDS + 31) / 32 * 32;  // stashes start on 128-byte boundaries (TMA destinations)
