@@ -7,6 +7,7 @@ visible, every entry point raises.
 from __future__ import annotations
 
 import ctypes as C
+import weakref
 import os
 from typing import Optional
 
@@ -159,9 +160,12 @@ class Context:
         if rc != STITCH_OK:
             raise StitchError(rc, f"stitch_ctx_create failed ({rc})")
         self.device = device
+        self._jobs = weakref.WeakSet()   # jobs still open: they hold device memory of this context
 
     def close(self) -> None:
         if self.handle:
+            for job in list(self._jobs):   # a job left open (an exception mid-band) must not outlive its context
+                job.close()
             self.lib.stitch_ctx_destroy(self.handle)
             self.handle = C.c_void_p()
 
@@ -284,12 +288,15 @@ class Job:
         self.canvas_w, self.canvas_h = canvas_w, canvas_h
         self._keep = []
         self.last_rows = 0
+        ctx._jobs.add(self)
 
     def close(self) -> None:
         if self.handle:
-            self.lib.stitch_job_destroy(self.handle)
+            if self.ctx.handle:
+                self.lib.stitch_job_destroy(self.handle)
             self.handle = C.c_void_p()
             self._keep.clear()
+            self.ctx._jobs.discard(self)
 
     def __enter__(self):
         return self

@@ -484,6 +484,342 @@ __global__ void __launch_bounds__(256) jpeg_stuff_kernel(const uint8_t *ubuf, co
   }
 }
 
+// =========================================================================================================
+// The one-pass route: colour, FDCT, quantisation AND Huffman coding in one kernel, with no coefficients in HBM.
+//
+//   M1 mcu      CTA = 128 MCUs of one MCU row ("chunk"), thread = one MCU.  The quantised coefficients never
+//               leave the registers: the unrolled zig-zag loop codes every non-zero one on the spot into the
+//               thread's bit accumulator, whose full words go to a private column of shared memory.  The MCU
+//               lengths are scanned across the CTA, the private words are shifted into place in a chunk buffer
+//               (the pixel staging area, dead by then) and the chunk goes to its fixed slot in HBM.
+//   M2 rowinfo  CTA = one MCU row: bit offsets of its chunks, size of the row segment, its 0xFF bytes
+//   J6 rowscan  final offsets (stuffing + RSTm), as on the other route
+//   M3 stuff    CTA = one MCU row: chunks funnelled together 32 bits at a time, stuffed, RSTm
+//
+// A thread holds JM_WORDS words of code for its MCU and a chunk JM_CHUNK_BYTES; content that needs more (noise
+// at quality 100) raises a flag and the band is done again by the J1..J7 route above.
+static constexpr int JM_MCUS = 128;
+static constexpr int JM_WORDS = 36;                       // 1152 bits per MCU: 6 bits per pixel
+static constexpr int JM_PX = JM_MCUS * 8 + 8;             // staged pixels per row: the MCU on the left, then the chunk's
+static constexpr uint32_t JM_CHUNK_BYTES = 8192;          // 4 bits per pixel on average over a chunk
+static constexpr uint32_t JM_CHUNK_WORDS = JM_CHUNK_BYTES / 4;
+
+struct JpegQuant {   // zig-zag order; [0] luminance, [1] chrominance; divisor = quantval << 3 as in c_q8
+  uint32_t half[2][64];    // divisor / 2
+  uint32_t recip[2][64];   // ceil(2^32 / divisor)
+};
+
+struct JmSmem {
+  uint8_t px[8][JM_PX * 4];              // RGBA rows; reused as the chunk buffer (words) once the pixels are consumed
+  uint32_t stage[JM_WORDS][JM_MCUS];     // word j of thread t's code at [j][t]
+  HuffSmem hs;
+  uint32_t warp_tot[JM_MCUS / 32];
+};
+
+// v - 128 for one pixel word (R | G << 8 | B << 16 | A << 24); the level shift rides in the rounding constant
+__device__ __forceinline__ int jm_y(uint32_t px) {
+  uint32_t v;
+  asm("dp2a.lo.u32.u32 %0, %1, %2, %3;" : "=r"(v) : "r"(19595u | (38470u << 16)), "r"(px), "r"(32768u - (128u << 16)));
+  asm("dp2a.hi.u32.u32 %0, %1, %2, %3;" : "=r"(v) : "r"(7471u), "r"(px), "r"(v));
+  return (int)v >> 16;
+}
+// chroma: (32767 - N) >> 16 with N = a1.lo R + a1.hi G + a2.lo B  (signed 16-bit weights: the + 32768 of the JFIF
+// formulas does not fit, its negative does, so the weights are the negated ones)
+__device__ __forceinline__ int jm_c(uint32_t px, uint32_t a1, uint32_t a2) {
+  int n;
+  asm("dp2a.lo.s32.u32 %0, %1, %2, %3;" : "=r"(n) : "r"(a1), "r"(px), "r"(0));
+  asm("dp2a.hi.s32.u32 %0, %1, %2, %3;" : "=r"(n) : "r"(a2), "r"(px), "r"(n));
+  return (32767 - n) >> 16;
+}
+static constexpr uint32_t JM_CB1 = 11059u | (21709u << 16), JM_CB2 = 0x8000u;    // N = 11059 R + 21709 G - 32768 B
+static constexpr uint32_t JM_CR1 = 0x8000u | (27439u << 16), JM_CR2 = 5329u;     // N = -32768 R + 27439 G + 5329 B
+
+struct JmBits {
+  unsigned long long acc;   // pending bits in the low nacc bits (above them: bits already stored)
+  uint32_t nacc, wr;        // wr: words produced so far
+  uint32_t ovf;             // a word had no room: the MCU goes to the other route
+  uint32_t *col;            // &stage[0][t]
+  // size <= 32; lim: first word of the column that is not free (JM_WORDS, or where the block's unread coefficients start)
+  __device__ __forceinline__ void put(uint32_t code, uint32_t size, uint32_t lim) {
+    acc = (acc << size) | code;
+    nacc += size;
+    if (nacc >= 32u) {
+      nacc -= 32u;
+      if (wr < lim) col[wr * JM_MCUS] = (uint32_t)(acc >> nacc); else ovf = 1u;
+      wr++;
+    }
+  }
+};
+
+__global__ void __launch_bounds__(JM_MCUS, 4) jpeg_mcu_kernel(const uint8_t *canvas, size_t pitch, JpegGeom g,
+                                                              const __grid_constant__ JpegQuant q, uint32_t *chunk_words,
+                                                              uint32_t *chunk_bits, unsigned long long *overflow) {
+  extern __shared__ __align__(16) uint8_t jm_raw[];
+  JmSmem &sm = *reinterpret_cast<JmSmem *>(jm_raw);
+  load_huff(sm.hs);
+  const uint32_t t = threadIdx.x, lane = t & 31u, warp = t >> 5;
+  const uint32_t m = blockIdx.x * JM_MCUS + t;          // MCU in the row
+  const uint32_t x0 = blockIdx.x * JM_MCUS * 8u;        // first pixel column of the chunk
+  const uint32_t px_here = min(g.width - x0, (uint32_t)JM_MCUS * 8u) + 8u;   // staged pixels that exist (with the 8 on the left)
+  const bool active = m < g.mcus;
+  const bool warp_active = blockIdx.x * JM_MCUS + warp * 32u < g.mcus;
+  uint32_t *cw = reinterpret_cast<uint32_t *>(&sm.px[0][0]);
+  for (uint32_t mr = blockIdx.y; mr < g.mrows; mr += gridDim.y) {
+    __syncthreads();   // the previous chunk has left the buffer (and the tables are loaded)
+    for (uint32_t c = t; c < 8u * (JM_PX / 4u); c += JM_MCUS) {
+      const uint32_t yy = c / (JM_PX / 4u), p4 = c % (JM_PX / 4u);   // row, 16-byte piece (4 pixels) in the row
+      if (p4 * 4u >= px_here || (x0 == 0u && p4 < 2u)) continue;
+      uint32_t y = g.y0 + mr * 8u + yy;
+      y = min(y, g.height - 1u) - g.y0;  // replicate the last image row below the bottom edge
+      const uint32_t sa = (uint32_t)__cvta_generic_to_shared(&sm.px[yy][p4 * 16u]);
+      const uint8_t *src = canvas + (size_t)y * pitch + ((size_t)x0 + p4 * 4u - 8u) * 4u;
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(src) : "memory");
+    }
+    asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+    if ((g.width & 7u) && x0 + (uint32_t)JM_MCUS * 8u >= g.width) {   // the chunk holds the image's partial MCU: replicate the last column
+      if (t < 56u) {
+        const uint32_t yy = t / 7u, p = g.width - x0 + 8u + t % 7u;   // staged pixel index of a column past the edge
+        if (p < ((g.width + 7u) & ~7u) - x0 + 8u)
+          *reinterpret_cast<uint32_t *>(&sm.px[yy][p * 4u]) = *reinterpret_cast<const uint32_t *>(&sm.px[yy][(g.width - 1u - x0 + 8u) * 4u]);
+      }
+      __syncthreads();
+    }
+    JmBits b;
+    b.acc = 0; b.nacc = 0; b.wr = 0; b.ovf = 0; b.col = &sm.stage[0][t];
+    if (warp_active) {
+      uint8_t *colb = reinterpret_cast<uint8_t *>(b.col);
+      for (uint32_t comp = 0; comp < 3u; comp++) {  // 0 Y, 1 Cb, 2 Cr
+        const uint32_t cls = comp ? 1u : 0u;
+        const uint32_t a1 = comp == 1u ? JM_CB1 : JM_CR1, a2 = comp == 1u ? JM_CB2 : JM_CR2;
+        // DC of the MCU on the warp's left (lane 0's predictor): the DC term of the islow FDCT is exactly the
+        // sum of the 64 level-shifted samples, so the warp adds them up, two pixels a lane
+        int left_dc = 0;
+        if (blockIdx.x != 0u || warp != 0u) {
+          const uint2 two = *reinterpret_cast<const uint2 *>(&sm.px[lane >> 2][(warp * 256u + (lane & 3u) * 2u) * 4u]);
+          int s2 = comp == 0u ? jm_y(two.x) + jm_y(two.y) : jm_c(two.x, a1, a2) + jm_c(two.y, a1, a2);
+          s2 = __reduce_add_sync(0xffffffffu, s2);
+          const int qa = (int)__umulhi((uint32_t)abs(s2) + q.half[cls][0], q.recip[cls][0]);
+          left_dc = s2 < 0 ? -qa : qa;
+        }
+        int d[64];
+#pragma unroll
+        for (int yy = 0; yy < 8; yy++) {
+          const uint4 a = *reinterpret_cast<const uint4 *>(&sm.px[yy][32u + t * 32u]), c4 = *reinterpret_cast<const uint4 *>(&sm.px[yy][48u + t * 32u]);
+          const uint32_t px[8] = {a.x, a.y, a.z, a.w, c4.x, c4.y, c4.z, c4.w};
+          if (comp == 0u) {
+#pragma unroll
+            for (int xx = 0; xx < 8; xx++) d[yy * 8 + xx] = jm_y(px[xx]);
+          } else {
+#pragma unroll
+            for (int xx = 0; xx < 8; xx++) d[yy * 8 + xx] = jm_c(px[xx], a1, a2);
+          }
+        }
+#pragma unroll
+        for (int i = 0; i < 8; i++)
+          fdct_1d(d[8 * i], d[8 * i + 1], d[8 * i + 2], d[8 * i + 3], d[8 * i + 4], d[8 * i + 5], d[8 * i + 6], d[8 * i + 7], true);
+#pragma unroll
+        for (int i = 0; i < 8; i++)
+          fdct_1d(d[i], d[8 + i], d[16 + i], d[24 + i], d[32 + i], d[40 + i], d[48 + i], d[56 + i], false);
+        const uint32_t *dct = sm.hs.dc[cls], *act = sm.hs.ac[cls];
+        const int qa0 = (int)__umulhi((uint32_t)abs(d[0]) + q.half[cls][0], q.recip[cls][0]);
+        const int dcq = d[0] < 0 ? -qa0 : qa0;
+        // Quantise the 63 AC terms in straight-line code; the non-zero ones go, 16 bits each (magnitude, sign in
+        // bit 15), to the far end of the thread's column of code words, growing towards the code: entry e at word
+        // JM_WORDS - 1 - e / 2, half e & 1.  Their zig-zag positions stay in a 64-bit mask.
+        unsigned long long nz = 0;
+        int woff = (JM_WORDS - 1) * JM_MCUS * 4, wstep = 2;
+#pragma unroll
+        for (int k = 1; k < 64; k++) {
+          const int c = d[zz_nat(k)];
+          const uint32_t a = __umulhi((uint32_t)abs(c) + q.half[cls][k], q.recip[cls][k]);
+          if (a != 0u) {
+            *reinterpret_cast<uint16_t *>(colb + woff) = (uint16_t)(a | (((uint32_t)c >> 16) & 0x8000u));
+            woff += wstep;
+            wstep = -JM_MCUS * 4 - wstep;   // 2, -514, 2, ...
+            nz |= 1ull << k;
+          }
+        }
+        // the entries must not have reached the code words written so far
+        const uint32_t n_ent = (uint32_t)__popcll(nz);
+        if ((uint32_t)JM_WORDS - ((n_ent + 1u) >> 1) < b.wr) b.ovf = 1u;
+        int roff = (JM_WORDS - 1) * JM_MCUS * 4, rstep = 2;
+        {  // DC difference against the MCU on the left (0 at the start of the row: a restart interval)
+          int pred = __shfl_up_sync(0xffffffffu, dcq, 1);
+          if (lane == 0u) pred = left_dc;
+          const int diff = dcq - pred;
+          const uint32_t a = (uint32_t)abs(diff), s = 32u - (uint32_t)__clz((int)a), e = dct[s];
+          b.put(((e >> 8) << s) | ((a ^ (uint32_t)(diff >> 31)) & ((1u << s) - 1u)), (e & 0xffu) + s, (uint32_t)JM_WORDS - ((n_ent + 1u) >> 1));
+        }
+        int prev = 0;
+        while (nz) {   // each lane walks ITS non-zero terms
+          const int k = __ffsll((long long)nz) - 1;
+          nz &= nz - 1ull;
+          const uint32_t x = *reinterpret_cast<const uint16_t *>(colb + roff);
+          roff += rstep;
+          rstep = -JM_MCUS * 4 - rstep;
+          const uint32_t lim = nz ? (uint32_t)roff / (JM_MCUS * 4u) : (uint32_t)JM_WORDS;   // the word of the next unread entry
+          uint32_t run = (uint32_t)(k - 1 - prev);
+          prev = k;
+          if (run > 15u) {
+            const uint32_t z = act[0xF0];
+            do { b.put(z >> 8, z & 0xffu, lim); run -= 16u; } while (run > 15u);
+          }
+          const uint32_t a = x & 0x7fffu, sg = 0u - (x >> 15);
+          const uint32_t s = 32u - (uint32_t)__clz((int)a), e = act[(run << 4) | s];
+          b.put(((e >> 8) << s) | ((a ^ sg) & ((1u << s) - 1u)), (e & 0xffu) + s, lim);
+        }
+        if (prev != 63) { const uint32_t e = act[0]; b.put(e >> 8, e & 0xffu, (uint32_t)JM_WORDS); }
+      }
+      if (b.nacc) {   // left-aligned tail, zeros below
+        if (b.wr < (uint32_t)JM_WORDS) b.col[b.wr * JM_MCUS] = (uint32_t)b.acc << (32u - b.nacc); else b.ovf = 1u;
+      }
+    }
+    // lengths -> bit offsets inside the chunk
+    const uint32_t len = active ? b.wr * 32u + b.nacc : 0u;
+    const int too_long = __syncthreads_or(active && (b.ovf || len > (uint32_t)JM_WORDS * 32u));   // also: every thread is done with the pixels
+    uint32_t incl = len;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= (uint32_t)o) incl += v; }
+    if (lane == 31u) sm.warp_tot[warp] = incl;
+    __syncthreads();
+    uint32_t off = incl - len, total = 0;
+#pragma unroll
+    for (uint32_t k = 0; k < (uint32_t)JM_MCUS / 32u; k++) { const uint32_t w = sm.warp_tot[k]; if (k < warp) off += w; total += w; }
+    const size_t ci = (size_t)mr * gridDim.x + blockIdx.x;
+    if (too_long || total > JM_CHUNK_BYTES * 8u) {   // uniform over the CTA
+      if (t == 0u) { atomicOr(overflow, 1ull); chunk_bits[ci] = 0u; }
+      continue;
+    }
+    const uint32_t nw = (total + 31u) >> 5;
+    for (uint32_t i = t; i <= nw; i += JM_MCUS) cw[i] = 0u;
+    __syncthreads();
+    for (uint32_t j = 0; j * 32u < len; j++) {
+      const uint32_t w = sm.stage[j][t], p = off + j * 32u, sh = p & 31u;
+      atomicOr(&cw[p >> 5], w >> sh);
+      if (sh) atomicOr(&cw[(p >> 5) + 1u], w << (32u - sh));
+    }
+    __syncthreads();
+    uint32_t *dst = chunk_words + ci * JM_CHUNK_WORDS;
+    for (uint32_t i = t; i < nw; i += JM_MCUS) dst[i] = __byte_perm(cw[i], 0, 0x0123);   // stream byte j = byte j of memory
+    if (t == 0u) chunk_bits[ci] = total;
+  }
+}
+
+// ---- M2 / M3: the chunks of an MCU row, read as one bit stream -------------------------------------------
+static constexpr uint32_t JM_MAX_CHUNKS = 64;   // 8191 MCUs at most (16-bit SOF0 width)
+
+// Bit offsets of the row's chunks (exclusive scan of their lengths) into off[0 .. n]; warp 0 does it.
+__device__ __forceinline__ void jm_row_offsets(const uint32_t *bits, uint32_t n, uint32_t *off) {
+  if (threadIdx.x < 32u) {
+    const uint32_t lane = threadIdx.x;
+    const uint32_t a = lane < n ? bits[lane] : 0u, c = lane + 32u < n ? bits[lane + 32u] : 0u;
+    uint32_t ia = a, ic = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t va = __shfl_up_sync(0xffffffffu, ia, o), vc = __shfl_up_sync(0xffffffffu, ic, o);
+      if (lane >= (uint32_t)o) { ia += va; ic += vc; }
+    }
+    const uint32_t first = __shfl_sync(0xffffffffu, ia, 31);
+    off[lane] = ia - a;
+    off[lane + 32u] = first + ic - c;
+    if (lane == 31u) off[64] = first + ic;
+  }
+}
+
+// 32 bits of the row's stream from bit position b (a multiple of 32), MSB first; zero past `total`, then the
+// 1-bits that pad the segment to a byte boundary.
+__device__ __forceinline__ uint32_t jm_row_word(const uint32_t *row_words, const uint32_t *off, uint32_t n, uint32_t total, uint32_t b) {
+  uint32_t lo = 0, hi = n;   // largest c with off[c] <= b
+  while (hi - lo > 1u) { const uint32_t mid = (lo + hi) >> 1; if (off[mid] <= b) lo = mid; else hi = mid; }
+  uint32_t c = lo, out = 0, got = 0;
+  while (got < 32u && b + got < total) {
+    const uint32_t lb = b + got - off[c], avail = off[c + 1u] - off[c] - lb;
+    if (avail == 0u) { c++; continue; }
+    const uint32_t take = min(32u - got, avail), sh = lb & 31u;
+    const uint32_t *w = row_words + (size_t)c * JM_CHUNK_WORDS + (lb >> 5);
+    const uint32_t w0 = __byte_perm(__ldg(w), 0, 0x0123), w1 = sh + take > 32u ? __byte_perm(__ldg(w + 1), 0, 0x0123) : 0u;
+    uint32_t v = __funnelshift_l(w1, w0, sh);
+    if (take < 32u) v &= ~(0xffffffffu >> take);
+    out |= v >> got;
+    got += take;
+    if (take == avail) c++;
+  }
+  if (b < total && total - b < 32u && (total & 7u)) {
+    const uint32_t from = total - b, to = ((total + 7u) & ~7u) - b;   // 1 <= to <= 32
+    out |= (0xffffffffu >> from) & (to == 32u ? 0xffffffffu : ~(0xffffffffu >> to));
+  }
+  return out;
+}
+
+__global__ void __launch_bounds__(256) jpeg_rowinfo_kernel(const uint32_t *chunk_words, const uint32_t *chunk_bits, uint32_t n_chunks,
+                                                           uint32_t n_rows, uint32_t *row_bits, uint32_t *row_ff) {
+  __shared__ uint32_t off[JM_MAX_CHUNKS + 1];
+  __shared__ uint32_t s_cnt;
+  for (uint32_t r = blockIdx.x; r < n_rows; r += gridDim.x) {
+    __syncthreads();
+    if (threadIdx.x == 0) s_cnt = 0;
+    jm_row_offsets(chunk_bits + (size_t)r * n_chunks, n_chunks, off);
+    __syncthreads();
+    const uint32_t total = off[n_chunks];
+    const uint32_t *rw = chunk_words + (size_t)r * n_chunks * JM_CHUNK_WORDS;
+    uint32_t c = 0;
+    for (uint32_t i = threadIdx.x; i * 32u < total; i += blockDim.x)
+      c += (uint32_t)__popc(__vcmpeq4(jm_row_word(rw, off, n_chunks, total, i * 32u), 0xffffffffu)) >> 3;
+    c = __reduce_add_sync(0xffffffffu, c);
+    if ((threadIdx.x & 31u) == 0 && c) atomicAdd(&s_cnt, c);
+    __syncthreads();
+    if (threadIdx.x == 0) { row_bits[r] = total; row_ff[r] = s_cnt; }
+  }
+}
+
+__global__ void __launch_bounds__(256) jpeg_stuff_chunks_kernel(const uint32_t *chunk_words, const uint32_t *chunk_bits, uint32_t n_chunks,
+                                                                const unsigned long long *out_base, uint32_t n_rows,
+                                                                uint32_t first_mrow, uint32_t total_mrows, uint8_t *out) {
+  __shared__ uint32_t off[JM_MAX_CHUNKS + 1];
+  __shared__ uint32_t warp_tot[8];
+  __shared__ uint32_t s_ff;
+  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  for (uint32_t r = blockIdx.x; r < n_rows; r += gridDim.x) {
+    __syncthreads();
+    if (threadIdx.x == 0) s_ff = 0;
+    jm_row_offsets(chunk_bits + (size_t)r * n_chunks, n_chunks, off);
+    __syncthreads();
+    const uint32_t total = off[n_chunks], n = (total + 7u) >> 3;
+    const uint32_t *rw = chunk_words + (size_t)r * n_chunks * JM_CHUNK_WORDS;
+    uint8_t *o = out + out_base[r];
+    for (uint32_t i0 = 0; i0 * 32u < total; i0 += 256u) {
+      const uint32_t i = i0 + threadIdx.x;
+      const uint32_t w = i * 32u < total ? jm_row_word(rw, off, n_chunks, total, i * 32u) : 0u;
+      const uint32_t ffm = __vcmpeq4(w, 0xffffffffu), cnt = (uint32_t)__popc(ffm) >> 3;   // bytes past the end are 0
+      uint32_t incl = cnt;
+#pragma unroll
+      for (int k = 1; k < 32; k <<= 1) { const uint32_t v = __shfl_up_sync(0xffffffffu, incl, k); if (lane >= (uint32_t)k) incl += v; }
+      if (lane == 31u) warp_tot[warp] = incl;
+      __syncthreads();
+      uint32_t wbase = 0;
+#pragma unroll
+      for (int k = 0; k < 8; k++) if ((uint32_t)k < warp) wbase += warp_tot[k];
+      uint32_t pos = i * 4u + s_ff + wbase + incl - cnt;
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        if (i * 4u + j < n) {
+          const uint32_t byte = (w >> (24 - 8 * j)) & 0xffu;
+          o[pos++] = (uint8_t)byte;
+          if (byte == 0xffu) o[pos++] = 0;
+        }
+      }
+      __syncthreads();
+      if (threadIdx.x == 255u) s_ff += wbase + incl;
+      __syncthreads();
+    }
+    if (threadIdx.x == 0 && first_mrow + r + 1u < total_mrows) {
+      o[n + s_ff] = 0xFF;
+      o[n + s_ff + 1] = (uint8_t)(0xD0u + ((first_mrow + r) & 7u));
+    }
+  }
+}
+
 int upload_tables(stitch_job *job) {
   stitch_ctx *ctx = job->ctx;
   const int quality = (int)job->desc.jpeg_quality;
@@ -509,24 +845,101 @@ int upload_tables(stitch_job *job) {
 
 }  // namespace
 
+// The one-pass route over a band.  Scratch: [0] chunk slots, [1] bits per chunk, [2] per-row sizes and totals.
+static int encode_band_one_pass(stitch_job *job, const JpegGeom &g, uint32_t first_mrow, uint32_t total_mrows, const uint8_t *canvas,
+                                size_t canvas_pitch, size_t *out_bytes, uint32_t *launches, bool *overflow) {
+  stitch_ctx *ctx = job->ctx;
+  int rc;
+  static_assert(sizeof(JmSmem) <= 56 * 1024, "four CTAs of the MCU kernel per SM");
+  const uint32_t n_chunks = (g.mcus + JM_MCUS - 1) / JM_MCUS;
+  if (n_chunks > JM_MAX_CHUNKS) { *overflow = true; return STITCH_OK; }
+  if (!job->jpeg_huff_ready) {  // Annex K tables: the same for every job and quality, so no job can disturb another's
+    uint32_t dc[2][16], ac[2][256];
+    build_huff(k_dc_lum_bits, k_dc_vals, dc[0], 16); build_huff(k_dc_chr_bits, k_dc_vals, dc[1], 16);
+    build_huff(k_ac_lum_bits, k_ac_lum_vals, ac[0], 256); build_huff(k_ac_chr_bits, k_ac_chr_vals, ac[1], 256);
+    STITCH_CK(cudaMemcpyToSymbolAsync(c_dc_tab, dc, sizeof dc, 0, cudaMemcpyHostToDevice, ctx->stream));   // pageable source: staged before the call returns
+    STITCH_CK(cudaMemcpyToSymbolAsync(c_ac_tab, ac, sizeof ac, 0, cudaMemcpyHostToDevice, ctx->stream));
+    STITCH_CK(cudaFuncSetAttribute(jpeg_mcu_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(JmSmem)));
+    job->jpeg_huff_ready = true;
+  }
+  JpegQuant q;
+  {
+    uint16_t ql[64], qc[64];
+    quant_tables((int)job->desc.jpeg_quality, ql, qc);
+    for (int k = 0; k < 64; k++) {
+      const uint32_t d0 = (uint32_t)ql[k_zigzag[k]] << 3, d1 = (uint32_t)qc[k_zigzag[k]] << 3;
+      q.half[0][k] = d0 >> 1; q.half[1][k] = d1 >> 1;
+      q.recip[0][k] = (uint32_t)(((1ull << 32) + d0 - 1) / d0); q.recip[1][k] = (uint32_t)(((1ull << 32) + d1 - 1) / d1);
+    }
+  }
+  const size_t n_slots = (size_t)g.mrows * n_chunks;
+  if ((rc = stitch_ensure_buffer(ctx, &job->d_jpeg[0], &job->jpeg_cap[0], n_slots * JM_CHUNK_BYTES + 16))) return rc;
+  if ((rc = stitch_ensure_buffer(ctx, &job->d_jpeg[1], &job->jpeg_cap[1], n_slots * 4))) return rc;
+  const size_t rows_pad = ((size_t)g.mrows + 3) / 4 * 4;
+  if ((rc = stitch_ensure_buffer(ctx, &job->d_jpeg[2], &job->jpeg_cap[2], rows_pad * 24 + 64))) return rc;
+  if (!job->h_jpeg_totals) STITCH_CK(cudaHostAlloc((void **)&job->h_jpeg_totals, 32, cudaHostAllocDefault));
+  uint32_t *chunk_words = reinterpret_cast<uint32_t *>(job->d_jpeg[0]);
+  uint32_t *chunk_bits = reinterpret_cast<uint32_t *>(job->d_jpeg[1]);
+  uint32_t *row_bits = reinterpret_cast<uint32_t *>(job->d_jpeg[2]);
+  uint32_t *row_ff = row_bits + rows_pad;
+  unsigned long long *row_base = reinterpret_cast<unsigned long long *>(row_ff + rows_pad);
+  unsigned long long *out_base = row_base + rows_pad;
+  unsigned long long *totals = out_base + rows_pad;   // [1] output bytes, [2] overflow flag
+  STITCH_CK(cudaMemsetAsync(totals, 0, 32, ctx->stream));
+  {
+    dim3 grid(n_chunks, g.mrows < 16384u ? g.mrows : 16384u);
+    jpeg_mcu_kernel<<<grid, JM_MCUS, sizeof(JmSmem), ctx->stream>>>(canvas, canvas_pitch, g, q, chunk_words, chunk_bits, totals + 2);
+    STITCH_CK(cudaGetLastError());
+  }
+  const uint32_t row_grid = g.mrows < 148u * 8u ? g.mrows : 148u * 8u;
+  jpeg_rowinfo_kernel<<<row_grid, 256, 0, ctx->stream>>>(chunk_words, chunk_bits, n_chunks, g.mrows, row_bits, row_ff);
+  STITCH_CK(cudaGetLastError());
+  jpeg_rowscan_kernel<<<1, 1024, 0, ctx->stream>>>(row_bits, row_ff, g.mrows, first_mrow, total_mrows, 1, out_base, totals);
+  STITCH_CK(cudaGetLastError());
+  STITCH_CK(cudaMemcpyAsync(job->h_jpeg_totals, totals, 24, cudaMemcpyDeviceToHost, ctx->stream));
+  STITCH_CK(cudaStreamSynchronize(ctx->stream));  // the size of the band's bytes decides the size of the output buffer
+  if (launches) *launches += 3;
+  if (job->h_jpeg_totals[2]) { *overflow = true; return STITCH_OK; }
+  const size_t n_out = (size_t)job->h_jpeg_totals[1];
+  if ((rc = stitch_ensure_buffer(ctx, &job->d_out, &job->out_bytes, n_out + 64))) return rc;
+  jpeg_stuff_chunks_kernel<<<row_grid, 256, 0, ctx->stream>>>(chunk_words, chunk_bits, n_chunks, out_base, g.mrows, first_mrow, total_mrows, job->d_out);
+  STITCH_CK(cudaGetLastError());
+  if (launches) *launches += 1;
+  *out_bytes = n_out;
+  return STITCH_OK;
+}
+
 int stitch_jpeg_encode_band(stitch_job *job, uint32_t y0, uint32_t y1, const uint8_t *canvas, size_t canvas_pitch,
                             size_t *out_bytes, uint32_t *launches) {
   stitch_ctx *ctx = job->ctx;
   const stitch_job_desc &jd = job->desc;
   int rc;
-  // tables are re-uploaded per band: another job (another quality) may have run on this device in between
-  if ((rc = upload_tables(job))) return rc;
   JpegGeom g;
   g.width = jd.canvas_w; g.height = jd.canvas_h; g.y0 = y0; g.mcus = (jd.canvas_w + 7) / 8; g.mrows = (y1 - y0 + 7) / 8;
   g.rows_in_band = y1 - y0;
   const uint32_t total_mrows = (jd.canvas_h + 7) / 8, first_mrow = y0 / 8;
+  // STITCH_JPEG_ONE_PASS: 0 = the J1..J7 route only, 2 = the one-pass route only (content it cannot hold is an
+  // error: tests), otherwise one pass first and J1..J7 for a band that overflowed
+  int one_pass = 1;
+  if (const char *e = getenv("STITCH_JPEG_ONE_PASS")) one_pass = atoi(e);
+  if (one_pass) {
+    bool overflow = false;
+    if ((rc = encode_band_one_pass(job, g, first_mrow, total_mrows, canvas, canvas_pitch, out_bytes, launches, &overflow))) return rc;
+    if (!overflow) return STITCH_OK;
+    if (one_pass == 2) {
+      return stitch_fail(ctx, STITCH_E_CAPACITY, "JPEG band [%u,%u): more than %d bits in an MCU or %u bytes in a chunk of %d MCUs (STITCH_JPEG_ONE_PASS=2)",
+                         y0, y1, JM_WORDS * 32, JM_CHUNK_BYTES, JM_MCUS);
+    }
+  }
+  // tables are re-uploaded per band: another job (another quality) may have run on this device in between
+  if ((rc = upload_tables(job))) return rc;
   const size_t n_blk = (size_t)g.mrows * g.mcus * 3;
   // scratch: [0] coefficients, [1] bit offsets, [2] per-row: bits | ff | base(u64) | out_base(u64) | totals(u64 x2), [3] unstuffed
   if ((rc = stitch_ensure_buffer(ctx, &job->d_jpeg[0], &job->jpeg_cap[0], n_blk * 128))) return rc;
   if ((rc = stitch_ensure_buffer(ctx, &job->d_jpeg[1], &job->jpeg_cap[1], n_blk * 4))) return rc;
   const size_t rows_pad = ((size_t)g.mrows + 3) / 4 * 4;
   if ((rc = stitch_ensure_buffer(ctx, &job->d_jpeg[2], &job->jpeg_cap[2], rows_pad * 24 + 64))) return rc;
-  if (!job->h_jpeg_totals) STITCH_CK(cudaHostAlloc((void **)&job->h_jpeg_totals, 16, cudaHostAllocDefault));
+  if (!job->h_jpeg_totals) STITCH_CK(cudaHostAlloc((void **)&job->h_jpeg_totals, 32, cudaHostAllocDefault));
   if ((rc = stitch_ensure_buffer(ctx, &job->d_jpeg[4], &job->jpeg_cap[4], n_blk * 8))) return rc;
   unsigned long long *nzmask = reinterpret_cast<unsigned long long *>(job->d_jpeg[4]);
   int16_t *coefs = reinterpret_cast<int16_t *>(job->d_jpeg[0]);

@@ -25,16 +25,29 @@ def _photo(rng, w, h):
     return np.clip(img, 0, 255).astype(np.uint8)
 
 
+@pytest.fixture(params=["one_pass_first", "j1_to_j7"], autouse=True)
+def jpeg_route(request, monkeypatch):
+    """Every test on both routes of csrc/jpeg.cu: the one-pass MCU kernel (with the J1..J7 kernels behind it for
+    content it cannot hold), and J1..J7 alone."""
+    if request.param == "j1_to_j7":
+        monkeypatch.setenv("STITCH_JPEG_ONE_PASS", "0")
+    else:
+        monkeypatch.delenv("STITCH_JPEG_ONE_PASS", raising=False)
+    return request.param
+
+
 def _gpu_entropy(ctx, rgba, w, h, quality, bands):
     job = _native.Job(ctx, w, h, 8, _native.OUT_JPEG_ENTROPY, False, bytes(4), jpeg_quality=quality)
     job.add_tile(rgba.tobytes(), width=w, height=h, bit_depth=8, color_type=6, interlace=0, filtered=0,
                  dst_x=0, dst_y=0, z_index=0, image_idx=0)
     sp = JpegBandSplicer()
     out = b""
-    for a, b in bands:
-        data, _ = job.run_band(a, b)
-        out += sp.push(data)
-    job.close()
+    try:
+        for a, b in bands:
+            data, _ = job.run_band(a, b)
+            out += sp.push(data)
+    finally:
+        job.close()
     return out
 
 
@@ -46,6 +59,38 @@ def test_entropy_bytes_match_oracle(ctx, w, h, quality):
     want = orc.jpeg_encode_rows(rgba, w, h, 0, h, quality)
     got = _gpu_entropy(ctx, rgba, w, h, quality, [(0, h)])
     assert got == want
+
+
+@pytest.mark.parametrize("w,h,quality", [(64, 48, 90), (8, 8, 50), (1, 1, 85), (1024, 8, 90), (1025, 16, 90), (1032, 24, 50),
+                                         (2051, 77, 75), (3000, 40, 60), (4099, 9, 85), (257, 300, 88)])
+def test_one_pass_route_alone(ctx, monkeypatch, w, h, quality):
+    """STITCH_JPEG_ONE_PASS=2: no second route behind the MCU kernel, so these bytes are its own.  Widths on both
+    sides of the 1024-pixel chunks (the DC predictor crosses from one CTA's chunk into the next)."""
+    monkeypatch.setenv("STITCH_JPEG_ONE_PASS", "2")
+    rng = np.random.default_rng(w * 7 + h)
+    rgba = _photo(rng, w, h).reshape(h, w * 4)
+    want = orc.jpeg_encode_rows(rgba, w, h, 0, h, quality)
+    assert _gpu_entropy(ctx, rgba, w, h, quality, [(0, h)]) == want
+
+
+def test_one_pass_route_reports_what_it_cannot_hold(ctx, monkeypatch):
+    monkeypatch.setenv("STITCH_JPEG_ONE_PASS", "2")
+    rng = np.random.default_rng(12)
+    w, h = 264, 16
+    rgba = rng.integers(0, 256, size=(h, w * 4), dtype=np.uint8)
+    with pytest.raises(_native.StitchError, match="bits in an MCU"):
+        _gpu_entropy(ctx, rgba, w, h, 100, [(0, h)])
+
+
+def test_smooth_and_noisy_bands_in_one_job(ctx):
+    """A job whose first band the MCU kernel holds and whose second it does not (noise at quality 100)."""
+    rng = np.random.default_rng(13)
+    w, h = 1100, 32
+    rgba = _photo(rng, w, h).reshape(h, w * 4).copy()
+    rgba[16:] = rng.integers(0, 256, size=(16, w * 4), dtype=np.uint8)
+    want = orc.jpeg_encode_rows(rgba, w, h, 0, h, 100)
+    assert _gpu_entropy(ctx, rgba, w, h, 100, [(0, 16), (16, 32)]) == want
+    assert _gpu_entropy(ctx, rgba, w, h, 100, [(0, 32)]) == want
 
 
 def test_random_noise_many_ff_bytes(ctx):
