@@ -1166,24 +1166,24 @@ static int run_band_impl(stitch_job *job, uint32_t y0, uint32_t y1, uint8_t *out
     if ((rc = decode_tiles(job, 0, &launches, y0, y1))) return rc;
     CK(cudaEventRecord(ctx->ev[2], ctx->stream));
     if (!job->finalized && (rc = finalize_job(job))) return rc;
-    ComposeParams cp{};
-    cp.tiles = job->d_tiles; cp.bin_start = job->d_bin_start; cp.bin_tiles = job->d_bin_tiles;
-    cp.bins_x = job->bins_x; cp.bin_w_log2 = job->bin_w_log2; cp.bin_h_log2 = job->bin_h_log2;
-    cp.bin_y_origin = job->bin_y_origin; cp.canvas_w = jd.canvas_w; cp.alpha_blend = jd.alpha_blend;
-    bg_words(jd, cp.bg_lo, cp.bg_hi);
-    // composite the band into HBM, then kernel (d); MCU rows are independent entropy segments (jpeg.cu)
-    job->canvas_pitch = pitch16;
-    if ((rc = ensure_buffer(ctx, &job->d_canvas, &job->canvas_bytes, pitch16 * (size_t)n_rows))) return rc;
-    {  // the quad compositor of fused.cu (16-byte loads inside a tile) feeding the canvas
-      FusedParams fq{};
-      fq.tiles = job->d_tiles; fq.bin_start = job->d_bin_start; fq.bin_tiles = job->d_bin_tiles;
-      fq.bins_x = job->bins_x; fq.canvas_w = jd.canvas_w; fq.alpha_blend = jd.alpha_blend;
-      bg_words(jd, fq.bg_lo, fq.bg_hi);
-      if (job->strip_ok) CK(launch_compose_plan(strip_params(job), false, job->d_canvas, pitch16, y0, y1, ctx->stream));
-      else CK(launch_compose_canvas(fq, false, job->d_canvas, pitch16, y0, y1, ctx->stream));
+    // an exact mosaic of RGBA8 tiles is coded straight from the tiles (jpeg.cu); anything else is composited
+    // into HBM first, then kernel (d) reads the canvas; MCU rows are independent entropy segments
+    bool need_canvas = false;
+    if ((rc = stitch_jpeg_encode_band(job, y0, y1, nullptr, 0, &jpeg_bytes, &launches, &need_canvas))) return rc;
+    if (need_canvas) {
+      job->canvas_pitch = pitch16;
+      if ((rc = ensure_buffer(ctx, &job->d_canvas, &job->canvas_bytes, pitch16 * (size_t)n_rows))) return rc;
+      {  // the quad compositor of fused.cu (16-byte loads inside a tile) feeding the canvas
+        FusedParams fq{};
+        fq.tiles = job->d_tiles; fq.bin_start = job->d_bin_start; fq.bin_tiles = job->d_bin_tiles;
+        fq.bins_x = job->bins_x; fq.canvas_w = jd.canvas_w; fq.alpha_blend = jd.alpha_blend;
+        bg_words(jd, fq.bg_lo, fq.bg_hi);
+        if (job->strip_ok) CK(launch_compose_plan(strip_params(job), false, job->d_canvas, pitch16, y0, y1, ctx->stream));
+        else CK(launch_compose_canvas(fq, false, job->d_canvas, pitch16, y0, y1, ctx->stream));
+      }
+      launches += 1;
+      if ((rc = stitch_jpeg_encode_band(job, y0, y1, job->d_canvas, pitch16, &jpeg_bytes, &launches, nullptr))) return rc;
     }
-    launches += 1;
-    if ((rc = stitch_jpeg_encode_band(job, y0, y1, job->d_canvas, pitch16, &jpeg_bytes, &launches))) return rc;
     job->out_pitch = jpeg_bytes; job->out_lead = 0; job->out_row_bytes = jpeg_bytes;
     CK(cudaEventRecord(ctx->ev[3], ctx->stream));
     if (out) {

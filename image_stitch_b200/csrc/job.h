@@ -111,6 +111,7 @@ struct stitch_job {
   size_t jpeg_cap[5] = {0, 0, 0, 0, 0};
   unsigned long long *h_jpeg_totals = nullptr;  // pinned: [0] unstuffed bytes, [1] output bytes
   int jpeg_tables_quality = -1;
+  bool jpeg_overflowed = false;                 // jpeg.cu: the try without a canvas overflowed a chunk
   bool jpeg_huff_ready = false;                 // jpeg.cu: the Annex K tables are in constant memory, the MCU kernel's shared memory is opted in
   // JPEG tiles (jpeg_decode.cu): one pinned status word per tile, written by the tile's last decode kernel;
   // jd_pending: (slot, tile) pairs not checked yet
@@ -159,5 +160,7 @@ uint32_t stitch_crc_finish(uint32_t raw, uint64_t n);
 int stitch_build_strip_plan(stitch_job *job, std::vector<stitch::DevTile> &dt, const std::vector<uint32_t> &src_words,
                             const std::vector<uint32_t> &src_rows);
 bool stitch_encode_tile_maps(const stitch::DevTile &t, uint32_t words_per_row, uint32_t rows, void *out3);
+// canvas == nullptr: try the band from the tiles themselves (an exact mosaic of RGBA8 tiles, no blending); when
+// that is not possible *need_canvas comes back true and the caller composites and calls again with the canvas.
 int stitch_jpeg_encode_band(stitch_job *job, uint32_t y0, uint32_t y1, const uint8_t *canvas, size_t canvas_pitch,
-                            size_t *out_bytes, uint32_t *launches);
+                            size_t *out_bytes, uint32_t *launches, bool *need_canvas);

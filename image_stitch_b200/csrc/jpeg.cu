@@ -23,7 +23,9 @@
 //   J7 stuff    CTA = one MCU row: byte stuffing, RSTm marker, final bytes
 #include "job.h"
 
+#include <algorithm>
 #include <cstdlib>
+#include <vector>
 
 #include <cstring>
 
@@ -223,6 +225,18 @@ struct HuffSmem {
   uint32_t dc[2][16];
   uint32_t ac[2][256];
 };
+// The MCU kernel's form of the tables: entry = ((code << s) << 6) | (code length + s), s = the symbol's low 4 bits
+// (its magnitude bits go into the s low bits of the code field).
+__device__ __forceinline__ void load_huff_sized(HuffSmem &h) {
+  for (uint32_t i = threadIdx.x; i < 32; i += blockDim.x) {
+    const uint32_t e = (&c_dc_tab[0][0])[i], s = i & 15u;
+    (&h.dc[0][0])[i] = (((e >> 8) << s) << 6) | ((e & 0xffu) + s);
+  }
+  for (uint32_t i = threadIdx.x; i < 512; i += blockDim.x) {
+    const uint32_t e = (&c_ac_tab[0][0])[i], s = i & 15u;
+    (&h.ac[0][0])[i] = (((e >> 8) << s) << 6) | ((e & 0xffu) + s);
+  }
+}
 __device__ __forceinline__ void load_huff(HuffSmem &h) {
   for (uint32_t i = threadIdx.x; i < 32; i += blockDim.x) (&h.dc[0][0])[i] = (&c_dc_tab[0][0])[i];
   for (uint32_t i = threadIdx.x; i < 512; i += blockDim.x) (&h.ac[0][0])[i] = (&c_ac_tab[0][0])[i];
@@ -509,6 +523,13 @@ struct JpegQuant {   // zig-zag order; [0] luminance, [1] chrominance; divisor =
   uint32_t recip[2][64];   // ceil(2^32 / divisor)
 };
 
+// Direct staging: where the band is an exact mosaic of RGBA8 tiles (nothing overlaps, nothing shows the background,
+// no blending) the MCU kernel reads the tiles themselves and no canvas is composited.  The band's rows are cut
+// at every tile edge into groups; inside a group the same tiles cover every row, left to right.
+struct JmSeg { uint32_t x0, pitch; const uint8_t *p; };          // p: the pixel at column x0 of the group's first row
+struct JmGroup { uint32_t row0, row1, seg0, nseg; };             // canvas rows [row0, row1)
+struct JmDirect { const JmGroup *groups; const JmSeg *segs; uint32_t n_groups; };
+
 struct JmSmem {
   uint8_t px[8][JM_PX * 4];              // RGBA rows; reused as the chunk buffer (words) once the pixels are consumed
   uint32_t stage[JM_WORDS][JM_MCUS];     // word j of thread t's code at [j][t]
@@ -552,11 +573,11 @@ struct JmBits {
 };
 
 __global__ void __launch_bounds__(JM_MCUS, 4) jpeg_mcu_kernel(const uint8_t *canvas, size_t pitch, JpegGeom g,
-                                                              const __grid_constant__ JpegQuant q, uint32_t *chunk_words,
+                                                              const __grid_constant__ JpegQuant q, const JmDirect dir, uint32_t *chunk_words,
                                                               uint32_t *chunk_bits, unsigned long long *overflow) {
   extern __shared__ __align__(16) uint8_t jm_raw[];
   JmSmem &sm = *reinterpret_cast<JmSmem *>(jm_raw);
-  load_huff(sm.hs);
+  load_huff_sized(sm.hs);
   const uint32_t t = threadIdx.x, lane = t & 31u, warp = t >> 5;
   const uint32_t m = blockIdx.x * JM_MCUS + t;          // MCU in the row
   const uint32_t x0 = blockIdx.x * JM_MCUS * 8u;        // first pixel column of the chunk
@@ -566,13 +587,34 @@ __global__ void __launch_bounds__(JM_MCUS, 4) jpeg_mcu_kernel(const uint8_t *can
   uint32_t *cw = reinterpret_cast<uint32_t *>(&sm.px[0][0]);
   for (uint32_t mr = blockIdx.y; mr < g.mrows; mr += gridDim.y) {
     __syncthreads();   // the previous chunk has left the buffer (and the tables are loaded)
+    JmGroup grp;
+    uint32_t seg_first = 0;
+    if (dir.groups) {   // the group of this MCU row, and its tile at the chunk's first staged column
+      uint32_t lo = 0, hi = dir.n_groups;
+      const uint32_t yf = g.y0 + mr * 8u;
+      while (hi - lo > 1u) { const uint32_t mid = (lo + hi) >> 1; if (__ldg(&dir.groups[mid].row0) <= yf) lo = mid; else hi = mid; }
+      grp = dir.groups[lo];
+      const uint32_t xf = x0 ? x0 - 8u : 0u;
+      lo = 0; hi = grp.nseg;
+      while (hi - lo > 1u) { const uint32_t mid = (lo + hi) >> 1; if (__ldg(&dir.segs[grp.seg0 + mid].x0) <= xf) lo = mid; else hi = mid; }
+      seg_first = grp.seg0 + lo;
+    }
     for (uint32_t c = t; c < 8u * (JM_PX / 4u); c += JM_MCUS) {
       const uint32_t yy = c / (JM_PX / 4u), p4 = c % (JM_PX / 4u);   // row, 16-byte piece (4 pixels) in the row
       if (p4 * 4u >= px_here || (x0 == 0u && p4 < 2u)) continue;
       uint32_t y = g.y0 + mr * 8u + yy;
-      y = min(y, g.height - 1u) - g.y0;  // replicate the last image row below the bottom edge
+      y = min(y, g.height - 1u);  // replicate the last image row below the bottom edge
       const uint32_t sa = (uint32_t)__cvta_generic_to_shared(&sm.px[yy][p4 * 16u]);
-      const uint8_t *src = canvas + (size_t)y * pitch + ((size_t)x0 + p4 * 4u - 8u) * 4u;
+      const uint8_t *src;
+      if (dir.groups) {
+        const uint32_t x = x0 + p4 * 4u - 8u, seg_end = grp.seg0 + grp.nseg;
+        uint32_t si = seg_first;
+        while (si + 1u < seg_end && __ldg(&dir.segs[si + 1u].x0) <= x) si++;
+        const JmSeg sg = dir.segs[si];
+        src = sg.p + (size_t)(y - grp.row0) * sg.pitch + (size_t)(x - sg.x0) * 4u;
+      } else {
+        src = canvas + (size_t)(y - g.y0) * pitch + ((size_t)x0 + p4 * 4u - 8u) * 4u;
+      }
       asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(src) : "memory");
     }
     asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
@@ -627,49 +669,59 @@ __global__ void __launch_bounds__(JM_MCUS, 4) jpeg_mcu_kernel(const uint8_t *can
         // Quantise the 63 AC terms in straight-line code; the non-zero ones go, 16 bits each (magnitude, sign in
         // bit 15), to the far end of the thread's column of code words, growing towards the code: entry e at word
         // JM_WORDS - 1 - e / 2, half e & 1.  Their zig-zag positions stay in a 64-bit mask.
-        unsigned long long nz = 0;
-        int woff = (JM_WORDS - 1) * JM_MCUS * 4, wstep = 2;
+        uint32_t nz_lo = 0, nz_hi = 0;
+        uint8_t *wp = colb + (JM_WORDS - 1) * JM_MCUS * 4;
+        int wstep = 2;
 #pragma unroll
         for (int k = 1; k < 64; k++) {
           const int c = d[zz_nat(k)];
           const uint32_t a = __umulhi((uint32_t)abs(c) + q.half[cls][k], q.recip[cls][k]);
           if (a != 0u) {
-            *reinterpret_cast<uint16_t *>(colb + woff) = (uint16_t)(a | (((uint32_t)c >> 16) & 0x8000u));
-            woff += wstep;
+            *reinterpret_cast<uint16_t *>(wp) = (uint16_t)(a ^ (uint32_t)(c >> 31));   // a, or ~a for a negative term: its magnitude bits as they are coded
+            wp += wstep;
             wstep = -JM_MCUS * 4 - wstep;   // 2, -514, 2, ...
-            nz |= 1ull << k;
+            if (k < 32) nz_lo |= 1u << k; else nz_hi |= 1u << (k - 32);
           }
         }
         // the entries must not have reached the code words written so far
-        const uint32_t n_ent = (uint32_t)__popcll(nz);
+        const uint32_t n_ent = (uint32_t)(__popc(nz_lo) + __popc(nz_hi));
         if ((uint32_t)JM_WORDS - ((n_ent + 1u) >> 1) < b.wr) b.ovf = 1u;
-        int roff = (JM_WORDS - 1) * JM_MCUS * 4, rstep = 2;
         {  // DC difference against the MCU on the left (0 at the start of the row: a restart interval)
           int pred = __shfl_up_sync(0xffffffffu, dcq, 1);
           if (lane == 0u) pred = left_dc;
           const int diff = dcq - pred;
           const uint32_t a = (uint32_t)abs(diff), s = 32u - (uint32_t)__clz((int)a), e = dct[s];
-          b.put(((e >> 8) << s) | ((a ^ (uint32_t)(diff >> 31)) & ((1u << s) - 1u)), (e & 0xffu) + s, (uint32_t)JM_WORDS - ((n_ent + 1u) >> 1));
+          b.put((e >> 6) | ((a ^ (uint32_t)(diff >> 31)) & ((1u << s) - 1u)), e & 63u, (uint32_t)JM_WORDS - ((n_ent + 1u) >> 1));
         }
         int prev = 0;
-        while (nz) {   // each lane walks ITS non-zero terms
-          const int k = __ffsll((long long)nz) - 1;
-          nz &= nz - 1ull;
-          const uint32_t x = *reinterpret_cast<const uint16_t *>(colb + roff);
-          roff += rstep;
-          rstep = -JM_MCUS * 4 - rstep;
-          const uint32_t lim = nz ? (uint32_t)roff / (JM_MCUS * 4u) : (uint32_t)JM_WORDS;   // the word of the next unread entry
-          uint32_t run = (uint32_t)(k - 1 - prev);
-          prev = k;
-          if (run > 15u) {
-            const uint32_t z = act[0xF0];
-            do { b.put(z >> 8, z & 0xffu, lim); run -= 16u; } while (run > 15u);
+        const uint8_t *rp = colb + (JM_WORDS - 1) * JM_MCUS * 4;
+        int rstep = 2;
+        uint32_t left = n_ent;
+        // each lane walks ITS non-zero terms: zig-zag positions 1..31, then 32..63
+#pragma unroll 1
+        for (int half = 0; half < 2; half++) {
+          uint32_t mk = half ? nz_hi : nz_lo;
+          const int kb = half * 32;
+          while (mk) {
+            const int k = kb + __ffs((int)mk) - 1;
+            mk &= mk - 1u;
+            const uint32_t x = *reinterpret_cast<const uint16_t *>(rp);
+            rp += rstep;
+            rstep = -JM_MCUS * 4 - rstep;
+            left--;
+            const uint32_t lim = left ? (uint32_t)(rp - colb) / (JM_MCUS * 4u) : (uint32_t)JM_WORDS;   // the word of the next unread entry
+            uint32_t run = (uint32_t)(k - 1 - prev);
+            prev = k;
+            if (run > 15u) {
+              const uint32_t z = act[0xF0];
+              do { b.put(z >> 6, z & 63u, lim); run -= 16u; } while (run > 15u);
+            }
+            const uint32_t a = (x ^ (0u - (x >> 15))) & 0x7fffu;
+            const uint32_t s = 32u - (uint32_t)__clz((int)a), e = act[(run << 4) | s];
+            b.put((e >> 6) | (x & ((1u << s) - 1u)), e & 63u, lim);
           }
-          const uint32_t a = x & 0x7fffu, sg = 0u - (x >> 15);
-          const uint32_t s = 32u - (uint32_t)__clz((int)a), e = act[(run << 4) | s];
-          b.put(((e >> 8) << s) | ((a ^ sg) & ((1u << s) - 1u)), (e & 0xffu) + s, lim);
         }
-        if (prev != 63) { const uint32_t e = act[0]; b.put(e >> 8, e & 0xffu, (uint32_t)JM_WORDS); }
+        if (prev != 63) { const uint32_t e = act[0]; b.put(e >> 6, e & 63u, (uint32_t)JM_WORDS); }
       }
       if (b.nacc) {   // left-aligned tail, zeros below
         if (b.wr < (uint32_t)JM_WORDS) b.col[b.wr * JM_MCUS] = (uint32_t)b.acc << (32u - b.nacc); else b.ovf = 1u;
@@ -727,30 +779,39 @@ __device__ __forceinline__ void jm_row_offsets(const uint32_t *bits, uint32_t n,
   }
 }
 
-// 32 bits of the row's stream from bit position b (a multiple of 32), MSB first; zero past `total`, then the
-// 1-bits that pad the segment to a byte boundary.
-__device__ __forceinline__ uint32_t jm_row_word(const uint32_t *row_words, const uint32_t *off, uint32_t n, uint32_t total, uint32_t b) {
-  uint32_t lo = 0, hi = n;   // largest c with off[c] <= b
-  while (hi - lo > 1u) { const uint32_t mid = (lo + hi) >> 1; if (off[mid] <= b) lo = mid; else hi = mid; }
-  uint32_t c = lo, out = 0, got = 0;
-  while (got < 32u && b + got < total) {
-    const uint32_t lb = b + got - off[c], avail = off[c + 1u] - off[c] - lb;
-    if (avail == 0u) { c++; continue; }
-    const uint32_t take = min(32u - got, avail), sh = lb & 31u;
-    const uint32_t *w = row_words + (size_t)c * JM_CHUNK_WORDS + (lb >> 5);
-    const uint32_t w0 = __byte_perm(__ldg(w), 0, 0x0123), w1 = sh + take > 32u ? __byte_perm(__ldg(w + 1), 0, 0x0123) : 0u;
-    uint32_t v = __funnelshift_l(w1, w0, sh);
-    if (take < 32u) v &= ~(0xffffffffu >> take);
-    out |= v >> got;
-    got += take;
-    if (take == avail) c++;
+// The row's stream read 32 bits at a time from a bit position that is a multiple of 32, MSB first; zero past
+// `total`, then the 1-bits that pad the segment to a byte boundary.
+struct JmRowReader {
+  const uint32_t *row_words, *off;
+  uint32_t n, total, c, pos;
+  __device__ __forceinline__ void seek(uint32_t b) {
+    uint32_t lo = 0, hi = n;   // largest c with off[c] <= b
+    while (hi - lo > 1u) { const uint32_t mid = (lo + hi) >> 1; if (off[mid] <= b) lo = mid; else hi = mid; }
+    c = lo; pos = b;
   }
-  if (b < total && total - b < 32u && (total & 7u)) {
-    const uint32_t from = total - b, to = ((total + 7u) & ~7u) - b;   // 1 <= to <= 32
-    out |= (0xffffffffu >> from) & (to == 32u ? 0xffffffffu : ~(0xffffffffu >> to));
+  __device__ __forceinline__ uint32_t next() {
+    const uint32_t b = pos;
+    uint32_t out = 0, got = 0;
+    while (got < 32u && b + got < total) {
+      const uint32_t lb = b + got - off[c], avail = off[c + 1u] - off[c] - lb;
+      if (avail == 0u) { c++; continue; }
+      const uint32_t take = min(32u - got, avail), sh = lb & 31u;
+      const uint32_t *w = row_words + (size_t)c * JM_CHUNK_WORDS + (lb >> 5);
+      const uint32_t w0 = __byte_perm(__ldg(w), 0, 0x0123), w1 = sh + take > 32u ? __byte_perm(__ldg(w + 1), 0, 0x0123) : 0u;
+      uint32_t v = __funnelshift_l(w1, w0, sh);
+      if (take < 32u) v &= ~(0xffffffffu >> take);
+      out |= v >> got;
+      got += take;
+      if (take == avail) c++;
+    }
+    if (b < total && total - b < 32u && (total & 7u)) {
+      const uint32_t from = total - b, to = ((total + 7u) & ~7u) - b;   // 1 <= to <= 32
+      out |= (0xffffffffu >> from) & (to == 32u ? 0xffffffffu : ~(0xffffffffu >> to));
+    }
+    pos = b + 32u;
+    return out;
   }
-  return out;
-}
+};
 
 __global__ void __launch_bounds__(256) jpeg_rowinfo_kernel(const uint32_t *chunk_words, const uint32_t *chunk_bits, uint32_t n_chunks,
                                                            uint32_t n_rows, uint32_t *row_bits, uint32_t *row_ff) {
@@ -764,8 +825,13 @@ __global__ void __launch_bounds__(256) jpeg_rowinfo_kernel(const uint32_t *chunk
     const uint32_t total = off[n_chunks];
     const uint32_t *rw = chunk_words + (size_t)r * n_chunks * JM_CHUNK_WORDS;
     uint32_t c = 0;
-    for (uint32_t i = threadIdx.x; i * 32u < total; i += blockDim.x)
-      c += (uint32_t)__popc(__vcmpeq4(jm_row_word(rw, off, n_chunks, total, i * 32u), 0xffffffffu)) >> 3;
+    JmRowReader rd;
+    rd.row_words = rw; rd.off = off; rd.n = n_chunks; rd.total = total;
+    for (uint32_t i = threadIdx.x * 4u; i * 32u < total; i += blockDim.x * 4u) {   // 16 bytes of the stream a thread
+      rd.seek(i * 32u);
+#pragma unroll
+      for (int j = 0; j < 4; j++) c += (uint32_t)__popc(__vcmpeq4(rd.next(), 0xffffffffu)) >> 3;
+    }
     c = __reduce_add_sync(0xffffffffu, c);
     if ((threadIdx.x & 31u) == 0 && c) atomicAdd(&s_cnt, c);
     __syncthreads();
@@ -779,6 +845,7 @@ __global__ void __launch_bounds__(256) jpeg_stuff_chunks_kernel(const uint32_t *
   __shared__ uint32_t off[JM_MAX_CHUNKS + 1];
   __shared__ uint32_t warp_tot[8];
   __shared__ uint32_t s_ff;
+  __shared__ __align__(16) uint8_t sbuf[16 + 8192 + 16];   // one round's stuffed bytes, placed so that shared and global addresses agree mod 16
   const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
   for (uint32_t r = blockIdx.x; r < n_rows; r += gridDim.x) {
     __syncthreads();
@@ -788,31 +855,54 @@ __global__ void __launch_bounds__(256) jpeg_stuff_chunks_kernel(const uint32_t *
     const uint32_t total = off[n_chunks], n = (total + 7u) >> 3;
     const uint32_t *rw = chunk_words + (size_t)r * n_chunks * JM_CHUNK_WORDS;
     uint8_t *o = out + out_base[r];
-    for (uint32_t i0 = 0; i0 * 32u < total; i0 += 256u) {
-      const uint32_t i = i0 + threadIdx.x;
-      const uint32_t w = i * 32u < total ? jm_row_word(rw, off, n_chunks, total, i * 32u) : 0u;
-      const uint32_t ffm = __vcmpeq4(w, 0xffffffffu), cnt = (uint32_t)__popc(ffm) >> 3;   // bytes past the end are 0
+    JmRowReader rd;
+    rd.row_words = rw; rd.off = off; rd.n = n_chunks; rd.total = total;
+    for (uint32_t i0 = 0; i0 * 32u < total; i0 += 1024u) {   // a round: 4096 bytes of the stream, 16 a thread
+      const uint32_t i = i0 + threadIdx.x * 4u;
+      uint32_t w[4] = {0u, 0u, 0u, 0u}, cnt = 0;
+      if (i * 32u < total) {
+        rd.seek(i * 32u);
+#pragma unroll
+        for (int j = 0; j < 4; j++) { w[j] = rd.next(); cnt += (uint32_t)__popc(__vcmpeq4(w[j], 0xffffffffu)) >> 3; }   // bytes past the end are 0
+      }
       uint32_t incl = cnt;
 #pragma unroll
       for (int k = 1; k < 32; k <<= 1) { const uint32_t v = __shfl_up_sync(0xffffffffu, incl, k); if (lane >= (uint32_t)k) incl += v; }
       if (lane == 31u) warp_tot[warp] = incl;
       __syncthreads();
-      uint32_t wbase = 0;
+      uint32_t wbase = 0, round_ff = 0;
 #pragma unroll
-      for (int k = 0; k < 8; k++) if ((uint32_t)k < warp) wbase += warp_tot[k];
-      uint32_t pos = i * 4u + s_ff + wbase + incl - cnt;
+      for (int k = 0; k < 8; k++) { const uint32_t v = warp_tot[k]; if ((uint32_t)k < warp) wbase += v; round_ff += v; }
+      uint8_t *dst = o + (size_t)i0 * 4u + s_ff;                        // where the round's bytes go
+      const uint32_t mis = (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 15u);
+      const uint32_t round_bytes = min(4096u, n - i0 * 4u) + round_ff;
+      uint32_t pos = mis + (i - i0) * 4u + wbase + incl - cnt;
+      if (cnt == 0u && i * 4u + 16u <= n && (pos & 3u) == 0u) {   // the usual case: 16 plain bytes, word-aligned in the buffer
 #pragma unroll
-      for (int j = 0; j < 4; j++) {
-        if (i * 4u + j < n) {
-          const uint32_t byte = (w >> (24 - 8 * j)) & 0xffu;
-          o[pos++] = (uint8_t)byte;
-          if (byte == 0xffu) o[pos++] = 0;
+        for (int j = 0; j < 4; j++) *reinterpret_cast<uint32_t *>(&sbuf[pos + 4u * j]) = __byte_perm(w[j], 0, 0x0123);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 16; j++) {
+          if (i * 4u + j < n) {
+            const uint32_t byte = (w[j >> 2] >> (24 - 8 * (j & 3))) & 0xffu;
+            sbuf[pos++] = (uint8_t)byte;
+            if (byte == 0xffu) sbuf[pos++] = 0;
+          }
         }
       }
       __syncthreads();
-      if (threadIdx.x == 255u) s_ff += wbase + incl;
+      // copy out: 16 bytes a thread where the piece lies wholly inside the round, single bytes at its two ends
+      for (uint32_t q = threadIdx.x * 16u; q < mis + round_bytes; q += 4096u) {
+        if (q >= mis && q + 16u <= mis + round_bytes) {
+          *reinterpret_cast<uint4 *>(dst - mis + q) = *reinterpret_cast<const uint4 *>(&sbuf[q]);
+        } else {
+          for (uint32_t e = max(q, mis); e < min(q + 16u, mis + round_bytes); e++) dst[e - mis] = sbuf[e];
+        }
+      }
       __syncthreads();
+      if (threadIdx.x == 0) s_ff += round_ff;
     }
+    __syncthreads();
     if (threadIdx.x == 0 && first_mrow + r + 1u < total_mrows) {
       o[n + s_ff] = 0xFF;
       o[n + s_ff + 1] = (uint8_t)(0xD0u + ((first_mrow + r) & 7u));
@@ -845,9 +935,68 @@ int upload_tables(stitch_job *job) {
 
 }  // namespace
 
+// Is the band [y0, y1) an exact mosaic of RGBA8 tiles the MCU kernel can read in place?  If so the groups and
+// their tiles go to the device (scratch [3], which only the J1..J7 route uses otherwise) and *dir describes them.
+static int jpeg_direct_plan(stitch_job *job, uint32_t y0, uint32_t y1, JmDirect *dir, bool *ok) {
+  stitch_ctx *ctx = job->ctx;
+  const stitch_job_desc &jd = job->desc;
+  *ok = false;
+  if (jd.alpha_blend || jd.out_bit_depth != 8) return STITCH_OK;
+  if (const char *e = getenv("STITCH_JPEG_DIRECT")) if (atoi(e) == 0) return STITCH_OK;
+  struct Rect { uint32_t xa, xb, ya, yb; const TileRec *t; };
+  std::vector<Rect> rs;
+  std::vector<uint32_t> cuts{y0, y1};
+  for (const TileRec &t : job->tiles) {
+    const stitch_tile_desc &d = t.d;
+    if (!d.vis_w || !d.vis_h) continue;
+    const uint32_t ya = (uint32_t)d.dst_y, yb = ya + d.vis_h, xa = (uint32_t)d.dst_x, xb = xa + d.vis_w;
+    if (yb <= y0 || ya >= y1) continue;
+    if (d.color_type != 6 || d.bit_depth != 8 || t.has_pal || !t.d_pix) return STITCH_OK;
+    if ((reinterpret_cast<uintptr_t>(t.d_pix) & 15u) || (t.pitch & 15u) || ((d.src_off_x - xa) & 3u)) return STITCH_OK;   // 16-byte pieces
+    if ((ya & 7u) || ((yb & 7u) && yb != jd.canvas_h)) return STITCH_OK;   // an MCU row has one set of tiles
+    rs.push_back({xa, xb, ya, yb, &t});
+    if (ya > y0) cuts.push_back(ya);
+    if (yb < y1) cuts.push_back(yb);
+    if (rs.size() > 4096) return STITCH_OK;
+  }
+  std::sort(cuts.begin(), cuts.end());
+  cuts.erase(std::unique(cuts.begin(), cuts.end()), cuts.end());
+  std::vector<JmGroup> groups;
+  std::vector<JmSeg> segs;
+  std::vector<const Rect *> row;
+  for (size_t k = 0; k + 1 < cuts.size(); k++) {
+    const uint32_t ra = cuts[k], rb = cuts[k + 1];
+    row.clear();
+    for (const Rect &r : rs) if (r.ya <= ra && r.yb >= rb) row.push_back(&r);
+    std::sort(row.begin(), row.end(), [](const Rect *a, const Rect *b) { return a->xa < b->xa; });
+    uint32_t x = 0;
+    JmGroup g{ra, rb, (uint32_t)segs.size(), (uint32_t)row.size()};
+    for (const Rect *r : row) {
+      if (r->xa != x) return STITCH_OK;   // a gap (the background shows) or an overlap
+      const stitch_tile_desc &d = r->t->d;
+      segs.push_back({r->xa, r->t->pitch, r->t->d_pix + (size_t)(d.src_off_y + (ra - r->ya)) * r->t->pitch + (size_t)d.src_off_x * 4u});
+      x = r->xb;
+    }
+    if (x != jd.canvas_w || segs.size() > 65536) return STITCH_OK;
+    groups.push_back(g);
+  }
+  // a tile that only touches a group partly was dropped from it above and would leave a gap, so reaching here
+  // means every row of the band is tiled exactly
+  const size_t gb = (groups.size() * sizeof(JmGroup) + 15) / 16 * 16, need = gb + segs.size() * sizeof(JmSeg);
+  int rc;
+  if ((rc = stitch_ensure_buffer(ctx, &job->d_jpeg[3], &job->jpeg_cap[3], need))) return rc;
+  STITCH_CK(cudaMemcpyAsync(job->d_jpeg[3], groups.data(), groups.size() * sizeof(JmGroup), cudaMemcpyHostToDevice, ctx->stream));   // pageable: staged before the call returns
+  STITCH_CK(cudaMemcpyAsync(job->d_jpeg[3] + gb, segs.data(), segs.size() * sizeof(JmSeg), cudaMemcpyHostToDevice, ctx->stream));
+  dir->groups = reinterpret_cast<const JmGroup *>(job->d_jpeg[3]);
+  dir->segs = reinterpret_cast<const JmSeg *>(job->d_jpeg[3] + gb);
+  dir->n_groups = (uint32_t)groups.size();
+  *ok = true;
+  return STITCH_OK;
+}
+
 // The one-pass route over a band.  Scratch: [0] chunk slots, [1] bits per chunk, [2] per-row sizes and totals.
 static int encode_band_one_pass(stitch_job *job, const JpegGeom &g, uint32_t first_mrow, uint32_t total_mrows, const uint8_t *canvas,
-                                size_t canvas_pitch, size_t *out_bytes, uint32_t *launches, bool *overflow) {
+                                size_t canvas_pitch, const JmDirect &dir, size_t *out_bytes, uint32_t *launches, bool *overflow) {
   stitch_ctx *ctx = job->ctx;
   int rc;
   static_assert(sizeof(JmSmem) <= 56 * 1024, "four CTAs of the MCU kernel per SM");
@@ -888,7 +1037,7 @@ static int encode_band_one_pass(stitch_job *job, const JpegGeom &g, uint32_t fir
   STITCH_CK(cudaMemsetAsync(totals, 0, 32, ctx->stream));
   {
     dim3 grid(n_chunks, g.mrows < 16384u ? g.mrows : 16384u);
-    jpeg_mcu_kernel<<<grid, JM_MCUS, sizeof(JmSmem), ctx->stream>>>(canvas, canvas_pitch, g, q, chunk_words, chunk_bits, totals + 2);
+    jpeg_mcu_kernel<<<grid, JM_MCUS, sizeof(JmSmem), ctx->stream>>>(canvas, canvas_pitch, g, q, dir, chunk_words, chunk_bits, totals + 2);
     STITCH_CK(cudaGetLastError());
   }
   const uint32_t row_grid = g.mrows < 148u * 8u ? g.mrows : 148u * 8u;
@@ -910,7 +1059,7 @@ static int encode_band_one_pass(stitch_job *job, const JpegGeom &g, uint32_t fir
 }
 
 int stitch_jpeg_encode_band(stitch_job *job, uint32_t y0, uint32_t y1, const uint8_t *canvas, size_t canvas_pitch,
-                            size_t *out_bytes, uint32_t *launches) {
+                            size_t *out_bytes, uint32_t *launches, bool *need_canvas) {
   stitch_ctx *ctx = job->ctx;
   const stitch_job_desc &jd = job->desc;
   int rc;
@@ -922,9 +1071,25 @@ int stitch_jpeg_encode_band(stitch_job *job, uint32_t y0, uint32_t y1, const uin
   // error: tests), otherwise one pass first and J1..J7 for a band that overflowed
   int one_pass = 1;
   if (const char *e = getenv("STITCH_JPEG_ONE_PASS")) one_pass = atoi(e);
-  if (one_pass) {
+  if (need_canvas) *need_canvas = false;
+  if (!canvas) {   // first try: the tiles themselves, if the band is an exact mosaic of them
+    JmDirect dir{};
+    bool ok = false;
+    if (one_pass && (rc = jpeg_direct_plan(job, y0, y1, &dir, &ok))) return rc;
     bool overflow = false;
-    if ((rc = encode_band_one_pass(job, g, first_mrow, total_mrows, canvas, canvas_pitch, out_bytes, launches, &overflow))) return rc;
+    if (ok && (rc = encode_band_one_pass(job, g, first_mrow, total_mrows, nullptr, 0, dir, out_bytes, launches, &overflow))) return rc;
+    if (!ok || overflow) *need_canvas = true;
+    job->jpeg_overflowed = overflow;   // the canvas would overflow the same chunks: the second call goes straight to J1..J7
+    return STITCH_OK;
+  }
+  const bool known_overflow = job->jpeg_overflowed;
+  job->jpeg_overflowed = false;
+  if (known_overflow && one_pass == 2)
+    return stitch_fail(ctx, STITCH_E_CAPACITY, "JPEG band [%u,%u): more than %d bits in an MCU or %u bytes in a chunk of %d MCUs (STITCH_JPEG_ONE_PASS=2)",
+                       y0, y1, JM_WORDS * 32, JM_CHUNK_BYTES, JM_MCUS);
+  if (one_pass && !known_overflow) {
+    bool overflow = false;
+    if ((rc = encode_band_one_pass(job, g, first_mrow, total_mrows, canvas, canvas_pitch, JmDirect{}, out_bytes, launches, &overflow))) return rc;
     if (!overflow) return STITCH_OK;
     if (one_pass == 2) {
       return stitch_fail(ctx, STITCH_E_CAPACITY, "JPEG band [%u,%u): more than %d bits in an MCU or %u bytes in a chunk of %d MCUs (STITCH_JPEG_ONE_PASS=2)",

@@ -93,6 +93,58 @@ def test_smooth_and_noisy_bands_in_one_job(ctx):
     assert _gpu_entropy(ctx, rgba, w, h, 100, [(0, 32)]) == want
 
 
+def _mosaic_entropy(ctx, tiles, w, h, quality, bands):
+    """tiles: (rgba array (th, tw, 4), dst_x, dst_y) pasted in order."""
+    job = _native.Job(ctx, w, h, 8, _native.OUT_JPEG_ENTROPY, False, bytes(4), jpeg_quality=quality)
+    sp = JpegBandSplicer()
+    out = b""
+    try:
+        for k, (px, x, y) in enumerate(tiles):
+            th, tw = px.shape[:2]
+            job.add_tile(px.tobytes(), width=tw, height=th, bit_depth=8, color_type=6, interlace=0, filtered=0,
+                         dst_x=x, dst_y=y, z_index=0, image_idx=k)
+        for a, b in bands:
+            data, _ = job.run_band(a, b)
+            out += sp.push(data)
+    finally:
+        job.close()
+    return out
+
+
+@pytest.mark.parametrize("layout", ["grid", "tall_and_short", "gap", "overlap", "odd_x", "ragged_bottom"])
+def test_mosaics_read_in_place_or_through_a_canvas(ctx, monkeypatch, layout):
+    """An exact mosaic of RGBA8 tiles is coded straight from the tiles (no canvas); a gap, an overlap or a tile at an
+    odd column is not one and goes through the compositor.  Either way: the oracle's bytes, and the same bytes
+    with the in-place route switched off."""
+    rng = np.random.default_rng(21)
+    w, h = 2304, 96
+    def t(tw, th):
+        return _photo(rng, tw, th)
+    if layout == "grid":
+        tiles = [(t(1152, 48), x, y) for y in (0, 48) for x in (0, 1152)]
+    elif layout == "tall_and_short":
+        tiles = [(t(1000, 96), 0, 0), (t(1304, 40), 1000, 0), (t(1304, 56), 1000, 40)]
+    elif layout == "gap":
+        tiles = [(t(1152, 96), 0, 0), (t(1100, 96), 1152, 0)]
+    elif layout == "overlap":
+        tiles = [(t(1200, 96), 0, 0), (t(1152, 96), 1152, 0)]
+    elif layout == "odd_x":
+        tiles = [(t(1150, 96), 0, 0), (t(1154, 96), 1150, 0)]
+    else:
+        h = 93
+        tiles = [(t(1152, 48), 0, 0), (t(1152, 48), 1152, 0), (t(2304, 45), 0, 48)]
+    canvas = np.zeros((h, w, 4), np.uint8)
+    for px, x, y in tiles:
+        canvas[y:y + px.shape[0], x:x + px.shape[1]] = px[:h - y]
+    canvas = canvas.reshape(h, w * 4)
+    want = orc.jpeg_encode_rows(canvas, w, h, 0, h, 85)
+    bands = [(0, 48), (48, h)]
+    assert _mosaic_entropy(ctx, tiles, w, h, 85, bands) == want
+    assert _mosaic_entropy(ctx, tiles, w, h, 85, [(0, h)]) == want
+    monkeypatch.setenv("STITCH_JPEG_DIRECT", "0")
+    assert _mosaic_entropy(ctx, tiles, w, h, 85, bands) == want
+
+
 def test_random_noise_many_ff_bytes(ctx):
     """Noise at quality 100 produces long codes and many 0xFF bytes: stuffing and worst-case lengths."""
     rng = np.random.default_rng(11)
