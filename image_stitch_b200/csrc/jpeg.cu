@@ -519,8 +519,7 @@ static constexpr uint32_t JM_CHUNK_BYTES = 8192;          // 4 bits per pixel on
 static constexpr uint32_t JM_CHUNK_WORDS = JM_CHUNK_BYTES / 4;
 
 struct JpegQuant {   // zig-zag order; [0] luminance, [1] chrominance; divisor = quantval << 3 as in c_q8
-  uint32_t half[2][64];    // divisor / 2
-  uint32_t recip[2][64];   // ceil(2^32 / divisor)
+  uint2 hr[2][64];         // x: divisor / 2, y: ceil(2^32 / divisor) -- one 64-bit constant load for the pair
 };
 
 // Direct staging: where the band is an exact mosaic of RGBA8 tiles (nothing overlaps, nothing shows the background,
@@ -528,7 +527,11 @@ struct JpegQuant {   // zig-zag order; [0] luminance, [1] chrominance; divisor =
 // at every tile edge into groups; inside a group the same tiles cover every row, left to right.
 struct JmSeg { uint32_t x0, pitch; const uint8_t *p; };          // p: the pixel at column x0 of the group's first row
 struct JmGroup { uint32_t row0, row1, seg0, nseg; };             // canvas rows [row0, row1)
-struct JmDirect { const JmGroup *groups; const JmSeg *segs; uint32_t n_groups; };
+struct JmDirect {
+  const JmGroup *groups; const JmSeg *segs;
+  const uint32_t *mrow_group;   // group of every MCU row of the band
+  const uint32_t *chunk_seg;    // [group][chunk]: index in segs of the tile at the chunk's first staged column
+};
 
 struct JmSmem {
   uint8_t px[8][JM_PX * 4];              // RGBA rows; reused as the chunk buffer (words) once the pixels are consumed
@@ -587,36 +590,43 @@ __global__ void __launch_bounds__(JM_MCUS, 4) jpeg_mcu_kernel(const uint8_t *can
   uint32_t *cw = reinterpret_cast<uint32_t *>(&sm.px[0][0]);
   for (uint32_t mr = blockIdx.y; mr < g.mrows; mr += gridDim.y) {
     __syncthreads();   // the previous chunk has left the buffer (and the tables are loaded)
+    // Staging: a lane takes a 16-byte piece (4 pixels) of the chunk's span and copies its 8 rows; the 256 pieces of the
+    // chunk are spread over the 4 warps (2 x 32 consecutive pieces each), the 2 pieces of the MCU on the left go to
+    // two lanes of warp 0.  Rows past the bottom edge repeat the last image row.
+    const uint32_t yf = g.y0 + mr * 8u, rows_here = min(8u, g.height - yf);
     JmGroup grp;
-    uint32_t seg_first = 0;
-    if (dir.groups) {   // the group of this MCU row, and its tile at the chunk's first staged column
-      uint32_t lo = 0, hi = dir.n_groups;
-      const uint32_t yf = g.y0 + mr * 8u;
-      while (hi - lo > 1u) { const uint32_t mid = (lo + hi) >> 1; if (__ldg(&dir.groups[mid].row0) <= yf) lo = mid; else hi = mid; }
-      grp = dir.groups[lo];
-      const uint32_t xf = x0 ? x0 - 8u : 0u;
-      lo = 0; hi = grp.nseg;
-      while (hi - lo > 1u) { const uint32_t mid = (lo + hi) >> 1; if (__ldg(&dir.segs[grp.seg0 + mid].x0) <= xf) lo = mid; else hi = mid; }
-      seg_first = grp.seg0 + lo;
+    uint32_t si0 = 0;
+    if (dir.groups) {
+      const uint32_t gi = __ldg(dir.mrow_group + mr);
+      grp = dir.groups[gi];
+      si0 = __ldg(dir.chunk_seg + (size_t)gi * gridDim.x + blockIdx.x);
     }
-    for (uint32_t c = t; c < 8u * (JM_PX / 4u); c += JM_MCUS) {
-      const uint32_t yy = c / (JM_PX / 4u), p4 = c % (JM_PX / 4u);   // row, 16-byte piece (4 pixels) in the row
-      if (p4 * 4u >= px_here || (x0 == 0u && p4 < 2u)) continue;
-      uint32_t y = g.y0 + mr * 8u + yy;
-      y = min(y, g.height - 1u);  // replicate the last image row below the bottom edge
-      const uint32_t sa = (uint32_t)__cvta_generic_to_shared(&sm.px[yy][p4 * 16u]);
+    auto stage_piece = [&](const uint32_t p4) {
+      if (p4 * 4u >= px_here) return;
+      const uint32_t x = x0 + p4 * 4u - 8u;
       const uint8_t *src;
+      size_t pit;
       if (dir.groups) {
-        const uint32_t x = x0 + p4 * 4u - 8u, seg_end = grp.seg0 + grp.nseg;
-        uint32_t si = seg_first;
+        const uint32_t seg_end = grp.seg0 + grp.nseg;
+        uint32_t si = si0;
         while (si + 1u < seg_end && __ldg(&dir.segs[si + 1u].x0) <= x) si++;
         const JmSeg sg = dir.segs[si];
-        src = sg.p + (size_t)(y - grp.row0) * sg.pitch + (size_t)(x - sg.x0) * 4u;
+        pit = sg.pitch;
+        src = sg.p + (size_t)(yf - grp.row0) * pit + (size_t)(x - sg.x0) * 4u;
       } else {
-        src = canvas + (size_t)(y - g.y0) * pitch + ((size_t)x0 + p4 * 4u - 8u) * 4u;
+        pit = pitch;
+        src = canvas + (size_t)(yf - g.y0) * pit + (size_t)x * 4u;
       }
-      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(src) : "memory");
-    }
+      const uint32_t sa = (uint32_t)__cvta_generic_to_shared(&sm.px[0][p4 * 16u]);
+#pragma unroll
+      for (uint32_t k = 0; k < 8u; k++) {
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa + k * (uint32_t)(JM_PX * 4)), "l"(src) : "memory");
+        if (k + 1u < rows_here) src += pit;
+      }
+    };
+    stage_piece(2u + warp * 64u + lane);
+    stage_piece(2u + warp * 64u + 32u + lane);
+    if (warp == 0u && lane < 2u && x0 != 0u) stage_piece(lane);
     asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
     __syncthreads();
     if ((g.width & 7u) && x0 + (uint32_t)JM_MCUS * 8u >= g.width) {   // the chunk holds the image's partial MCU: replicate the last column
@@ -641,7 +651,7 @@ __global__ void __launch_bounds__(JM_MCUS, 4) jpeg_mcu_kernel(const uint8_t *can
           const uint2 two = *reinterpret_cast<const uint2 *>(&sm.px[lane >> 2][(warp * 256u + (lane & 3u) * 2u) * 4u]);
           int s2 = comp == 0u ? jm_y(two.x) + jm_y(two.y) : jm_c(two.x, a1, a2) + jm_c(two.y, a1, a2);
           s2 = __reduce_add_sync(0xffffffffu, s2);
-          const int qa = (int)__umulhi((uint32_t)abs(s2) + q.half[cls][0], q.recip[cls][0]);
+          const int qa = (int)__umulhi((uint32_t)abs(s2) + q.hr[cls][0].x, q.hr[cls][0].y);
           left_dc = s2 < 0 ? -qa : qa;
         }
         int d[64];
@@ -664,7 +674,7 @@ __global__ void __launch_bounds__(JM_MCUS, 4) jpeg_mcu_kernel(const uint8_t *can
         for (int i = 0; i < 8; i++)
           fdct_1d(d[i], d[8 + i], d[16 + i], d[24 + i], d[32 + i], d[40 + i], d[48 + i], d[56 + i], false);
         const uint32_t *dct = sm.hs.dc[cls], *act = sm.hs.ac[cls];
-        const int qa0 = (int)__umulhi((uint32_t)abs(d[0]) + q.half[cls][0], q.recip[cls][0]);
+        const int qa0 = (int)__umulhi((uint32_t)abs(d[0]) + q.hr[cls][0].x, q.hr[cls][0].y);
         const int dcq = d[0] < 0 ? -qa0 : qa0;
         // Quantise the 63 AC terms in straight-line code; the non-zero ones go, 16 bits each (magnitude, sign in
         // bit 15), to the far end of the thread's column of code words, growing towards the code: entry e at word
@@ -675,7 +685,8 @@ __global__ void __launch_bounds__(JM_MCUS, 4) jpeg_mcu_kernel(const uint8_t *can
 #pragma unroll
         for (int k = 1; k < 64; k++) {
           const int c = d[zz_nat(k)];
-          const uint32_t a = __umulhi((uint32_t)abs(c) + q.half[cls][k], q.recip[cls][k]);
+          const uint2 hr = q.hr[cls][k];
+          const uint32_t a = __umulhi((uint32_t)abs(c) + hr.x, hr.y);
           if (a != 0u) {
             *reinterpret_cast<uint16_t *>(wp) = (uint16_t)(a ^ (uint32_t)(c >> 31));   // a, or ~a for a negative term: its magnitude bits as they are coded
             wp += wstep;
@@ -982,14 +993,28 @@ static int jpeg_direct_plan(stitch_job *job, uint32_t y0, uint32_t y1, JmDirect 
   }
   // a tile that only touches a group partly was dropped from it above and would leave a gap, so reaching here
   // means every row of the band is tiled exactly
-  const size_t gb = (groups.size() * sizeof(JmGroup) + 15) / 16 * 16, need = gb + segs.size() * sizeof(JmSeg);
+  const uint32_t mrows = (y1 - y0 + 7) / 8, n_chunks = ((jd.canvas_w + 7) / 8 + JM_MCUS - 1) / JM_MCUS;
+  if (groups.size() * n_chunks > (1u << 20)) return STITCH_OK;
+  std::vector<uint32_t> idx(mrows + groups.size() * n_chunks);   // mrow_group | chunk_seg
+  for (uint32_t gi = 0, mr = 0; gi < groups.size(); gi++) {
+    for (; mr < mrows && y0 + mr * 8u < groups[gi].row1; mr++) idx[mr] = gi;
+    uint32_t si = groups[gi].seg0;
+    for (uint32_t c = 0; c < n_chunks; c++) {
+      const uint32_t xf = c ? c * JM_MCUS * 8u - 8u : 0u;
+      while (si + 1 < groups[gi].seg0 + groups[gi].nseg && segs[si + 1].x0 <= xf) si++;
+      idx[mrows + (size_t)gi * n_chunks + c] = si;
+    }
+  }
+  const size_t gb = (groups.size() * sizeof(JmGroup) + 15) / 16 * 16, sb = segs.size() * sizeof(JmSeg), need = gb + sb + idx.size() * 4;
   int rc;
   if ((rc = stitch_ensure_buffer(ctx, &job->d_jpeg[3], &job->jpeg_cap[3], need))) return rc;
   STITCH_CK(cudaMemcpyAsync(job->d_jpeg[3], groups.data(), groups.size() * sizeof(JmGroup), cudaMemcpyHostToDevice, ctx->stream));   // pageable: staged before the call returns
-  STITCH_CK(cudaMemcpyAsync(job->d_jpeg[3] + gb, segs.data(), segs.size() * sizeof(JmSeg), cudaMemcpyHostToDevice, ctx->stream));
+  STITCH_CK(cudaMemcpyAsync(job->d_jpeg[3] + gb, segs.data(), sb, cudaMemcpyHostToDevice, ctx->stream));
+  STITCH_CK(cudaMemcpyAsync(job->d_jpeg[3] + gb + sb, idx.data(), idx.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
   dir->groups = reinterpret_cast<const JmGroup *>(job->d_jpeg[3]);
   dir->segs = reinterpret_cast<const JmSeg *>(job->d_jpeg[3] + gb);
-  dir->n_groups = (uint32_t)groups.size();
+  dir->mrow_group = reinterpret_cast<const uint32_t *>(job->d_jpeg[3] + gb + sb);
+  dir->chunk_seg = dir->mrow_group + mrows;
   *ok = true;
   return STITCH_OK;
 }
@@ -1017,8 +1042,8 @@ static int encode_band_one_pass(stitch_job *job, const JpegGeom &g, uint32_t fir
     quant_tables((int)job->desc.jpeg_quality, ql, qc);
     for (int k = 0; k < 64; k++) {
       const uint32_t d0 = (uint32_t)ql[k_zigzag[k]] << 3, d1 = (uint32_t)qc[k_zigzag[k]] << 3;
-      q.half[0][k] = d0 >> 1; q.half[1][k] = d1 >> 1;
-      q.recip[0][k] = (uint32_t)(((1ull << 32) + d0 - 1) / d0); q.recip[1][k] = (uint32_t)(((1ull << 32) + d1 - 1) / d1);
+      q.hr[0][k] = make_uint2(d0 >> 1, (uint32_t)(((1ull << 32) + d0 - 1) / d0));
+      q.hr[1][k] = make_uint2(d1 >> 1, (uint32_t)(((1ull << 32) + d1 - 1) / d1));
     }
   }
   const size_t n_slots = (size_t)g.mrows * n_chunks;
