@@ -822,75 +822,132 @@ struct JmRowReader {
     pos = b + 32u;
     return out;
   }
+  // the next 128 bits: five loads and four funnel shifts where they lie inside one chunk (nearly always)
+  __device__ __forceinline__ void next4(uint32_t w[4]) {
+    const uint32_t lb = pos - off[c];
+    if (pos + 128u <= total && lb + 128u <= off[c + 1u] - off[c]) {
+      const uint32_t *p = row_words + (size_t)c * JM_CHUNK_WORDS + (lb >> 5);
+      const uint32_t sh = lb & 31u;
+      uint32_t v[5];
+#pragma unroll
+      for (int j = 0; j < 5; j++) v[j] = __byte_perm(__ldg(p + j), 0, 0x0123);   // p[4] is inside the slot (or the 16 spare bytes behind the last one); unused when sh == 0
+#pragma unroll
+      for (int j = 0; j < 4; j++) w[j] = __funnelshift_l(v[j + 1], v[j], sh);
+      pos += 128u;
+    } else {
+#pragma unroll
+      for (int j = 0; j < 4; j++) w[j] = next();
+    }
+  }
 };
 
+static constexpr uint32_t JM_MAX_ROUNDS = JM_MAX_CHUNKS * JM_CHUNK_BYTES / 4096u;   // rounds of 4096 stream bytes in a row
+
+// M2: per MCU row the size of its segment, and the 0xFF bytes of every round of 4096 bytes of it (so that M3 can do
+// the rounds independently of each other).
 __global__ void __launch_bounds__(256) jpeg_rowinfo_kernel(const uint32_t *chunk_words, const uint32_t *chunk_bits, uint32_t n_chunks,
-                                                           uint32_t n_rows, uint32_t *row_bits, uint32_t *row_ff) {
+                                                           uint32_t n_rows, uint32_t *row_bits, uint32_t *row_ff, uint32_t *round_ff) {
   __shared__ uint32_t off[JM_MAX_CHUNKS + 1];
-  __shared__ uint32_t s_cnt;
+  __shared__ uint32_t s_round[JM_MAX_ROUNDS];
+  __shared__ uint32_t s_tot[4];
   for (uint32_t r = blockIdx.x; r < n_rows; r += gridDim.x) {
     __syncthreads();
-    if (threadIdx.x == 0) s_cnt = 0;
+    if (threadIdx.x < JM_MAX_ROUNDS) s_round[threadIdx.x] = 0;
     jm_row_offsets(chunk_bits + (size_t)r * n_chunks, n_chunks, off);
     __syncthreads();
-    const uint32_t total = off[n_chunks];
+    const uint32_t total = off[n_chunks], n_rounds = (total + 32767u) >> 15;
     const uint32_t *rw = chunk_words + (size_t)r * n_chunks * JM_CHUNK_WORDS;
-    uint32_t c = 0;
     JmRowReader rd;
     rd.row_words = rw; rd.off = off; rd.n = n_chunks; rd.total = total;
-    for (uint32_t i = threadIdx.x * 4u; i * 32u < total; i += blockDim.x * 4u) {   // 16 bytes of the stream a thread
-      rd.seek(i * 32u);
+    for (uint32_t k = 0; k < n_rounds; k++) {   // 16 bytes of the stream a thread
+      const uint32_t i = k * 1024u + threadIdx.x * 4u;
+      uint32_t c = 0;
+      if (i * 32u < total) {
+        rd.seek(i * 32u);
+        uint32_t w[4];
+        rd.next4(w);
 #pragma unroll
-      for (int j = 0; j < 4; j++) c += (uint32_t)__popc(__vcmpeq4(rd.next(), 0xffffffffu)) >> 3;
+        for (int j = 0; j < 4; j++) c += (uint32_t)__popc(__vcmpeq4(w[j], 0xffffffffu)) >> 3;
+      }
+      c = __reduce_add_sync(0xffffffffu, c);
+      if ((threadIdx.x & 31u) == 0 && c) atomicAdd(&s_round[k], c);
     }
-    c = __reduce_add_sync(0xffffffffu, c);
-    if ((threadIdx.x & 31u) == 0 && c) atomicAdd(&s_cnt, c);
     __syncthreads();
-    if (threadIdx.x == 0) { row_bits[r] = total; row_ff[r] = s_cnt; }
+    uint32_t v = 0;
+    if (threadIdx.x < JM_MAX_ROUNDS) { v = s_round[threadIdx.x]; if (threadIdx.x < n_rounds) round_ff[(size_t)r * JM_MAX_ROUNDS + threadIdx.x] = v; }
+    if (threadIdx.x < 128u) {   // JM_MAX_ROUNDS == 128: four warps hold the counts
+      v = __reduce_add_sync(0xffffffffu, v);
+      if ((threadIdx.x & 31u) == 0) s_tot[threadIdx.x >> 5] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) { row_bits[r] = total; row_ff[r] = s_tot[0] + s_tot[1] + s_tot[2] + s_tot[3]; }
   }
 }
+static_assert(JM_MAX_ROUNDS == 128u, "jpeg_rowinfo_kernel adds the round counts up with four warps");
 
+// M3: a CTA takes rounds of 4096 stream bytes of an MCU row (blockIdx.y, then every gridDim.y-th): funnels the chunks
+// together, stuffs, writes.  The 0xFF bytes of the rounds before come from M2, so rounds do not wait for each other.
 __global__ void __launch_bounds__(256) jpeg_stuff_chunks_kernel(const uint32_t *chunk_words, const uint32_t *chunk_bits, uint32_t n_chunks,
-                                                                const unsigned long long *out_base, uint32_t n_rows,
+                                                                const unsigned long long *out_base, const uint32_t *round_ff, uint32_t n_rows,
                                                                 uint32_t first_mrow, uint32_t total_mrows, uint8_t *out) {
   __shared__ uint32_t off[JM_MAX_CHUNKS + 1];
   __shared__ uint32_t warp_tot[8];
-  __shared__ uint32_t s_ff;
+  __shared__ uint32_t s_before[4];
   __shared__ __align__(16) uint8_t sbuf[16 + 8192 + 16];   // one round's stuffed bytes, placed so that shared and global addresses agree mod 16
   const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
   for (uint32_t r = blockIdx.x; r < n_rows; r += gridDim.x) {
     __syncthreads();
-    if (threadIdx.x == 0) s_ff = 0;
     jm_row_offsets(chunk_bits + (size_t)r * n_chunks, n_chunks, off);
     __syncthreads();
-    const uint32_t total = off[n_chunks], n = (total + 7u) >> 3;
+    const uint32_t total = off[n_chunks], n = (total + 7u) >> 3, n_rounds = (total + 32767u) >> 15;
     const uint32_t *rw = chunk_words + (size_t)r * n_chunks * JM_CHUNK_WORDS;
     uint8_t *o = out + out_base[r];
     JmRowReader rd;
     rd.row_words = rw; rd.off = off; rd.n = n_chunks; rd.total = total;
-    for (uint32_t i0 = 0; i0 * 32u < total; i0 += 1024u) {   // a round: 4096 bytes of the stream, 16 a thread
-      const uint32_t i = i0 + threadIdx.x * 4u;
+    for (uint32_t k = blockIdx.y; k < n_rounds; k += gridDim.y) {
+      const uint32_t i0 = k * 1024u, i = i0 + threadIdx.x * 4u;   // the thread's 4 words: 16 bytes of the stream
       uint32_t w[4] = {0u, 0u, 0u, 0u}, cnt = 0;
       if (i * 32u < total) {
         rd.seek(i * 32u);
+        rd.next4(w);
 #pragma unroll
-        for (int j = 0; j < 4; j++) { w[j] = rd.next(); cnt += (uint32_t)__popc(__vcmpeq4(w[j], 0xffffffffu)) >> 3; }   // bytes past the end are 0
+        for (int j = 0; j < 4; j++) cnt += (uint32_t)__popc(__vcmpeq4(w[j], 0xffffffffu)) >> 3;   // bytes past the end are 0
       }
       uint32_t incl = cnt;
 #pragma unroll
-      for (int k = 1; k < 32; k <<= 1) { const uint32_t v = __shfl_up_sync(0xffffffffu, incl, k); if (lane >= (uint32_t)k) incl += v; }
+      for (int q = 1; q < 32; q <<= 1) { const uint32_t v = __shfl_up_sync(0xffffffffu, incl, q); if (lane >= (uint32_t)q) incl += v; }
       if (lane == 31u) warp_tot[warp] = incl;
+      if (threadIdx.x < 128u) {   // 0xFF bytes of the rounds before this one
+        uint32_t v = threadIdx.x < k ? round_ff[(size_t)r * JM_MAX_ROUNDS + threadIdx.x] : 0u;
+        v = __reduce_add_sync(0xffffffffu, v);
+        if (lane == 0u) s_before[warp] = v;
+      }
       __syncthreads();
-      uint32_t wbase = 0, round_ff = 0;
+      uint32_t wbase = 0, round_ff_here = 0;
 #pragma unroll
-      for (int k = 0; k < 8; k++) { const uint32_t v = warp_tot[k]; if ((uint32_t)k < warp) wbase += v; round_ff += v; }
-      uint8_t *dst = o + (size_t)i0 * 4u + s_ff;                        // where the round's bytes go
+      for (int q = 0; q < 8; q++) { const uint32_t v = warp_tot[q]; if ((uint32_t)q < warp) wbase += v; round_ff_here += v; }
+      const uint32_t before = s_before[0] + s_before[1] + s_before[2] + s_before[3];
+      uint8_t *dst = o + (size_t)i0 * 4u + before;                      // where the round's bytes go
       const uint32_t mis = (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 15u);
-      const uint32_t round_bytes = min(4096u, n - i0 * 4u) + round_ff;
+      const uint32_t round_bytes = min(4096u, n - i0 * 4u) + round_ff_here;
       uint32_t pos = mis + (i - i0) * 4u + wbase + incl - cnt;
-      if (cnt == 0u && i * 4u + 16u <= n && (pos & 3u) == 0u) {   // the usual case: 16 plain bytes, word-aligned in the buffer
+      if (cnt == 0u && i * 4u + 16u <= n) {   // 16 plain bytes (nearly every thread): words where the buffer allows, bytes at the ends
+        uint32_t v[4];
 #pragma unroll
-        for (int j = 0; j < 4; j++) *reinterpret_cast<uint32_t *>(&sbuf[pos + 4u * j]) = __byte_perm(w[j], 0, 0x0123);
+        for (int j = 0; j < 4; j++) v[j] = __byte_perm(w[j], 0, 0x0123);   // memory order
+        const uint32_t a = pos & 3u;
+        if (a == 0u) {
+#pragma unroll
+          for (int j = 0; j < 4; j++) *reinterpret_cast<uint32_t *>(&sbuf[pos + 4u * j]) = v[j];
+        } else {
+          const uint32_t head = 4u - a, sh = head * 8u;   // head bytes of v[0], then three whole words, then a bytes of v[3]
+#pragma unroll
+          for (uint32_t bb = 0; bb < 3u; bb++) if (bb < head) sbuf[pos + bb] = (uint8_t)(v[0] >> (8u * bb));
+#pragma unroll
+          for (int j = 0; j < 3; j++) *reinterpret_cast<uint32_t *>(&sbuf[pos + head + 4u * j]) = __funnelshift_r(v[j], v[j + 1], sh);
+#pragma unroll
+          for (uint32_t bb = 0; bb < 3u; bb++) if (bb < a) sbuf[pos + 16u - a + bb] = (uint8_t)(v[3] >> (sh + 8u * bb));
+        }
       } else {
 #pragma unroll
         for (int j = 0; j < 16; j++) {
@@ -910,13 +967,11 @@ __global__ void __launch_bounds__(256) jpeg_stuff_chunks_kernel(const uint32_t *
           for (uint32_t e = max(q, mis); e < min(q + 16u, mis + round_bytes); e++) dst[e - mis] = sbuf[e];
         }
       }
+      if (k + 1u == n_rounds && threadIdx.x == 0 && first_mrow + r + 1u < total_mrows) {   // the last round ends the segment: RSTm
+        dst[round_bytes] = 0xFF;
+        dst[round_bytes + 1u] = (uint8_t)(0xD0u + ((first_mrow + r) & 7u));
+      }
       __syncthreads();
-      if (threadIdx.x == 0) s_ff += round_ff;
-    }
-    __syncthreads();
-    if (threadIdx.x == 0 && first_mrow + r + 1u < total_mrows) {
-      o[n + s_ff] = 0xFF;
-      o[n + s_ff + 1] = (uint8_t)(0xD0u + ((first_mrow + r) & 7u));
     }
   }
 }
@@ -1054,6 +1109,8 @@ static int encode_band_one_pass(stitch_job *job, const JpegGeom &g, uint32_t fir
   if (!job->h_jpeg_totals) STITCH_CK(cudaHostAlloc((void **)&job->h_jpeg_totals, 32, cudaHostAllocDefault));
   uint32_t *chunk_words = reinterpret_cast<uint32_t *>(job->d_jpeg[0]);
   uint32_t *chunk_bits = reinterpret_cast<uint32_t *>(job->d_jpeg[1]);
+  if ((rc = stitch_ensure_buffer(ctx, &job->d_jpeg[4], &job->jpeg_cap[4], (size_t)g.mrows * JM_MAX_ROUNDS * 4))) return rc;
+  uint32_t *round_ff = reinterpret_cast<uint32_t *>(job->d_jpeg[4]);
   uint32_t *row_bits = reinterpret_cast<uint32_t *>(job->d_jpeg[2]);
   uint32_t *row_ff = row_bits + rows_pad;
   unsigned long long *row_base = reinterpret_cast<unsigned long long *>(row_ff + rows_pad);
@@ -1066,7 +1123,7 @@ static int encode_band_one_pass(stitch_job *job, const JpegGeom &g, uint32_t fir
     STITCH_CK(cudaGetLastError());
   }
   const uint32_t row_grid = g.mrows < 148u * 8u ? g.mrows : 148u * 8u;
-  jpeg_rowinfo_kernel<<<row_grid, 256, 0, ctx->stream>>>(chunk_words, chunk_bits, n_chunks, g.mrows, row_bits, row_ff);
+  jpeg_rowinfo_kernel<<<row_grid, 256, 0, ctx->stream>>>(chunk_words, chunk_bits, n_chunks, g.mrows, row_bits, row_ff, round_ff);
   STITCH_CK(cudaGetLastError());
   jpeg_rowscan_kernel<<<1, 1024, 0, ctx->stream>>>(row_bits, row_ff, g.mrows, first_mrow, total_mrows, 1, out_base, totals);
   STITCH_CK(cudaGetLastError());
@@ -1076,7 +1133,13 @@ static int encode_band_one_pass(stitch_job *job, const JpegGeom &g, uint32_t fir
   if (job->h_jpeg_totals[2]) { *overflow = true; return STITCH_OK; }
   const size_t n_out = (size_t)job->h_jpeg_totals[1];
   if ((rc = stitch_ensure_buffer(ctx, &job->d_out, &job->out_bytes, n_out + 64))) return rc;
-  jpeg_stuff_chunks_kernel<<<row_grid, 256, 0, ctx->stream>>>(chunk_words, chunk_bits, n_chunks, out_base, g.mrows, first_mrow, total_mrows, job->d_out);
+  {  // rounds of 4096 bytes are independent: enough CTAs per row that the device is full whatever the band's height
+    const uint32_t max_rounds = (n_chunks * JM_CHUNK_BYTES + 4095u) / 4096u;
+    uint32_t per_row = (4u * 148u * 8u + g.mrows - 1u) / g.mrows;
+    per_row = per_row < 1u ? 1u : per_row > max_rounds ? max_rounds : per_row > 8u ? 8u : per_row;
+    dim3 grid(g.mrows < 16384u ? g.mrows : 16384u, per_row);
+    jpeg_stuff_chunks_kernel<<<grid, 256, 0, ctx->stream>>>(chunk_words, chunk_bits, n_chunks, out_base, round_ff, g.mrows, first_mrow, total_mrows, job->d_out);
+  }
   STITCH_CK(cudaGetLastError());
   if (launches) *launches += 1;
   *out_bytes = n_out;
