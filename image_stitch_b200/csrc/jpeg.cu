@@ -931,7 +931,9 @@ __global__ void __launch_bounds__(256) jpeg_stuff_chunks_kernel(const uint32_t *
       const uint32_t mis = (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 15u);
       const uint32_t round_bytes = min(4096u, n - i0 * 4u) + round_ff_here;
       uint32_t pos = mis + (i - i0) * 4u + wbase + incl - cnt;
-      if (cnt == 0u && i * 4u + 16u <= n) {   // 16 plain bytes (nearly every thread): words where the buffer allows, bytes at the ends
+      if (i * 4u + 16u <= n) {
+        // The thread's 16 bytes as they are, at its place: words where the buffer allows, bytes at the two ends.  A
+        // thread with 0xFF bytes owns cnt more bytes behind them and puts things right below.
         uint32_t v[4];
 #pragma unroll
         for (int j = 0; j < 4; j++) v[j] = __byte_perm(w[j], 0, 0x0123);   // memory order
@@ -948,14 +950,33 @@ __global__ void __launch_bounds__(256) jpeg_stuff_chunks_kernel(const uint32_t *
 #pragma unroll
           for (uint32_t bb = 0; bb < 3u; bb++) if (bb < a) sbuf[pos + 16u - a + bb] = (uint8_t)(v[3] >> (sh + 8u * bb));
         }
-      } else {
+        if (cnt) {   // from the first 0xFF on: a zero behind each, everything after it moves up
+          uint32_t zc = 0;
+#pragma unroll 1
+          for (uint32_t j = 0; j < 4u; j++) {
+            const uint32_t wj = j == 0u ? w[0] : j == 1u ? w[1] : j == 2u ? w[2] : w[3];
+            if (__vcmpeq4(wj, 0xffffffffu) == 0u) {
+              if (zc) {
 #pragma unroll
-        for (int j = 0; j < 16; j++) {
-          if (i * 4u + j < n) {
-            const uint32_t byte = (w[j >> 2] >> (24 - 8 * (j & 3))) & 0xffu;
-            sbuf[pos++] = (uint8_t)byte;
-            if (byte == 0xffu) sbuf[pos++] = 0;
+                for (uint32_t bb = 0; bb < 4u; bb++) sbuf[pos + 4u * j + bb + zc] = (uint8_t)(wj >> (24u - 8u * bb));
+              }
+            } else {
+#pragma unroll
+              for (uint32_t bb = 0; bb < 4u; bb++) {
+                const uint32_t byte = (wj >> (24u - 8u * bb)) & 0xffu;
+                sbuf[pos + 4u * j + bb + zc] = (uint8_t)byte;
+                if (byte == 0xffu) { zc++; sbuf[pos + 4u * j + bb + zc] = 0; }
+              }
+            }
           }
+        }
+      } else if (i * 4u < n) {   // the row's last bytes
+#pragma unroll 1
+        for (uint32_t jb = 0; jb < 16u && i * 4u + jb < n; jb++) {
+          const uint32_t wj = (jb >> 2) == 0u ? w[0] : (jb >> 2) == 1u ? w[1] : (jb >> 2) == 2u ? w[2] : w[3];
+          const uint32_t byte = (wj >> (24u - 8u * (jb & 3u))) & 0xffu;
+          sbuf[pos++] = (uint8_t)byte;
+          if (byte == 0xffu) sbuf[pos++] = 0;
         }
       }
       __syncthreads();
