@@ -1163,38 +1163,79 @@ static int run_band_impl(stitch_job *job, uint32_t y0, uint32_t y1, uint8_t *out
       break;
     }
   if (jpeg) {
-    if ((rc = decode_tiles(job, 0, &launches, y0, y1))) return rc;
-    CK(cudaEventRecord(ctx->ev[2], ctx->stream));
-    if (!job->finalized && (rc = finalize_job(job))) return rc;
-    // an exact mosaic of RGBA8 tiles is coded straight from the tiles (jpeg.cu); anything else is composited
-    // into HBM first, then kernel (d) reads the canvas; MCU rows are independent entropy segments
-    bool need_canvas = false;
-    if ((rc = stitch_jpeg_encode_band(job, y0, y1, nullptr, 0, &jpeg_bytes, &launches, &need_canvas))) return rc;
-    if (need_canvas) {
-      job->canvas_pitch = pitch16;
-      if ((rc = ensure_buffer(ctx, &job->d_canvas, &job->canvas_bytes, pitch16 * (size_t)n_rows))) return rc;
-      {  // the quad compositor of fused.cu (16-byte loads inside a tile) feeding the canvas
-        FusedParams fq{};
-        fq.tiles = job->d_tiles; fq.bin_start = job->d_bin_start; fq.bin_tiles = job->d_bin_tiles;
-        fq.bins_x = job->bins_x; fq.canvas_w = jd.canvas_w; fq.alpha_blend = jd.alpha_blend;
-        bg_words(jd, fq.bg_lo, fq.bg_hi);
-        if (job->strip_ok) CK(launch_compose_plan(strip_params(job), false, job->d_canvas, pitch16, y0, y1, ctx->stream));
-        else CK(launch_compose_canvas(fq, false, job->d_canvas, pitch16, y0, y1, ctx->stream));
-      }
-      launches += 1;
-      if ((rc = stitch_jpeg_encode_band(job, y0, y1, job->d_canvas, pitch16, &jpeg_bytes, &launches, nullptr))) return rc;
+    // With a host destination the band is coded in sub-bands of about 512 MB of pixels: the bytes of sub-band k go
+    // down the bus (two device buffers take turns) while sub-band k+1 is coded and while later tiles still come up.
+    // (tools/jpeg_d2h.py: 32768^2 with its 285 MB downloaded 11.8 ms in one piece, 7.6 ms at 512 MB, 7.9 at 256 MB or
+    // 1 GB, 11.0 at 64 MB -- a sub-band costs about 70 us of host work and one synchronisation)
+    uint32_t chunk = n_rows;
+    if (out) {
+      size_t chunk_bytes = (size_t)512 << 20;
+      if (const char *e = getenv("STITCH_JPEG_CHUNK_BYTES")) chunk_bytes = std::max<size_t>(1, strtoull(e, nullptr, 10));  // tuning / tests
+      const size_t want = chunk_bytes / std::max<size_t>(row_bytes, 1);
+      chunk = (uint32_t)std::min<size_t>(n_rows, std::max<size_t>(8, want / 8 * 8));
     }
-    job->out_pitch = jpeg_bytes; job->out_lead = 0; job->out_row_bytes = jpeg_bytes;
+    bool first = true;
+    uint32_t n_sub = 0;
+    size_t total = 0;
+    for (uint32_t a = y0; a < y1; a += chunk) {
+      const uint32_t b = (uint32_t)std::min<uint64_t>((uint64_t)a + chunk, y1);
+      if ((rc = decode_tiles(job, 0, &launches, a, b))) return rc;
+      if (first) CK(cudaEventRecord(ctx->ev[2], ctx->stream));
+      first = false;
+      if (!job->finalized && (rc = finalize_job(job))) return rc;
+      const uint32_t k = n_sub++ & 1u;
+      if (out) {   // the coder writes into job->d_out: lend it the buffer whose turn it is
+        if (job->ev_pack[k]) CK(cudaStreamWaitEvent(ctx->stream, job->ev_pack[k], 0));  // its last download is over
+        std::swap(job->d_out, job->d_pack[k]);
+        std::swap(job->out_bytes, job->pack_bytes[k]);
+      }
+      // an exact mosaic of RGBA8 tiles is coded straight from the tiles (jpeg.cu); anything else is composited
+      // into HBM first, then kernel (d) reads the canvas; MCU rows are independent entropy segments
+      size_t sub_bytes = 0;
+      bool need_canvas = false;
+      rc = stitch_jpeg_encode_band(job, a, b, nullptr, 0, &sub_bytes, &launches, &need_canvas);
+      if (!rc && need_canvas) {
+        job->canvas_pitch = pitch16;
+        rc = ensure_buffer(ctx, &job->d_canvas, &job->canvas_bytes, pitch16 * (size_t)(b - a));
+        if (!rc) {  // the quad compositor of fused.cu (16-byte loads inside a tile) feeding the canvas
+          FusedParams fq{};
+          fq.tiles = job->d_tiles; fq.bin_start = job->d_bin_start; fq.bin_tiles = job->d_bin_tiles;
+          fq.bins_x = job->bins_x; fq.canvas_w = jd.canvas_w; fq.alpha_blend = jd.alpha_blend;
+          bg_words(jd, fq.bg_lo, fq.bg_hi);
+          cudaError_t ce = job->strip_ok ? launch_compose_plan(strip_params(job), false, job->d_canvas, pitch16, a, b, ctx->stream)
+                                         : launch_compose_canvas(fq, false, job->d_canvas, pitch16, a, b, ctx->stream);
+          if (ce != cudaSuccess) rc = fail(ctx, STITCH_E_CUDA, "compositor launch failed: %s", cudaGetErrorString(ce));
+          launches += 1;
+        }
+        if (!rc) rc = stitch_jpeg_encode_band(job, a, b, job->d_canvas, pitch16, &sub_bytes, &launches, nullptr);
+      }
+      if (out) {
+        std::swap(job->d_out, job->d_pack[k]);
+        std::swap(job->out_bytes, job->pack_bytes[k]);
+      }
+      if (rc) return rc;
+      if (out) {
+        const size_t need = sizeof(stitch_jpeg_band_info) + total + sub_bytes;
+        if (cap < need) return fail(ctx, STITCH_E_CAPACITY, "output buffer too small: need %zu bytes", need);
+        CK(cudaEventRecord(ctx->ev_chunk, ctx->stream));
+        CK(cudaStreamWaitEvent(ctx->down, ctx->ev_chunk, 0));
+        if (sub_bytes && (rc = download_pieces(job, out + sizeof(stitch_jpeg_band_info) + total, job->d_pack[k], sub_bytes))) return rc;
+        if (!job->ev_pack[k]) CK(cudaEventCreateWithFlags(&job->ev_pack[k], cudaEventDisableTiming));
+        CK(cudaEventRecord(job->ev_pack[k], ctx->down));
+      }
+      total += sub_bytes;
+    }
+    jpeg_bytes = total;
+    job->out_pitch = jpeg_bytes; job->out_lead = 0; job->out_row_bytes = jpeg_bytes;   // without a host destination: the one sub-band, in d_out
     CK(cudaEventRecord(ctx->ev[3], ctx->stream));
     if (out) {
-      const size_t need = sizeof(stitch_jpeg_band_info) + jpeg_bytes;
-      if (cap < need) return fail(ctx, STITCH_E_CAPACITY, "output buffer too small: need %zu bytes", need);
+      CK(cudaEventRecord(ctx->ev_down, ctx->down));
+      CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_down, 0));
       stitch_jpeg_band_info info;
       memset(&info, 0, sizeof info);
       info.n_bits = (uint64_t)jpeg_bytes * 8;  // every MCU row restarts the DC predictors: last_dc stays 0
       memcpy(out, &info, sizeof info);
-      if (jpeg_bytes) CK(cudaMemcpyAsync(out + sizeof info, job->d_out, jpeg_bytes, cudaMemcpyDeviceToHost, ctx->stream));
-      if (out_len) *out_len = need;
+      if (out_len) *out_len = sizeof info + jpeg_bytes;
     }
   } else {
     if (png) { job->out_pitch = 16 + pitch16; job->out_lead = 15; }

@@ -164,6 +164,19 @@ def test_bands_equal_whole(ctx):
     assert parts == whole == orc.jpeg_encode_rows(rgba, w, h, 0, h, 90)
 
 
+@pytest.mark.parametrize("chunk_rows", [8, 24, 64])
+def test_band_downloaded_in_sub_bands(ctx, monkeypatch, chunk_rows):
+    """With a host destination a band is coded and downloaded in sub-bands (two device buffers taking turns); the bytes
+    are those of the band coded at once."""
+    rng = np.random.default_rng(6)
+    w, h = 1300, 203
+    rgba = _photo(rng, w, h).reshape(h, w * 4)
+    want = orc.jpeg_encode_rows(rgba, w, h, 0, h, 80)
+    monkeypatch.setenv("STITCH_JPEG_CHUNK_BYTES", str(w * 4 * chunk_rows))
+    assert _gpu_entropy(ctx, rgba, w, h, 80, [(0, h)]) == want
+    assert _gpu_entropy(ctx, rgba, w, h, 80, [(0, 104), (104, h)]) == want
+
+
 def test_band_alignment_is_checked(ctx):
     job = _native.Job(ctx, 16, 32, 8, _native.OUT_JPEG_ENTROPY, False, bytes(4), jpeg_quality=85)
     job.add_tile(bytes(16 * 32 * 4), width=16, height=32, bit_depth=8, color_type=6, filtered=0)
