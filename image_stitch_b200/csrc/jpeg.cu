@@ -513,9 +513,9 @@ __global__ void __launch_bounds__(256) jpeg_stuff_kernel(const uint8_t *ubuf, co
 // A thread holds JM_WORDS words of code for its MCU and a chunk JM_CHUNK_BYTES; content that needs more (noise
 // at quality 100) raises a flag and the band is done again by the J1..J7 route above.
 static constexpr int JM_MCUS = 128;
-static constexpr int JM_WORDS = 36;                       // 1152 bits per MCU: 6 bits per pixel
+static constexpr int JM_WORDS = 40;                       // 1280 bits per MCU (20 per pixel); what four CTAs per SM leave room for
 static constexpr int JM_PX = JM_MCUS * 8 + 8;             // staged pixels per row: the MCU on the left, then the chunk's
-static constexpr uint32_t JM_CHUNK_BYTES = 8192;          // 4 bits per pixel on average over a chunk
+static constexpr uint32_t JM_CHUNK_BYTES = 8192;          // 8 bits per pixel on average over a chunk
 static constexpr uint32_t JM_CHUNK_WORDS = JM_CHUNK_BYTES / 4;
 
 struct JpegQuant {   // zig-zag order; [0] luminance, [1] chrominance; divisor = quantval << 3 as in c_q8
