@@ -111,6 +111,7 @@ struct stitch_job {
   size_t jpeg_cap[5] = {0, 0, 0, 0, 0};
   unsigned long long *h_jpeg_totals = nullptr;  // pinned: [0] unstuffed bytes, [1] output bytes
   int jpeg_tables_quality = -1;
+  uint32_t jpeg_skip_bands = 0, jpeg_overflow_streak = 0;   // jpeg.cu: bands that skip the one-pass route after overflows
   bool jpeg_overflowed = false;                 // jpeg.cu: the try without a canvas overflowed a chunk
   bool jpeg_huff_ready = false;                 // jpeg.cu: the Annex K tables are in constant memory, the MCU kernel's shared memory is opted in
   // JPEG tiles (jpeg_decode.cu): one pinned status word per tile, written by the tile's last decode kernel;

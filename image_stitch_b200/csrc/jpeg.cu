@@ -1181,17 +1181,26 @@ int stitch_jpeg_encode_band(stitch_job *job, uint32_t y0, uint32_t y1, const uin
   int one_pass = 1;
   if (const char *e = getenv("STITCH_JPEG_ONE_PASS")) one_pass = atoi(e);
   if (need_canvas) *need_canvas = false;
+  // A band that overflowed the one-pass route has cost its MCU kernel for nothing, and busy content comes in runs:
+  // after an overflow the next 1, 2, 4, 8 bands (doubling while it keeps happening) go straight to J1..J7.
+  const bool backing_off = one_pass == 1 && job->jpeg_skip_bands > 0;
   if (!canvas) {   // first try: the tiles themselves, if the band is an exact mosaic of them
     JmDirect dir{};
     bool ok = false;
-    if (one_pass && (rc = jpeg_direct_plan(job, y0, y1, &dir, &ok))) return rc;
+    if (one_pass && !backing_off && (rc = jpeg_direct_plan(job, y0, y1, &dir, &ok))) return rc;
     bool overflow = false;
     if (ok && (rc = encode_band_one_pass(job, g, first_mrow, total_mrows, nullptr, 0, dir, out_bytes, launches, &overflow))) return rc;
     if (!ok || overflow) *need_canvas = true;
     job->jpeg_overflowed = overflow;   // the canvas would overflow the same chunks: the second call goes straight to J1..J7
+    if (ok && !overflow) job->jpeg_overflow_streak = 0;
     return STITCH_OK;
   }
-  const bool known_overflow = job->jpeg_overflowed;
+  const bool known_overflow = job->jpeg_overflowed || backing_off;
+  if (backing_off) job->jpeg_skip_bands--;
+  if (job->jpeg_overflowed) {
+    job->jpeg_overflow_streak = job->jpeg_overflow_streak < 3u ? job->jpeg_overflow_streak + 1u : 3u;
+    job->jpeg_skip_bands = 1u << job->jpeg_overflow_streak >> 1;   // 1, 2, 4
+  }
   job->jpeg_overflowed = false;
   if (known_overflow && one_pass == 2)
     return stitch_fail(ctx, STITCH_E_CAPACITY, "JPEG band [%u,%u): more than %d bits in an MCU or %u bytes in a chunk of %d MCUs (STITCH_JPEG_ONE_PASS=2)",
@@ -1199,7 +1208,9 @@ int stitch_jpeg_encode_band(stitch_job *job, uint32_t y0, uint32_t y1, const uin
   if (one_pass && !known_overflow) {
     bool overflow = false;
     if ((rc = encode_band_one_pass(job, g, first_mrow, total_mrows, canvas, canvas_pitch, JmDirect{}, out_bytes, launches, &overflow))) return rc;
-    if (!overflow) return STITCH_OK;
+    if (!overflow) { job->jpeg_overflow_streak = 0; return STITCH_OK; }
+    job->jpeg_overflow_streak = job->jpeg_overflow_streak < 3u ? job->jpeg_overflow_streak + 1u : 3u;
+    job->jpeg_skip_bands = 1u << job->jpeg_overflow_streak >> 1;
     if (one_pass == 2) {
       return stitch_fail(ctx, STITCH_E_CAPACITY, "JPEG band [%u,%u): more than %d bits in an MCU or %u bytes in a chunk of %d MCUs (STITCH_JPEG_ONE_PASS=2)",
                          y0, y1, JM_WORDS * 32, JM_CHUNK_BYTES, JM_MCUS);

@@ -145,6 +145,18 @@ def test_mosaics_read_in_place_or_through_a_canvas(ctx, monkeypatch, layout):
     assert _mosaic_entropy(ctx, tiles, w, h, 85, bands) == want
 
 
+def test_bands_after_an_overflow_skip_the_one_pass_route(ctx):
+    """After a band the MCU kernel could not hold, the next bands go straight to J1..J7 (1, 2, 4 of them while it
+    keeps happening), then the one-pass route is tried again: whatever the route, the oracle's bytes."""
+    rng = np.random.default_rng(14)
+    w, h = 520, 16 * 9
+    rgba = _photo(rng, w, h).reshape(h, w * 4).copy()
+    for k in (0, 1, 4):   # noisy bands
+        rgba[16 * k:16 * k + 16] = rng.integers(0, 256, size=(16, w * 4), dtype=np.uint8)
+    want = orc.jpeg_encode_rows(rgba, w, h, 0, h, 97)
+    assert _gpu_entropy(ctx, rgba, w, h, 97, [(16 * k, 16 * k + 16) for k in range(9)]) == want
+
+
 def test_random_noise_many_ff_bytes(ctx):
     """Noise at quality 100 produces long codes and many 0xFF bytes: stuffing and worst-case lengths."""
     rng = np.random.default_rng(11)

@@ -32,6 +32,14 @@ for name, extra in (("device inflate + deflate", {"device_inflate": True, "devic
         best = min(best, time.perf_counter() - t0)
     results[name] = out
     print(f"{name}: {best*1e3:.0f} ms, {len(out)/1e6:.1f} MB out, {G*T*G*T/best/1e6:.0f} MPix/s")
+if "--jpeg" in sys.argv:   # the same files to one JPEG (q = 90): the device inflates, unfilters and codes; the host splices the bands
+    for name, extra in (("device inflate", {"device_inflate": True}),):
+        best = 1e9
+        for rep in range(3):
+            t0 = time.perf_counter()
+            jpg = stitch.concat_to_buffer(dict({"inputs": inputs, "layout": {"columns": G}, "output_format": "jpeg", "jpeg_quality": 90}, **extra))
+            best = min(best, time.perf_counter() - t0)
+        print(f"JPEG, {name}: {best*1e3:.0f} ms, {len(jpg)/1e6:.1f} MB out, {G*T*G*T/best/1e6:.0f} MPix/s")
 rows = [read_png(o)[1] for o in results.values()]
 assert all(r == rows[0] for r in rows), "outputs differ"
 print("all outputs decode to the same filtered rows")
