@@ -99,10 +99,11 @@ def _mosaic_entropy(ctx, tiles, w, h, quality, bands):
     sp = JpegBandSplicer()
     out = b""
     try:
-        for k, (px, x, y) in enumerate(tiles):
+        for k, (px, x, y, *clip) in enumerate(tiles):
             th, tw = px.shape[:2]
+            extra = dict(zip(("src_off_x", "src_off_y", "vis_w", "vis_h"), clip[0])) if clip else {}
             job.add_tile(px.tobytes(), width=tw, height=th, bit_depth=8, color_type=6, interlace=0, filtered=0,
-                         dst_x=x, dst_y=y, z_index=0, image_idx=k)
+                         dst_x=x, dst_y=y, z_index=0, image_idx=k, **extra)
         for a, b in bands:
             data, _ = job.run_band(a, b)
             out += sp.push(data)
@@ -111,7 +112,7 @@ def _mosaic_entropy(ctx, tiles, w, h, quality, bands):
     return out
 
 
-@pytest.mark.parametrize("layout", ["grid", "tall_and_short", "gap", "overlap", "odd_x", "ragged_bottom"])
+@pytest.mark.parametrize("layout", ["grid", "tall_and_short", "gap", "overlap", "odd_x", "ragged_bottom", "clipped"])
 def test_mosaics_read_in_place_or_through_a_canvas(ctx, monkeypatch, layout):
     """An exact mosaic of RGBA8 tiles is coded straight from the tiles (no canvas); a gap, an overlap or a tile at an
     odd column is not one and goes through the compositor.  Either way: the oracle's bytes, and the same bytes
@@ -130,11 +131,16 @@ def test_mosaics_read_in_place_or_through_a_canvas(ctx, monkeypatch, layout):
         tiles = [(t(1200, 96), 0, 0), (t(1152, 96), 1152, 0)]
     elif layout == "odd_x":
         tiles = [(t(1150, 96), 0, 0), (t(1154, 96), 1150, 0)]
+    elif layout == "clipped":   # tiles larger than what shows of them (ClippedImageInfo.sourceOffsetX/Y), still an exact mosaic
+        tiles = [(t(1200, 120), 0, 0, (16, 24, 1152, 96)), (t(1160, 96), 1152, 0, (8, 0, 1152, 96))]
     else:
         h = 93
         tiles = [(t(1152, 48), 0, 0), (t(1152, 48), 1152, 0), (t(2304, 45), 0, 48)]
     canvas = np.zeros((h, w, 4), np.uint8)
-    for px, x, y in tiles:
+    for px, x, y, *clip in tiles:
+        if clip:
+            ox, oy, vw, vh = clip[0]
+            px = px[oy:oy + vh, ox:ox + vw]
         canvas[y:y + px.shape[0], x:x + px.shape[1]] = px[:h - y]
     canvas = canvas.reshape(h, w * 4)
     want = orc.jpeg_encode_rows(canvas, w, h, 0, h, 85)
