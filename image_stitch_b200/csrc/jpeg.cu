@@ -1048,6 +1048,7 @@ static int jpeg_direct_plan(stitch_job *job, uint32_t y0, uint32_t y1, JmDirect 
   }
   std::sort(cuts.begin(), cuts.end());
   cuts.erase(std::unique(cuts.begin(), cuts.end()), cuts.end());
+  if (cuts.size() * rs.size() > ((size_t)4 << 20)) return STITCH_OK;   // the loop below would cost more host time than the compositor saves
   std::vector<JmGroup> groups;
   std::vector<JmSeg> segs;
   std::vector<const Rect *> row;
