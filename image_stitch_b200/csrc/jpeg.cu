@@ -24,6 +24,7 @@
 #include "job.h"
 
 #include <algorithm>
+#include <cstdio>
 #include <cstdlib>
 #include <vector>
 
@@ -518,6 +519,10 @@ static constexpr int JM_PX = JM_MCUS * 8 + 8;             // staged pixels per r
 static constexpr uint32_t JM_CHUNK_BYTES = 8192;          // 8 bits per pixel on average over a chunk
 static constexpr uint32_t JM_CHUNK_WORDS = JM_CHUNK_BYTES / 4;
 
+__constant__ uint8_t c_zigzag_dev[64] = {0,  1,  8,  16, 9,  2,  3,  10, 17, 24, 32, 25, 18, 11, 4,  5,  12, 19, 26, 33, 40, 48,
+                                         41, 34, 27, 20, 13, 6,  7,  14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23,
+                                         30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
+
 struct JpegQuant {   // zig-zag order; [0] luminance, [1] chrominance; divisor = quantval << 3 as in c_q8
   uint2 hr[2][64];         // x: divisor / 2, y: ceil(2^32 / divisor) -- one 64-bit constant load for the pair
 };
@@ -575,9 +580,74 @@ struct JmBits {
   }
 };
 
+// An MCU whose code does not fit its column (the corner where four tiles meet inside a block; a patch of noise): the
+// thread codes it again, from its staged pixels, into a slot of worst-case size in HBM -- rolled loops, the block in
+// local memory, a step per coefficient: slow, and rare.  Returns the length in bits.
+static constexpr uint32_t JM_ESC_WORDS = 160;     // 3 x (20 bits of DC + 63 x 26 bits of AC) = 4974 bits
+static constexpr uint32_t JM_ESC_SLOTS = 16384;   // more MCUs than that in a band: the band goes to the J1..J7 route
+__device__ __noinline__ uint32_t jm_mcu_slow(const JmSmem &sm, const JpegQuant &q, const uint32_t t, const bool has_left, uint32_t *esc) {
+  unsigned long long acc = 0;
+  uint32_t nacc = 0, wr = 0;
+  auto put = [&](uint32_t code, uint32_t size) {
+    acc = (acc << size) | code;
+    nacc += size;
+    if (nacc >= 32u) { nacc -= 32u; esc[wr++] = (uint32_t)(acc >> nacc); }
+  };
+  for (uint32_t comp = 0; comp < 3u; comp++) {
+    const uint32_t cls = comp ? 1u : 0u;
+    const uint32_t a1 = comp == 1u ? JM_CB1 : JM_CR1, a2 = comp == 1u ? JM_CB2 : JM_CR2;
+    int d[64];
+    int pred = 0;
+    if (has_left) {   // the quantised DC of the MCU on the left: the sum of its samples (staged 8 pixels before this thread's)
+      int s2 = 0;
+#pragma unroll 1
+      for (uint32_t i = 0; i < 64u; i++) {
+        const uint32_t px = *reinterpret_cast<const uint32_t *>(&sm.px[i >> 3][t * 32u + (i & 7u) * 4u]);
+        s2 += comp == 0u ? jm_y(px) : jm_c(px, a1, a2);
+      }
+      const int qa = (int)__umulhi((uint32_t)abs(s2) + q.hr[cls][0].x, q.hr[cls][0].y);
+      pred = s2 < 0 ? -qa : qa;
+    }
+#pragma unroll 1
+    for (uint32_t i = 0; i < 64u; i++) {
+      const uint32_t px = *reinterpret_cast<const uint32_t *>(&sm.px[i >> 3][32u + t * 32u + (i & 7u) * 4u]);
+      d[i] = comp == 0u ? jm_y(px) : jm_c(px, a1, a2);
+    }
+#pragma unroll 1
+    for (int i = 0; i < 8; i++)
+      fdct_1d(d[8 * i], d[8 * i + 1], d[8 * i + 2], d[8 * i + 3], d[8 * i + 4], d[8 * i + 5], d[8 * i + 6], d[8 * i + 7], true);
+#pragma unroll 1
+    for (int i = 0; i < 8; i++)
+      fdct_1d(d[i], d[8 + i], d[16 + i], d[24 + i], d[32 + i], d[40 + i], d[48 + i], d[56 + i], false);
+    const uint32_t *dct = sm.hs.dc[cls], *act = sm.hs.ac[cls];
+    {
+      const int qa = (int)__umulhi((uint32_t)abs(d[0]) + q.hr[cls][0].x, q.hr[cls][0].y);
+      const int diff = (d[0] < 0 ? -qa : qa) - pred;
+      const uint32_t a = (uint32_t)abs(diff), sz = 32u - (uint32_t)__clz((int)a), e = dct[sz];
+      put((e >> 6) | ((a ^ (uint32_t)(diff >> 31)) & ((1u << sz) - 1u)), e & 63u);
+    }
+    int prev = 0;
+#pragma unroll 1
+    for (int k = 1; k < 64; k++) {
+      const int c = d[c_zigzag_dev[k]];
+      const uint32_t a = __umulhi((uint32_t)abs(c) + q.hr[cls][k].x, q.hr[cls][k].y);
+      if (a == 0u) continue;
+      uint32_t run = (uint32_t)(k - 1 - prev);
+      prev = k;
+      const uint32_t z = act[0xF0];
+      while (run > 15u) { put(z >> 6, z & 63u); run -= 16u; }
+      const uint32_t sz = 32u - (uint32_t)__clz((int)a), e = act[(run << 4) | sz];
+      put((e >> 6) | ((a ^ (uint32_t)(c >> 31)) & ((1u << sz) - 1u)), e & 63u);
+    }
+    if (prev != 63) { const uint32_t e = act[0]; put(e >> 6, e & 63u); }
+  }
+  if (nacc) esc[wr] = (uint32_t)acc << (32u - nacc);
+  return wr * 32u + nacc;
+}
+
 __global__ void __launch_bounds__(JM_MCUS, 4) jpeg_mcu_kernel(const uint8_t *canvas, size_t pitch, JpegGeom g,
                                                               const __grid_constant__ JpegQuant q, const JmDirect dir, uint32_t *chunk_words,
-                                                              uint32_t *chunk_bits, unsigned long long *overflow) {
+                                                              uint32_t *chunk_bits, uint32_t *esc_pool, unsigned long long *overflow) {
   extern __shared__ __align__(16) uint8_t jm_raw[];
   JmSmem &sm = *reinterpret_cast<JmSmem *>(jm_raw);
   load_huff_sized(sm.hs);
@@ -595,15 +665,16 @@ __global__ void __launch_bounds__(JM_MCUS, 4) jpeg_mcu_kernel(const uint8_t *can
     // two lanes of warp 0.  Rows past the bottom edge repeat the last image row.
     const uint32_t yf = g.y0 + mr * 8u, rows_here = min(8u, g.height - yf);
     JmGroup grp;
-    uint32_t si0 = 0;
+    uint32_t si0 = 0, gi = 0;
     if (dir.groups) {
-      const uint32_t gi = __ldg(dir.mrow_group + mr);
+      gi = __ldg(dir.mrow_group + mr);
       grp = dir.groups[gi];
       si0 = __ldg(dir.chunk_seg + (size_t)gi * gridDim.x + blockIdx.x);
     }
     auto stage_piece = [&](const uint32_t p4) {
       if (p4 * 4u >= px_here) return;
       const uint32_t x = x0 + p4 * 4u - 8u;
+      const uint32_t sa = (uint32_t)__cvta_generic_to_shared(&sm.px[0][p4 * 16u]);
       const uint8_t *src;
       size_t pit;
       if (dir.groups) {
@@ -611,13 +682,42 @@ __global__ void __launch_bounds__(JM_MCUS, 4) jpeg_mcu_kernel(const uint8_t *can
         uint32_t si = si0;
         while (si + 1u < seg_end && __ldg(&dir.segs[si + 1u].x0) <= x) si++;
         const JmSeg sg = dir.segs[si];
+        const uint32_t x_end = si + 1u < seg_end ? __ldg(&dir.segs[si + 1u].x0) : g.width;   // where the tile's columns end
         pit = sg.pitch;
         src = sg.p + (size_t)(yf - grp.row0) * pit + (size_t)(x - sg.x0) * 4u;
+        if (yf + rows_here <= grp.row1 && x + 4u <= x_end && (((reinterpret_cast<uintptr_t>(src) | pit) & 15u) != 0u)) {
+          // one tile, but its rows are not 16-byte aligned here (an odd width or position): four 4-byte copies a row
+#pragma unroll
+          for (uint32_t k = 0; k < 8u; k++) {
+#pragma unroll
+            for (uint32_t j = 0; j < 4u; j++)
+              asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa + k * (uint32_t)(JM_PX * 4) + j * 4u), "l"(src + j * 4u) : "memory");
+            if (k + 1u < rows_here) src += pit;
+          }
+          return;
+        }
+        if (yf + rows_here > grp.row1 || x + 4u > x_end) {
+          // The general case, pixel by pixel: the MCU row crosses a tile edge (its rows belong to two groups), or the piece
+          // does (two tiles, or the canvas ends inside it).  Rare: tile edges.
+          uint32_t gk = gi;
+          JmGroup gr = grp;
+          for (uint32_t k = 0; k < 8u; k++) {
+            const uint32_t y = yf + min(k, rows_here - 1u);
+            while (y >= gr.row1) gr = dir.groups[++gk];
+            for (uint32_t j = 0; j < 4u && x + j < g.width; j++) {
+              uint32_t lo = 0, hi = gr.nseg;   // the group's tile at column x + j
+              while (hi - lo > 1u) { const uint32_t mid = (lo + hi) >> 1; if (__ldg(&dir.segs[gr.seg0 + mid].x0) <= x + j) lo = mid; else hi = mid; }
+              const JmSeg s1 = dir.segs[gr.seg0 + lo];
+              const uint8_t *s = s1.p + (size_t)(y - gr.row0) * s1.pitch + (size_t)(x + j - s1.x0) * 4u;
+              asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa + k * (uint32_t)(JM_PX * 4) + j * 4u), "l"(s) : "memory");
+            }
+          }
+          return;
+        }
       } else {
         pit = pitch;
         src = canvas + (size_t)(yf - g.y0) * pit + (size_t)x * 4u;
       }
-      const uint32_t sa = (uint32_t)__cvta_generic_to_shared(&sm.px[0][p4 * 16u]);
 #pragma unroll
       for (uint32_t k = 0; k < 8u; k++) {
         asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa + k * (uint32_t)(JM_PX * 4)), "l"(src) : "memory");
@@ -739,8 +839,23 @@ __global__ void __launch_bounds__(JM_MCUS, 4) jpeg_mcu_kernel(const uint8_t *can
       }
     }
     // lengths -> bit offsets inside the chunk
-    const uint32_t len = active ? b.wr * 32u + b.nacc : 0u;
-    const int too_long = __syncthreads_or(active && (b.ovf || len > (uint32_t)JM_WORDS * 32u));   // also: every thread is done with the pixels
+    uint32_t len = active ? b.wr * 32u + b.nacc : 0u;
+    const bool no_room = active && (b.ovf || len > (uint32_t)JM_WORDS * 32u);
+    const uint32_t *esc = nullptr;   // where this MCU's code is when it is not in its column
+    int hard = 0;
+    if (__syncthreads_or(no_room)) {   // rare.  The pixels are still staged: the threads concerned code their MCUs again, into HBM
+      if (no_room) {
+        const unsigned long long slot = atomicAdd(overflow + 1, 1ull);
+        if (slot < JM_ESC_SLOTS) {
+          uint32_t *e = esc_pool + slot * JM_ESC_WORDS;
+          len = jm_mcu_slow(sm, q, t, blockIdx.x != 0u || t != 0u, e);
+          esc = e;
+        } else {
+          hard = 1;
+        }
+      }
+      hard = __syncthreads_or(hard);
+    }
     uint32_t incl = len;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) { const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= (uint32_t)o) incl += v; }
@@ -750,7 +865,7 @@ __global__ void __launch_bounds__(JM_MCUS, 4) jpeg_mcu_kernel(const uint8_t *can
 #pragma unroll
     for (uint32_t k = 0; k < (uint32_t)JM_MCUS / 32u; k++) { const uint32_t w = sm.warp_tot[k]; if (k < warp) off += w; total += w; }
     const size_t ci = (size_t)mr * gridDim.x + blockIdx.x;
-    if (too_long || total > JM_CHUNK_BYTES * 8u) {   // uniform over the CTA
+    if (hard || total > JM_CHUNK_BYTES * 8u) {   // uniform over the CTA: the band goes to the other route
       if (t == 0u) { atomicOr(overflow, 1ull); chunk_bits[ci] = 0u; }
       continue;
     }
@@ -758,7 +873,7 @@ __global__ void __launch_bounds__(JM_MCUS, 4) jpeg_mcu_kernel(const uint8_t *can
     for (uint32_t i = t; i <= nw; i += JM_MCUS) cw[i] = 0u;
     __syncthreads();
     for (uint32_t j = 0; j * 32u < len; j++) {
-      const uint32_t w = sm.stage[j][t], p = off + j * 32u, sh = p & 31u;
+      const uint32_t w = esc ? esc[j] : sm.stage[j][t], p = off + j * 32u, sh = p & 31u;
       atomicOr(&cw[p >> 5], w >> sh);
       if (sh) atomicOr(&cw[(p >> 5) + 1u], w << (32u - sh));
     }
@@ -1039,13 +1154,14 @@ static int jpeg_direct_plan(stitch_job *job, uint32_t y0, uint32_t y1, JmDirect 
     const uint32_t ya = (uint32_t)d.dst_y, yb = ya + d.vis_h, xa = (uint32_t)d.dst_x, xb = xa + d.vis_w;
     if (yb <= y0 || ya >= y1) continue;
     if (d.color_type != 6 || d.bit_depth != 8 || t.has_pal || !t.d_pix) return STITCH_OK;
-    if ((reinterpret_cast<uintptr_t>(t.d_pix) & 15u) || (t.pitch & 15u) || ((d.src_off_x - xa) & 3u)) return STITCH_OK;   // 16-byte pieces
-    if ((ya & 7u) || ((yb & 7u) && yb != jd.canvas_h)) return STITCH_OK;   // an MCU row has one set of tiles
+    if ((reinterpret_cast<uintptr_t>(t.d_pix) & 3u) || (t.pitch & 3u)) return STITCH_OK;   // pixels are read as words (16 bytes at a time where the rows allow)
     rs.push_back({xa, xb, ya, yb, &t});
     if (ya > y0) cuts.push_back(ya);
     if (yb < y1) cuts.push_back(yb);
     if (rs.size() > 4096) return STITCH_OK;
   }
+  // (tiles whose rows are not 16-byte aligned come in by 4-byte copies: tools/jpeg_bench.py 1023 takes 2.45 ms from the
+  // tiles and 2.38 ms through the compositor's canvas, against 1.7 ms from aligned tiles -- no reason to prefer the canvas)
   std::sort(cuts.begin(), cuts.end());
   cuts.erase(std::unique(cuts.begin(), cuts.end()), cuts.end());
   if (cuts.size() * rs.size() > ((size_t)4 << 20)) return STITCH_OK;   // the loop below would cost more host time than the compositor saves
@@ -1125,7 +1241,8 @@ static int encode_band_one_pass(stitch_job *job, const JpegGeom &g, uint32_t fir
   }
   const size_t n_slots = (size_t)g.mrows * n_chunks;
   if ((rc = stitch_ensure_buffer(ctx, &job->d_jpeg[0], &job->jpeg_cap[0], n_slots * JM_CHUNK_BYTES + 16))) return rc;
-  if ((rc = stitch_ensure_buffer(ctx, &job->d_jpeg[1], &job->jpeg_cap[1], n_slots * 4))) return rc;
+  const size_t bits_bytes = (n_slots * 4 + 15) / 16 * 16;   // bits per chunk, then the slots of MCUs that did not fit their columns
+  if ((rc = stitch_ensure_buffer(ctx, &job->d_jpeg[1], &job->jpeg_cap[1], bits_bytes + (size_t)JM_ESC_SLOTS * JM_ESC_WORDS * 4))) return rc;
   const size_t rows_pad = ((size_t)g.mrows + 3) / 4 * 4;
   if ((rc = stitch_ensure_buffer(ctx, &job->d_jpeg[2], &job->jpeg_cap[2], rows_pad * 24 + 64))) return rc;
   if (!job->h_jpeg_totals) STITCH_CK(cudaHostAlloc((void **)&job->h_jpeg_totals, 32, cudaHostAllocDefault));
@@ -1137,11 +1254,12 @@ static int encode_band_one_pass(stitch_job *job, const JpegGeom &g, uint32_t fir
   uint32_t *row_ff = row_bits + rows_pad;
   unsigned long long *row_base = reinterpret_cast<unsigned long long *>(row_ff + rows_pad);
   unsigned long long *out_base = row_base + rows_pad;
-  unsigned long long *totals = out_base + rows_pad;   // [1] output bytes, [2] overflow flag
+  unsigned long long *totals = out_base + rows_pad;   // [1] output bytes, [2] overflow flag, [3] MCUs coded into the slots
   STITCH_CK(cudaMemsetAsync(totals, 0, 32, ctx->stream));
   {
     dim3 grid(n_chunks, g.mrows < 16384u ? g.mrows : 16384u);
-    jpeg_mcu_kernel<<<grid, JM_MCUS, sizeof(JmSmem), ctx->stream>>>(canvas, canvas_pitch, g, q, dir, chunk_words, chunk_bits, totals + 2);
+    jpeg_mcu_kernel<<<grid, JM_MCUS, sizeof(JmSmem), ctx->stream>>>(canvas, canvas_pitch, g, q, dir, chunk_words, chunk_bits,
+                                                                    reinterpret_cast<uint32_t *>(job->d_jpeg[1] + bits_bytes), totals + 2);
     STITCH_CK(cudaGetLastError());
   }
   const uint32_t row_grid = g.mrows < 148u * 8u ? g.mrows : 148u * 8u;
@@ -1149,9 +1267,12 @@ static int encode_band_one_pass(stitch_job *job, const JpegGeom &g, uint32_t fir
   STITCH_CK(cudaGetLastError());
   jpeg_rowscan_kernel<<<1, 1024, 0, ctx->stream>>>(row_bits, row_ff, g.mrows, first_mrow, total_mrows, 1, out_base, totals);
   STITCH_CK(cudaGetLastError());
-  STITCH_CK(cudaMemcpyAsync(job->h_jpeg_totals, totals, 24, cudaMemcpyDeviceToHost, ctx->stream));
+  STITCH_CK(cudaMemcpyAsync(job->h_jpeg_totals, totals, 32, cudaMemcpyDeviceToHost, ctx->stream));
   STITCH_CK(cudaStreamSynchronize(ctx->stream));  // the size of the band's bytes decides the size of the output buffer
   if (launches) *launches += 3;
+  if (getenv("STITCH_JPEG_DEBUG"))
+    fprintf(stderr, "[stitch jpeg] band of %u MCU rows x %u MCUs: %llu MCUs coded into slots, overflow %llu, %s\n", g.mrows, g.mcus,
+            job->h_jpeg_totals[3], job->h_jpeg_totals[2], dir.groups ? "tiles read in place" : "from a canvas");
   if (job->h_jpeg_totals[2]) { *overflow = true; return STITCH_OK; }
   const size_t n_out = (size_t)job->h_jpeg_totals[1];
   if ((rc = stitch_ensure_buffer(ctx, &job->d_out, &job->out_bytes, n_out + 64))) return rc;

@@ -112,10 +112,10 @@ def _mosaic_entropy(ctx, tiles, w, h, quality, bands):
     return out
 
 
-@pytest.mark.parametrize("layout", ["grid", "tall_and_short", "gap", "overlap", "odd_x", "ragged_bottom", "clipped"])
+@pytest.mark.parametrize("layout", ["grid", "tall_and_short", "gap", "overlap", "odd_x", "ragged_bottom", "clipped", "odd_y", "bricks"])
 def test_mosaics_read_in_place_or_through_a_canvas(ctx, monkeypatch, layout):
-    """An exact mosaic of RGBA8 tiles is coded straight from the tiles (no canvas); a gap, an overlap or a tile at an
-    odd column is not one and goes through the compositor.  Either way: the oracle's bytes, and the same bytes
+    """An exact mosaic of RGBA8 tiles is coded straight from the tiles (no canvas), 16 bytes at a time where the rows
+    allow and pixel by pixel at tile edges and odd sizes; a gap or an overlap goes through the compositor.  Either way: the oracle's bytes, and the same bytes
     with the in-place route switched off."""
     rng = np.random.default_rng(21)
     w, h = 2304, 96
@@ -131,6 +131,10 @@ def test_mosaics_read_in_place_or_through_a_canvas(ctx, monkeypatch, layout):
         tiles = [(t(1200, 96), 0, 0), (t(1152, 96), 1152, 0)]
     elif layout == "odd_x":
         tiles = [(t(1150, 96), 0, 0), (t(1154, 96), 1150, 0)]
+    elif layout == "odd_y":     # tile edges inside MCU rows
+        tiles = [(t(2304, 43), 0, 0), (t(1000, 53), 0, 43), (t(1304, 21), 1000, 43), (t(1304, 32), 1000, 64)]
+    elif layout == "bricks":    # odd sizes everywhere: edges inside MCU rows and inside 4-pixel pieces, unaligned rows
+        tiles = [(t(701, 37), 0, 0), (t(1603, 37), 701, 0), (t(1201, 59), 0, 37), (t(1103, 59), 1201, 37)]
     elif layout == "clipped":   # tiles larger than what shows of them (ClippedImageInfo.sourceOffsetX/Y), still an exact mosaic
         tiles = [(t(1200, 120), 0, 0, (16, 24, 1152, 96)), (t(1160, 96), 1152, 0, (8, 0, 1152, 96))]
     else:

@@ -1,10 +1,11 @@
-"""C5 shape: grid mosaic -> JPEG q=90 entropy bytes on the GPU (one 16384 x 16384 band per run), device timings."""
+"""C5 shape: grid mosaic -> JPEG q=90 entropy bytes on the GPU (one 16384 x 16384 band per run), device timings.
+python tools/jpeg_bench.py [tile]   (tile = 1023: rows that are not 16-byte aligned, tile edges inside MCU rows)"""
 import sys, os, time
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from image_stitch_b200 import _native, synth
 
-grid, tile = 16, 1024
+grid, tile = 16, (int(sys.argv[1]) if len(sys.argv) > 1 else 1024)
 canvas = grid * tile
 rng = np.random.default_rng(5)
 raws = [synth.smooth_rgba8(rng, tile, tile, "opaque") for _ in range(4)]
@@ -14,7 +15,7 @@ with _native.Job(ctx, canvas, canvas, 8, _native.OUT_JPEG_ENTROPY, False, bytes(
         for c in range(grid):
             job.add_tile(raws[(r * 5 + c * 3) % 4].reshape(-1), width=tile, height=tile, bit_depth=8, color_type=6,
                          filtered=0, dst_x=c * tile, dst_y=r * tile, image_idx=r * grid + c)
-    for rows in (canvas, 2048):
+    for rows in (canvas, 2048 // 8 * 8):
         best = None
         for _ in range(4):
             t0 = time.perf_counter()
