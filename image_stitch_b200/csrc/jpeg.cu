@@ -659,7 +659,12 @@ __global__ void __launch_bounds__(JM_MCUS, 4) jpeg_mcu_kernel(const uint8_t *can
   const bool warp_active = blockIdx.x * JM_MCUS + warp * 32u < g.mcus;
   uint32_t *cw = reinterpret_cast<uint32_t *>(&sm.px[0][0]);
   for (uint32_t mr = blockIdx.y; mr < g.mrows; mr += gridDim.y) {
-    __syncthreads();   // the previous chunk has left the buffer (and the tables are loaded)
+    // the previous chunk has left the buffer (and the tables are loaded); and once the band is lost to the other route
+    // (a chunk beyond its 8 KB, no slot left) the chunks not yet begun are not worth coding
+    if (__syncthreads_or(t == 0u && *reinterpret_cast<const volatile unsigned long long *>(overflow) != 0ull)) {
+      if (t == 0u) for (; mr < g.mrows; mr += gridDim.y) chunk_bits[(size_t)mr * gridDim.x + blockIdx.x] = 0u;   // the row kernels still run over the band
+      return;
+    }
     // Staging: a lane takes a 16-byte piece (4 pixels) of the chunk's span and copies its 8 rows; the 256 pieces of the
     // chunk are spread over the 4 warps (2 x 32 consecutive pieces each), the 2 pieces of the MCU on the left go to
     // two lanes of warp 0.  Rows past the bottom edge repeat the last image row.
