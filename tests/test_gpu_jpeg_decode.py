@@ -146,6 +146,17 @@ def test_public_api_with_jpeg_inputs():
     assert read_png(png)[1] == want.tobytes()
 
 
+def test_jpeg_files_in_jpeg_out():
+    """JPEG tiles decoded on the device and coded again as one JPEG (the MCU kernel reads the decoded tiles in place:
+    an exact mosaic of RGBA8 rows), against the two oracles chained."""
+    ins = [_file("c420_q80"), _file("c420_q80"), _file("c420_q80"), _file("c420_q80")]
+    opts = {"inputs": ins, "layout": {"columns": 2}, "output_format": "jpeg", "jpeg_quality": 88}
+    jpg = stitch.concat_to_buffer(opts)
+    plan, raw = H.oracle_stitch_rows(dict(opts, output_format="png"), out_kind=1)
+    w, h = plan.canvas_w, plan.canvas_h
+    assert jpg == orc.jpeg_file(np.frombuffer(raw, np.uint8).reshape(h, w * 4), w, h, 88)
+
+
 def test_decoder_plugin_contract():
     """JpegBufferDecoder: getHeader + scanlines (jpeg-decoder.ts:284-347) over the device decoder."""
     from image_stitch_b200.decoders import JpegBufferDecoder, detect_image_format
