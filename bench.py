@@ -490,10 +490,28 @@ def jpeg_decode_section(ctx):
         ms = ((t1 - t0) * 1e3, (t2 - t0) * 1e3, tm["compose_ms"])
         best = ms if best is None or ms[1] < best[1] else best
     px = grid * grid * tile * tile
+    # the same tiles to ONE JPEG (q = 90): decoded on the device, read in place by the encoder, entropy bytes downloaded
+    jj = None
+    host = None
+    for _ in range(4):
+        with _native.Job(ctx, tile * grid, tile * grid, 8, _native.OUT_JPEG_ENTROPY, False, bytes(4), jpeg_quality=90) as job:
+            t0 = time.perf_counter()
+            for k in range(grid * grid):
+                job.add_tile_jpeg(data, dst_x=(k % grid) * tile, dst_y=(k // grid) * tile, image_idx=k)
+            if host is None:
+                import torch
+                host = torch.empty(job.band_bytes(0, 8) * (tile * grid // 8) // 8 + (1 << 20), dtype=torch.uint8, pin_memory=True)
+            out, tm = job.run_band(0, tile * grid, out=host)
+            ms = (time.perf_counter() - t0) * 1e3
+        if jj is None or ms < jj[0]:
+            jj = (ms, int(len(out)), tm["compose_ms"])
     return {"workload": f"{grid * grid} JPEG tiles of {tile}x{tile} (4:2:0, q=85, {len(data)} bytes each, no restart markers) -> "
                         f"{tile * grid}x{tile * grid} filtered PNG scanlines",
             "queued_ms": best[0], "wall_ms": best[1], "composite_filter_ms": best[2], "value_MPix_s": px / 1e6 / (best[1] / 1e3),
             "h2d_bytes": len(data) * grid * grid, "libjpeg_turbo_one_core_ms_per_tile": cpu_ms,
+            "jpeg_to_jpeg": {"wall_ms": jj[0], "value_MPix_s": px / 1e6 / (jj[0] / 1e3), "d2h_bytes": jj[1], "encode_ms": jj[2],
+                             "note": "the same 16 files decoded on the device and coded again as one JPEG (q = 90, the decoded tiles read "
+                                     "in place by the MCU kernel), host buffers both ways"},
             "note": "wall clock around add_tile_jpeg x 16 + run_band (decode kernels are queued at add time on four streams); "
                     "byte-exact against libjpeg-turbo (tests/test_gpu_jpeg_decode.py)"}
 
