@@ -515,6 +515,7 @@ __global__ void __launch_bounds__(256) jpeg_stuff_kernel(const uint8_t *ubuf, co
 // at quality 100) raises a flag and the band is done again by the J1..J7 route above.
 static constexpr int JM_MCUS = 128;
 static constexpr int JM_WORDS = 40;                       // 1280 bits per MCU (20 per pixel); what four CTAs per SM leave room for
+static constexpr int JM_GAP = 3;                          // words between a block's first entry and the code before it (the pending word, the DC code, slack)
 static constexpr int JM_PX = JM_MCUS * 8 + 8;             // staged pixels per row: the MCU on the left, then the chunk's
 static constexpr uint32_t JM_CHUNK_BYTES = 8192;          // 8 bits per pixel on average over a chunk
 static constexpr uint32_t JM_CHUNK_WORDS = JM_CHUNK_BYTES / 4;
@@ -781,36 +782,41 @@ __global__ void __launch_bounds__(JM_MCUS, 4) jpeg_mcu_kernel(const uint8_t *can
         const uint32_t *dct = sm.hs.dc[cls], *act = sm.hs.ac[cls];
         const int qa0 = (int)__umulhi((uint32_t)abs(d[0]) + q.hr[cls][0].x, q.hr[cls][0].y);
         const int dcq = d[0] < 0 ? -qa0 : qa0;
-        // Quantise the 63 AC terms in straight-line code; the non-zero ones go, 16 bits each (magnitude, sign in
-        // bit 15), to the far end of the thread's column of code words, growing towards the code: entry e at word
-        // JM_WORDS - 1 - e / 2, half e & 1.  Their zig-zag positions stay in a 64-bit mask.
+        // Quantise the 63 AC terms in straight-line code; the non-zero ones go, 16 bits each, into the thread's column
+        // of code words a little above the code written so far, in zig-zag order upwards: entry e in half e & 1 of word
+        // first + e / 2.  The walk below reads them from the bottom while the code comes up behind it (a word of code
+        // may only be stored below the word of the next unread entry), so the entries' room is used twice.  Their
+        // zig-zag positions stay in a 64-bit mask.  Entries that find no room below the column's end are dropped and
+        // counted: the MCU is then coded again into a slot (jm_mcu_slow), like one whose code catches up with its entries.
         uint32_t nz_lo = 0, nz_hi = 0;
-        uint8_t *wp = colb + (JM_WORDS - 1) * JM_MCUS * 4;
-        int wstep = 2;
+        const uint32_t first = min(b.wr + (uint32_t)JM_GAP, (uint32_t)JM_WORDS);
+        const uint32_t col32 = (uint32_t)__cvta_generic_to_shared(colb);
+        const uint32_t wa_last = col32 + (JM_WORDS - 1) * JM_MCUS * 4 + 2;   // the column's last place: entries beyond it pile up there
+        uint32_t wa = min(col32 + first * (JM_MCUS * 4), wa_last), wstep = 2;
 #pragma unroll
         for (int k = 1; k < 64; k++) {
           const int c = d[zz_nat(k)];
           const uint2 hr = q.hr[cls][k];
           const uint32_t a = __umulhi((uint32_t)abs(c) + hr.x, hr.y);
           if (a != 0u) {
-            *reinterpret_cast<uint16_t *>(wp) = (uint16_t)(a ^ (uint32_t)(c >> 31));   // a, or ~a for a negative term: its magnitude bits as they are coded
-            wp += wstep;
-            wstep = -JM_MCUS * 4 - wstep;   // 2, -514, 2, ...
             if (k < 32) nz_lo |= 1u << k; else nz_hi |= 1u << (k - 32);
+            asm volatile("st.shared.u16 [%0], %1;" ::"r"(wa), "h"((uint16_t)(a ^ (uint32_t)(c >> 31))) : "memory");   // a, or ~a for a negative term: its magnitude bits as they are coded
+            wa = min(wa + wstep, wa_last);
+            wstep = JM_MCUS * 4 - wstep;   // 2, 510, 2, ...
           }
         }
-        // the entries must not have reached the code words written so far
         const uint32_t n_ent = (uint32_t)(__popc(nz_lo) + __popc(nz_hi));
-        if ((uint32_t)JM_WORDS - ((n_ent + 1u) >> 1) < b.wr) b.ovf = 1u;
+        if (n_ent > 2u * ((uint32_t)JM_WORDS - first)) b.ovf = 1u;   // entries without a place of their own
+        int pred = __shfl_up_sync(0xffffffffu, dcq, 1);
+        if (lane == 0u) pred = left_dc;
+        if (b.ovf) continue;   // the MCU will be coded again (and its entries may be incomplete): no walk
         {  // DC difference against the MCU on the left (0 at the start of the row: a restart interval)
-          int pred = __shfl_up_sync(0xffffffffu, dcq, 1);
-          if (lane == 0u) pred = left_dc;
           const int diff = dcq - pred;
           const uint32_t a = (uint32_t)abs(diff), s = 32u - (uint32_t)__clz((int)a), e = dct[s];
-          b.put((e >> 6) | ((a ^ (uint32_t)(diff >> 31)) & ((1u << s) - 1u)), e & 63u, (uint32_t)JM_WORDS - ((n_ent + 1u) >> 1));
+          b.put((e >> 6) | ((a ^ (uint32_t)(diff >> 31)) & ((1u << s) - 1u)), e & 63u, n_ent ? first : (uint32_t)JM_WORDS);
         }
         int prev = 0;
-        const uint8_t *rp = colb + (JM_WORDS - 1) * JM_MCUS * 4;
+        const uint8_t *rp = colb + first * (JM_MCUS * 4);
         int rstep = 2;
         uint32_t left = n_ent;
         // each lane walks ITS non-zero terms: zig-zag positions 1..31, then 32..63
@@ -823,7 +829,7 @@ __global__ void __launch_bounds__(JM_MCUS, 4) jpeg_mcu_kernel(const uint8_t *can
             mk &= mk - 1u;
             const uint32_t x = *reinterpret_cast<const uint16_t *>(rp);
             rp += rstep;
-            rstep = -JM_MCUS * 4 - rstep;
+            rstep = JM_MCUS * 4 - rstep;
             left--;
             const uint32_t lim = left ? (uint32_t)(rp - colb) / (JM_MCUS * 4u) : (uint32_t)JM_WORDS;   // the word of the next unread entry
             uint32_t run = (uint32_t)(k - 1 - prev);
