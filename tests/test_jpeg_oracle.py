@@ -82,6 +82,35 @@ def test_decodes_to_libjpeg_pixels(w, h, quality):
     assert np.array_equal(a, b), "oracle coefficients differ from libjpeg-turbo's"
 
 
+def _pil_scan(rgb, quality):
+    """libjpeg-turbo's own baseline encode of rgb (4:4:4, Annex K tables, a restart interval of one MCU row, which is the
+    oracle's framing): the entropy-coded bytes between the SOS header and EOI."""
+    buf = io.BytesIO()
+    try:
+        PIL.fromarray(rgb, "RGB").save(buf, "JPEG", quality=quality, subsampling=0, restart_marker_rows=1)
+    except TypeError:
+        pytest.skip("this Pillow has no restart_marker_rows")
+    d = buf.getvalue()
+    i = d.index(b"\xff\xda")
+    return d[i + 2 + int.from_bytes(d[i + 2:i + 4], "big"):-2]
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_entropy_bytes_are_libjpeg_turbos(seed):
+    """The strongest pin this box allows for kernel (d): with the oracle's framing (DRI = one MCU row) libjpeg-turbo's
+    encoder writes exactly the oracle's entropy-coded bytes -- colour transform, islow FDCT, quantiser rounding, edge
+    replication, Huffman coding, stuffing and RSTm numbering all included.  Random sizes, contents and qualities 1..100."""
+    rng = np.random.default_rng(100 + seed)
+    for _ in range(12):
+        w, h = int(rng.integers(1, 220)), int(rng.integers(1, 130))
+        quality = int(rng.choice([rng.integers(1, 101), 90, 100]))
+        y, x = np.mgrid[0:h, 0:w].astype(np.float64)
+        rgb = np.stack([np.clip(127 + 80 * np.sin(x / (5 + c)) * np.cos(y / (7 + c)) + rng.normal(0, rng.uniform(0, 25), (h, w)), 0, 255).astype(np.uint8)
+                        for c in range(3)], -1)
+        rgba = np.concatenate([rgb, np.full((h, w, 1), int(rng.integers(0, 256)), np.uint8)], -1).reshape(h, w * 4)
+        assert orc.jpeg_encode_rows(rgba, w, h, 0, h, quality) == _pil_scan(np.ascontiguousarray(rgb), quality), (w, h, quality)
+
+
 def test_structure_like_reference_tests():
     """tests/unit/jpeg-structure.test.ts:52-167: one SOI at 0, one EOI at the end, decodable, dims, red stays red."""
     w, h = 40, 23

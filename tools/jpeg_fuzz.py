@@ -1,13 +1,17 @@
 """Randomised parity run of the JPEG encoder against the oracle: random canvas sizes, qualities, contents (smooth,
 steps, patches of noise: MCUs that do not fit their columns), mosaics of randomly sized tiles (read in place or through
 the canvas), random band cuts.  python tools/jpeg_fuzz.py [seconds] [seed].  GPU box only."""
-import os, sys, time
+import io, os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
 import numpy as np
 import oracle_py as orc
 from image_stitch_b200 import _native
 from image_stitch_b200.jpeg_container import JpegBandSplicer
+try:
+    from PIL import Image as _pil
+except ImportError:
+    _pil = None
 
 rng = None
 ctx = None
@@ -82,6 +86,17 @@ def run(budget, seed, context=None):
         finally:
             job.close()
         want = orc.jpeg_encode_rows(canvas.reshape(h, w * 4), w, h, 0, h, q)
+        if n % 4 == 0 and _pil is not None:   # and libjpeg-turbo itself: its encoder, with the same framing, writes these very bytes
+            buf = io.BytesIO()
+            try:
+                _pil.fromarray(np.ascontiguousarray(canvas[..., :3]), "RGB").save(buf, "JPEG", quality=q, subsampling=0, restart_marker_rows=1)
+                d = buf.getvalue()
+                i = d.index(b"\xff\xda")
+                if d[i + 2 + int.from_bytes(d[i + 2:i + 4], "big"):-2] != want:
+                    print(f"ORACLE differs from libjpeg-turbo: w={w} h={h} q={q}")
+                    return -1
+            except (TypeError, OSError):
+                pass
         if got != want:
             print(f"MISMATCH: w={w} h={h} q={q} xs={xs} ys={ys} bands={bands} ({len(got)} vs {len(want)} bytes)")
             first = next((i for i in range(min(len(got), len(want))) if got[i] != want[i]), min(len(got), len(want)))
