@@ -454,7 +454,7 @@ def jpeg_section(ctx, dev, peak: float):
                              "frac": alg / (avg / 1e3) / 1e9 / peak,
                              "note": "one-pass route of csrc/jpeg.cu: the MCU kernel reads the tiles in place (an exact mosaic: no canvas), colour + FDCT + "
                                      "quantise + Huffman coding in registers and shared memory, then row info + stuffing; algorithmic = 4 B/px read + "
-                                     "entropy bytes written; the MCU kernel is bound by instruction issue (profiles/r2f_prof_jpeg.summary.csv), not by HBM"},
+                                     "entropy bytes written; the MCU kernel is bound by instruction issue (profiles/r2h_prof_jpeg.summary.csv), not by HBM"},
                 "through_canvas": {"avg_ms": float(np.mean(ms_canvas)), "value_MPix_s": px / 1e6 / (float(np.mean(ms_canvas)) / 1e3)},
                 "with_d2h_of_the_entropy_bytes_ms": d2h_ms})
     return res
