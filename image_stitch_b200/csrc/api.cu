@@ -21,6 +21,9 @@ static int fail(stitch_ctx *ctx, int code, const char *fmt, ...) {
   vsnprintf(buf, sizeof buf, fmt, ap);
   va_end(ap);
   if (ctx) ctx->err = buf;
+  // a failed runtime call leaves its code as the thread's "last error" until someone reads it: read it here, or the
+  // next call's cudaGetLastError() after its launches reports this failure as its own (found by tools/jpeg_corrupt_fuzz.py)
+  if (code == STITCH_E_CUDA || code == STITCH_E_NOMEM) cudaGetLastError();
   return code;
 }
 int stitch_fail(stitch_ctx *ctx, int code, const char *fmt, ...) {
@@ -30,6 +33,7 @@ int stitch_fail(stitch_ctx *ctx, int code, const char *fmt, ...) {
   vsnprintf(buf, sizeof buf, fmt, ap);
   va_end(ap);
   if (ctx) ctx->err = buf;
+  if (code == STITCH_E_CUDA || code == STITCH_E_NOMEM) cudaGetLastError();   // see fail()
   return code;
 }
 
@@ -439,7 +443,13 @@ static int add_tile_common(stitch_job *job, const stitch_tile_desc *tile, const 
     }
   }
   int rc = prepare_tile(ctx, job, t, (uint32_t)job->tiles.size());
-  if (rc) { free_tile(ctx, t); return rc; }
+  if (rc) {
+    // rows a kernel chain is still producing stay the caller's to free, on the chain's stream (it frees them when this
+    // call fails; freeing them here as well was a double free whose error surfaced in the NEXT call: tools/jpeg_corrupt_fuzz.py)
+    if (own_dev) t.src_external = true;
+    free_tile(ctx, t);
+    return rc;
+  }
   if (host && len) {
     cudaError_t e = cudaMemcpyAsync(z ? t.d_z : t.d_src, host, len, cudaMemcpyHostToDevice, ctx->up);
     if (e != cudaSuccess) { free_tile(ctx, t); return fail(ctx, STITCH_E_CUDA, "H2D failed: %s", cudaGetErrorString(e)); }
@@ -447,7 +457,7 @@ static int add_tile_common(stitch_job *job, const stitch_tile_desc *tile, const 
   if (!dev || z || own_dev) {  // also orders the allocation of an inflate target made on the upload stream
     cudaError_t e = cudaEventCreateWithFlags(&t.up_event, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventRecord(t.up_event, own_dev && produced_on ? produced_on : ctx->up);
-    if (e != cudaSuccess) { free_tile(ctx, t); return fail(ctx, STITCH_E_CUDA, "H2D failed: %s", cudaGetErrorString(e)); }
+    if (e != cudaSuccess) { if (own_dev) t.src_external = true; free_tile(ctx, t); return fail(ctx, STITCH_E_CUDA, "H2D failed: %s", cudaGetErrorString(e)); }
     t.up_waited = false;
   }
   job->tiles.push_back(std::move(t));
