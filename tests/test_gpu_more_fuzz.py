@@ -23,3 +23,8 @@ def test_random_jobs_through_the_public_api():
         warnings.simplefilter("ignore")   # clipped / invisible images are announced like the reference announces them
         n = api_fuzz.run(8.0, 42)
     assert n > 20, "mismatch against the oracle (see the output)" if n < 0 else f"only {n} jobs in 8 s"
+
+
+def test_damaged_zlib_streams_are_refused_like_zlib_refuses_them(ctx):
+    import inflate_corrupt_fuzz
+    assert inflate_corrupt_fuzz.run(5.0, 43, ctx) > 100
