@@ -525,7 +525,7 @@ static int check_inflate(stitch_ctx *ctx, stitch_job *job) {
     if (rc) break;
     const InfResult &r = job->h_infres[idx];
     const TileRec &t = job->tiles[idx];
-    if (r.status) {
+    if (r.status) {   // (even with every byte of the image out: the window in which the error was met may have made some of them)
       job->status = STITCH_E_INFLATE;
       rc = fail(ctx, STITCH_E_INFLATE, "Inflate error: %s", inflate_message(r.status));
     } else if (r.out_len < t.src_len) {

@@ -28,3 +28,8 @@ def test_random_jobs_through_the_public_api():
 def test_damaged_zlib_streams_are_refused_like_zlib_refuses_them(ctx):
     import inflate_corrupt_fuzz
     assert inflate_corrupt_fuzz.run(5.0, 43, ctx) > 100
+
+
+def test_damaged_png_inputs_raise_like_the_oracle_side():
+    import png_corrupt_fuzz
+    assert png_corrupt_fuzz.run(5.0, 44) > 100
