@@ -74,3 +74,42 @@ def test_marker_segment_variants(name, decoded):
             orc.jpeg_decode(data)
     else:
         assert np.array_equal(orc.jpeg_decode(data)[..., :3], decoded[same_as])
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_oracle_matches_libjpeg_turbo_on_random_files(seed):
+    """Where Pillow is at hand: random sizes, contents, qualities, subsamplings, optimised tables and restart intervals,
+    encoded AND decoded by libjpeg-turbo, against the oracle's pixels (the GPU suite runs the device decoder through the
+    same mill, tools/jpeg_decode_fuzz.py)."""
+    import io
+    Image = pytest.importorskip("PIL.Image")
+    rng = np.random.default_rng(300 + seed)
+    done = 0
+    for _ in range(40):
+        w, h = int(rng.integers(1, 260)), int(rng.integers(1, 200))
+        gray = rng.integers(0, 5) == 0
+        y, x = np.mgrid[0:h, 0:w].astype(np.float64)
+        chans = [np.clip(127 + rng.uniform(10, 100) * np.sin(x / rng.uniform(2, 40) + c) * np.cos(y / rng.uniform(2, 40))
+                         + rng.normal(0, rng.uniform(0, 30), (h, w)), 0, 255).astype(np.uint8) for c in range(1 if gray else 3)]
+        pic = chans[0] if gray else np.stack(chans, -1)
+        opts = dict(quality=int(rng.choice([rng.integers(1, 101), 75, 95, 100])))
+        if not gray:
+            opts["subsampling"] = int(rng.integers(0, 3))
+        if rng.integers(0, 3) == 0:
+            opts["optimize"] = True
+        r = rng.integers(0, 4)
+        if r == 1:
+            opts["restart_marker_blocks"] = int(rng.integers(1, 40))
+        elif r == 2:
+            opts["restart_marker_rows"] = int(rng.integers(1, 4))
+        buf = io.BytesIO()
+        try:
+            Image.fromarray(pic, "L" if gray else "RGB").save(buf, "JPEG", **opts)
+        except (TypeError, OSError):   # an older Pillow without restart_marker_*, or its encoder giving up on the option set
+            continue
+        data = buf.getvalue()
+        want = np.array(Image.open(io.BytesIO(data)))
+        got = orc.jpeg_decode(data)
+        assert np.array_equal(got if gray else got[..., :3], want), (w, h, gray, opts)
+        done += 1
+    assert done > 20
