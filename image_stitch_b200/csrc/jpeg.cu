@@ -503,16 +503,19 @@ __global__ void __launch_bounds__(256) jpeg_stuff_kernel(const uint8_t *ubuf, co
 // The one-pass route: colour, FDCT, quantisation AND Huffman coding in one kernel, with no coefficients in HBM.
 //
 //   M1 mcu      CTA = 128 MCUs of one MCU row ("chunk"), thread = one MCU.  The quantised coefficients never
-//               leave the registers: the unrolled zig-zag loop codes every non-zero one on the spot into the
-//               thread's bit accumulator, whose full words go to a private column of shared memory.  The MCU
-//               lengths are scanned across the CTA, the private words are shifted into place in a chunk buffer
-//               (the pixel staging area, dead by then) and the chunk goes to its fixed slot in HBM.
+//               leave the SM: the unrolled zig-zag loop keeps the non-zero ones, 16 bits each, in the thread's
+//               private column of shared memory, a short loop codes them into the thread's bit accumulator,
+//               whose full words come up the same column behind them.  The MCU lengths are scanned across the
+//               CTA, the private words are shifted into place in a chunk buffer (the pixel staging area, dead by
+//               then) and the chunk goes to its fixed slot in HBM.  An exact mosaic of RGBA8 tiles is read in
+//               place (jpeg_direct_plan), anything else from the composited canvas.
 //   M2 rowinfo  CTA = one MCU row: bit offsets of its chunks, size of the row segment, its 0xFF bytes
 //   J6 rowscan  final offsets (stuffing + RSTm), as on the other route
 //   M3 stuff    CTA = one MCU row: chunks funnelled together 32 bits at a time, stuffed, RSTm
 //
-// A thread holds JM_WORDS words of code for its MCU and a chunk JM_CHUNK_BYTES; content that needs more (noise
-// at quality 100) raises a flag and the band is done again by the J1..J7 route above.
+// A thread holds JM_WORDS words of code for its MCU; an MCU that needs more is coded again into a slot in HBM
+// (jm_mcu_slow).  A chunk holds JM_CHUNK_BYTES; a band with a chunk beyond that, or with more MCUs in slots than
+// there are slots (noise at quality 95 and up), raises a flag and is done again by the J1..J7 route above.
 static constexpr int JM_MCUS = 128;
 static constexpr int JM_WORDS = 40;                       // 1280 bits per MCU (20 per pixel); what four CTAs per SM leave room for
 static constexpr int JM_GAP = 3;                          // words between a block's first entry and the code before it (the pending word, the DC code, slack)
